@@ -1,0 +1,92 @@
+"""TEST INFRASTRUCTURE ONLY — CPU restatement of `kSpider cluster`
+(pykSpider/kSpider2/ks_clustering.py:22-137,150-163).
+
+Parity status: "parity unpinned" for the connected-components step — the reference calls
+rustworkx.connected_components (third-party Rust module, listed unpinned in setup.py:203-210, not
+vendored, not installed here) and none of the reference's tests touch clustering.  This
+restatement follows the Python control flow line by line and substitutes
+scipy.sparse.csgraph.connected_components for the rustworkx call; connected components of an
+undirected graph are unique as a PARTITION, which is what is compared.  The threshold arithmetic
+(text -> Python float -> *100 -> `<`) is plain Python and is followed exactly.
+
+Deliberately NOT restated (reference defect): ks_clustering.py:107-113 drops
+the current edge whenever a 10 M-edge batch fills up; which edge is lost depends on the hash-map
+row order of the TSV, so it is not reproducible.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Tuple
+
+import numpy as np
+from scipy.sparse import coo_matrix
+from scipy.sparse.csgraph import connected_components
+
+DISTANCE_TO_COL = {"min_cont": 3, "avg_cont": 4, "max_cont": 5, "ani": 6}  # ks_clustering.py:12-17
+
+
+def load_names_map(path: str) -> Dict[int, str]:
+    """ks_clustering.py:56-61 — skip the count header, `int(id) -> name`, dict keeps file order."""
+    names: Dict[int, str] = {}
+    with open(path) as f:
+        next(f)
+        for row in f:
+            row = row.strip().split()
+            names[int(row[0])] = row[1]
+    return names
+
+
+def edges_from_tsv(pairwise_tsv: str, dist_col: int, cutoff01: float) -> List[Tuple[int, int]]:
+    """ks_clustering.py:97-105,157 — cut_off_threshold = float(cutoff)*100 ;
+    distance = float(text)*100 ; the row is skipped iff distance < cut_off_threshold
+    (so NaN distances are KEPT)."""
+    cut = float(cutoff01) * 100
+    edges = []
+    with open(pairwise_tsv) as f:
+        next(f)
+        for row in f:
+            row = row.strip().split("\t")
+            seq1 = int(row[0]) - 1
+            seq2 = int(row[1]) - 1
+            distance = float(row[dist_col]) * 100
+            if distance < cut:
+                continue
+            edges.append((seq1, seq2))
+    return edges
+
+
+def components(n_nodes: int, edges: List[Tuple[int, int]]) -> np.ndarray:
+    """Stand-in for rx.connected_components (ks_clustering.py:120): label per node index."""
+    if edges:
+        e = np.asarray(edges, dtype=np.int64)
+        g = coo_matrix((np.ones(len(e), dtype=np.int8), (e[:, 0], e[:, 1])), shape=(n_nodes, n_nodes))
+    else:
+        g = coo_matrix((n_nodes, n_nodes), dtype=np.int8)
+    _, labels = connected_components(g, directed=False)
+    return labels
+
+
+def cluster(index_prefix: str, cutoff01: float, dist_type: str = "max_cont") -> List[List[str]]:
+    """Whole command: returns the partition as sorted lists of names (canonical form: members
+    sorted, clusters sorted) — line/member order in the reference's file is rustworkx-internal."""
+    names = load_names_map(index_prefix + ".namesMap")
+    node_ids = list(names.keys())  # node index = position in file (ks_clustering.py:45-47)
+    edges = edges_from_tsv(index_prefix + "_kSpider_pairwise.tsv", DISTANCE_TO_COL[dist_type], cutoff01)
+    labels = components(len(node_ids), edges)
+    groups: Dict[int, List[str]] = {}
+    for node, lab in enumerate(labels):
+        groups.setdefault(int(lab), []).append(names[node + 1])  # names_map[node + 1] (:135)
+    return canonical(list(groups.values()))
+
+
+def canonical(clusters: List[List[str]]) -> List[List[str]]:
+    return sorted(sorted(c) for c in clusters)
+
+
+def read_clusters_file(path: str) -> List[List[str]]:
+    with open(path) as f:
+        return canonical([line.rstrip("\n").split(",") for line in f if line.rstrip("\n")])
+
+
+def output_name(index_prefix: str, cutoff01: float) -> str:
+    """ks_clustering.py:31-32,157 — f"_kSpider_clusters_{float(cutoff)*100}%.tsv"."""
+    return index_prefix + f"_kSpider_clusters_{float(cutoff01) * 100}%.tsv"
