@@ -1,0 +1,191 @@
+/*
+ * kspider_b200.h — C-ABI of libkspider_b200.so: the B200-native replacement of kSpider's pairwise
+ * hot path (dib-lab/kSpider @ 466a267).
+ *
+ * Everything the reference does between "read the three index files" and "write the pairwise TSV /
+ * cluster file" sits behind these entry points.  Plain pointers and sizes only; no exceptions cross
+ * the boundary; every function returns 0 (KSB_OK) or a negative error code and leaves a message
+ * retrievable with ksb_last_error() (thread-local).  The library owns every buffer it hands out
+ * until the matching ksb_*_free.
+ *
+ * Reference interface each entry point replaces (file:line in /root/reference):
+ *   ksb_index_load            load_colors_to_sources + load_colors_count + totals load
+ *                             (src/pairwise.cpp:95-121,125-137,166-170)
+ *   ksb_index_from_csr        the state after src/pairwise.cpp:194 (vec_color_to_ids, colorsCount,
+ *                             groupID_to_kmerCount) handed over directly instead of through files
+ *   ksb_write_seq_to_kmers    src/pairwise.cpp:173-180
+ *   ksb_pairwise              the OpenMP pair loop + PAIRS_COUNTER accumulation
+ *                             (src/pairwise.cpp:191-237, Combo :39-70) and the per-edge containment
+ *                             math of the writer loop (src/pairwise.cpp:253-264)
+ *   ksb_upload/ksb_accumulate/ksb_postpass   the same, split so the accumulation can be timed with
+ *                             inputs already resident in HBM
+ *   ksb_write_tsv             src/pairwise.cpp:242-275 (header, column order, ostream<<float text)
+ *   ksb_cluster               pykSpider/kSpider2/ks_clustering.py:63-120 (threshold on the printed
+ *                             containment text, graph build, rx.connected_components)
+ *   kSpider::pairwise(std::string,int)  (C++ symbol exported by the same library; declared in
+ *                             kspider_b200/csrc/kspider_dropin.hpp) include/kSpider.hpp:11
+ *
+ * There is NO CPU fallback: every compute entry point fails with KSB_ERR_CUDA when no sm_100
+ * device is usable.
+ */
+#ifndef KSPIDER_B200_H
+#define KSPIDER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KSB_OK 0
+#define KSB_ERR_IO (-1)       /* file missing / unreadable / short */
+#define KSB_ERR_FORMAT (-2)   /* not a phmap dump of the expected shape, or reference assert would fire */
+#define KSB_ERR_NOMEM (-3)
+#define KSB_ERR_CUDA (-4)     /* no device, launch or runtime failure */
+#define KSB_ERR_ARG (-5)
+#define KSB_ERR_BUDGET (-6)   /* owned triangle block does not fit the dense budget and spill is disabled */
+
+#define KSB_ABI_VERSION 1
+
+typedef struct ksb_index ksb_index;    /* host side: parsed, sample-compacted, size-binned CSR (pinned) */
+typedef struct ksb_device ksb_device;  /* one GPU: resident CSR + owned triangle block */
+typedef struct ksb_result ksb_result;  /* records / edges / labels of one run */
+
+/* Shape of a loaded index.  U = sum over multi-member colours of s(s-1)/2 = weighted pair-updates. */
+typedef struct ksb_index_info {
+    uint64_t n_samples;        /* N: distinct sample ids in totals U members */
+    uint64_t n_colors_file;    /* records in _color_to_sources.bin after u32-key de-duplication */
+    uint64_t n_colors;         /* C: colours with >= 2 members */
+    uint64_t n_members;        /* M: members of those colours */
+    uint64_t n_updates;        /* U */
+    uint64_t n_small_colors;   /* 2 <= s <= 64  (flat pair-space kernel) */
+    uint64_t n_mid_colors;     /* s > 64        (shared-memory tiled kernel) */
+    uint64_t n_zero_colors;    /* multi-member colours whose narrowed count is 0 (touched-with-zero rows) */
+    uint64_t max_color_size;
+    uint64_t payload_bytes;    /* size of the binned CSR blob (what H2D / NCCL broadcast moves) */
+    uint64_t triangle_cells;   /* N(N-1)/2 */
+    uint32_t pinned;           /* 1 if the payload lives in cudaMallocHost memory */
+    uint32_t reserved;
+} ksb_index_info;
+
+typedef struct ksb_opts {
+    int32_t device;              /* CUDA ordinal; -1 = current device */
+    int32_t rank;                /* this process owns row block `rank` of `world` (balanced by updates) */
+    int32_t world;               /* 0 or 1 = whole triangle */
+    int32_t want_records;        /* 1: build the {i,j,shared,min,avg,max} records and bring them to the host */
+    uint64_t dense_budget_bytes; /* 0 = library default (80% of free HBM) */
+    uint64_t reserved[4];
+} ksb_opts;
+
+/* One TSV row before formatting: 32 bytes, ids are the ORIGINAL sample ids of the index files. */
+typedef struct ksb_record {
+    uint32_t source_1;
+    uint32_t source_2;
+    uint64_t shared_kmers;
+    float min_containment;
+    float avg_containment;
+    float max_containment;
+    uint32_t pad;
+} ksb_record;
+
+typedef struct ksb_timings {
+    float h2d_ms;         /* CSR blob host->device */
+    float zero_ms;        /* clearing the owned triangle block */
+    float small_ms;       /* K1 flat pair-space kernel (2 <= s <= 64) */
+    float mid_ms;         /* K2 tiled kernel (s > 64) */
+    float zero_touch_ms;  /* touched-bitmap pass for zero-weight colours */
+    float accumulate_ms;  /* zero + small + mid + zero_touch measured as one interval */
+    float post_ms;        /* K5 count + compact */
+    float d2h_ms;         /* records device->host */
+    float cluster_ms;     /* K6 + K7 */
+    float reserved[7];
+} ksb_timings;
+
+typedef struct ksb_result_info {
+    uint64_t n_rows;          /* R: touched pairs in the owned row block */
+    uint64_t n_updates;       /* updates applied by this device (its row block) */
+    uint64_t row_begin;       /* owned rows [row_begin,row_end) in compact sample index space */
+    uint64_t row_end;
+    uint64_t owned_cells;
+    uint64_t gpu_launches;    /* kernels launched by the library for this result so far */
+    ksb_timings t;
+} ksb_result_info;
+
+const char* ksb_last_error(void);
+int ksb_abi_version(void);
+/* 0 if a usable sm_100 device exists, KSB_ERR_CUDA otherwise (message says why). */
+int ksb_cuda_available(void);
+
+/* ---- host: index ------------------------------------------------------------------------- */
+int ksb_index_load(const char* index_prefix, int host_threads, ksb_index** out);
+/* members need not be sorted; sample ids are arbitrary u32; colours with < 2 members are ignored. */
+int ksb_index_from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members,
+                       const uint32_t* weights, uint64_t n_totals, const uint32_t* total_ids,
+                       const uint32_t* total_vals, int host_threads, ksb_index** out);
+int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info);
+/* compact index -> original sample id (ascending), and per-sample totals in the same order */
+const uint32_t* ksb_index_sample_ids(const ksb_index* ix);
+const uint32_t* ksb_index_totals(const ksb_index* ix);
+/* the binned CSR blob + its fixed-size descriptor: what another rank needs to adopt the index */
+const void* ksb_index_payload(const ksb_index* ix, uint64_t* bytes);
+const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes);
+int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path);
+void ksb_index_free(ksb_index* ix);
+
+/* ---- device: resident CSR + accumulation ---------------------------------------------------- */
+/* Copies the blob to the device (timed: t.h2d_ms) and allocates the owned triangle block. */
+int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out);
+/* Adopts a blob that is ALREADY in device memory (e.g. received by an NCCL broadcast).  The
+ * descriptor is host memory.  The device buffer must outlive the ksb_device. */
+int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, const void* d_payload,
+                             uint64_t payload_bytes, const ksb_opts* opts, ksb_device** out);
+/* Clears the owned block and runs the pair-emission kernels on `stream` (a cudaStream_t passed as
+ * void*; NULL = the library's own stream).  Returns after enqueueing unless sync != 0. */
+int ksb_accumulate(ksb_device* dev, void* stream, int sync);
+/* device pointer of the owned block of the packed upper triangle (u64 cells) */
+void* ksb_device_triangle(const ksb_device* dev, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end);
+/* K5: containment + record compaction (rows sorted by (i,j)); records land on the host if want_records */
+int ksb_postpass(ksb_device* dev, int want_records, ksb_result** out);
+void ksb_device_free(ksb_device* dev);
+
+/* upload + accumulate + postpass in one call (the end-to-end path) */
+int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out);
+
+/* ---- results ---------------------------------------------------------------------------------- */
+int ksb_result_get_info(const ksb_result* r, ksb_result_info* info);
+const ksb_record* ksb_result_records(const ksb_result* r, uint64_t* n_rows);
+int ksb_write_tsv(const ksb_result* r, const char* path, int host_threads);
+/* Appends rows of further results (other row blocks) to an existing TSV without a header. */
+int ksb_append_tsv(const ksb_result* r, const char* path, int host_threads);
+/* K6+K7: threshold column dist_col (3=min,4=avg,5=max) at cutoff01 with the reference's text
+ * semantics, union-find over the kept edges.  labels_out[N]: label = smallest compact sample index of
+ * the component.  parent_inout (optional, N entries, device-independent host buffer) lets several row
+ * blocks be merged: pass the labels of the previous block in, get the merged labels out. */
+int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* labels_out,
+                uint64_t* n_edges);
+int ksb_cluster_merge(uint64_t n, const uint32_t* labels_a, const uint32_t* labels_b, uint32_t* labels_out);
+/* smallest float32 c such that the reference keeps an edge whose printed containment is c
+ * (strtod("%g" of c) * 100 >= cutoff01 * 100); exposed for tests */
+float ksb_threshold_float(double cutoff01);
+void ksb_result_free(ksb_result* r);
+
+/* ---- text ---------------------------------------------------------------------------------- */
+/* ostream<<float of the reference = "%g": writes at most 16 bytes, returns length (no NUL). */
+int ksb_format_float(float v, char* buf);
+
+/* ---- synthetic index files (bench / tests): real phmap dump bytes ------------------------- */
+int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uint64_t* color_ids,
+                          const uint64_t* offsets, const uint32_t* members, uint64_t n_counts,
+                          const uint64_t* count_ids, const uint64_t* count_vals, uint64_t n_totals,
+                          const uint32_t* total_ids, const uint32_t* total_vals);
+
+/* ---- micro-benchmarks used by bench.py to measure the red/atomic roofline in-run ---------- */
+/* n_ops random (pattern 0) / warp-contiguous (pattern 1) red.global.add.{u64,u32} into a buffer of
+ * `cells` cells; returns the best-of-`reps` milliseconds. */
+int ksb_bench_red(uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, int reps, float* best_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KSPIDER_B200_H */

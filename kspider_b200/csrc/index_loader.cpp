@@ -1,0 +1,556 @@
+// Host loader: the reference's three index files (or an in-memory CSR) -> sample-compacted,
+// member-sorted, size-binned CSR blob in pinned memory.
+//
+// Replaces, with identical observable semantics, the load phase of kSpider::pairwise:
+//   load_colors_to_sources  src/pairwise.cpp:95-111  (colour id narrowed u64->u32, insert_or_assign:
+//                                                    the LAST record with a given narrowed id wins)
+//   load_colors_count       src/pairwise.cpp:113-121 (key AND value narrowed to u32, slot order,
+//                                                    last wins; assert(size) must hold)
+//   totals load             src/pairwise.cpp:166-170 (flat_hash_map<u32,u32>; assert(size))
+//   colorsCount[colour]     src/pairwise.cpp:221     (missing colour -> weight 0)
+// The per-colour work the reference does inside its hot loop that depends only on the index
+// (ascending(), Combo enumeration order) is folded in here: members are sorted once.
+#include <algorithm>
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <numeric>
+#include <thread>
+
+#include <cuda_runtime_api.h>
+
+#include "ksb_common.hpp"
+#include "phmap_format.hpp"
+
+namespace ksb {
+
+static thread_local std::string g_err;
+
+void set_error(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+}
+const char* last_error() { return g_err.c_str(); }
+
+void parallel_chunks(uint64_t n, int threads, const std::function<void(int, uint64_t, uint64_t)>& fn) {
+    if (threads < 1) threads = 1;
+    if ((uint64_t)threads > n) threads = n ? (int)n : 1;
+    if (threads == 1) { fn(0, 0, n); return; }
+    std::vector<std::thread> pool;
+    pool.reserve(threads);
+    for (int t = 0; t < threads; t++) {
+        const uint64_t b = n * (uint64_t)t / (uint64_t)threads, e = n * (uint64_t)(t + 1) / (uint64_t)threads;
+        pool.emplace_back(fn, t, b, e);
+    }
+    for (auto& th : pool) th.join();
+}
+
+// u32 id -> u32 value lookup; direct array when ids are small, open addressing otherwise.
+class IdTable {
+public:
+    void init(uint64_t n_expected, uint32_t max_id) {
+        dense_ = (uint64_t)max_id + 1 <= std::max<uint64_t>(n_expected * 8, 1u << 20);
+        if (dense_) {
+            val_.assign((uint64_t)max_id + 1, 0);
+            used_.assign((uint64_t)max_id + 1, 0);
+        } else {
+            uint64_t cap = 64;
+            while (cap < n_expected * 2 + 2) cap <<= 1;
+            mask_ = cap - 1;
+            key_.assign(cap, 0);
+            val_.assign(cap, 0);
+            used_.assign(cap, 0);
+        }
+    }
+    // insert_or_assign; returns true if the key was already present
+    bool put(uint32_t k, uint32_t v) {
+        const uint64_t s = slot(k);
+        const bool had = used_[s];
+        used_[s] = 1;
+        if (!dense_) key_[s] = k;
+        val_[s] = v;
+        return had;
+    }
+    bool get(uint32_t k, uint32_t* v) const {
+        if (dense_) {
+            if (k >= val_.size() || !used_[k]) return false;
+            *v = val_[k];
+            return true;
+        }
+        uint64_t h = mix(k) & mask_;
+        while (used_[h]) {
+            if (key_[h] == k) { *v = val_[h]; return true; }
+            h = (h + 1) & mask_;
+        }
+        return false;
+    }
+private:
+    static uint64_t mix(uint64_t x) { x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; return x; }
+    uint64_t slot(uint32_t k) const {
+        if (dense_) return k;
+        uint64_t h = mix(k) & mask_;
+        while (used_[h] && key_[h] != k) h = (h + 1) & mask_;
+        return h;
+    }
+    bool dense_ = true;
+    uint64_t mask_ = 0;
+    std::vector<uint32_t> key_, val_;
+    std::vector<uint8_t> used_;
+};
+
+static inline uint64_t align256(uint64_t x) { return (x + 255) & ~255ULL; }
+
+// Intermediate form shared by both front ends: every colour of the file / input, members sorted
+// ascending and de-duplicated (ORIGINAL sample ids), weight already narrowed.
+struct RawIndex {
+    std::vector<uint64_t> off;      // [C+1]
+    std::vector<uint32_t> members;  // [M]
+    std::vector<uint32_t> weights;  // [C]
+    std::vector<uint32_t> total_ids, total_vals;  // slot / input order
+    uint64_t n_colors_file = 0;
+};
+
+static int build_index(RawIndex& raw, int threads, ksb_index** out) {
+    std::unique_ptr<ksb_index> ix(new ksb_index());
+    IndexDesc& d = ix->desc;
+    std::memset(&d, 0, sizeof d);
+    d.magic = kIndexMagic;
+    d.n_colors_file = raw.n_colors_file;
+    const uint64_t C = raw.weights.size();
+
+    // ---- sample compaction: ascending original id -> 0..N-1 (order preserving)
+    uint32_t max_id = 0;
+    for (uint32_t v : raw.total_ids) max_id = std::max(max_id, v);
+    {
+        std::vector<uint32_t> tmax(threads > 0 ? threads : 1, 0);
+        parallel_chunks(raw.members.size(), threads, [&](int t, uint64_t b, uint64_t e) {
+            uint32_t m = 0;
+            for (uint64_t i = b; i < e; i++) m = std::max(m, raw.members[i]);
+            tmax[t] = m;
+        });
+        for (uint32_t v : tmax) max_id = std::max(max_id, v);
+    }
+    std::vector<uint32_t> sample_ids;
+    std::vector<uint32_t> remap;  // dense path: original id -> compact
+    const bool dense_ids = (uint64_t)max_id + 1 <= (1ull << 28);
+    if (dense_ids) {
+        std::vector<uint8_t> present((uint64_t)max_id + 1, 0);
+        for (uint32_t v : raw.total_ids) present[v] = 1;
+        parallel_chunks(raw.members.size(), threads, [&](int, uint64_t b, uint64_t e) {
+            for (uint64_t i = b; i < e; i++) present[raw.members[i]] = 1;  // benign same-value race
+        });
+        remap.assign((uint64_t)max_id + 1, 0);
+        for (uint64_t v = 0; v <= max_id; v++)
+            if (present[v]) { remap[v] = (uint32_t)sample_ids.size(); sample_ids.push_back((uint32_t)v); }
+    } else {
+        sample_ids = raw.members;
+        sample_ids.insert(sample_ids.end(), raw.total_ids.begin(), raw.total_ids.end());
+        std::sort(sample_ids.begin(), sample_ids.end());
+        sample_ids.erase(std::unique(sample_ids.begin(), sample_ids.end()), sample_ids.end());
+    }
+    const uint64_t N = sample_ids.size();
+    auto compact = [&](uint32_t id) -> uint32_t {
+        if (dense_ids) return remap[id];
+        return (uint32_t)(std::lower_bound(sample_ids.begin(), sample_ids.end(), id) - sample_ids.begin());
+    };
+    d.n_samples = N;
+
+    // ---- classify colours; per-chunk class counts so the fill can run in parallel, in input order
+    const int T = std::max(1, threads);
+    const uint32_t K_MID = kSmallMax + 1, K_ZERO = kSmallMax + 2, K_N = kSmallMax + 3;
+    std::vector<std::vector<uint64_t>> cnt(T, std::vector<uint64_t>(K_N, 0));      // colours per class
+    std::vector<std::vector<uint64_t>> mcnt(T, std::vector<uint64_t>(K_N, 0));     // members per class
+    std::vector<uint64_t> chunk_b(T + 1, C);
+    auto klass = [&](uint64_t c) -> uint32_t {
+        const uint64_t s = raw.off[c + 1] - raw.off[c];
+        if (s < 2) return 0;
+        if (raw.weights[c] == 0) return K_ZERO;
+        return s <= kSmallMax ? (uint32_t)s : K_MID;
+    };
+    parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+        chunk_b[t] = b;
+        for (uint64_t c = b; c < e; c++) {
+            const uint32_t k = klass(c);
+            if (!k) continue;
+            cnt[t][k]++;
+            mcnt[t][k] += raw.off[c + 1] - raw.off[c];
+        }
+    });
+    std::vector<uint64_t> tot(K_N, 0), mtot(K_N, 0);
+    std::vector<std::vector<uint64_t>> base(T, std::vector<uint64_t>(K_N, 0)), mbase(T, std::vector<uint64_t>(K_N, 0));
+    for (uint32_t k = 0; k < K_N; k++)
+        for (int t = 0; t < T; t++) {
+            base[t][k] = tot[k]; mbase[t][k] = mtot[k];
+            tot[k] += cnt[t][k]; mtot[k] += mcnt[t][k];
+        }
+    uint64_t moff = 0, woff = 0;
+    for (uint32_t s = 2; s <= kSmallMax; s++) {
+        SmallClass& sc = d.cls[s];
+        sc.s = s;
+        sc.pairs = s * (s - 1) / 2;
+        sc.magic = (uint32_t)(((1ull << 32) + sc.pairs - 1) / sc.pairs);
+        sc.n = tot[s];
+        sc.member_off = moff;
+        sc.weight_off = woff;
+        moff += tot[s] * s;
+        woff += tot[s];
+        d.n_updates += tot[s] * sc.pairs;
+    }
+    d.n_small_colors = woff;
+    d.n_small_members = moff;
+    d.n_mid_colors = tot[K_MID];
+    d.n_mid_members = mtot[K_MID];
+    d.n_zero_colors = tot[K_ZERO];
+    d.n_zero_members = mtot[K_ZERO];
+    d.n_colors = d.n_small_colors + d.n_mid_colors + d.n_zero_colors;
+    d.n_members = d.n_small_members + d.n_mid_members + d.n_zero_members;
+
+    // ---- payload layout
+    uint64_t p = 0;
+    auto section = [&](uint64_t bytes) { const uint64_t o = p; p = align256(p + bytes); return o; };
+    d.off_totals = section(4 * N);
+    d.off_sample_ids = section(4 * N);
+    d.off_row_updates = section(8 * N);
+    d.off_small_members = section(4 * d.n_small_members);
+    d.off_small_weights = section(4 * d.n_small_colors);
+    d.off_mid_offsets = section(8 * (d.n_mid_colors + 1));
+    d.off_mid_members = section(4 * d.n_mid_members);
+    d.off_mid_weights = section(4 * d.n_mid_colors);
+    d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
+    d.off_zero_members = section(4 * d.n_zero_members);
+    d.payload_bytes = std::max<uint64_t>(p, 256);
+
+    void* mem = nullptr;
+    if (cudaMallocHost(&mem, d.payload_bytes) == cudaSuccess) {
+        ix->pinned = true;
+    } else {
+        (void)cudaGetLastError();  // no device / no driver: plain memory is fine for host-only use
+        if (posix_memalign(&mem, 4096, d.payload_bytes) != 0) { set_error("out of host memory (%llu bytes)", (unsigned long long)d.payload_bytes); return KSB_ERR_NOMEM; }
+        ix->pinned = false;
+    }
+    ix->payload = static_cast<uint8_t*>(mem);
+    std::memset(ix->payload, 0, d.payload_bytes);
+    uint8_t* P = ix->payload;
+    uint32_t* totals = reinterpret_cast<uint32_t*>(P + d.off_totals);
+    uint32_t* sids = reinterpret_cast<uint32_t*>(P + d.off_sample_ids);
+    uint64_t* row_updates = reinterpret_cast<uint64_t*>(P + d.off_row_updates);
+    uint32_t* small_m = reinterpret_cast<uint32_t*>(P + d.off_small_members);
+    uint32_t* small_w = reinterpret_cast<uint32_t*>(P + d.off_small_weights);
+    uint64_t* mid_off = reinterpret_cast<uint64_t*>(P + d.off_mid_offsets);
+    uint32_t* mid_m = reinterpret_cast<uint32_t*>(P + d.off_mid_members);
+    uint32_t* mid_w = reinterpret_cast<uint32_t*>(P + d.off_mid_weights);
+    uint64_t* zero_off = reinterpret_cast<uint64_t*>(P + d.off_zero_offsets);
+    uint32_t* zero_m = reinterpret_cast<uint32_t*>(P + d.off_zero_members);
+
+    std::copy(sample_ids.begin(), sample_ids.end(), sids);
+    // groupID_to_kmerCount[id]: a map, so one value per id; missing -> 0 (operator[] default)
+    for (size_t i = 0; i < raw.total_ids.size(); i++) totals[compact(raw.total_ids[i])] = raw.total_vals[i];
+
+    // ---- fill (parallel, deterministic placement = input order within each class)
+    std::vector<std::vector<uint64_t>> t_rows(T), t_rowsum(T);
+    std::vector<uint64_t> t_maxs(T, 0), t_mid_updates(T, 0);
+    parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+        std::vector<uint64_t>& rows = t_rows[t];
+        std::vector<uint64_t>& rowsum = t_rowsum[t];
+        rows.assign(N, 0);
+        rowsum.assign(N, 0);
+        std::vector<uint64_t> at = base[t], mat = mbase[t];
+        uint64_t maxs = 0, midu = 0;
+        for (uint64_t c = b; c < e; c++) {
+            const uint32_t k = klass(c);
+            if (!k) continue;
+            const uint64_t s = raw.off[c + 1] - raw.off[c];
+            const uint32_t* src = &raw.members[raw.off[c]];
+            const uint32_t w = raw.weights[c];
+            uint32_t* dst;
+            if (k == K_MID) {
+                dst = mid_m + mat[k];
+                mid_off[at[k]] = mat[k];
+                mid_w[at[k]] = w;
+                midu += s * (s - 1) / 2;
+            } else if (k == K_ZERO) {
+                dst = zero_m + mat[k];
+                zero_off[at[k]] = mat[k];
+            } else {
+                const SmallClass& sc = d.cls[k];
+                dst = small_m + sc.member_off + at[k] * s;
+                small_w[sc.weight_off + at[k]] = w;
+            }
+            for (uint64_t i = 0; i < s; i++) {
+                const uint32_t ci = compact(src[i]);
+                dst[i] = ci;
+                if (k != K_ZERO) { rows[ci] += s - 1 - i; rowsum[ci] += w; }
+            }
+            maxs = std::max(maxs, s);
+            at[k]++;
+            mat[k] += s;
+        }
+        t_maxs[t] = maxs;
+        t_mid_updates[t] = midu;
+    });
+    mid_off[d.n_mid_colors] = d.n_mid_members;
+    zero_off[d.n_zero_colors] = d.n_zero_members;
+    for (int t = 0; t < T; t++) {
+        d.max_color_size = std::max(d.max_color_size, t_maxs[t]);
+        d.n_updates += t_mid_updates[t];
+    }
+    parallel_chunks(N, T, [&](int, uint64_t b, uint64_t e) {
+        for (uint64_t i = b; i < e; i++) {
+            uint64_t r = 0;
+            for (int t = 0; t < T; t++) if (!t_rows[t].empty()) r += t_rows[t][i];
+            row_updates[i] = r;
+        }
+    });
+    for (uint64_t i = 0; i < N; i++) {
+        uint64_t r = 0;
+        for (int t = 0; t < T; t++) if (!t_rowsum[t].empty()) r += t_rowsum[t][i];
+        d.max_row_sum = std::max(d.max_row_sum, r);
+    }
+    ix->totals_file_ids = std::move(raw.total_ids);
+    ix->totals_file_vals = std::move(raw.total_vals);
+    *out = ix.release();
+    return KSB_OK;
+}
+
+static int load_files(const char* prefix, int threads, ksb_index** out) {
+    const std::string P(prefix);
+    RawIndex raw;
+    MappedFile fs, fc, ft;
+    if (!fs.open(P + "_color_to_sources.bin")) return KSB_ERR_IO;
+    if (!fc.open(P + "_color_count.bin")) return KSB_ERR_IO;
+    if (!ft.open(P + "_groupID_to_kmerCount.bin")) return KSB_ERR_IO;
+
+    // ---- pass 1 over colour->sources: record boundaries (sequential: sizes depend on capacity)
+    if (fs.size < 8) { set_error("%s_color_to_sources.bin: shorter than its record count", prefix); return KSB_ERR_FORMAT; }
+    uint64_t n_rec;
+    std::memcpy(&n_rec, fs.data, 8);
+    if (n_rec > fs.size / 24) { set_error("%s_color_to_sources.bin: record count %llu impossible for %llu bytes", prefix, (unsigned long long)n_rec, (unsigned long long)fs.size); return KSB_ERR_FORMAT; }
+    struct Rec { uint64_t pos; uint32_t id; uint32_t size; };
+    std::vector<Rec> recs(n_rec);
+    {
+        uint64_t pos = 8;
+        uint32_t max_id = 0;
+        bool wide = false;
+        for (uint64_t r = 0; r < n_rec; r++) {
+            if (fs.size - pos < 8) { set_error("%s_color_to_sources.bin: truncated at record %llu", prefix, (unsigned long long)r); return KSB_ERR_FORMAT; }
+            uint64_t color;
+            std::memcpy(&color, fs.data + pos, 8);
+            DumpView v;
+            if (!open_dump(fs.data + pos + 8, fs.size - pos - 8, 4, &v)) return KSB_ERR_FORMAT;
+            if (v.size > 0xFFFFFFFFull) { set_error("colour with more than 2^32 members"); return KSB_ERR_FORMAT; }
+            recs[r] = Rec{pos + 8, (uint32_t)color, (uint32_t)v.size};
+            wide |= (color >> 32) != 0;
+            max_id = std::max(max_id, (uint32_t)color);
+            pos += 8 + v.bytes;
+        }
+        // int_vec_map key is uint32_t: insert_or_assign keeps the last record per narrowed id
+        IdTable last;
+        last.init(n_rec, max_id);
+        bool dup = false;
+        for (uint64_t r = 0; r < n_rec; r++) dup |= last.put(recs[r].id, (uint32_t)std::min<uint64_t>(r, 0xFFFFFFFFull));
+        if (dup) {
+            if (n_rec > 0xFFFFFFFFull) { set_error("duplicate colour ids with more than 2^32 records are not supported"); return KSB_ERR_FORMAT; }
+            std::vector<Rec> kept;
+            kept.reserve(n_rec);
+            for (uint64_t r = 0; r < n_rec; r++) {
+                uint32_t lr = 0;
+                last.get(recs[r].id, &lr);
+                if (lr == r) kept.push_back(recs[r]);
+            }
+            recs.swap(kept);
+        }
+        (void)wide;
+    }
+    const uint64_t C = recs.size();
+    raw.n_colors_file = C;
+
+    // ---- colour counts: narrowed key -> narrowed value, slot order, last wins
+    IdTable wt;
+    {
+        DumpView v;
+        if (!open_dump(fc.data, fc.size, 16, &v)) return KSB_ERR_FORMAT;
+        if (v.size == 0) { set_error("%s_color_count.bin is empty (reference: assert(tmpMap.size()), src/pairwise.cpp:117)", prefix); return KSB_ERR_FORMAT; }
+        uint32_t max_id = 0;
+        uint64_t live = 0;
+        for (uint64_t i = 0; i < v.capacity; i++)
+            if (v.ctrl[i] >= 0) { uint64_t k; std::memcpy(&k, v.slots + 16 * i, 8); max_id = std::max(max_id, (uint32_t)k); live++; }
+        if (live != v.size) { set_error("%s_color_count.bin: %llu live slots, header says %llu", prefix, (unsigned long long)live, (unsigned long long)v.size); return KSB_ERR_FORMAT; }
+        wt.init(v.size, max_id);
+        for (uint64_t i = 0; i < v.capacity; i++)
+            if (v.ctrl[i] >= 0) {
+                uint64_t kv[2];
+                std::memcpy(kv, v.slots + 16 * i, 16);
+                wt.put((uint32_t)kv[0], (uint32_t)kv[1]);
+            }
+    }
+
+    // ---- totals, slot order
+    {
+        DumpView v;
+        if (!open_dump(ft.data, ft.size, 8, &v)) return KSB_ERR_FORMAT;
+        if (v.size == 0) { set_error("%s_groupID_to_kmerCount.bin is empty (reference: assert, src/pairwise.cpp:170)", prefix); return KSB_ERR_FORMAT; }
+        raw.total_ids.reserve(v.size);
+        raw.total_vals.reserve(v.size);
+        for (uint64_t i = 0; i < v.capacity; i++)
+            if (v.ctrl[i] >= 0) {
+                uint32_t kv[2];
+                std::memcpy(kv, v.slots + 8 * i, 8);
+                raw.total_ids.push_back(kv[0]);
+                raw.total_vals.push_back(kv[1]);
+            }
+        if (raw.total_ids.size() != v.size) { set_error("%s_groupID_to_kmerCount.bin: live slots != size", prefix); return KSB_ERR_FORMAT; }
+    }
+
+    // ---- pass 2: extract + sort members in parallel
+    raw.off.assign(C + 1, 0);
+    for (uint64_t c = 0; c < C; c++) raw.off[c + 1] = raw.off[c] + recs[c].size;
+    raw.members.resize(raw.off[C]);
+    raw.weights.resize(C);
+    std::atomic<int> bad{0};
+    parallel_chunks(C, threads, [&](int, uint64_t b, uint64_t e) {
+        for (uint64_t c = b; c < e; c++) {
+            DumpView v;
+            open_dump(fs.data + recs[c].pos, fs.size - recs[c].pos, 4, &v);  // validated in pass 1
+            uint32_t* dst = &raw.members[raw.off[c]];
+            uint64_t k = 0;
+            for (uint64_t i = 0; i < v.capacity && v.size; i++)
+                if (v.ctrl[i] >= 0) { if (k < v.size) std::memcpy(&dst[k], v.slots + 4 * i, 4); k++; }
+            if (k != v.size) { bad = 1; continue; }
+            std::sort(dst, dst + k);
+            uint32_t w = 0;
+            wt.get(recs[c].id, &w);  // colorsCount[id] default-inserts 0 when absent
+            raw.weights[c] = w;
+        }
+    });
+    if (bad) { set_error("%s_color_to_sources.bin: a member set has live slots != size", prefix); return KSB_ERR_FORMAT; }
+    return build_index(raw, threads, out);
+}
+
+static int from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members, const uint32_t* weights,
+                    uint64_t n_totals, const uint32_t* total_ids, const uint32_t* total_vals, int threads, ksb_index** out) {
+    RawIndex raw;
+    raw.n_colors_file = n_colors;
+    raw.off.assign(offsets, offsets + n_colors + 1);
+    if (n_colors && raw.off[0] != 0) { set_error("offsets[0] must be 0"); return KSB_ERR_ARG; }
+    for (uint64_t c = 0; c < n_colors; c++)
+        if (raw.off[c + 1] < raw.off[c]) { set_error("offsets not monotone at colour %llu", (unsigned long long)c); return KSB_ERR_ARG; }
+    raw.members.assign(members, members + raw.off[n_colors]);
+    raw.weights.assign(weights, weights + n_colors);
+    // the reference's member lists come from sets: sort, and require distinct members
+    std::atomic<int> dup{0};
+    parallel_chunks(n_colors, threads, [&](int, uint64_t b, uint64_t e) {
+        for (uint64_t c = b; c < e; c++) {
+            uint32_t* m = &raw.members[raw.off[c]];
+            const uint64_t s = raw.off[c + 1] - raw.off[c];
+            std::sort(m, m + s);
+            if (std::adjacent_find(m, m + s) != m + s) dup = 1;
+        }
+    });
+    if (dup) { set_error("a colour lists the same sample twice (member lists are sets in the reference)"); return KSB_ERR_ARG; }
+    // totals: a map in the reference; last value wins for a repeated id
+    raw.total_ids.assign(total_ids, total_ids + n_totals);
+    raw.total_vals.assign(total_vals, total_vals + n_totals);
+    return build_index(raw, threads, out);
+}
+
+}  // namespace ksb
+
+// ------------------------------------------------------------------------------------------- C-ABI
+
+extern "C" {
+
+const char* ksb_last_error(void) { return ksb::last_error(); }
+int ksb_abi_version(void) { return KSB_ABI_VERSION; }
+
+int ksb_index_load(const char* index_prefix, int host_threads, ksb_index** out) {
+    if (!index_prefix || !out) { ksb::set_error("ksb_index_load: null argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    try {
+        return ksb::load_files(index_prefix, host_threads, out);
+    } catch (const std::bad_alloc&) {
+        ksb::set_error("out of host memory while loading %s", index_prefix);
+        return KSB_ERR_NOMEM;
+    } catch (const std::exception& e) {
+        ksb::set_error("ksb_index_load: %s", e.what());
+        return KSB_ERR_FORMAT;
+    }
+}
+
+int ksb_index_from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members, const uint32_t* weights,
+                       uint64_t n_totals, const uint32_t* total_ids, const uint32_t* total_vals, int host_threads,
+                       ksb_index** out) {
+    if (!out || !offsets || (!members && n_colors && offsets[n_colors]) || (!weights && n_colors) ||
+        (n_totals && (!total_ids || !total_vals))) {
+        ksb::set_error("ksb_index_from_csr: null argument");
+        return KSB_ERR_ARG;
+    }
+    *out = nullptr;
+    try {
+        return ksb::from_csr(n_colors, offsets, members, weights, n_totals, total_ids, total_vals, host_threads, out);
+    } catch (const std::bad_alloc&) {
+        ksb::set_error("out of host memory");
+        return KSB_ERR_NOMEM;
+    } catch (const std::exception& e) {
+        ksb::set_error("ksb_index_from_csr: %s", e.what());
+        return KSB_ERR_ARG;
+    }
+}
+
+int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
+    if (!ix || !info) { ksb::set_error("null argument"); return KSB_ERR_ARG; }
+    const ksb::IndexDesc& d = ix->desc;
+    std::memset(info, 0, sizeof *info);
+    info->n_samples = d.n_samples;
+    info->n_colors_file = d.n_colors_file;
+    info->n_colors = d.n_colors;
+    info->n_members = d.n_members;
+    info->n_updates = d.n_updates;
+    info->n_small_colors = d.n_small_colors;
+    info->n_mid_colors = d.n_mid_colors;
+    info->n_zero_colors = d.n_zero_colors;
+    info->max_color_size = d.max_color_size;
+    info->payload_bytes = d.payload_bytes;
+    info->triangle_cells = d.n_samples ? d.n_samples * (d.n_samples - 1) / 2 : 0;
+    info->pinned = ix->pinned ? 1 : 0;
+    return KSB_OK;
+}
+
+const uint32_t* ksb_index_sample_ids(const ksb_index* ix) { return ix ? reinterpret_cast<const uint32_t*>(ix->payload + ix->desc.off_sample_ids) : nullptr; }
+const uint32_t* ksb_index_totals(const ksb_index* ix) { return ix ? reinterpret_cast<const uint32_t*>(ix->payload + ix->desc.off_totals) : nullptr; }
+const void* ksb_index_payload(const ksb_index* ix, uint64_t* bytes) {
+    if (!ix) return nullptr;
+    if (bytes) *bytes = ix->desc.payload_bytes;
+    return ix->payload;
+}
+const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes) {
+    if (!ix) return nullptr;
+    if (bytes) *bytes = sizeof(ksb::IndexDesc);
+    return &ix->desc;
+}
+
+int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path) {
+    if (!ix || !path) { ksb::set_error("null argument"); return KSB_ERR_ARG; }
+    FILE* f = fopen(path, "w");
+    if (!f) { ksb::set_error("cannot write %s", path); return KSB_ERR_IO; }
+    fputs("ID\tseq\tkmers\n", f);
+    for (size_t i = 0; i < ix->totals_file_ids.size(); i++)
+        fprintf(f, "%llu\t%u\t%u\n", (unsigned long long)(i + 1), ix->totals_file_ids[i], ix->totals_file_vals[i]);
+    if (fclose(f) != 0) { ksb::set_error("write error on %s", path); return KSB_ERR_IO; }
+    return KSB_OK;
+}
+
+void ksb_index_free(ksb_index* ix) {
+    if (!ix) return;
+    if (ix->payload) {
+        if (ix->pinned) cudaFreeHost(ix->payload); else free(ix->payload);
+    }
+    delete ix;
+}
+
+}  // extern "C"

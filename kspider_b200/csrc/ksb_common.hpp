@@ -1,0 +1,71 @@
+// Shared host-side declarations of libkspider_b200 (not part of the public C-ABI).
+#pragma once
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/kspider_b200.h"
+
+namespace ksb {
+
+void set_error(const char* fmt, ...);  // thread-local message for ksb_last_error()
+
+// Simple blocking parallel-for over [0,n) in contiguous chunks, one chunk per thread.
+void parallel_chunks(uint64_t n, int threads, const std::function<void(int, uint64_t, uint64_t)>& fn);
+
+constexpr uint32_t kSmallMax = 64;     // colours with 2..64 members go to the flat pair-space kernel
+constexpr uint32_t kMaxPairsSmall = kSmallMax * (kSmallMax - 1) / 2;  // 2016
+
+// One size class of small colours: all colours with exactly s members, stored as a dense
+// [n x s] block of (sorted, compact) member ids and an [n] block of weights.
+struct SmallClass {
+    uint32_t s;        // members per colour
+    uint32_t pairs;    // s(s-1)/2
+    uint32_t magic;    // ceil(2^32 / pairs): t / pairs == umulhi(t, magic) for t < 2^16
+    uint32_t pad;
+    uint64_t n;        // colours in the class
+    uint64_t member_off;  // in u32 units, relative to the small-members section
+    uint64_t weight_off;  // in u32 units, relative to the small-weights section
+};
+
+// Fixed-size, trivially copyable description of the binned CSR blob.  Together with the blob it is
+// everything a device (or another rank) needs.
+struct IndexDesc {
+    uint64_t magic;           // 'KSBIDX01'
+    uint64_t n_samples;
+    uint64_t n_colors_file;
+    uint64_t n_colors;        // multi-member, weight != 0 ... plus zero-weight ones
+    uint64_t n_members;
+    uint64_t n_updates;
+    uint64_t n_small_colors, n_small_members;
+    uint64_t n_mid_colors, n_mid_members;
+    uint64_t n_zero_colors, n_zero_members;
+    uint64_t max_color_size;
+    uint64_t max_row_sum;     // max over samples of sum of weights of colours containing it (cell bound)
+    SmallClass cls[kSmallMax + 1];  // indexed by s; cls[0], cls[1] unused
+    // byte offsets of the sections inside the payload (each 256-byte aligned)
+    uint64_t off_totals;        // u32[N]
+    uint64_t off_sample_ids;    // u32[N]
+    uint64_t off_row_updates;   // u64[N]   updates whose row (= smaller sample) is i
+    uint64_t off_small_members; // u32[n_small_members]
+    uint64_t off_small_weights; // u32[n_small_colors]
+    uint64_t off_mid_offsets;   // u64[n_mid_colors+1]
+    uint64_t off_mid_members;   // u32[n_mid_members]
+    uint64_t off_mid_weights;   // u32[n_mid_colors]
+    uint64_t off_zero_offsets;  // u64[n_zero_colors+1]
+    uint64_t off_zero_members;  // u32[n_zero_members]
+    uint64_t payload_bytes;
+};
+constexpr uint64_t kIndexMagic = 0x31305844494253ULL | (0x4BULL << 56);
+
+}  // namespace ksb
+
+struct ksb_index {
+    ksb::IndexDesc desc;
+    uint8_t* payload = nullptr;
+    bool pinned = false;
+    // totals file in slot order, for the seqToKmersNo.tsv writer (src/pairwise.cpp:173-180)
+    std::vector<uint32_t> totals_file_ids, totals_file_vals;
+};
