@@ -145,8 +145,16 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
 int ksb_accumulate(ksb_device* dev, void* stream, int sync);
 /* device pointer of the owned block of the packed upper triangle (u64 cells) */
 void* ksb_device_triangle(const ksb_device* dev, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end);
-/* K5: containment + record compaction (rows sorted by (i,j)); records land on the host if want_records */
-int ksb_postpass(ksb_device* dev, int want_records, ksb_result** out);
+/* When the owned row block does not fit dense_budget_bytes it is processed in several dense passes
+ * (sub-blocks of rows): select one with ksb_device_set_pass before ksb_accumulate / ksb_postpass. */
+int ksb_device_n_passes(const ksb_device* dev);
+int ksb_device_set_pass(ksb_device* dev, int pass);
+/* owned rows / cells / updates, launches and timings so far */
+int ksb_device_get_info(const ksb_device* dev, ksb_result_info* info);
+/* K5: containment + record compaction of the current pass (rows sorted by (i,j)).  *inout == NULL
+ * creates the result, otherwise the rows are appended to it.  Records also land on the host if
+ * want_records (the flag of the creating call decides). */
+int ksb_postpass(ksb_device* dev, int want_records, ksb_result** inout);
 void ksb_device_free(ksb_device* dev);
 
 /* upload + accumulate + postpass in one call (the end-to-end path) */
@@ -165,6 +173,9 @@ int ksb_append_tsv(const ksb_result* r, const char* path, int host_threads);
 int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* labels_out,
                 uint64_t* n_edges);
 int ksb_cluster_merge(uint64_t n, const uint32_t* labels_a, const uint32_t* labels_b, uint32_t* labels_out);
+/* same on DEVICE buffers of the current device (e.g. the output of an NCCL all-gather):
+ * d_labels_all is [world][n], merged labels land in d_out[n]; stream is a cudaStream_t (NULL = default) */
+int ksb_cluster_merge_device(uint64_t n, int world, const uint32_t* d_labels_all, uint32_t* d_out, void* stream);
 /* smallest float32 c such that the reference keeps an edge whose printed containment is c
  * (strtod("%g" of c) * 100 >= cutoff01 * 100); exposed for tests */
 float ksb_threshold_float(double cutoff01);

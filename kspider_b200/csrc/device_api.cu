@@ -1,0 +1,678 @@
+// Device half of the C-ABI (include/kspider_b200.h): resident CSR, owned triangle block(s),
+// accumulation, post-pass, clustering.  No CPU fallback: every entry point here needs a CUDA device.
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <new>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace ksb {
+cudaError_t scan_block_counts(void* temp, size_t* temp_bytes, const unsigned long long* in, unsigned long long* out,
+                              uint64_t n, cudaStream_t stream);
+}
+
+#define KSB_CUDA(call)                                                                               \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            ksb::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+            (void)cudaGetLastError();                                                                \
+            return KSB_ERR_CUDA;                                                                     \
+        }                                                                                            \
+    } while (0)
+
+// One dense pass: rows [rb, re) of the triangle are accumulated and scanned together.
+struct ksb_pass {
+    uint64_t rb, re, base, cells, updates;
+};
+
+struct ksb_device {
+    ksb::IndexDesc desc;
+    int device = 0, sms = 148;
+    int rank = 0, world = 1;
+    uint8_t* d_payload = nullptr;
+    bool own_payload = false;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
+    uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
+    uint64_t tri_cells_alloc = 0;
+    std::vector<ksb_pass> passes;
+    uint32_t cur_pass = 0;
+    uint64_t row_begin = 0, row_end = 0, owned_cells = 0, owned_updates = 0;
+    ksb::K1Params k1;
+    ksb_timings t;
+    uint64_t launches = 0;
+    // scratch of the post pass
+    unsigned long long* d_block_counts = nullptr;
+    void* d_scan_tmp = nullptr;
+    size_t scan_tmp_bytes = 0;
+    uint64_t post_blocks_alloc = 0;
+};
+
+struct ksb_segment {
+    ksb_record* d_records = nullptr;
+    unsigned long long* d_pairs = nullptr;
+    uint64_t n = 0;
+};
+
+struct ksb_result {
+    int device = 0;
+    uint64_t n_samples = 0;
+    std::vector<ksb_segment> seg;
+    ksb_record* h_records = nullptr;  // pinned, all segments concatenated (only when want_records)
+    uint64_t h_capacity = 0;
+    bool have_host = false;
+    ksb_result_info info;
+};
+
+namespace ksb {
+
+static inline uint64_t rowstart(uint64_t r, uint64_t n) { return r * (2 * n - 1 - r) / 2; }
+
+static TriGeom geom_of(const ksb_device* d, const ksb_pass& p) {
+    TriGeom g;
+    g.tri = d->d_tri;
+    g.base = p.base;
+    g.cells = p.cells;
+    g.two_n_m1 = (uint32_t)(2 * d->desc.n_samples - 1);
+    g.n = (uint32_t)d->desc.n_samples;
+    g.rb = (uint32_t)p.rb;
+    g.nrows = (uint32_t)(p.re - p.rb);
+    return g;
+}
+
+static int check_device(int device, int* sms) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        set_error("no CUDA device: %s (libkspider_b200 has no CPU fallback)", e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        (void)cudaGetLastError();
+        return KSB_ERR_CUDA;
+    }
+    if (device < 0) KSB_CUDA(cudaGetDevice(&device));
+    if (device >= n) { set_error("device %d out of range (%d devices)", device, n); return KSB_ERR_ARG; }
+    cudaDeviceProp prop;
+    KSB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+        return KSB_ERR_CUDA;
+    }
+    KSB_CUDA(cudaSetDevice(device));
+    if (sms) *sms = prop.multiProcessorCount;
+    return device;
+}
+
+static void build_k1(ksb_device* d) {
+    K1Params& p = d->k1;
+    std::memset(&p, 0, sizeof p);
+    unsigned long long task = 0;
+    uint32_t n = 0;
+    // largest colours first: the long tasks start early, the tail is made of short ones
+    for (uint32_t s = kSmallMax; s >= 2; s--) {
+        const SmallClass& sc = d->desc.cls[s];
+        if (sc.n == 0) continue;
+        K1Class& c = p.cls[n++];
+        c.task_begin = task;
+        c.n = sc.n;
+        c.member_off = sc.member_off;
+        c.weight_off = sc.weight_off;
+        c.s = s;
+        c.k = s <= 32 ? 32 / s : 1;
+        task += (sc.n + c.k - 1) / c.k;
+    }
+    p.n_cls = n;
+    p.n_tasks = task;
+}
+
+// Row block of `rank` (equal weighted pair-updates per rank), then dense passes under the budget.
+static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget_bytes) {
+    const uint64_t N = d->desc.n_samples;
+    const uint64_t U = d->desc.n_updates;
+    const int W = std::max(1, d->world);
+    std::vector<uint64_t> cut(W + 1, N);
+    cut[0] = 0;
+    {
+        uint64_t acc = 0;
+        int r = 1;
+        for (uint64_t i = 0; i < N && r < W; i++) {
+            acc += row_updates[i];
+            // rank r starts after the first row at which the prefix reaches r/W of the updates
+            while (r < W && (unsigned __int128)acc * W >= (unsigned __int128)U * r) cut[r++] = i + 1;
+        }
+        cut[W] = N;
+    }
+    d->row_begin = cut[d->rank];
+    d->row_end = cut[d->rank + 1];
+    if (d->rank == W - 1) d->row_end = N;
+    d->owned_cells = N ? rowstart(std::min(d->row_end, N), N) - rowstart(d->row_begin, N) : 0;
+    if (d->row_end == N && N) d->owned_cells = N * (N - 1) / 2 - rowstart(d->row_begin, N);
+    d->owned_updates = 0;
+    for (uint64_t i = d->row_begin; i < d->row_end; i++) d->owned_updates += row_updates[i];
+
+    // bytes per cell: 8 (u64) + 1/8 (touched bit) when needed
+    const bool need_touch = d->desc.n_zero_colors != 0;
+    uint64_t max_cells = budget_bytes / 8;
+    if (need_touch) max_cells = (uint64_t)((double)budget_bytes / 8.125);
+    if (max_cells < N) max_cells = N;  // at least one row
+    d->passes.clear();
+    uint64_t rb = d->row_begin;
+    while (rb < d->row_end) {
+        uint64_t re = rb, cells = 0, upd = 0;
+        while (re < d->row_end) {
+            const uint64_t rc = N - 1 - re;
+            if (re > rb && cells + rc > max_cells) break;
+            cells += rc;
+            upd += row_updates[re];
+            re++;
+        }
+        d->passes.push_back(ksb_pass{rb, re, rowstart(rb, N), cells, upd});
+        rb = re;
+    }
+    if (d->passes.empty()) d->passes.push_back(ksb_pass{d->row_begin, d->row_begin, N ? rowstart(d->row_begin, N) : 0, 0, 0});
+    uint64_t mx = 0;
+    for (const ksb_pass& p : d->passes) mx = std::max(mx, p.cells);
+    d->tri_cells_alloc = mx;
+    return KSB_OK;
+}
+
+static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_opts* opts) {
+    if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
+    if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    for (auto& e : d->ev) KSB_CUDA(cudaEventCreate(&e));
+    uint64_t budget = opts ? opts->dense_budget_bytes : 0;
+    if (budget == 0) {
+        size_t fr = 0, tot = 0;
+        KSB_CUDA(cudaMemGetInfo(&fr, &tot));
+        budget = (uint64_t)((double)fr * 0.8);
+    }
+    int rc = plan_rows(d, row_updates, budget);
+    if (rc) return rc;
+    const uint64_t cells = d->tri_cells_alloc;
+    KSB_CUDA(cudaMalloc(&d->d_tri, 8 * (cells + 8)));
+    if (d->desc.n_zero_colors) KSB_CUDA(cudaMalloc(&d->d_touched, 4 * (cells / 32 + 2)));
+    d->post_blocks_alloc = post_blocks(cells) + 1;
+    KSB_CUDA(cudaMalloc(&d->d_block_counts, 8 * d->post_blocks_alloc * 2));
+    d->scan_tmp_bytes = 0;
+    KSB_CUDA(scan_block_counts(nullptr, &d->scan_tmp_bytes, d->d_block_counts, d->d_block_counts + d->post_blocks_alloc,
+                               d->post_blocks_alloc, d->stream));
+    KSB_CUDA(cudaMalloc(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256)));
+    build_k1(d);
+    return KSB_OK;
+}
+
+}  // namespace ksb
+
+using namespace ksb;
+
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, a, b) != cudaSuccess) { (void)cudaGetLastError(); return 0.f; }
+    return ms;
+}
+
+extern "C" {
+
+int ksb_cuda_available(void) {
+    int sms = 0;
+    const int rc = check_device(-1, &sms);
+    return rc < 0 ? rc : KSB_OK;
+}
+
+void ksb_device_free(ksb_device* d) {
+    if (!d) return;
+    cudaSetDevice(d->device);
+    if (d->stream) cudaStreamSynchronize(d->stream);
+    if (d->own_payload && d->d_payload) cudaFree(d->d_payload);
+    if (d->d_tri) cudaFree(d->d_tri);
+    if (d->d_touched) cudaFree(d->d_touched);
+    if (d->d_block_counts) cudaFree(d->d_block_counts);
+    if (d->d_scan_tmp) cudaFree(d->d_scan_tmp);
+    for (auto& e : d->ev) if (e) cudaEventDestroy(e);
+    if (d->stream) cudaStreamDestroy(d->stream);
+    (void)cudaGetLastError();
+    delete d;
+}
+
+static int opts_common(ksb_device* d, const ksb_opts* opts) {
+    d->rank = opts ? opts->rank : 0;
+    d->world = (opts && opts->world > 1) ? opts->world : 1;
+    if (d->rank < 0 || d->rank >= d->world) { set_error("rank %d outside world %d", d->rank, d->world); return KSB_ERR_ARG; }
+    std::memset(&d->t, 0, sizeof d->t);
+    return KSB_OK;
+}
+
+int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
+    if (!ix || !out) { set_error("ksb_upload: null argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    int sms = 0;
+    const int dev = check_device(opts ? opts->device : -1, &sms);
+    if (dev < 0) return dev;
+    ksb_device* d = new (std::nothrow) ksb_device();
+    if (!d) { set_error("out of memory"); return KSB_ERR_NOMEM; }
+    d->device = dev;
+    d->sms = sms;
+    d->desc = ix->desc;
+    int rc = opts_common(d, opts);
+    if (rc) { ksb_device_free(d); return rc; }
+    auto fail = [&](int code) { ksb_device_free(d); return code; };
+    cudaError_t e = cudaMalloc(&d->d_payload, d->desc.payload_bytes);
+    if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
+    d->own_payload = true;
+    const uint64_t* row_updates = reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_row_updates);
+    rc = finish_device(d, row_updates, opts);
+    if (rc) return fail(rc);
+    cudaEventRecord(d->ev[0], d->stream);
+    e = cudaMemcpyAsync(d->d_payload, ix->payload, d->desc.payload_bytes, cudaMemcpyHostToDevice, d->stream);
+    cudaEventRecord(d->ev[1], d->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
+    if (e != cudaSuccess) { set_error("index H2D copy: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
+    d->t.h2d_ms = ev_ms(d->ev[0], d->ev[1]);
+    *out = d;
+    return KSB_OK;
+}
+
+int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, const void* d_payload,
+                             uint64_t payload_bytes, const ksb_opts* opts, ksb_device** out) {
+    if (!descriptor || !d_payload || !out) { set_error("ksb_adopt_device_payload: null argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    if (descriptor_bytes != sizeof(IndexDesc)) { set_error("descriptor is %llu bytes, expected %zu", (unsigned long long)descriptor_bytes, sizeof(IndexDesc)); return KSB_ERR_ARG; }
+    int sms = 0;
+    const int dev = check_device(opts ? opts->device : -1, &sms);
+    if (dev < 0) return dev;
+    ksb_device* d = new (std::nothrow) ksb_device();
+    if (!d) { set_error("out of memory"); return KSB_ERR_NOMEM; }
+    d->device = dev;
+    d->sms = sms;
+    std::memcpy(&d->desc, descriptor, sizeof(IndexDesc));
+    if (d->desc.payload_bytes != payload_bytes) { set_error("payload is %llu bytes, descriptor says %llu", (unsigned long long)payload_bytes, (unsigned long long)d->desc.payload_bytes); delete d; return KSB_ERR_ARG; }
+    int rc = opts_common(d, opts);
+    if (rc) { ksb_device_free(d); return rc; }
+    d->d_payload = const_cast<uint8_t*>(static_cast<const uint8_t*>(d_payload));
+    d->own_payload = false;
+    std::vector<uint64_t> row_updates(d->desc.n_samples);
+    if (d->desc.n_samples) {
+        cudaError_t e = cudaMemcpy(row_updates.data(), d->d_payload + d->desc.off_row_updates, 8 * d->desc.n_samples, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { set_error("reading row histogram from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
+    }
+    rc = finish_device(d, row_updates.data(), opts);
+    if (rc) { ksb_device_free(d); return rc; }
+    *out = d;
+    return KSB_OK;
+}
+
+int ksb_device_n_passes(const ksb_device* d) { return d ? (int)d->passes.size() : 0; }
+int ksb_device_set_pass(ksb_device* d, int pass) {
+    if (!d || pass < 0 || (size_t)pass >= d->passes.size()) { set_error("pass out of range"); return KSB_ERR_ARG; }
+    d->cur_pass = (uint32_t)pass;
+    return KSB_OK;
+}
+
+int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
+    if (!d) { set_error("ksb_accumulate: null device"); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t st = stream_v ? static_cast<cudaStream_t>(stream_v) : d->stream;
+    const ksb_pass& p = d->passes[d->cur_pass];
+    const TriGeom g = geom_of(d, p);
+    const LaunchCfg lc{d->sms, st};
+    const IndexDesc& D = d->desc;
+    const uint8_t* P = d->d_payload;
+    KSB_CUDA(cudaEventRecord(d->ev[0], st));
+    KSB_CUDA(cudaMemsetAsync(d->d_tri, 0, 8 * (p.cells + 8), st));
+    if (d->d_touched) KSB_CUDA(cudaMemsetAsync(d->d_touched, 0, 4 * (p.cells / 32 + 2), st));
+    KSB_CUDA(cudaEventRecord(d->ev[1], st));
+    if (p.cells) {
+        KSB_CUDA(launch_k1_small(d->k1, reinterpret_cast<const uint32_t*>(P + D.off_small_members),
+                                 reinterpret_cast<const uint32_t*>(P + D.off_small_weights), g, lc));
+        if (d->k1.n_tasks) d->launches++;
+    }
+    KSB_CUDA(cudaEventRecord(d->ev[2], st));
+    if (p.cells && D.n_mid_items) {
+        KSB_CUDA(launch_k2_mid(reinterpret_cast<const MidItem*>(P + D.off_mid_items), D.n_mid_items,
+                               reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
+                               reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
+                               reinterpret_cast<const uint32_t*>(P + D.off_mid_members),
+                               reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, lc));
+        d->launches++;
+    }
+    KSB_CUDA(cudaEventRecord(d->ev[3], st));
+    if (p.cells && D.n_zero_colors) {
+        KSB_CUDA(launch_kz_touch(D.n_zero_colors, reinterpret_cast<const unsigned long long*>(P + D.off_zero_offsets),
+                                 reinterpret_cast<const uint32_t*>(P + D.off_zero_members), d->d_touched, g, lc));
+        d->launches++;
+    }
+    KSB_CUDA(cudaEventRecord(d->ev[4], st));
+    if (sync) {
+        KSB_CUDA(cudaStreamSynchronize(st));
+        d->t.zero_ms += ev_ms(d->ev[0], d->ev[1]);
+        d->t.small_ms += ev_ms(d->ev[1], d->ev[2]);
+        d->t.mid_ms += ev_ms(d->ev[2], d->ev[3]);
+        d->t.zero_touch_ms += ev_ms(d->ev[3], d->ev[4]);
+        d->t.accumulate_ms += ev_ms(d->ev[0], d->ev[4]);
+    }
+    return KSB_OK;
+}
+
+void* ksb_device_triangle(const ksb_device* d, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end) {
+    if (!d) return nullptr;
+    const ksb_pass& p = d->passes[d->cur_pass];
+    if (cells) *cells = p.cells;
+    if (row_begin) *row_begin = p.rb;
+    if (row_end) *row_end = p.re;
+    return d->d_tri;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------ post pass (K5)
+
+extern "C" {
+
+void ksb_result_free(ksb_result* r) {
+    if (!r) return;
+    cudaSetDevice(r->device);
+    for (ksb_segment& s : r->seg) {
+        if (s.d_records) cudaFree(s.d_records);
+        if (s.d_pairs) cudaFree(s.d_pairs);
+    }
+    if (r->h_records) cudaFreeHost(r->h_records);
+    (void)cudaGetLastError();
+    delete r;
+}
+
+// Scans the current pass of `d` and appends its rows to *inout (created when *inout == NULL).
+int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
+    if (!d || !inout) { set_error("ksb_postpass: null argument"); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(d->device));
+    ksb_result* r = *inout;
+    const bool created = (r == nullptr);
+    if (created) {
+        r = new (std::nothrow) ksb_result();
+        if (!r) { set_error("out of memory"); return KSB_ERR_NOMEM; }
+        r->device = d->device;
+        r->n_samples = d->desc.n_samples;
+        std::memset(&r->info, 0, sizeof r->info);
+        r->info.row_begin = d->row_begin;
+        r->info.row_end = d->row_end;
+        r->info.owned_cells = d->owned_cells;
+        r->have_host = want_records != 0;
+    }
+    auto fail = [&](int code) { if (created) ksb_result_free(r); return code; };
+#define KSB_CUDA_R(call)                                                                              \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);    \
+            (void)cudaGetLastError();                                                                 \
+            return fail(KSB_ERR_CUDA);                                                                \
+        }                                                                                             \
+    } while (0)
+    const ksb_pass& p = d->passes[d->cur_pass];
+    const TriGeom g = geom_of(d, p);
+    const LaunchCfg lc{d->sms, d->stream};
+    const uint64_t nb = post_blocks(p.cells);
+    unsigned long long* counts = d->d_block_counts;
+    unsigned long long* offsets = d->d_block_counts + d->post_blocks_alloc;
+    uint64_t n_rows = 0;
+    ksb_segment seg;
+    KSB_CUDA_R(cudaEventRecord(d->ev[5], d->stream));
+    if (nb) {
+        KSB_CUDA_R(cudaMemsetAsync(counts + nb, 0, 8, d->stream));
+        KSB_CUDA_R(launch_k5_count(g, d->d_touched, counts, lc));
+        size_t tb = d->scan_tmp_bytes;
+        KSB_CUDA_R(scan_block_counts(d->d_scan_tmp, &tb, counts, offsets, nb + 1, d->stream));
+        unsigned long long total = 0;
+        KSB_CUDA_R(cudaMemcpyAsync(&total, offsets + nb, 8, cudaMemcpyDeviceToHost, d->stream));
+        KSB_CUDA_R(cudaStreamSynchronize(d->stream));
+        d->launches += 2;  // k5_count + the scan
+        n_rows = total;
+        if (n_rows) {
+            KSB_CUDA_R(cudaMalloc(&seg.d_records, sizeof(ksb_record) * n_rows));
+            cudaError_t e = cudaMalloc(&seg.d_pairs, 8 * n_rows);
+            if (e != cudaSuccess) { cudaFree(seg.d_records); set_error("cudaMalloc pairs: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
+            seg.n = n_rows;
+            r->seg.push_back(seg);
+            const uint8_t* P = d->d_payload;
+            KSB_CUDA_R(launch_k5_emit(g, d->d_touched, offsets, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals),
+                                      reinterpret_cast<const uint32_t*>(P + d->desc.off_sample_ids), seg.d_records, seg.d_pairs, lc));
+            d->launches++;
+        }
+    }
+    KSB_CUDA_R(cudaEventRecord(d->ev[6], d->stream));
+    if (r->have_host && n_rows) {
+        const uint64_t have = r->info.n_rows, need = have + n_rows;
+        if (need > r->h_capacity) {
+            const uint64_t cap = std::max<uint64_t>(need, r->h_capacity * 2);
+            ksb_record* nh = nullptr;
+            KSB_CUDA_R(cudaMallocHost(&nh, sizeof(ksb_record) * cap));
+            if (have) std::memcpy(nh, r->h_records, sizeof(ksb_record) * have);
+            if (r->h_records) cudaFreeHost(r->h_records);
+            r->h_records = nh;
+            r->h_capacity = cap;
+        }
+        KSB_CUDA_R(cudaMemcpyAsync(r->h_records + have, seg.d_records, sizeof(ksb_record) * n_rows, cudaMemcpyDeviceToHost, d->stream));
+    }
+    KSB_CUDA_R(cudaEventRecord(d->ev[7], d->stream));
+    KSB_CUDA_R(cudaStreamSynchronize(d->stream));
+#undef KSB_CUDA_R
+    d->t.post_ms += ev_ms(d->ev[5], d->ev[6]);
+    d->t.d2h_ms += ev_ms(d->ev[6], d->ev[7]);
+    r->info.n_rows += n_rows;
+    r->info.n_updates += p.updates;
+    r->info.gpu_launches = d->launches;
+    r->info.t = d->t;
+    *inout = r;
+    return KSB_OK;
+}
+
+int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
+    if (!ix || !out) { set_error("ksb_pairwise: null argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    ksb_device* d = nullptr;
+    int rc = ksb_upload(ix, opts, &d);
+    if (rc) return rc;
+    ksb_result* r = nullptr;
+    const int want = opts ? opts->want_records : 1;
+    for (int p = 0; p < (int)d->passes.size() && rc == KSB_OK; p++) {
+        rc = ksb_device_set_pass(d, p);
+        if (rc == KSB_OK) rc = ksb_accumulate(d, nullptr, 1);
+        if (rc == KSB_OK) rc = ksb_postpass(d, want, &r);
+    }
+    ksb_device_free(d);
+    if (rc) { ksb_result_free(r); return rc; }
+    *out = r;
+    return KSB_OK;
+}
+
+int ksb_device_get_info(const ksb_device* d, ksb_result_info* info) {
+    if (!d || !info) { set_error("null argument"); return KSB_ERR_ARG; }
+    std::memset(info, 0, sizeof *info);
+    info->n_updates = d->owned_updates;
+    info->row_begin = d->row_begin;
+    info->row_end = d->row_end;
+    info->owned_cells = d->owned_cells;
+    info->gpu_launches = d->launches;
+    info->t = d->t;
+    return KSB_OK;
+}
+
+int ksb_result_get_info(const ksb_result* r, ksb_result_info* info) {
+    if (!r || !info) { set_error("null argument"); return KSB_ERR_ARG; }
+    *info = r->info;
+    return KSB_OK;
+}
+
+const ksb_record* ksb_result_records(const ksb_result* r, uint64_t* n_rows) {
+    if (!r) return nullptr;
+    if (n_rows) *n_rows = r->have_host ? r->info.n_rows : 0;
+    return r->have_host ? r->h_records : nullptr;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------- threshold + CC (K6 + K7)
+
+extern "C" {
+
+int ksb_format_float(float v, char* buf);
+
+// ks_clustering.py:97-105: the edge is dropped iff float(text) * 100 < float(cutoff) * 100 where
+// text is the "%g" rendering of the float32 containment.  Both steps are monotone non-decreasing
+// in the float, so the kept set is {c >= c*}: binary search of the bit pattern over [+0, +inf].
+float ksb_threshold_float(double cutoff01) {
+    const double cut = cutoff01 * 100.0;
+    auto kept = [&](uint32_t bits) {
+        float c;
+        std::memcpy(&c, &bits, 4);
+        char buf[32];
+        const int n = ksb_format_float(c, buf);
+        buf[n] = 0;
+        const double distance = strtod(buf, nullptr) * 100.0;
+        return !(distance < cut);
+    };
+    uint32_t lo = 0, hi = 0x7F800000u;  // +0 .. +inf
+    if (kept(lo)) return 0.0f;
+    if (!kept(hi)) return std::nanf("");  // cutoff above +inf: nothing but NaN rows survives
+    while (hi - lo > 1) {  // invariant: !kept(lo), kept(hi)
+        const uint32_t mid = lo + (hi - lo) / 2;
+        if (kept(mid)) hi = mid; else lo = mid;
+    }
+    float c;
+    std::memcpy(&c, &hi, 4);
+    return c;
+}
+
+int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* labels_out, uint64_t* n_edges) {
+    if (!r || !labels_out) { set_error("ksb_cluster: null argument"); return KSB_ERR_ARG; }
+    if (dist_col < 3 || dist_col > 5) { set_error("ksb_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
+    int sms = 0;
+    const int dev = check_device(r->device, &sms);
+    if (dev < 0) return dev;
+    const uint32_t N = (uint32_t)r->n_samples;
+    if (n_edges) *n_edges = 0;
+    if (N == 0) return KSB_OK;
+    float cstar = ksb_threshold_float(cutoff01);
+    if (cstar != cstar) cstar = INFINITY;  // keep NaN rows only: c < inf drops every number... except inf itself
+    uint32_t* d_parent = nullptr;
+    unsigned long long* d_edges = nullptr;
+    cudaStream_t st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    int rc = KSB_OK;
+    cudaError_t e = cudaSuccess;
+    do {
+        if ((e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) != cudaSuccess) break;
+        if ((e = cudaEventCreate(&e0)) != cudaSuccess) break;
+        if ((e = cudaEventCreate(&e1)) != cudaSuccess) break;
+        if ((e = cudaMalloc(&d_parent, 4ull * N)) != cudaSuccess) break;
+        if ((e = cudaMalloc(&d_edges, 8)) != cudaSuccess) break;
+        const LaunchCfg lc{sms, st};
+        cudaEventRecord(e0, st);
+        if ((e = cudaMemsetAsync(d_edges, 0, 8, st)) != cudaSuccess) break;
+        if ((e = launch_k7_init(d_parent, N, lc)) != cudaSuccess) break;
+        for (const ksb_segment& s : r->seg)
+            if ((e = launch_k67_union(s.d_records, s.d_pairs, s.n, dist_col, cstar, d_parent, d_edges, lc)) != cudaSuccess) break;
+        if (e != cudaSuccess) break;
+        if ((e = launch_k7_compress(d_parent, N, lc)) != cudaSuccess) break;
+        cudaEventRecord(e1, st);
+        unsigned long long ne = 0;
+        if ((e = cudaMemcpyAsync(labels_out, d_parent, 4ull * N, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(&ne, d_edges, 8, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+        if ((e = cudaStreamSynchronize(st)) != cudaSuccess) break;
+        if (n_edges) *n_edges = ne;
+        ksb_result* rw = const_cast<ksb_result*>(r);
+        rw->info.t.cluster_ms = ev_ms(e0, e1);
+        rw->info.gpu_launches += 2 + r->seg.size();
+    } while (0);
+    if (e != cudaSuccess) { set_error("ksb_cluster: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); rc = KSB_ERR_CUDA; }
+    if (d_parent) cudaFree(d_parent);
+    if (d_edges) cudaFree(d_edges);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (st) cudaStreamDestroy(st);
+    return rc;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------- multi-GPU label merge + red micro-benchmark
+
+namespace ksb {
+// union(v, other[v]) for every v: merges the partition `other` into `parent`
+cudaError_t launch_k7_merge(uint32_t* parent, const uint32_t* other, uint32_t n, const LaunchCfg& lc);
+}  // namespace ksb
+
+extern "C" {
+
+// Device-side merge for callers that already hold the label arrays on the GPU (e.g. after an NCCL
+// all-gather): d_labels_all is [world][n]; the merged labels are written to d_out[n].
+int ksb_cluster_merge_device(uint64_t n, int world, const uint32_t* d_labels_all, uint32_t* d_out, void* stream_v) {
+    if (!d_labels_all || !d_out || world < 1) { set_error("ksb_cluster_merge_device: bad argument"); return KSB_ERR_ARG; }
+    if (n == 0) return KSB_OK;
+    int dev = 0, sms = 148;
+    KSB_CUDA(cudaGetDevice(&dev));
+    KSB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    cudaStream_t st = static_cast<cudaStream_t>(stream_v);
+    const LaunchCfg lc{sms, st};
+    KSB_CUDA(cudaMemcpyAsync(d_out, d_labels_all, 4 * n, cudaMemcpyDeviceToDevice, st));
+    for (int w = 1; w < world; w++) KSB_CUDA(launch_k7_merge(d_out, d_labels_all + (uint64_t)w * n, (uint32_t)n, lc));
+    KSB_CUDA(launch_k7_compress(d_out, (uint32_t)n, lc));
+    return KSB_OK;
+}
+
+int ksb_cluster_merge(uint64_t n, const uint32_t* labels_a, const uint32_t* labels_b, uint32_t* labels_out) {
+    if ((n && (!labels_a || !labels_b || !labels_out))) { set_error("ksb_cluster_merge: null argument"); return KSB_ERR_ARG; }
+    if (n == 0) return KSB_OK;
+    const int dev = check_device(-1, nullptr);
+    if (dev < 0) return dev;
+    for (uint64_t i = 0; i < n; i++)
+        if (labels_a[i] >= n || labels_b[i] >= n) { set_error("ksb_cluster_merge: label out of range at %llu", (unsigned long long)i); return KSB_ERR_ARG; }
+    uint32_t* d_all = nullptr;
+    uint32_t* d_out = nullptr;
+    KSB_CUDA(cudaMalloc(&d_all, 8 * n));
+    cudaError_t e = cudaMalloc(&d_out, 4 * n);
+    int rc = KSB_OK;
+    if (e == cudaSuccess) e = cudaMemcpy(d_all, labels_a, 4 * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_all + n, labels_b, 4 * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) rc = ksb_cluster_merge_device(n, 2, d_all, d_out, nullptr);
+    if (e == cudaSuccess && rc == KSB_OK) e = cudaMemcpy(labels_out, d_out, 4 * n, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { set_error("ksb_cluster_merge: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); rc = KSB_ERR_CUDA; }
+    cudaFree(d_all);
+    if (d_out) cudaFree(d_out);
+    return rc;
+}
+
+int ksb_bench_red(uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, int reps, float* best_ms) {
+    if (!best_ms || cells < 64 || (cell_bits != 32 && cell_bits != 64) || reps < 1) { set_error("ksb_bench_red: bad argument"); return KSB_ERR_ARG; }
+    int sms = 0;
+    const int dev = check_device(-1, &sms);
+    if (dev < 0) return dev;
+    void* buf = nullptr;
+    KSB_CUDA(cudaMalloc(&buf, cells * (cell_bits / 8)));
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    cudaMemset(buf, 0, cells * (cell_bits / 8));
+    const LaunchCfg lc{sms, nullptr};
+    float best = 1e30f;
+    cudaError_t e = cudaSuccess;
+    for (int i = 0; i < reps + 1 && e == cudaSuccess; i++) {  // first launch = warm-up
+        cudaEventRecord(a, nullptr);
+        e = launch_bench_red(buf, cells, n_ops, cell_bits, pattern, lc);
+        cudaEventRecord(b, nullptr);
+        if (e == cudaSuccess) e = cudaEventSynchronize(b);
+        if (i > 0 && e == cudaSuccess) best = std::min(best, ev_ms(a, b));
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    cudaFree(buf);
+    if (e != cudaSuccess) { set_error("ksb_bench_red: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return KSB_ERR_CUDA; }
+    *best_ms = best;
+    return KSB_OK;
+}
+
+}  // extern "C"

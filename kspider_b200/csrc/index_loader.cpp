@@ -106,6 +106,17 @@ private:
 
 static inline uint64_t align256(uint64_t x) { return (x + 255) & ~255ULL; }
 
+// K2 items of one mid colour of s members: for every block of kMidCols columns, the rows below
+// the block's last column, in chunks of kMidRows.
+static inline uint64_t mid_items_of(uint64_t s) {
+    uint64_t n = 0;
+    for (uint64_t b0 = 0; b0 < s; b0 += kMidCols) {
+        const uint64_t rows = std::min<uint64_t>(s - 1, b0 + kMidCols - 1);  // rows a < rows can pair with the block
+        n += (rows + kMidRows - 1) / kMidRows;
+    }
+    return n;
+}
+
 // Intermediate form shared by both front ends: every colour of the file / input, members sorted
 // ascending and de-duplicated (ORIGINAL sample ids), weight already narrowed.
 struct RawIndex {
@@ -167,6 +178,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     std::vector<std::vector<uint64_t>> cnt(T, std::vector<uint64_t>(K_N, 0));      // colours per class
     std::vector<std::vector<uint64_t>> mcnt(T, std::vector<uint64_t>(K_N, 0));     // members per class
     std::vector<uint64_t> chunk_b(T + 1, C);
+    std::vector<uint64_t> icnt(T, 0), ibase(T, 0);  // K2 items per chunk
     auto klass = [&](uint64_t c) -> uint32_t {
         const uint64_t s = raw.off[c + 1] - raw.off[c];
         if (s < 2) return 0;
@@ -179,9 +191,13 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             const uint32_t k = klass(c);
             if (!k) continue;
             cnt[t][k]++;
-            mcnt[t][k] += raw.off[c + 1] - raw.off[c];
+            const uint64_t s = raw.off[c + 1] - raw.off[c];
+            mcnt[t][k] += (k == K_MID) ? ((s + 3) & ~3ULL) : s;  // mid colours start 16-byte aligned
+            if (k == K_MID) icnt[t] += mid_items_of(s);
         }
     });
+    uint64_t n_items = 0;
+    for (int t = 0; t < T; t++) { ibase[t] = n_items; n_items += icnt[t]; }
     std::vector<uint64_t> tot(K_N, 0), mtot(K_N, 0);
     std::vector<std::vector<uint64_t>> base(T, std::vector<uint64_t>(K_N, 0)), mbase(T, std::vector<uint64_t>(K_N, 0));
     for (uint32_t k = 0; k < K_N; k++)
@@ -205,11 +221,11 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.n_small_colors = woff;
     d.n_small_members = moff;
     d.n_mid_colors = tot[K_MID];
-    d.n_mid_members = mtot[K_MID];
+    d.n_mid_members_padded = mtot[K_MID];
+    d.n_mid_items = n_items;
     d.n_zero_colors = tot[K_ZERO];
     d.n_zero_members = mtot[K_ZERO];
     d.n_colors = d.n_small_colors + d.n_mid_colors + d.n_zero_colors;
-    d.n_members = d.n_small_members + d.n_mid_members + d.n_zero_members;
 
     // ---- payload layout
     uint64_t p = 0;
@@ -220,8 +236,10 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_small_members = section(4 * d.n_small_members);
     d.off_small_weights = section(4 * d.n_small_colors);
     d.off_mid_offsets = section(8 * (d.n_mid_colors + 1));
-    d.off_mid_members = section(4 * d.n_mid_members);
+    d.off_mid_sizes = section(4 * d.n_mid_colors);
+    d.off_mid_members = section(4 * d.n_mid_members_padded + 16);
     d.off_mid_weights = section(4 * d.n_mid_colors);
+    d.off_mid_items = section(sizeof(MidItem) * d.n_mid_items);
     d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
     d.off_zero_members = section(4 * d.n_zero_members);
     d.payload_bytes = std::max<uint64_t>(p, 256);
@@ -245,6 +263,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     uint64_t* mid_off = reinterpret_cast<uint64_t*>(P + d.off_mid_offsets);
     uint32_t* mid_m = reinterpret_cast<uint32_t*>(P + d.off_mid_members);
     uint32_t* mid_w = reinterpret_cast<uint32_t*>(P + d.off_mid_weights);
+    uint32_t* mid_sz = reinterpret_cast<uint32_t*>(P + d.off_mid_sizes);
+    MidItem* mid_items = reinterpret_cast<MidItem*>(P + d.off_mid_items);
     uint64_t* zero_off = reinterpret_cast<uint64_t*>(P + d.off_zero_offsets);
     uint32_t* zero_m = reinterpret_cast<uint32_t*>(P + d.off_zero_members);
 
@@ -254,14 +274,14 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
     // ---- fill (parallel, deterministic placement = input order within each class)
     std::vector<std::vector<uint64_t>> t_rows(T), t_rowsum(T);
-    std::vector<uint64_t> t_maxs(T, 0), t_mid_updates(T, 0);
+    std::vector<uint64_t> t_maxs(T, 0), t_mid_updates(T, 0), t_mid_members(T, 0);
     parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
         std::vector<uint64_t>& rows = t_rows[t];
         std::vector<uint64_t>& rowsum = t_rowsum[t];
         rows.assign(N, 0);
         rowsum.assign(N, 0);
         std::vector<uint64_t> at = base[t], mat = mbase[t];
-        uint64_t maxs = 0, midu = 0;
+        uint64_t maxs = 0, midu = 0, midm = 0, iat = ibase[t];
         for (uint64_t c = b; c < e; c++) {
             const uint32_t k = klass(c);
             if (!k) continue;
@@ -272,8 +292,15 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             if (k == K_MID) {
                 dst = mid_m + mat[k];
                 mid_off[at[k]] = mat[k];
+                mid_sz[at[k]] = (uint32_t)s;
                 mid_w[at[k]] = w;
                 midu += s * (s - 1) / 2;
+                midm += s;
+                for (uint64_t b0 = 0; b0 < s; b0 += kMidCols) {
+                    const uint64_t rows = std::min<uint64_t>(s - 1, b0 + kMidCols - 1);
+                    for (uint64_t a0 = 0; a0 < rows; a0 += kMidRows)
+                        mid_items[iat++] = MidItem{(uint32_t)at[k], (uint32_t)b0, (uint32_t)a0, 0};
+                }
             } else if (k == K_ZERO) {
                 dst = zero_m + mat[k];
                 zero_off[at[k]] = mat[k];
@@ -289,17 +316,20 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             }
             maxs = std::max(maxs, s);
             at[k]++;
-            mat[k] += s;
+            mat[k] += (k == K_MID) ? ((s + 3) & ~3ULL) : s;
         }
         t_maxs[t] = maxs;
         t_mid_updates[t] = midu;
+        t_mid_members[t] = midm;
     });
-    mid_off[d.n_mid_colors] = d.n_mid_members;
+    mid_off[d.n_mid_colors] = d.n_mid_members_padded;
     zero_off[d.n_zero_colors] = d.n_zero_members;
     for (int t = 0; t < T; t++) {
         d.max_color_size = std::max(d.max_color_size, t_maxs[t]);
         d.n_updates += t_mid_updates[t];
+        d.n_mid_members += t_mid_members[t];
     }
+    d.n_members = d.n_small_members + d.n_mid_members + d.n_zero_members;
     parallel_chunks(N, T, [&](int, uint64_t b, uint64_t e) {
         for (uint64_t i = b; i < e; i++) {
             uint64_t r = 0;

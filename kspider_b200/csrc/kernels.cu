@@ -1,0 +1,515 @@
+// sm_100a kernels of the kSpider pairwise hot path (see kernels.cuh for the reference lines each one replaces).
+//
+// Common idea of the pair-emission kernels: member lists are sorted, so the smaller member of a
+// pair (the triangle ROW) is the one with the smaller position.  Every lane/thread keeps ONE member
+// as its COLUMN in a register; rows are broadcast (warp shuffle in K1, shared memory in K2) as a
+// ready-made 64-bit "row address" (address of the virtual cell (row, 0) of the owned block, or 0
+// when this GPU does not own the row), so one update is: add 8*column, red.global.add.u64.
+// Updates of one step land in ONE row of the triangle, in ascending address order.
+#include "kernels.cuh"
+
+#include <cub/device/device_scan.cuh>
+
+namespace ksb {
+
+#define KSB_FULL 0xffffffffu
+
+__device__ __forceinline__ unsigned long long row_addr(uint32_t x, const TriGeom& g) {
+    if (x - g.rb >= g.nrows) return 0ull;
+    const unsigned long long t = ((unsigned long long)x * (unsigned long long)(g.two_n_m1 - x)) >> 1;
+    return (unsigned long long)g.tri + 8ull * (t - (unsigned long long)x - 1ull - g.base);
+}
+
+__device__ __forceinline__ void red_add_u64(unsigned long long addr, unsigned long long w) {
+    asm volatile("red.global.add.u64 [%0], %1;" ::"l"(addr), "l"(w) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long shfl_u64(unsigned long long v, uint32_t src) {
+    const uint32_t lo = __shfl_sync(KSB_FULL, (uint32_t)v, src);
+    const uint32_t hi = __shfl_sync(KSB_FULL, (uint32_t)(v >> 32), src);
+    return ((unsigned long long)hi << 32) | lo;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: one warp per small colour (2 <= s <= 64).  Colours of one size s are a dense [n x s] block, so
+// a warp task loads 32/s whole colours (s <= 32) or one colour in two registers (s > 32) with one
+// coalesced load, then walks the rows: step a broadcasts row a of every group by shuffle and the
+// lanes holding a later member add the colour's weight into cell (row, own member).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params P,
+                                                const uint32_t* __restrict__ members,
+                                                const uint32_t* __restrict__ weights,
+                                                const __grid_constant__ TriGeom G) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long task = warp; task < P.n_tasks; task += nwarps) {
+        uint32_t lo = 0, hi = P.n_cls;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (P.cls[mid].task_begin <= task) lo = mid; else hi = mid;
+        }
+        const unsigned long long t_in = task - P.cls[lo].task_begin;
+        const unsigned long long n = P.cls[lo].n;
+        const uint32_t s = P.cls[lo].s;
+        const uint32_t* mcls = members + P.cls[lo].member_off;
+        const uint32_t* wcls = weights + P.cls[lo].weight_off;
+        if (s <= 32) {
+            const uint32_t k = P.cls[lo].k;
+            const uint32_t g = lane / s, a = lane - g * s;
+            const unsigned long long col0 = t_in * k;
+            const bool valid = g < k && col0 + g < n;
+            uint32_t x = 0, w = 0;
+            if (valid) {
+                x = __ldg(mcls + col0 * s + lane);
+                w = __ldg(wcls + col0 + g);
+            }
+            const unsigned long long ra = valid ? row_addr(x, G) : 0ull;
+            if (__ballot_sync(KSB_FULL, ra != 0ull) == 0u) continue;  // no owned row in this task
+            const unsigned long long cadd = 8ull * x;
+            const uint32_t gb = g * s;
+            for (uint32_t ar = 0; ar + 1 < s; ar++) {
+                const unsigned long long r = shfl_u64(ra, gb + ar);
+                if (valid && a > ar && r != 0ull) red_add_u64(r + cadd, w);
+            }
+        } else {
+            const uint32_t* m = mcls + t_in * s;
+            const bool v1 = lane + 32 < s;
+            const uint32_t x0 = __ldg(m + lane);
+            const uint32_t x1 = v1 ? __ldg(m + 32 + lane) : 0u;
+            const unsigned long long w = __ldg(wcls + t_in);
+            const unsigned long long ra0 = row_addr(x0, G);
+            const unsigned long long ra1 = v1 ? row_addr(x1, G) : 0ull;
+            if (__ballot_sync(KSB_FULL, (ra0 | ra1) != 0ull) == 0u) continue;
+            const unsigned long long c0 = 8ull * x0, c1 = 8ull * x1;
+#pragma unroll 4
+            for (uint32_t ar = 0; ar < 32; ar++) {
+                const unsigned long long r = shfl_u64(ra0, ar);
+                if (r != 0ull) {  // warp-uniform
+                    if (lane > ar) red_add_u64(r + c0, w);
+                    if (v1) red_add_u64(r + c1, w);
+                }
+            }
+            for (uint32_t ar = 32; ar + 1 < s; ar++) {
+                const unsigned long long r = shfl_u64(ra1, ar - 32);
+                if (r != 0ull && v1 && lane + 32 > ar) red_add_u64(r + c1, w);
+            }
+        }
+    }
+}
+
+cudaError_t launch_k1_small(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
+                            const LaunchCfg& lc) {
+    if (p.n_tasks == 0) return cudaSuccess;
+    const unsigned long long warps_per_cta = 8;
+    unsigned long long ctas = (p.n_tasks + warps_per_cta - 1) / warps_per_cta;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;  // 8 x 256 threads = 2048 resident threads / SM
+    if (ctas > cap) ctas = cap;
+    k1_small<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, members, weights, g);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: block-tiled mid/large colours (s > 64).  One CTA item = 256 columns (one per thread, kept in
+// a register) x up to 512 rows.  The rows' member ids are staged into shared memory with one TMA
+// bulk copy (cp.async.bulk + mbarrier), converted once to row addresses, then every warp sweeps the
+// rows: one shared-memory broadcast + one red per update.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    }
+}
+
+__global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ items, unsigned long long n_items,
+                                                   const unsigned long long* __restrict__ mid_off,
+                                                   const uint32_t* __restrict__ mid_sizes,
+                                                   const uint32_t* __restrict__ mid_members,
+                                                   const uint32_t* __restrict__ mid_weights,
+                                                   const __grid_constant__ TriGeom G) {
+    __shared__ __align__(128) uint32_t sm_rows[kMidRows];
+    __shared__ __align__(16) unsigned long long sm_ra[kMidRows];
+    __shared__ __align__(8) unsigned long long sm_bar;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t bar = smem_u32(&sm_bar);
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint32_t phase = 0;
+    const bool sharded = G.nrows < G.n;
+    for (unsigned long long it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const MidItem item = items[it];
+        const uint32_t s = __ldg(mid_sizes + item.color);
+        const uint32_t* m = mid_members + __ldg(mid_off + item.color);
+        const unsigned long long w = __ldg(mid_weights + item.color);
+        const uint32_t row_lim = min(s - 1u, item.b0 + kMidCols - 1u);
+        const uint32_t a_end = min(item.a0 + kMidRows, row_lim);
+        const uint32_t nr = a_end - item.a0;
+        if (sharded) {  // rows are sorted ids: reject the item when none can be owned (uniform)
+            const uint32_t first = __ldg(m + item.a0), last = __ldg(m + a_end - 1);
+            if (last < G.rb || first - G.rb >= G.nrows && first >= G.rb) continue;
+        }
+        if (tid == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            const uint32_t bytes = 4u * ((nr + 3u) & ~3u);
+            mbar_expect_tx(bar, bytes);
+            tma_load_1d(smem_u32(sm_rows), m + item.a0, bytes, bar);
+        }
+        const uint32_t b = item.b0 + tid;
+        const uint32_t x = (b < s) ? __ldg(m + b) : 0u;
+        mbar_wait(bar, phase);
+        phase ^= 1u;
+        for (uint32_t r = tid; r < nr; r += kMidCols) sm_ra[r] = row_addr(sm_rows[r], G);
+        __syncthreads();
+        // rows r with a0 + r < b pair with this thread's column
+        const uint32_t lim = (b < s && b > item.a0) ? min(nr, b - item.a0) : 0u;
+        const uint32_t wlim = __reduce_max_sync(KSB_FULL, lim);
+        const unsigned long long cadd = 8ull * x;
+#pragma unroll 4
+        for (uint32_t r = 0; r < wlim; r++) {
+            const unsigned long long ra = sm_ra[r];
+            if (ra != 0ull && r < lim) red_add_u64(ra + cadd, w);
+        }
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned long long* mid_off,
+                          const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                          const TriGeom& g, const LaunchCfg& lc) {
+    if (n_items == 0) return cudaSuccess;
+    unsigned long long ctas = n_items;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k2_mid<<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, n_items, mid_off, mid_sizes, mid_members, mid_weights, g);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kz: colours whose narrowed count is 0 still create a row in the reference (edges.try_emplace_l
+// inserts the pair with value 0, src/pairwise.cpp:222-225).  They set a bit in a touched-bitmap.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) kz_touch(unsigned long long n_zero, const unsigned long long* __restrict__ zero_off,
+                                                const uint32_t* __restrict__ zero_members, uint32_t* touched,
+                                                const __grid_constant__ TriGeom G) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long c = warp; c < n_zero; c += nwarps) {
+        const unsigned long long off = zero_off[c];
+        const uint32_t s = (uint32_t)(zero_off[c + 1] - off);
+        const uint32_t* m = zero_members + off;
+        for (uint32_t a = 0; a + 1 < s; a++) {
+            const uint32_t i = m[a];
+            if (i - G.rb >= G.nrows) continue;
+            const unsigned long long rowcell =
+                (((unsigned long long)i * (unsigned long long)(G.two_n_m1 - i)) >> 1) - i - 1ull - G.base;
+            for (uint32_t b = a + 1 + lane; b < s; b += 32) {
+                const unsigned long long cell = rowcell + m[b];
+                atomicOr(touched + (cell >> 5), 1u << (cell & 31u));
+            }
+        }
+    }
+}
+
+cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const uint32_t* zero_members,
+                            uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc) {
+    if (n_zero == 0) return cudaSuccess;
+    unsigned long long ctas = (n_zero + 7) / 8;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    kz_touch<<<(unsigned)ctas, 256, 0, lc.stream>>>(n_zero, zero_off, zero_members, touched_bits, g);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: containment + record build over the owned block (two passes: count, then emit in cell order,
+// i.e. rows sorted by (source_1, source_2)).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t k5_flags(const TriGeom& G, const uint32_t* __restrict__ touched,
+                                             unsigned long long cell0, unsigned long long v[kPostPerThread]) {
+    uint32_t flags = 0;
+    if (cell0 + kPostPerThread <= G.cells) {
+        const ulonglong2* p = reinterpret_cast<const ulonglong2*>(G.tri + cell0);
+#pragma unroll
+        for (uint32_t q = 0; q < kPostPerThread / 2; q++) {
+            const ulonglong2 t = p[q];
+            v[2 * q] = t.x;
+            v[2 * q + 1] = t.y;
+        }
+    } else {
+#pragma unroll
+        for (uint32_t q = 0; q < kPostPerThread; q++) v[q] = (cell0 + q < G.cells) ? G.tri[cell0 + q] : 0ull;
+    }
+    uint32_t tb = 0;
+    if (touched != nullptr && cell0 < G.cells) tb = (touched[cell0 >> 5] >> (cell0 & 31u)) & 0xffu;  // 8 | 32
+#pragma unroll
+    for (uint32_t q = 0; q < kPostPerThread; q++)
+        if (v[q] != 0ull || ((tb >> q) & 1u)) flags |= 1u << q;
+    if (cell0 >= G.cells) flags = 0;
+    else if (cell0 + kPostPerThread > G.cells) flags &= (1u << (uint32_t)(G.cells - cell0)) - 1u;
+    return flags;
+}
+
+__global__ void __launch_bounds__(kPostThreads) k5_count(const __grid_constant__ TriGeom G,
+                                                         const uint32_t* __restrict__ touched,
+                                                         unsigned long long* __restrict__ block_counts) {
+    __shared__ uint32_t sm[kPostThreads / 32];
+    const unsigned long long cell0 = ((unsigned long long)blockIdx.x * kPostThreads + threadIdx.x) * kPostPerThread;
+    unsigned long long v[kPostPerThread];
+    uint32_t c = __popc(k5_flags(G, touched, cell0, v));
+    c = __reduce_add_sync(KSB_FULL, c);
+    if ((threadIdx.x & 31u) == 0) sm[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (uint32_t i = 0; i < kPostThreads / 32; i++) t += sm[i];
+        block_counts[blockIdx.x] = t;
+    }
+}
+
+// float32 containment math of src/pairwise.cpp:260-264, IEEE round-to-nearest, no contraction.
+// NaNs are canonicalised to the x86 default NaN (0xFFC00000, printed "-nan" like the reference).
+__device__ __forceinline__ float canon_nan(float f) { return (f != f) ? __int_as_float(0xFFC00000) : f; }
+
+__device__ __forceinline__ void containment(unsigned long long shared, uint32_t k1, uint32_t k2, float& cmin,
+                                            float& cavg, float& cmax) {
+    const float sh = __ull2float_rn(shared);
+    const float c12 = canon_nan(__fdiv_rn(sh, __uint2float_rn(k2)));  // cont_1_in_2
+    const float c21 = canon_nan(__fdiv_rn(sh, __uint2float_rn(k1)));  // cont_2_in_1
+    cmin = (c21 < c12) ? c21 : c12;  // std::min(a,b) = (b<a) ? b : a
+    cmax = (c12 < c21) ? c21 : c12;  // std::max(a,b) = (a<b) ? b : a
+    const float sum = canon_nan(__fadd_rn(c12, c21));
+    cavg = canon_nan(__double2float_rn(__ddiv_rn((double)sum, 2.0)));
+}
+
+__global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ TriGeom G,
+                                                        const uint32_t* __restrict__ touched,
+                                                        const unsigned long long* __restrict__ block_offsets,
+                                                        const uint32_t* __restrict__ totals,
+                                                        const uint32_t* __restrict__ sample_ids,
+                                                        ksb_record* __restrict__ records,
+                                                        unsigned long long* __restrict__ pairs) {
+    __shared__ uint32_t sm[kPostThreads / 32];
+    const unsigned long long cell0 = ((unsigned long long)blockIdx.x * kPostThreads + threadIdx.x) * kPostPerThread;
+    unsigned long long v[kPostPerThread];
+    const uint32_t flags = k5_flags(G, touched, cell0, v);
+    const uint32_t c = __popc(flags);
+    // block exclusive scan of c
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    uint32_t incl = c;
+#pragma unroll
+    for (uint32_t d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(KSB_FULL, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) sm[wid] = incl;
+    __syncthreads();
+    uint32_t wbase = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < kPostThreads / 32; i++)
+        if (i < wid) wbase += sm[i];
+    if (flags == 0) return;
+    unsigned long long out = block_offsets[blockIdx.x] + wbase + (incl - c);
+    // decode (i,j) of the first cell, then walk
+    const unsigned long long g0 = G.base + cell0;
+    const double tn = (double)G.two_n_m1;
+    uint32_t i = (uint32_t)((tn - sqrt(tn * tn - 8.0 * (double)g0)) * 0.5);
+    auto rowstart = [&](uint32_t r) { return ((unsigned long long)r * (unsigned long long)(G.two_n_m1 - r)) >> 1; };
+    while (i + 1 < G.n && rowstart(i + 1) <= g0) i++;
+    while (i > 0 && rowstart(i) > g0) i--;
+    uint32_t j = i + 1 + (uint32_t)(g0 - rowstart(i));
+#pragma unroll
+    for (uint32_t q = 0; q < kPostPerThread; q++) {
+        if (j >= G.n) { i++; j = i + 1; }
+        if ((flags >> q) & 1u) {
+            float cmin, cavg, cmax;
+            containment(v[q], __ldg(totals + i), __ldg(totals + j), cmin, cavg, cmax);
+            uint4 a, b;
+            a.x = __ldg(sample_ids + i);
+            a.y = __ldg(sample_ids + j);
+            a.z = (uint32_t)v[q];
+            a.w = (uint32_t)(v[q] >> 32);
+            b.x = __float_as_uint(cmin);
+            b.y = __float_as_uint(cavg);
+            b.z = __float_as_uint(cmax);
+            b.w = 0;
+            uint4* dst = reinterpret_cast<uint4*>(records + out);
+            dst[0] = a;
+            dst[1] = b;
+            pairs[out] = ((unsigned long long)i << 32) | j;
+            out++;
+        }
+        j++;
+    }
+}
+
+cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsigned long long* block_counts,
+                            const LaunchCfg& lc) {
+    const uint64_t nb = post_blocks(g.cells);
+    if (nb == 0) return cudaSuccess;
+    k5_count<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_counts);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const unsigned long long* block_offsets,
+                           const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
+                           unsigned long long* pairs, const LaunchCfg& lc) {
+    const uint64_t nb = post_blocks(g.cells);
+    if (nb == 0) return cudaSuccess;
+    k5_emit<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_offsets, totals, sample_ids, records,
+                                                         pairs);
+    return cudaGetLastError();
+}
+
+cudaError_t scan_block_counts(void* temp, size_t* temp_bytes, const unsigned long long* in, unsigned long long* out,
+                              uint64_t n, cudaStream_t stream) {
+    return cub::DeviceScan::ExclusiveSum(temp, *temp_bytes, in, out, (int64_t)n, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6 + K7: threshold on the selected containment column and lock-free union-find (smaller root wins,
+// so the final label of a component is its smallest compact sample index).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t uf_find(uint32_t* parent, uint32_t x) {
+    volatile uint32_t* p = parent;
+    for (;;) {
+        const uint32_t px = p[x];
+        if (px == x) return x;
+        const uint32_t ppx = p[px];
+        if (ppx != px) p[x] = ppx;  // path halving
+        x = px;
+    }
+}
+
+__device__ __forceinline__ void uf_union(uint32_t* parent, uint32_t a, uint32_t b) {
+    for (;;) {
+        a = uf_find(parent, a);
+        b = uf_find(parent, b);
+        if (a == b) return;
+        if (a < b) { const uint32_t t = a; a = b; b = t; }
+        if (atomicCAS(parent + a, a, b) == a) return;
+    }
+}
+
+__global__ void __launch_bounds__(256) k67_union(const ksb_record* __restrict__ records,
+                                                 const unsigned long long* __restrict__ pairs,
+                                                 unsigned long long n_rows, int dist_col, float cstar,
+                                                 uint32_t* parent, unsigned long long* n_edges) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    uint32_t kept = 0;
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+        const float* cols = &records[r].min_containment;
+        const float c = __ldg(cols + (dist_col - 3));
+        if (c < cstar) continue;  // NaN is kept, as in `if distance < cutoff: continue`
+        const unsigned long long ij = __ldg(pairs + r);
+        uf_union(parent, (uint32_t)(ij >> 32), (uint32_t)ij);
+        kept++;
+    }
+    kept = __reduce_add_sync(KSB_FULL, kept);
+    if ((threadIdx.x & 31u) == 0 && kept) atomicAdd(n_edges, (unsigned long long)kept);
+}
+
+__global__ void k7_init(uint32_t* parent, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) parent[i] = i;
+}
+__global__ void k7_compress(uint32_t* parent, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        uint32_t r = i;
+        while (parent[r] != r) r = parent[r];
+        parent[i] = r;  // roots never change here; writing a root over an ancestor is safe
+    }
+}
+
+cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, uint64_t n_rows, int dist_col,
+                             float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc) {
+    if (n_rows == 0) return cudaSuccess;
+    unsigned long long ctas = (n_rows + 255) / 256;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k67_union<<<(unsigned)ctas, 256, 0, lc.stream>>>(records, pairs, n_rows, dist_col, cstar, parent, n_edges);
+    return cudaGetLastError();
+}
+cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc) {
+    if (n == 0) return cudaSuccess;
+    k7_init<<<(n + 255) / 256, 256, 0, lc.stream>>>(parent, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc) {
+    if (n == 0) return cudaSuccess;
+    k7_compress<<<(n + 255) / 256, 256, 0, lc.stream>>>(parent, n);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// red micro-benchmark: the roofline the accumulation kernels are measured against.
+// pattern 0: every lane a uniformly random cell; pattern 1: a random 32-cell run per warp.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long mix64(unsigned long long x) {
+    x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+    return x;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bench_red(T* buf, unsigned long long cells, unsigned long long n_ops, int pattern) {
+    const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (unsigned long long op = tid; op < n_ops; op += stride) {
+        unsigned long long cell;
+        if (pattern == 0) {
+            cell = __umul64hi(mix64(op + 0x9E3779B97F4A7C15ULL), cells);
+        } else {
+            cell = __umul64hi(mix64((op >> 5) + 0x9E3779B97F4A7C15ULL), cells - 32) + lane;
+        }
+        atomicAdd(buf + cell, (T)1);
+    }
+}
+
+cudaError_t launch_bench_red(void* buf, uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, const LaunchCfg& lc) {
+    const unsigned ctas = (unsigned)lc.sms * 8u;
+    if (cell_bits == 64)
+        bench_red<unsigned long long><<<ctas, 256, 0, lc.stream>>>((unsigned long long*)buf, cells, n_ops, pattern);
+    else
+        bench_red<unsigned int><<<ctas, 256, 0, lc.stream>>>((unsigned int*)buf, cells, n_ops, pattern);
+    return cudaGetLastError();
+}
+
+}  // namespace ksb
+
+namespace ksb {
+__global__ void __launch_bounds__(256) k7_merge(uint32_t* parent, const uint32_t* __restrict__ other, uint32_t n) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n) {
+        const uint32_t o = __ldg(other + v);
+        if (o != v) uf_union(parent, v, o);
+    }
+}
+cudaError_t launch_k7_merge(uint32_t* parent, const uint32_t* other, uint32_t n, const LaunchCfg& lc) {
+    if (n == 0) return cudaSuccess;
+    k7_merge<<<(n + 255) / 256, 256, 0, lc.stream>>>(parent, other, n);
+    return cudaGetLastError();
+}
+}  // namespace ksb

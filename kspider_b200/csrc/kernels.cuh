@@ -1,0 +1,78 @@
+// sm_100a kernels of the pairwise hot path.  Everything here is device code + thin launch helpers;
+// the C-ABI lives in device_api.cu.
+//
+// Reference semantics reproduced (dib-lab/kSpider @ 466a267):
+//   K1/K2/Kz  src/pairwise.cpp:209-225  every member pair (a<b) of a colour: edges[(min,max)] += (uint32_t)count
+//             (Combo::combinations :39-70 enumerates the pairs, ascending() :73-78 orders the ids)
+//   K5        src/pairwise.cpp:253-264  float32 containments of every touched pair
+//   K6/K7     pykSpider/kSpider2/ks_clustering.py:97-120  threshold + connected components
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "ksb_common.hpp"
+
+namespace ksb {
+
+// Geometry of the owned row block of the packed upper triangle.
+// cell(i,j), i<j  ->  i(2N-1-i)/2 + (j-i-1) - base      (rows [rb, rb+nrows) are owned)
+struct TriGeom {
+    unsigned long long* tri;   // owned cells (u64)
+    unsigned long long base;   // packed index of cell (rb, rb+1)
+    unsigned long long cells;  // owned cells
+    uint32_t two_n_m1;         // 2N-1
+    uint32_t n;                // N
+    uint32_t rb;               // first owned row
+    uint32_t nrows;            // owned rows
+};
+
+struct K1Class {
+    unsigned long long task_begin;  // first warp task of this class
+    unsigned long long n;           // colours in the class
+    unsigned long long member_off;  // u32 units into small-members
+    unsigned long long weight_off;  // u32 units into small-weights
+    uint32_t s;                     // members per colour
+    uint32_t k;                     // colours per warp task (32/s for s<=32, else 1)
+};
+struct K1Params {
+    K1Class cls[kSmallMax];
+    unsigned long long n_tasks;
+    uint32_t n_cls;
+    uint32_t pad;
+};
+
+struct LaunchCfg {
+    int sms;
+    cudaStream_t stream;
+};
+
+// launchers (return cudaError_t of the launch)
+cudaError_t launch_k1_small(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
+                            const LaunchCfg& lc);
+cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned long long* mid_off,
+                          const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                          const TriGeom& g, const LaunchCfg& lc);
+cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const uint32_t* zero_members,
+                            uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc);
+
+// K5: two passes over the owned block.  block_counts has post_blocks(cells)+1 entries.
+constexpr uint32_t kPostThreads = 256;
+constexpr uint32_t kPostPerThread = 8;
+constexpr uint32_t kPostChunk = kPostThreads * kPostPerThread;
+inline uint64_t post_blocks(uint64_t cells) { return (cells + kPostChunk - 1) / kPostChunk; }
+cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsigned long long* block_counts,
+                            const LaunchCfg& lc);
+cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const unsigned long long* block_offsets,
+                           const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
+                           unsigned long long* pairs, const LaunchCfg& lc);
+
+// K6+K7
+cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, uint64_t n_rows, int dist_col,
+                             float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc);
+cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
+cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
+
+// red micro-benchmark
+cudaError_t launch_bench_red(void* buf, uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, const LaunchCfg& lc);
+
+}  // namespace ksb

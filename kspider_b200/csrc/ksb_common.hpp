@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -15,8 +16,20 @@ void set_error(const char* fmt, ...);  // thread-local message for ksb_last_erro
 // Simple blocking parallel-for over [0,n) in contiguous chunks, one chunk per thread.
 void parallel_chunks(uint64_t n, int threads, const std::function<void(int, uint64_t, uint64_t)>& fn);
 
-constexpr uint32_t kSmallMax = 64;     // colours with 2..64 members go to the flat pair-space kernel
+constexpr uint32_t kSmallMax = 64;     // colours with 2..64 members go to the warp-per-colour kernel (K1)
 constexpr uint32_t kMaxPairsSmall = kSmallMax * (kSmallMax - 1) / 2;  // 2016
+// K2 (s > 64) work decomposition: one CTA item = kMidCols columns (threads) x up to kMidRows rows
+constexpr uint32_t kMidCols = 256;
+constexpr uint32_t kMidRows = 512;
+
+// One K2 work item: columns [b0, b0+kMidCols) x rows [a0, a0+kMidRows) of mid colour `color`
+// (positions in the colour's sorted member list; only pairs with row position < column position count).
+struct MidItem {
+    uint32_t color;  // index into the mid-colour arrays
+    uint32_t b0;
+    uint32_t a0;
+    uint32_t pad;
+};
 
 // One size class of small colours: all colours with exactly s members, stored as a dense
 // [n x s] block of (sorted, compact) member ids and an [n] block of weights.
@@ -51,9 +64,14 @@ struct IndexDesc {
     uint64_t off_row_updates;   // u64[N]   updates whose row (= smaller sample) is i
     uint64_t off_small_members; // u32[n_small_members]
     uint64_t off_small_weights; // u32[n_small_colors]
-    uint64_t off_mid_offsets;   // u64[n_mid_colors+1]
-    uint64_t off_mid_members;   // u32[n_mid_members]
+    uint64_t off_mid_offsets;   // u64[n_mid_colors+1]  start of each colour in the mid-members section,
+                                //                       always a multiple of 4 elements (16 B: TMA bulk copies)
+    uint64_t off_mid_sizes;     // u32[n_mid_colors]
+    uint64_t off_mid_members;   // u32[n_mid_members_padded]
     uint64_t off_mid_weights;   // u32[n_mid_colors]
+    uint64_t off_mid_items;     // MidItem[n_mid_items]
+    uint64_t n_mid_items;
+    uint64_t n_mid_members_padded;
     uint64_t off_zero_offsets;  // u64[n_zero_colors+1]
     uint64_t off_zero_members;  // u32[n_zero_members]
     uint64_t payload_bytes;

@@ -1,0 +1,139 @@
+// Host text side of the path: the pairwise TSV (src/pairwise.cpp:242-275), "%g" float text
+// (ostream<<float with default flags), and the synthetic index-file writer used by tests / bench.
+#include <cerrno>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "ksb_common.hpp"
+#include "phmap_format.hpp"
+
+namespace ksb {
+
+// decimal text of a u64; returns length
+static inline int u64_to_dec(uint64_t v, char* out) {
+    char tmp[24];
+    int n = 0;
+    do { tmp[n++] = (char)('0' + v % 10); v /= 10; } while (v);
+    for (int i = 0; i < n; i++) out[i] = tmp[n - 1 - i];
+    return n;
+}
+
+static const char kTsvHeader[] =
+    "source_1\tsource_2\tshared_kmers\tmin_containment\tavg_containment\tmax_containment\n";  // src/pairwise.cpp:244-251
+
+static int write_records(const ksb_record* rec, uint64_t n, FILE* f, int threads) {
+    const uint64_t kBatch = 1ull << 21;
+    if (threads < 1) threads = 1;
+    std::vector<std::string> bufs(threads);
+    for (uint64_t b0 = 0; b0 < n; b0 += kBatch) {
+        const uint64_t bn = std::min(kBatch, n - b0);
+        int used = 0;
+        parallel_chunks(bn, threads, [&](int t, uint64_t b, uint64_t e) {
+            std::string& s = bufs[t];
+            s.clear();
+            s.reserve((e - b) * 64);
+            char line[160];
+            for (uint64_t i = b; i < e; i++) {
+                const ksb_record& r = rec[b0 + i];
+                int p = 0;
+                p += u64_to_dec(r.source_1, line + p); line[p++] = '\t';
+                p += u64_to_dec(r.source_2, line + p); line[p++] = '\t';
+                p += u64_to_dec(r.shared_kmers, line + p); line[p++] = '\t';
+                p += ksb_format_float(r.min_containment, line + p); line[p++] = '\t';
+                p += ksb_format_float(r.avg_containment, line + p); line[p++] = '\t';
+                p += ksb_format_float(r.max_containment, line + p); line[p++] = '\n';
+                s.append(line, (size_t)p);
+            }
+        });
+        used = (int)std::min<uint64_t>((uint64_t)threads, bn ? bn : 1);
+        for (int t = 0; t < used; t++)
+            if (!bufs[t].empty() && fwrite(bufs[t].data(), 1, bufs[t].size(), f) != bufs[t].size()) return KSB_ERR_IO;
+        for (auto& s : bufs) s.clear();
+    }
+    return KSB_OK;
+}
+
+static int write_tsv_impl(const ksb_result* r, const char* path, int threads, bool append) {
+    if (!r || !path) { set_error("ksb_write_tsv: null argument"); return KSB_ERR_ARG; }
+    uint64_t n = 0;
+    const ksb_record* rec = ksb_result_records(r, &n);
+    ksb_result_info info;
+    ksb_result_get_info(r, &info);
+    if (info.n_rows && !rec) { set_error("ksb_write_tsv: the result holds no host records (run with want_records = 1)"); return KSB_ERR_ARG; }
+    FILE* f = fopen(path, append ? "ab" : "wb");
+    if (!f) { set_error("cannot write %s: %s", path, strerror(errno)); return KSB_ERR_IO; }
+    std::vector<char> iobuf(1 << 22);
+    setvbuf(f, iobuf.data(), _IOFBF, iobuf.size());
+    int rc = KSB_OK;
+    if (!append && fputs(kTsvHeader, f) < 0) rc = KSB_ERR_IO;
+    if (rc == KSB_OK) rc = write_records(rec, n, f, threads);
+    if (fclose(f) != 0) rc = KSB_ERR_IO;
+    if (rc == KSB_ERR_IO) set_error("write error on %s", path);
+    return rc;
+}
+
+}  // namespace ksb
+
+extern "C" {
+
+// ostream<<float with default flags == printf("%g") of the promoted value (libstdc++ num_put uses
+// __convert_from_v with "%.*g", precision 6).  nan/inf come out as "nan"/"-nan"/"inf" either way.
+int ksb_format_float(float v, char* buf) {
+    char tmp[32];
+    const int n = snprintf(tmp, sizeof tmp, "%g", (double)v);
+    std::memcpy(buf, tmp, (size_t)n);
+    return n;
+}
+
+int ksb_write_tsv(const ksb_result* r, const char* path, int host_threads) { return ksb::write_tsv_impl(r, path, host_threads, false); }
+int ksb_append_tsv(const ksb_result* r, const char* path, int host_threads) { return ksb::write_tsv_impl(r, path, host_threads, true); }
+
+int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uint64_t* color_ids, const uint64_t* offsets,
+                          const uint32_t* members, uint64_t n_counts, const uint64_t* count_ids, const uint64_t* count_vals,
+                          uint64_t n_totals, const uint32_t* total_ids, const uint32_t* total_vals) {
+    if (!index_prefix || (n_colors && (!color_ids || !offsets)) || (n_counts && (!count_ids || !count_vals)) ||
+        (n_totals && (!total_ids || !total_vals))) {
+        ksb::set_error("ksb_write_index_files: null argument");
+        return KSB_ERR_ARG;
+    }
+    const std::string P(index_prefix);
+    auto put = [&](const std::string& path, const std::vector<uint8_t>& bytes) {
+        FILE* f = fopen(path.c_str(), "wb");
+        if (!f) { ksb::set_error("cannot write %s: %s", path.c_str(), strerror(errno)); return false; }
+        const bool ok = bytes.empty() || fwrite(bytes.data(), 1, bytes.size(), f) == bytes.size();
+        if (fclose(f) != 0 || !ok) { ksb::set_error("write error on %s", path.c_str()); return false; }
+        return true;
+    };
+    try {
+        std::vector<uint8_t> out;
+        ksb::append_dump(out, total_ids, total_vals, n_totals, 4, 4);
+        if (!put(P + "_groupID_to_kmerCount.bin", out)) return KSB_ERR_IO;
+        out.clear();
+        ksb::append_dump(out, count_ids, count_vals, n_counts, 8, 8);
+        if (!put(P + "_color_count.bin", out)) return KSB_ERR_IO;
+        out.clear();
+        out.resize(8);
+        std::memcpy(out.data(), &n_colors, 8);
+        // stream the colour records in blocks so a 1 GB file does not need 2 GB of vector growth
+        FILE* f = fopen((P + "_color_to_sources.bin").c_str(), "wb");
+        if (!f) { ksb::set_error("cannot write %s_color_to_sources.bin: %s", index_prefix, strerror(errno)); return KSB_ERR_IO; }
+        bool ok = true;
+        for (uint64_t c = 0; c < n_colors && ok; c++) {
+            const size_t at = out.size();
+            out.resize(at + 8);
+            std::memcpy(&out[at], &color_ids[c], 8);
+            ksb::append_dump(out, members + offsets[c], nullptr, offsets[c + 1] - offsets[c], 4, 0);
+            if (out.size() >= (1u << 24)) { ok = fwrite(out.data(), 1, out.size(), f) == out.size(); out.clear(); }
+        }
+        if (ok && !out.empty()) ok = fwrite(out.data(), 1, out.size(), f) == out.size();
+        if (fclose(f) != 0 || !ok) { ksb::set_error("write error on %s_color_to_sources.bin", index_prefix); return KSB_ERR_IO; }
+    } catch (const std::bad_alloc&) {
+        ksb::set_error("out of host memory");
+        return KSB_ERR_NOMEM;
+    }
+    return KSB_OK;
+}
+
+}  // extern "C"
