@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py — weighted pair-updates/s of the pairwise hot path on N B200s (one process per GPU).
+
+A "step" = one pass of the hot path over the whole synthetic index with the binned CSR already
+resident in HBM: clear the owned triangle block, pair-emission kernels (K1/K2/Kz), containment +
+record compaction (K5), threshold + union-find (K6/K7) and, for N > 1, the label all-gather + merge.
+`value` = U (weighted pair-updates of the index) x steps / time, max over ranks.
+`e2e`   = the same through the host-facing call (ksb_pairwise on the pinned host CSR: H2D of the
+          blob, kernels, D2H of the records) — wall clock around the call.
+`--impl reference` times the UNMODIFIED reference (oracle/_ref/pairwise_ref = src/pairwise.cpp,
+OpenMP + parallel-hashmap) on the host cores on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "weighted_pair_updates_per_s"
+UNIT = "pair-updates/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg2_small", "cfg3", "cfg4", "cfg5"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cutoff", type=float, default=0.3)
+    ap.add_argument("--dense-budget-gb", type=float, default=0.0)
+    return ap.parse_args()
+
+
+def make_workload(name: str):
+    from kspider_b200 import synth
+    if name == "cfg2":
+        return synth.zipf_index(1000, 10_000_000, seed=12345, name="cfg2")
+    if name == "cfg2_small":
+        return synth.zipf_index(1000, 1_000_000, seed=12345, name="cfg2_small")
+    if name == "cfg3":
+        return synth.cfg3()
+    if name == "cfg4":
+        return synth.cfg4()
+    if name == "cfg5":
+        return synth.giant_index()
+    raise ValueError(name)
+
+
+WORKLOAD_DESC = {
+    "cfg2": "synthetic kProcessor-style colour table: 1k samples, 10M colours, Zipf(1.5) colour sizes 2..64 (BASELINE configs[1])",
+    "cfg2_small": "cfg2 at 1/10 scale: 1k samples, 1M colours",
+    "cfg3": "synthetic FracMinHash index: 10k genomes (200 clades x 50), sketch 5000, dense u64 triangle (BASELINE configs[2])",
+    "cfg4": "synthetic 100k-sample index (2000 clades x 50), row-block sharded triangle (BASELINE configs[3])",
+    "cfg5": "cfg2-style background + 16 giant colours of 4000 members, N = 10k (BASELINE configs[4])",
+}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        if shutil.which("nvidia-smi") is None:
+            return
+        self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                      "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        self.t = threading.Thread(target=self._read, daemon=True)
+        self.t.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for k, nme in enumerate(names):
+                if len(r) > 5 + k and r[5 + k].lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- reference / CPU arm
+
+def reference_sample(name: str):
+    """Bounded sample of the workload for the CPU reference: the same generator and seed at a colour
+    count the reference finishes in ~10-30 s on the box's cores."""
+    from kspider_b200 import synth
+    if name in ("cfg2", "cfg2_small"):
+        return synth.zipf_index(1000, 1_000_000, seed=12345, name="cfg2_sample"), \
+            "first 1/10 of the workload: same generator/seed at 1M colours (U = 1.21e8 pair-updates)"
+    if name == "cfg3":
+        return synth.fracminhash_index(n_clades=20, seed=31, name="cfg3_sample"), "20 of the 200 clades (2 of 10 families)"
+    if name == "cfg4":
+        return synth.fracminhash_index(n_clades=40, clade_size=50, sketch=1000, core=600, family_pool=400, seed=100,
+                                       name="cfg4_sample"), "40 of the 2000 clades"
+    return synth.giant_index(n_background=200_000, n_giant=4, giant_size=2000, name="cfg5_sample"), \
+        "200k background colours + 4 giant colours of 2000"
+
+
+def run_reference_once(prefix: str, threads: int) -> float:
+    from oracle import reftools
+    r = reftools.run_pairwise_ref(prefix, threads=threads, timeout=3600)
+    if r["construct_secs"] is None:
+        raise RuntimeError("reference did not print its 'pairwise hashmap construction' timer")
+    return r["construct_secs"]
+
+
+def reference_arm(args, steps: int, warmup: int) -> dict:
+    """Times oracle/_ref/pairwise_ref (unmodified src/pairwise.cpp) with all host threads; the
+    reference's own timer around its OpenMP pair loop (src/pairwise.cpp:191-239) is the clock."""
+    from kspider_b200 import synth
+    from oracle import reftools
+    if not reftools.have_ref():
+        raise RuntimeError("oracle/_ref/pairwise_ref is missing (built by __graft_entry__.build() where /root/reference exists)")
+    sample, desc = reference_sample(args.workload)
+    threads = max(1, min(os.cpu_count() or 1, 128))
+    td = tempfile.mkdtemp(prefix="ksb_ref_")
+    try:
+        prefix = os.path.join(td, sample.name)
+        synth.write_index_files(sample, prefix, with_names=False)
+        secs = []
+        for i in range(warmup + steps):
+            s = run_reference_once(prefix, threads)
+            if i >= warmup:
+                secs.append(s)
+    finally:
+        shutil.rmtree(td, ignore_errors=True)
+    t = float(np.mean(secs))
+    return {"value": sample.n_updates / t, "unit": UNIT, "cores": threads, "kind": "reference",
+            "sample": f"{desc}; {len(secs)} timed run(s) of the reference's own 'pairwise hashmap construction' timer, "
+                      f"{t:.2f} s each", "secs": t, "updates": sample.n_updates}
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 3))      # each step is a ~10-30 s CPU run: keep the arm within minutes
+    warmup = 1 if args.warmup > 0 else 0
+    cb = reference_arm(args, steps, warmup)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": warmup, "ms_per_step": cb["secs"] * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[args.workload], "name": args.workload, "sample": cb["sample"]},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------- B200 arm
+
+def main_b200(args):
+    import torch
+    import torch.distributed as dist
+    from kspider_b200 import Index, bench_red
+    from kspider_b200 import distributed as kd
+    from kspider_b200.capi import check, lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != max(1, args.gpus) and rank == 0:
+        print(f"warning: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
+    check(lib().ksb_cuda_available())
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    budget = int(args.dense_budget_gb * 1e9)
+
+    # ---- synthetic index: generated and parsed on rank 0 only, blob broadcast once
+    idx = None
+    shape = np.zeros(8, dtype=np.int64)
+    if rank == 0:
+        s = make_workload(args.workload)
+        idx = Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals,
+                             host_threads=min(32, os.cpu_count() or 1))
+        inf = idx.info
+        sizes = np.diff(s.offsets).astype(np.int64)
+        upd = sizes * (sizes - 1) // 2
+        small = (sizes >= 2) & (sizes <= 64)
+        shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, int(upd[small].sum()),
+                    int(sizes[small].sum()), int(small.sum()), inf.payload_bytes]
+        del s
+    if world > 1:
+        t = torch.from_numpy(shape).to(device)
+        dist.broadcast(t, 0)
+        shape = t.cpu().numpy()
+        desc, d_payload = kd.broadcast_blob(idx, device, 0)
+        dev = kd.adopt(desc, d_payload, dense_budget_bytes=budget)
+    else:
+        dev = idx.upload(device=local_rank, dense_budget_bytes=budget)
+    N, C_, M, U, U_small, M_small, C_small, payload_bytes = (int(v) for v in shape)
+
+    def step():
+        res = dev.run_all_passes(want_records=False)
+        labels, ne = res.cluster(N, "max_cont", args.cutoff)
+        if world > 1:
+            labels = kd.merge_labels(labels, device)
+        launches = res.info.gpu_launches
+        rows = res.info.n_rows
+        res.close()
+        return launches, rows, ne
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    t_before = dev.info.t
+    l_before = dev.info.gpu_launches
+    before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "accumulate_ms", "post_ms")}
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    w0 = time.perf_counter()
+    launches = 0
+    for _ in range(args.steps):
+        l, rows, n_edges = step()
+        launches = l
+    ev1.record()
+    torch.cuda.synchronize()
+    wall_ms = (time.perf_counter() - w0) * 1e3
+    dev_ms = ev0.elapsed_time(ev1)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    t_after = dev.info.t
+    phase = {k: (getattr(t_after, k) - before[k]) / args.steps for k in before}
+    # launches: the result's counter is cumulative over the device handle (+ the cluster kernels of the last step)
+    per_step_launches = (dev.info.gpu_launches - l_before) / args.steps + (launches - dev.info.gpu_launches)
+    ms = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms = (float(v) for v in ms.cpu())
+    ms_per_step = dev_ms / args.steps
+    value = U / (ms_per_step * 1e-3)
+
+    # ---- end to end through the host-facing call (host CSR in pinned memory -> records on the host)
+    e2e = None
+    if not args.no_e2e:
+        n_e2e = max(1, min(args.steps, 5))
+        d2h = 0
+
+        def e2e_step():
+            nonlocal d2h
+            if world == 1:
+                res = idx.pairwise(device=local_rank, want_records=True, dense_budget_bytes=budget)
+            else:
+                desc2, pay2 = kd.broadcast_blob(idx, device, 0)
+                dv = kd.adopt(desc2, pay2, dense_budget_bytes=budget)
+                res = dv.run_all_passes(want_records=True)
+            labels, _ = res.cluster(N, "max_cont", args.cutoff)
+            if world > 1:
+                labels = kd.merge_labels(labels, device)
+            d2h = res.info.n_rows * 32 + 4 * N
+            res.close()
+            if world > 1:
+                dv.close()
+
+        e2e_step()
+        barrier()
+        w0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        e_ms = torch.tensor([(time.perf_counter() - w0) * 1e3 / n_e2e], dtype=torch.float64, device=device)
+        d2h_t = torch.tensor([d2h], dtype=torch.int64, device=device)
+        if world > 1:
+            dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(d2h_t, op=dist.ReduceOp.SUM)
+        e2e = {"value": U / (float(e_ms.cpu()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": payload_bytes,
+               "d2h_bytes_per_step": int(d2h_t.cpu()), "ms_per_step": float(e_ms.cpu()), "steps": n_e2e,
+               "timer": "host wall clock around ksb_pairwise + ksb_cluster (synchronous calls)"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (rank 0's launch; algorithmic bytes per SURVEY 8d)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    own_frac = dev.info.n_updates / U if U else 1.0
+    if phase["small_ms"] >= phase["mid_ms"]:
+        kname, k_ms = "k1_small", phase["small_ms"]
+        k_bytes = 16 * U_small * own_frac + 4 * M_small + 4 * C_small
+        k_upd = U_small * own_frac
+    else:
+        kname, k_ms = "k2_mid", phase["mid_ms"]
+        k_bytes = 16 * (U - U_small) * own_frac + 4 * (M - M_small) + 12 * (C_ - C_small)
+        k_upd = (U - U_small) * own_frac
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(kname)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "kernel_ms": k_ms, "algorithmic_bytes": k_bytes,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
+                "updates_per_s": k_upd / (k_ms * 1e-3) if k_ms > 0 else 0.0}
+    # in-run red.global.add.u64 ceiling on a buffer of the owned block's size
+    red = None
+    try:
+        cells = max(dev.info.owned_cells, 1024)
+        n_ops = 1 << 28
+        red = {}
+        for pat, nm in ((0, "random"), (1, "warp_contiguous")):
+            red[nm + "_ops_per_s"] = n_ops / (bench_red(cells, n_ops, 64, pat, 3) * 1e-3)
+        red["cells"] = cells
+        red["kernel_frac_of_warp_contiguous"] = roofline["updates_per_s"] / red["warp_contiguous_ops_per_s"]
+    except Exception as e:  # the micro-benchmark is informative only
+        red = {"error": str(e)}
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            cb = reference_arm(args, 1, 0)
+            cpu = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as e:
+            cpu = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": WORKLOAD_DESC[args.workload], "name": args.workload, "samples": N, "colors": C_,
+                       "members": M, "pair_updates": U, "rows": rows, "edges": int(n_edges), "cutoff": args.cutoff,
+                       "parallelism": f"row-blocks x{world}", "passes": dev.n_passes,
+                       "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the triangle block is cleared every step)"},
+            "phases_ms": phase, "wall_ms_per_step": wall_ms / args.steps,
+            "timer": "torch.cuda.Event pair on the current stream around the K steps (every library call is stream-synchronous); phases: library CUDA events on the launching stream",
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(round(per_step_launches * args.steps)),
+            "roofline": roofline, "red_roofline": red, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        main_reference(a)
+    else:
+        main_b200(a)

@@ -130,6 +130,9 @@ const uint32_t* ksb_index_totals(const ksb_index* ix);
 /* the binned CSR blob + its fixed-size descriptor: what another rank needs to adopt the index */
 const void* ksb_index_payload(const ksb_index* ix, uint64_t* bytes);
 const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes);
+/* row-block ownership for `world` GPUs: cuts_out[world+1], rank r owns triangle rows
+ * [cuts[r], cuts[r+1]) (compact sample indices), balanced by weighted pair-updates */
+int ksb_index_row_cuts(const ksb_index* ix, int world, uint64_t* cuts_out);
 int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path);
 void ksb_index_free(ksb_index* ix);
 
@@ -145,6 +148,8 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
 int ksb_accumulate(ksb_device* dev, void* stream, int sync);
 /* device pointer of the owned block of the packed upper triangle (u64 cells) */
 void* ksb_device_triangle(const ksb_device* dev, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end);
+/* copies the current pass's block to host memory (cells must equal the pass's cell count) */
+int ksb_device_read_triangle(const ksb_device* dev, uint64_t* host_out, uint64_t cells);
 /* When the owned row block does not fit dense_budget_bytes it is processed in several dense passes
  * (sub-blocks of rows): select one with ksb_device_set_pass before ksb_accumulate / ksb_postpass. */
 int ksb_device_n_passes(const ksb_device* dev);
@@ -172,6 +177,10 @@ int ksb_append_tsv(const ksb_result* r, const char* path, int host_threads);
  * blocks be merged: pass the labels of the previous block in, get the merged labels out. */
 int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* labels_out,
                 uint64_t* n_edges);
+/* same with the threshold already in percent, i.e. the reference's Clusters(cut_off_threshold=...)
+ * constructor argument (ks_clustering.py:22,157: float(cutoff) * 100) */
+int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges);
+float ksb_threshold_float_pct(double cut_pct);
 int ksb_cluster_merge(uint64_t n, const uint32_t* labels_a, const uint32_t* labels_b, uint32_t* labels_out);
 /* same on DEVICE buffers of the current device (e.g. the output of an NCCL all-gather):
  * d_labels_all is [world][n], merged labels land in d_out[n]; stream is a cudaStream_t (NULL = default) */
@@ -180,6 +189,11 @@ int ksb_cluster_merge_device(uint64_t n, int world, const uint32_t* d_labels_all
  * (strtod("%g" of c) * 100 >= cutoff01 * 100); exposed for tests */
 float ksb_threshold_float(double cutoff01);
 void ksb_result_free(ksb_result* r);
+
+/* ---- drop-in ------------------------------------------------------------------------------ */
+/* kSpider::pairwise(std::string index_prefix, int user_threads) (include/kSpider.hpp:11) behind a
+ * C signature: load -> pairwise on KSPIDER_GPUS devices -> both TSVs, same stdout lines. */
+int ksb_dropin_pairwise(const char* index_prefix, int user_threads);
 
 /* ---- text ---------------------------------------------------------------------------------- */
 /* ostream<<float of the reference = "%g": writes at most 16 bytes, returns length (no NUL). */

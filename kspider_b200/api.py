@@ -1,0 +1,268 @@
+"""Thin object layer over the C-ABI: Index (host CSR), Device (resident CSR + owned triangle
+block), Result (records / labels).  Everything that computes happens inside libkspider_b200.so."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import capi
+from .capi import IndexInfo, Opts, Record, ResultInfo, check, lib
+
+RECORD_DTYPE = np.dtype([("source_1", "<u4"), ("source_2", "<u4"), ("shared_kmers", "<u8"),
+                         ("min_containment", "<f4"), ("avg_containment", "<f4"), ("max_containment", "<f4"),
+                         ("pad", "<u4")])
+assert RECORD_DTYPE.itemsize == C.sizeof(Record) == 32
+
+DIST_COL = {"min_cont": 3, "avg_cont": 4, "max_cont": 5}  # ks_clustering.py:12-17 ("ani": 6 is a next-row)
+
+
+def _view(ptr: int, n: int, dtype) -> np.ndarray:
+    dt = np.dtype(dtype)
+    if n == 0 or not ptr:
+        return np.empty(0, dtype=dt)
+    buf = (C.c_char * (n * dt.itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dt)
+
+
+def make_opts(device: int = -1, rank: int = 0, world: int = 1, want_records: bool = True,
+              dense_budget_bytes: int = 0) -> Opts:
+    o = Opts()
+    o.device, o.rank, o.world = device, rank, world
+    o.want_records = 1 if want_records else 0
+    o.dense_budget_bytes = int(dense_budget_bytes)
+    return o
+
+
+class Index:
+    """Parsed index = the state of the reference after src/pairwise.cpp:194."""
+
+    def __init__(self, handle: C.c_void_p):
+        self._h = handle
+
+    @classmethod
+    def load(cls, index_prefix: str, host_threads: int = 1) -> "Index":
+        h = C.c_void_p()
+        check(lib().ksb_index_load(str(index_prefix).encode(), int(host_threads), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def from_csr(cls, offsets, members, weights, total_ids, total_vals, host_threads: int = 1) -> "Index":
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        members = np.ascontiguousarray(members, dtype=np.uint32)
+        weights = np.ascontiguousarray(weights, dtype=np.uint32)
+        total_ids = np.ascontiguousarray(total_ids, dtype=np.uint32)
+        total_vals = np.ascontiguousarray(total_vals, dtype=np.uint32)
+        if offsets.size < 1 or weights.size != offsets.size - 1 or total_ids.size != total_vals.size:
+            raise ValueError("inconsistent CSR arrays")
+        h = C.c_void_p()
+        check(lib().ksb_index_from_csr(offsets.size - 1, offsets.ctypes.data, members.ctypes.data,
+                                       weights.ctypes.data, total_ids.size, total_ids.ctypes.data,
+                                       total_vals.ctypes.data, int(host_threads), C.byref(h)))
+        return cls(h)
+
+    @property
+    def info(self) -> IndexInfo:
+        inf = IndexInfo()
+        check(lib().ksb_index_get_info(self._h, C.byref(inf)))
+        return inf
+
+    @property
+    def sample_ids(self) -> np.ndarray:
+        return _view(lib().ksb_index_sample_ids(self._h), self.info.n_samples, np.uint32).copy()
+
+    @property
+    def totals(self) -> np.ndarray:
+        return _view(lib().ksb_index_totals(self._h), self.info.n_samples, np.uint32).copy()
+
+    def payload(self) -> np.ndarray:
+        """The binned CSR blob (view, valid while the Index lives)."""
+        n = C.c_uint64()
+        p = lib().ksb_index_payload(self._h, C.byref(n))
+        return _view(p, n.value, np.uint8)
+
+    def descriptor(self) -> bytes:
+        n = C.c_uint64()
+        p = lib().ksb_index_descriptor(self._h, C.byref(n))
+        return C.string_at(p, n.value)
+
+    def row_cuts(self, world: int) -> np.ndarray:
+        cuts = np.empty(world + 1, dtype=np.uint64)
+        check(lib().ksb_index_row_cuts(self._h, int(world), cuts.ctypes.data))
+        return cuts
+
+    def write_seq_to_kmers(self, path: str) -> None:
+        check(lib().ksb_write_seq_to_kmers(self._h, str(path).encode()))
+
+    def upload(self, **kw) -> "Device":
+        o = make_opts(**kw)
+        h = C.c_void_p()
+        check(lib().ksb_upload(self._h, C.byref(o), C.byref(h)))
+        return Device(h)
+
+    def pairwise(self, **kw) -> "Result":
+        o = make_opts(**kw)
+        h = C.c_void_p()
+        check(lib().ksb_pairwise(self._h, C.byref(o), C.byref(h)))
+        return Result(h)
+
+    def close(self) -> None:
+        if self._h:
+            lib().ksb_index_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Device:
+    def __init__(self, handle: C.c_void_p, keepalive=None):
+        self._h = handle
+        self._keep = keepalive  # e.g. the torch tensor holding an adopted payload
+
+    @classmethod
+    def adopt(cls, descriptor: bytes, d_payload_ptr: int, payload_bytes: int, keepalive=None, **kw) -> "Device":
+        o = make_opts(**kw)
+        h = C.c_void_p()
+        buf = C.create_string_buffer(descriptor, len(descriptor))
+        check(lib().ksb_adopt_device_payload(buf, len(descriptor), C.c_void_p(d_payload_ptr), payload_bytes,
+                                             C.byref(o), C.byref(h)))
+        return cls(h, keepalive)
+
+    @property
+    def n_passes(self) -> int:
+        return lib().ksb_device_n_passes(self._h)
+
+    def set_pass(self, p: int) -> None:
+        check(lib().ksb_device_set_pass(self._h, p))
+
+    def accumulate(self, stream: int = 0, sync: bool = True) -> None:
+        check(lib().ksb_accumulate(self._h, C.c_void_p(stream) if stream else None, 1 if sync else 0))
+
+    @property
+    def info(self) -> ResultInfo:
+        inf = ResultInfo()
+        check(lib().ksb_device_get_info(self._h, C.byref(inf)))
+        return inf
+
+    def triangle(self):
+        """(device pointer, cells, row_begin, row_end) of the current pass."""
+        c, rb, re = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        p = lib().ksb_device_triangle(self._h, C.byref(c), C.byref(rb), C.byref(re))
+        return p, c.value, rb.value, re.value
+
+    def read_triangle(self) -> np.ndarray:
+        _, cells, _, _ = self.triangle()
+        out = np.empty(cells, dtype=np.uint64)
+        check(lib().ksb_device_read_triangle(self._h, out.ctypes.data, cells))
+        return out
+
+    def postpass(self, want_records: bool = True, into: Optional["Result"] = None) -> "Result":
+        h = into._h if into is not None else C.c_void_p()
+        check(lib().ksb_postpass(self._h, 1 if want_records else 0, C.byref(h)))
+        if into is not None:
+            return into
+        return Result(h)
+
+    def run_all_passes(self, want_records: bool = True) -> "Result":
+        res = None
+        for p in range(self.n_passes):
+            self.set_pass(p)
+            self.accumulate(sync=True)
+            res = self.postpass(want_records, into=res)
+        return res
+
+    def close(self) -> None:
+        if self._h:
+            lib().ksb_device_free(self._h)
+            self._h = None
+            self._keep = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Result:
+    def __init__(self, handle: C.c_void_p):
+        self._h = handle
+
+    @property
+    def info(self) -> ResultInfo:
+        inf = ResultInfo()
+        check(lib().ksb_result_get_info(self._h, C.byref(inf)))
+        return inf
+
+    def records(self) -> np.ndarray:
+        n = C.c_uint64()
+        p = lib().ksb_result_records(self._h, C.byref(n))
+        return _view(p, n.value, RECORD_DTYPE).copy()
+
+    def write_tsv(self, path: str, host_threads: int = 1, append: bool = False) -> None:
+        fn = lib().ksb_append_tsv if append else lib().ksb_write_tsv
+        check(fn(self._h, str(path).encode(), int(host_threads)))
+
+    def cluster(self, n_samples: int, dist_type: str = "max_cont", cutoff01: float = 0.0, cut_pct=None):
+        """labels[N] (label = smallest compact sample index of the component), number of kept edges.
+        cut_pct (the reference's cut_off_threshold = float(cutoff)*100) overrides cutoff01."""
+        labels = np.empty(n_samples, dtype=np.uint32)
+        ne = C.c_uint64()
+        if cut_pct is None:
+            check(lib().ksb_cluster(self._h, DIST_COL[dist_type], float(cutoff01), labels.ctypes.data, C.byref(ne)))
+        else:
+            check(lib().ksb_cluster_pct(self._h, DIST_COL[dist_type], float(cut_pct), labels.ctypes.data, C.byref(ne)))
+        return labels, ne.value
+
+    def close(self) -> None:
+        if self._h:
+            lib().ksb_result_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def threshold_float(cutoff01: float) -> float:
+    return float(lib().ksb_threshold_float(float(cutoff01)))
+
+
+def format_float(v: float) -> str:
+    buf = C.create_string_buffer(32)
+    n = lib().ksb_format_float(C.c_float(v), buf)
+    return buf.raw[:n].decode()
+
+
+def cluster_merge(labels_a: np.ndarray, labels_b: np.ndarray) -> np.ndarray:
+    a = np.ascontiguousarray(labels_a, dtype=np.uint32)
+    b = np.ascontiguousarray(labels_b, dtype=np.uint32)
+    out = np.empty_like(a)
+    check(lib().ksb_cluster_merge(a.size, a.ctypes.data, b.ctypes.data, out.ctypes.data))
+    return out
+
+
+def write_index_files(prefix: str, color_ids, offsets, members, count_ids, count_vals, total_ids, total_vals) -> None:
+    color_ids = np.ascontiguousarray(color_ids, dtype=np.uint64)
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    members = np.ascontiguousarray(members, dtype=np.uint32)
+    count_ids = np.ascontiguousarray(count_ids, dtype=np.uint64)
+    count_vals = np.ascontiguousarray(count_vals, dtype=np.uint64)
+    total_ids = np.ascontiguousarray(total_ids, dtype=np.uint32)
+    total_vals = np.ascontiguousarray(total_vals, dtype=np.uint32)
+    check(lib().ksb_write_index_files(str(prefix).encode(), color_ids.size, color_ids.ctypes.data, offsets.ctypes.data,
+                                      members.ctypes.data, count_ids.size, count_ids.ctypes.data, count_vals.ctypes.data,
+                                      total_ids.size, total_ids.ctypes.data, total_vals.ctypes.data))
+
+
+def bench_red(cells: int, n_ops: int, cell_bits: int = 64, pattern: int = 0, reps: int = 5) -> float:
+    ms = C.c_float()
+    check(lib().ksb_bench_red(int(cells), int(n_ops), cell_bits, pattern, reps, C.byref(ms)))
+    return ms.value

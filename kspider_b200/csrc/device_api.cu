@@ -135,17 +135,7 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     const uint64_t U = d->desc.n_updates;
     const int W = std::max(1, d->world);
     std::vector<uint64_t> cut(W + 1, N);
-    cut[0] = 0;
-    {
-        uint64_t acc = 0;
-        int r = 1;
-        for (uint64_t i = 0; i < N && r < W; i++) {
-            acc += row_updates[i];
-            // rank r starts after the first row at which the prefix reaches r/W of the updates
-            while (r < W && (unsigned __int128)acc * W >= (unsigned __int128)U * r) cut[r++] = i + 1;
-        }
-        cut[W] = N;
-    }
+    row_cuts(row_updates, N, U, W, cut.data());
     d->row_begin = cut[d->rank];
     d->row_end = cut[d->rank + 1];
     if (d->rank == W - 1) d->row_end = N;
@@ -358,6 +348,16 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     return KSB_OK;
 }
 
+int ksb_device_read_triangle(const ksb_device* d, uint64_t* host_out, uint64_t cells) {
+    if (!d || (!host_out && cells)) { set_error("ksb_device_read_triangle: null argument"); return KSB_ERR_ARG; }
+    const ksb_pass& p = d->passes[d->cur_pass];
+    if (cells != p.cells) { set_error("ksb_device_read_triangle: the current pass has %llu cells, caller asked for %llu", (unsigned long long)p.cells, (unsigned long long)cells); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(d->device));
+    KSB_CUDA(cudaStreamSynchronize(d->stream));
+    if (cells) KSB_CUDA(cudaMemcpy(host_out, d->d_tri, 8 * cells, cudaMemcpyDeviceToHost));
+    return KSB_OK;
+}
+
 void* ksb_device_triangle(const ksb_device* d, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end) {
     if (!d) return nullptr;
     const ksb_pass& p = d->passes[d->cur_pass];
@@ -524,8 +524,11 @@ int ksb_format_float(float v, char* buf);
 // ks_clustering.py:97-105: the edge is dropped iff float(text) * 100 < float(cutoff) * 100 where
 // text is the "%g" rendering of the float32 containment.  Both steps are monotone non-decreasing
 // in the float, so the kept set is {c >= c*}: binary search of the bit pattern over [+0, +inf].
-float ksb_threshold_float(double cutoff01) {
-    const double cut = cutoff01 * 100.0;
+float ksb_threshold_float_pct(double cut);
+float ksb_threshold_float(double cutoff01) { return ksb_threshold_float_pct(cutoff01 * 100.0); }
+
+// cut = the reference's cut_off_threshold, already in percent (= float(cutoff) * 100)
+float ksb_threshold_float_pct(double cut) {
     auto kept = [&](uint32_t bits) {
         float c;
         std::memcpy(&c, &bits, 4);
@@ -547,7 +550,12 @@ float ksb_threshold_float(double cutoff01) {
     return c;
 }
 
+int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges);
 int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* labels_out, uint64_t* n_edges) {
+    return ksb_cluster_pct(r, dist_col, cutoff01 * 100.0, labels_out, n_edges);
+}
+
+int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges) {
     if (!r || !labels_out) { set_error("ksb_cluster: null argument"); return KSB_ERR_ARG; }
     if (dist_col < 3 || dist_col > 5) { set_error("ksb_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
     int sms = 0;
@@ -556,7 +564,7 @@ int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* la
     const uint32_t N = (uint32_t)r->n_samples;
     if (n_edges) *n_edges = 0;
     if (N == 0) return KSB_OK;
-    float cstar = ksb_threshold_float(cutoff01);
+    float cstar = ksb_threshold_float_pct(cut_pct);
     if (cstar != cstar) cstar = INFINITY;  // keep NaN rows only: c < inf drops every number... except inf itself
     uint32_t* d_parent = nullptr;
     unsigned long long* d_edges = nullptr;

@@ -79,3 +79,18 @@ void pairwise(std::string index_prefix, int user_threads) {
 }
 
 }  // namespace kSpider
+
+// C-ABI door to the drop-in for hosts that cannot pass a std::string by value (ctypes, cgo ...):
+// what a SWIG/pybind `_kSpider_internal.pairwise` wrapper would call.  Returns KSB_OK or a negative
+// code with the exception text in ksb_last_error().
+extern "C" int ksb_dropin_pairwise(const char* index_prefix, int user_threads) {
+    if (!index_prefix) { ksb::set_error("ksb_dropin_pairwise: null prefix"); return KSB_ERR_ARG; }
+    try {
+        kSpider::pairwise(std::string(index_prefix), user_threads);
+    } catch (const std::exception& e) {
+        const std::string msg = e.what();
+        ksb::set_error("%s", msg.c_str());
+        return msg.find("CUDA") != std::string::npos || msg.find("GPU") != std::string::npos ? KSB_ERR_CUDA : KSB_ERR_IO;
+    }
+    return KSB_OK;
+}

@@ -51,6 +51,20 @@ void parallel_chunks(uint64_t n, int threads, const std::function<void(int, uint
     for (auto& th : pool) th.join();
 }
 
+void row_cuts(const uint64_t* row_updates, uint64_t N, uint64_t U, int W, uint64_t* cut) {
+    if (W < 1) W = 1;
+    for (int r = 0; r <= W; r++) cut[r] = N;
+    cut[0] = 0;
+    uint64_t acc = 0;
+    int r = 1;
+    for (uint64_t i = 0; i < N && r < W; i++) {
+        acc += row_updates[i];
+        // rank r starts after the first row at which the prefix reaches r/W of the updates
+        while (r < W && (unsigned __int128)acc * (unsigned)W >= (unsigned __int128)U * (unsigned)r) cut[r++] = i + 1;
+    }
+    cut[W] = N;
+}
+
 // u32 id -> u32 value lookup; direct array when ids are small, open addressing otherwise.
 class IdTable {
 public:
@@ -562,6 +576,13 @@ const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes) {
     if (!ix) return nullptr;
     if (bytes) *bytes = sizeof(ksb::IndexDesc);
     return &ix->desc;
+}
+
+int ksb_index_row_cuts(const ksb_index* ix, int world, uint64_t* cuts_out) {
+    if (!ix || !cuts_out || world < 1) { ksb::set_error("ksb_index_row_cuts: bad argument"); return KSB_ERR_ARG; }
+    ksb::row_cuts(reinterpret_cast<const uint64_t*>(ix->payload + ix->desc.off_row_updates), ix->desc.n_samples,
+                  ix->desc.n_updates, world, cuts_out);
+    return KSB_OK;
 }
 
 int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path) {

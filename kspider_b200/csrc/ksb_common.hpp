@@ -16,6 +16,10 @@ void set_error(const char* fmt, ...);  // thread-local message for ksb_last_erro
 // Simple blocking parallel-for over [0,n) in contiguous chunks, one chunk per thread.
 void parallel_chunks(uint64_t n, int threads, const std::function<void(int, uint64_t, uint64_t)>& fn);
 
+// Row-block ownership: cut[r] = first triangle row of rank r (cut[0] = 0, cut[W] = N), chosen so
+// that every rank gets ~U/W weighted pair-updates (row_updates[i] = updates whose smaller sample is i).
+void row_cuts(const uint64_t* row_updates, uint64_t n_samples, uint64_t n_updates, int world, uint64_t* cut);
+
 constexpr uint32_t kSmallMax = 64;     // colours with 2..64 members go to the warp-per-colour kernel (K1)
 constexpr uint32_t kMaxPairsSmall = kSmallMax * (kSmallMax - 1) / 2;  // 2016
 // K2 (s > 64) work decomposition: one CTA item = kMidCols columns (threads) x up to kMidRows rows
