@@ -63,7 +63,7 @@ CASES = {
     "mid_colors": lambda: from_csr(random_csr(13, 400, 200, 2, 40, big=(65, 66, 130, 257, 399))),
     "wide_counts": lambda: from_csr(random_csr(14, 50, 200, 2, 8), wide_ids=True),
 }
-KEEP_BINS = {"micro_kat", "small_dense"}
+KEEP_BINS = set(CASES)
 
 
 def main():
