@@ -133,6 +133,9 @@ const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes);
 /* row-block ownership for `world` GPUs: cuts_out[world+1], rank r owns triangle rows
  * [cuts[r], cuts[r+1]) (compact sample indices), balanced by weighted pair-updates */
 int ksb_index_row_cuts(const ksb_index* ix, int world, uint64_t* cuts_out);
+/* the same from a (descriptor, HOST payload) pair, for ranks that received the blob by broadcast */
+int ksb_blob_row_cuts(const void* descriptor, uint64_t descriptor_bytes, const void* payload, uint64_t payload_bytes,
+                      int world, uint64_t* cuts_out);
 int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path);
 void ksb_index_free(ksb_index* ix);
 

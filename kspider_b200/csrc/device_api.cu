@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -86,6 +87,17 @@ static TriGeom geom_of(const ksb_device* d, const ksb_pass& p) {
     return g;
 }
 
+// Per-ordinal state that is expensive to (re)create: properties, a service stream for results and
+// clustering, two events, and the stream-ordered memory pool configured to keep its memory.
+struct DevCtx {
+    bool ready = false;
+    int major = 0, sms = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+static DevCtx g_ctx[64];
+static std::mutex g_ctx_mu;
+
 static int check_device(int device, int* sms) {
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -95,15 +107,31 @@ static int check_device(int device, int* sms) {
         return KSB_ERR_CUDA;
     }
     if (device < 0) KSB_CUDA(cudaGetDevice(&device));
-    if (device >= n) { set_error("device %d out of range (%d devices)", device, n); return KSB_ERR_ARG; }
-    cudaDeviceProp prop;
-    KSB_CUDA(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10) {
-        set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    if (device >= n || device >= 64) { set_error("device %d out of range (%d devices)", device, n); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(device));
+    DevCtx& c = g_ctx[device];
+    {
+        std::lock_guard<std::mutex> lk(g_ctx_mu);
+        if (!c.ready) {
+            KSB_CUDA(cudaDeviceGetAttribute(&c.major, cudaDevAttrComputeCapabilityMajor, device));
+            KSB_CUDA(cudaDeviceGetAttribute(&c.sms, cudaDevAttrMultiProcessorCount, device));
+            if (c.major == 10) {
+                KSB_CUDA(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+                KSB_CUDA(cudaEventCreate(&c.e0));
+                KSB_CUDA(cudaEventCreate(&c.e1));
+                cudaMemPool_t pool;
+                KSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+                uint64_t keep = UINT64_MAX;  // freed blocks stay in the pool: a step re-uses them
+                KSB_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+            }
+            c.ready = true;
+        }
+    }
+    if (c.major != 10) {
+        set_error("device %d is sm_%dx; this library is built for sm_100a only", device, c.major);
         return KSB_ERR_CUDA;
     }
-    KSB_CUDA(cudaSetDevice(device));
-    if (sms) *sms = prop.multiProcessorCount;
+    if (sms) *sms = c.sms;
     return device;
 }
 
@@ -173,7 +201,7 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
 static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_opts* opts) {
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
-    KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    if (!d->stream) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     for (auto& e : d->ev) KSB_CUDA(cudaEventCreate(&e));
     uint64_t budget = opts ? opts->dense_budget_bytes : 0;
     if (budget == 0) {
@@ -184,16 +212,46 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
     int rc = plan_rows(d, row_updates, budget);
     if (rc) return rc;
     const uint64_t cells = d->tri_cells_alloc;
-    KSB_CUDA(cudaMalloc(&d->d_tri, 8 * (cells + 8)));
-    if (d->desc.n_zero_colors) KSB_CUDA(cudaMalloc(&d->d_touched, 4 * (cells / 32 + 2)));
+    KSB_CUDA(cudaMallocAsync(&d->d_tri, 8 * (cells + 8), d->stream));
+    if (d->desc.n_zero_colors) KSB_CUDA(cudaMallocAsync(&d->d_touched, 4 * (cells / 32 + 2), d->stream));
     d->post_blocks_alloc = post_blocks(cells) + 1;
-    KSB_CUDA(cudaMalloc(&d->d_block_counts, 8 * d->post_blocks_alloc * 2));
+    KSB_CUDA(cudaMallocAsync(&d->d_block_counts, 8 * d->post_blocks_alloc * 2, d->stream));
     d->scan_tmp_bytes = 0;
     KSB_CUDA(scan_block_counts(nullptr, &d->scan_tmp_bytes, d->d_block_counts, d->d_block_counts + d->post_blocks_alloc,
                                d->post_blocks_alloc, d->stream));
-    KSB_CUDA(cudaMalloc(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256)));
+    KSB_CUDA(cudaMallocAsync(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256), d->stream));
     build_k1(d);
     return KSB_OK;
+}
+
+// One-slot cache of pinned host memory: cudaMallocHost costs ~0.3 ms per MB, a result's record
+// buffer is re-used by the next run of the same shape.
+static std::mutex g_pin_mu;
+static void* g_pin_ptr = nullptr;
+static uint64_t g_pin_bytes = 0;
+
+static cudaError_t pinned_acquire(void** out, uint64_t* bytes) {
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        if (g_pin_ptr && g_pin_bytes >= *bytes) {
+            *out = g_pin_ptr;
+            *bytes = g_pin_bytes;
+            g_pin_ptr = nullptr;
+            g_pin_bytes = 0;
+            return cudaSuccess;
+        }
+    }
+    return cudaMallocHost(out, *bytes);
+}
+
+static void pinned_release(void* p, uint64_t bytes) {
+    void* drop = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        if (bytes > g_pin_bytes) { drop = g_pin_ptr; g_pin_ptr = p; g_pin_bytes = bytes; }
+        else drop = p;
+    }
+    if (drop) cudaFreeHost(drop);
 }
 
 }  // namespace ksb
@@ -218,11 +276,13 @@ void ksb_device_free(ksb_device* d) {
     if (!d) return;
     cudaSetDevice(d->device);
     if (d->stream) cudaStreamSynchronize(d->stream);
-    if (d->own_payload && d->d_payload) cudaFree(d->d_payload);
-    if (d->d_tri) cudaFree(d->d_tri);
-    if (d->d_touched) cudaFree(d->d_touched);
-    if (d->d_block_counts) cudaFree(d->d_block_counts);
-    if (d->d_scan_tmp) cudaFree(d->d_scan_tmp);
+    cudaStream_t fs = d->stream ? d->stream : g_ctx[d->device].stream;
+    if (d->own_payload && d->d_payload) cudaFreeAsync(d->d_payload, fs);
+    if (d->d_tri) cudaFreeAsync(d->d_tri, fs);
+    if (d->d_touched) cudaFreeAsync(d->d_touched, fs);
+    if (d->d_block_counts) cudaFreeAsync(d->d_block_counts, fs);
+    if (d->d_scan_tmp) cudaFreeAsync(d->d_scan_tmp, fs);
+    if (fs) cudaStreamSynchronize(fs);
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
     if (d->stream) cudaStreamDestroy(d->stream);
     (void)cudaGetLastError();
@@ -251,7 +311,8 @@ int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
     int rc = opts_common(d, opts);
     if (rc) { ksb_device_free(d); return rc; }
     auto fail = [&](int code) { ksb_device_free(d); return code; };
-    cudaError_t e = cudaMalloc(&d->d_payload, d->desc.payload_bytes);
+    cudaError_t e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaMallocAsync(&d->d_payload, d->desc.payload_bytes, d->stream);
     if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
     d->own_payload = true;
     const uint64_t* row_updates = reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_row_updates);
@@ -377,10 +438,10 @@ void ksb_result_free(ksb_result* r) {
     if (!r) return;
     cudaSetDevice(r->device);
     for (ksb_segment& s : r->seg) {
-        if (s.d_records) cudaFree(s.d_records);
-        if (s.d_pairs) cudaFree(s.d_pairs);
+        if (s.d_records) cudaFreeAsync(s.d_records, g_ctx[r->device].stream);
+        if (s.d_pairs) cudaFreeAsync(s.d_pairs, g_ctx[r->device].stream);
     }
-    if (r->h_records) cudaFreeHost(r->h_records);
+    if (r->h_records) pinned_release(r->h_records, sizeof(ksb_record) * r->h_capacity);
     (void)cudaGetLastError();
     delete r;
 }
@@ -432,9 +493,9 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
         d->launches += 2;  // k5_count + the scan
         n_rows = total;
         if (n_rows) {
-            KSB_CUDA_R(cudaMalloc(&seg.d_records, sizeof(ksb_record) * n_rows));
-            cudaError_t e = cudaMalloc(&seg.d_pairs, 8 * n_rows);
-            if (e != cudaSuccess) { cudaFree(seg.d_records); set_error("cudaMalloc pairs: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
+            KSB_CUDA_R(cudaMallocAsync(&seg.d_records, sizeof(ksb_record) * n_rows, d->stream));
+            cudaError_t e = cudaMallocAsync(&seg.d_pairs, 8 * n_rows, d->stream);
+            if (e != cudaSuccess) { cudaFreeAsync(seg.d_records, d->stream); set_error("cudaMalloc pairs: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
             seg.n = n_rows;
             r->seg.push_back(seg);
             const uint8_t* P = d->d_payload;
@@ -449,11 +510,13 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
         if (need > r->h_capacity) {
             const uint64_t cap = std::max<uint64_t>(need, r->h_capacity * 2);
             ksb_record* nh = nullptr;
-            KSB_CUDA_R(cudaMallocHost(&nh, sizeof(ksb_record) * cap));
+            uint64_t got = sizeof(ksb_record) * cap;
+            KSB_CUDA_R(pinned_acquire(reinterpret_cast<void**>(&nh), &got));
             if (have) std::memcpy(nh, r->h_records, sizeof(ksb_record) * have);
-            if (r->h_records) cudaFreeHost(r->h_records);
+            if (r->h_records) pinned_release(r->h_records, sizeof(ksb_record) * r->h_capacity);
+            const uint64_t cap_got = got / sizeof(ksb_record);
             r->h_records = nh;
-            r->h_capacity = cap;
+            r->h_capacity = cap_got;
         }
         KSB_CUDA_R(cudaMemcpyAsync(r->h_records + have, seg.d_records, sizeof(ksb_record) * n_rows, cudaMemcpyDeviceToHost, d->stream));
     }
@@ -568,16 +631,13 @@ int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t*
     if (cstar != cstar) cstar = INFINITY;  // keep NaN rows only: c < inf drops every number... except inf itself
     uint32_t* d_parent = nullptr;
     unsigned long long* d_edges = nullptr;
-    cudaStream_t st = nullptr;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaStream_t st = g_ctx[dev].stream;
+    cudaEvent_t e0 = g_ctx[dev].e0, e1 = g_ctx[dev].e1;
     int rc = KSB_OK;
     cudaError_t e = cudaSuccess;
     do {
-        if ((e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) != cudaSuccess) break;
-        if ((e = cudaEventCreate(&e0)) != cudaSuccess) break;
-        if ((e = cudaEventCreate(&e1)) != cudaSuccess) break;
-        if ((e = cudaMalloc(&d_parent, 4ull * N)) != cudaSuccess) break;
-        if ((e = cudaMalloc(&d_edges, 8)) != cudaSuccess) break;
+        if ((e = cudaMallocAsync(&d_parent, 4ull * N, st)) != cudaSuccess) break;
+        if ((e = cudaMallocAsync(&d_edges, 8, st)) != cudaSuccess) break;
         const LaunchCfg lc{sms, st};
         cudaEventRecord(e0, st);
         if ((e = cudaMemsetAsync(d_edges, 0, 8, st)) != cudaSuccess) break;
@@ -597,11 +657,8 @@ int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t*
         rw->info.gpu_launches += 2 + r->seg.size();
     } while (0);
     if (e != cudaSuccess) { set_error("ksb_cluster: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); rc = KSB_ERR_CUDA; }
-    if (d_parent) cudaFree(d_parent);
-    if (d_edges) cudaFree(d_edges);
-    if (e0) cudaEventDestroy(e0);
-    if (e1) cudaEventDestroy(e1);
-    if (st) cudaStreamDestroy(st);
+    if (d_parent) cudaFreeAsync(d_parent, st);
+    if (d_edges) cudaFreeAsync(d_edges, st);
     return rc;
 }
 

@@ -585,6 +585,18 @@ int ksb_index_row_cuts(const ksb_index* ix, int world, uint64_t* cuts_out) {
     return KSB_OK;
 }
 
+int ksb_blob_row_cuts(const void* descriptor, uint64_t descriptor_bytes, const void* payload, uint64_t payload_bytes,
+                      int world, uint64_t* cuts_out) {
+    if (!descriptor || !cuts_out || world < 1 || descriptor_bytes != sizeof(ksb::IndexDesc)) { ksb::set_error("ksb_blob_row_cuts: bad argument"); return KSB_ERR_ARG; }
+    ksb::IndexDesc d;
+    std::memcpy(&d, descriptor, sizeof d);
+    if (d.magic != ksb::kIndexMagic || d.payload_bytes != payload_bytes || (!payload && payload_bytes) ||
+        d.off_row_updates + 8 * d.n_samples > payload_bytes) { ksb::set_error("ksb_blob_row_cuts: descriptor does not match the payload"); return KSB_ERR_ARG; }
+    ksb::row_cuts(reinterpret_cast<const uint64_t*>(static_cast<const uint8_t*>(payload) + d.off_row_updates), d.n_samples,
+                  d.n_updates, world, cuts_out);
+    return KSB_OK;
+}
+
 int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path) {
     if (!ix || !path) { ksb::set_error("null argument"); return KSB_ERR_ARG; }
     FILE* f = fopen(path, "w");
