@@ -61,6 +61,8 @@ typedef struct ksb_index_info {
     uint64_t n_updates;        /* U */
     uint64_t n_small_colors;   /* 2 <= s <= 64  (flat pair-space kernel) */
     uint64_t n_mid_colors;     /* s > 64        (shared-memory tiled kernel) */
+    uint64_t n_gram_colors;    /* colours routed to the int8 tcgen05 Gram kernel (K4); 0 = path unused */
+    uint64_t gram_min_size;    /* routing rule applied: s >= gram_min_size (KSPIDER_GRAM=off|auto|<n>) */
     uint64_t n_zero_colors;    /* multi-member colours whose narrowed count is 0 (touched-with-zero rows) */
     uint64_t max_color_size;
     uint64_t payload_bytes;    /* size of the binned CSR blob (what H2D / NCCL broadcast moves) */
@@ -99,7 +101,8 @@ typedef struct ksb_timings {
     float post_ms;        /* K5 count + compact */
     float d2h_ms;         /* records device->host */
     float cluster_ms;     /* K6 + K7 */
-    float reserved[7];
+    float gram_ms;        /* K4: bitmap build + int8 tcgen05 Gram kernel (inside accumulate_ms) */
+    float reserved[6];
 } ksb_timings;
 
 typedef struct ksb_result_info {

@@ -25,7 +25,7 @@ class KsbError(RuntimeError):
 class IndexInfo(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "n_samples", "n_colors_file", "n_colors", "n_members", "n_updates", "n_small_colors",
-        "n_mid_colors", "n_zero_colors", "max_color_size", "payload_bytes", "triangle_cells")] + \
+        "n_mid_colors", "n_gram_colors", "gram_min_size", "n_zero_colors", "max_color_size", "payload_bytes", "triangle_cells")] + \
         [("pinned", C.c_uint32), ("reserved", C.c_uint32)]
 
 
@@ -42,8 +42,8 @@ class Record(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("h2d_ms", "zero_ms", "small_ms", "mid_ms", "zero_touch_ms",
-                                         "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms")] + \
-        [("reserved", C.c_float * 7)]
+                                         "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "gram_ms")] + \
+        [("reserved", C.c_float * 6)]
 
 
 class ResultInfo(C.Structure):

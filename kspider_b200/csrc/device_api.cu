@@ -38,7 +38,7 @@ struct ksb_device {
     uint8_t* d_payload = nullptr;
     bool own_payload = false;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[8] = {};
+    cudaEvent_t ev[9] = {};
     unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
     uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
     uint64_t tri_cells_alloc = 0;
@@ -53,6 +53,10 @@ struct ksb_device {
     void* d_scan_tmp = nullptr;
     size_t scan_tmp_bytes = 0;
     uint64_t post_blocks_alloc = 0;
+    // K4 (Gram) scratch: bitmap of one chunk of colours + weight byte planes
+    uint32_t* d_gbits = nullptr;
+    uint8_t* d_gwq = nullptr;
+    uint32_t g_npad = 0, g_chunk_kblocks = 0, g_planes = 0;
 };
 
 struct ksb_segment {
@@ -221,6 +225,17 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
                                d->post_blocks_alloc, d->stream));
     KSB_CUDA(cudaMallocAsync(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256), d->stream));
     build_k1(d);
+    if (d->desc.n_gram_colors) {
+        // chunk of colours whose bitmap (npad x 16 B per K-block) stays L2-resident (<= 32 MB)
+        d->g_npad = (uint32_t)((d->desc.n_samples + kGramTile - 1) / kGramTile * kGramTile);
+        const uint64_t kb_total = (d->desc.n_gram_colors + kGramKBlock - 1) / kGramKBlock;
+        uint64_t kb_chunk = (32ull << 20) / ((uint64_t)d->g_npad * 16);
+        kb_chunk = std::max<uint64_t>(1, std::min<uint64_t>(kb_chunk, 16384));  // 255 * 128 * 16384 < 2^31
+        d->g_chunk_kblocks = (uint32_t)std::min(kb_total, kb_chunk);
+        d->g_planes = d->desc.gram_planes <= 1 ? 1 : (d->desc.gram_planes == 2 ? 2 : 4);
+        KSB_CUDA(cudaMallocAsync(&d->d_gbits, (uint64_t)d->g_chunk_kblocks * d->g_npad * 16, d->stream));
+        KSB_CUDA(cudaMallocAsync(&d->d_gwq, (uint64_t)d->g_planes * d->g_chunk_kblocks * kGramKBlock, d->stream));
+    }
     return KSB_OK;
 }
 
@@ -282,6 +297,8 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_touched) cudaFreeAsync(d->d_touched, fs);
     if (d->d_block_counts) cudaFreeAsync(d->d_block_counts, fs);
     if (d->d_scan_tmp) cudaFreeAsync(d->d_scan_tmp, fs);
+    if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
+    if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
     if (fs) cudaStreamSynchronize(fs);
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
     if (d->stream) cudaStreamDestroy(d->stream);
@@ -398,13 +415,48 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         d->launches++;
     }
     KSB_CUDA(cudaEventRecord(d->ev[4], st));
+    if (p.cells && D.n_gram_colors) {
+        const uint32_t T = d->g_npad / kGramTile;
+        const uint32_t tile_lo = (uint32_t)(p.rb / kGramTile);
+        const uint32_t tile_hi = (uint32_t)std::min<uint64_t>(T, (p.re + kGramTile - 1) / kGramTile);
+        uint64_t pairs = 0;
+        for (uint32_t ti = tile_lo; ti < tile_hi; ti++) pairs += T - ti;
+        const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
+        const uint32_t* gmem = reinterpret_cast<const uint32_t*>(P + D.off_gram_members);
+        const uint32_t* gw = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
+        const uint64_t chunk_colors = (uint64_t)d->g_chunk_kblocks * kGramKBlock;
+        for (uint64_t c0 = 0; c0 < D.n_gram_colors && pairs; c0 += chunk_colors) {
+            const uint32_t n = (uint32_t)std::min<uint64_t>(chunk_colors, D.n_gram_colors - c0);
+            GramParams gp;
+            gp.bits = d->d_gbits;
+            gp.wq = d->d_gwq;
+            gp.npad = d->g_npad;
+            gp.kblocks = (n + kGramKBlock - 1) / kGramKBlock;
+            gp.kpad = d->g_chunk_kblocks * kGramKBlock;
+            gp.planes = d->g_planes;
+            gp.tiles = T;
+            gp.tile_lo = tile_lo;
+            gp.pad = 0;
+            // enough items for two waves of CTAs, never more splits than K-blocks
+            uint64_t ks = (2ull * (uint64_t)d->sms + pairs - 1) / pairs;
+            gp.ksplit = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ks, gp.kblocks));
+            gp.n_items = pairs * gp.ksplit;
+            KSB_CUDA(cudaMemsetAsync(d->d_gbits, 0, (uint64_t)gp.kblocks * d->g_npad * 16, st));
+            KSB_CUDA(cudaMemsetAsync(d->d_gwq, 0, (uint64_t)d->g_planes * gp.kpad, st));
+            KSB_CUDA(launch_kb_build(goff, gmem, gw, c0, n, gp.npad, gp.kpad, gp.planes, d->d_gbits, d->d_gwq, lc));
+            KSB_CUDA(launch_k4_gram(gp, g, lc));
+            d->launches += 2;
+        }
+    }
+    KSB_CUDA(cudaEventRecord(d->ev[8], st));
     if (sync) {
         KSB_CUDA(cudaStreamSynchronize(st));
         d->t.zero_ms += ev_ms(d->ev[0], d->ev[1]);
         d->t.small_ms += ev_ms(d->ev[1], d->ev[2]);
         d->t.mid_ms += ev_ms(d->ev[2], d->ev[3]);
         d->t.zero_touch_ms += ev_ms(d->ev[3], d->ev[4]);
-        d->t.accumulate_ms += ev_ms(d->ev[0], d->ev[4]);
+        d->t.gram_ms += ev_ms(d->ev[4], d->ev[8]);
+        d->t.accumulate_ms += ev_ms(d->ev[0], d->ev[8]);
     }
     return KSB_OK;
 }

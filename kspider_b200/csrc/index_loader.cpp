@@ -12,6 +12,7 @@
 // (ascending(), Combo enumeration order) is folded in here: members are sorted once.
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <functional>
@@ -186,9 +187,57 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     };
     d.n_samples = N;
 
-    // ---- classify colours; per-chunk class counts so the fill can run in parallel, in input order
     const int T = std::max(1, threads);
-    const uint32_t K_MID = kSmallMax + 1, K_ZERO = kSmallMax + 2, K_N = kSmallMax + 3;
+
+    // ---- routing rule of the int8 Gram path (K4): colours with s >= gram_min (and weight != 0).
+    // KSPIDER_GRAM = off | auto (default) | <min size>.  auto: per colour the Gram path costs
+    // ~Npad^2 * planes tensor MACs against s^2/2 reds, so it pays for s above a fixed fraction of N;
+    // it is used only if the routed set also beats the atomic path including the fixed costs.
+    uint64_t gram_min = 0, gram_planes = 1;
+    if (N >= 2 && N <= kGramMaxSamples) {
+        const char* env = std::getenv("KSPIDER_GRAM");
+        long forced = -1;
+        bool off = false;
+        if (env && *env) {
+            if (!std::strcmp(env, "off")) off = true;
+            else if (std::strcmp(env, "auto")) { forced = std::strtol(env, nullptr, 10); if (forced < 2) off = true; }
+        }
+        if (!off) {
+            const double npad = (double)((N + kGramTile - 1) / kGramTile * kGramTile);
+            auto scan = [&](uint64_t smin, uint64_t* kg, uint64_t* ug) {
+                std::vector<uint64_t> tk(T, 0), tu(T, 0);
+                std::vector<uint32_t> tw(T, 0);
+                parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+                    for (uint64_t c = b; c < e; c++) {
+                        const uint64_t sz = raw.off[c + 1] - raw.off[c];
+                        if (sz < 2 || sz < smin || raw.weights[c] == 0) continue;
+                        tk[t]++; tu[t] += sz * (sz - 1) / 2; tw[t] = std::max(tw[t], raw.weights[c]);
+                    }
+                });
+                uint32_t wmax = 0;
+                *kg = 0; *ug = 0;
+                for (int t = 0; t < T; t++) { *kg += tk[t]; *ug += tu[t]; wmax = std::max(wmax, tw[t]); }
+                return wmax;
+            };
+            uint64_t kg = 0, ug = 0;
+            uint32_t wmax = scan(2, &kg, &ug);
+            auto planes_of = [](uint32_t w) -> uint64_t { return w < (1u << 8) ? 1 : (w < (1u << 16) ? 2 : 4); };
+            uint64_t smin = forced >= 2 ? (uint64_t)forced
+                                        : std::max<uint64_t>(16, (uint64_t)std::ceil(kGramCrossover * npad * std::sqrt((double)planes_of(wmax))));
+            wmax = scan(smin, &kg, &ug);
+            if (kg) {
+                const double kpad = (double)((kg + kGramKBlock - 1) / kGramKBlock * kGramKBlock);
+                const double t_gram = npad * npad * kpad * (double)planes_of(wmax) / kGramMacRate + npad * npad * 8.0 / 4e12 + 30e-6;
+                const double t_red = (double)ug / kGramRedRate;
+                if (forced >= 2 || t_gram < t_red) { gram_min = smin; gram_planes = planes_of(wmax); }
+            }
+        }
+    }
+    d.gram_min_size = gram_min;
+    d.gram_planes = gram_planes;
+
+    // ---- classify colours; per-chunk class counts so the fill can run in parallel, in input order
+    const uint32_t K_MID = kSmallMax + 1, K_ZERO = kSmallMax + 2, K_GRAM = kSmallMax + 3, K_N = kSmallMax + 4;
     std::vector<std::vector<uint64_t>> cnt(T, std::vector<uint64_t>(K_N, 0));      // colours per class
     std::vector<std::vector<uint64_t>> mcnt(T, std::vector<uint64_t>(K_N, 0));     // members per class
     std::vector<uint64_t> chunk_b(T + 1, C);
@@ -197,6 +246,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         const uint64_t s = raw.off[c + 1] - raw.off[c];
         if (s < 2) return 0;
         if (raw.weights[c] == 0) return K_ZERO;
+        if (gram_min && s >= gram_min) return K_GRAM;
         return s <= kSmallMax ? (uint32_t)s : K_MID;
     };
     parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
@@ -239,7 +289,9 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.n_mid_items = n_items;
     d.n_zero_colors = tot[K_ZERO];
     d.n_zero_members = mtot[K_ZERO];
-    d.n_colors = d.n_small_colors + d.n_mid_colors + d.n_zero_colors;
+    d.n_gram_colors = tot[K_GRAM];
+    d.n_gram_members = mtot[K_GRAM];
+    d.n_colors = d.n_small_colors + d.n_mid_colors + d.n_zero_colors + d.n_gram_colors;
 
     // ---- payload layout
     uint64_t p = 0;
@@ -256,6 +308,9 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_mid_items = section(sizeof(MidItem) * d.n_mid_items);
     d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
     d.off_zero_members = section(4 * d.n_zero_members);
+    d.off_gram_offsets = section(8 * (d.n_gram_colors + 1));
+    d.off_gram_members = section(4 * d.n_gram_members);
+    d.off_gram_weights = section(4 * d.n_gram_colors);
     d.payload_bytes = std::max<uint64_t>(p, 256);
 
     void* mem = nullptr;
@@ -281,6 +336,9 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     MidItem* mid_items = reinterpret_cast<MidItem*>(P + d.off_mid_items);
     uint64_t* zero_off = reinterpret_cast<uint64_t*>(P + d.off_zero_offsets);
     uint32_t* zero_m = reinterpret_cast<uint32_t*>(P + d.off_zero_members);
+    uint64_t* gram_off = reinterpret_cast<uint64_t*>(P + d.off_gram_offsets);
+    uint32_t* gram_m = reinterpret_cast<uint32_t*>(P + d.off_gram_members);
+    uint32_t* gram_w = reinterpret_cast<uint32_t*>(P + d.off_gram_weights);
 
     std::copy(sample_ids.begin(), sample_ids.end(), sids);
     // groupID_to_kmerCount[id]: a map, so one value per id; missing -> 0 (operator[] default)
@@ -288,14 +346,14 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
     // ---- fill (parallel, deterministic placement = input order within each class)
     std::vector<std::vector<uint64_t>> t_rows(T), t_rowsum(T);
-    std::vector<uint64_t> t_maxs(T, 0), t_mid_updates(T, 0), t_mid_members(T, 0);
+    std::vector<uint64_t> t_maxs(T, 0), t_mid_updates(T, 0), t_mid_members(T, 0), t_gram_updates(T, 0);
     parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
         std::vector<uint64_t>& rows = t_rows[t];
         std::vector<uint64_t>& rowsum = t_rowsum[t];
         rows.assign(N, 0);
         rowsum.assign(N, 0);
         std::vector<uint64_t> at = base[t], mat = mbase[t];
-        uint64_t maxs = 0, midu = 0, midm = 0, iat = ibase[t];
+        uint64_t maxs = 0, midu = 0, midm = 0, gramu = 0, iat = ibase[t];
         for (uint64_t c = b; c < e; c++) {
             const uint32_t k = klass(c);
             if (!k) continue;
@@ -318,6 +376,11 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             } else if (k == K_ZERO) {
                 dst = zero_m + mat[k];
                 zero_off[at[k]] = mat[k];
+            } else if (k == K_GRAM) {
+                dst = gram_m + mat[k];
+                gram_off[at[k]] = mat[k];
+                gram_w[at[k]] = w;
+                gramu += s * (s - 1) / 2;
             } else {
                 const SmallClass& sc = d.cls[k];
                 dst = small_m + sc.member_off + at[k] * s;
@@ -335,15 +398,19 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         t_maxs[t] = maxs;
         t_mid_updates[t] = midu;
         t_mid_members[t] = midm;
+        t_gram_updates[t] = gramu;
     });
+    gram_off[d.n_gram_colors] = d.n_gram_members;
     mid_off[d.n_mid_colors] = d.n_mid_members_padded;
     zero_off[d.n_zero_colors] = d.n_zero_members;
     for (int t = 0; t < T; t++) {
         d.max_color_size = std::max(d.max_color_size, t_maxs[t]);
         d.n_updates += t_mid_updates[t];
         d.n_mid_members += t_mid_members[t];
+        d.n_gram_updates += t_gram_updates[t];
     }
-    d.n_members = d.n_small_members + d.n_mid_members + d.n_zero_members;
+    d.n_updates += d.n_gram_updates;
+    d.n_members = d.n_small_members + d.n_mid_members + d.n_zero_members + d.n_gram_members;
     parallel_chunks(N, T, [&](int, uint64_t b, uint64_t e) {
         for (uint64_t i = b; i < e; i++) {
             uint64_t r = 0;
@@ -557,6 +624,8 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     info->n_updates = d.n_updates;
     info->n_small_colors = d.n_small_colors;
     info->n_mid_colors = d.n_mid_colors;
+    info->n_gram_colors = d.n_gram_colors;
+    info->gram_min_size = d.gram_min_size;
     info->n_zero_colors = d.n_zero_colors;
     info->max_color_size = d.max_color_size;
     info->payload_bytes = d.payload_bytes;

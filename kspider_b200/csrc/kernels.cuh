@@ -72,6 +72,25 @@ cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 
+// K4: int8 tcgen05 Gram path (gram.cu)
+struct GramParams {
+    const uint32_t* bits;   // [kblocks][npad][4] u32: bit (colour % 128) of sample, K-block-major
+    const uint8_t* wq;      // [planes][kpad] weight byte planes
+    uint32_t npad;          // N rounded up to kGramTile
+    uint32_t kblocks;       // K-blocks of this chunk
+    uint32_t kpad;          // row pitch of wq (>= kblocks * 128, multiple of 128)
+    uint32_t planes;        // 1, 2 or 4
+    uint32_t tiles;         // npad / kGramTile
+    uint32_t ksplit;        // K splits per tile pair
+    uint32_t tile_lo;       // first row tile intersecting the owned rows
+    uint32_t pad;
+    unsigned long long n_items;  // tile pairs (ti in [tile_lo, tile_hi), tj >= ti) x ksplit
+};
+cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* gram_members,
+                            const uint32_t* gram_weights, uint64_t c0, uint32_t n, uint32_t npad, uint32_t kpad,
+                            uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
+cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
+
 // red micro-benchmark
 cudaError_t launch_bench_red(void* buf, uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, const LaunchCfg& lc);
 

@@ -26,6 +26,17 @@ constexpr uint32_t kMaxPairsSmall = kSmallMax * (kSmallMax - 1) / 2;  // 2016
 constexpr uint32_t kMidCols = 256;
 constexpr uint32_t kMidRows = 512;
 
+// K4 (Gram) geometry: 128 x 128 sample tiles, K-blocks of 128 colours
+constexpr uint32_t kGramTile = 128;
+constexpr uint32_t kGramKBlock = 128;
+constexpr uint32_t kGramMaxSamples = 32768;  // bitmap rows / tile grid are O(N), O(N^2): larger N stays on K1/K2
+// routing cost model (calibrated on B200): effective Gram MAC rate (u8 MACs/s over the
+// full Npad^2 x K x planes box, i.e. including the half that the symmetric tile skips), red rate of
+// the atomic kernels, and the resulting per-colour crossover s / Npad = sqrt(2 * red / mac) (x sqrt(planes))
+constexpr double kGramMacRate = 1.0e15;
+constexpr double kGramRedRate = 2.5e11;
+constexpr double kGramCrossover = 0.0224;
+
 // One K2 work item: columns [b0, b0+kMidCols) x rows [a0, a0+kMidRows) of mid colour `color`
 // (positions in the colour's sorted member list; only pairs with row position < column position count).
 struct MidItem {
@@ -78,9 +89,16 @@ struct IndexDesc {
     uint64_t n_mid_members_padded;
     uint64_t off_zero_offsets;  // u64[n_zero_colors+1]
     uint64_t off_zero_members;  // u32[n_zero_members]
+    // colours routed to the int8 Gram path (K4): plain CSR
+    uint64_t n_gram_colors, n_gram_members, n_gram_updates;
+    uint64_t gram_planes;       // byte planes needed by the largest Gram weight (1..4)
+    uint64_t gram_min_size;     // the routing rule that was applied: s >= gram_min_size (0 = path unused)
+    uint64_t off_gram_offsets;  // u64[n_gram_colors+1]
+    uint64_t off_gram_members;  // u32[n_gram_members]
+    uint64_t off_gram_weights;  // u32[n_gram_colors]
     uint64_t payload_bytes;
 };
-constexpr uint64_t kIndexMagic = 0x31305844494253ULL | (0x4BULL << 56);
+constexpr uint64_t kIndexMagic = 0x32305844494253ULL | (0x4BULL << 56);
 
 }  // namespace ksb
 

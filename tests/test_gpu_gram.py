@@ -1,0 +1,107 @@
+"""K4 (int8 tcgen05 Gram path) parity, -m gpu.  The routing rule is forced with KSPIDER_GRAM=<min size>
+so that the same seeded indexes the atomic kernels are checked on go through the tensor-core path;
+results must stay bit-exact against the oracle (integers, float32 bit patterns)."""
+import os
+
+import numpy as np
+import pytest
+
+from util import assert_records_equal, oracle_records, random_csr, sort_records
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ksb(built_lib):
+    from kspider_b200.capi import check
+    check(built_lib.ksb_cuda_available())
+    import kspider_b200
+    return kspider_b200
+
+
+@pytest.fixture
+def gram_env():
+    old = os.environ.get("KSPIDER_GRAM")
+
+    def set_(v):
+        os.environ["KSPIDER_GRAM"] = str(v)
+    yield set_
+    if old is None:
+        os.environ.pop("KSPIDER_GRAM", None)
+    else:
+        os.environ["KSPIDER_GRAM"] = old
+
+
+CASES = [
+    # name, gram min size, random_csr kwargs
+    ("tiny_one_tile", 2, dict(seed=41, n_samples=40, n_colors=300, s_lo=1, s_hi=12, w_hi=200)),
+    ("exact_128", 2, dict(seed=42, n_samples=128, n_colors=500, s_lo=2, s_hi=30, w_hi=255)),
+    ("three_tiles_1plane", 2, dict(seed=43, n_samples=300, n_colors=4000, s_lo=1, s_hi=40, w_hi=255, big=(70, 150, 299))),
+    ("two_planes", 2, dict(seed=44, n_samples=200, n_colors=2000, s_lo=2, s_hi=20, w_hi=65535)),
+    ("four_planes", 2, dict(seed=45, n_samples=260, n_colors=1500, s_lo=2, s_hi=64, w_hi=2 ** 32 - 1, big=(200, 260))),
+    ("mixed_routing", 20, dict(seed=46, n_samples=700, n_colors=5000, s_lo=1, s_hi=64, w_hi=1000, big=(100, 400, 700), zero_every=13)),
+    ("sparse_ids", 2, dict(seed=47, n_samples=400, n_colors=1000, s_lo=1, s_hi=40, id_mode="sparse", big=(100, 399))),
+    ("many_kblocks", 2, dict(seed=48, n_samples=150, n_colors=40000, s_lo=2, s_hi=6, w_hi=100)),
+    ("whole_population", 2, dict(seed=49, n_samples=1100, n_colors=30, s_lo=2, s_hi=10, w_hi=2 ** 32 - 1, big=(1100, 1100, 1099))),
+]
+
+
+@pytest.mark.parametrize("name,gmin,kw", CASES, ids=[c[0] for c in CASES])
+def test_gram_bit_exact_vs_oracle(ksb, gram_env, name, gmin, kw):
+    gram_env(gmin)
+    csr = random_csr(**kw)
+    idx = ksb.Index.from_csr(**csr, host_threads=3)
+    inf = idx.info
+    assert inf.gram_min_size == gmin and inf.n_gram_colors > 0
+    res = idx.pairwise(device=0)
+    got = res.records()
+    want = oracle_records(csr)
+    assert_records_equal(got, want)
+    assert np.array_equal(got, sort_records(got))
+    assert res.info.t.gram_ms > 0.0 and res.info.n_updates == inf.n_updates
+
+
+def test_gram_off_and_auto(ksb, gram_env):
+    csr = random_csr(seed=50, n_samples=300, n_colors=2000, s_lo=2, s_hi=40, big=(250,))
+    gram_env("off")
+    assert ksb.Index.from_csr(**csr).info.n_gram_colors == 0
+    gram_env("auto")
+    idx = ksb.Index.from_csr(**csr)
+    # whatever auto decides, the result is the oracle's
+    assert_records_equal(idx.pairwise().records(), oracle_records(csr))
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gram_row_blocks_and_passes(ksb, gram_env, world):
+    gram_env(8)
+    csr = random_csr(seed=51, n_samples=500, n_colors=3000, s_lo=1, s_hi=50, big=(120, 300, 499), zero_every=17)
+    idx = ksb.Index.from_csr(**csr)
+    assert idx.info.n_gram_colors > 0
+    want = oracle_records(csr)
+    parts = [idx.pairwise(rank=r, world=world).records() for r in range(world)]
+    assert_records_equal(np.concatenate(parts), want)
+    dev = idx.upload(dense_budget_bytes=200_000)
+    assert dev.n_passes >= 4
+    assert_records_equal(dev.run_all_passes().records(), want)
+
+
+def test_gram_giant_colours_checksum(ksb, gram_env):
+    """BASELINE config 5 shape, scaled: giant dense colours with full-range u32 weights on N = 3000;
+    the oracle is too slow here, so: per-sample row sums and the checksum of checksums, and equality
+    with the atomic path (KSPIDER_GRAM=off) on the same index."""
+    rng = np.random.default_rng(52)
+    n, g, s = 3000, 40, 1200
+    members = np.concatenate([np.sort(rng.choice(n, size=s, replace=False)) + 1 for _ in range(g)]).astype(np.uint32)
+    offsets = (np.arange(g + 1) * s).astype(np.uint64)
+    weights = rng.integers(1, 2 ** 32 - 1, size=g, dtype=np.int64).astype(np.uint32)
+    ids = np.arange(1, n + 1, dtype=np.uint32)
+    totals = rng.integers(1, 10 ** 6, size=n, dtype=np.int64).astype(np.uint32)
+    gram_env("auto")
+    idx = ksb.Index.from_csr(offsets, members, weights, ids, totals)
+    assert idx.info.n_gram_colors == g, "auto routing must pick the giant colours"
+    rec = idx.pairwise().records()
+    w = weights.astype(object)
+    assert sum(int(v) for v in rec["shared_kmers"]) == sum(int(x) * (s * (s - 1) // 2) for x in w)
+    gram_env("off")
+    ref = ksb.Index.from_csr(offsets, members, weights, ids, totals).pairwise().records()
+    assert_records_equal(rec, ref)
