@@ -42,10 +42,12 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cutoff", type=float, default=0.3)
     ap.add_argument("--dense-budget-gb", type=float, default=0.0)
+    ap.add_argument("--n-giant", type=int, default=16, help="cfg5: number of giant colours")
+    ap.add_argument("--giant-size", type=int, default=4000, help="cfg5: members per giant colour")
     return ap.parse_args()
 
 
-def make_workload(name: str):
+def make_workload(name: str, args=None):
     from kspider_b200 import synth
     if name == "cfg2":
         return synth.zipf_index(1000, 10_000_000, seed=12345, name="cfg2")
@@ -56,7 +58,7 @@ def make_workload(name: str):
     if name == "cfg4":
         return synth.cfg4()
     if name == "cfg5":
-        return synth.giant_index()
+        return synth.giant_index(n_giant=args.n_giant if args else 16, giant_size=args.giant_size if args else 4000)
     raise ValueError(name)
 
 
@@ -205,7 +207,7 @@ def main_b200(args):
     idx = None
     shape = np.zeros(8, dtype=np.int64)
     if rank == 0:
-        s = make_workload(args.workload)
+        s = make_workload(args.workload, args)
         idx = Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals,
                              host_threads=min(32, os.cpu_count() or 1))
         inf = idx.info
@@ -247,7 +249,7 @@ def main_b200(args):
         sampler.start()
     t_before = dev.info.t
     l_before = dev.info.gpu_launches
-    before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "accumulate_ms", "post_ms")}
+    before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "gram_ms", "accumulate_ms", "post_ms")}
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
