@@ -82,7 +82,7 @@ class ClockSampler:
     def start(self):
         if shutil.which("nvidia-smi") is None:
             return
-        self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+        self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
                                       "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         self.t = threading.Thread(target=self._read, daemon=True)
         self.t.start()
@@ -205,7 +205,7 @@ def main_b200(args):
 
     # ---- synthetic index: generated and parsed on rank 0 only, blob broadcast once
     idx = None
-    shape = np.zeros(8, dtype=np.int64)
+    shape = np.zeros(12, dtype=np.int64)
     if rank == 0:
         s = make_workload(args.workload, args)
         idx = Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals,
@@ -213,9 +213,14 @@ def main_b200(args):
         inf = idx.info
         sizes = np.diff(s.offsets).astype(np.int64)
         upd = sizes * (sizes - 1) // 2
-        small = (sizes >= 2) & (sizes <= 64)
+        gmin = int(inf.gram_min_size) if inf.n_gram_colors else (1 << 62)
+        nz = s.weights != 0
+        small = (sizes >= 2) & (sizes <= 64) & (sizes < gmin) & nz     # what K1 runs
+        gram = (sizes >= 2) & (sizes >= gmin) & nz                      # what K4 runs
+        assert int(gram.sum()) == inf.n_gram_colors, (int(gram.sum()), inf.n_gram_colors)
         shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, int(upd[small].sum()),
-                    int(sizes[small].sum()), int(small.sum()), inf.payload_bytes]
+                    int(sizes[small].sum()), int(small.sum()), inf.payload_bytes, inf.n_gram_colors,
+                    inf.gram_planes, int(upd[gram].sum()), int(sizes[gram].sum())]
         del s
     if world > 1:
         t = torch.from_numpy(shape).to(device)
@@ -225,7 +230,7 @@ def main_b200(args):
         dev = kd.adopt(desc, d_payload, dense_budget_bytes=budget)
     else:
         dev = idx.upload(device=local_rank, dense_budget_bytes=budget)
-    N, C_, M, U, U_small, M_small, C_small, payload_bytes = (int(v) for v in shape)
+    N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram = (int(v) for v in shape)
 
     def step():
         res = dev.run_all_passes(want_records=False)
@@ -242,11 +247,11 @@ def main_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
     sampler = ClockSampler(local_rank)
     if rank == 0:
-        sampler.start()
+        sampler.start()   # sampled from the warm-up on: the timed region alone can be shorter than one sample
+    for _ in range(args.warmup):
+        step()
     t_before = dev.info.t
     l_before = dev.info.gpu_launches
     before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "gram_ms", "accumulate_ms", "post_ms")}
@@ -325,14 +330,26 @@ def main_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     own_frac = dev.info.n_updates / U if U else 1.0
+    peak_tensor = 2.0 * float(peaks.get("bf16_tflops", 2250.0))  # int8 dense = 2 x bf16 on the same tensor pipe
+    gram_roof = None
+    if C_gram:
+        # useful int8 ops of the Gram launches of one step: 2 * (owned cells) * colours * byte planes
+        g_ops = 2.0 * dev.info.owned_cells * C_gram * P_gram
+        g_ms = phase["gram_ms"]
+        gram_roof = {"bound": "tensor", "kernel": "k4_gram (+kb_build, memsets)", "achieved": g_ops / (g_ms * 1e-3) / 1e12,
+                     "peak": peak_tensor, "unit": "TFLOP/s", "frac": g_ops / (g_ms * 1e-3) / 1e12 / peak_tensor,
+                     "traffic": None, "kernel_ms": g_ms, "algorithmic_ops": g_ops, "ops": "u8 x u8 -> s32 multiply-adds x 2",
+                     "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (burst); no int8 figure in that file",
+                     "updates_per_s": U_gram * own_frac / (g_ms * 1e-3) if g_ms > 0 else 0.0,
+                     "colors": C_gram, "planes": P_gram}
     if phase["small_ms"] >= phase["mid_ms"]:
         kname, k_ms = "k1_small", phase["small_ms"]
         k_bytes = 16 * U_small * own_frac + 4 * M_small + 4 * C_small
         k_upd = U_small * own_frac
     else:
         kname, k_ms = "k2_mid", phase["mid_ms"]
-        k_bytes = 16 * (U - U_small) * own_frac + 4 * (M - M_small) + 12 * (C_ - C_small)
-        k_upd = (U - U_small) * own_frac
+        k_bytes = 16 * (U - U_small - U_gram) * own_frac + 4 * (M - M_small - M_gram) + 12 * (C_ - C_small - C_gram)
+        k_upd = (U - U_small - U_gram) * own_frac
     achieved = k_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     traffic = None
     try:
@@ -343,6 +360,11 @@ def main_b200(args):
                 "frac": achieved / peak, "traffic": traffic, "kernel_ms": k_ms, "algorithmic_bytes": k_bytes,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
                 "updates_per_s": k_upd / (k_ms * 1e-3) if k_ms > 0 else 0.0}
+    if gram_roof is not None and phase["gram_ms"] > k_ms:
+        gram_roof["other"] = roofline       # the atomic kernel's HBM roofline rides along
+        roofline = gram_roof
+    elif gram_roof is not None:
+        roofline["other"] = gram_roof
     # in-run red.global.add.u64 ceiling on a buffer of the owned block's size
     red = None
     try:
@@ -352,7 +374,7 @@ def main_b200(args):
         for pat, nm in ((0, "random"), (1, "warp_contiguous")):
             red[nm + "_ops_per_s"] = n_ops / (bench_red(cells, n_ops, 64, pat, 3) * 1e-3)
         red["cells"] = cells
-        red["kernel_frac_of_warp_contiguous"] = roofline["updates_per_s"] / red["warp_contiguous_ops_per_s"]
+        red["kernel_frac_of_warp_contiguous"] = k_upd / (k_ms * 1e-3) / red["warp_contiguous_ops_per_s"] if k_ms > 0 else None
     except Exception as e:  # the micro-benchmark is informative only
         red = {"error": str(e)}
 

@@ -63,6 +63,8 @@ typedef struct ksb_index_info {
     uint64_t n_mid_colors;     /* s > 64        (shared-memory tiled kernel) */
     uint64_t n_gram_colors;    /* colours routed to the int8 tcgen05 Gram kernel (K4); 0 = path unused */
     uint64_t gram_min_size;    /* routing rule applied: s >= gram_min_size (KSPIDER_GRAM=off|auto|<n>) */
+    uint64_t gram_planes;      /* weight byte planes the Gram kernel runs (1, 2 or 4) */
+    uint64_t n_gram_updates;   /* pair-updates covered by the Gram colours */
     uint64_t n_zero_colors;    /* multi-member colours whose narrowed count is 0 (touched-with-zero rows) */
     uint64_t max_color_size;
     uint64_t payload_bytes;    /* size of the binned CSR blob (what H2D / NCCL broadcast moves) */

@@ -234,7 +234,7 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
         d->g_chunk_kblocks = (uint32_t)std::min(kb_total, kb_chunk);
         d->g_planes = d->desc.gram_planes <= 1 ? 1 : (d->desc.gram_planes == 2 ? 2 : 4);
         KSB_CUDA(cudaMallocAsync(&d->d_gbits, (uint64_t)d->g_chunk_kblocks * d->g_npad * 16, d->stream));
-        KSB_CUDA(cudaMallocAsync(&d->d_gwq, (uint64_t)d->g_planes * d->g_chunk_kblocks * kGramKBlock, d->stream));
+        KSB_CUDA(cudaMallocAsync(&d->d_gwq, (uint64_t)d->g_planes * d->g_chunk_kblocks * kGramKBlock + 256, d->stream));
     }
     return KSB_OK;
 }
@@ -419,8 +419,9 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         const uint32_t T = d->g_npad / kGramTile;
         const uint32_t tile_lo = (uint32_t)(p.rb / kGramTile);
         const uint32_t tile_hi = (uint32_t)std::min<uint64_t>(T, (p.re + kGramTile - 1) / kGramTile);
-        uint64_t pairs = 0;
-        for (uint32_t ti = tile_lo; ti < tile_hi; ti++) pairs += T - ti;
+        const uint32_t nbcol = gram_cols_per_item((int)d->g_planes);
+        uint64_t pairs = 0;  // (row tile, column-tile group) items
+        for (uint32_t ti = tile_lo; ti < tile_hi; ti++) pairs += (T - ti + nbcol - 1) / nbcol;
         const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
         const uint32_t* gmem = reinterpret_cast<const uint32_t*>(P + D.off_gram_members);
         const uint32_t* gw = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
@@ -436,13 +437,14 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
             gp.planes = d->g_planes;
             gp.tiles = T;
             gp.tile_lo = tile_lo;
-            gp.pad = 0;
-            // enough items for two waves of CTAs, never more splits than K-blocks
-            uint64_t ks = (2ull * (uint64_t)d->sms + pairs - 1) / pairs;
+            gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
+            // enough items for ~four waves of CTAs (items differ in size and are fetched dynamically),
+            // never more splits than K-blocks
+            uint64_t ks = (4ull * (uint64_t)d->sms + pairs - 1) / pairs;
             gp.ksplit = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ks, gp.kblocks));
-            gp.n_items = pairs * gp.ksplit;
+            gp.n_items = (uint32_t)(pairs * gp.ksplit);
             KSB_CUDA(cudaMemsetAsync(d->d_gbits, 0, (uint64_t)gp.kblocks * d->g_npad * 16, st));
-            KSB_CUDA(cudaMemsetAsync(d->d_gwq, 0, (uint64_t)d->g_planes * gp.kpad, st));
+            KSB_CUDA(cudaMemsetAsync(d->d_gwq, 0, (uint64_t)d->g_planes * gp.kpad + 256, st));
             KSB_CUDA(launch_kb_build(goff, gmem, gw, c0, n, gp.npad, gp.kpad, gp.planes, d->d_gbits, d->d_gwq, lc));
             KSB_CUDA(launch_k4_gram(gp, g, lc));
             d->launches += 2;

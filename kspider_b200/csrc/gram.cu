@@ -19,8 +19,11 @@ namespace {
 constexpr uint32_t kTile = kGramTile;        // 128 samples per tile side (UMMA M = N = 128)
 constexpr uint32_t kKB = kGramKBlock;        // 128 colours per K-block = one 128-byte swizzle atom of u8
 constexpr uint32_t kStages = 2;
-constexpr uint32_t kThreads = 256;
+constexpr uint32_t kProducerWarps = 16;
+constexpr uint32_t kProducers = kProducerWarps * 32;   // expansion + epilogue threads
+constexpr uint32_t kThreads = kProducers + 32;          // + the MMA-issuing warp
 constexpr uint32_t kTileBytes = kTile * kKB;  // 16 KB: one operand tile (128 rows x 128 B)
+constexpr uint32_t kTmemCols = 512;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -48,16 +51,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 // Instruction descriptor (cute::UMMA::InstrDescriptor) for kind::i8:
 //   c_format [4,6) = 2 (S32), a_format [7,10) = 0 (u8), b_format [10,13) = 0 (u8), a/b major = K (0),
 //   n_dim [17,23) = N >> 3, m_dim [24,29) = M >> 4
-constexpr uint32_t kIdesc = (2u << 4) | ((kTile >> 3) << 17) | ((kTile >> 4) << 24);
+__device__ __forceinline__ constexpr uint32_t umma_idesc(uint32_t n) { return (2u << 4) | ((n >> 3) << 17) | ((kTile >> 4) << 24); }
 
-__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t"
         "}\n" ::"r"(tmem_d),
-        "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -65,6 +68,21 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
 
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
@@ -123,171 +141,219 @@ cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* 
     return cudaGetLastError();
 }
 
+
 // ------------------------------------------------------------------------------------------------
-// k4_gram<P>: persistent, one CTA per SM.  Work item = (row tile ti, column tile tj >= ti, K split).
-// Per K-block of 128 colours all 256 threads expand bitmap words into the swizzled u8 tiles
-// (A_p[row][k] = bit ? byte_p(w_k) : 0, B[row][k] = bit), thread 0 issues 4 x P UMMAs
-// (128 x 128 x 32, u8 x u8 -> s32 in TMEM) and commits them to the stage's mbarrier, so the
-// expansion of block kb+1 overlaps the MMAs of block kb.  Epilogue: TMEM -> registers
-// (tcgen05.ld), planes combined to u64, 32x32 transposes through shared memory so that one warp
-// instruction adds 32 consecutive cells of one triangle row.
+// k4_gram<P>: persistent, one CTA per SM, 16 producer/epilogue warps + 1 MMA-issuing warp.
+// Work item = (row tile ti, NB = 4/P adjacent column tiles >= ti, K split), fetched from a global
+// counter.  Per K-block of 128 colours the producers expand bitmap bytes through two 256-entry
+// look-up tables (byte -> 8 bytes of 0x01 / 0xFF) into the 128B-swizzled K-major u8 tiles of the
+// stage: A_p[row][k] = bit ? byte_p(w_k) : 0 (one tile per weight byte plane), B[row][k] = bit
+// (NB tiles, contiguous, so two column tiles are ONE N = 256 UMMA).  Each producer warp arrives on
+// the stage's `full` mbarrier; the MMA thread waits for it, issues 4 K-steps x P planes of
+// tcgen05.mma kind::i8 (u8 x u8 -> s32, accumulators in the 512 TMEM columns) and commits them to
+// the stage's `empty` mbarrier, so expansion of block kb+1 overlaps the MMAs of block kb.
+// Epilogue: tcgen05.ld, byte planes combined to u64, 32x16 transposes through shared memory so that
+// one warp instruction adds 2 x 16 consecutive cells of triangle rows (red.global.add.u64).
 // ------------------------------------------------------------------------------------------------
 template <int P>
 __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ GramParams prm,
                                                         const __grid_constant__ TriGeom G) {
+    constexpr uint32_t NB = 4 / P;
+    constexpr uint32_t kStageBytes = (P + NB) * kTileBytes;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    // stage layout: [P A tiles][B tile]; after the stages: weights ring, barriers, tmem pointer
-    constexpr uint32_t kStageBytes = (P + 1) * kTileBytes;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint32_t* wsm = reinterpret_cast<uint32_t*>(smem + kStages * kStageBytes);          // [2][P][32] u32 = 128 B per plane
-    unsigned long long* bars = reinterpret_cast<unsigned long long*>(wsm + 2 * P * 32);  // empty[kStages], done
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kStages + 1);
+    unsigned long long* lut01 = reinterpret_cast<unsigned long long*>(smem + kStages * kStageBytes);
+    unsigned long long* lutff = lut01 + 256;
+    unsigned long long* bars = lutff + 256;  // full[kStages], empty[kStages], done
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 1);
+    uint32_t* item_slot = tmem_slot + 1;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
-    constexpr uint32_t kCols = (P == 1) ? 128u : (P == 2 ? 256u : 512u);
 
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kCols) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (tid == 32) {
-        for (uint32_t s = 0; s <= kStages; s++) mbar_init(smem_u32(bars + s), 1);
+        for (uint32_t s = 0; s < kStages; s++) {
+            mbar_init(smem_u32(bars + s), kProducerWarps);
+            mbar_init(smem_u32(bars + kStages + s), 1);
+        }
+        mbar_init(smem_u32(bars + 2 * kStages), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 256) {
+        const unsigned long long lo = ((tid & 0xFu) * 0x00204081u) & 0x01010101u;
+        const unsigned long long hi = ((tid >> 4) * 0x00204081u) & 0x01010101u;
+        const unsigned long long e = lo | (hi << 32);
+        lut01[tid] = e;
+        lutff[tid] = e * 0xFFull;
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-    const uint32_t bar_done = smem_u32(bars + kStages);
-
-    const uint32_t r = tid & 127u;   // tile row this thread expands
-    const uint32_t h = tid >> 7;     // which half of the K-block (words 2h, 2h+1)
-    const uint32_t row_off = (r >> 3) * 1024u + (r & 7u) * 128u;
-    const uint32_t sw = r & 7u;
+    const uint32_t bar_done = smem_u32(bars + 2 * kStages);
     const uint32_t T = prm.tiles;
-    const uint4* wq4 = reinterpret_cast<const uint4*>(prm.wq);
+    uint32_t it = 0, done_phase = 0;
 
-    uint32_t it = 0;          // K-blocks processed by this CTA so far (all items): stage / phase bookkeeping
-    uint32_t done_phase = 0;
-    for (unsigned long long item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
-        uint32_t q = (uint32_t)(item / prm.ksplit);
-        const uint32_t sp = (uint32_t)(item % prm.ksplit);
+    for (;;) {
+        if (tid == 0) *item_slot = atomicAdd(prm.counter, 1u);
+        __syncthreads();
+        const uint32_t item = *item_slot;
+        if (item >= prm.n_items) break;
+        uint32_t q = item / prm.ksplit;
+        const uint32_t sp = item - q * prm.ksplit;
         uint32_t ti = prm.tile_lo;
-        while (q >= T - ti) { q -= T - ti; ti++; }
-        const uint32_t tj = ti + q;
+        for (;;) {
+            const uint32_t ng = (T - ti + NB - 1) / NB;
+            if (q < ng) break;
+            q -= ng;
+            ti++;
+        }
+        const uint32_t tj0 = ti + q * NB;
+        const uint32_t ncol = min(NB, T - tj0);
         const uint32_t kb0 = (uint32_t)((unsigned long long)prm.kblocks * sp / prm.ksplit);
         const uint32_t kb1 = (uint32_t)((unsigned long long)prm.kblocks * (sp + 1) / prm.ksplit);
-        if (kb0 >= kb1) continue;
-        const uint32_t i0 = ti * kTile, j0 = tj * kTile;
+        const uint32_t i0 = ti * kTile;
 
-        // prologue: weights of kb0 straight to the ring, weights of kb0+1 and bits of kb0 to registers
-        uint4 wreg = make_uint4(0, 0, 0, 0);
-        if (tid < 8 * P) {
-            const uint32_t p = tid >> 3, c = tid & 7u;
-            reinterpret_cast<uint4*>(wsm + ((kb0 & 1u) * P + p) * 32)[c] = __ldg(wq4 + ((unsigned long long)p * prm.kpad + (unsigned long long)kb0 * kKB) / 16 + c);
-            if (kb0 + 1 < kb1) wreg = __ldg(wq4 + ((unsigned long long)p * prm.kpad + (unsigned long long)(kb0 + 1) * kKB) / 16 + c);
-        }
-        const uint2* abits = reinterpret_cast<const uint2*>(prm.bits) + ((unsigned long long)i0 + r) * 2 + h;
-        const uint2* bbits = reinterpret_cast<const uint2*>(prm.bits) + ((unsigned long long)j0 + r) * 2 + h;
-        const unsigned long long kb_stride = (unsigned long long)prm.npad * 2;  // uint2 per K-block
-        uint2 an = __ldg(abits + kb_stride * kb0), bn = __ldg(bbits + kb_stride * kb0);
-        __syncthreads();
-
-        for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
-            const uint32_t st = it % kStages;
-            const uint2 a = an, b = bn;
-            if (kb + 1 < kb1) { an = __ldg(abits + kb_stride * (kb + 1)); bn = __ldg(bbits + kb_stride * (kb + 1)); }
-            // weights: ring slot of kb+1 <- registers, registers <- kb+2
-            if (tid < 8 * P) {
-                const uint32_t p = tid >> 3, c = tid & 7u;
-                if (kb + 1 < kb1) reinterpret_cast<uint4*>(wsm + (((kb + 1) & 1u) * P + p) * 32)[c] = wreg;
-                if (kb + 2 < kb1) wreg = __ldg(wq4 + ((unsigned long long)p * prm.kpad + (unsigned long long)(kb + 2) * kKB) / 16 + c);
+        if (warp < kProducerWarps) {
+            // ---------------- producers: expansion
+            const uint32_t nunits = (1u + ncol) * 256u;  // (tile, row, half K-block)
+            const uint2* src[3];
+            uint32_t dst_off[3];
+            uint2 nb[3];
+            const unsigned long long kb_stride = (unsigned long long)prm.npad * 2;  // uint2 per K-block
+#pragma unroll
+            for (uint32_t k = 0; k < 3; k++) {
+                const uint32_t u = tid + kProducers * k;
+                const uint32_t tsel = u >> 8, r = (u & 255u) >> 1, h = u & 1u;
+                const uint32_t sample = (tsel == 0 ? i0 : (tj0 + tsel - 1) * kTile) + r;
+                src[k] = reinterpret_cast<const uint2*>(prm.bits) + (unsigned long long)sample * 2 + h;
+                // byte offset inside the stage of chunk 0 of this unit's row; the chunk index is XOR-ed in later
+                dst_off[k] = (tsel == 0 ? 0u : (P + tsel - 1) * kTileBytes) + (r >> 3) * 1024u + (r & 7u) * 128u;
+                nb[k] = make_uint2(0, 0);
+                if (u < nunits && kb0 < kb1) nb[k] = __ldg(src[k] + kb_stride * kb0);
             }
-            if (it >= kStages) mbar_wait(smem_u32(bars + st), ((it / kStages) - 1u) & 1u);  // MMAs that read this stage are done
-            uint8_t* stage = smem + st * kStageBytes;
-            const uint32_t* wk = wsm + (kb & 1u) * P * 32 + h * 16;
+            for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
+                const uint32_t st = it % kStages;
+                uint2 cur[3];
 #pragma unroll
-            for (uint32_t wd = 0; wd < 2; wd++) {
-                const uint32_t av = wd ? a.y : a.x, bv = wd ? b.y : b.x;
-                uint32_t sa[8], sb[8];
-#pragma unroll
-                for (uint32_t n = 0; n < 8; n++) {
-                    sa[n] = (((av >> (4 * n)) & 0xFu) * 0x00204081u) & 0x01010101u;
-                    sb[n] = (((bv >> (4 * n)) & 0xFu) * 0x00204081u) & 0x01010101u;
+                for (uint32_t k = 0; k < 3; k++) {
+                    cur[k] = nb[k];
+                    if (tid + kProducers * k < nunits && kb + 1 < kb1) nb[k] = __ldg(src[k] + kb_stride * (kb + 1));
                 }
+                if (it >= kStages) mbar_wait(smem_u32(bars + kStages + st), ((it / kStages) - 1u) & 1u);
+                uint8_t* stage = smem + st * kStageBytes;
 #pragma unroll
-                for (uint32_t c = 0; c < 2; c++) {
-                    const uint32_t chunk = (h * 2 + wd) * 2 + c;            // 16-byte chunk index inside the 128-byte row
-                    const uint32_t off = row_off + ((chunk ^ sw) << 4);
-                    *reinterpret_cast<uint4*>(stage + P * kTileBytes + off) = make_uint4(sb[4 * c], sb[4 * c + 1], sb[4 * c + 2], sb[4 * c + 3]);
+                for (uint32_t k = 0; k < 3; k++) {
+                    const uint32_t u = tid + kProducers * k;
+                    if (u >= nunits) continue;
+                    const uint32_t h = u & 1u, sw = ((u & 255u) >> 1) & 7u;
+                    const bool is_a = u < 256u;
+#pragma unroll
+                    for (uint32_t wd = 0; wd < 2; wd++) {
+                        const uint32_t word = wd ? cur[k].y : cur[k].x;
+#pragma unroll
+                        for (uint32_t c = 0; c < 2; c++) {
+                            const uint32_t b0 = (word >> (16 * c)) & 0xFFu, b1 = (word >> (16 * c + 8)) & 0xFFu;
+                            const uint32_t chunk = (h * 2 + wd) * 2 + c;
+                            uint8_t* dst = stage + dst_off[k] + ((chunk ^ sw) << 4);
+                            if (!is_a) {
+                                const unsigned long long e0 = lut01[b0], e1 = lut01[b1];
+                                *reinterpret_cast<uint4*>(dst) = make_uint4((uint32_t)e0, (uint32_t)(e0 >> 32), (uint32_t)e1, (uint32_t)(e1 >> 32));
+                            } else {
+                                const unsigned long long e0 = lutff[b0], e1 = lutff[b1];
+#pragma unroll
+                                for (int p = 0; p < P; p++) {
+                                    const uint4 w = __ldg(reinterpret_cast<const uint4*>(prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)kb * kKB) + chunk);
+                                    *reinterpret_cast<uint4*>(dst + p * kTileBytes) =
+                                        make_uint4((uint32_t)e0 & w.x, (uint32_t)(e0 >> 32) & w.y, (uint32_t)e1 & w.z, (uint32_t)(e1 >> 32) & w.w);
+                                }
+                            }
+                        }
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(bars + st));
+            }
+            // ---------------- epilogue
+            if (kb0 < kb1) {
+                mbar_wait(bar_done, done_phase);
+                done_phase ^= 1u;
+                tc_fence_after();
+                uint32_t* tp = reinterpret_cast<uint32_t*>(smem) + warp * (32 * 17);  // stage memory is idle now
+                const uint32_t lq = warp & 3u, wg = warp >> 2;
+                const uint32_t rsel = lane >> 4, csel = lane & 15u;
+                for (uint32_t ch = wg; ch < ncol * 8u; ch += 4) {
+                    const uint32_t ct = ch >> 3, c16 = ch & 7u;
+                    unsigned long long acc[16];
+#pragma unroll
+                    for (uint32_t y = 0; y < 16; y++) acc[y] = 0ull;
 #pragma unroll
                     for (int p = 0; p < P; p++) {
-                        const uint32_t* w4 = wk + p * 32 + wd * 8 + c * 4;
-                        *reinterpret_cast<uint4*>(stage + p * kTileBytes + off) =
-                            make_uint4((sa[4 * c] * 0xFFu) & w4[0], (sa[4 * c + 1] * 0xFFu) & w4[1],
-                                       (sa[4 * c + 2] * 0xFFu) & w4[2], (sa[4 * c + 3] * 0xFFu) & w4[3]);
+                        uint32_t v[16];
+                        tmem_ld16(tmem + ((32u * lq) << 16) + (p * NB + ct) * kTile + c16 * 16u, v);
+                        __syncwarp();
+#pragma unroll
+                        for (uint32_t x = 0; x < 16; x++) tp[lane * 17 + x] = v[x];  // row = lane, column = x
+                        __syncwarp();
+#pragma unroll
+                        for (uint32_t y = 0; y < 16; y++)
+                            acc[y] += (unsigned long long)tp[(2 * y + rsel) * 17 + csel] << (8 * p);  // row = 2y + rsel, column = csel
+                    }
+                    const uint32_t j = (tj0 + ct) * kTile + c16 * 16u + csel;
+#pragma unroll
+                    for (uint32_t y = 0; y < 16; y++) {
+                        const uint32_t i = i0 + 32u * lq + 2 * y + rsel;
+                        if (i < j && j < G.n && acc[y] != 0ull) {
+                            const unsigned long long ra = gram_row_addr(i, G);
+                            if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
+                        }
                     }
                 }
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
-            __syncthreads();
-            if (tid == 0) {
+        } else if (lane == 0) {
+            // ---------------- MMA issuer (one thread)
+            const uint32_t n0 = kTile * min(ncol, 2u);
+            const uint32_t n1 = ncol > 2 ? kTile * (ncol - 2) : 0u;
+            for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
+                const uint32_t st = it % kStages;
+                mbar_wait(smem_u32(bars + st), (it / kStages) & 1u);
                 tc_fence_after();
-                const uint32_t sbase = smem_u32(stage);
-                const uint64_t bdesc = umma_desc_sw128(sbase + P * kTileBytes);
+                const uint32_t sbase = smem_u32(smem + st * kStageBytes);
+                const uint64_t bdesc0 = umma_desc_sw128(sbase + P * kTileBytes);
+                const uint64_t bdesc1 = umma_desc_sw128(sbase + (P + 2) * kTileBytes);
 #pragma unroll
                 for (int p = 0; p < P; p++) {
                     const uint64_t adesc = umma_desc_sw128(sbase + p * kTileBytes);
 #pragma unroll
-                    for (uint32_t k = 0; k < 4; k++)  // 4 x K=32 inside the swizzle atom: +32 B = +2 in the address field
-                        umma_i8(tmem + p * kTile, adesc + 2 * k, bdesc + 2 * k, (kb > kb0 || k > 0) ? 1u : 0u);
+                    for (uint32_t k = 0; k < 4; k++) {  // 4 x K=32 inside the swizzle atom: +32 B = +2 in the address field
+                        const uint32_t acc = (kb > kb0 || k > 0) ? 1u : 0u;
+                        umma_i8(tmem + (p * NB) * kTile, adesc + 2 * k, bdesc0 + 2 * k, umma_idesc(n0), acc);
+                        if (NB > 2 && n1) umma_i8(tmem + (p * NB + 2) * kTile, adesc + 2 * k, bdesc1 + 2 * k, umma_idesc(n1), acc);
+                    }
                 }
-                umma_commit(smem_u32(bars + st));
+                umma_commit(smem_u32(bars + kStages + st));
                 if (kb + 1 == kb1) umma_commit(bar_done);
             }
-        }
-        // ---- epilogue
-        mbar_wait(bar_done, done_phase);
-        done_phase ^= 1u;
-        tc_fence_after();
-        uint32_t* tp = reinterpret_cast<uint32_t*>(smem) + warp * (32 * 33);  // stage memory is idle now
-        const uint32_t lane_base = 32u * (warp & 3u);
-        const uint32_t col_base = 64u * (warp >> 2);
-#pragma unroll 1
-        for (uint32_t cc = 0; cc < 2; cc++) {
-            unsigned long long acc[32];
-#pragma unroll
-            for (uint32_t x = 0; x < 32; x++) acc[x] = 0ull;
-#pragma unroll
-            for (int p = 0; p < P; p++) {
-                uint32_t v[32];
-                tmem_ld32(tmem + (lane_base << 16) + p * kTile + col_base + 32 * cc, v);
-                __syncwarp();
-#pragma unroll
-                for (uint32_t x = 0; x < 32; x++) tp[lane * 33 + x] = v[x];   // row = lane, column = x
-                __syncwarp();
-#pragma unroll
-                for (uint32_t x = 0; x < 32; x++) acc[x] += (unsigned long long)tp[x * 33 + lane] << (8 * p);  // row = x, column = lane
-            }
-            const uint32_t j = j0 + col_base + 32 * cc + lane;
-#pragma unroll
-            for (uint32_t x = 0; x < 32; x++) {
-                const uint32_t i = i0 + lane_base + x;
-                if (i < j && j < G.n && acc[x] != 0ull) {
-                    const unsigned long long ra = gram_row_addr(i, G);
-                    if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[x]) : "memory");
-                }
-            }
+        } else {
+            it += kb1 - kb0;
         }
         tc_fence_before();
-        __syncthreads();
+        __syncthreads();  // TMEM drained, stage memory free, item_slot reusable
+        tc_fence_after();
     }
     if (warp == 0) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kCols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
     }
 }
 
-size_t gram_smem_bytes(int planes) {
-    return 1024 + kStages * (size_t)(planes + 1) * kTileBytes + 2 * planes * 128 + 8 * (kStages + 1) + 16;
+uint32_t gram_cols_per_item(int planes) { return planes <= 1 ? 4u : (planes == 2 ? 2u : 1u); }
+
+static size_t gram_smem_bytes(int P) {
+    const size_t nb = 4 / P;
+    return 1024 + kStages * (P + nb) * (size_t)kTileBytes + 2 * 256 * 8 + 8 * (2 * kStages + 1) + 16;
 }
 
 template <int P>
@@ -305,7 +371,6 @@ cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const Launch
     switch (prm.planes) {
         case 1: return launch_gram_p<1>(prm, g, lc);
         case 2: return launch_gram_p<2>(prm, g, lc);
-        case 3:
         case 4: return launch_gram_p<4>(prm, g, lc);
         default: return cudaErrorInvalidValue;
     }

@@ -626,6 +626,8 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     info->n_mid_colors = d.n_mid_colors;
     info->n_gram_colors = d.n_gram_colors;
     info->gram_min_size = d.gram_min_size;
+    info->gram_planes = d.gram_planes;
+    info->n_gram_updates = d.n_gram_updates;
     info->n_zero_colors = d.n_zero_colors;
     info->max_color_size = d.max_color_size;
     info->payload_bytes = d.payload_bytes;

@@ -83,9 +83,10 @@ struct GramParams {
     uint32_t tiles;         // npad / kGramTile
     uint32_t ksplit;        // K splits per tile pair
     uint32_t tile_lo;       // first row tile intersecting the owned rows
-    uint32_t pad;
-    unsigned long long n_items;  // tile pairs (ti in [tile_lo, tile_hi), tj >= ti) x ksplit
+    uint32_t n_items;       // (row tile, group of gram_cols_per_item(planes) column tiles) x ksplit
+    uint32_t* counter;      // work counter, zeroed before the launch
 };
+uint32_t gram_cols_per_item(int planes);
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* gram_members,
                             const uint32_t* gram_weights, uint64_t c0, uint32_t n, uint32_t npad, uint32_t kpad,
                             uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
