@@ -229,7 +229,9 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
         // chunk of colours whose bitmap (npad x 16 B per K-block) stays L2-resident (<= 32 MB)
         d->g_npad = (uint32_t)((d->desc.n_samples + kGramTile - 1) / kGramTile * kGramTile);
         const uint64_t kb_total = (d->desc.n_gram_colors + kGramKBlock - 1) / kGramKBlock;
-        uint64_t kb_chunk = (32ull << 20) / ((uint64_t)d->g_npad * 16);
+        const char* cm = std::getenv("KSPIDER_GRAM_CHUNK_MB");  // tuning knob; default keeps the chunk's bitmap L2-resident
+        const uint64_t chunk_mb = (cm && std::atoi(cm) > 0) ? (uint64_t)std::atoi(cm) : 32;
+        uint64_t kb_chunk = (chunk_mb << 20) / ((uint64_t)d->g_npad * 16);
         kb_chunk = std::max<uint64_t>(1, std::min<uint64_t>(kb_chunk, 16384));  // 255 * 128 * 16384 < 2^31
         d->g_chunk_kblocks = (uint32_t)std::min(kb_total, kb_chunk);
         d->g_planes = d->desc.gram_planes <= 1 ? 1 : (d->desc.gram_planes == 2 ? 2 : 4);
@@ -440,7 +442,9 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
             gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
             // enough items for ~four waves of CTAs (items differ in size and are fetched dynamically),
             // never more splits than K-blocks
-            uint64_t ks = (4ull * (uint64_t)d->sms + pairs - 1) / pairs;
+            const char* wv = std::getenv("KSPIDER_GRAM_WAVES");  // tuning knob
+            const uint64_t waves = (wv && std::atoi(wv) > 0) ? (uint64_t)std::atoi(wv) : 4;
+            uint64_t ks = (waves * (uint64_t)d->sms + pairs - 1) / pairs;
             gp.ksplit = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ks, gp.kblocks));
             gp.n_items = (uint32_t)(pairs * gp.ksplit);
             KSB_CUDA(cudaMemsetAsync(d->d_gbits, 0, (uint64_t)gp.kblocks * d->g_npad * 16, st));

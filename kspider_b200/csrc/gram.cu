@@ -21,7 +21,8 @@ constexpr uint32_t kKB = kGramKBlock;        // 128 colours per K-block = one 12
 constexpr uint32_t kStages = 2;
 constexpr uint32_t kProducerWarps = 16;
 constexpr uint32_t kProducers = kProducerWarps * 32;   // expansion + epilogue threads
-constexpr uint32_t kThreads = kProducers + 32;          // + the MMA-issuing warp
+constexpr uint32_t kThreads = kProducers + 64;          // + the MMA-issuing warp + the TMA loader warp
+constexpr uint32_t kRing = 4;                           // ring of TMA-loaded bitmap rows + weights, one slot per K-block
 constexpr uint32_t kTileBytes = kTile * kKB;  // 16 KB: one operand tile (128 rows x 128 B)
 constexpr uint32_t kTmemCols = 512;
 
@@ -69,6 +70,14 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
@@ -143,29 +152,36 @@ cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* 
 
 
 // ------------------------------------------------------------------------------------------------
-// k4_gram<P>: persistent, one CTA per SM, 16 producer/epilogue warps + 1 MMA-issuing warp.
-// Work item = (row tile ti, NB = 4/P adjacent column tiles >= ti, K split), fetched from a global
-// counter.  Per K-block of 128 colours the producers expand bitmap bytes through two 256-entry
-// look-up tables (byte -> 8 bytes of 0x01 / 0xFF) into the 128B-swizzled K-major u8 tiles of the
-// stage: A_p[row][k] = bit ? byte_p(w_k) : 0 (one tile per weight byte plane), B[row][k] = bit
-// (NB tiles, contiguous, so two column tiles are ONE N = 256 UMMA).  Each producer warp arrives on
-// the stage's `full` mbarrier; the MMA thread waits for it, issues 4 K-steps x P planes of
-// tcgen05.mma kind::i8 (u8 x u8 -> s32, accumulators in the 512 TMEM columns) and commits them to
-// the stage's `empty` mbarrier, so expansion of block kb+1 overlaps the MMAs of block kb.
-// Epilogue: tcgen05.ld, byte planes combined to u64, 32x16 transposes through shared memory so that
-// one warp instruction adds 2 x 16 consecutive cells of triangle rows (red.global.add.u64).
+// k4_gram<P>: persistent, one CTA per SM: 16 producer/epilogue warps, 1 MMA-issuing thread, 1 TMA
+// loader thread.  Work item = (row tile ti, NB = 4/P adjacent column tiles >= ti, K split), fetched
+// from a global counter.
+//   loader    per K-block of 128 colours: cp.async.bulk of the bitmap rows of the A tile (2 KB), of
+//             the NB B tiles (NB x 2 KB, contiguous) and of the weight byte planes (P x 128 B) into a
+//             4-slot ring, two K-blocks ahead of the producers (`ready` mbarriers, complete_tx).
+//   producers expand the bits into the 128B-swizzled K-major u8 tiles of a stage:
+//             A_p[row][k] = bit ? byte_p(w_k) : 0 (one tile per weight byte plane), B[row][k] = bit
+//             (NB tiles, contiguous, so two column tiles are ONE N = 256 UMMA); every warp arrives on
+//             the stage's `full` mbarrier.
+//   MMA       waits `full`, issues 4 K-steps x P planes of tcgen05.mma kind::i8 (u8 x u8 -> s32,
+//             accumulators in the 512 TMEM columns), commits them to the stage's `empty` mbarrier:
+//             expansion of block kb+1 overlaps the MMAs of block kb.
+//   epilogue  tcgen05.ld, byte planes combined to u64, 32x16 transposes through shared memory so
+//             that one warp instruction adds 2 x 16 consecutive cells of triangle rows
+//             (red.global.add.u64).
 // ------------------------------------------------------------------------------------------------
 template <int P>
 __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ GramParams prm,
                                                         const __grid_constant__ TriGeom G) {
     constexpr uint32_t NB = 4 / P;
     constexpr uint32_t kStageBytes = (P + NB) * kTileBytes;
+    constexpr uint32_t kSlotBytes = (1 + NB) * 2048 + P * 128;  // bitmap rows of (1 + NB) tiles + weight planes
+    constexpr uint32_t kWOff = (1 + NB) * 2048;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    unsigned long long* lut01 = reinterpret_cast<unsigned long long*>(smem + kStages * kStageBytes);
-    unsigned long long* lutff = lut01 + 256;
-    unsigned long long* bars = lutff + 256;  // full[kStages], empty[kStages], done
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 1);
+    uint8_t* ring = smem + kStages * kStageBytes;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(ring + kRing * kSlotBytes);
+    // bars: full[kStages], empty[kStages], done, ready[kRing]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 1 + kRing);
     uint32_t* item_slot = tmem_slot + 1;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 
@@ -179,22 +195,17 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
             mbar_init(smem_u32(bars + kStages + s), 1);
         }
         mbar_init(smem_u32(bars + 2 * kStages), 1);
+        for (uint32_t s = 0; s < kRing; s++) mbar_init(smem_u32(bars + 2 * kStages + 1 + s), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (tid < 256) {
-        const unsigned long long lo = ((tid & 0xFu) * 0x00204081u) & 0x01010101u;
-        const unsigned long long hi = ((tid >> 4) * 0x00204081u) & 0x01010101u;
-        const unsigned long long e = lo | (hi << 32);
-        lut01[tid] = e;
-        lutff[tid] = e * 0xFFull;
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     const uint32_t bar_done = smem_u32(bars + 2 * kStages);
+    const uint32_t bar_ready0 = smem_u32(bars + 2 * kStages + 1);
     const uint32_t T = prm.tiles;
-    uint32_t it = 0, done_phase = 0;
+    uint32_t it = 0, done_phase = 0;  // it: K-blocks processed by this CTA so far, the same in every role
 
     for (;;) {
         if (tid == 0) *item_slot = atomicAdd(prm.counter, 1u);
@@ -219,55 +230,38 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
         if (warp < kProducerWarps) {
             // ---------------- producers: expansion
             const uint32_t nunits = (1u + ncol) * 256u;  // (tile, row, half K-block)
-            const uint2* src[3];
-            uint32_t dst_off[3];
-            uint2 nb[3];
-            const unsigned long long kb_stride = (unsigned long long)prm.npad * 2;  // uint2 per K-block
-#pragma unroll
-            for (uint32_t k = 0; k < 3; k++) {
-                const uint32_t u = tid + kProducers * k;
-                const uint32_t tsel = u >> 8, r = (u & 255u) >> 1, h = u & 1u;
-                const uint32_t sample = (tsel == 0 ? i0 : (tj0 + tsel - 1) * kTile) + r;
-                src[k] = reinterpret_cast<const uint2*>(prm.bits) + (unsigned long long)sample * 2 + h;
-                // byte offset inside the stage of chunk 0 of this unit's row; the chunk index is XOR-ed in later
-                dst_off[k] = (tsel == 0 ? 0u : (P + tsel - 1) * kTileBytes) + (r >> 3) * 1024u + (r & 7u) * 128u;
-                nb[k] = make_uint2(0, 0);
-                if (u < nunits && kb0 < kb1) nb[k] = __ldg(src[k] + kb_stride * kb0);
-            }
             for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
-                const uint32_t st = it % kStages;
-                uint2 cur[3];
-#pragma unroll
-                for (uint32_t k = 0; k < 3; k++) {
-                    cur[k] = nb[k];
-                    if (tid + kProducers * k < nunits && kb + 1 < kb1) nb[k] = __ldg(src[k] + kb_stride * (kb + 1));
-                }
-                if (it >= kStages) mbar_wait(smem_u32(bars + kStages + st), ((it / kStages) - 1u) & 1u);
+                const uint32_t st = it % kStages, slot = it % kRing;
+                mbar_wait(bar_ready0 + 8u * slot, (it / kRing) & 1u);                                      // bits + weights landed
+                if (it >= kStages) mbar_wait(smem_u32(bars + kStages + st), ((it / kStages) - 1u) & 1u);  // stage drained by the MMAs
                 uint8_t* stage = smem + st * kStageBytes;
+                const uint8_t* rs = ring + slot * kSlotBytes;
 #pragma unroll
                 for (uint32_t k = 0; k < 3; k++) {
                     const uint32_t u = tid + kProducers * k;
                     if (u >= nunits) continue;
-                    const uint32_t h = u & 1u, sw = ((u & 255u) >> 1) & 7u;
-                    const bool is_a = u < 256u;
+                    const uint32_t tsel = u >> 8, r = (u & 255u) >> 1, h = u & 1u, sw = r & 7u;
+                    const uint2 bits = *reinterpret_cast<const uint2*>(rs + u * 8u);  // slot rows are (tile, row, half) ordered
+                    uint8_t* drow = stage + (tsel == 0 ? 0u : (P + tsel - 1) * kTileBytes) + (r >> 3) * 1024u + (r & 7u) * 128u;
 #pragma unroll
                     for (uint32_t wd = 0; wd < 2; wd++) {
-                        const uint32_t word = wd ? cur[k].y : cur[k].x;
+                        const uint32_t word = wd ? bits.y : bits.x;
+                        uint32_t s4[8];  // 4 bits -> 4 bytes of 0/1
+#pragma unroll
+                        for (uint32_t n = 0; n < 8; n++) s4[n] = (((word >> (4 * n)) & 0xFu) * 0x00204081u) & 0x01010101u;
 #pragma unroll
                         for (uint32_t c = 0; c < 2; c++) {
-                            const uint32_t b0 = (word >> (16 * c)) & 0xFFu, b1 = (word >> (16 * c + 8)) & 0xFFu;
-                            const uint32_t chunk = (h * 2 + wd) * 2 + c;
-                            uint8_t* dst = stage + dst_off[k] + ((chunk ^ sw) << 4);
-                            if (!is_a) {
-                                const unsigned long long e0 = lut01[b0], e1 = lut01[b1];
-                                *reinterpret_cast<uint4*>(dst) = make_uint4((uint32_t)e0, (uint32_t)(e0 >> 32), (uint32_t)e1, (uint32_t)(e1 >> 32));
+                            const uint32_t chunk = (h * 2 + wd) * 2 + c;  // 16-byte chunk inside the 128-byte row
+                            uint8_t* dst = drow + ((chunk ^ sw) << 4);
+                            if (tsel != 0) {
+                                *reinterpret_cast<uint4*>(dst) = make_uint4(s4[4 * c], s4[4 * c + 1], s4[4 * c + 2], s4[4 * c + 3]);
                             } else {
-                                const unsigned long long e0 = lutff[b0], e1 = lutff[b1];
 #pragma unroll
                                 for (int p = 0; p < P; p++) {
-                                    const uint4 w = __ldg(reinterpret_cast<const uint4*>(prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)kb * kKB) + chunk);
+                                    const uint4 w = *reinterpret_cast<const uint4*>(rs + kWOff + p * 128 + chunk * 16);
                                     *reinterpret_cast<uint4*>(dst + p * kTileBytes) =
-                                        make_uint4((uint32_t)e0 & w.x, (uint32_t)(e0 >> 32) & w.y, (uint32_t)e1 & w.z, (uint32_t)(e1 >> 32) & w.w);
+                                        make_uint4((s4[4 * c] * 0xFFu) & w.x, (s4[4 * c + 1] * 0xFFu) & w.y,
+                                                   (s4[4 * c + 2] * 0xFFu) & w.z, (s4[4 * c + 3] * 0xFFu) & w.w);
                                 }
                             }
                         }
@@ -313,35 +307,59 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                     }
                 }
             }
-        } else if (lane == 0) {
+        } else if (warp == kProducerWarps) {
             // ---------------- MMA issuer (one thread)
-            const uint32_t n0 = kTile * min(ncol, 2u);
-            const uint32_t n1 = ncol > 2 ? kTile * (ncol - 2) : 0u;
-            for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
-                const uint32_t st = it % kStages;
-                mbar_wait(smem_u32(bars + st), (it / kStages) & 1u);
-                tc_fence_after();
-                const uint32_t sbase = smem_u32(smem + st * kStageBytes);
-                const uint64_t bdesc0 = umma_desc_sw128(sbase + P * kTileBytes);
-                const uint64_t bdesc1 = umma_desc_sw128(sbase + (P + 2) * kTileBytes);
+            if (lane == 0) {
+                const uint32_t n0 = kTile * min(ncol, 2u);
+                const uint32_t n1 = ncol > 2 ? kTile * (ncol - 2) : 0u;
+                for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
+                    const uint32_t st = it % kStages;
+                    mbar_wait(smem_u32(bars + st), (it / kStages) & 1u);
+                    tc_fence_after();
+                    const uint32_t sbase = smem_u32(smem + st * kStageBytes);
+                    const uint64_t bdesc0 = umma_desc_sw128(sbase + P * kTileBytes);
+                    const uint64_t bdesc1 = umma_desc_sw128(sbase + (P + 2) * kTileBytes);
 #pragma unroll
-                for (int p = 0; p < P; p++) {
-                    const uint64_t adesc = umma_desc_sw128(sbase + p * kTileBytes);
+                    for (int p = 0; p < P; p++) {
+                        const uint64_t adesc = umma_desc_sw128(sbase + p * kTileBytes);
 #pragma unroll
-                    for (uint32_t k = 0; k < 4; k++) {  // 4 x K=32 inside the swizzle atom: +32 B = +2 in the address field
-                        const uint32_t acc = (kb > kb0 || k > 0) ? 1u : 0u;
-                        umma_i8(tmem + (p * NB) * kTile, adesc + 2 * k, bdesc0 + 2 * k, umma_idesc(n0), acc);
-                        if (NB > 2 && n1) umma_i8(tmem + (p * NB + 2) * kTile, adesc + 2 * k, bdesc1 + 2 * k, umma_idesc(n1), acc);
+                        for (uint32_t k = 0; k < 4; k++) {  // 4 x K=32 inside the swizzle atom: +32 B = +2 in the address field
+                            const uint32_t acc = (kb > kb0 || k > 0) ? 1u : 0u;
+                            umma_i8(tmem + (p * NB) * kTile, adesc + 2 * k, bdesc0 + 2 * k, umma_idesc(n0), acc);
+                            if (NB > 2 && n1) umma_i8(tmem + (p * NB + 2) * kTile, adesc + 2 * k, bdesc1 + 2 * k, umma_idesc(n1), acc);
+                        }
                     }
+                    umma_commit(smem_u32(bars + kStages + st));
+                    if (kb + 1 == kb1) umma_commit(bar_done);
                 }
-                umma_commit(smem_u32(bars + kStages + st));
-                if (kb + 1 == kb1) umma_commit(bar_done);
+            } else {
+                it += kb1 - kb0;
             }
         } else {
-            it += kb1 - kb0;
+            // ---------------- TMA loader (one thread): bitmap rows + weights, two K-blocks ahead
+            if (lane == 0) {
+                const uint32_t bytes = (1u + ncol) * 2048u + P * 128u;
+                const uint8_t* gbits = reinterpret_cast<const uint8_t*>(prm.bits);
+                for (uint32_t kb = kb0; kb < kb1; kb++, it++) {
+                    // slot it % 4 was read for K-block it - 4; its readers finished before `full` of it - 2 completed
+                    if (kb >= kb0 + 2) mbar_wait(smem_u32(bars + (it & 1u)), ((it - 2u) / kStages) & 1u);
+                    const uint32_t slot = it % kRing;
+                    const uint32_t bar = bar_ready0 + 8u * slot;
+                    const uint32_t dst = smem_u32(ring + slot * kSlotBytes);
+                    const uint8_t* kbase = gbits + (unsigned long long)kb * prm.npad * 16ull;
+                    mbar_expect_tx(bar, bytes);
+                    tma_load_1d(dst, kbase + (unsigned long long)i0 * 16ull, 2048u, bar);
+                    tma_load_1d(dst + 2048u, kbase + (unsigned long long)tj0 * kTile * 16ull, ncol * 2048u, bar);
+#pragma unroll
+                    for (int p = 0; p < P; p++)
+                        tma_load_1d(dst + kWOff + p * 128, prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)kb * kKB, 128u, bar);
+                }
+            } else {
+                it += kb1 - kb0;
+            }
         }
         tc_fence_before();
-        __syncthreads();  // TMEM drained, stage memory free, item_slot reusable
+        __syncthreads();  // TMEM drained, stage + ring memory free, item_slot reusable
         tc_fence_after();
     }
     if (warp == 0) {
@@ -353,7 +371,7 @@ uint32_t gram_cols_per_item(int planes) { return planes <= 1 ? 4u : (planes == 2
 
 static size_t gram_smem_bytes(int P) {
     const size_t nb = 4 / P;
-    return 1024 + kStages * (P + nb) * (size_t)kTileBytes + 2 * 256 * 8 + 8 * (2 * kStages + 1) + 16;
+    return 1024 + kStages * (P + nb) * (size_t)kTileBytes + kRing * ((1 + nb) * 2048 + P * 128) + 8 * (2 * kStages + 1 + kRing) + 16;
 }
 
 template <int P>
