@@ -226,11 +226,11 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
     KSB_CUDA(cudaMallocAsync(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256), d->stream));
     build_k1(d);
     if (d->desc.n_gram_colors) {
-        // chunk of colours whose bitmap (npad x 16 B per K-block) stays L2-resident (<= 32 MB)
+        // chunk of colours whose bitmap (npad x 16 B per K-block) stays L2-resident (<= 64 MB of the 126 MB L2)
         d->g_npad = (uint32_t)((d->desc.n_samples + kGramTile - 1) / kGramTile * kGramTile);
         const uint64_t kb_total = (d->desc.n_gram_colors + kGramKBlock - 1) / kGramKBlock;
         const char* cm = std::getenv("KSPIDER_GRAM_CHUNK_MB");  // tuning knob; default keeps the chunk's bitmap L2-resident
-        const uint64_t chunk_mb = (cm && std::atoi(cm) > 0) ? (uint64_t)std::atoi(cm) : 32;
+        const uint64_t chunk_mb = (cm && std::atoi(cm) > 0) ? (uint64_t)std::atoi(cm) : 64;
         uint64_t kb_chunk = (chunk_mb << 20) / ((uint64_t)d->g_npad * 16);
         kb_chunk = std::max<uint64_t>(1, std::min<uint64_t>(kb_chunk, 16384));  // 255 * 128 * 16384 < 2^31
         d->g_chunk_kblocks = (uint32_t)std::min(kb_total, kb_chunk);
