@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cutoff", type=float, default=0.3)
     ap.add_argument("--dense-budget-gb", type=float, default=0.0)
+    ap.add_argument("--spill", default="auto", choices=["auto", "always", "never"], help="K3 sort-reduce spill path")
     ap.add_argument("--n-giant", type=int, default=16, help="cfg5: number of giant colours")
     ap.add_argument("--giant-size", type=int, default=4000, help="cfg5: members per giant colour")
     return ap.parse_args()
@@ -227,9 +228,9 @@ def main_b200(args):
         dist.broadcast(t, 0)
         shape = t.cpu().numpy()
         desc, d_payload = kd.broadcast_blob(idx, device, 0)
-        dev = kd.adopt(desc, d_payload, dense_budget_bytes=budget)
+        dev = kd.adopt(desc, d_payload, dense_budget_bytes=budget, spill=args.spill)
     else:
-        dev = idx.upload(device=local_rank, dense_budget_bytes=budget)
+        dev = idx.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
     N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram = (int(v) for v in shape)
 
     def step():
@@ -254,7 +255,7 @@ def main_b200(args):
         step()
     t_before = dev.info.t
     l_before = dev.info.gpu_launches
-    before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "gram_ms", "accumulate_ms", "post_ms")}
+    before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "gram_ms", "spill_emit_ms", "spill_sort_ms", "accumulate_ms", "post_ms")}
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -289,10 +290,10 @@ def main_b200(args):
         def e2e_step():
             nonlocal d2h
             if world == 1:
-                res = idx.pairwise(device=local_rank, want_records=True, dense_budget_bytes=budget)
+                res = idx.pairwise(device=local_rank, want_records=True, dense_budget_bytes=budget, spill=args.spill)
             else:
                 desc2, pay2 = kd.broadcast_blob(idx, device, 0)
-                dv = kd.adopt(desc2, pay2, dense_budget_bytes=budget)
+                dv = kd.adopt(desc2, pay2, dense_budget_bytes=budget, spill=args.spill)
                 res = dv.run_all_passes(want_records=True)
             labels, _ = res.cluster(N, "max_cont", args.cutoff)
             if world > 1:
@@ -391,7 +392,7 @@ def main_b200(args):
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "name": args.workload, "samples": N, "colors": C_,
                        "members": M, "pair_updates": U, "rows": rows, "edges": int(n_edges), "cutoff": args.cutoff,
-                       "parallelism": f"row-blocks x{world}", "passes": dev.n_passes,
+                       "parallelism": f"row-blocks x{world}", "passes": dev.n_passes, "spill": bool(dev.is_spill),
                        "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the triangle block is cleared every step)"},
             "phases_ms": phase, "wall_ms_per_step": wall_ms / args.steps,
             "timer": "torch.cuda.Event pair on the current stream around the K steps (every library call is stream-synchronous); phases: library CUDA events on the launching stream",

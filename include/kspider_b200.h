@@ -79,7 +79,9 @@ typedef struct ksb_opts {
     int32_t world;               /* 0 or 1 = whole triangle */
     int32_t want_records;        /* 1: build the {i,j,shared,min,avg,max} records and bring them to the host */
     uint64_t dense_budget_bytes; /* 0 = library default (80% of free HBM) */
-    uint64_t reserved[4];
+    uint64_t spill_mode;         /* K3 sort-reduce path: 0 = auto (only when the owned block would need more than
+                                    16 dense passes under the budget), 1 = always, 2 = never */
+    uint64_t reserved[3];
 } ksb_opts;
 
 /* One TSV row before formatting: 32 bytes, ids are the ORIGINAL sample ids of the index files. */
@@ -104,7 +106,9 @@ typedef struct ksb_timings {
     float d2h_ms;         /* records device->host */
     float cluster_ms;     /* K6 + K7 */
     float gram_ms;        /* K4: bitmap build + int8 tcgen05 Gram kernel (inside accumulate_ms) */
-    float reserved[6];
+    float spill_emit_ms;  /* K3: pair emission into chunk buffers */
+    float spill_sort_ms;  /* K3: radix sorts + reduce-by-key + run merges */
+    float reserved[4];
 } ksb_timings;
 
 typedef struct ksb_result_info {
@@ -162,6 +166,11 @@ int ksb_device_read_triangle(const ksb_device* dev, uint64_t* host_out, uint64_t
  * (sub-blocks of rows): select one with ksb_device_set_pass before ksb_accumulate / ksb_postpass. */
 int ksb_device_n_passes(const ksb_device* dev);
 int ksb_device_set_pass(ksb_device* dev, int pass);
+/* K3: 1 if this device handle runs the sort-reduce spill path (no dense block is allocated; the
+ * pass API above does not apply), and the spill run itself: emission in chunks of at most
+ * dense_budget_bytes / 40 updates, sort + reduce per chunk, merge, records in (i,j) order. */
+int ksb_device_is_spill(const ksb_device* dev);
+int ksb_device_run_spill(ksb_device* dev, int want_records, ksb_result** out);
 /* owned rows / cells / updates, launches and timings so far */
 int ksb_device_get_info(const ksb_device* dev, ksb_result_info* info);
 /* K5: containment + record compaction of the current pass (rows sorted by (i,j)).  *inout == NULL

@@ -27,11 +27,12 @@ def _view(ptr: int, n: int, dtype) -> np.ndarray:
 
 
 def make_opts(device: int = -1, rank: int = 0, world: int = 1, want_records: bool = True,
-              dense_budget_bytes: int = 0) -> Opts:
+              dense_budget_bytes: int = 0, spill: str = "auto") -> Opts:
     o = Opts()
     o.device, o.rank, o.world = device, rank, world
     o.want_records = 1 if want_records else 0
     o.dense_budget_bytes = int(dense_budget_bytes)
+    o.spill_mode = {"auto": 0, "always": 1, "never": 2}[spill]
     return o
 
 
@@ -168,7 +169,15 @@ class Device:
             return into
         return Result(h)
 
+    @property
+    def is_spill(self) -> bool:
+        return bool(lib().ksb_device_is_spill(self._h))
+
     def run_all_passes(self, want_records: bool = True) -> "Result":
+        if self.is_spill:  # K3: no dense passes, one sort-reduce run
+            h = C.c_void_p()
+            check(lib().ksb_device_run_spill(self._h, 1 if want_records else 0, C.byref(h)))
+            return Result(h)
         res = None
         for p in range(self.n_passes):
             self.set_pass(p)

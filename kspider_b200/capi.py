@@ -31,7 +31,7 @@ class IndexInfo(C.Structure):
 
 class Opts(C.Structure):
     _fields_ = [("device", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32), ("want_records", C.c_int32),
-                ("dense_budget_bytes", C.c_uint64), ("reserved", C.c_uint64 * 4)]
+                ("dense_budget_bytes", C.c_uint64), ("spill_mode", C.c_uint64), ("reserved", C.c_uint64 * 3)]
 
 
 class Record(C.Structure):
@@ -42,8 +42,8 @@ class Record(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("h2d_ms", "zero_ms", "small_ms", "mid_ms", "zero_touch_ms",
-                                         "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "gram_ms")] + \
-        [("reserved", C.c_float * 6)]
+                                         "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "gram_ms", "spill_emit_ms", "spill_sort_ms")] + \
+        [("reserved", C.c_float * 4)]
 
 
 class ResultInfo(C.Structure):
@@ -75,6 +75,8 @@ _PROTOS = {
     "ksb_device_triangle": (C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                          C.POINTER(C.c_uint64)]),
     "ksb_device_read_triangle": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "ksb_device_is_spill": (C.c_int, [C.c_void_p]),
+    "ksb_device_run_spill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "ksb_device_n_passes": (C.c_int, [C.c_void_p]),
     "ksb_device_set_pass": (C.c_int, [C.c_void_p, C.c_int]),
     "ksb_device_get_info": (C.c_int, [C.c_void_p, C.POINTER(ResultInfo)]),

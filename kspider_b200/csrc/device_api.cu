@@ -57,6 +57,9 @@ struct ksb_device {
     uint32_t* d_gbits = nullptr;
     uint8_t* d_gwq = nullptr;
     uint32_t g_npad = 0, g_chunk_kblocks = 0, g_planes = 0;
+    // K3 (spill)
+    uint64_t spill_mode = 0, budget = 0;
+    bool spill = false;
 };
 
 struct ksb_segment {
@@ -215,6 +218,14 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
     }
     int rc = plan_rows(d, row_updates, budget);
     if (rc) return rc;
+    d->budget = budget;
+    d->spill = d->spill_mode == 1 || (d->spill_mode == 0 && d->passes.size() > 16);
+    if (d->spill) {  // K3: one pseudo-pass over all owned rows, no dense block
+        const uint64_t N = d->desc.n_samples;
+        d->passes.assign(1, ksb_pass{d->row_begin, d->row_end, N ? rowstart(d->row_begin, N) : 0, d->owned_cells, d->owned_updates});
+        build_k1(d);
+        return KSB_OK;
+    }
     const uint64_t cells = d->tri_cells_alloc;
     KSB_CUDA(cudaMallocAsync(&d->d_tri, 8 * (cells + 8), d->stream));
     if (d->desc.n_zero_colors) KSB_CUDA(cudaMallocAsync(&d->d_touched, 4 * (cells / 32 + 2), d->stream));
@@ -313,6 +324,8 @@ static int opts_common(ksb_device* d, const ksb_opts* opts) {
     d->world = (opts && opts->world > 1) ? opts->world : 1;
     if (d->rank < 0 || d->rank >= d->world) { set_error("rank %d outside world %d", d->rank, d->world); return KSB_ERR_ARG; }
     std::memset(&d->t, 0, sizeof d->t);
+    d->spill_mode = opts ? opts->spill_mode : 0;
+    if (d->spill_mode > 2) { set_error("spill_mode must be 0 (auto), 1 (always) or 2 (never)"); return KSB_ERR_ARG; }
     return KSB_OK;
 }
 
@@ -383,8 +396,11 @@ int ksb_device_set_pass(ksb_device* d, int pass) {
     return KSB_OK;
 }
 
+int ksb_device_is_spill(const ksb_device* d) { return d && d->spill ? 1 : 0; }
+
 int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     if (!d) { set_error("ksb_accumulate: null device"); return KSB_ERR_ARG; }
+    if (d->spill) { set_error("ksb_accumulate: this device runs the spill path (ksb_device_run_spill)"); return KSB_ERR_ARG; }
     KSB_CUDA(cudaSetDevice(d->device));
     cudaStream_t st = stream_v ? static_cast<cudaStream_t>(stream_v) : d->stream;
     const ksb_pass& p = d->passes[d->cur_pass];
@@ -469,6 +485,7 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
 
 int ksb_device_read_triangle(const ksb_device* d, uint64_t* host_out, uint64_t cells) {
     if (!d || (!host_out && cells)) { set_error("ksb_device_read_triangle: null argument"); return KSB_ERR_ARG; }
+    if (d->spill) { set_error("ksb_device_read_triangle: the spill path has no dense block"); return KSB_ERR_ARG; }
     const ksb_pass& p = d->passes[d->cur_pass];
     if (cells != p.cells) { set_error("ksb_device_read_triangle: the current pass has %llu cells, caller asked for %llu", (unsigned long long)p.cells, (unsigned long long)cells); return KSB_ERR_ARG; }
     KSB_CUDA(cudaSetDevice(d->device));
@@ -507,6 +524,7 @@ void ksb_result_free(ksb_result* r) {
 // Scans the current pass of `d` and appends its rows to *inout (created when *inout == NULL).
 int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
     if (!d || !inout) { set_error("ksb_postpass: null argument"); return KSB_ERR_ARG; }
+    if (d->spill) { set_error("ksb_postpass: this device runs the spill path (ksb_device_run_spill)"); return KSB_ERR_ARG; }
     KSB_CUDA(cudaSetDevice(d->device));
     ksb_result* r = *inout;
     const bool created = (r == nullptr);
@@ -591,6 +609,188 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
     return KSB_OK;
 }
 
+// K3: emission in chunks -> sort + reduce per chunk -> merge into the accumulated run -> records.
+int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
+    if (!d || !out) { set_error("ksb_device_run_spill: null argument"); return KSB_ERR_ARG; }
+    if (!d->spill) { set_error("ksb_device_run_spill: this device runs the dense path"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    KSB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t st = d->stream;
+    const LaunchCfg lc{d->sms, st};
+    const IndexDesc& D = d->desc;
+    const uint8_t* P = d->d_payload;
+    const uint64_t N = D.n_samples;
+    uint32_t shift = 1;
+    while ((1ull << shift) < N) shift++;
+    const int end_bit = (int)(2 * shift);
+    TriGeom g = geom_of(d, d->passes[0]);
+    g.tri = nullptr;
+
+    // chunk capacity in updates: 8 + 4 bytes per entry, double-buffered for the sort, + 16 for the reduced run
+    const uint64_t biggest = std::max<uint64_t>({(uint64_t)kMidCols * kMidRows, (uint64_t)32 * kMaxPairsSmall,
+                                                 D.n_gram_colors || D.n_zero_colors ? D.max_color_size * (D.max_color_size - 1) / 2 : 0});
+    uint64_t cap = std::max<uint64_t>(d->budget / 40, 1ull << 20);
+    cap = std::min<uint64_t>(cap, std::max<uint64_t>(d->owned_updates + D.n_zero_members * D.max_color_size, 1ull << 20));
+    if (cap < biggest) { set_error("dense_budget_bytes too small for the spill path: one work unit emits up to %llu updates", (unsigned long long)biggest); return KSB_ERR_BUDGET; }
+    struct Chunk { int kind; uint64_t b, e; };
+    std::vector<Chunk> chunks;
+    for (uint32_t c = 0; c < d->k1.n_cls; c++) {  // K1 task ranges, class by class
+        const K1Class& kc = d->k1.cls[c];
+        const uint64_t per_task = (uint64_t)kc.k * kc.s * (kc.s - 1) / 2;
+        const uint64_t n_tasks = (kc.n + kc.k - 1) / kc.k, step = std::max<uint64_t>(1, cap / per_task);
+        for (uint64_t t = 0; t < n_tasks; t += step) chunks.push_back({0, kc.task_begin + t, kc.task_begin + std::min(n_tasks, t + step)});
+    }
+    {
+        const uint64_t step = std::max<uint64_t>(1, cap / ((uint64_t)kMidCols * kMidRows));
+        for (uint64_t t = 0; t < D.n_mid_items; t += step) chunks.push_back({1, t, std::min<uint64_t>(D.n_mid_items, t + step)});
+        const uint64_t per = std::max<uint64_t>(1, D.max_color_size * (D.max_color_size - 1) / 2), cstep = std::max<uint64_t>(1, cap / per);
+        for (uint64_t t = 0; t < D.n_gram_colors; t += cstep) chunks.push_back({2, t, std::min<uint64_t>(D.n_gram_colors, t + cstep)});
+        for (uint64_t t = 0; t < D.n_zero_colors; t += cstep) chunks.push_back({3, t, std::min<uint64_t>(D.n_zero_colors, t + cstep)});
+    }
+
+    unsigned long long *keys = nullptr, *keys2 = nullptr, *uniq = nullptr, *sums = nullptr, *d_cnt = nullptr;
+    uint32_t *vals = nullptr, *vals2 = nullptr;
+    void* tmp = nullptr;
+    size_t tmp_bytes = 0;
+    unsigned long long *acc_k = nullptr, *acc_s = nullptr;  // accumulated run
+    uint64_t acc_n = 0;
+    ksb_result* r = nullptr;
+    ksb_segment seg;
+    int rc = KSB_OK;
+    cudaError_t e = cudaSuccess;
+    cudaEvent_t e0 = g_ctx[d->device].e0, e1 = g_ctx[d->device].e1;
+    float emit_ms = 0.f, sort_ms = 0.f;
+#define SP(call) do { e = (call); if (e != cudaSuccess) goto cuda_fail; } while (0)
+    SP(spill_temp_bytes(cap, end_bit, &tmp_bytes));
+    SP(cudaMallocAsync(&keys, 8 * cap, st));
+    SP(cudaMallocAsync(&keys2, 8 * cap, st));
+    SP(cudaMallocAsync(&vals, 4 * cap, st));
+    SP(cudaMallocAsync(&vals2, 4 * cap, st));
+    SP(cudaMallocAsync(&uniq, 8 * cap, st));
+    SP(cudaMallocAsync(&sums, 8 * cap, st));
+    SP(cudaMallocAsync(&d_cnt, 16, st));
+    SP(cudaMallocAsync(&tmp, std::max<size_t>(tmp_bytes, 256), st));
+    for (const Chunk& ch : chunks) {
+        const SpillBuf sb{keys, vals, d_cnt, shift};
+        SP(cudaMemsetAsync(d_cnt, 0, 16, st));
+        SP(cudaEventRecord(e0, st));
+        if (ch.kind == 0)
+            SP(launch_k1_spill(d->k1, reinterpret_cast<const uint32_t*>(P + D.off_small_members),
+                               reinterpret_cast<const uint32_t*>(P + D.off_small_weights), g, sb, ch.b, ch.e, lc));
+        else if (ch.kind == 1)
+            SP(launch_k2_spill(reinterpret_cast<const MidItem*>(P + D.off_mid_items), ch.b, ch.e,
+                               reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
+                               reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
+                               reinterpret_cast<const uint32_t*>(P + D.off_mid_members),
+                               reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, sb, lc));
+        else if (ch.kind == 2)
+            SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets),
+                                  reinterpret_cast<const uint32_t*>(P + D.off_gram_members),
+                                  reinterpret_cast<const uint32_t*>(P + D.off_gram_weights), g, sb, lc));
+        else
+            SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_zero_offsets),
+                                  reinterpret_cast<const uint32_t*>(P + D.off_zero_members), nullptr, g, sb, lc));
+        SP(cudaEventRecord(e1, st));
+        d->launches++;
+        unsigned long long n = 0;
+        SP(cudaMemcpyAsync(&n, d_cnt, 8, cudaMemcpyDeviceToHost, st));
+        SP(cudaStreamSynchronize(st));
+        emit_ms += ev_ms(e0, e1);
+        if (n > cap) { set_error("spill chunk overflow: %llu > %llu", n, (unsigned long long)cap); rc = KSB_ERR_CUDA; goto done; }
+        if (n == 0) continue;
+        SP(cudaEventRecord(e0, st));
+        SP(spill_sort_reduce_chunk(tmp, tmp_bytes, keys, keys2, vals, vals2, n, end_bit, uniq, sums, d_cnt + 1, st));
+        unsigned long long m = 0;
+        SP(cudaMemcpyAsync(&m, d_cnt + 1, 8, cudaMemcpyDeviceToHost, st));
+        SP(cudaStreamSynchronize(st));
+        d->launches += 2;
+        if (acc_n == 0) {
+            SP(cudaMallocAsync(&acc_k, 8 * m, st));
+            SP(cudaMallocAsync(&acc_s, 8 * m, st));
+            SP(cudaMemcpyAsync(acc_k, uniq, 8 * m, cudaMemcpyDeviceToDevice, st));
+            SP(cudaMemcpyAsync(acc_s, sums, 8 * m, cudaMemcpyDeviceToDevice, st));
+            acc_n = m;
+        } else {  // merge: concat(acc, run) -> sort -> reduce
+            const uint64_t tot = acc_n + m;
+            unsigned long long *ck = nullptr, *cs = nullptr, *ck2 = nullptr, *cs2 = nullptr, *nk = nullptr, *ns = nullptr;
+            void* mtmp = nullptr;
+            size_t mtb = 0;
+            SP(spill_temp_bytes(tot, end_bit, &mtb));
+            SP(cudaMallocAsync(&ck, 8 * tot, st));
+            SP(cudaMallocAsync(&cs, 8 * tot, st));
+            SP(cudaMallocAsync(&ck2, 8 * tot, st));
+            SP(cudaMallocAsync(&cs2, 8 * tot, st));
+            SP(cudaMallocAsync(&nk, 8 * tot, st));
+            SP(cudaMallocAsync(&ns, 8 * tot, st));
+            SP(cudaMallocAsync(&mtmp, std::max<size_t>(mtb, 256), st));
+            SP(cudaMemcpyAsync(ck, acc_k, 8 * acc_n, cudaMemcpyDeviceToDevice, st));
+            SP(cudaMemcpyAsync(ck + acc_n, uniq, 8 * m, cudaMemcpyDeviceToDevice, st));
+            SP(cudaMemcpyAsync(cs, acc_s, 8 * acc_n, cudaMemcpyDeviceToDevice, st));
+            SP(cudaMemcpyAsync(cs + acc_n, sums, 8 * m, cudaMemcpyDeviceToDevice, st));
+            SP(spill_sort_reduce_runs(mtmp, mtb, ck, ck2, cs, cs2, tot, end_bit, nk, ns, d_cnt + 1, st));
+            unsigned long long mm = 0;
+            SP(cudaMemcpyAsync(&mm, d_cnt + 1, 8, cudaMemcpyDeviceToHost, st));
+            SP(cudaStreamSynchronize(st));
+            d->launches += 2;
+            cudaFreeAsync(acc_k, st); cudaFreeAsync(acc_s, st);
+            cudaFreeAsync(ck, st); cudaFreeAsync(cs, st); cudaFreeAsync(ck2, st); cudaFreeAsync(cs2, st); cudaFreeAsync(mtmp, st);
+            acc_k = nk; acc_s = ns; acc_n = mm;
+        }
+        SP(cudaEventRecord(e1, st));
+        SP(cudaStreamSynchronize(st));
+        sort_ms += ev_ms(e0, e1);
+    }
+    // ---- records from the final run
+    r = new (std::nothrow) ksb_result();
+    if (!r) { set_error("out of memory"); rc = KSB_ERR_NOMEM; goto done; }
+    r->device = d->device;
+    r->n_samples = N;
+    std::memset(&r->info, 0, sizeof r->info);
+    r->info.row_begin = d->row_begin;
+    r->info.row_end = d->row_end;
+    r->info.owned_cells = d->owned_cells;
+    r->have_host = want_records != 0;
+    SP(cudaEventRecord(e0, st));
+    if (acc_n) {
+        SP(cudaMallocAsync(&seg.d_records, sizeof(ksb_record) * acc_n, st));
+        SP(cudaMallocAsync(&seg.d_pairs, 8 * acc_n, st));
+        seg.n = acc_n;
+        r->seg.push_back(seg);
+        SP(launch_k5_sparse(acc_k, acc_s, acc_n, shift, reinterpret_cast<const uint32_t*>(P + D.off_totals),
+                            reinterpret_cast<const uint32_t*>(P + D.off_sample_ids), seg.d_records, seg.d_pairs, lc));
+        d->launches++;
+        if (r->have_host) {
+            uint64_t got = sizeof(ksb_record) * acc_n;
+            SP(pinned_acquire(reinterpret_cast<void**>(&r->h_records), &got));
+            r->h_capacity = got / sizeof(ksb_record);
+            SP(cudaMemcpyAsync(r->h_records, seg.d_records, sizeof(ksb_record) * acc_n, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    SP(cudaEventRecord(e1, st));
+    SP(cudaStreamSynchronize(st));
+    d->t.post_ms += ev_ms(e0, e1);
+    d->t.spill_emit_ms += emit_ms;
+    d->t.spill_sort_ms += sort_ms;
+    d->t.accumulate_ms += emit_ms + sort_ms;
+    r->info.n_rows = acc_n;
+    r->info.n_updates = d->owned_updates;
+    r->info.gpu_launches = d->launches;
+    r->info.t = d->t;
+    goto done;
+cuda_fail:
+    set_error("spill path: %s", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    rc = KSB_ERR_CUDA;
+done:
+#undef SP
+    for (void* p : {(void*)keys, (void*)keys2, (void*)vals, (void*)vals2, (void*)uniq, (void*)sums, (void*)d_cnt, tmp, (void*)acc_k, (void*)acc_s})
+        if (p) cudaFreeAsync(p, st);
+    cudaStreamSynchronize(st);
+    if (rc != KSB_OK) { if (r) ksb_result_free(r); return rc; }
+    *out = r;
+    return KSB_OK;
+}
+
 int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     if (!ix || !out) { set_error("ksb_pairwise: null argument"); return KSB_ERR_ARG; }
     *out = nullptr;
@@ -599,7 +799,8 @@ int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     if (rc) return rc;
     ksb_result* r = nullptr;
     const int want = opts ? opts->want_records : 1;
-    for (int p = 0; p < (int)d->passes.size() && rc == KSB_OK; p++) {
+    if (d->spill) rc = ksb_device_run_spill(d, want, &r);
+    for (int p = 0; !d->spill && p < (int)d->passes.size() && rc == KSB_OK; p++) {
         rc = ksb_device_set_pass(d, p);
         if (rc == KSB_OK) rc = ksb_accumulate(d, nullptr, 1);
         if (rc == KSB_OK) rc = ksb_postpass(d, want, &r);

@@ -30,20 +30,57 @@ __device__ __forceinline__ unsigned long long shfl_u64(unsigned long long v, uin
     return ((unsigned long long)hi << 32) | lo;
 }
 
+// Where an update goes.  Dense: `row` is the address of the virtual cell (row, 0) of the owned block
+// and the update is one red.  Spill (K3): `row` is (row index + 1) and the update is appended as
+// (key = row_index << shift | column, weight) to a chunk buffer through a warp-aggregated cursor;
+// every lane of the warp must call add() (the predicate says whether it has an update).
+struct DenseSink {
+    static __device__ __forceinline__ unsigned long long row(uint32_t x, const TriGeom& g) { return row_addr(x, g); }
+    static __device__ __forceinline__ unsigned long long col(uint32_t x) { return 8ull * x; }
+    __device__ __forceinline__ void add(bool pred, unsigned long long r, unsigned long long c, unsigned long long w) const {
+        if (pred) red_add_u64(r + c, w);
+    }
+};
+struct SpillSink {
+    unsigned long long* keys;
+    uint32_t* vals;
+    unsigned long long* cursor;
+    uint32_t shift;
+    static __device__ __forceinline__ unsigned long long row(uint32_t x, const TriGeom& g) {
+        return (x - g.rb >= g.nrows) ? 0ull : (unsigned long long)x + 1ull;
+    }
+    static __device__ __forceinline__ unsigned long long col(uint32_t x) { return x; }
+    __device__ __forceinline__ void add(bool pred, unsigned long long r, unsigned long long c, unsigned long long w) const {
+        const uint32_t m = __ballot_sync(KSB_FULL, pred);
+        if (m == 0u) return;
+        const uint32_t lane = threadIdx.x & 31u;
+        unsigned long long base = 0;
+        if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(cursor, (unsigned long long)__popc(m));
+        base = shfl_u64(base, __ffs(m) - 1);
+        if (pred) {
+            const unsigned long long o = base + __popc(m & ((1u << lane) - 1u));
+            keys[o] = ((r - 1ull) << shift) | c;
+            vals[o] = (uint32_t)w;
+        }
+    }
+};
+
 // ------------------------------------------------------------------------------------------------
 // K1: one warp per small colour (2 <= s <= 64).  Colours of one size s are a dense [n x s] block, so
 // a warp task loads 32/s whole colours (s <= 32) or one colour in two registers (s > 32) with one
 // coalesced load, then walks the rows: step a broadcasts row a of every group by shuffle and the
 // lanes holding a later member add the colour's weight into cell (row, own member).
 // ------------------------------------------------------------------------------------------------
+template <class Sink>
 __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params P,
                                                 const uint32_t* __restrict__ members,
                                                 const uint32_t* __restrict__ weights,
-                                                const __grid_constant__ TriGeom G) {
+                                                const __grid_constant__ TriGeom G, const Sink sink,
+                                                unsigned long long task_begin, unsigned long long task_end) {
     const uint32_t lane = threadIdx.x & 31u;
     const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
-    for (unsigned long long task = warp; task < P.n_tasks; task += nwarps) {
+    for (unsigned long long task = task_begin + warp; task < task_end; task += nwarps) {
         uint32_t lo = 0, hi = P.n_cls;
         while (hi - lo > 1) {
             const uint32_t mid = (lo + hi) >> 1;
@@ -64,13 +101,13 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
                 x = __ldg(mcls + col0 * s + lane);
                 w = __ldg(wcls + col0 + g);
             }
-            const unsigned long long ra = valid ? row_addr(x, G) : 0ull;
+            const unsigned long long ra = valid ? Sink::row(x, G) : 0ull;
             if (__ballot_sync(KSB_FULL, ra != 0ull) == 0u) continue;  // no owned row in this task
-            const unsigned long long cadd = 8ull * x;
+            const unsigned long long cadd = Sink::col(x);
             const uint32_t gb = g * s;
             for (uint32_t ar = 0; ar + 1 < s; ar++) {
                 const unsigned long long r = shfl_u64(ra, gb + ar);
-                if (valid && a > ar && r != 0ull) red_add_u64(r + cadd, w);
+                sink.add(valid && a > ar && r != 0ull, r, cadd, w);
             }
         } else {
             const uint32_t* m = mcls + t_in * s;
@@ -78,21 +115,21 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
             const uint32_t x0 = __ldg(m + lane);
             const uint32_t x1 = v1 ? __ldg(m + 32 + lane) : 0u;
             const unsigned long long w = __ldg(wcls + t_in);
-            const unsigned long long ra0 = row_addr(x0, G);
-            const unsigned long long ra1 = v1 ? row_addr(x1, G) : 0ull;
+            const unsigned long long ra0 = Sink::row(x0, G);
+            const unsigned long long ra1 = v1 ? Sink::row(x1, G) : 0ull;
             if (__ballot_sync(KSB_FULL, (ra0 | ra1) != 0ull) == 0u) continue;
-            const unsigned long long c0 = 8ull * x0, c1 = 8ull * x1;
+            const unsigned long long c0 = Sink::col(x0), c1 = Sink::col(x1);
 #pragma unroll 4
             for (uint32_t ar = 0; ar < 32; ar++) {
                 const unsigned long long r = shfl_u64(ra0, ar);
                 if (r != 0ull) {  // warp-uniform
-                    if (lane > ar) red_add_u64(r + c0, w);
-                    if (v1) red_add_u64(r + c1, w);
+                    sink.add(lane > ar, r, c0, w);
+                    sink.add(v1, r, c1, w);
                 }
             }
             for (uint32_t ar = 32; ar + 1 < s; ar++) {
                 const unsigned long long r = shfl_u64(ra1, ar - 32);
-                if (r != 0ull && v1 && lane + 32 > ar) red_add_u64(r + c1, w);
+                sink.add(r != 0ull && v1 && lane + 32 > ar, r, c1, w);
             }
         }
     }
@@ -105,7 +142,19 @@ cudaError_t launch_k1_small(const K1Params& p, const uint32_t* members, const ui
     unsigned long long ctas = (p.n_tasks + warps_per_cta - 1) / warps_per_cta;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;  // 8 x 256 threads = 2048 resident threads / SM
     if (ctas > cap) ctas = cap;
-    k1_small<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, members, weights, g);
+    k1_small<DenseSink><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, members, weights, g, DenseSink{}, 0ull, p.n_tasks);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k1_spill(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
+                            const SpillBuf& sb, unsigned long long task_begin, unsigned long long task_end,
+                            const LaunchCfg& lc) {
+    if (task_end <= task_begin) return cudaSuccess;
+    unsigned long long ctas = (task_end - task_begin + 7) / 8;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k1_small<SpillSink><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, members, weights, g, SpillSink{sb.keys, sb.vals, sb.cursor, sb.shift},
+                                                               task_begin, task_end);
     return cudaGetLastError();
 }
 
@@ -138,12 +187,14 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
-__global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ items, unsigned long long n_items,
+template <class Sink>
+__global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ items, unsigned long long item_begin,
+                                                   unsigned long long n_items,
                                                    const unsigned long long* __restrict__ mid_off,
                                                    const uint32_t* __restrict__ mid_sizes,
                                                    const uint32_t* __restrict__ mid_members,
                                                    const uint32_t* __restrict__ mid_weights,
-                                                   const __grid_constant__ TriGeom G) {
+                                                   const __grid_constant__ TriGeom G, const Sink sink) {
     __shared__ __align__(128) uint32_t sm_rows[kMidRows];
     __shared__ __align__(16) unsigned long long sm_ra[kMidRows];
     __shared__ __align__(8) unsigned long long sm_bar;
@@ -156,7 +207,7 @@ __global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ i
     __syncthreads();
     uint32_t phase = 0;
     const bool sharded = G.nrows < G.n;
-    for (unsigned long long it = blockIdx.x; it < n_items; it += gridDim.x) {
+    for (unsigned long long it = item_begin + blockIdx.x; it < n_items; it += gridDim.x) {
         const MidItem item = items[it];
         const uint32_t s = __ldg(mid_sizes + item.color);
         const uint32_t* m = mid_members + __ldg(mid_off + item.color);
@@ -178,16 +229,16 @@ __global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ i
         const uint32_t x = (b < s) ? __ldg(m + b) : 0u;
         mbar_wait(bar, phase);
         phase ^= 1u;
-        for (uint32_t r = tid; r < nr; r += kMidCols) sm_ra[r] = row_addr(sm_rows[r], G);
+        for (uint32_t r = tid; r < nr; r += kMidCols) sm_ra[r] = Sink::row(sm_rows[r], G);
         __syncthreads();
         // rows r with a0 + r < b pair with this thread's column
         const uint32_t lim = (b < s && b > item.a0) ? min(nr, b - item.a0) : 0u;
         const uint32_t wlim = __reduce_max_sync(KSB_FULL, lim);
-        const unsigned long long cadd = 8ull * x;
+        const unsigned long long cadd = Sink::col(x);
 #pragma unroll 4
         for (uint32_t r = 0; r < wlim; r++) {
             const unsigned long long ra = sm_ra[r];
-            if (ra != 0ull && r < lim) red_add_u64(ra + cadd, w);
+            sink.add(ra != 0ull && r < lim, ra, cadd, w);
         }
         __syncthreads();
     }
@@ -200,7 +251,57 @@ cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned
     unsigned long long ctas = n_items;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k2_mid<<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, n_items, mid_off, mid_sizes, mid_members, mid_weights, g);
+    k2_mid<DenseSink><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, mid_members, mid_weights, g,
+                                                                  DenseSink{});
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k2_spill(const MidItem* items, uint64_t item_begin, uint64_t item_end, const unsigned long long* mid_off,
+                            const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                            const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc) {
+    if (item_end <= item_begin) return cudaSuccess;
+    unsigned long long ctas = item_end - item_begin;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k2_mid<SpillSink><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, item_begin, item_end, mid_off, mid_sizes, mid_members, mid_weights, g,
+                                                                  SpillSink{sb.keys, sb.vals, sb.cursor, sb.shift});
+    return cudaGetLastError();
+}
+
+// Generic warp-per-colour emitter over a plain CSR section (Gram-routed and zero-weight colours in
+// spill mode; a zero weight appends (key, 0), which is exactly the reference's insert-with-0).
+__global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, unsigned long long c_end,
+                                                   const unsigned long long* __restrict__ off,
+                                                   const uint32_t* __restrict__ members,
+                                                   const uint32_t* __restrict__ weights,  // nullptr = weight 0
+                                                   const __grid_constant__ TriGeom G, const SpillSink sink) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long c = c_begin + warp; c < c_end; c += nwarps) {
+        const unsigned long long o = off[c];
+        const uint32_t s = (uint32_t)(off[c + 1] - o);
+        const uint32_t* m = members + o;
+        const unsigned long long w = weights ? __ldg(weights + c) : 0ull;
+        for (uint32_t a = 0; a + 1 < s; a++) {
+            const unsigned long long r = SpillSink::row(__ldg(m + a), G);
+            if (r == 0ull) continue;  // warp-uniform
+            for (uint32_t b0 = a + 1; b0 < s; b0 += 32) {
+                const uint32_t b = b0 + lane;
+                sink.add(b < s, r, b < s ? __ldg(m + b) : 0u, w);
+            }
+        }
+    }
+}
+
+cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const uint32_t* members,
+                               const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc) {
+    if (c_end <= c_begin) return cudaSuccess;
+    unsigned long long ctas = (c_end - c_begin + 7) / 8;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k3_emit_csr<<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, members, weights, g,
+                                                       SpillSink{sb.keys, sb.vals, sb.cursor, sb.shift});
     return cudaGetLastError();
 }
 
@@ -379,6 +480,45 @@ cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const
     if (nb == 0) return cudaSuccess;
     k5_emit<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_offsets, totals, sample_ids, records,
                                                          pairs);
+    return cudaGetLastError();
+}
+
+// K5 for the spill path: one thread per (key, sum) of the final sorted run.
+__global__ void __launch_bounds__(256) k5_sparse(const unsigned long long* __restrict__ keys,
+                                                 const unsigned long long* __restrict__ sums, unsigned long long n,
+                                                 uint32_t shift, const uint32_t* __restrict__ totals,
+                                                 const uint32_t* __restrict__ sample_ids, ksb_record* __restrict__ records,
+                                                 unsigned long long* __restrict__ pairs) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
+        const unsigned long long k = keys[r], v = sums[r];
+        const uint32_t i = (uint32_t)(k >> shift), j = (uint32_t)(k & ((1ull << shift) - 1ull));
+        float cmin, cavg, cmax;
+        containment(v, __ldg(totals + i), __ldg(totals + j), cmin, cavg, cmax);
+        uint4 a, b;
+        a.x = __ldg(sample_ids + i);
+        a.y = __ldg(sample_ids + j);
+        a.z = (uint32_t)v;
+        a.w = (uint32_t)(v >> 32);
+        b.x = __float_as_uint(cmin);
+        b.y = __float_as_uint(cavg);
+        b.z = __float_as_uint(cmax);
+        b.w = 0;
+        uint4* dst = reinterpret_cast<uint4*>(records + r);
+        dst[0] = a;
+        dst[1] = b;
+        pairs[r] = ((unsigned long long)i << 32) | j;
+    }
+}
+
+cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
+                             const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
+                             unsigned long long* pairs, const LaunchCfg& lc) {
+    if (n == 0) return cudaSuccess;
+    unsigned long long ctas = (n + 255) / 256;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k5_sparse<<<(unsigned)ctas, 256, 0, lc.stream>>>(keys, sums, n, shift, totals, sample_ids, records, pairs);
     return cudaGetLastError();
 }
 

@@ -55,6 +55,35 @@ cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned
 cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const uint32_t* zero_members,
                             uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc);
 
+// K3 (spill): chunk buffer the emit kernels append (key = row << shift | column, u32 weight) to
+struct SpillBuf {
+    unsigned long long* keys;
+    uint32_t* vals;
+    unsigned long long* cursor;  // entries appended so far
+    uint32_t shift;              // bits of a column index
+};
+cudaError_t launch_k1_spill(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
+                            const SpillBuf& sb, unsigned long long task_begin, unsigned long long task_end,
+                            const LaunchCfg& lc);
+cudaError_t launch_k2_spill(const MidItem* items, uint64_t item_begin, uint64_t item_end, const unsigned long long* mid_off,
+                            const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                            const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
+cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const uint32_t* members,
+                               const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
+
+cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
+                             const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
+                             unsigned long long* pairs, const LaunchCfg& lc);
+cudaError_t spill_temp_bytes(uint64_t n, int end_bit, size_t* bytes);
+cudaError_t spill_sort_reduce_chunk(void* tmp, size_t tmp_bytes, const unsigned long long* keys_in,
+                                    unsigned long long* keys_sorted, const uint32_t* vals_in, uint32_t* vals_sorted,
+                                    uint64_t n, int end_bit, unsigned long long* uniq, unsigned long long* sums,
+                                    unsigned long long* d_runs, cudaStream_t st);
+cudaError_t spill_sort_reduce_runs(void* tmp, size_t tmp_bytes, const unsigned long long* keys_in,
+                                   unsigned long long* keys_sorted, const unsigned long long* sums_in,
+                                   unsigned long long* sums_sorted, uint64_t n, int end_bit, unsigned long long* uniq,
+                                   unsigned long long* sums, unsigned long long* d_runs, cudaStream_t st);
+
 // K5: two passes over the owned block.  block_counts has post_blocks(cells)+1 entries.
 constexpr uint32_t kPostThreads = 256;
 constexpr uint32_t kPostPerThread = 8;
