@@ -286,6 +286,7 @@ def main_b200(args):
     if not args.no_e2e:
         n_e2e = max(1, min(args.steps, 5))
         d2h = 0
+        e2e_lib = {}
 
         def e2e_step():
             nonlocal d2h
@@ -299,6 +300,8 @@ def main_b200(args):
             if world > 1:
                 labels = kd.merge_labels(labels, device)
             d2h = res.info.n_rows * 32 + 4 * N
+            tt = res.info.t
+            e2e_lib.update({k: round(float(getattr(tt, k)), 3) for k in ("h2d_ms", "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms")})
             res.close()
             if world > 1:
                 dv.close()
@@ -316,7 +319,8 @@ def main_b200(args):
             dist.all_reduce(d2h_t, op=dist.ReduceOp.SUM)
         e2e = {"value": U / (float(e_ms.cpu()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": payload_bytes,
                "d2h_bytes_per_step": int(d2h_t.cpu()), "ms_per_step": float(e_ms.cpu()), "steps": n_e2e,
-               "timer": "host wall clock around ksb_pairwise + ksb_cluster (synchronous calls)"}
+               "timer": "host wall clock around ksb_pairwise + ksb_cluster (synchronous calls)",
+               "library_phases_ms_last_step": e2e_lib}
 
     if rank != 0:
         if world > 1:

@@ -136,6 +136,11 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info);
 /* compact index -> original sample id (ascending), and per-sample totals in the same order */
 const uint32_t* ksb_index_sample_ids(const ksb_index* ix);
 const uint32_t* ksb_index_totals(const ksb_index* ix);
+/* Row bands of the accumulator: row i (compact index) is only ever paired with columns
+ * lo[i] <= j < hi[i]; the device stores exactly these cells, row after row (cell (i,j) of the block
+ * ksb_device_triangle returns is at sum_{r<i, r owned}(hi[r]-lo[r]) + j - lo[i]).  Without locality in
+ * the colours this is the packed upper triangle. */
+int ksb_index_bands(const ksb_index* ix, const uint32_t** lo, const uint32_t** hi, uint64_t* band_cells);
 /* the binned CSR blob + its fixed-size descriptor: what another rank needs to adopt the index */
 const void* ksb_index_payload(const ksb_index* ix, uint64_t* bytes);
 const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes);

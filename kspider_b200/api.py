@@ -88,6 +88,13 @@ class Index:
         p = lib().ksb_index_descriptor(self._h, C.byref(n))
         return C.string_at(p, n.value)
 
+    def bands(self):
+        """(lo[N], hi[N], band_cells): the columns every row of the accumulator stores."""
+        lo, hi, n = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        check(lib().ksb_index_bands(self._h, C.byref(lo), C.byref(hi), C.byref(n)))
+        ns = int(self.info.n_samples)
+        return _view(lo.value, ns, np.uint32).copy(), _view(hi.value, ns, np.uint32).copy(), n.value
+
     def row_cuts(self, world: int) -> np.ndarray:
         cuts = np.empty(world + 1, dtype=np.uint64)
         check(lib().ksb_index_row_cuts(self._h, int(world), cuts.ctypes.data))

@@ -45,6 +45,9 @@ struct ksb_device {
     std::vector<ksb_pass> passes;
     uint32_t cur_pass = 0;
     uint64_t row_begin = 0, row_end = 0, owned_cells = 0, owned_updates = 0;
+    std::vector<uint64_t> bandstart;       // host copy, [N+1]: first cell of row i in the banded accumulator
+    unsigned long long* d_bandstart = nullptr;  // [N+1]
+    unsigned long long* d_rowbase = nullptr;    // [N]  bandstart[i] - band_lo[i]
     ksb::K1Params k1;
     ksb_timings t;
     uint64_t launches = 0;
@@ -80,14 +83,18 @@ struct ksb_result {
 
 namespace ksb {
 
-static inline uint64_t rowstart(uint64_t r, uint64_t n) { return r * (2 * n - 1 - r) / 2; }
+static inline uint64_t rowstart(const ksb_device* d, uint64_t r) { return d->bandstart.empty() ? 0 : d->bandstart[r]; }
 
 static TriGeom geom_of(const ksb_device* d, const ksb_pass& p) {
     TriGeom g;
     g.tri = d->d_tri;
     g.base = p.base;
     g.cells = p.cells;
-    g.two_n_m1 = (uint32_t)(2 * d->desc.n_samples - 1);
+    g.rowbase = d->d_rowbase;
+    g.bandstart = d->d_bandstart;
+    g.band_lo = reinterpret_cast<const uint32_t*>(d->d_payload + d->desc.off_band_lo);
+    g.band_hi = reinterpret_cast<const uint32_t*>(d->d_payload + d->desc.off_band_hi);
+    g.pad = 0;
     g.n = (uint32_t)d->desc.n_samples;
     g.rb = (uint32_t)p.rb;
     g.nrows = (uint32_t)(p.re - p.rb);
@@ -174,8 +181,7 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     d->row_begin = cut[d->rank];
     d->row_end = cut[d->rank + 1];
     if (d->rank == W - 1) d->row_end = N;
-    d->owned_cells = N ? rowstart(std::min(d->row_end, N), N) - rowstart(d->row_begin, N) : 0;
-    if (d->row_end == N && N) d->owned_cells = N * (N - 1) / 2 - rowstart(d->row_begin, N);
+    d->owned_cells = rowstart(d, d->row_end) - rowstart(d, d->row_begin);
     d->owned_updates = 0;
     for (uint64_t i = d->row_begin; i < d->row_end; i++) d->owned_updates += row_updates[i];
 
@@ -189,23 +195,24 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     while (rb < d->row_end) {
         uint64_t re = rb, cells = 0, upd = 0;
         while (re < d->row_end) {
-            const uint64_t rc = N - 1 - re;
+            const uint64_t rc = d->bandstart[re + 1] - d->bandstart[re];
             if (re > rb && cells + rc > max_cells) break;
             cells += rc;
             upd += row_updates[re];
             re++;
         }
-        d->passes.push_back(ksb_pass{rb, re, rowstart(rb, N), cells, upd});
+        d->passes.push_back(ksb_pass{rb, re, rowstart(d, rb), cells, upd});
         rb = re;
     }
-    if (d->passes.empty()) d->passes.push_back(ksb_pass{d->row_begin, d->row_begin, N ? rowstart(d->row_begin, N) : 0, 0, 0});
+    if (d->passes.empty()) d->passes.push_back(ksb_pass{d->row_begin, d->row_begin, rowstart(d, d->row_begin), 0, 0});
     uint64_t mx = 0;
     for (const ksb_pass& p : d->passes) mx = std::max(mx, p.cells);
     d->tri_cells_alloc = mx;
     return KSB_OK;
 }
 
-static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_opts* opts) {
+static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint32_t* band_lo, const uint32_t* band_hi,
+                         const ksb_opts* opts) {
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
     if (!d->stream) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
@@ -216,13 +223,28 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const ksb_o
         KSB_CUDA(cudaMemGetInfo(&fr, &tot));
         budget = (uint64_t)((double)fr * 0.8);
     }
+    {   // banded accumulator: prefix of the band lengths, and the per-row base the kernels add columns to
+        const uint64_t N = d->desc.n_samples;
+        d->bandstart.assign(N + 1, 0);
+        std::vector<unsigned long long> rowbase(N ? N : 1, 0);
+        for (uint64_t i = 0; i < N; i++) {
+            if (band_hi[i] < band_lo[i] || band_hi[i] > N) { set_error("corrupt row band at %llu", (unsigned long long)i); return KSB_ERR_ARG; }
+            d->bandstart[i + 1] = d->bandstart[i] + (band_hi[i] - band_lo[i]);
+            rowbase[i] = d->bandstart[i] - band_lo[i];  // wraps for rows whose band starts past their first cells; used modulo 2^64
+        }
+        KSB_CUDA(cudaMallocAsync(&d->d_bandstart, 8 * (N + 1), d->stream));
+        KSB_CUDA(cudaMallocAsync(&d->d_rowbase, 8 * (N ? N : 1), d->stream));
+        KSB_CUDA(cudaMemcpyAsync(d->d_bandstart, d->bandstart.data(), 8 * (N + 1), cudaMemcpyHostToDevice, d->stream));
+        KSB_CUDA(cudaMemcpyAsync(d->d_rowbase, rowbase.data(), 8 * (N ? N : 1), cudaMemcpyHostToDevice, d->stream));
+        KSB_CUDA(cudaStreamSynchronize(d->stream));  // rowbase is a local
+    }
     int rc = plan_rows(d, row_updates, budget);
     if (rc) return rc;
     d->budget = budget;
     d->spill = d->spill_mode == 1 || (d->spill_mode == 0 && d->passes.size() > 16);
     if (d->spill) {  // K3: one pseudo-pass over all owned rows, no dense block
         const uint64_t N = d->desc.n_samples;
-        d->passes.assign(1, ksb_pass{d->row_begin, d->row_end, N ? rowstart(d->row_begin, N) : 0, d->owned_cells, d->owned_updates});
+        d->passes.assign(1, ksb_pass{d->row_begin, d->row_end, rowstart(d, d->row_begin), d->owned_cells, d->owned_updates});
         build_k1(d);
         return KSB_OK;
     }
@@ -310,6 +332,8 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_touched) cudaFreeAsync(d->d_touched, fs);
     if (d->d_block_counts) cudaFreeAsync(d->d_block_counts, fs);
     if (d->d_scan_tmp) cudaFreeAsync(d->d_scan_tmp, fs);
+    if (d->d_bandstart) cudaFreeAsync(d->d_bandstart, fs);
+    if (d->d_rowbase) cudaFreeAsync(d->d_rowbase, fs);
     if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
     if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
     if (fs) cudaStreamSynchronize(fs);
@@ -348,7 +372,8 @@ int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
     if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
     d->own_payload = true;
     const uint64_t* row_updates = reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_row_updates);
-    rc = finish_device(d, row_updates, opts);
+    rc = finish_device(d, row_updates, reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_lo),
+                       reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_hi), opts);
     if (rc) return fail(rc);
     cudaEventRecord(d->ev[0], d->stream);
     e = cudaMemcpyAsync(d->d_payload, ix->payload, d->desc.payload_bytes, cudaMemcpyHostToDevice, d->stream);
@@ -383,7 +408,13 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
         cudaError_t e = cudaMemcpy(row_updates.data(), d->d_payload + d->desc.off_row_updates, 8 * d->desc.n_samples, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { set_error("reading row histogram from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
     }
-    rc = finish_device(d, row_updates.data(), opts);
+    std::vector<uint32_t> blo(d->desc.n_samples), bhi(d->desc.n_samples);
+    if (d->desc.n_samples) {
+        cudaError_t e = cudaMemcpy(blo.data(), d->d_payload + d->desc.off_band_lo, 4 * d->desc.n_samples, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(bhi.data(), d->d_payload + d->desc.off_band_hi, 4 * d->desc.n_samples, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { set_error("reading row bands from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
+    }
+    rc = finish_device(d, row_updates.data(), blo.data(), bhi.data(), opts);
     if (rc) { ksb_device_free(d); return rc; }
     *out = d;
     return KSB_OK;

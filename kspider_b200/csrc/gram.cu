@@ -109,8 +109,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 
 __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const TriGeom& g) {
     if (x - g.rb >= g.nrows) return 0ull;
-    const unsigned long long t = ((unsigned long long)x * (unsigned long long)(g.two_n_m1 - x)) >> 1;
-    return (unsigned long long)g.tri + 8ull * (t - (unsigned long long)x - 1ull - g.base);
+    return (unsigned long long)g.tri + 8ull * (__ldg(g.rowbase + x) - g.base);
 }
 
 }  // namespace

@@ -299,6 +299,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_totals = section(4 * N);
     d.off_sample_ids = section(4 * N);
     d.off_row_updates = section(8 * N);
+    d.off_band_lo = section(4 * N);
+    d.off_band_hi = section(4 * N);
     d.off_small_members = section(4 * d.n_small_members);
     d.off_small_weights = section(4 * d.n_small_colors);
     d.off_mid_offsets = section(8 * (d.n_mid_colors + 1));
@@ -327,6 +329,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     uint32_t* totals = reinterpret_cast<uint32_t*>(P + d.off_totals);
     uint32_t* sids = reinterpret_cast<uint32_t*>(P + d.off_sample_ids);
     uint64_t* row_updates = reinterpret_cast<uint64_t*>(P + d.off_row_updates);
+    uint32_t* band_lo = reinterpret_cast<uint32_t*>(P + d.off_band_lo);
+    uint32_t* band_hi = reinterpret_cast<uint32_t*>(P + d.off_band_hi);
     uint32_t* small_m = reinterpret_cast<uint32_t*>(P + d.off_small_members);
     uint32_t* small_w = reinterpret_cast<uint32_t*>(P + d.off_small_weights);
     uint64_t* mid_off = reinterpret_cast<uint64_t*>(P + d.off_mid_offsets);
@@ -346,12 +350,17 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
     // ---- fill (parallel, deterministic placement = input order within each class)
     std::vector<std::vector<uint64_t>> t_rows(T), t_rowsum(T);
+    std::vector<std::vector<uint32_t>> t_lo(T), t_hi(T);  // per row: columns it is ever paired with, [lo, hi)
     std::vector<uint64_t> t_maxs(T, 0), t_mid_updates(T, 0), t_mid_members(T, 0), t_gram_updates(T, 0);
     parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
         std::vector<uint64_t>& rows = t_rows[t];
         std::vector<uint64_t>& rowsum = t_rowsum[t];
         rows.assign(N, 0);
         rowsum.assign(N, 0);
+        std::vector<uint32_t>& blo = t_lo[t];
+        std::vector<uint32_t>& bhi = t_hi[t];
+        blo.assign(N, 0xFFFFFFFFu);
+        bhi.assign(N, 0);
         std::vector<uint64_t> at = base[t], mat = mbase[t];
         uint64_t maxs = 0, midu = 0, midm = 0, gramu = 0, iat = ibase[t];
         for (uint64_t c = b; c < e; c++) {
@@ -391,6 +400,11 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 dst[i] = ci;
                 if (k != K_ZERO) { rows[ci] += s - 1 - i; rowsum[ci] += w; }
             }
+            // members are ascending: row dst[i] pairs with columns dst[i+1] .. dst[s-1]
+            for (uint64_t i = 0; i + 1 < s; i++) {
+                blo[dst[i]] = std::min(blo[dst[i]], dst[i + 1]);
+                bhi[dst[i]] = std::max(bhi[dst[i]], dst[s - 1] + 1);
+            }
             maxs = std::max(maxs, s);
             at[k]++;
             mat[k] += (k == K_MID) ? ((s + 3) & ~3ULL) : s;
@@ -422,6 +436,18 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         uint64_t r = 0;
         for (int t = 0; t < T; t++) if (!t_rowsum[t].empty()) r += t_rowsum[t][i];
         d.max_row_sum = std::max(d.max_row_sum, r);
+    }
+    // ---- row bands: cell (i, j) can only be touched for band_lo[i] <= j < band_hi[i]; the accumulator
+    // stores exactly these cells, row after row (the full triangle when the colours have no locality)
+    d.band_cells = 0;
+    for (uint64_t i = 0; i < N; i++) {
+        uint32_t lo = 0xFFFFFFFFu, hi = 0;
+        for (int t = 0; t < T; t++)
+            if (!t_lo[t].empty()) { lo = std::min(lo, t_lo[t][i]); hi = std::max(hi, t_hi[t][i]); }
+        if (hi <= lo) lo = hi = 0;
+        band_lo[i] = lo;
+        band_hi[i] = hi;
+        d.band_cells += hi - lo;
     }
     ix->totals_file_ids = std::move(raw.total_ids);
     ix->totals_file_vals = std::move(raw.total_vals);
@@ -647,6 +673,14 @@ const void* ksb_index_descriptor(const ksb_index* ix, uint64_t* bytes) {
     if (!ix) return nullptr;
     if (bytes) *bytes = sizeof(ksb::IndexDesc);
     return &ix->desc;
+}
+
+int ksb_index_bands(const ksb_index* ix, const uint32_t** lo, const uint32_t** hi, uint64_t* band_cells) {
+    if (!ix) { ksb::set_error("ksb_index_bands: null index"); return KSB_ERR_ARG; }
+    if (lo) *lo = reinterpret_cast<const uint32_t*>(ix->payload + ix->desc.off_band_lo);
+    if (hi) *hi = reinterpret_cast<const uint32_t*>(ix->payload + ix->desc.off_band_hi);
+    if (band_cells) *band_cells = ix->desc.band_cells;
+    return KSB_OK;
 }
 
 int ksb_index_row_cuts(const ksb_index* ix, int world, uint64_t* cuts_out) {

@@ -16,8 +16,7 @@ namespace ksb {
 
 __device__ __forceinline__ unsigned long long row_addr(uint32_t x, const TriGeom& g) {
     if (x - g.rb >= g.nrows) return 0ull;
-    const unsigned long long t = ((unsigned long long)x * (unsigned long long)(g.two_n_m1 - x)) >> 1;
-    return (unsigned long long)g.tri + 8ull * (t - (unsigned long long)x - 1ull - g.base);
+    return (unsigned long long)g.tri + 8ull * (__ldg(g.rowbase + x) - g.base);
 }
 
 __device__ __forceinline__ void red_add_u64(unsigned long long addr, unsigned long long w) {
@@ -322,8 +321,7 @@ __global__ void __launch_bounds__(256) kz_touch(unsigned long long n_zero, const
         for (uint32_t a = 0; a + 1 < s; a++) {
             const uint32_t i = m[a];
             if (i - G.rb >= G.nrows) continue;
-            const unsigned long long rowcell =
-                (((unsigned long long)i * (unsigned long long)(G.two_n_m1 - i)) >> 1) - i - 1ull - G.base;
+            const unsigned long long rowcell = __ldg(G.rowbase + i) - G.base;
             for (uint32_t b = a + 1 + lane; b < s; b += 32) {
                 const unsigned long long cell = rowcell + m[b];
                 atomicOr(touched + (cell >> 5), 1u << (cell & 31u));
@@ -434,15 +432,19 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
     unsigned long long out = block_offsets[blockIdx.x] + wbase + (incl - c);
     // decode (i,j) of the first cell, then walk
     const unsigned long long g0 = G.base + cell0;
-    const double tn = (double)G.two_n_m1;
-    uint32_t i = (uint32_t)((tn - sqrt(tn * tn - 8.0 * (double)g0)) * 0.5);
-    auto rowstart = [&](uint32_t r) { return ((unsigned long long)r * (unsigned long long)(G.two_n_m1 - r)) >> 1; };
-    while (i + 1 < G.n && rowstart(i + 1) <= g0) i++;
-    while (i > 0 && rowstart(i) > g0) i--;
-    uint32_t j = i + 1 + (uint32_t)(g0 - rowstart(i));
+    uint32_t lo = G.rb, hi = G.rb + G.nrows;  // last row with bandstart <= g0 (rows with an empty band share their start)
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(G.bandstart + mid) <= g0) lo = mid; else hi = mid;
+    }
+    uint32_t i = lo;
+    uint32_t j = __ldg(G.band_lo + i) + (uint32_t)(g0 - __ldg(G.bandstart + i));
+    uint32_t jend = __ldg(G.band_hi + i);
 #pragma unroll
     for (uint32_t q = 0; q < kPostPerThread; q++) {
-        if (j >= G.n) { i++; j = i + 1; }
+        if (j >= jend && ((flags >> q) != 0u)) {  // next row with a non-empty band (only while flagged cells remain)
+            do { i++; jend = __ldg(G.band_hi + i); j = __ldg(G.band_lo + i); } while (j >= jend);
+        }
         if ((flags >> q) & 1u) {
             float cmin, cavg, cmax;
             containment(v[q], __ldg(totals + i), __ldg(totals + j), cmin, cavg, cmax);

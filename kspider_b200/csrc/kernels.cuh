@@ -14,16 +14,23 @@
 
 namespace ksb {
 
-// Geometry of the owned row block of the packed upper triangle.
-// cell(i,j), i<j  ->  i(2N-1-i)/2 + (j-i-1) - base      (rows [rb, rb+nrows) are owned)
+// Geometry of the owned row block of the banded upper triangle.  Row i stores the cells
+// band_lo[i] <= j < band_hi[i] (the only columns row i is ever paired with; the loader computes
+// the bands, see index_loader.cpp), rows back to back:
+//   cell(i,j) -> bandstart[i] + (j - band_lo[i]) - base = rowbase[i] + j - base   (rows [rb, rb+nrows) are owned)
+// Without locality in the colours the bands are [i+1, N) and this is the packed upper triangle.
 struct TriGeom {
-    unsigned long long* tri;   // owned cells (u64)
-    unsigned long long base;   // packed index of cell (rb, rb+1)
-    unsigned long long cells;  // owned cells
-    uint32_t two_n_m1;         // 2N-1
-    uint32_t n;                // N
-    uint32_t rb;               // first owned row
-    uint32_t nrows;            // owned rows
+    unsigned long long* tri;              // owned cells (u64)
+    const unsigned long long* rowbase;    // [N]   bandstart[i] - band_lo[i] (wrapping): index of the virtual cell (i, 0)
+    const unsigned long long* bandstart;  // [N+1] first cell of row i
+    const uint32_t* band_lo;              // [N]
+    const uint32_t* band_hi;              // [N]
+    unsigned long long base;              // bandstart[rb]
+    unsigned long long cells;             // owned cells
+    uint32_t n;                           // N
+    uint32_t rb;                          // first owned row
+    uint32_t nrows;                       // owned rows
+    uint32_t pad;
 };
 
 struct K1Class {

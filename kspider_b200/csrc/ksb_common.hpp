@@ -77,6 +77,9 @@ struct IndexDesc {
     uint64_t off_totals;        // u32[N]
     uint64_t off_sample_ids;    // u32[N]
     uint64_t off_row_updates;   // u64[N]   updates whose row (= smaller sample) is i
+    uint64_t off_band_lo;       // u32[N]   first column row i is ever paired with
+    uint64_t off_band_hi;       // u32[N]   one past the last such column (lo = hi = 0: row never touched)
+    uint64_t band_cells;        // sum of (hi - lo): cells of the banded accumulator
     uint64_t off_small_members; // u32[n_small_members]
     uint64_t off_small_weights; // u32[n_small_colors]
     uint64_t off_mid_offsets;   // u64[n_mid_colors+1]  start of each colour in the mid-members section,
@@ -98,7 +101,7 @@ struct IndexDesc {
     uint64_t off_gram_weights;  // u32[n_gram_colors]
     uint64_t payload_bytes;
 };
-constexpr uint64_t kIndexMagic = 0x32305844494253ULL | (0x4BULL << 56);
+constexpr uint64_t kIndexMagic = 0x33305844494253ULL | (0x4BULL << 56);
 
 }  // namespace ksb
 

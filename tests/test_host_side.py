@@ -178,3 +178,25 @@ def test_product_never_imports_oracle():
                 src = open(os.path.join(dirpath, fn), errors="replace").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), fn
                 assert "oracle/" not in src or fn == "README", fn
+
+
+def test_row_bands_are_tight_and_cover_every_pair(built_lib, oracle_lib):
+    """Loader: band_lo/band_hi of a row = exactly the min / max+1 column it is paired with in the
+    oracle's rows (zero-weight colours included); untouched rows have an empty band."""
+    import kspider_b200 as ksb
+    from util import oracle_records, random_csr
+    csr = random_csr(seed=71, n_samples=90, n_colors=150, s_lo=1, s_hi=5, id_mode="sparse", zero_every=9)
+    idx = ksb.Index.from_csr(**csr, host_threads=3)
+    lo, hi, cells = idx.bands()
+    ids = idx.sample_ids
+    want = oracle_records(csr)
+    i = np.searchsorted(ids, want["source_1"])
+    j = np.searchsorted(ids, want["source_2"])
+    n = ids.size
+    wlo = np.full(n, 2 ** 32 - 1, dtype=np.int64)
+    whi = np.zeros(n, dtype=np.int64)
+    np.minimum.at(wlo, i, j)
+    np.maximum.at(whi, i, j + 1)
+    wlo[whi == 0] = 0
+    assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
+    assert cells == int((whi - wlo).sum()) and cells < n * (n - 1) // 2
