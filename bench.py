@@ -212,16 +212,9 @@ def main_b200(args):
         idx = Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals,
                              host_threads=min(32, os.cpu_count() or 1))
         inf = idx.info
-        sizes = np.diff(s.offsets).astype(np.int64)
-        upd = sizes * (sizes - 1) // 2
-        gmin = int(inf.gram_min_size) if inf.n_gram_colors else (1 << 62)
-        nz = s.weights != 0
-        small = (sizes >= 2) & (sizes <= 64) & (sizes < gmin) & nz     # what K1 runs
-        gram = (sizes >= 2) & (sizes >= gmin) & nz                      # what K4 runs
-        assert int(gram.sum()) == inf.n_gram_colors, (int(gram.sum()), inf.n_gram_colors)
-        shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, int(upd[small].sum()),
-                    int(sizes[small].sum()), int(small.sum()), inf.payload_bytes, inf.n_gram_colors,
-                    inf.gram_planes, int(upd[gram].sum()), int(sizes[gram].sum())]
+        M_small, U_small, C_small = int(inf.n_small_members), int(inf.n_small_updates), int(inf.n_small_colors)
+        shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, U_small, M_small, C_small,
+                    inf.payload_bytes, inf.n_gram_colors, inf.gram_planes, inf.n_gram_updates, inf.n_gram_members]
         del s
     if world > 1:
         t = torch.from_numpy(shape).to(device)

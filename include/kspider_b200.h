@@ -62,13 +62,18 @@ typedef struct ksb_index_info {
     uint64_t n_small_colors;   /* 2 <= s <= 64  (flat pair-space kernel) */
     uint64_t n_mid_colors;     /* s > 64        (shared-memory tiled kernel) */
     uint64_t n_gram_colors;    /* colours routed to the int8 tcgen05 Gram kernel (K4); 0 = path unused */
-    uint64_t gram_min_size;    /* routing rule applied: s >= gram_min_size (KSPIDER_GRAM=off|auto|<n>) */
+    uint64_t gram_min_size;    /* smallest colour routed to K4 (0 = none); the rule is per Gram window, see DESIGN.md
+                                  (KSPIDER_GRAM=off|auto|<min size>) */
     uint64_t gram_planes;      /* weight byte planes the Gram kernel runs (1, 2 or 4) */
     uint64_t n_gram_updates;   /* pair-updates covered by the Gram colours */
     uint64_t n_zero_colors;    /* multi-member colours whose narrowed count is 0 (touched-with-zero rows) */
     uint64_t max_color_size;
     uint64_t payload_bytes;    /* size of the binned CSR blob (what H2D / NCCL broadcast moves) */
     uint64_t triangle_cells;   /* N(N-1)/2 */
+    uint64_t n_small_members;  /* members / pair-updates of the K1 colours, members of the K4 colours */
+    uint64_t n_small_updates;
+    uint64_t n_gram_members;
+    uint64_t n_gram_windows;   /* sample windows the K4 colours are grouped into */
     uint32_t pinned;           /* 1 if the payload lives in cudaMallocHost memory */
     uint32_t reserved;
 } ksb_index_info;

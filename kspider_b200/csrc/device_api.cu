@@ -31,6 +31,21 @@ struct ksb_pass {
     uint64_t rb, re, base, cells, updates;
 };
 
+// One K4 launch: (sub-)windows whose bitmaps share the chunk buffer, and the work items over them.
+struct ksb_gram_chunk {
+    uint64_t c_begin = 0, n_colors = 0;   // contiguous range of the Gram CSR
+    uint64_t bits_rows = 0;               // 16-byte bitmap rows of the chunk
+    uint32_t win_begin = 0, n_wins = 0;   // into the plan's window array
+    uint32_t item_begin = 0, n_items = 0; // into the plan's item array
+    uint32_t kblocks = 0;                 // K-blocks of all windows = pitch of the weight planes / 128
+};
+struct ksb_gram_plan {
+    bool built = false;
+    std::vector<ksb_gram_chunk> chunks;
+    ksb::GramWinDev* d_wins = nullptr;
+    ksb::GramItem* d_items = nullptr;
+};
+
 struct ksb_device {
     ksb::IndexDesc desc;
     int device = 0, sms = 148;
@@ -38,7 +53,9 @@ struct ksb_device {
     uint8_t* d_payload = nullptr;
     bool own_payload = false;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[9] = {};
+    cudaStream_t stream2 = nullptr;        // K4 runs here, beside K1/K2 (tensor/ALU-bound next to red-bound)
+    cudaEvent_t ev[12] = {};
+    bool overlap = true;                   // KSPIDER_OVERLAP=0 serialises K4 after K1/K2
     unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
     uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
     uint64_t tri_cells_alloc = 0;
@@ -59,7 +76,10 @@ struct ksb_device {
     // K4 (Gram) scratch: bitmap of one chunk of colours + weight byte planes
     uint32_t* d_gbits = nullptr;
     uint8_t* d_gwq = nullptr;
-    uint32_t g_npad = 0, g_chunk_kblocks = 0, g_planes = 0;
+    uint64_t gbits_bytes = 0, gwq_bytes = 0;
+    uint32_t g_planes = 0;
+    std::vector<ksb::GramWin> gwins;       // host copy of the blob's Gram windows
+    std::vector<ksb_gram_plan> gplan;      // per dense pass, built on first use
     // K3 (spill)
     uint64_t spill_mode = 0, budget = 0;
     bool spill = false;
@@ -216,7 +236,9 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
     if (!d->stream) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    if (!d->stream2) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking));
     for (auto& e : d->ev) KSB_CUDA(cudaEventCreate(&e));
+    { const char* ov = std::getenv("KSPIDER_OVERLAP"); d->overlap = !(ov && ov[0] == '0'); }
     uint64_t budget = opts ? opts->dense_budget_bytes : 0;
     if (budget == 0) {
         size_t fr = 0, tot = 0;
@@ -258,19 +280,8 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
                                d->post_blocks_alloc, d->stream));
     KSB_CUDA(cudaMallocAsync(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256), d->stream));
     build_k1(d);
-    if (d->desc.n_gram_colors) {
-        // chunk of colours whose bitmap (npad x 16 B per K-block) stays L2-resident (<= 64 MB of the 126 MB L2)
-        d->g_npad = (uint32_t)((d->desc.n_samples + kGramTile - 1) / kGramTile * kGramTile);
-        const uint64_t kb_total = (d->desc.n_gram_colors + kGramKBlock - 1) / kGramKBlock;
-        const char* cm = std::getenv("KSPIDER_GRAM_CHUNK_MB");  // tuning knob; default keeps the chunk's bitmap L2-resident
-        const uint64_t chunk_mb = (cm && std::atoi(cm) > 0) ? (uint64_t)std::atoi(cm) : 64;
-        uint64_t kb_chunk = (chunk_mb << 20) / ((uint64_t)d->g_npad * 16);
-        kb_chunk = std::max<uint64_t>(1, std::min<uint64_t>(kb_chunk, 16384));  // 255 * 128 * 16384 < 2^31
-        d->g_chunk_kblocks = (uint32_t)std::min(kb_total, kb_chunk);
-        d->g_planes = d->desc.gram_planes <= 1 ? 1 : (d->desc.gram_planes == 2 ? 2 : 4);
-        KSB_CUDA(cudaMallocAsync(&d->d_gbits, (uint64_t)d->g_chunk_kblocks * d->g_npad * 16, d->stream));
-        KSB_CUDA(cudaMallocAsync(&d->d_gwq, (uint64_t)d->g_planes * d->g_chunk_kblocks * kGramKBlock + 256, d->stream));
-    }
+    d->g_planes = d->desc.gram_planes <= 1 ? 1 : (d->desc.gram_planes == 2 ? 2 : 4);
+    d->gplan.assign(d->passes.size(), ksb_gram_plan());
     return KSB_OK;
 }
 
@@ -334,11 +345,16 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_scan_tmp) cudaFreeAsync(d->d_scan_tmp, fs);
     if (d->d_bandstart) cudaFreeAsync(d->d_bandstart, fs);
     if (d->d_rowbase) cudaFreeAsync(d->d_rowbase, fs);
+    for (ksb_gram_plan& gp : d->gplan) {
+        if (gp.d_wins) cudaFreeAsync(gp.d_wins, fs);
+        if (gp.d_items) cudaFreeAsync(gp.d_items, fs);
+    }
     if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
     if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
     if (fs) cudaStreamSynchronize(fs);
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
     if (d->stream) cudaStreamDestroy(d->stream);
+    if (d->stream2) { cudaStreamSynchronize(d->stream2); cudaStreamDestroy(d->stream2); }
     (void)cudaGetLastError();
     delete d;
 }
@@ -372,6 +388,10 @@ int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
     if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
     d->own_payload = true;
     const uint64_t* row_updates = reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_row_updates);
+    if (d->desc.n_gram_wins) {
+        const GramWin* gw = reinterpret_cast<const GramWin*>(ix->payload + d->desc.off_gram_wins);
+        d->gwins.assign(gw, gw + d->desc.n_gram_wins);
+    }
     rc = finish_device(d, row_updates, reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_lo),
                        reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_hi), opts);
     if (rc) return fail(rc);
@@ -414,6 +434,11 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
         if (e == cudaSuccess) e = cudaMemcpy(bhi.data(), d->d_payload + d->desc.off_band_hi, 4 * d->desc.n_samples, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { set_error("reading row bands from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
     }
+    if (d->desc.n_gram_wins) {
+        d->gwins.resize(d->desc.n_gram_wins);
+        cudaError_t e = cudaMemcpy(d->gwins.data(), d->d_payload + d->desc.off_gram_wins, sizeof(GramWin) * d->desc.n_gram_wins, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { set_error("reading Gram windows from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
+    }
     rc = finish_device(d, row_updates.data(), blo.data(), bhi.data(), opts);
     if (rc) { ksb_device_free(d); return rc; }
     *out = d;
@@ -429,6 +454,164 @@ int ksb_device_set_pass(ksb_device* d, int pass) {
 
 int ksb_device_is_spill(const ksb_device* d) { return d && d->spill ? 1 : 0; }
 
+// Plans K4 for one dense pass (rows [p.rb, p.re)): windows that intersect the rows are cut into
+// sub-windows of at most 16384 K-blocks (255 * 128 * 16384 < 2^31: an s32 accumulator cannot
+// overflow) whose bitmap fits the chunk budget, sub-windows are packed into chunks (one bitmap
+// buffer, one launch each), and every chunk gets its work items, largest first.
+static int plan_gram(ksb_device* d, uint32_t pass) {
+    using namespace ksb;
+    ksb_gram_plan& plan = d->gplan[pass];
+    if (plan.built) return KSB_OK;
+    const ksb_pass& p = d->passes[pass];
+    const uint32_t NB = gram_cols_per_item((int)d->g_planes);
+    const char* cm = std::getenv("KSPIDER_GRAM_CHUNK_MB");  // tuning knob; default keeps a chunk's bitmap L2-resident
+    const uint64_t chunk_rows = ((cm && std::atoi(cm) > 0) ? (uint64_t)std::atoi(cm) : 64) << 16;  // MB -> 16-byte rows
+    const char* wv = std::getenv("KSPIDER_GRAM_WAVES");     // tuning knob
+    const uint64_t waves = (wv && std::atoi(wv) > 0) ? (uint64_t)std::atoi(wv) : 4;
+    std::vector<GramWinDev> wins;
+    std::vector<GramItem> items;
+    struct Rows { uint32_t tlo, thi; };
+    std::vector<Rows> wrows;
+    ksb_gram_chunk cur;
+    auto close_chunk = [&]() {
+        if (cur.n_wins == 0) return;
+        // base items, then K splits so that there are ~`waves` items per SM
+        uint64_t base = 0;
+        for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++)
+            for (uint32_t ti = wrows[w].tlo; ti < wrows[w].thi; ti++) base += (wins[w].tiles - ti + NB - 1) / NB;
+        const uint64_t ks = base ? (waves * (uint64_t)d->sms + base - 1) / base : 1;
+        cur.item_begin = (uint32_t)items.size();
+        for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) {
+            const uint32_t kblocks = (wins[w].n + kGramKBlock - 1) / kGramKBlock;
+            const uint32_t split = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ks, kblocks));
+            for (uint32_t ti = wrows[w].tlo; ti < wrows[w].thi; ti++)
+                for (uint32_t tj0 = ti; tj0 < wins[w].tiles; tj0 += NB)
+                    for (uint32_t sp = 0; sp < split; sp++) {
+                        GramItem it;
+                        it.win = w - cur.win_begin;
+                        it.ti = (uint16_t)ti;
+                        it.tj0 = (uint16_t)tj0;
+                        it.kb0 = (uint32_t)((uint64_t)kblocks * sp / split);
+                        it.kb1 = (uint32_t)((uint64_t)kblocks * (sp + 1) / split);
+                        if (it.kb1 > it.kb0) items.push_back(it);
+                    }
+        }
+        cur.n_items = (uint32_t)items.size() - cur.item_begin;
+        auto cost = [&](const GramItem& it) {
+            return (uint64_t)(it.kb1 - it.kb0) * (1 + std::min<uint32_t>(NB, wins[cur.win_begin + it.win].tiles - it.tj0));
+        };
+        std::stable_sort(items.begin() + cur.item_begin, items.end(), [&](const GramItem& a, const GramItem& b) { return cost(a) > cost(b); });
+        if (cur.n_items) plan.chunks.push_back(cur);
+    };
+    auto new_chunk = [&](uint64_t c_begin) {
+        cur = ksb_gram_chunk();
+        cur.c_begin = c_begin;
+        cur.win_begin = (uint32_t)wins.size();
+    };
+    new_chunk(0);
+    for (const GramWin& w : d->gwins) {
+        const uint64_t x0 = w.x0, x1 = (uint64_t)w.x0 + w.width;
+        if (p.re <= x0 || p.rb >= x1 || w.n == 0) {  // no owned row inside the window
+            if (cur.n_wins) { close_chunk(); }
+            new_chunk(w.c0 + w.n);
+            continue;
+        }
+        const uint32_t tiles = w.width / kGramTile;
+        const Rows rows{(uint32_t)(p.rb > x0 ? (p.rb - x0) / kGramTile : 0),
+                        (uint32_t)std::min<uint64_t>(tiles, (p.re - x0 + kGramTile - 1) / kGramTile)};
+        const uint64_t kb_total = ((uint64_t)w.n + kGramKBlock - 1) / kGramKBlock;
+        const uint64_t kb_max = std::max<uint64_t>(1, std::min<uint64_t>(16384, chunk_rows / w.width));
+        for (uint64_t kb = 0; kb < kb_total; kb += kb_max) {
+            const uint64_t kbs = std::min(kb_max, kb_total - kb);
+            if (cur.n_wins && cur.bits_rows + kbs * w.width > chunk_rows) { close_chunk(); new_chunk(w.c0 + kb * kGramKBlock); }
+            if (cur.n_wins == 0) cur.c_begin = w.c0 + kb * kGramKBlock;
+            GramWinDev wd;
+            wd.c0 = w.c0 + kb * kGramKBlock;
+            wd.n = (uint32_t)std::min<uint64_t>(kbs * kGramKBlock, w.n - kb * kGramKBlock);
+            wd.bits_off = cur.bits_rows;
+            wd.x0 = w.x0;
+            wd.width = w.width;
+            wd.tiles = tiles;
+            wd.k0 = cur.kblocks;
+            wd.pad = 0;
+            wins.push_back(wd);
+            wrows.push_back(rows);
+            cur.n_wins++;
+            cur.n_colors = wd.c0 + wd.n - cur.c_begin;
+            cur.bits_rows += kbs * w.width;
+            cur.kblocks += (uint32_t)kbs;
+        }
+    }
+    close_chunk();
+    uint64_t need_bits = 0, need_wq = 0;
+    for (const ksb_gram_chunk& c : plan.chunks) {
+        need_bits = std::max(need_bits, c.bits_rows * 16);
+        need_wq = std::max<uint64_t>(need_wq, (uint64_t)d->g_planes * c.kblocks * kGramKBlock + 256);
+    }
+    if (!plan.chunks.empty()) {
+        KSB_CUDA(cudaStreamSynchronize(d->stream2));  // a grown buffer must not be in use
+        if (need_bits > d->gbits_bytes) {
+            if (d->d_gbits) KSB_CUDA(cudaFreeAsync(d->d_gbits, d->stream));
+            KSB_CUDA(cudaMallocAsync(&d->d_gbits, need_bits, d->stream));
+            d->gbits_bytes = need_bits;
+        }
+        if (need_wq > d->gwq_bytes) {
+            if (d->d_gwq) KSB_CUDA(cudaFreeAsync(d->d_gwq, d->stream));
+            KSB_CUDA(cudaMallocAsync(&d->d_gwq, need_wq, d->stream));
+            d->gwq_bytes = need_wq;
+        }
+        KSB_CUDA(cudaMallocAsync(&plan.d_wins, sizeof(GramWinDev) * wins.size(), d->stream));
+        KSB_CUDA(cudaMallocAsync(&plan.d_items, sizeof(GramItem) * items.size(), d->stream));
+        KSB_CUDA(cudaMemcpyAsync(plan.d_wins, wins.data(), sizeof(GramWinDev) * wins.size(), cudaMemcpyHostToDevice, d->stream));
+        KSB_CUDA(cudaMemcpyAsync(plan.d_items, items.data(), sizeof(GramItem) * items.size(), cudaMemcpyHostToDevice, d->stream));
+        KSB_CUDA(cudaStreamSynchronize(d->stream));  // wins / items are locals
+    }
+    plan.built = true;
+    return KSB_OK;
+}
+
+// K4 over the Gram-routed colours of the current pass, chunk by chunk, on `st`.  The bitmap build of
+// the first chunk runs on `st_build` (the main stream): K1 is launched behind it there, so the Gram
+// kernel (one big CTA per SM) and K1 become runnable together and the Gram CTAs, submitted first, get
+// their slots before K1's CTAs fill the rest of every SM.
+static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build, cudaStream_t st, cudaEvent_t ev_built) {
+    using namespace ksb;
+    const int prc = plan_gram(d, d->cur_pass);
+    if (prc) return prc;
+    const ksb_gram_plan& plan = d->gplan[d->cur_pass];
+    const IndexDesc& D = d->desc;
+    const uint8_t* P = d->d_payload;
+    const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
+    const uint32_t* gmem = reinterpret_cast<const uint32_t*>(P + D.off_gram_members);
+    const uint32_t* gw = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
+    bool first = true;
+    for (const ksb_gram_chunk& c : plan.chunks) {
+        GramParams gp;
+        gp.bits = d->d_gbits;
+        gp.wq = d->d_gwq;
+        gp.wins = plan.d_wins + c.win_begin;
+        gp.items = plan.d_items + c.item_begin;
+        gp.n_wins = c.n_wins;
+        gp.n_items = c.n_items;
+        gp.kpad = c.kblocks * kGramKBlock;
+        gp.planes = d->g_planes;
+        gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
+        cudaStream_t sb = first ? st_build : st;
+        KSB_CUDA(cudaMemsetAsync(d->d_gbits, 0, c.bits_rows * 16, sb));
+        KSB_CUDA(cudaMemsetAsync(d->d_gwq, 0, (uint64_t)d->g_planes * gp.kpad + 256, sb));
+        KSB_CUDA(launch_kb_build(goff, gmem, gw, c.c_begin, c.n_colors, gp.wins, gp.n_wins, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
+                                 LaunchCfg{d->sms, sb}));
+        if (sb != st) {
+            KSB_CUDA(cudaEventRecord(ev_built, sb));
+            KSB_CUDA(cudaStreamWaitEvent(st, ev_built, 0));
+        }
+        KSB_CUDA(launch_k4_gram(gp, g, LaunchCfg{d->sms, st}));
+        d->launches += 2;
+        first = false;
+    }
+    return KSB_OK;
+}
+
 int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     if (!d) { set_error("ksb_accumulate: null device"); return KSB_ERR_ARG; }
     if (d->spill) { set_error("ksb_accumulate: this device runs the spill path (ksb_device_run_spill)"); return KSB_ERR_ARG; }
@@ -443,6 +626,15 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     KSB_CUDA(cudaMemsetAsync(d->d_tri, 0, 8 * (p.cells + 8), st));
     if (d->d_touched) KSB_CUDA(cudaMemsetAsync(d->d_touched, 0, 4 * (p.cells / 32 + 2), st));
     KSB_CUDA(cudaEventRecord(d->ev[1], st));
+    // K4 goes first, on its own stream: one big CTA per SM (tensor pipe + integer expansion) leaves
+    // thread slots for the red-bound K1/K2 CTAs launched right after it on the main stream.
+    const bool has_gram = p.cells && D.n_gram_colors;
+    if (has_gram && d->overlap) {
+        KSB_CUDA(cudaEventRecord(d->ev[9], st));
+        const int grc = run_gram(d, g, st, d->stream2, d->ev[11]);
+        if (grc) return grc;
+        KSB_CUDA(cudaEventRecord(d->ev[10], d->stream2));
+    }
     if (p.cells) {
         KSB_CUDA(launch_k1_small(d->k1, reinterpret_cast<const uint32_t*>(P + D.off_small_members),
                                  reinterpret_cast<const uint32_t*>(P + D.off_small_weights), g, lc));
@@ -464,42 +656,12 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         d->launches++;
     }
     KSB_CUDA(cudaEventRecord(d->ev[4], st));
-    if (p.cells && D.n_gram_colors) {
-        const uint32_t T = d->g_npad / kGramTile;
-        const uint32_t tile_lo = (uint32_t)(p.rb / kGramTile);
-        const uint32_t tile_hi = (uint32_t)std::min<uint64_t>(T, (p.re + kGramTile - 1) / kGramTile);
-        const uint32_t nbcol = gram_cols_per_item((int)d->g_planes);
-        uint64_t pairs = 0;  // (row tile, column-tile group) items
-        for (uint32_t ti = tile_lo; ti < tile_hi; ti++) pairs += (T - ti + nbcol - 1) / nbcol;
-        const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
-        const uint32_t* gmem = reinterpret_cast<const uint32_t*>(P + D.off_gram_members);
-        const uint32_t* gw = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
-        const uint64_t chunk_colors = (uint64_t)d->g_chunk_kblocks * kGramKBlock;
-        for (uint64_t c0 = 0; c0 < D.n_gram_colors && pairs; c0 += chunk_colors) {
-            const uint32_t n = (uint32_t)std::min<uint64_t>(chunk_colors, D.n_gram_colors - c0);
-            GramParams gp;
-            gp.bits = d->d_gbits;
-            gp.wq = d->d_gwq;
-            gp.npad = d->g_npad;
-            gp.kblocks = (n + kGramKBlock - 1) / kGramKBlock;
-            gp.kpad = d->g_chunk_kblocks * kGramKBlock;
-            gp.planes = d->g_planes;
-            gp.tiles = T;
-            gp.tile_lo = tile_lo;
-            gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
-            // enough items for ~four waves of CTAs (items differ in size and are fetched dynamically),
-            // never more splits than K-blocks
-            const char* wv = std::getenv("KSPIDER_GRAM_WAVES");  // tuning knob
-            const uint64_t waves = (wv && std::atoi(wv) > 0) ? (uint64_t)std::atoi(wv) : 4;
-            uint64_t ks = (waves * (uint64_t)d->sms + pairs - 1) / pairs;
-            gp.ksplit = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ks, gp.kblocks));
-            gp.n_items = (uint32_t)(pairs * gp.ksplit);
-            KSB_CUDA(cudaMemsetAsync(d->d_gbits, 0, (uint64_t)gp.kblocks * d->g_npad * 16, st));
-            KSB_CUDA(cudaMemsetAsync(d->d_gwq, 0, (uint64_t)d->g_planes * gp.kpad + 256, st));
-            KSB_CUDA(launch_kb_build(goff, gmem, gw, c0, n, gp.npad, gp.kpad, gp.planes, d->d_gbits, d->d_gwq, lc));
-            KSB_CUDA(launch_k4_gram(gp, g, lc));
-            d->launches += 2;
-        }
+    if (has_gram && d->overlap) {
+        KSB_CUDA(cudaStreamWaitEvent(st, d->ev[10], 0));
+    } else {
+        KSB_CUDA(cudaEventRecord(d->ev[9], st));
+        if (has_gram) { const int grc = run_gram(d, g, st, st, d->ev[11]); if (grc) return grc; }
+        KSB_CUDA(cudaEventRecord(d->ev[10], st));
     }
     KSB_CUDA(cudaEventRecord(d->ev[8], st));
     if (sync) {
@@ -508,7 +670,7 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         d->t.small_ms += ev_ms(d->ev[1], d->ev[2]);
         d->t.mid_ms += ev_ms(d->ev[2], d->ev[3]);
         d->t.zero_touch_ms += ev_ms(d->ev[3], d->ev[4]);
-        d->t.gram_ms += ev_ms(d->ev[4], d->ev[8]);
+        d->t.gram_ms += ev_ms(d->ev[9], d->ev[10]);  // overlaps small_ms/mid_ms unless KSPIDER_OVERLAP=0
         d->t.accumulate_ms += ev_ms(d->ev[0], d->ev[8]);
     }
     return KSB_OK;

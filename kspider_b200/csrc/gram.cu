@@ -115,45 +115,56 @@ __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const Tr
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
-// kb_build: one warp per Gram colour of the chunk [c0, c0 + n).  Sets bit (colour, sample) in the
-// K-block-major bitmap  bits[(kblock * npad + sample) * 4 + word]  and writes the byte planes of the
-// colour's weight to wq[plane * kpad + colour].
+// kb_build: one warp per Gram colour of the chunk [c_begin, c_begin + n).  Finds the colour's
+// (sub-)window, sets bit (colour, local sample) in the window's K-block-major bitmap
+//     bits[(bits_off + kblock * width + sample - x0) * 4 + word]
+// and writes the byte planes of the colour's weight to wq[plane * kpad + k0 * 128 + colour - c0].
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __restrict__ gram_off,
                                                 const uint32_t* __restrict__ gram_members,
-                                                const uint32_t* __restrict__ gram_weights, unsigned long long c0,
-                                                uint32_t n, uint32_t npad, uint32_t kpad, uint32_t planes,
-                                                uint32_t* __restrict__ bits, uint8_t* __restrict__ wq) {
+                                                const uint32_t* __restrict__ gram_weights, unsigned long long c_begin,
+                                                unsigned long long n, const GramWinDev* __restrict__ wins, uint32_t n_wins,
+                                                uint32_t kpad, uint32_t planes, uint32_t* __restrict__ bits,
+                                                uint8_t* __restrict__ wq) {
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t cl = warp; cl < n; cl += nwarps) {
-        const unsigned long long off = gram_off[c0 + cl];
-        const uint32_t s = (uint32_t)(gram_off[c0 + cl + 1] - off);
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long ci = warp; ci < n; ci += nwarps) {
+        const unsigned long long c = c_begin + ci;
+        uint32_t lo = 0, hi = n_wins;  // last window with c0 <= c
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(&wins[mid].c0) <= c) lo = mid; else hi = mid;
+        }
+        const GramWinDev w = wins[lo];
+        const uint32_t cl = (uint32_t)(c - w.c0);
+        const unsigned long long off = gram_off[c];
+        const uint32_t s = (uint32_t)(gram_off[c + 1] - off);
         const uint32_t* m = gram_members + off;
-        uint32_t* base = bits + (unsigned long long)(cl >> 7) * npad * 4ull + ((cl & 127u) >> 5);
+        uint32_t* base = bits + (w.bits_off + (unsigned long long)(cl >> 7) * w.width) * 4ull + ((cl & 127u) >> 5);
         const uint32_t bit = 1u << (cl & 31u);
-        for (uint32_t a = lane; a < s; a += 32) atomicOr(base + 4ull * __ldg(m + a), bit);
-        if (lane < planes) wq[(unsigned long long)lane * kpad + cl] = (uint8_t)(__ldg(gram_weights + c0 + cl) >> (8u * lane));
+        for (uint32_t a = lane; a < s; a += 32) atomicOr(base + 4ull * (__ldg(m + a) - w.x0), bit);
+        if (lane < planes) wq[(unsigned long long)lane * kpad + (unsigned long long)w.k0 * kKB + cl] = (uint8_t)(__ldg(gram_weights + c) >> (8u * lane));
     }
 }
 
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* gram_members,
-                            const uint32_t* gram_weights, uint64_t c0, uint32_t n, uint32_t npad, uint32_t kpad,
-                            uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {
+                            const uint32_t* gram_weights, uint64_t c_begin, uint64_t n, const GramWinDev* wins,
+                            uint32_t n_wins, uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq,
+                            const LaunchCfg& lc) {
     if (n == 0) return cudaSuccess;
-    unsigned ctas = (n + 7) / 8;
-    const unsigned cap = (unsigned)lc.sms * 8u;
+    unsigned long long ctas = (n + 7) / 8;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    kb_build<<<ctas, 256, 0, lc.stream>>>(gram_off, gram_members, gram_weights, c0, n, npad, kpad, planes, bits, wq);
+    kb_build<<<(unsigned)ctas, 256, 0, lc.stream>>>(gram_off, gram_members, gram_weights, c_begin, n, wins, n_wins, kpad, planes, bits, wq);
     return cudaGetLastError();
 }
 
 
 // ------------------------------------------------------------------------------------------------
 // k4_gram<P>: persistent, one CTA per SM: 16 producer/epilogue warps, 1 MMA-issuing thread, 1 TMA
-// loader thread.  Work item = (row tile ti, NB = 4/P adjacent column tiles >= ti, K split), fetched
-// from a global counter.
+// loader thread.  Work item = (window, row tile ti, NB = 4/P adjacent column tiles >= ti, K-block
+// range), read from the chunk's item list at an index fetched from a global counter.
 //   loader    per K-block of 128 colours: cp.async.bulk of the bitmap rows of the A tile (2 KB), of
 //             the NB B tiles (NB x 2 KB, contiguous) and of the weight byte planes (P x 128 B) into a
 //             4-slot ring, two K-blocks ahead of the producers (`ready` mbarriers, complete_tx).
@@ -203,7 +214,6 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
     const uint32_t tmem = *tmem_slot;
     const uint32_t bar_done = smem_u32(bars + 2 * kStages);
     const uint32_t bar_ready0 = smem_u32(bars + 2 * kStages + 1);
-    const uint32_t T = prm.tiles;
     uint32_t it = 0, done_phase = 0;  // it: K-blocks processed by this CTA so far, the same in every role
 
     for (;;) {
@@ -211,19 +221,11 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
         __syncthreads();
         const uint32_t item = *item_slot;
         if (item >= prm.n_items) break;
-        uint32_t q = item / prm.ksplit;
-        const uint32_t sp = item - q * prm.ksplit;
-        uint32_t ti = prm.tile_lo;
-        for (;;) {
-            const uint32_t ng = (T - ti + NB - 1) / NB;
-            if (q < ng) break;
-            q -= ng;
-            ti++;
-        }
-        const uint32_t tj0 = ti + q * NB;
-        const uint32_t ncol = min(NB, T - tj0);
-        const uint32_t kb0 = (uint32_t)((unsigned long long)prm.kblocks * sp / prm.ksplit);
-        const uint32_t kb1 = (uint32_t)((unsigned long long)prm.kblocks * (sp + 1) / prm.ksplit);
+        const GramItem gi = prm.items[item];
+        const GramWinDev win = prm.wins[gi.win];
+        const uint32_t ti = gi.ti, tj0 = gi.tj0;
+        const uint32_t ncol = min(NB, win.tiles - tj0);
+        const uint32_t kb0 = gi.kb0, kb1 = gi.kb1;
         const uint32_t i0 = ti * kTile;
 
         if (warp < kProducerWarps) {
@@ -295,10 +297,10 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                         for (uint32_t y = 0; y < 16; y++)
                             acc[y] += (unsigned long long)tp[(2 * y + rsel) * 17 + csel] << (8 * p);  // row = 2y + rsel, column = csel
                     }
-                    const uint32_t j = (tj0 + ct) * kTile + c16 * 16u + csel;
+                    const uint32_t j = win.x0 + (tj0 + ct) * kTile + c16 * 16u + csel;
 #pragma unroll
                     for (uint32_t y = 0; y < 16; y++) {
-                        const uint32_t i = i0 + 32u * lq + 2 * y + rsel;
+                        const uint32_t i = win.x0 + i0 + 32u * lq + 2 * y + rsel;
                         if (i < j && j < G.n && acc[y] != 0ull) {
                             const unsigned long long ra = gram_row_addr(i, G);
                             if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
@@ -345,13 +347,13 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                     const uint32_t slot = it % kRing;
                     const uint32_t bar = bar_ready0 + 8u * slot;
                     const uint32_t dst = smem_u32(ring + slot * kSlotBytes);
-                    const uint8_t* kbase = gbits + (unsigned long long)kb * prm.npad * 16ull;
+                    const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.width) * 16ull;
                     mbar_expect_tx(bar, bytes);
                     tma_load_1d(dst, kbase + (unsigned long long)i0 * 16ull, 2048u, bar);
                     tma_load_1d(dst + 2048u, kbase + (unsigned long long)tj0 * kTile * 16ull, ncol * 2048u, bar);
 #pragma unroll
                     for (int p = 0; p < P; p++)
-                        tma_load_1d(dst + kWOff + p * 128, prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)kb * kKB, 128u, bar);
+                        tma_load_1d(dst + kWOff + p * 128, prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)(win.k0 + kb) * kKB, 128u, bar);
                 }
             } else {
                 it += kb1 - kb0;

@@ -189,12 +189,18 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
     const int T = std::max(1, threads);
 
-    // ---- routing rule of the int8 Gram path (K4): colours with s >= gram_min (and weight != 0).
-    // KSPIDER_GRAM = off | auto (default) | <min size>.  auto: per colour the Gram path costs
-    // ~Npad^2 * planes tensor MACs against s^2/2 reds, so it pays for s above a fixed fraction of N;
-    // it is used only if the routed set also beats the atomic path including the fixed costs.
+    // ---- routing of the int8 Gram path (K4), per sample window.  A colour whose members all lie in a
+    // window of `width` samples costs ~width^2 * planes tensor MACs there against s^2/2 reds on K1/K2,
+    // so it is a candidate when s >= kGramCrossover * width * sqrt(planes) (and >= kGramMinSize) for
+    // the SMALLEST window of the multi-level grid that contains it; a window is used only if its
+    // candidates together beat the atomic path including the window's fixed costs.
+    // KSPIDER_GRAM = off | auto (default) | <min size> (forces every colour of at least that size).
+    const uint64_t NOKEY = ~0ull;
+    std::vector<uint64_t> gkey;        // per colour: window key, then (once the windows are fixed) its Gram CSR index
+    std::vector<GramWin> gwins;
+    std::vector<uint64_t> gram_list;   // colours in Gram CSR order (grouped by window)
     uint64_t gram_min = 0, gram_planes = 1;
-    if (N >= 2 && N <= kGramMaxSamples) {
+    if (N >= 2) {
         const char* env = std::getenv("KSPIDER_GRAM");
         long forced = -1;
         bool off = false;
@@ -203,40 +209,122 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             else if (std::strcmp(env, "auto")) { forced = std::strtol(env, nullptr, 10); if (forced < 2) off = true; }
         }
         if (!off) {
-            const double npad = (double)((N + kGramTile - 1) / kGramTile * kGramTile);
-            auto scan = [&](uint64_t smin, uint64_t* kg, uint64_t* ug) {
-                std::vector<uint64_t> tk(T, 0), tu(T, 0);
-                std::vector<uint32_t> tw(T, 0);
-                parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
-                    for (uint64_t c = b; c < e; c++) {
-                        const uint64_t sz = raw.off[c + 1] - raw.off[c];
-                        if (sz < 2 || sz < smin || raw.weights[c] == 0) continue;
-                        tk[t]++; tu[t] += sz * (sz - 1) / 2; tw[t] = std::max(tw[t], raw.weights[c]);
-                    }
-                });
-                uint32_t wmax = 0;
-                *kg = 0; *ug = 0;
-                for (int t = 0; t < T; t++) { *kg += tk[t]; *ug += tu[t]; wmax = std::max(wmax, tw[t]); }
-                return wmax;
+            const uint64_t npad = (N + kGramTile - 1) / kGramTile * kGramTile;
+            const uint64_t s_any = forced >= 2 ? (uint64_t)forced : kGramMinSize;
+            std::vector<uint32_t> tw(T, 0);
+            parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+                uint32_t m = 0;
+                for (uint64_t c = b; c < e; c++)
+                    if (raw.off[c + 1] - raw.off[c] >= s_any) m = std::max(m, raw.weights[c]);
+                tw[t] = m;
+            });
+            uint32_t wmax = 0;
+            for (uint32_t v : tw) wmax = std::max(wmax, v);
+            const uint64_t planes = wmax < (1u << 8) ? 1 : (wmax < (1u << 16) ? 2 : 4);
+            struct Level { uint64_t width, stride, smin; bool top; };
+            std::vector<Level> levels;
+            auto smin_of = [&](uint64_t width) -> uint64_t {
+                if (forced >= 2) return (uint64_t)forced;
+                return std::max<uint64_t>(kGramMinSize, (uint64_t)std::ceil(kGramCrossover * (double)width * std::sqrt((double)planes)));
             };
-            uint64_t kg = 0, ug = 0;
-            uint32_t wmax = scan(2, &kg, &ug);
-            auto planes_of = [](uint32_t w) -> uint64_t { return w < (1u << 8) ? 1 : (w < (1u << 16) ? 2 : 4); };
-            uint64_t smin = forced >= 2 ? (uint64_t)forced
-                                        : std::max<uint64_t>(16, (uint64_t)std::ceil(kGramCrossover * npad * std::sqrt((double)planes_of(wmax))));
-            wmax = scan(smin, &kg, &ug);
-            if (kg) {
-                const double kpad = (double)((kg + kGramKBlock - 1) / kGramKBlock * kGramKBlock);
-                const double t_gram = npad * npad * kpad * (double)planes_of(wmax) / kGramMacRate + npad * npad * 8.0 / 4e12 + 30e-6;
-                const double t_red = (double)ug / kGramRedRate;
-                if (forced >= 2 || t_gram < t_red) { gram_min = smin; gram_planes = planes_of(wmax); }
+            for (uint64_t w = kGramTile;; w <<= 1) {
+                if (w >= npad) { if (npad <= kGramMaxSamples) levels.push_back({npad, npad, smin_of(npad), true}); break; }
+                if (w > kGramMaxSamples) break;
+                levels.push_back({w, w / 2, smin_of(w), false});
             }
+            gkey.assign(C, NOKEY);
+            std::vector<uint64_t> tn(T, 0);
+            parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+                uint64_t n = 0;
+                for (uint64_t c = b; c < e; c++) {
+                    const uint64_t sz = raw.off[c + 1] - raw.off[c];
+                    if (sz < 2 || sz < s_any || raw.weights[c] == 0) continue;
+                    const uint64_t first = compact(raw.members[raw.off[c]]), last = compact(raw.members[raw.off[c + 1] - 1]);
+                    for (size_t l = 0; l < levels.size(); l++) {
+                        const Level& lv = levels[l];
+                        const uint64_t x0 = lv.top ? 0 : first / lv.stride * lv.stride;
+                        if (last >= x0 + lv.width) continue;
+                        if (sz >= lv.smin) { gkey[c] = (x0 << 8) | l; n++; }
+                        break;  // larger windows only raise the bar
+                    }
+                }
+                tn[t] = n;
+            });
+            uint64_t n_cand = 0;
+            for (uint64_t v : tn) n_cand += v;
+            std::vector<std::pair<uint64_t, uint64_t>> cand;  // (window key, colour), input order inside a window
+            cand.reserve(n_cand);
+            for (uint64_t c = 0; c < C; c++)
+                if (gkey[c] != NOKEY) cand.emplace_back(gkey[c], c);
+            std::sort(cand.begin(), cand.end());
+            // per window: keep it only if the tensor path wins (bitmap build + MMAs + per-item overhead + one pass of reds)
+            double gain = 0.0;
+            std::vector<std::pair<uint64_t, uint64_t>> kept;  // [begin, end) ranges of cand
+            for (uint64_t b = 0; b < cand.size();) {
+                uint64_t e = b, upd = 0, mem = 0;
+                while (e < cand.size() && cand[e].first == cand[b].first) {
+                    const uint64_t sz = raw.off[cand[e].second + 1] - raw.off[cand[e].second];
+                    upd += sz * (sz - 1) / 2;
+                    mem += sz;
+                    e++;
+                }
+                const Level& lv = levels[cand[b].first & 0xFF];
+                const double width = (double)lv.width, tiles = width / kGramTile;
+                const double kpad = (double)((e - b + kGramKBlock - 1) / kGramKBlock * kGramKBlock);
+                const double rate = lv.width >= 4 * kGramTile ? kGramMacRate : 0.5 * kGramMacRate;
+                const double t_gram = width * width * kpad * (double)planes / rate + (double)mem / 1.0e11 +
+                                      tiles * (tiles + 1) / 2 / (double)(4 / planes) * 30e-9 + width * width / 2 / kGramRedRate;
+                const double t_red = (double)upd / kGramRedRate;
+                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); gain += t_red - t_gram; }
+                b = e;
+            }
+            if (forced < 2 && gain < 30e-6) kept.clear();  // launches + memsets of the path itself
+            std::fill(gkey.begin(), gkey.end(), NOKEY);
+            uint64_t smallest = ~0ull;
+            for (auto& r : kept) {
+                const Level& lv = levels[cand[r.first].first & 0xFF];
+                GramWin w;
+                w.c0 = gram_list.size();
+                w.n = (uint32_t)(r.second - r.first);
+                w.x0 = (uint32_t)(cand[r.first].first >> 8);
+                w.width = (uint32_t)std::min<uint64_t>(lv.width, (npad - w.x0 + kGramTile - 1) / kGramTile * kGramTile);
+                w.pad = 0;
+                gwins.push_back(w);
+                for (uint64_t i = r.first; i < r.second; i++) {
+                    gkey[cand[i].second] = gram_list.size();
+                    gram_list.push_back(cand[i].second);
+                    smallest = std::min<uint64_t>(smallest, raw.off[cand[i].second + 1] - raw.off[cand[i].second]);
+                }
+            }
+            if (!gram_list.empty()) { gram_min = smallest; gram_planes = planes; }
         }
     }
+    const bool any_gram = !gram_list.empty();
     d.gram_min_size = gram_min;
     d.gram_planes = gram_planes;
 
-    // ---- classify colours; per-chunk class counts so the fill can run in parallel, in input order
+    // ---- locality order: when the accumulator cannot be L2-resident, colours are placed in the blob
+    // by ascending first member (= the triangle row of their first updates), so the colours the SMs
+    // work on at the same time hit the same neighbourhood of rows and the reds stay in L2 instead of
+    // each one costing an HBM sector read + write-back.  KSPIDER_SORT = auto (default) | on | off.
+    std::vector<uint64_t> order;  // empty = input order
+    {
+        const char* env = std::getenv("KSPIDER_SORT");
+        bool on = N >= 2 && (double)N * (double)(N - 1) * 4.0 > 48.0 * 1048576.0;
+        if (env && !std::strcmp(env, "on")) on = true;
+        if (env && !std::strcmp(env, "off")) on = false;
+        if (on && C > 1) {  // stable counting sort by compact first member (empty colours first)
+            std::vector<uint64_t> start(N + 2, 0);
+            auto key = [&](uint64_t c) -> uint64_t { return raw.off[c + 1] > raw.off[c] ? 1 + compact(raw.members[raw.off[c]]) : 0; };
+            for (uint64_t c = 0; c < C; c++) start[key(c) + 1]++;
+            for (uint64_t k = 0; k <= N; k++) start[k + 1] += start[k];
+            order.resize(C);
+            for (uint64_t c = 0; c < C; c++) order[start[key(c)]++] = c;
+        }
+    }
+    auto ord = [&](uint64_t ci) -> uint64_t { return order.empty() ? ci : order[ci]; };
+
+    // ---- classify colours; per-chunk class counts so the fill can run in parallel, in blob order
     const uint32_t K_MID = kSmallMax + 1, K_ZERO = kSmallMax + 2, K_GRAM = kSmallMax + 3, K_N = kSmallMax + 4;
     std::vector<std::vector<uint64_t>> cnt(T, std::vector<uint64_t>(K_N, 0));      // colours per class
     std::vector<std::vector<uint64_t>> mcnt(T, std::vector<uint64_t>(K_N, 0));     // members per class
@@ -246,12 +334,13 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         const uint64_t s = raw.off[c + 1] - raw.off[c];
         if (s < 2) return 0;
         if (raw.weights[c] == 0) return K_ZERO;
-        if (gram_min && s >= gram_min) return K_GRAM;
+        if (any_gram && gkey[c] != NOKEY) return K_GRAM;
         return s <= kSmallMax ? (uint32_t)s : K_MID;
     };
     parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
         chunk_b[t] = b;
-        for (uint64_t c = b; c < e; c++) {
+        for (uint64_t ci = b; ci < e; ci++) {
+            const uint64_t c = ord(ci);
             const uint32_t k = klass(c);
             if (!k) continue;
             cnt[t][k]++;
@@ -283,6 +372,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         d.n_updates += tot[s] * sc.pairs;
     }
     d.n_small_colors = woff;
+    d.n_small_updates = d.n_updates;
     d.n_small_members = moff;
     d.n_mid_colors = tot[K_MID];
     d.n_mid_members_padded = mtot[K_MID];
@@ -313,6 +403,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_gram_offsets = section(8 * (d.n_gram_colors + 1));
     d.off_gram_members = section(4 * d.n_gram_members);
     d.off_gram_weights = section(4 * d.n_gram_colors);
+    d.n_gram_wins = gwins.size();
+    d.off_gram_wins = section(sizeof(GramWin) * d.n_gram_wins);
     d.payload_bytes = std::max<uint64_t>(p, 256);
 
     void* mem = nullptr;
@@ -345,6 +437,11 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     uint32_t* gram_w = reinterpret_cast<uint32_t*>(P + d.off_gram_weights);
 
     std::copy(sample_ids.begin(), sample_ids.end(), sids);
+    if (!gwins.empty()) std::memcpy(P + d.off_gram_wins, gwins.data(), sizeof(GramWin) * gwins.size());
+    for (uint64_t g = 0, o = 0; g < gram_list.size(); g++) {  // Gram CSR: colours grouped by window
+        gram_off[g] = o;
+        o += raw.off[gram_list[g] + 1] - raw.off[gram_list[g]];
+    }
     // groupID_to_kmerCount[id]: a map, so one value per id; missing -> 0 (operator[] default)
     for (size_t i = 0; i < raw.total_ids.size(); i++) totals[compact(raw.total_ids[i])] = raw.total_vals[i];
 
@@ -363,7 +460,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         bhi.assign(N, 0);
         std::vector<uint64_t> at = base[t], mat = mbase[t];
         uint64_t maxs = 0, midu = 0, midm = 0, gramu = 0, iat = ibase[t];
-        for (uint64_t c = b; c < e; c++) {
+        for (uint64_t ci = b; ci < e; ci++) {
+            const uint64_t c = ord(ci);
             const uint32_t k = klass(c);
             if (!k) continue;
             const uint64_t s = raw.off[c + 1] - raw.off[c];
@@ -386,9 +484,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 dst = zero_m + mat[k];
                 zero_off[at[k]] = mat[k];
             } else if (k == K_GRAM) {
-                dst = gram_m + mat[k];
-                gram_off[at[k]] = mat[k];
-                gram_w[at[k]] = w;
+                dst = gram_m + gram_off[gkey[c]];
+                gram_w[gkey[c]] = w;
                 gramu += s * (s - 1) / 2;
             } else {
                 const SmallClass& sc = d.cls[k];
@@ -658,6 +755,10 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     info->max_color_size = d.max_color_size;
     info->payload_bytes = d.payload_bytes;
     info->triangle_cells = d.n_samples ? d.n_samples * (d.n_samples - 1) / 2 : 0;
+    info->n_small_members = d.n_small_members;
+    info->n_small_updates = d.n_small_updates;
+    info->n_gram_members = d.n_gram_members;
+    info->n_gram_windows = d.n_gram_wins;
     info->pinned = ix->pinned ? 1 : 0;
     return KSB_OK;
 }

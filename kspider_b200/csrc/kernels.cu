@@ -101,10 +101,16 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
                 w = __ldg(wcls + col0 + g);
             }
             const unsigned long long ra = valid ? Sink::row(x, G) : 0ull;
-            if (__ballot_sync(KSB_FULL, ra != 0ull) == 0u) continue;  // no owned row in this task
+            const uint32_t own = __ballot_sync(KSB_FULL, ra != 0ull);
+            if (own == 0u) continue;  // no owned row in this task
             const unsigned long long cadd = Sink::col(x);
             const uint32_t gb = g * s;
-            for (uint32_t ar = 0; ar + 1 < s; ar++) {
+            // members are sorted, so the owned rows of a colour are one run of positions: walk only the
+            // union of those runs over the task's colours (everything when the triangle is not sharded)
+            const uint32_t gm = (own >> gb) & (0xffffffffu >> (32u - s));
+            const uint32_t ar0 = __reduce_min_sync(KSB_FULL, gm ? (uint32_t)__ffs(gm) - 1u : s);
+            const uint32_t ar1 = min(__reduce_max_sync(KSB_FULL, gm ? 32u - (uint32_t)__clz(gm) : 0u), s - 1u);
+            for (uint32_t ar = ar0; ar < ar1; ar++) {
                 const unsigned long long r = shfl_u64(ra, gb + ar);
                 sink.add(valid && a > ar && r != 0ull, r, cadd, w);
             }

@@ -108,24 +108,39 @@ cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 
-// K4: int8 tcgen05 Gram path (gram.cu)
+// K4: int8 tcgen05 Gram path (gram.cu).  One launch handles a CHUNK: a list of (sub-)windows whose
+// bitmaps share one buffer, and a list of work items over them.
+struct GramWinDev {
+    unsigned long long c0;        // first Gram colour (index into the Gram CSR) of this (sub-)window
+    unsigned long long bits_off;  // first 16-byte bitmap row of its K-block 0 inside the chunk buffer
+    uint32_t n;                   // colours
+    uint32_t x0;                  // first sample of the window
+    uint32_t width;               // samples (multiple of kGramTile)
+    uint32_t tiles;               // width / kGramTile
+    uint32_t k0;                  // first K-block of the window in the chunk's weight planes
+    uint32_t pad;
+};
+struct GramItem {
+    uint32_t win;                 // index into the chunk's window list
+    uint16_t ti, tj0;             // row tile, first of the (up to NB) column tiles
+    uint32_t kb0, kb1;            // K-block range inside the window
+};
 struct GramParams {
-    const uint32_t* bits;   // [kblocks][npad][4] u32: bit (colour % 128) of sample, K-block-major
-    const uint8_t* wq;      // [planes][kpad] weight byte planes
-    uint32_t npad;          // N rounded up to kGramTile
-    uint32_t kblocks;       // K-blocks of this chunk
-    uint32_t kpad;          // row pitch of wq (>= kblocks * 128, multiple of 128)
-    uint32_t planes;        // 1, 2 or 4
-    uint32_t tiles;         // npad / kGramTile
-    uint32_t ksplit;        // K splits per tile pair
-    uint32_t tile_lo;       // first row tile intersecting the owned rows
-    uint32_t n_items;       // (row tile, group of gram_cols_per_item(planes) column tiles) x ksplit
-    uint32_t* counter;      // work counter, zeroed before the launch
+    const uint32_t* bits;         // chunk bitmap: per window [kblocks][width][4] u32, bit (colour % 128) of local sample
+    const uint8_t* wq;            // [planes][kpad] weight byte planes
+    const GramWinDev* wins;
+    const GramItem* items;
+    uint32_t n_wins;
+    uint32_t n_items;
+    uint32_t kpad;                // row pitch of wq (multiple of 128)
+    uint32_t planes;              // 1, 2 or 4
+    uint32_t* counter;            // work counter, zeroed before the launch
 };
 uint32_t gram_cols_per_item(int planes);
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* gram_members,
-                            const uint32_t* gram_weights, uint64_t c0, uint32_t n, uint32_t npad, uint32_t kpad,
-                            uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
+                            const uint32_t* gram_weights, uint64_t c_begin, uint64_t n, const GramWinDev* wins,
+                            uint32_t n_wins, uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq,
+                            const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 
 // red micro-benchmark

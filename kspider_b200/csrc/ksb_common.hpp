@@ -29,13 +29,27 @@ constexpr uint32_t kMidRows = 512;
 // K4 (Gram) geometry: 128 x 128 sample tiles, K-blocks of 128 colours
 constexpr uint32_t kGramTile = 128;
 constexpr uint32_t kGramKBlock = 128;
-constexpr uint32_t kGramMaxSamples = 32768;  // bitmap rows / tile grid are O(N), O(N^2): larger N stays on K1/K2
+constexpr uint32_t kGramMaxSamples = 32768;  // widest Gram window (bitmap rows / tile grid are O(width), O(width^2))
+constexpr uint32_t kGramMinSize = 16;        // colours smaller than this never go to K4
 // routing cost model (calibrated on B200): effective Gram MAC rate (u8 MACs/s over the
 // full Npad^2 x K x planes box, i.e. including the half that the symmetric tile skips), red rate of
 // the atomic kernels, and the resulting per-colour crossover s / Npad = sqrt(2 * red / mac) (x sqrt(planes))
 constexpr double kGramMacRate = 1.0e15;
 constexpr double kGramRedRate = 2.5e11;
 constexpr double kGramCrossover = 0.0224;
+
+// One Gram window: the colours [c0, c0 + n) of the Gram CSR have all their members inside the sample
+// range [x0, x0 + width) (x0 and width multiples of kGramTile), so their contribution is the Gram
+// product of a (n x width) incidence block -- the int8 tensor-core work is O(width^2 n) instead of
+// O(N^2 n).  Windows come from a fixed multi-level grid (width 128 << level, stride width / 2; the
+// top level is the whole padded sample range when it is at most kGramMaxSamples wide).
+struct GramWin {
+    uint64_t c0;
+    uint32_t n;
+    uint32_t x0;
+    uint32_t width;
+    uint32_t pad;
+};
 
 // One K2 work item: columns [b0, b0+kMidCols) x rows [a0, a0+kMidRows) of mid colour `color`
 // (positions in the colour's sorted member list; only pairs with row position < column position count).
@@ -99,6 +113,9 @@ struct IndexDesc {
     uint64_t off_gram_offsets;  // u64[n_gram_colors+1]
     uint64_t off_gram_members;  // u32[n_gram_members]
     uint64_t off_gram_weights;  // u32[n_gram_colors]
+    uint64_t off_gram_wins;     // GramWin[n_gram_wins], ascending (x0, width); colours are grouped by window
+    uint64_t n_gram_wins;
+    uint64_t n_small_updates;   // pair-updates of the K1 colours
     uint64_t payload_bytes;
 };
 constexpr uint64_t kIndexMagic = 0x33305844494253ULL | (0x4BULL << 56);
