@@ -38,6 +38,7 @@ struct ksb_gram_chunk {
     uint32_t win_begin = 0, n_wins = 0;   // into the plan's window array
     uint32_t item_begin = 0, n_items = 0; // into the plan's item array
     uint32_t kblocks = 0;                 // K-blocks of all windows = pitch of the weight planes / 128
+    uint32_t n_units = 0;                 // bitmap-build units (K-block x sample segment)
 };
 struct ksb_gram_plan {
     bool built = false;
@@ -56,6 +57,13 @@ struct ksb_device {
     cudaStream_t stream2 = nullptr;        // K4 runs here, beside K1/K2 (tensor/ALU-bound next to red-bound)
     cudaEvent_t ev[12] = {};
     bool overlap = true;                   // KSPIDER_OVERLAP=0 serialises K4 after K1/K2
+    // pipelined upload (ksb_pairwise): the blob is copied in pieces on copy_stream and the first
+    // accumulation waits for exactly the piece each kernel reads
+    cudaStream_t copy_stream = nullptr;
+    bool copy_pending = false;
+    cudaEvent_t ev_copy[4] = {};           // copy start, head landed, tail landed, copy end
+    struct k1_piece { cudaEvent_t ev; unsigned long long task_begin, task_end; };
+    std::vector<k1_piece> k1_pieces;       // K1 task ranges in the order their classes are copied
     unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
     uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
     uint64_t tri_cells_alloc = 0;
@@ -234,6 +242,7 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
 static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint32_t* band_lo, const uint32_t* band_hi,
                          const ksb_opts* opts) {
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
+    if (d->desc.member_bits != 16 && d->desc.member_bits != 32) { set_error("descriptor: member_bits must be 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
     if (!d->stream) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     if (!d->stream2) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking));
@@ -355,6 +364,9 @@ void ksb_device_free(ksb_device* d) {
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
     if (d->stream) cudaStreamDestroy(d->stream);
     if (d->stream2) { cudaStreamSynchronize(d->stream2); cudaStreamDestroy(d->stream2); }
+    if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); cudaStreamDestroy(d->copy_stream); }
+    for (auto& e : d->ev_copy) if (e) cudaEventDestroy(e);
+    for (auto& pc : d->k1_pieces) if (pc.ev) cudaEventDestroy(pc.ev);
     (void)cudaGetLastError();
     delete d;
 }
@@ -369,7 +381,49 @@ static int opts_common(ksb_device* d, const ksb_opts* opts) {
     return KSB_OK;
 }
 
-int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
+// Enqueues the blob copy in pieces on the copy stream: head (totals, ids, bands), tail (mid, zero and
+// Gram sections: K4's bitmap build starts first), then the small-colour classes from the largest
+// size down in a few chunks -- the order K1 consumes them -- each followed by an event.
+static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
+    const IndexDesc& D = d->desc;
+    KSB_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+    for (auto& e : d->ev_copy) KSB_CUDA(cudaEventCreate(&e));
+    cudaStream_t cs = d->copy_stream;
+    auto copy = [&](uint64_t b, uint64_t e) -> cudaError_t {
+        return e > b ? cudaMemcpyAsync(d->d_payload + b, ix->payload + b, e - b, cudaMemcpyHostToDevice, cs) : cudaSuccess;
+    };
+    KSB_CUDA(cudaEventRecord(d->ev_copy[0], cs));
+    KSB_CUDA(copy(0, D.off_small_members));
+    KSB_CUDA(cudaEventRecord(d->ev_copy[1], cs));
+    KSB_CUDA(copy(D.off_mid_offsets, D.payload_bytes));
+    KSB_CUDA(cudaEventRecord(d->ev_copy[2], cs));
+    const uint64_t mbytes = D.member_bits / 8;
+    const uint64_t small_bytes = mbytes * D.n_small_members + 4 * D.n_small_colors;
+    const uint64_t chunk = std::max<uint64_t>(8ull << 20, small_bytes / 6);
+    const K1Params& k1 = d->k1;  // classes in descending size = task order
+    for (uint32_t c = 0; c < k1.n_cls;) {
+        uint32_t e = c;
+        uint64_t bytes = 0;
+        while (e < k1.n_cls && (e == c || bytes < chunk)) { bytes += k1.cls[e].n * (mbytes * k1.cls[e].s + 4); e++; }
+        // classes c..e-1 have descending s, i.e. DEscending offsets: their members / weights are one run each
+        const K1Class &hi = k1.cls[c], &lo = k1.cls[e - 1];
+        KSB_CUDA(copy(D.off_small_members + mbytes * lo.member_off, D.off_small_members + mbytes * (hi.member_off + hi.n * hi.s)));
+        KSB_CUDA(copy(D.off_small_weights + 4 * lo.weight_off, D.off_small_weights + 4 * (hi.weight_off + hi.n)));
+        ksb_device::k1_piece pc;
+        pc.ev = nullptr;
+        KSB_CUDA(cudaEventCreateWithFlags(&pc.ev, cudaEventDisableTiming));
+        KSB_CUDA(cudaEventRecord(pc.ev, cs));
+        pc.task_begin = hi.task_begin;
+        pc.task_end = e < k1.n_cls ? k1.cls[e].task_begin : k1.n_tasks;
+        d->k1_pieces.push_back(pc);
+        c = e;
+    }
+    KSB_CUDA(cudaEventRecord(d->ev_copy[3], cs));
+    d->copy_pending = true;
+    return KSB_OK;
+}
+
+static int upload_impl(const ksb_index* ix, const ksb_opts* opts, ksb_device** out, bool pipelined) {
     if (!ix || !out) { set_error("ksb_upload: null argument"); return KSB_ERR_ARG; }
     *out = nullptr;
     int sms = 0;
@@ -395,6 +449,12 @@ int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
     rc = finish_device(d, row_updates, reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_lo),
                        reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_hi), opts);
     if (rc) return fail(rc);
+    if (pipelined && ix->pinned && !d->spill) {
+        rc = enqueue_pipelined_copy(d, ix);
+        if (rc) return fail(rc);
+        *out = d;
+        return KSB_OK;
+    }
     cudaEventRecord(d->ev[0], d->stream);
     e = cudaMemcpyAsync(d->d_payload, ix->payload, d->desc.payload_bytes, cudaMemcpyHostToDevice, d->stream);
     cudaEventRecord(d->ev[1], d->stream);
@@ -404,6 +464,8 @@ int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) {
     *out = d;
     return KSB_OK;
 }
+
+int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out) { return upload_impl(ix, opts, out, false); }
 
 int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, const void* d_payload,
                              uint64_t payload_bytes, const ksb_opts* opts, ksb_device** out) {
@@ -533,7 +595,8 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
             wd.width = w.width;
             wd.tiles = tiles;
             wd.k0 = cur.kblocks;
-            wd.pad = 0;
+            wd.u0 = cur.n_units;
+            cur.n_units += (uint32_t)kbs * ((w.width + kGramSeg - 1) / kGramSeg);
             wins.push_back(wd);
             wrows.push_back(rows);
             cur.n_wins++;
@@ -582,7 +645,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
     const IndexDesc& D = d->desc;
     const uint8_t* P = d->d_payload;
     const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
-    const uint32_t* gmem = reinterpret_cast<const uint32_t*>(P + D.off_gram_members);
+    const void* gmem = P + D.off_gram_members;
     const uint32_t* gw = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
     bool first = true;
     for (const ksb_gram_chunk& c : plan.chunks) {
@@ -597,9 +660,8 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
         gp.planes = d->g_planes;
         gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
         cudaStream_t sb = first ? st_build : st;
-        KSB_CUDA(cudaMemsetAsync(d->d_gbits, 0, c.bits_rows * 16, sb));
-        KSB_CUDA(cudaMemsetAsync(d->d_gwq, 0, (uint64_t)d->g_planes * gp.kpad + 256, sb));
-        KSB_CUDA(launch_kb_build(goff, gmem, gw, c.c_begin, c.n_colors, gp.wins, gp.n_wins, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
+        KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
+        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.member_bits, gw, gp.wins, gp.n_wins, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
                                  LaunchCfg{d->sms, sb}));
         if (sb != st) {
             KSB_CUDA(cudaEventRecord(ev_built, sb));
@@ -626,6 +688,10 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     KSB_CUDA(cudaMemsetAsync(d->d_tri, 0, 8 * (p.cells + 8), st));
     if (d->d_touched) KSB_CUDA(cudaMemsetAsync(d->d_touched, 0, 4 * (p.cells / 32 + 2), st));
     KSB_CUDA(cudaEventRecord(d->ev[1], st));
+    if (d->copy_pending) {  // first accumulation after a pipelined upload
+        KSB_CUDA(cudaStreamWaitEvent(st, d->ev_copy[1], 0));
+        KSB_CUDA(cudaStreamWaitEvent(st, d->ev_copy[2], 0));
+    }
     // K4 goes first, on its own stream: one big CTA per SM (tensor pipe + integer expansion) leaves
     // thread slots for the red-bound K1/K2 CTAs launched right after it on the main stream.
     const bool has_gram = p.cells && D.n_gram_colors;
@@ -636,23 +702,38 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         KSB_CUDA(cudaEventRecord(d->ev[10], d->stream2));
     }
     if (p.cells) {
-        KSB_CUDA(launch_k1_small(d->k1, reinterpret_cast<const uint32_t*>(P + D.off_small_members),
-                                 reinterpret_cast<const uint32_t*>(P + D.off_small_weights), g, lc));
-        if (d->k1.n_tasks) d->launches++;
+        LaunchCfg lc1 = lc;
+        if (has_gram && d->overlap) {  // tuning knob: K4 holds 576 threads and ~37K registers of an SM (measured: no gain from leaving it room, both kernels are issue-bound)
+            const char* kc = std::getenv("KSPIDER_K1_CTAS");
+            lc1.k1_ctas = (kc && std::atoi(kc) > 0 && std::atoi(kc) <= 8) ? std::atoi(kc) : 8;
+        }
+        const void* sm_m = P + D.off_small_members;
+        const uint32_t mb = (uint32_t)D.member_bits;
+        const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(P + D.off_small_weights);
+        if (d->copy_pending) {
+            for (const ksb_device::k1_piece& pc : d->k1_pieces) {
+                KSB_CUDA(cudaStreamWaitEvent(st, pc.ev, 0));
+                KSB_CUDA(launch_k1_small(d->k1, sm_m, mb, sm_w, g, lc1, pc.task_begin, pc.task_end));
+                d->launches++;
+            }
+        } else {
+            KSB_CUDA(launch_k1_small(d->k1, sm_m, mb, sm_w, g, lc1, 0ull, d->k1.n_tasks));
+            if (d->k1.n_tasks) d->launches++;
+        }
     }
     KSB_CUDA(cudaEventRecord(d->ev[2], st));
     if (p.cells && D.n_mid_items) {
         KSB_CUDA(launch_k2_mid(reinterpret_cast<const MidItem*>(P + D.off_mid_items), D.n_mid_items,
                                reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
-                               reinterpret_cast<const uint32_t*>(P + D.off_mid_members),
+                               P + D.off_mid_members, (uint32_t)D.member_bits,
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, lc));
         d->launches++;
     }
     KSB_CUDA(cudaEventRecord(d->ev[3], st));
     if (p.cells && D.n_zero_colors) {
         KSB_CUDA(launch_kz_touch(D.n_zero_colors, reinterpret_cast<const unsigned long long*>(P + D.off_zero_offsets),
-                                 reinterpret_cast<const uint32_t*>(P + D.off_zero_members), d->d_touched, g, lc));
+                                 P + D.off_zero_members, (uint32_t)D.member_bits, d->d_touched, g, lc));
         d->launches++;
     }
     KSB_CUDA(cudaEventRecord(d->ev[4], st));
@@ -664,6 +745,12 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         KSB_CUDA(cudaEventRecord(d->ev[10], st));
     }
     KSB_CUDA(cudaEventRecord(d->ev[8], st));
+    if (d->copy_pending) {
+        KSB_CUDA(cudaStreamWaitEvent(st, d->ev_copy[3], 0));
+        KSB_CUDA(cudaStreamSynchronize(st));
+        d->t.h2d_ms = ev_ms(d->ev_copy[0], d->ev_copy[3]);  // overlaps accumulate_ms
+        d->copy_pending = false;
+    }
     if (sync) {
         KSB_CUDA(cudaStreamSynchronize(st));
         d->t.zero_ms += ev_ms(d->ev[0], d->ev[1]);
@@ -868,21 +955,21 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
         SP(cudaMemsetAsync(d_cnt, 0, 16, st));
         SP(cudaEventRecord(e0, st));
         if (ch.kind == 0)
-            SP(launch_k1_spill(d->k1, reinterpret_cast<const uint32_t*>(P + D.off_small_members),
+            SP(launch_k1_spill(d->k1, P + D.off_small_members, (uint32_t)D.member_bits,
                                reinterpret_cast<const uint32_t*>(P + D.off_small_weights), g, sb, ch.b, ch.e, lc));
         else if (ch.kind == 1)
             SP(launch_k2_spill(reinterpret_cast<const MidItem*>(P + D.off_mid_items), ch.b, ch.e,
                                reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
-                               reinterpret_cast<const uint32_t*>(P + D.off_mid_members),
+                               P + D.off_mid_members, (uint32_t)D.member_bits,
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, sb, lc));
         else if (ch.kind == 2)
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets),
-                                  reinterpret_cast<const uint32_t*>(P + D.off_gram_members),
+                                  P + D.off_gram_members, (uint32_t)D.member_bits,
                                   reinterpret_cast<const uint32_t*>(P + D.off_gram_weights), g, sb, lc));
         else
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_zero_offsets),
-                                  reinterpret_cast<const uint32_t*>(P + D.off_zero_members), nullptr, g, sb, lc));
+                                  P + D.off_zero_members, (uint32_t)D.member_bits, nullptr, g, sb, lc));
         SP(cudaEventRecord(e1, st));
         d->launches++;
         unsigned long long n = 0;
@@ -988,7 +1075,7 @@ int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     if (!ix || !out) { set_error("ksb_pairwise: null argument"); return KSB_ERR_ARG; }
     *out = nullptr;
     ksb_device* d = nullptr;
-    int rc = ksb_upload(ix, opts, &d);
+    int rc = upload_impl(ix, opts, &d, true);
     if (rc) return rc;
     ksb_result* r = nullptr;
     const int want = opts ? opts->want_records : 1;

@@ -115,48 +115,92 @@ __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const Tr
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------
-// kb_build: one warp per Gram colour of the chunk [c_begin, c_begin + n).  Finds the colour's
-// (sub-)window, sets bit (colour, local sample) in the window's K-block-major bitmap
-//     bits[(bits_off + kblock * width + sample - x0) * 4 + word]
-// and writes the byte planes of the colour's weight to wq[plane * kpad + k0 * 128 + colour - c0].
+// kb_build: one CTA per build unit = (sub-window, K-block of 128 colours, segment of kGramSeg
+// samples).  The unit's piece of the K-block-major bitmap
+//     bits[(bits_off + kblock * width + sample - x0) * 4 + word]      bit (colour % 128) of the sample
+// is assembled in shared memory (shared atomicOr, 16 colours per warp with their loads batched) and written out once,
+// coalesced -- zeros included, so the bitmap needs no memset and no global atomics.  Segment 0 also
+// writes the byte planes of the weights to wq[plane * kpad + (k0 + kblock) * 128 + k].
 // ------------------------------------------------------------------------------------------------
+template <class MT>
 __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __restrict__ gram_off,
-                                                const uint32_t* __restrict__ gram_members,
-                                                const uint32_t* __restrict__ gram_weights, unsigned long long c_begin,
-                                                unsigned long long n, const GramWinDev* __restrict__ wins, uint32_t n_wins,
+                                                const MT* __restrict__ gram_members,
+                                                const uint32_t* __restrict__ gram_weights,
+                                                const GramWinDev* __restrict__ wins, uint32_t n_wins, uint32_t n_units,
                                                 uint32_t kpad, uint32_t planes, uint32_t* __restrict__ bits,
                                                 uint8_t* __restrict__ wq) {
-    const uint32_t lane = threadIdx.x & 31u;
-    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
-    for (unsigned long long ci = warp; ci < n; ci += nwarps) {
-        const unsigned long long c = c_begin + ci;
-        uint32_t lo = 0, hi = n_wins;  // last window with c0 <= c
+    __shared__ __align__(16) uint32_t sm[kGramSeg * 4];
+    __shared__ unsigned long long sm_off[kKB + 1];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    for (uint32_t unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+        uint32_t lo = 0, hi = n_wins;  // last window with u0 <= unit
         while (hi - lo > 1) {
             const uint32_t mid = (lo + hi) >> 1;
-            if (__ldg(&wins[mid].c0) <= c) lo = mid; else hi = mid;
+            if (__ldg(&wins[mid].u0) <= unit) lo = mid; else hi = mid;
         }
         const GramWinDev w = wins[lo];
-        const uint32_t cl = (uint32_t)(c - w.c0);
-        const unsigned long long off = gram_off[c];
-        const uint32_t s = (uint32_t)(gram_off[c + 1] - off);
-        const uint32_t* m = gram_members + off;
-        uint32_t* base = bits + (w.bits_off + (unsigned long long)(cl >> 7) * w.width) * 4ull + ((cl & 127u) >> 5);
-        const uint32_t bit = 1u << (cl & 31u);
-        for (uint32_t a = lane; a < s; a += 32) atomicOr(base + 4ull * (__ldg(m + a) - w.x0), bit);
-        if (lane < planes) wq[(unsigned long long)lane * kpad + (unsigned long long)w.k0 * kKB + cl] = (uint8_t)(__ldg(gram_weights + c) >> (8u * lane));
+        const uint32_t segs = (w.width + kGramSeg - 1) / kGramSeg;
+        const uint32_t kb = (unit - w.u0) / segs, seg = (unit - w.u0) - kb * segs;
+        const uint32_t s0 = seg * kGramSeg, slen = min(kGramSeg, w.width - s0);
+        uint4* sm4 = reinterpret_cast<uint4*>(sm);
+        for (uint32_t r = tid; r < slen; r += 256) sm4[r] = make_uint4(0u, 0u, 0u, 0u);
+        __syncthreads();
+        const uint32_t kn = min(kKB, w.n - kb * kKB);  // colours of this K-block
+        // offsets of the K-block's colours staged once; then every warp takes 16 colours and issues the
+        // loads of all of them before the first shared atomic (the loads are independent: one memory
+        // latency per unit instead of one per colour)
+        const unsigned long long c0k = w.c0 + (unsigned long long)kb * kKB;
+        if (tid <= kn) sm_off[tid] = gram_off[c0k + tid];
+        __syncthreads();
+        uint32_t x[16];
+#pragma unroll
+        for (uint32_t kk = 0; kk < 16; kk++) {
+            const uint32_t k = warp + 8u * kk;
+            x[kk] = 0xFFFFFFFFu;
+            if (k < kn) {
+                const unsigned long long o = sm_off[k];
+                if (lane < (uint32_t)(sm_off[k + 1] - o)) x[kk] = __ldg(gram_members + o + lane) - w.x0 - s0;
+            }
+        }
+#pragma unroll
+        for (uint32_t kk = 0; kk < 16; kk++) {
+            const uint32_t k = warp + 8u * kk;
+            if (x[kk] < slen) atomicOr(sm + 4u * x[kk] + (k >> 5), 1u << (k & 31u));  // members outside the segment wrap to >= slen
+        }
+        for (uint32_t kk = 0; kk < 16; kk++) {  // colours with more than 32 members
+            const uint32_t k = warp + 8u * kk;
+            if (k >= kn) break;
+            const unsigned long long o = sm_off[k];
+            const uint32_t s = (uint32_t)(sm_off[k + 1] - o);
+            const uint32_t bit = 1u << (k & 31u), word = k >> 5;
+#pragma unroll 4
+            for (uint32_t a = 32u + lane; a < s; a += 32) {
+                const uint32_t xx = __ldg(gram_members + o + a) - w.x0 - s0;
+                if (xx < slen) atomicOr(sm + 4u * xx + word, bit);
+            }
+        }
+        if (seg == 0 && tid < kKB) {
+            const uint32_t wt = tid < kn ? __ldg(gram_weights + w.c0 + (unsigned long long)kb * kKB + tid) : 0u;
+            for (uint32_t p = 0; p < planes; p++)
+                wq[(unsigned long long)p * kpad + (unsigned long long)(w.k0 + kb) * kKB + tid] = (uint8_t)(wt >> (8u * p));
+        }
+        __syncthreads();
+        uint4* dst = reinterpret_cast<uint4*>(bits) + w.bits_off + (unsigned long long)kb * w.width + s0;
+        for (uint32_t r = tid; r < slen; r += 256) dst[r] = sm4[r];
+        __syncthreads();
     }
 }
 
-cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* gram_members,
-                            const uint32_t* gram_weights, uint64_t c_begin, uint64_t n, const GramWinDev* wins,
-                            uint32_t n_wins, uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq,
-                            const LaunchCfg& lc) {
-    if (n == 0) return cudaSuccess;
-    unsigned long long ctas = (n + 7) / 8;
-    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
-    if (ctas > cap) ctas = cap;
-    kb_build<<<(unsigned)ctas, 256, 0, lc.stream>>>(gram_off, gram_members, gram_weights, c_begin, n, wins, n_wins, kpad, planes, bits, wq);
+cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
+                            const uint32_t* gram_weights, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
+                            uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {
+    if (n_units == 0) return cudaSuccess;
+    const unsigned cap = (unsigned)lc.sms * 6u;  // 32 KB of shared memory per CTA
+    const unsigned ctas = n_units < cap ? n_units : cap;
+    if (member_bits == 16)
+        kb_build<uint16_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, wins, n_wins, n_units, kpad, planes, bits, wq);
+    else
+        kb_build<uint32_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint32_t*>(gram_members), gram_weights, wins, n_wins, n_units, kpad, planes, bits, wq);
     return cudaGetLastError();
 }
 

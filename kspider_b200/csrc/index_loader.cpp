@@ -345,7 +345,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             if (!k) continue;
             cnt[t][k]++;
             const uint64_t s = raw.off[c + 1] - raw.off[c];
-            mcnt[t][k] += (k == K_MID) ? ((s + 3) & ~3ULL) : s;  // mid colours start 16-byte aligned
+            mcnt[t][k] += (k == K_MID) ? ((s + 7) & ~7ULL) : s;  // mid colours start 16-byte aligned (u16 or u32 members)
             if (k == K_MID) icnt[t] += mid_items_of(s);
         }
     });
@@ -383,6 +383,14 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.n_gram_members = mtot[K_GRAM];
     d.n_colors = d.n_small_colors + d.n_mid_colors + d.n_zero_colors + d.n_gram_colors;
 
+    // ---- member width: u16 when every compact id fits (halves the blob = the H2D / broadcast time);
+    // KSPIDER_MEMBER_BITS=32 forces u32 (tests)
+    {
+        const char* mb = std::getenv("KSPIDER_MEMBER_BITS");
+        d.member_bits = (N <= 65536 && !(mb && std::atoi(mb) == 32)) ? 16 : 32;
+    }
+    const uint64_t MB = d.member_bits / 8;
+
     // ---- payload layout
     uint64_t p = 0;
     auto section = [&](uint64_t bytes) { const uint64_t o = p; p = align256(p + bytes); return o; };
@@ -391,17 +399,17 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_row_updates = section(8 * N);
     d.off_band_lo = section(4 * N);
     d.off_band_hi = section(4 * N);
-    d.off_small_members = section(4 * d.n_small_members);
+    d.off_small_members = section(MB * d.n_small_members);
     d.off_small_weights = section(4 * d.n_small_colors);
     d.off_mid_offsets = section(8 * (d.n_mid_colors + 1));
     d.off_mid_sizes = section(4 * d.n_mid_colors);
-    d.off_mid_members = section(4 * d.n_mid_members_padded + 16);
+    d.off_mid_members = section(MB * d.n_mid_members_padded + 64);
     d.off_mid_weights = section(4 * d.n_mid_colors);
     d.off_mid_items = section(sizeof(MidItem) * d.n_mid_items);
     d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
-    d.off_zero_members = section(4 * d.n_zero_members);
+    d.off_zero_members = section(MB * d.n_zero_members);
     d.off_gram_offsets = section(8 * (d.n_gram_colors + 1));
-    d.off_gram_members = section(4 * d.n_gram_members);
+    d.off_gram_members = section(MB * d.n_gram_members);
     d.off_gram_weights = section(4 * d.n_gram_colors);
     d.n_gram_wins = gwins.size();
     d.off_gram_wins = section(sizeof(GramWin) * d.n_gram_wins);
@@ -423,17 +431,17 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     uint64_t* row_updates = reinterpret_cast<uint64_t*>(P + d.off_row_updates);
     uint32_t* band_lo = reinterpret_cast<uint32_t*>(P + d.off_band_lo);
     uint32_t* band_hi = reinterpret_cast<uint32_t*>(P + d.off_band_hi);
-    uint32_t* small_m = reinterpret_cast<uint32_t*>(P + d.off_small_members);
+    uint8_t* small_m = P + d.off_small_members;  // member sections: u16 or u32 elements
     uint32_t* small_w = reinterpret_cast<uint32_t*>(P + d.off_small_weights);
     uint64_t* mid_off = reinterpret_cast<uint64_t*>(P + d.off_mid_offsets);
-    uint32_t* mid_m = reinterpret_cast<uint32_t*>(P + d.off_mid_members);
+    uint8_t* mid_m = P + d.off_mid_members;
     uint32_t* mid_w = reinterpret_cast<uint32_t*>(P + d.off_mid_weights);
     uint32_t* mid_sz = reinterpret_cast<uint32_t*>(P + d.off_mid_sizes);
     MidItem* mid_items = reinterpret_cast<MidItem*>(P + d.off_mid_items);
     uint64_t* zero_off = reinterpret_cast<uint64_t*>(P + d.off_zero_offsets);
-    uint32_t* zero_m = reinterpret_cast<uint32_t*>(P + d.off_zero_members);
+    uint8_t* zero_m = P + d.off_zero_members;
     uint64_t* gram_off = reinterpret_cast<uint64_t*>(P + d.off_gram_offsets);
-    uint32_t* gram_m = reinterpret_cast<uint32_t*>(P + d.off_gram_members);
+    uint8_t* gram_m = P + d.off_gram_members;
     uint32_t* gram_w = reinterpret_cast<uint32_t*>(P + d.off_gram_weights);
 
     std::copy(sample_ids.begin(), sample_ids.end(), sids);
@@ -460,6 +468,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         bhi.assign(N, 0);
         std::vector<uint64_t> at = base[t], mat = mbase[t];
         uint64_t maxs = 0, midu = 0, midm = 0, gramu = 0, iat = ibase[t];
+        std::vector<uint32_t> cm;  // compact members of the current colour
         for (uint64_t ci = b; ci < e; ci++) {
             const uint64_t c = ord(ci);
             const uint32_t k = klass(c);
@@ -467,9 +476,9 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             const uint64_t s = raw.off[c + 1] - raw.off[c];
             const uint32_t* src = &raw.members[raw.off[c]];
             const uint32_t w = raw.weights[c];
-            uint32_t* dst;
+            uint8_t* dst;  // element 0 of this colour in its member section
             if (k == K_MID) {
-                dst = mid_m + mat[k];
+                dst = mid_m + MB * mat[k];
                 mid_off[at[k]] = mat[k];
                 mid_sz[at[k]] = (uint32_t)s;
                 mid_w[at[k]] = w;
@@ -481,30 +490,33 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                         mid_items[iat++] = MidItem{(uint32_t)at[k], (uint32_t)b0, (uint32_t)a0, 0};
                 }
             } else if (k == K_ZERO) {
-                dst = zero_m + mat[k];
+                dst = zero_m + MB * mat[k];
                 zero_off[at[k]] = mat[k];
             } else if (k == K_GRAM) {
-                dst = gram_m + gram_off[gkey[c]];
+                dst = gram_m + MB * gram_off[gkey[c]];
                 gram_w[gkey[c]] = w;
                 gramu += s * (s - 1) / 2;
             } else {
                 const SmallClass& sc = d.cls[k];
-                dst = small_m + sc.member_off + at[k] * s;
+                dst = small_m + MB * (sc.member_off + at[k] * s);
                 small_w[sc.weight_off + at[k]] = w;
             }
+            cm.resize(s);
             for (uint64_t i = 0; i < s; i++) {
                 const uint32_t ci = compact(src[i]);
-                dst[i] = ci;
+                cm[i] = ci;
+                if (MB == 2) reinterpret_cast<uint16_t*>(dst)[i] = (uint16_t)ci;
+                else reinterpret_cast<uint32_t*>(dst)[i] = ci;
                 if (k != K_ZERO) { rows[ci] += s - 1 - i; rowsum[ci] += w; }
             }
-            // members are ascending: row dst[i] pairs with columns dst[i+1] .. dst[s-1]
+            // members are ascending: row cm[i] pairs with columns cm[i+1] .. cm[s-1]
             for (uint64_t i = 0; i + 1 < s; i++) {
-                blo[dst[i]] = std::min(blo[dst[i]], dst[i + 1]);
-                bhi[dst[i]] = std::max(bhi[dst[i]], dst[s - 1] + 1);
+                blo[cm[i]] = std::min(blo[cm[i]], cm[i + 1]);
+                bhi[cm[i]] = std::max(bhi[cm[i]], cm[s - 1] + 1);
             }
             maxs = std::max(maxs, s);
             at[k]++;
-            mat[k] += (k == K_MID) ? ((s + 3) & ~3ULL) : s;
+            mat[k] += (k == K_MID) ? ((s + 7) & ~7ULL) : s;
         }
         t_maxs[t] = maxs;
         t_mid_updates[t] = midu;

@@ -70,9 +70,9 @@ struct SpillSink {
 // coalesced load, then walks the rows: step a broadcasts row a of every group by shuffle and the
 // lanes holding a later member add the colour's weight into cell (row, own member).
 // ------------------------------------------------------------------------------------------------
-template <class Sink>
+template <class Sink, class MT>
 __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params P,
-                                                const uint32_t* __restrict__ members,
+                                                const MT* __restrict__ members,
                                                 const uint32_t* __restrict__ weights,
                                                 const __grid_constant__ TriGeom G, const Sink sink,
                                                 unsigned long long task_begin, unsigned long long task_end) {
@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
         const unsigned long long t_in = task - P.cls[lo].task_begin;
         const unsigned long long n = P.cls[lo].n;
         const uint32_t s = P.cls[lo].s;
-        const uint32_t* mcls = members + P.cls[lo].member_off;
+        const MT* mcls = members + P.cls[lo].member_off;
         const uint32_t* wcls = weights + P.cls[lo].weight_off;
         if (s <= 32) {
             const uint32_t k = P.cls[lo].k;
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
                 sink.add(valid && a > ar && r != 0ull, r, cadd, w);
             }
         } else {
-            const uint32_t* m = mcls + t_in * s;
+            const MT* m = mcls + t_in * s;
             const bool v1 = lane + 32 < s;
             const uint32_t x0 = __ldg(m + lane);
             const uint32_t x1 = v1 ? __ldg(m + 32 + lane) : 0u;
@@ -140,26 +140,32 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
     }
 }
 
-cudaError_t launch_k1_small(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
-                            const LaunchCfg& lc) {
-    if (p.n_tasks == 0) return cudaSuccess;
+cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
+                            const LaunchCfg& lc, unsigned long long task_begin, unsigned long long task_end) {
+    if (task_end <= task_begin) return cudaSuccess;
     const unsigned long long warps_per_cta = 8;
-    unsigned long long ctas = (p.n_tasks + warps_per_cta - 1) / warps_per_cta;
-    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;  // 8 x 256 threads = 2048 resident threads / SM
+    unsigned long long ctas = (task_end - task_begin + warps_per_cta - 1) / warps_per_cta;
+    const unsigned long long cap = (unsigned long long)lc.sms * (unsigned long long)lc.k1_ctas;  // 8 x 256 threads = 2048 resident threads / SM
     if (ctas > cap) ctas = cap;
-    k1_small<DenseSink><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, members, weights, g, DenseSink{}, 0ull, p.n_tasks);
+    if (member_bits == 16)
+        k1_small<DenseSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
+    else
+        k1_small<DenseSink, uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint32_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
     return cudaGetLastError();
 }
 
-cudaError_t launch_k1_spill(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
+cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
                             const SpillBuf& sb, unsigned long long task_begin, unsigned long long task_end,
                             const LaunchCfg& lc) {
     if (task_end <= task_begin) return cudaSuccess;
     unsigned long long ctas = (task_end - task_begin + 7) / 8;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k1_small<SpillSink><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, members, weights, g, SpillSink{sb.keys, sb.vals, sb.cursor, sb.shift},
-                                                               task_begin, task_end);
+    const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
+    if (member_bits == 16)
+        k1_small<SpillSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, sink, task_begin, task_end);
+    else
+        k1_small<SpillSink, uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint32_t*>(members), weights, g, sink, task_begin, task_end);
     return cudaGetLastError();
 }
 
@@ -192,15 +198,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
-template <class Sink>
+template <class Sink, class MT>
 __global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ items, unsigned long long item_begin,
                                                    unsigned long long n_items,
                                                    const unsigned long long* __restrict__ mid_off,
                                                    const uint32_t* __restrict__ mid_sizes,
-                                                   const uint32_t* __restrict__ mid_members,
+                                                   const MT* __restrict__ mid_members,
                                                    const uint32_t* __restrict__ mid_weights,
                                                    const __grid_constant__ TriGeom G, const Sink sink) {
-    __shared__ __align__(128) uint32_t sm_rows[kMidRows];
+    __shared__ __align__(128) MT sm_rows[kMidRows];
     __shared__ __align__(16) unsigned long long sm_ra[kMidRows];
     __shared__ __align__(8) unsigned long long sm_bar;
     const uint32_t tid = threadIdx.x;
@@ -215,7 +221,7 @@ __global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ i
     for (unsigned long long it = item_begin + blockIdx.x; it < n_items; it += gridDim.x) {
         const MidItem item = items[it];
         const uint32_t s = __ldg(mid_sizes + item.color);
-        const uint32_t* m = mid_members + __ldg(mid_off + item.color);
+        const MT* m = mid_members + __ldg(mid_off + item.color);
         const unsigned long long w = __ldg(mid_weights + item.color);
         const uint32_t row_lim = min(s - 1u, item.b0 + kMidCols - 1u);
         const uint32_t a_end = min(item.a0 + kMidRows, row_lim);
@@ -226,7 +232,7 @@ __global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ i
         }
         if (tid == 0) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            const uint32_t bytes = 4u * ((nr + 3u) & ~3u);
+            const uint32_t bytes = (uint32_t)sizeof(MT) * ((nr + 7u) & ~7u);  // colours are padded to 8 members
             mbar_expect_tx(bar, bytes);
             tma_load_1d(smem_u32(sm_rows), m + item.a0, bytes, bar);
         }
@@ -250,34 +256,40 @@ __global__ void __launch_bounds__(kMidCols) k2_mid(const MidItem* __restrict__ i
 }
 
 cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned long long* mid_off,
-                          const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                          const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
                           const TriGeom& g, const LaunchCfg& lc) {
     if (n_items == 0) return cudaSuccess;
     unsigned long long ctas = n_items;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k2_mid<DenseSink><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, mid_members, mid_weights, g,
-                                                                  DenseSink{});
+    if (member_bits == 16)
+        k2_mid<DenseSink, uint16_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, static_cast<const uint16_t*>(mid_members), mid_weights, g, DenseSink{});
+    else
+        k2_mid<DenseSink, uint32_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, static_cast<const uint32_t*>(mid_members), mid_weights, g, DenseSink{});
     return cudaGetLastError();
 }
 
 cudaError_t launch_k2_spill(const MidItem* items, uint64_t item_begin, uint64_t item_end, const unsigned long long* mid_off,
-                            const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                            const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
                             const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc) {
     if (item_end <= item_begin) return cudaSuccess;
     unsigned long long ctas = item_end - item_begin;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k2_mid<SpillSink><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, item_begin, item_end, mid_off, mid_sizes, mid_members, mid_weights, g,
-                                                                  SpillSink{sb.keys, sb.vals, sb.cursor, sb.shift});
+    const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
+    if (member_bits == 16)
+        k2_mid<SpillSink, uint16_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, item_begin, item_end, mid_off, mid_sizes, static_cast<const uint16_t*>(mid_members), mid_weights, g, sink);
+    else
+        k2_mid<SpillSink, uint32_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, item_begin, item_end, mid_off, mid_sizes, static_cast<const uint32_t*>(mid_members), mid_weights, g, sink);
     return cudaGetLastError();
 }
 
 // Generic warp-per-colour emitter over a plain CSR section (Gram-routed and zero-weight colours in
 // spill mode; a zero weight appends (key, 0), which is exactly the reference's insert-with-0).
+template <class MT>
 __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, unsigned long long c_end,
                                                    const unsigned long long* __restrict__ off,
-                                                   const uint32_t* __restrict__ members,
+                                                   const MT* __restrict__ members,
                                                    const uint32_t* __restrict__ weights,  // nullptr = weight 0
                                                    const __grid_constant__ TriGeom G, const SpillSink sink) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -286,7 +298,7 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
     for (unsigned long long c = c_begin + warp; c < c_end; c += nwarps) {
         const unsigned long long o = off[c];
         const uint32_t s = (uint32_t)(off[c + 1] - o);
-        const uint32_t* m = members + o;
+        const MT* m = members + o;
         const unsigned long long w = weights ? __ldg(weights + c) : 0ull;
         for (uint32_t a = 0; a + 1 < s; a++) {
             const unsigned long long r = SpillSink::row(__ldg(m + a), G);
@@ -299,14 +311,17 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
     }
 }
 
-cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const uint32_t* members,
-                               const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc) {
+cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
+                               uint32_t member_bits, const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc) {
     if (c_end <= c_begin) return cudaSuccess;
     unsigned long long ctas = (c_end - c_begin + 7) / 8;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k3_emit_csr<<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, members, weights, g,
-                                                       SpillSink{sb.keys, sb.vals, sb.cursor, sb.shift});
+    const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
+    if (member_bits == 16)
+        k3_emit_csr<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint16_t*>(members), weights, g, sink);
+    else
+        k3_emit_csr<uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint32_t*>(members), weights, g, sink);
     return cudaGetLastError();
 }
 
@@ -314,8 +329,9 @@ cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned 
 // Kz: colours whose narrowed count is 0 still create a row in the reference (edges.try_emplace_l
 // inserts the pair with value 0, src/pairwise.cpp:222-225).  They set a bit in a touched-bitmap.
 // ------------------------------------------------------------------------------------------------
+template <class MT>
 __global__ void __launch_bounds__(256) kz_touch(unsigned long long n_zero, const unsigned long long* __restrict__ zero_off,
-                                                const uint32_t* __restrict__ zero_members, uint32_t* touched,
+                                                const MT* __restrict__ zero_members, uint32_t* touched,
                                                 const __grid_constant__ TriGeom G) {
     const uint32_t lane = threadIdx.x & 31u;
     const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -323,7 +339,7 @@ __global__ void __launch_bounds__(256) kz_touch(unsigned long long n_zero, const
     for (unsigned long long c = warp; c < n_zero; c += nwarps) {
         const unsigned long long off = zero_off[c];
         const uint32_t s = (uint32_t)(zero_off[c + 1] - off);
-        const uint32_t* m = zero_members + off;
+        const MT* m = zero_members + off;
         for (uint32_t a = 0; a + 1 < s; a++) {
             const uint32_t i = m[a];
             if (i - G.rb >= G.nrows) continue;
@@ -336,13 +352,16 @@ __global__ void __launch_bounds__(256) kz_touch(unsigned long long n_zero, const
     }
 }
 
-cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const uint32_t* zero_members,
-                            uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc) {
+cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const void* zero_members,
+                            uint32_t member_bits, uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc) {
     if (n_zero == 0) return cudaSuccess;
     unsigned long long ctas = (n_zero + 7) / 8;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    kz_touch<<<(unsigned)ctas, 256, 0, lc.stream>>>(n_zero, zero_off, zero_members, touched_bits, g);
+    if (member_bits == 16)
+        kz_touch<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(n_zero, zero_off, static_cast<const uint16_t*>(zero_members), touched_bits, g);
+    else
+        kz_touch<uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(n_zero, zero_off, static_cast<const uint32_t*>(zero_members), touched_bits, g);
     return cudaGetLastError();
 }
 
@@ -408,6 +427,9 @@ __device__ __forceinline__ void containment(unsigned long long shared, uint32_t 
     cavg = canon_nan(__double2float_rn(__ddiv_rn((double)sum, 2.0)));
 }
 
+// Emit pass.  A warp owns 256 consecutive cells and takes them 32 at a time (lane = cell), so the
+// flagged lanes of one step write CONSECUTIVE records: the record stores of a warp instruction fill
+// whole 32-byte sectors instead of one scattered sector per lane.
 __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ TriGeom G,
                                                         const uint32_t* __restrict__ touched,
                                                         const unsigned long long* __restrict__ block_offsets,
@@ -416,28 +438,35 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
                                                         ksb_record* __restrict__ records,
                                                         unsigned long long* __restrict__ pairs) {
     __shared__ uint32_t sm[kPostThreads / 32];
-    const unsigned long long cell0 = ((unsigned long long)blockIdx.x * kPostThreads + threadIdx.x) * kPostPerThread;
-    unsigned long long v[kPostPerThread];
-    const uint32_t flags = k5_flags(G, touched, cell0, v);
-    const uint32_t c = __popc(flags);
-    // block exclusive scan of c
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-    uint32_t incl = c;
+    const unsigned long long wcell0 = (unsigned long long)blockIdx.x * kPostChunk + wid * (32u * kPostPerThread);
+    unsigned long long v[kPostPerThread];
+    uint32_t ball[kPostPerThread];
+    uint32_t wtotal = 0, mine = 0;
 #pragma unroll
-    for (uint32_t d = 1; d < 32; d <<= 1) {
-        const uint32_t t = __shfl_up_sync(KSB_FULL, incl, d);
-        if (lane >= d) incl += t;
+    for (uint32_t q = 0; q < kPostPerThread; q++) {
+        const unsigned long long cell = wcell0 + 32u * q + lane;
+        bool f = false;
+        v[q] = 0ull;
+        if (cell < G.cells) {
+            v[q] = G.tri[cell];
+            f = v[q] != 0ull;
+            if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
+        }
+        ball[q] = __ballot_sync(KSB_FULL, f);
+        wtotal += __popc(ball[q]);
+        mine |= (uint32_t)f << q;
     }
-    if (lane == 31) sm[wid] = incl;
+    if (lane == 0) sm[wid] = wtotal;
     __syncthreads();
     uint32_t wbase = 0;
 #pragma unroll
     for (uint32_t i = 0; i < kPostThreads / 32; i++)
         if (i < wid) wbase += sm[i];
-    if (flags == 0) return;
-    unsigned long long out = block_offsets[blockIdx.x] + wbase + (incl - c);
-    // decode (i,j) of the first cell, then walk
-    const unsigned long long g0 = G.base + cell0;
+    if (mine == 0) return;
+    unsigned long long out = block_offsets[blockIdx.x] + wbase;
+    // decode (i,j) of this lane's first cell, then walk 32 cells per step
+    const unsigned long long g0 = G.base + wcell0 + lane;
     uint32_t lo = G.rb, hi = G.rb + G.nrows;  // last row with bandstart <= g0 (rows with an empty band share their start)
     while (hi - lo > 1) {
         const uint32_t mid = (lo + hi) >> 1;
@@ -446,12 +475,19 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
     uint32_t i = lo;
     uint32_t j = __ldg(G.band_lo + i) + (uint32_t)(g0 - __ldg(G.bandstart + i));
     uint32_t jend = __ldg(G.band_hi + i);
+    const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
     for (uint32_t q = 0; q < kPostPerThread; q++) {
-        if (j >= jend && ((flags >> q) != 0u)) {  // next row with a non-empty band (only while flagged cells remain)
-            do { i++; jend = __ldg(G.band_hi + i); j = __ldg(G.band_lo + i); } while (j >= jend);
+        if ((mine >> q) != 0u) {  // only while flagged cells remain for this lane
+            while (j >= jend) {   // into the next row(s): cells of consecutive rows are back to back
+                const uint32_t over = j - jend;
+                i++;
+                jend = __ldg(G.band_hi + i);
+                j = __ldg(G.band_lo + i) + over;
+            }
         }
-        if ((flags >> q) & 1u) {
+        if ((mine >> q) & 1u) {
+            const unsigned long long o = out + __popc(ball[q] & lt);
             float cmin, cavg, cmax;
             containment(v[q], __ldg(totals + i), __ldg(totals + j), cmin, cavg, cmax);
             uint4 a, b;
@@ -463,13 +499,13 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
             b.y = __float_as_uint(cavg);
             b.z = __float_as_uint(cmax);
             b.w = 0;
-            uint4* dst = reinterpret_cast<uint4*>(records + out);
+            uint4* dst = reinterpret_cast<uint4*>(records + o);
             dst[0] = a;
             dst[1] = b;
-            pairs[out] = ((unsigned long long)i << 32) | j;
-            out++;
+            pairs[o] = ((unsigned long long)i << 32) | j;
         }
-        j++;
+        out += __popc(ball[q]);
+        j += 32;
     }
 }
 

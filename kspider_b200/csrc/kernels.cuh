@@ -51,16 +51,19 @@ struct K1Params {
 struct LaunchCfg {
     int sms;
     cudaStream_t stream;
+    int k1_ctas = 8;  // K1 CTAs (256 threads) per SM; fewer when K4 runs beside it and needs its slot
 };
 
 // launchers (return cudaError_t of the launch)
-cudaError_t launch_k1_small(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
-                            const LaunchCfg& lc);
+// warp tasks [task_begin, task_end) of the K1 task list
+// member sections hold u16 or u32 compact sample ids (IndexDesc::member_bits)
+cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
+                            const LaunchCfg& lc, unsigned long long task_begin, unsigned long long task_end);
 cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned long long* mid_off,
-                          const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                          const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
                           const TriGeom& g, const LaunchCfg& lc);
-cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const uint32_t* zero_members,
-                            uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc);
+cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off, const void* zero_members,
+                            uint32_t member_bits, uint32_t* touched_bits, const TriGeom& g, const LaunchCfg& lc);
 
 // K3 (spill): chunk buffer the emit kernels append (key = row << shift | column, u32 weight) to
 struct SpillBuf {
@@ -69,14 +72,14 @@ struct SpillBuf {
     unsigned long long* cursor;  // entries appended so far
     uint32_t shift;              // bits of a column index
 };
-cudaError_t launch_k1_spill(const K1Params& p, const uint32_t* members, const uint32_t* weights, const TriGeom& g,
+cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
                             const SpillBuf& sb, unsigned long long task_begin, unsigned long long task_end,
                             const LaunchCfg& lc);
 cudaError_t launch_k2_spill(const MidItem* items, uint64_t item_begin, uint64_t item_end, const unsigned long long* mid_off,
-                            const uint32_t* mid_sizes, const uint32_t* mid_members, const uint32_t* mid_weights,
+                            const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
                             const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
-cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const uint32_t* members,
-                               const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
+cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
+                               uint32_t member_bits, const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
 
 cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
                              const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
@@ -118,8 +121,9 @@ struct GramWinDev {
     uint32_t width;               // samples (multiple of kGramTile)
     uint32_t tiles;               // width / kGramTile
     uint32_t k0;                  // first K-block of the window in the chunk's weight planes
-    uint32_t pad;
+    uint32_t u0;                  // first bitmap-build unit (K-block x segment of kGramSeg samples) of the window
 };
+constexpr uint32_t kGramSeg = 2048;  // samples per bitmap-build unit: 32 KB of shared memory
 struct GramItem {
     uint32_t win;                 // index into the chunk's window list
     uint16_t ti, tj0;             // row tile, first of the (up to NB) column tiles
@@ -137,10 +141,9 @@ struct GramParams {
     uint32_t* counter;            // work counter, zeroed before the launch
 };
 uint32_t gram_cols_per_item(int planes);
-cudaError_t launch_kb_build(const unsigned long long* gram_off, const uint32_t* gram_members,
-                            const uint32_t* gram_weights, uint64_t c_begin, uint64_t n, const GramWinDev* wins,
-                            uint32_t n_wins, uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq,
-                            const LaunchCfg& lc);
+cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
+                            const uint32_t* gram_weights, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
+                            uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 
 // red micro-benchmark

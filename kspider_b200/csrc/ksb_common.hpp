@@ -94,7 +94,7 @@ struct IndexDesc {
     uint64_t off_band_lo;       // u32[N]   first column row i is ever paired with
     uint64_t off_band_hi;       // u32[N]   one past the last such column (lo = hi = 0: row never touched)
     uint64_t band_cells;        // sum of (hi - lo): cells of the banded accumulator
-    uint64_t off_small_members; // u32[n_small_members]
+    uint64_t off_small_members; // member_bits/8 x [n_small_members]
     uint64_t off_small_weights; // u32[n_small_colors]
     uint64_t off_mid_offsets;   // u64[n_mid_colors+1]  start of each colour in the mid-members section,
                                 //                       always a multiple of 4 elements (16 B: TMA bulk copies)
@@ -116,6 +116,8 @@ struct IndexDesc {
     uint64_t off_gram_wins;     // GramWin[n_gram_wins], ascending (x0, width); colours are grouped by window
     uint64_t n_gram_wins;
     uint64_t n_small_updates;   // pair-updates of the K1 colours
+    uint64_t member_bits;       // 16 or 32: width of the compact sample ids in the four member sections
+                                // (u16 when N <= 65536: halves the blob, i.e. the H2D / broadcast time)
     uint64_t payload_bytes;
 };
 constexpr uint64_t kIndexMagic = 0x33305844494253ULL | (0x4BULL << 56);
