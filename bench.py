@@ -220,17 +220,30 @@ def main_b200(args):
         t = torch.from_numpy(shape).to(device)
         dist.broadcast(t, 0)
         shape = t.cpu().numpy()
-        desc, d_payload = kd.broadcast_blob(idx, device, 0)
+        # every rank receives the row-block shard of its own rows (cut on the host once, part of loading)
+        shards = kd.make_shards(idx, world, host_threads=min(32, os.cpu_count() or 1)) if rank == 0 else None
+        desc, d_payload = kd.scatter_shards(shards, device, 0)
         dev = kd.adopt(desc, d_payload, dense_budget_bytes=budget, spill=args.spill)
+        payload_bytes_rank = torch.tensor([d_payload.numel()], dtype=torch.int64, device=device)
+        dist.all_reduce(payload_bytes_rank)
+        shape[7] = int(payload_bytes_rank.cpu())  # bytes moved host -> GPUs per e2e step: all shards
     else:
         dev = idx.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
     N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram = (int(v) for v in shape)
 
+    host_ms = {"accumulate+post": 0.0, "cluster+merge": 0.0}
+
     def step():
+        t0 = time.perf_counter()
         res = dev.run_all_passes(want_records=False)
-        labels, ne = res.cluster(N, "max_cont", args.cutoff)
+        t1 = time.perf_counter()
         if world > 1:
-            labels = kd.merge_labels(labels, device)
+            labels, ne = kd.cluster_merged(res, N, "max_cont", args.cutoff, device, to_host=True)  # the step's result reaches the host
+        else:
+            labels, ne = res.cluster(N, "max_cont", args.cutoff)
+        t2 = time.perf_counter()
+        host_ms["accumulate+post"] += (t1 - t0) * 1e3
+        host_ms["cluster+merge"] += (t2 - t1) * 1e3
         launches = res.info.gpu_launches
         rows = res.info.n_rows
         res.close()
@@ -251,6 +264,7 @@ def main_b200(args):
     before = {k: getattr(t_before, k) for k in ("zero_ms", "small_ms", "mid_ms", "zero_touch_ms", "gram_ms", "spill_emit_ms", "spill_sort_ms", "accumulate_ms", "post_ms")}
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    host_ms.update({k: 0.0 for k in host_ms})
     ev0.record()
     w0 = time.perf_counter()
     launches = 0
@@ -286,12 +300,13 @@ def main_b200(args):
             if world == 1:
                 res = idx.pairwise(device=local_rank, want_records=True, dense_budget_bytes=budget, spill=args.spill)
             else:
-                desc2, pay2 = kd.broadcast_blob(idx, device, 0)
+                desc2, pay2 = kd.scatter_shards(shards, device, 0)
                 dv = kd.adopt(desc2, pay2, dense_budget_bytes=budget, spill=args.spill)
                 res = dv.run_all_passes(want_records=True)
-            labels, _ = res.cluster(N, "max_cont", args.cutoff)
             if world > 1:
-                labels = kd.merge_labels(labels, device)
+                labels, _ = kd.cluster_merged(res, N, "max_cont", args.cutoff, device, to_host=True)
+            else:
+                labels, _ = res.cluster(N, "max_cont", args.cutoff)
             d2h = res.info.n_rows * 32 + 4 * N
             tt = res.info.t
             e2e_lib.update({k: round(float(getattr(tt, k)), 3) for k in ("h2d_ms", "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms")})
@@ -391,7 +406,7 @@ def main_b200(args):
                        "members": M, "pair_updates": U, "rows": rows, "edges": int(n_edges), "cutoff": args.cutoff,
                        "parallelism": f"row-blocks x{world}", "passes": dev.n_passes, "spill": bool(dev.is_spill),
                        "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the triangle block is cleared every step)"},
-            "phases_ms": phase, "wall_ms_per_step": wall_ms / args.steps,
+            "phases_ms": phase, "host_ms_per_step": {k: v / args.steps for k, v in host_ms.items()}, "wall_ms_per_step": wall_ms / args.steps,
             "timer": "torch.cuda.Event pair on the current stream around the K steps (every library call is stream-synchronous); phases: library CUDA events on the launching stream",
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(round(per_step_launches * args.steps)),
             "roofline": roofline, "red_roofline": red, "cpu_baseline": cpu}

@@ -155,6 +155,14 @@ int ksb_index_row_cuts(const ksb_index* ix, int world, uint64_t* cuts_out);
 /* the same from a (descriptor, HOST payload) pair, for ranks that received the blob by broadcast */
 int ksb_blob_row_cuts(const void* descriptor, uint64_t descriptor_bytes, const void* payload, uint64_t payload_bytes,
                       int world, uint64_t* cuts_out);
+/* Row-block shard of an index for rank `rank` of `world` (same cuts as ksb_index_row_cuts): a new,
+ * smaller index holding only the colours that have a member in the rank's rows, each cut down to its
+ * members >= the first owned row, re-binned for the kernels.  A device created from it owns exactly
+ * those rows (opts.rank / opts.world are ignored) and produces the same block, bit for bit, as the
+ * whole index with opts.rank / opts.world -- but its per-step work is proportional to the rank's
+ * share of the pair-updates instead of the whole colour table.  This is what each GPU of a
+ * multi-GPU run receives. */
+int ksb_index_shard(const ksb_index* ix, int rank, int world, int host_threads, ksb_index** out);
 int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path);
 void ksb_index_free(ksb_index* ix);
 
@@ -207,6 +215,9 @@ int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* la
 /* same with the threshold already in percent, i.e. the reference's Clusters(cut_off_threshold=...)
  * constructor argument (ks_clustering.py:22,157: float(cutoff) * 100) */
 int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges);
+/* same, labels left in DEVICE memory of the result's device (d_labels_out[N]): the multi-GPU path
+ * all-gathers and merges them there (ksb_cluster_merge_device) without a host round trip */
+int ksb_cluster_pct_device(const ksb_result* r, int dist_col, double cut_pct, uint32_t* d_labels_out, uint64_t* n_edges);
 float ksb_threshold_float_pct(double cut_pct);
 int ksb_cluster_merge(uint64_t n, const uint32_t* labels_a, const uint32_t* labels_b, uint32_t* labels_out);
 /* same on DEVICE buffers of the current device (e.g. the output of an NCCL all-gather):

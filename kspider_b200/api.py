@@ -100,6 +100,13 @@ class Index:
         check(lib().ksb_index_row_cuts(self._h, int(world), cuts.ctypes.data))
         return cuts
 
+    def shard(self, rank: int, world: int, host_threads: int = 1) -> "Index":
+        """Row-block shard for `rank` of `world`: only the colours (cut down to the members) that the
+        owner of that row block needs, re-binned (ksb_index_shard).  A Device made from it owns those rows."""
+        h = C.c_void_p()
+        check(lib().ksb_index_shard(self._h, int(rank), int(world), int(host_threads), C.byref(h)))
+        return Index(h)
+
     def write_seq_to_kmers(self, path: str) -> None:
         check(lib().ksb_write_seq_to_kmers(self._h, str(path).encode()))
 
@@ -234,6 +241,13 @@ class Result:
         else:
             check(lib().ksb_cluster_pct(self._h, DIST_COL[dist_type], float(cut_pct), labels.ctypes.data, C.byref(ne)))
         return labels, ne.value
+
+    def cluster_into(self, d_labels_ptr: int, dist_type: str = "max_cont", cutoff01: float = 0.0) -> int:
+        """Same as cluster(), labels written to DEVICE memory at `d_labels_ptr` (uint32[N] on this result's
+        device; e.g. a torch tensor's data_ptr()).  Returns the number of kept edges."""
+        ne = C.c_uint64()
+        check(lib().ksb_cluster_pct_device(self._h, DIST_COL[dist_type], float(cutoff01) * 100.0, C.c_void_p(d_labels_ptr), C.byref(ne)))
+        return ne.value
 
     def close(self) -> None:
         if self._h:

@@ -68,6 +68,7 @@ _PROTOS = {
     "ksb_index_row_cuts": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "ksb_index_bands": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ksb_blob_row_cuts": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]),
+    "ksb_index_shard": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
     "ksb_write_seq_to_kmers": (C.c_int, [C.c_void_p, C.c_char_p]),
     "ksb_index_free": (None, [C.c_void_p]),
     "ksb_upload": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_void_p)]),
@@ -91,6 +92,7 @@ _PROTOS = {
     "ksb_append_tsv": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "ksb_cluster": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_cluster_pct": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "ksb_cluster_pct_device": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_threshold_float_pct": (C.c_float, [C.c_double]),
     "ksb_cluster_merge": (C.c_int, [C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ksb_cluster_merge_device": (C.c_int, [C.c_uint64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),

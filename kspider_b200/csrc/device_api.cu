@@ -209,6 +209,10 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     d->row_begin = cut[d->rank];
     d->row_end = cut[d->rank + 1];
     if (d->rank == W - 1) d->row_end = N;
+    if (d->desc.shard_world) {  // a row-block shard owns the rows it was cut for, whatever opts say
+        d->row_begin = d->desc.shard_rb;
+        d->row_end = d->desc.shard_re;
+    }
     d->owned_cells = rowstart(d, d->row_end) - rowstart(d, d->row_begin);
     d->owned_updates = 0;
     for (uint64_t i = d->row_begin; i < d->row_end; i++) d->owned_updates += row_updates[i];
@@ -532,7 +536,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     const uint64_t waves = (wv && std::atoi(wv) > 0) ? (uint64_t)std::atoi(wv) : 4;
     std::vector<GramWinDev> wins;
     std::vector<GramItem> items;
-    struct Rows { uint32_t tlo, thi; };
+    struct Rows { uint32_t ilo, ihi; };  // owned rows of a window, as offsets inside it
     std::vector<Rows> wrows;
     ksb_gram_chunk cur;
     auto close_chunk = [&]() {
@@ -540,19 +544,20 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         // base items, then K splits so that there are ~`waves` items per SM
         uint64_t base = 0;
         for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++)
-            for (uint32_t ti = wrows[w].tlo; ti < wrows[w].thi; ti++) base += (wins[w].tiles - ti + NB - 1) / NB;
+            for (uint32_t i0 = wrows[w].ilo; i0 < wrows[w].ihi; i0 += kGramTile)
+                base += ((wins[w].width - i0 + kGramTile - 1) / kGramTile + NB - 1) / NB;
         const uint64_t ks = base ? (waves * (uint64_t)d->sms + base - 1) / base : 1;
         cur.item_begin = (uint32_t)items.size();
         for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) {
             const uint32_t kblocks = (wins[w].n + kGramKBlock - 1) / kGramKBlock;
             const uint32_t split = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(ks, kblocks));
-            for (uint32_t ti = wrows[w].tlo; ti < wrows[w].thi; ti++)
-                for (uint32_t tj0 = ti; tj0 < wins[w].tiles; tj0 += NB)
+            for (uint32_t i0 = wrows[w].ilo; i0 < wrows[w].ihi; i0 += kGramTile)
+                for (uint32_t j0 = i0; j0 < wins[w].width; j0 += NB * kGramTile)
                     for (uint32_t sp = 0; sp < split; sp++) {
                         GramItem it;
                         it.win = w - cur.win_begin;
-                        it.ti = (uint16_t)ti;
-                        it.tj0 = (uint16_t)tj0;
+                        it.i0 = (uint16_t)i0;
+                        it.j0 = (uint16_t)j0;
                         it.kb0 = (uint32_t)((uint64_t)kblocks * sp / split);
                         it.kb1 = (uint32_t)((uint64_t)kblocks * (sp + 1) / split);
                         if (it.kb1 > it.kb0) items.push_back(it);
@@ -560,7 +565,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         }
         cur.n_items = (uint32_t)items.size() - cur.item_begin;
         auto cost = [&](const GramItem& it) {
-            return (uint64_t)(it.kb1 - it.kb0) * (1 + std::min<uint32_t>(NB, wins[cur.win_begin + it.win].tiles - it.tj0));
+            return (uint64_t)(it.kb1 - it.kb0) * (1 + std::min<uint32_t>(NB, (wins[cur.win_begin + it.win].width - it.j0 + kGramTile - 1) / kGramTile));
         };
         std::stable_sort(items.begin() + cur.item_begin, items.end(), [&](const GramItem& a, const GramItem& b) { return cost(a) > cost(b); });
         if (cur.n_items) plan.chunks.push_back(cur);
@@ -579,8 +584,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
             continue;
         }
         const uint32_t tiles = w.width / kGramTile;
-        const Rows rows{(uint32_t)(p.rb > x0 ? (p.rb - x0) / kGramTile : 0),
-                        (uint32_t)std::min<uint64_t>(tiles, (p.re - x0 + kGramTile - 1) / kGramTile)};
+        const Rows rows{(uint32_t)(p.rb > x0 ? p.rb - x0 : 0), (uint32_t)(std::min<uint64_t>(p.re, x1) - x0)};
         const uint64_t kb_total = ((uint64_t)w.n + kGramKBlock - 1) / kGramKBlock;
         const uint64_t kb_max = std::max<uint64_t>(1, std::min<uint64_t>(16384, chunk_rows / w.width));
         for (uint64_t kb = 0; kb < kb_total; kb += kb_max) {
@@ -608,7 +612,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     close_chunk();
     uint64_t need_bits = 0, need_wq = 0;
     for (const ksb_gram_chunk& c : plan.chunks) {
-        need_bits = std::max(need_bits, c.bits_rows * 16);
+        need_bits = std::max(need_bits, (c.bits_rows + kGramTile) * 16);  // tiles start at any row: the last may hang over
         need_wq = std::max<uint64_t>(need_wq, (uint64_t)d->g_planes * c.kblocks * kGramKBlock + 256);
     }
     if (!plan.chunks.empty()) {
@@ -1157,8 +1161,20 @@ int ksb_cluster(const ksb_result* r, int dist_col, double cutoff01, uint32_t* la
     return ksb_cluster_pct(r, dist_col, cutoff01 * 100.0, labels_out, n_edges);
 }
 
+static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint32_t* d_labels_out,
+                        uint64_t* n_edges);
 int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges) {
-    if (!r || !labels_out) { set_error("ksb_cluster: null argument"); return KSB_ERR_ARG; }
+    if (!labels_out) { set_error("ksb_cluster: null argument"); return KSB_ERR_ARG; }
+    return cluster_core(r, dist_col, cut_pct, labels_out, nullptr, n_edges);
+}
+int ksb_cluster_pct_device(const ksb_result* r, int dist_col, double cut_pct, uint32_t* d_labels_out, uint64_t* n_edges) {
+    if (!d_labels_out) { set_error("ksb_cluster_pct_device: null argument"); return KSB_ERR_ARG; }
+    return cluster_core(r, dist_col, cut_pct, nullptr, d_labels_out, n_edges);
+}
+// labels land in host memory (labels_out) or stay on the device (d_labels_out, N entries on r's device)
+static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint32_t* d_labels_out,
+                        uint64_t* n_edges) {
+    if (!r) { set_error("ksb_cluster: null argument"); return KSB_ERR_ARG; }
     if (dist_col < 3 || dist_col > 5) { set_error("ksb_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
     int sms = 0;
     const int dev = check_device(r->device, &sms);
@@ -1175,7 +1191,8 @@ int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t*
     int rc = KSB_OK;
     cudaError_t e = cudaSuccess;
     do {
-        if ((e = cudaMallocAsync(&d_parent, 4ull * N, st)) != cudaSuccess) break;
+        if (d_labels_out) d_parent = d_labels_out;
+        else if ((e = cudaMallocAsync(&d_parent, 4ull * N, st)) != cudaSuccess) break;
         if ((e = cudaMallocAsync(&d_edges, 8, st)) != cudaSuccess) break;
         const LaunchCfg lc{sms, st};
         cudaEventRecord(e0, st);
@@ -1187,7 +1204,7 @@ int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t*
         if ((e = launch_k7_compress(d_parent, N, lc)) != cudaSuccess) break;
         cudaEventRecord(e1, st);
         unsigned long long ne = 0;
-        if ((e = cudaMemcpyAsync(labels_out, d_parent, 4ull * N, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+        if (labels_out && (e = cudaMemcpyAsync(labels_out, d_parent, 4ull * N, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
         if ((e = cudaMemcpyAsync(&ne, d_edges, 8, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
         if ((e = cudaStreamSynchronize(st)) != cudaSuccess) break;
         if (n_edges) *n_edges = ne;
@@ -1196,7 +1213,7 @@ int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t*
         rw->info.gpu_launches += 2 + r->seg.size();
     } while (0);
     if (e != cudaSuccess) { set_error("ksb_cluster: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); rc = KSB_ERR_CUDA; }
-    if (d_parent) cudaFreeAsync(d_parent, st);
+    if (d_parent && d_parent != d_labels_out) cudaFreeAsync(d_parent, st);
     if (d_edges) cudaFreeAsync(d_edges, st);
     return rc;
 }

@@ -267,10 +267,9 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
         if (item >= prm.n_items) break;
         const GramItem gi = prm.items[item];
         const GramWinDev win = prm.wins[gi.win];
-        const uint32_t ti = gi.ti, tj0 = gi.tj0;
-        const uint32_t ncol = min(NB, win.tiles - tj0);
+        const uint32_t i0 = gi.i0, j0 = gi.j0;
+        const uint32_t ncol = min(NB, (win.width - j0 + kTile - 1) / kTile);
         const uint32_t kb0 = gi.kb0, kb1 = gi.kb1;
-        const uint32_t i0 = ti * kTile;
 
         if (warp < kProducerWarps) {
             // ---------------- producers: expansion
@@ -341,11 +340,13 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                         for (uint32_t y = 0; y < 16; y++)
                             acc[y] += (unsigned long long)tp[(2 * y + rsel) * 17 + csel] << (8 * p);  // row = 2y + rsel, column = csel
                     }
-                    const uint32_t j = win.x0 + (tj0 + ct) * kTile + c16 * 16u + csel;
+                    const uint32_t jl = j0 + ct * kTile + c16 * 16u + csel;  // tiles may hang over the window's end:
+                    const uint32_t j = win.x0 + jl;                           // those rows / columns hold foreign bits
 #pragma unroll
                     for (uint32_t y = 0; y < 16; y++) {
-                        const uint32_t i = win.x0 + i0 + 32u * lq + 2 * y + rsel;
-                        if (i < j && j < G.n && acc[y] != 0ull) {
+                        const uint32_t il = i0 + 32u * lq + 2 * y + rsel;
+                        const uint32_t i = win.x0 + il;
+                        if (il < jl && jl < win.width && j < G.n && acc[y] != 0ull) {
                             const unsigned long long ra = gram_row_addr(i, G);
                             if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
                         }
@@ -394,7 +395,7 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                     const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.width) * 16ull;
                     mbar_expect_tx(bar, bytes);
                     tma_load_1d(dst, kbase + (unsigned long long)i0 * 16ull, 2048u, bar);
-                    tma_load_1d(dst + 2048u, kbase + (unsigned long long)tj0 * kTile * 16ull, ncol * 2048u, bar);
+                    tma_load_1d(dst + 2048u, kbase + (unsigned long long)j0 * 16ull, ncol * 2048u, bar);
 #pragma unroll
                     for (int p = 0; p < P; p++)
                         tma_load_1d(dst + kWOff + p * 128, prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)(win.k0 + kb) * kKB, 128u, bar);

@@ -705,6 +705,76 @@ static int from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* 
     return build_index(raw, threads, out);
 }
 
+// Row-block shard: walks every colour of the binned blob, keeps those with a member in rows
+// [r0, r1) (as a ROW, i.e. not as the colour's last member), cut down to their members >= r0, and
+// bins the result again.  Sample ids / totals are passed through unchanged so the compaction (and
+// therefore every cell address of the owned rows) is the one of the whole index.
+static int shard_index(const ksb_index* ix, int rank, int world, int threads, ksb_index** out) {
+    const IndexDesc& D = ix->desc;
+    const uint8_t* P = ix->payload;
+    const uint64_t N = D.n_samples;
+    std::vector<uint64_t> cut(world + 1, N);
+    row_cuts(reinterpret_cast<const uint64_t*>(P + D.off_row_updates), N, D.n_updates, world, cut.data());
+    const uint32_t r0 = (uint32_t)cut[rank], r1 = (uint32_t)(rank == world - 1 ? N : cut[rank + 1]);
+    const uint32_t* sids = reinterpret_cast<const uint32_t*>(P + D.off_sample_ids);
+    const uint32_t* totals = reinterpret_cast<const uint32_t*>(P + D.off_totals);
+    const uint64_t MB = D.member_bits / 8;
+    auto member = [&](const uint8_t* sec, uint64_t i) -> uint32_t {
+        return MB == 2 ? reinterpret_cast<const uint16_t*>(sec)[i] : reinterpret_cast<const uint32_t*>(sec)[i];
+    };
+    RawIndex raw;
+    raw.n_colors_file = D.n_colors_file;
+    raw.off.push_back(0);
+    // one colour: sorted compact members sec[b .. b+s)
+    auto take = [&](const uint8_t* sec, uint64_t b, uint64_t s, uint32_t w) {
+        uint64_t lo = 0, hi = s;  // first member >= r0
+        while (lo < hi) { const uint64_t mid = (lo + hi) / 2; if (member(sec, b + mid) < r0) lo = mid + 1; else hi = mid; }
+        if (s - lo < 2 || member(sec, b + lo) >= r1) return;  // no owned row with a later column
+        for (uint64_t i = lo; i < s; i++) raw.members.push_back(sids[member(sec, b + i)]);
+        raw.off.push_back(raw.members.size());
+        raw.weights.push_back(w);
+    };
+    for (uint32_t sz = 2; sz <= kSmallMax; sz++) {
+        const SmallClass& sc = D.cls[sz];
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(P + D.off_small_weights) + sc.weight_off;
+        for (uint64_t c = 0; c < sc.n; c++) take(P + D.off_small_members, sc.member_off + c * sz, sz, w[c]);
+    }
+    {
+        const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_mid_offsets);
+        const uint32_t* szs = reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(P + D.off_mid_weights);
+        for (uint64_t c = 0; c < D.n_mid_colors; c++) take(P + D.off_mid_members, off[c], szs[c], w[c]);
+    }
+    {
+        const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_zero_offsets);
+        for (uint64_t c = 0; c < D.n_zero_colors; c++) take(P + D.off_zero_members, off[c], off[c + 1] - off[c], 0);
+    }
+    {
+        const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_gram_offsets);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
+        for (uint64_t c = 0; c < D.n_gram_colors; c++) take(P + D.off_gram_members, off[c], off[c + 1] - off[c], w[c]);
+    }
+    raw.total_ids.assign(sids, sids + N);
+    raw.total_vals.assign(totals, totals + N);
+    ksb_index* sh = nullptr;
+    const int rc = build_index(raw, threads, &sh);
+    if (rc) return rc;
+    if (sh->desc.n_samples != N) { ksb_index_free(sh); set_error("shard: sample compaction changed"); return KSB_ERR_ARG; }
+    sh->desc.shard_world = (uint64_t)world;
+    sh->desc.shard_rank = (uint64_t)rank;
+    sh->desc.shard_rb = r0;
+    sh->desc.shard_re = r1;
+    // pair-updates this shard applies = those of its rows (the cut colours also hold pairs of later rows)
+    const uint64_t* ru = reinterpret_cast<const uint64_t*>(sh->payload + sh->desc.off_row_updates);
+    uint64_t own = 0;
+    for (uint32_t i = r0; i < r1; i++) own += ru[i];
+    sh->desc.n_updates = own;
+    sh->totals_file_ids = ix->totals_file_ids;
+    sh->totals_file_vals = ix->totals_file_vals;
+    *out = sh;
+    return KSB_OK;
+}
+
 }  // namespace ksb
 
 // ------------------------------------------------------------------------------------------- C-ABI
@@ -744,6 +814,21 @@ int ksb_index_from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_
         return KSB_ERR_NOMEM;
     } catch (const std::exception& e) {
         ksb::set_error("ksb_index_from_csr: %s", e.what());
+        return KSB_ERR_ARG;
+    }
+}
+
+int ksb_index_shard(const ksb_index* ix, int rank, int world, int host_threads, ksb_index** out) {
+    if (!ix || !out || world < 1 || rank < 0 || rank >= world) { ksb::set_error("ksb_index_shard: bad argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    if (ix->desc.shard_world) { ksb::set_error("ksb_index_shard: the index is already a shard"); return KSB_ERR_ARG; }
+    try {
+        return ksb::shard_index(ix, rank, world, host_threads, out);
+    } catch (const std::bad_alloc&) {
+        ksb::set_error("out of host memory");
+        return KSB_ERR_NOMEM;
+    } catch (const std::exception& e) {
+        ksb::set_error("ksb_index_shard: %s", e.what());
         return KSB_ERR_ARG;
     }
 }

@@ -126,7 +126,9 @@ struct GramWinDev {
 constexpr uint32_t kGramSeg = 2048;  // samples per bitmap-build unit: 32 KB of shared memory
 struct GramItem {
     uint32_t win;                 // index into the chunk's window list
-    uint16_t ti, tj0;             // row tile, first of the (up to NB) column tiles
+    uint16_t i0, j0;              // first row of the 128-row tile and first column of its (up to NB) 128-column
+                                  // tiles, as sample offsets inside the window: j0 = i0 + 128 k, i0 starts at the
+                                  // first OWNED row, so a row block never pays for a tile it owns a sliver of
     uint32_t kb0, kb1;            // K-block range inside the window
 };
 struct GramParams {

@@ -118,6 +118,10 @@ struct IndexDesc {
     uint64_t n_small_updates;   // pair-updates of the K1 colours
     uint64_t member_bits;       // 16 or 32: width of the compact sample ids in the four member sections
                                 // (u16 when N <= 65536: halves the blob, i.e. the H2D / broadcast time)
+    // row-block shard (ksb_index_shard): this blob holds only what the owner of triangle rows
+    // [shard_rb, shard_re) needs -- colours with a member in that range, cut down to their members
+    // >= shard_rb.  shard_world == 0: the whole index.
+    uint64_t shard_world, shard_rank, shard_rb, shard_re;
     uint64_t payload_bytes;
 };
 constexpr uint64_t kIndexMagic = 0x33305844494253ULL | (0x4BULL << 56);

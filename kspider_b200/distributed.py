@@ -43,11 +43,82 @@ def broadcast_blob(index: Optional[Index], device: torch.device, src: int = 0) -
     return bytes(d_desc.cpu().numpy().tobytes()), d_payload
 
 
+def make_shards(index: Index, world: int, host_threads: int = 4):
+    """Row-block shards of `index`, one per rank (built on the host, part of loading the index)."""
+    return [index.shard(r, world, host_threads) for r in range(world)]
+
+
+def scatter_shards(shards, device: torch.device, src: int = 0) -> Tuple[bytes, torch.Tensor]:
+    """Rank `src` holds the row-block shards (make_shards); every rank receives ITS shard's
+    (descriptor, payload): host -> GPU of `src` -> peer GPU over NVLink (NCCL send/recv; gloo in the
+    CPU tests).  Unlike broadcast_blob every rank gets only the colours of its own rows, so a step's
+    work is proportional to the rank's share of the pair-updates."""
+    rank, world = dist.get_rank(), dist.get_world_size()
+    head = torch.zeros(2 * world, dtype=torch.int64)
+    if rank == src:
+        assert shards is not None and len(shards) == world
+        descs = [s.descriptor() for s in shards]
+        pays = [torch.from_numpy(s.payload()) for s in shards]
+        for r in range(world):
+            head[2 * r], head[2 * r + 1] = len(descs[r]), pays[r].numel()
+    head = head.to(device)
+    dist.broadcast(head, src)
+    head = head.cpu()
+    n_desc, n_payload = int(head[2 * rank]), int(head[2 * rank + 1])
+    if rank == src:
+        mine = None
+        for r in range(world):
+            d_desc = torch.frombuffer(bytearray(descs[r]), dtype=torch.uint8).to(device)
+            d_pay = pays[r].to(device, non_blocking=False)
+            if r == src:
+                mine = (descs[r], d_pay)
+            else:
+                dist.send(d_desc, r)
+                dist.send(d_pay, r)
+        return mine
+    d_desc = torch.empty(n_desc, dtype=torch.uint8, device=device)
+    d_payload = torch.empty(n_payload, dtype=torch.uint8, device=device)
+    dist.recv(d_desc, src)
+    dist.recv(d_payload, src)
+    return bytes(d_desc.cpu().numpy().tobytes()), d_payload
+
+
 def adopt(desc: bytes, d_payload: torch.Tensor, **opts) -> Device:
     """Device handle of this rank's row block over an already-resident blob (CUDA tensor)."""
     assert d_payload.is_cuda and d_payload.dtype == torch.uint8
     return Device.adopt(desc, d_payload.data_ptr(), d_payload.numel(), keepalive=d_payload,
                         device=d_payload.device.index, rank=dist.get_rank(), world=dist.get_world_size(), **opts)
+
+
+def cluster_merged(result, n_samples: int, dist_type: str, cutoff01: float, device: torch.device, to_host: bool = False):
+    """K6 + K7 on this rank's records with the labels left on the GPU, all-gather of every rank's
+    labels over NVLink, K7 merge kernel: (global labels as a CUDA int32 tensor -- with to_host a numpy view of a
+    pinned buffer that the next call overwrites --, this rank's kept edges).
+    No host round trip between the three."""
+    world = dist.get_world_size()
+    key = (n_samples, world, device.index)
+    buf = _LABEL_BUFFERS.get(key)
+    if buf is None:  # allocated once per shape: a step must not pay for allocator calls
+        buf = (torch.empty(n_samples, dtype=torch.int32, device=device),
+               torch.empty(world * n_samples, dtype=torch.int32, device=device),
+               torch.empty(n_samples, dtype=torch.int32, device=device),
+               torch.empty(n_samples, dtype=torch.int32, pin_memory=True))
+        _LABEL_BUFFERS.clear()
+        _LABEL_BUFFERS[key] = buf
+    mine, allv, out, host = buf
+    n_edges = result.cluster_into(mine.data_ptr(), dist_type, cutoff01)
+    dist.all_gather_into_tensor(allv, mine)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
+                                         C.c_void_p(stream)))
+    if to_host:
+        host.copy_(out, non_blocking=True)
+        torch.cuda.current_stream(device).synchronize()
+        return host.numpy().view(np.uint32), n_edges
+    return out, n_edges
+
+
+_LABEL_BUFFERS = {}
 
 
 def merge_labels(labels: np.ndarray, device: torch.device) -> np.ndarray:

@@ -102,6 +102,21 @@ def _worker(rank: int, world: int, port: int, q) -> None:
         dist.all_gather(lst, upd)
         assert sum(int(t) for t in lst) == total_upd
         assert max(int(t) for t in lst) <= 0.6 * total_upd  # 2 ranks: each near one half
+        # row-block shards: rank 0 cuts the index, every rank receives exactly its own shard
+        shards = kd.make_shards(idx, world, host_threads=2) if rank == 0 else None
+        sdesc, spay = kd.scatter_shards(shards, torch.device("cpu"), 0)
+        sums = torch.zeros(world, dtype=torch.int64)
+        if rank == 0:
+            for r in range(world):
+                sums[r] = int(shards[r].payload().astype(np.int64).sum()) + len(shards[r].descriptor())
+            assert sdesc == shards[0].descriptor()
+        dist.broadcast(sums, 0)
+        assert int(spay.numpy().astype(np.int64).sum()) + len(sdesc) == int(sums[rank])
+        scuts = np.zeros(2, dtype=np.uint64)  # a shard's blob still yields row cuts (world 1 = everything)
+        sp = np.ascontiguousarray(spay.numpy())
+        sbuf = C.create_string_buffer(sdesc, len(sdesc))
+        check(lib().ksb_blob_row_cuts(sbuf, len(sdesc), sp.ctypes.data, sp.size, 1, scuts.ctypes.data))
+        assert scuts[0] == 0 and scuts[1] == n
         dist.barrier()
         dist.destroy_process_group()
         q.put((rank, "ok"))

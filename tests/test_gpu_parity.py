@@ -277,3 +277,47 @@ def test_banded_accumulator_on_clade_structured_index(ksb):
     dev = idx.upload(dense_budget_bytes=8 * 3000, spill="never")
     assert dev.n_passes >= 3
     assert_records_equal(dev.run_all_passes().records(), want)
+
+
+@pytest.mark.parametrize("world", [2, 3, 7])
+def test_row_block_shards_equal_row_blocks(ksb, world):
+    """A device made from rank r's shard produces the same records as the whole index run with
+    rank=r/world, and all shards together are the oracle's result."""
+    csr = random_csr(seed=91, n_samples=400, n_colors=6000, s_lo=1, s_hi=50, big=(80, 200, 399), zero_every=23)
+    idx = ksb.Index.from_csr(**csr, host_threads=2)
+    parts = []
+    for r in range(world):
+        sh = idx.shard(r, world)
+        got = sh.pairwise().records()
+        assert_records_equal(got, idx.pairwise(rank=r, world=world).records())
+        parts.append(got)
+    assert_records_equal(np.concatenate(parts), oracle_records(csr))
+
+
+def test_cluster_labels_left_on_device_and_merged_there(ksb):
+    """ksb_cluster_pct_device + ksb_cluster_merge_device (what the multi-GPU step uses between the
+    NCCL all-gather): same labels as the host-returning calls."""
+    import ctypes as C
+    import torch
+    from kspider_b200.capi import check, lib
+    csr = random_csr(seed=93, n_samples=300, n_colors=3000, s_lo=1, s_hi=12, big=(40,))
+    idx = ksb.Index.from_csr(**csr)
+    n = int(idx.info.n_samples)
+    whole, ne = idx.pairwise().cluster(n, "max_cont", 0.05)
+    parts, dparts, edges = [], [], 0
+    for r in range(3):
+        res = idx.shard(r, 3).pairwise()
+        lab, e1 = res.cluster(n, "max_cont", 0.05)
+        t = torch.empty(n, dtype=torch.int32, device="cuda:0")
+        e2 = res.cluster_into(t.data_ptr(), "max_cont", 0.05)
+        torch.cuda.synchronize()
+        assert e1 == e2 and np.array_equal(t.cpu().numpy().view(np.uint32), lab)
+        parts.append(lab)
+        dparts.append(t)
+        edges += e1
+    assert edges == ne
+    allv = torch.cat(dparts)
+    out = torch.empty(n, dtype=torch.int32, device="cuda:0")
+    check(lib().ksb_cluster_merge_device(n, 3, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    assert canonical_partition(out.cpu().numpy().view(np.uint32)) == canonical_partition(whole)

@@ -200,3 +200,41 @@ def test_row_bands_are_tight_and_cover_every_pair(built_lib, oracle_lib):
     wlo[whi == 0] = 0
     assert np.array_equal(lo, wlo) and np.array_equal(hi, whi)
     assert cells == int((whi - wlo).sum()) and cells < n * (n - 1) // 2
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_row_block_shards_hold_exactly_the_needed_colours(built_lib, world):
+    """ksb_index_shard: rank r's shard = colours with a row in [cut[r], cut[r+1]), cut down to their
+    members >= cut[r]; the owned rows keep their bands, and the shards' updates add up to U."""
+    from kspider_b200 import Index
+    from util import random_csr
+    csr = random_csr(seed=77, n_samples=300, n_colors=4000, s_lo=1, s_hi=40, big=(70, 150, 290), zero_every=31)
+    idx = Index.from_csr(**csr, host_threads=2)
+    cuts = idx.row_cuts(world).astype(np.int64)
+    lo, hi, _ = idx.bands()
+    ids = np.unique(np.concatenate([csr["total_ids"], csr["members"]]))
+    off = csr["offsets"].astype(np.int64)
+    total = 0
+    for r in range(world):
+        sh = idx.shard(r, world, host_threads=2)
+        inf = sh.info
+        assert inf.n_samples == idx.info.n_samples and np.array_equal(sh.sample_ids, idx.sample_ids)
+        assert np.array_equal(sh.totals, idx.totals)
+        want_members = want_colors = want_upd = 0
+        for c in range(off.size - 1):
+            m = np.sort(np.searchsorted(ids, csr["members"][off[c]:off[c + 1]]))
+            t = m[m >= cuts[r]]
+            if t.size >= 2 and t[0] < cuts[r + 1]:
+                want_colors += 1
+                want_members += t.size
+                if csr["weights"][c] != 0:
+                    p = np.nonzero(t < cuts[r + 1])[0]
+                    want_upd += int((t.size - 1 - p).sum())
+        assert (inf.n_colors, inf.n_members, inf.n_updates) == (want_colors, want_members, want_upd)
+        slo, shi, _ = sh.bands()
+        a, b = int(cuts[r]), int(cuts[r + 1])
+        assert np.array_equal(slo[a:b], lo[a:b]) and np.array_equal(shi[a:b], hi[a:b])
+        total += inf.n_updates
+        with pytest.raises(Exception):
+            sh.shard(0, 2)
+    assert total == idx.info.n_updates
