@@ -206,7 +206,7 @@ def main_b200(args):
 
     # ---- synthetic index: generated and parsed on rank 0 only, blob broadcast once
     idx = None
-    shape = np.zeros(12, dtype=np.int64)
+    shape = np.zeros(13, dtype=np.int64)
     if rank == 0:
         s = make_workload(args.workload, args)
         idx = Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals,
@@ -214,7 +214,7 @@ def main_b200(args):
         inf = idx.info
         M_small, U_small, C_small = int(inf.n_small_members), int(inf.n_small_updates), int(inf.n_small_colors)
         shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, U_small, M_small, C_small,
-                    inf.payload_bytes, inf.n_gram_colors, inf.gram_planes, inf.n_gram_updates, inf.n_gram_members]
+                    inf.payload_bytes, inf.n_gram_colors, inf.gram_planes, inf.n_gram_updates, inf.n_gram_members, inf.n_gram_macs]
         del s
     if world > 1:
         t = torch.from_numpy(shape).to(device)
@@ -229,7 +229,7 @@ def main_b200(args):
         shape[7] = int(payload_bytes_rank.cpu())  # bytes moved host -> GPUs per e2e step: all shards
     else:
         dev = idx.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
-    N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram = (int(v) for v in shape)
+    N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram, MAC_gram = (int(v) for v in shape)
 
     host_ms = {"accumulate+post": 0.0, "cluster+merge": 0.0}
 
@@ -281,6 +281,18 @@ def main_b200(args):
     phase = {k: (getattr(t_after, k) - before[k]) / args.steps for k in before}
     # launches: the result's counter is cumulative over the device handle (+ the cluster kernels of the last step)
     per_step_launches = (dev.info.gpu_launches - l_before) / args.steps + (launches - dev.info.gpu_launches)
+    # roofline leg: the same passes with K4 serialised after K1/K2, so that each kernel's library
+    # timer is that kernel running alone (in the timed steps above K4 runs beside K1/K2 on a 2nd stream)
+    n_alone = 3
+    dev.set_overlap(False)
+    dev.run_all_passes(want_records=False).close()
+    t0 = dev.info.t
+    b0 = {k: getattr(t0, k) for k in before}
+    for _ in range(n_alone):
+        dev.run_all_passes(want_records=False).close()
+    t1 = dev.info.t
+    alone = {k: (getattr(t1, k) - b0[k]) / n_alone for k in before}
+    dev.set_overlap(True)
     ms = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -345,22 +357,28 @@ def main_b200(args):
     own_frac = dev.info.n_updates / U if U else 1.0
     peak_tensor = 2.0 * float(peaks.get("bf16_tflops", 2250.0))  # int8 dense = 2 x bf16 on the same tensor pipe
     gram_roof = None
+    gram_traffic = None
+    try:
+        gram_traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get("k4_gram")
+    except Exception:
+        pass
     if C_gram:
-        # useful int8 ops of the Gram launches of one step: 2 * (owned cells) * colours * byte planes
-        g_ops = 2.0 * dev.info.owned_cells * C_gram * P_gram
-        g_ms = phase["gram_ms"]
+        # int8 ops the Gram launches of one step must evaluate: per window, colours x cells of the window's
+        # upper triangle x byte planes (the loader's n_gram_macs), x 2, x this rank's share of the rows
+        g_ops = 2.0 * MAC_gram * own_frac
+        g_ms = alone["gram_ms"]
         gram_roof = {"bound": "tensor", "kernel": "k4_gram (+kb_build, memsets)", "achieved": g_ops / (g_ms * 1e-3) / 1e12,
                      "peak": peak_tensor, "unit": "TFLOP/s", "frac": g_ops / (g_ms * 1e-3) / 1e12 / peak_tensor,
-                     "traffic": None, "kernel_ms": g_ms, "algorithmic_ops": g_ops, "ops": "u8 x u8 -> s32 multiply-adds x 2",
+                     "traffic": gram_traffic, "kernel_ms": g_ms, "algorithmic_ops": g_ops, "ops": "u8 x u8 -> s32 multiply-adds x 2",
                      "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (burst); no int8 figure in that file",
                      "updates_per_s": U_gram * own_frac / (g_ms * 1e-3) if g_ms > 0 else 0.0,
                      "colors": C_gram, "planes": P_gram}
-    if phase["small_ms"] >= phase["mid_ms"]:
-        kname, k_ms = "k1_small", phase["small_ms"]
+    if alone["small_ms"] >= alone["mid_ms"]:
+        kname, k_ms = "k1_small", alone["small_ms"]
         k_bytes = 16 * U_small * own_frac + 4 * M_small + 4 * C_small
         k_upd = U_small * own_frac
     else:
-        kname, k_ms = "k2_mid", phase["mid_ms"]
+        kname, k_ms = "k2_mid", alone["mid_ms"]
         k_bytes = 16 * (U - U_small - U_gram) * own_frac + 4 * (M - M_small - M_gram) + 12 * (C_ - C_small - C_gram)
         k_upd = (U - U_small - U_gram) * own_frac
     achieved = k_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
@@ -373,7 +391,7 @@ def main_b200(args):
                 "frac": achieved / peak, "traffic": traffic, "kernel_ms": k_ms, "algorithmic_bytes": k_bytes,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650 GB/s",
                 "updates_per_s": k_upd / (k_ms * 1e-3) if k_ms > 0 else 0.0}
-    if gram_roof is not None and phase["gram_ms"] > k_ms:
+    if gram_roof is not None and alone["gram_ms"] > k_ms:
         gram_roof["other"] = roofline       # the atomic kernel's HBM roofline rides along
         roofline = gram_roof
     elif gram_roof is not None:
@@ -406,7 +424,7 @@ def main_b200(args):
                        "members": M, "pair_updates": U, "rows": rows, "edges": int(n_edges), "cutoff": args.cutoff,
                        "parallelism": f"row-blocks x{world}", "passes": dev.n_passes, "spill": bool(dev.is_spill),
                        "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the triangle block is cleared every step)"},
-            "phases_ms": phase, "host_ms_per_step": {k: v / args.steps for k, v in host_ms.items()}, "wall_ms_per_step": wall_ms / args.steps,
+            "phases_ms": phase, "kernels_alone_ms": alone, "host_ms_per_step": {k: v / args.steps for k, v in host_ms.items()}, "wall_ms_per_step": wall_ms / args.steps,
             "timer": "torch.cuda.Event pair on the current stream around the K steps (every library call is stream-synchronous); phases: library CUDA events on the launching stream",
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(round(per_step_launches * args.steps)),
             "roofline": roofline, "red_roofline": red, "cpu_baseline": cpu}

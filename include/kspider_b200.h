@@ -74,6 +74,7 @@ typedef struct ksb_index_info {
     uint64_t n_small_updates;
     uint64_t n_gram_members;
     uint64_t n_gram_windows;   /* sample windows the K4 colours are grouped into */
+    uint64_t n_gram_macs;      /* sum over windows of colours x width(width-1)/2 x planes: u8 MACs K4 must evaluate */
     uint32_t pinned;           /* 1 if the payload lives in cudaMallocHost memory */
     uint32_t reserved;
 } ksb_index_info;
@@ -188,6 +189,10 @@ int ksb_device_set_pass(ksb_device* dev, int pass);
  * pass API above does not apply), and the spill run itself: emission in chunks of at most
  * dense_budget_bytes / 40 updates, sort + reduce per chunk, merge, records in (i,j) order. */
 int ksb_device_is_spill(const ksb_device* dev);
+/* K4 normally runs on a second stream beside K1/K2 (default, or KSPIDER_OVERLAP=0 to disable at
+ * creation).  on = 0 serialises the kernels so that the per-kernel timings of ksb_timings are those of
+ * each kernel running alone (bench.py's roofline leg); results are identical either way. */
+int ksb_device_set_overlap(ksb_device* dev, int on);
 int ksb_device_run_spill(ksb_device* dev, int want_records, ksb_result** out);
 /* owned rows / cells / updates, launches and timings so far */
 int ksb_device_get_info(const ksb_device* dev, ksb_result_info* info);

@@ -155,6 +155,10 @@ class Device:
     def set_pass(self, p: int) -> None:
         check(lib().ksb_device_set_pass(self._h, p))
 
+    def set_overlap(self, on: bool) -> None:
+        """K4 beside K1/K2 on a second stream (default) or one kernel after the other (per-kernel timings)."""
+        check(lib().ksb_device_set_overlap(self._h, 1 if on else 0))
+
     def accumulate(self, stream: int = 0, sync: bool = True) -> None:
         check(lib().ksb_accumulate(self._h, C.c_void_p(stream) if stream else None, 1 if sync else 0))
 

@@ -26,7 +26,7 @@ class IndexInfo(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "n_samples", "n_colors_file", "n_colors", "n_members", "n_updates", "n_small_colors",
         "n_mid_colors", "n_gram_colors", "gram_min_size", "gram_planes", "n_gram_updates", "n_zero_colors", "max_color_size", "payload_bytes", "triangle_cells",
-        "n_small_members", "n_small_updates", "n_gram_members", "n_gram_windows")] + \
+        "n_small_members", "n_small_updates", "n_gram_members", "n_gram_windows", "n_gram_macs")] + \
         [("pinned", C.c_uint32), ("reserved", C.c_uint32)]
 
 
@@ -79,6 +79,7 @@ _PROTOS = {
                                          C.POINTER(C.c_uint64)]),
     "ksb_device_read_triangle": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     "ksb_device_is_spill": (C.c_int, [C.c_void_p]),
+    "ksb_device_set_overlap": (C.c_int, [C.c_void_p, C.c_int]),
     "ksb_device_run_spill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
     "ksb_device_n_passes": (C.c_int, [C.c_void_p]),
     "ksb_device_set_pass": (C.c_int, [C.c_void_p, C.c_int]),

@@ -520,6 +520,12 @@ int ksb_device_set_pass(ksb_device* d, int pass) {
 
 int ksb_device_is_spill(const ksb_device* d) { return d && d->spill ? 1 : 0; }
 
+int ksb_device_set_overlap(ksb_device* d, int on) {
+    if (!d) { set_error("ksb_device_set_overlap: null device"); return KSB_ERR_ARG; }
+    d->overlap = on != 0;
+    return KSB_OK;
+}
+
 // Plans K4 for one dense pass (rows [p.rb, p.re)): windows that intersect the rows are cut into
 // sub-windows of at most 16384 K-blocks (255 * 128 * 16384 < 2^31: an s32 accumulator cannot
 // overflow) whose bitmap fits the chunk budget, sub-windows are packed into chunks (one bitmap
@@ -705,6 +711,37 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         if (grc) return grc;
         KSB_CUDA(cudaEventRecord(d->ev[10], d->stream2));
     }
+    // L2 blocking of the atomic kernels: when the pass's block is far larger than L2 every red costs an
+    // HBM sector read + write-back (27 G reds/s measured on 400 MB against 190 G/s on an L2-resident
+    // block).  K1/K2 are then launched once per sub-block of rows sized to stay in L2: each launch
+    // streams the whole colour list again (cheap: rows outside the sub-block are skipped by warp-uniform
+    // tests) but its reds hit L2.  Used when the updates per streamed member make that a win.
+    std::vector<TriGeom> subs(1, g);
+    {
+        const char* env = std::getenv("KSPIDER_L2_BLOCK_MB");  // 0 = off
+        const uint64_t blk_mb = env ? (uint64_t)std::atoi(env) : 48;
+        const uint64_t atom_upd = D.n_updates - D.n_gram_updates, atom_mem = D.n_members - D.n_gram_members - D.n_zero_members;
+        const uint64_t bytes = 8 * p.cells;
+        if (blk_mb && bytes > 2 * (blk_mb << 20) && atom_mem) {
+            uint64_t n_sub = std::min<uint64_t>(64, (bytes + (blk_mb << 20) - 1) / (blk_mb << 20));
+            const double upd_per_member = (double)atom_upd * ((double)p.updates / (double)std::max<uint64_t>(1, D.n_updates)) / (double)atom_mem;
+            while (n_sub > 1 && upd_per_member < 0.1 * (double)n_sub) n_sub /= 2;
+            if (n_sub > 1) {
+                subs.clear();
+                const uint64_t per = (p.cells + n_sub - 1) / n_sub;
+                uint64_t rb = p.rb;
+                while (rb < p.re) {
+                    uint64_t re = rb + 1;
+                    while (re < p.re && d->bandstart[re + 1] - d->bandstart[rb] <= per) re++;
+                    TriGeom gs = g;
+                    gs.rb = (uint32_t)rb;
+                    gs.nrows = (uint32_t)(re - rb);
+                    subs.push_back(gs);
+                    rb = re;
+                }
+            }
+        }
+    }
     if (p.cells) {
         LaunchCfg lc1 = lc;
         if (has_gram && d->overlap) {  // tuning knob: K4 holds 576 threads and ~37K registers of an SM (measured: no gain from leaving it room, both kernels are issue-bound)
@@ -714,25 +751,29 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         const void* sm_m = P + D.off_small_members;
         const uint32_t mb = (uint32_t)D.member_bits;
         const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(P + D.off_small_weights);
-        if (d->copy_pending) {
-            for (const ksb_device::k1_piece& pc : d->k1_pieces) {
-                KSB_CUDA(cudaStreamWaitEvent(st, pc.ev, 0));
-                KSB_CUDA(launch_k1_small(d->k1, sm_m, mb, sm_w, g, lc1, pc.task_begin, pc.task_end));
-                d->launches++;
+        for (const TriGeom& gs : subs) {
+            if (d->copy_pending) {
+                for (const ksb_device::k1_piece& pc : d->k1_pieces) {
+                    KSB_CUDA(cudaStreamWaitEvent(st, pc.ev, 0));
+                    KSB_CUDA(launch_k1_small(d->k1, sm_m, mb, sm_w, gs, lc1, pc.task_begin, pc.task_end));
+                    d->launches++;
+                }
+            } else {
+                KSB_CUDA(launch_k1_small(d->k1, sm_m, mb, sm_w, gs, lc1, 0ull, d->k1.n_tasks));
+                if (d->k1.n_tasks) d->launches++;
             }
-        } else {
-            KSB_CUDA(launch_k1_small(d->k1, sm_m, mb, sm_w, g, lc1, 0ull, d->k1.n_tasks));
-            if (d->k1.n_tasks) d->launches++;
         }
     }
     KSB_CUDA(cudaEventRecord(d->ev[2], st));
     if (p.cells && D.n_mid_items) {
-        KSB_CUDA(launch_k2_mid(reinterpret_cast<const MidItem*>(P + D.off_mid_items), D.n_mid_items,
-                               reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
-                               reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
-                               P + D.off_mid_members, (uint32_t)D.member_bits,
-                               reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, lc));
-        d->launches++;
+        for (const TriGeom& gs : subs) {
+            KSB_CUDA(launch_k2_mid(reinterpret_cast<const MidItem*>(P + D.off_mid_items), D.n_mid_items,
+                                   reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
+                                   reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
+                                   P + D.off_mid_members, (uint32_t)D.member_bits,
+                                   reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), gs, lc));
+            d->launches++;
+        }
     }
     KSB_CUDA(cudaEventRecord(d->ev[3], st));
     if (p.cells && D.n_zero_colors) {

@@ -412,6 +412,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_gram_members = section(MB * d.n_gram_members);
     d.off_gram_weights = section(4 * d.n_gram_colors);
     d.n_gram_wins = gwins.size();
+    for (const GramWin& w : gwins) d.n_gram_macs += (uint64_t)w.n * ((uint64_t)w.width * (w.width - 1) / 2) * gram_planes;
     d.off_gram_wins = section(sizeof(GramWin) * d.n_gram_wins);
     d.payload_bytes = std::max<uint64_t>(p, 256);
 
@@ -856,6 +857,7 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     info->n_small_updates = d.n_small_updates;
     info->n_gram_members = d.n_gram_members;
     info->n_gram_windows = d.n_gram_wins;
+    info->n_gram_macs = d.n_gram_macs;
     info->pinned = ix->pinned ? 1 : 0;
     return KSB_OK;
 }

@@ -116,6 +116,7 @@ struct IndexDesc {
     uint64_t off_gram_wins;     // GramWin[n_gram_wins], ascending (x0, width); colours are grouped by window
     uint64_t n_gram_wins;
     uint64_t n_small_updates;   // pair-updates of the K1 colours
+    uint64_t n_gram_macs;       // sum over Gram windows of colours x width(width-1)/2 x planes: the u8 MACs K4 must evaluate
     uint64_t member_bits;       // 16 or 32: width of the compact sample ids in the four member sections
                                 // (u16 when N <= 65536: halves the blob, i.e. the H2D / broadcast time)
     // row-block shard (ksb_index_shard): this blob holds only what the owner of triangle rows

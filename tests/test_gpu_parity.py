@@ -321,3 +321,20 @@ def test_cluster_labels_left_on_device_and_merged_there(ksb):
     check(lib().ksb_cluster_merge_device(n, 3, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
     torch.cuda.synchronize()
     assert canonical_partition(out.cpu().numpy().view(np.uint32)) == canonical_partition(whole)
+
+
+def test_l2_blocking_of_atomic_kernels(ksb, monkeypatch):
+    """K1/K2 launched once per row sub-block (KSPIDER_L2_BLOCK_MB; on by default only for blocks far
+    larger than L2): same result, also on a row-block shard and with the pipelined upload."""
+    monkeypatch.setenv("KSPIDER_GRAM", "off")
+    csr = random_csr(seed=95, n_samples=900, n_colors=20000, s_lo=2, s_hi=40, big=(100, 300, 899), zero_every=29)
+    want = ksb.Index.from_csr(**csr).pairwise().records()
+    monkeypatch.setenv("KSPIDER_L2_BLOCK_MB", "1")
+    idx = ksb.Index.from_csr(**csr)
+    dev = idx.upload()
+    got = dev.run_all_passes().records()
+    assert dev.info.gpu_launches >= 6  # several K1 + K2 launches
+    assert_records_equal(got, want)
+    assert_records_equal(idx.pairwise().records(), want)
+    parts = [idx.shard(r, 2).pairwise().records() for r in range(2)]
+    assert_records_equal(np.concatenate(parts), want)
