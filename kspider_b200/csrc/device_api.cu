@@ -95,7 +95,7 @@ struct ksb_device {
 
 struct ksb_segment {
     ksb_record* d_records = nullptr;
-    unsigned long long* d_pairs = nullptr;
+    unsigned long long* d_pairs = nullptr;  // [n] (i << 32 | j) compact indices, followed by float cmax[n] (K6's default column)
     uint64_t n = 0;
 };
 
@@ -718,14 +718,17 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     // tests) but its reds hit L2.  Used when the updates per streamed member make that a win.
     std::vector<TriGeom> subs(1, g);
     {
-        const char* env = std::getenv("KSPIDER_L2_BLOCK_MB");  // 0 = off
+        const char* env = std::getenv("KSPIDER_L2_BLOCK_MB");  // 0 = off; set = forced (no gain/cost rule)
         const uint64_t blk_mb = env ? (uint64_t)std::atoi(env) : 48;
         const uint64_t atom_upd = D.n_updates - D.n_gram_updates, atom_mem = D.n_members - D.n_gram_members - D.n_zero_members;
         const uint64_t bytes = 8 * p.cells;
         if (blk_mb && bytes > 2 * (blk_mb << 20) && atom_mem) {
             uint64_t n_sub = std::min<uint64_t>(64, (bytes + (blk_mb << 20) - 1) / (blk_mb << 20));
-            const double upd_per_member = (double)atom_upd * ((double)p.updates / (double)std::max<uint64_t>(1, D.n_updates)) / (double)atom_mem;
-            while (n_sub > 1 && upd_per_member < 0.1 * (double)n_sub) n_sub /= 2;
+            // gain: the pass's atomic updates at the L2 rate instead of the HBM rate (1/27G - 1/190G s each);
+            // cost: every extra launch streams the atomic colours again (~2.8 ps per member) + ~8 us of launches
+            const double upd = (double)atom_upd * ((double)p.updates / (double)std::max<uint64_t>(1, D.n_updates));
+            const double gain = upd * 32e-12;
+            while (!env && n_sub > 1 && gain < 2.0 * (double)(n_sub - 1) * (8e-6 + (double)atom_mem * 2.8e-12)) n_sub /= 2;
             if (n_sub > 1) {
                 subs.clear();
                 const uint64_t per = (p.cells + n_sub - 1) / n_sub;
@@ -895,13 +898,13 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
         n_rows = total;
         if (n_rows) {
             KSB_CUDA_R(cudaMallocAsync(&seg.d_records, sizeof(ksb_record) * n_rows, d->stream));
-            cudaError_t e = cudaMallocAsync(&seg.d_pairs, 8 * n_rows, d->stream);
+            cudaError_t e = cudaMallocAsync(&seg.d_pairs, 12 * n_rows, d->stream);
             if (e != cudaSuccess) { cudaFreeAsync(seg.d_records, d->stream); set_error("cudaMalloc pairs: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
             seg.n = n_rows;
             r->seg.push_back(seg);
             const uint8_t* P = d->d_payload;
             KSB_CUDA_R(launch_k5_emit(g, d->d_touched, offsets, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals),
-                                      reinterpret_cast<const uint32_t*>(P + d->desc.off_sample_ids), seg.d_records, seg.d_pairs, lc));
+                                      reinterpret_cast<const uint32_t*>(P + d->desc.off_sample_ids), seg.d_records, seg.d_pairs, reinterpret_cast<float*>(seg.d_pairs + n_rows), lc));
             d->launches++;
         }
     }
@@ -1078,11 +1081,11 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
     SP(cudaEventRecord(e0, st));
     if (acc_n) {
         SP(cudaMallocAsync(&seg.d_records, sizeof(ksb_record) * acc_n, st));
-        SP(cudaMallocAsync(&seg.d_pairs, 8 * acc_n, st));
+        SP(cudaMallocAsync(&seg.d_pairs, 12 * acc_n, st));
         seg.n = acc_n;
         r->seg.push_back(seg);
         SP(launch_k5_sparse(acc_k, acc_s, acc_n, shift, reinterpret_cast<const uint32_t*>(P + D.off_totals),
-                            reinterpret_cast<const uint32_t*>(P + D.off_sample_ids), seg.d_records, seg.d_pairs, lc));
+                            reinterpret_cast<const uint32_t*>(P + D.off_sample_ids), seg.d_records, seg.d_pairs, reinterpret_cast<float*>(seg.d_pairs + acc_n), lc));
         d->launches++;
         if (r->have_host) {
             uint64_t got = sizeof(ksb_record) * acc_n;
@@ -1176,6 +1179,11 @@ float ksb_threshold_float(double cutoff01) { return ksb_threshold_float_pct(cuto
 
 // cut = the reference's cut_off_threshold, already in percent (= float(cutoff) * 100)
 float ksb_threshold_float_pct(double cut) {
+    static thread_local double last_cut = 0.0;   // the search below formats ~31 floats: keep the last answer
+    static thread_local float last_val = 0.0f;
+    static thread_local bool have_last = false;
+    if (have_last && std::memcmp(&last_cut, &cut, sizeof cut) == 0) return last_val;
+    auto remember = [&](float v) { last_cut = cut; last_val = v; have_last = true; return v; };
     auto kept = [&](uint32_t bits) {
         float c;
         std::memcpy(&c, &bits, 4);
@@ -1186,15 +1194,15 @@ float ksb_threshold_float_pct(double cut) {
         return !(distance < cut);
     };
     uint32_t lo = 0, hi = 0x7F800000u;  // +0 .. +inf
-    if (kept(lo)) return 0.0f;
-    if (!kept(hi)) return std::nanf("");  // cutoff above +inf: nothing but NaN rows survives
+    if (kept(lo)) return remember(0.0f);
+    if (!kept(hi)) return remember(std::nanf(""));  // cutoff above +inf: nothing but NaN rows survives
     while (hi - lo > 1) {  // invariant: !kept(lo), kept(hi)
         const uint32_t mid = lo + (hi - lo) / 2;
         if (kept(mid)) hi = mid; else lo = mid;
     }
     float c;
     std::memcpy(&c, &hi, 4);
-    return c;
+    return remember(c);
 }
 
 int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges);
@@ -1240,7 +1248,7 @@ static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint3
         if ((e = cudaMemsetAsync(d_edges, 0, 8, st)) != cudaSuccess) break;
         if ((e = launch_k7_init(d_parent, N, lc)) != cudaSuccess) break;
         for (const ksb_segment& s : r->seg)
-            if ((e = launch_k67_union(s.d_records, s.d_pairs, s.n, dist_col, cstar, d_parent, d_edges, lc)) != cudaSuccess) break;
+            if ((e = launch_k67_union(s.d_records, s.d_pairs, dist_col == 5 ? reinterpret_cast<const float*>(s.d_pairs + s.n) : nullptr, s.n, dist_col, cstar, d_parent, d_edges, lc)) != cudaSuccess) break;
         if (e != cudaSuccess) break;
         if ((e = launch_k7_compress(d_parent, N, lc)) != cudaSuccess) break;
         cudaEventRecord(e1, st);

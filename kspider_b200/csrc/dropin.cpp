@@ -46,11 +46,18 @@ void pairwise(std::string index_prefix, int user_threads) {
     auto work = [&](int g) {
         ksb_opts o{};
         o.device = dev0 + g;
-        o.rank = g;
-        o.world = gpus;
         o.want_records = 1;
         o.dense_budget_bytes = (uint64_t)(budget_gb * 1e9);
-        rcs[g] = ksb_pairwise(ix, &o, &res[g]);
+        if (gpus == 1) {
+            rcs[g] = ksb_pairwise(ix, &o, &res[g]);
+        } else {
+            // every GPU gets the row-block shard of its own rows (only its colours, cut down and
+            // re-binned) over its own PCIe link; owned cells are disjoint, nothing is reduced
+            ksb_index* sh = nullptr;
+            rcs[g] = ksb_index_shard(ix, g, gpus, std::max(1, threads / gpus), &sh);
+            if (rcs[g] == KSB_OK) rcs[g] = ksb_pairwise(sh, &o, &res[g]);
+            ksb_index_free(sh);
+        }
         if (rcs[g] != KSB_OK) errs[g] = ksb_last_error();
     };
     if (gpus == 1) work(0);

@@ -436,7 +436,8 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
                                                         const uint32_t* __restrict__ totals,
                                                         const uint32_t* __restrict__ sample_ids,
                                                         ksb_record* __restrict__ records,
-                                                        unsigned long long* __restrict__ pairs) {
+                                                        unsigned long long* __restrict__ pairs,
+                                                        float* __restrict__ cmax_out) {
     __shared__ uint32_t sm[kPostThreads / 32];
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
     const unsigned long long wcell0 = (unsigned long long)blockIdx.x * kPostChunk + wid * (32u * kPostPerThread);
@@ -503,6 +504,7 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
             dst[0] = a;
             dst[1] = b;
             pairs[o] = ((unsigned long long)i << 32) | j;
+            cmax_out[o] = cmax;  // the default clustering column, as a dense array for K6
         }
         out += __popc(ball[q]);
         j += 32;
@@ -519,11 +521,11 @@ cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsi
 
 cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const unsigned long long* block_offsets,
                            const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
-                           unsigned long long* pairs, const LaunchCfg& lc) {
+                           unsigned long long* pairs, float* cmax, const LaunchCfg& lc) {
     const uint64_t nb = post_blocks(g.cells);
     if (nb == 0) return cudaSuccess;
     k5_emit<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_offsets, totals, sample_ids, records,
-                                                         pairs);
+                                                         pairs, cmax);
     return cudaGetLastError();
 }
 
@@ -532,7 +534,7 @@ __global__ void __launch_bounds__(256) k5_sparse(const unsigned long long* __res
                                                  const unsigned long long* __restrict__ sums, unsigned long long n,
                                                  uint32_t shift, const uint32_t* __restrict__ totals,
                                                  const uint32_t* __restrict__ sample_ids, ksb_record* __restrict__ records,
-                                                 unsigned long long* __restrict__ pairs) {
+                                                 unsigned long long* __restrict__ pairs, float* __restrict__ cmax_out) {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
         const unsigned long long k = keys[r], v = sums[r];
@@ -552,17 +554,18 @@ __global__ void __launch_bounds__(256) k5_sparse(const unsigned long long* __res
         dst[0] = a;
         dst[1] = b;
         pairs[r] = ((unsigned long long)i << 32) | j;
+        cmax_out[r] = cmax;
     }
 }
 
 cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
                              const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
-                             unsigned long long* pairs, const LaunchCfg& lc) {
+                             unsigned long long* pairs, float* cmax, const LaunchCfg& lc) {
     if (n == 0) return cudaSuccess;
     unsigned long long ctas = (n + 255) / 256;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k5_sparse<<<(unsigned)ctas, 256, 0, lc.stream>>>(keys, sums, n, shift, totals, sample_ids, records, pairs);
+    k5_sparse<<<(unsigned)ctas, 256, 0, lc.stream>>>(keys, sums, n, shift, totals, sample_ids, records, pairs, cmax);
     return cudaGetLastError();
 }
 
@@ -598,13 +601,13 @@ __device__ __forceinline__ void uf_union(uint32_t* parent, uint32_t a, uint32_t 
 
 __global__ void __launch_bounds__(256) k67_union(const ksb_record* __restrict__ records,
                                                  const unsigned long long* __restrict__ pairs,
+                                                 const float* __restrict__ colvals,  // dense copy of the column, or null
                                                  unsigned long long n_rows, int dist_col, float cstar,
                                                  uint32_t* parent, unsigned long long* n_edges) {
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     uint32_t kept = 0;
     for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += stride) {
-        const float* cols = &records[r].min_containment;
-        const float c = __ldg(cols + (dist_col - 3));
+        const float c = colvals ? __ldg(colvals + r) : __ldg(&records[r].min_containment + (dist_col - 3));
         if (c < cstar) continue;  // NaN is kept, as in `if distance < cutoff: continue`
         const unsigned long long ij = __ldg(pairs + r);
         uf_union(parent, (uint32_t)(ij >> 32), (uint32_t)ij);
@@ -627,13 +630,13 @@ __global__ void k7_compress(uint32_t* parent, uint32_t n) {
     }
 }
 
-cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, uint64_t n_rows, int dist_col,
-                             float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc) {
+cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
+                             int dist_col, float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc) {
     if (n_rows == 0) return cudaSuccess;
     unsigned long long ctas = (n_rows + 255) / 256;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
-    k67_union<<<(unsigned)ctas, 256, 0, lc.stream>>>(records, pairs, n_rows, dist_col, cstar, parent, n_edges);
+    k67_union<<<(unsigned)ctas, 256, 0, lc.stream>>>(records, pairs, colvals, n_rows, dist_col, cstar, parent, n_edges);
     return cudaGetLastError();
 }
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc) {

@@ -83,7 +83,7 @@ cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned 
 
 cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
                              const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
-                             unsigned long long* pairs, const LaunchCfg& lc);
+                             unsigned long long* pairs, float* cmax, const LaunchCfg& lc);
 cudaError_t spill_temp_bytes(uint64_t n, int end_bit, size_t* bytes);
 cudaError_t spill_sort_reduce_chunk(void* tmp, size_t tmp_bytes, const unsigned long long* keys_in,
                                     unsigned long long* keys_sorted, const uint32_t* vals_in, uint32_t* vals_sorted,
@@ -103,11 +103,11 @@ cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsi
                             const LaunchCfg& lc);
 cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const unsigned long long* block_offsets,
                            const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
-                           unsigned long long* pairs, const LaunchCfg& lc);
+                           unsigned long long* pairs, float* cmax, const LaunchCfg& lc);
 
 // K6+K7
-cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, uint64_t n_rows, int dist_col,
-                             float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc);
+cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
+                             int dist_col, float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc);
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 

@@ -338,3 +338,23 @@ def test_l2_blocking_of_atomic_kernels(ksb, monkeypatch):
     assert_records_equal(idx.pairwise().records(), want)
     parts = [idx.shard(r, 2).pairwise().records() for r in range(2)]
     assert_records_equal(np.concatenate(parts), want)
+
+
+@pytest.mark.parametrize("name", ["small_dense", "mid_colors"])
+def test_dropin_on_two_gpus_writes_the_same_tsv(ksb, name, tmp_path, monkeypatch, capfd):
+    """KSPIDER_GPUS=2: each device gets the row-block shard of its rows; the concatenated TSV is the
+    golden one.  Needs two devices (skipped on a single-GPU box)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from kspider_b200 import kSpider_internal
+    prefix = str(tmp_path / name)
+    copy_golden_bins(name, prefix)
+    monkeypatch.setenv("KSPIDER_GPUS", "2")
+    kSpider_internal.pairwise(index_prefix=prefix, user_threads=4)
+    capfd.readouterr()
+    header, want = golden_rows(name)
+    with open(prefix + "_kSpider_pairwise.tsv") as f:
+        assert f.readline() == header
+        got = f.read().splitlines()
+    assert got == want
