@@ -238,6 +238,26 @@ void ksb_result_free(ksb_result* r);
  * C signature: load -> pairwise on KSPIDER_GPUS devices -> both TSVs, same stdout lines. */
 int ksb_dropin_pairwise(const char* index_prefix, int user_threads);
 
+/* ---- colour construction on the GPU ---------------------------------------- */
+/* Replaces the end state of the reference's incremental colouring loop (src/sourmash_indexing.cpp:
+ * 141-277, src/index.cpp:189-331): sample s (s = 0..n_samples-1) lists the u64 hashes
+ * hashes[offsets[s] .. offsets[s+1]); colour = the exact set of samples containing a hash,
+ * count = number of distinct hashes with that set (colorsCount, :262-266), total[s] = entries listed
+ * for s (mins.size(), :205).  One radix sort by hash, segmentation, a sort of the segments by a
+ * signature of their sample lists and an exact grouping, all on `device` (-1 = current).  Members
+ * are sample POSITIONS, ascending; singleton colours are included (the pairwise pass skips them).
+ * Feed the arrays to ksb_index_from_csr / ksb_write_index_files. */
+typedef struct ksb_colors ksb_colors;
+int ksb_colors_build(uint64_t n_samples, const uint64_t* offsets, const uint64_t* hashes, int device, ksb_colors** out);
+uint64_t ksb_colors_count(const ksb_colors* c);
+uint64_t ksb_colors_distinct_hashes(const ksb_colors* c);
+const uint64_t* ksb_colors_offsets(const ksb_colors* c);   /* [count + 1] */
+const uint32_t* ksb_colors_members(const ksb_colors* c);
+const uint64_t* ksb_colors_counts(const ksb_colors* c);    /* [count] */
+const uint64_t* ksb_colors_totals(const ksb_colors* c);    /* [n_samples] */
+float ksb_colors_device_ms(const ksb_colors* c);           /* H2D + sorts + kernels + D2H, CUDA events */
+void ksb_colors_free(ksb_colors* c);
+
 /* ---- text ---------------------------------------------------------------------------------- */
 /* ostream<<float of the reference = "%g": writes at most 16 bytes, returns length (no NUL). */
 int ksb_format_float(float v, char* buf);

@@ -100,6 +100,15 @@ _PROTOS = {
     "ksb_threshold_float": (C.c_float, [C.c_double]),
     "ksb_result_free": (None, [C.c_void_p]),
     "ksb_dropin_pairwise": (C.c_int, [C.c_char_p, C.c_int]),
+    "ksb_colors_build": (C.c_int, [C.c_uint64, C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "ksb_colors_count": (C.c_uint64, [C.c_void_p]),
+    "ksb_colors_distinct_hashes": (C.c_uint64, [C.c_void_p]),
+    "ksb_colors_offsets": (C.c_void_p, [C.c_void_p]),
+    "ksb_colors_members": (C.c_void_p, [C.c_void_p]),
+    "ksb_colors_counts": (C.c_void_p, [C.c_void_p]),
+    "ksb_colors_totals": (C.c_void_p, [C.c_void_p]),
+    "ksb_colors_device_ms": (C.c_float, [C.c_void_p]),
+    "ksb_colors_free": (None, [C.c_void_p]),
     "ksb_format_float": (C.c_int, [C.c_float, C.c_char_p]),
     "ksb_write_index_files": (C.c_int, [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
                                         C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),

@@ -21,3 +21,11 @@ def pairwise(index_prefix: str, user_threads: int = 1) -> None:
     rc = L.ksb_dropin_pairwise(str(index_prefix).encode(), int(user_threads))
     if rc != 0:
         raise KsbError(rc, (L.ksb_last_error() or b"").decode(errors="replace"))
+
+
+def sourmash_sigs_indexing(sigs_dir: str, kSize: int) -> None:
+    """kSpider_internal.sourmash_sigs_indexing(sigs_dir, kSize) (kSpider_internal.i:18,
+    src/sourmash_indexing.cpp:50-327): index file set with prefix basename(sigs_dir) in the working
+    directory; the colour table is built on the GPU (csrc/colors.cu)."""
+    from .indexing import sourmash_sigs_indexing as _impl
+    _impl(str(sigs_dir), int(kSize))
