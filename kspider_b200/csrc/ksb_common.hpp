@@ -36,7 +36,7 @@ constexpr uint32_t kGramMinSize = 16;        // colours smaller than this never 
 // the atomic kernels, and the resulting per-colour crossover s / Npad = sqrt(2 * red / mac) (x sqrt(planes))
 constexpr double kGramMacRate = 1.0e15;
 constexpr double kGramRedRate = 2.5e11;
-constexpr double kGramCrossover = 0.0224;
+constexpr double kGramCrossover = 0.0224;  // cfg2 sweep in profiles/r01p_crossover.txt: flat between 20 and 23 of 1024; 23 keeps the e2e copy order better
 
 // One Gram window: the colours [c0, c0 + n) of the Gram CSR have all their members inside the sample
 // range [x0, x0 + width) (x0 and width multiples of kGramTile), so their contribution is the Gram

@@ -358,3 +358,37 @@ def test_dropin_on_two_gpus_writes_the_same_tsv(ksb, name, tmp_path, monkeypatch
         assert f.readline() == header
         got = f.read().splitlines()
     assert got == want
+
+
+@pytest.mark.parametrize("name", ["cfg3", "cfg4"])
+def test_full_size_properties_clade_structured(ksb, name):
+    """BASELINE configs 3 and 4 at FULL size (10 k / 100 k samples; windowed K4, banded accumulator,
+    u16 resp. u32 members): too many updates for the oracle, so size-independent properties —
+    checksum of checksums, per-sample row sums, sortedness — and, for cfg3, equality with the atomic
+    path (KSPIDER_GRAM=off) on the same index."""
+    from kspider_b200 import synth
+    s = getattr(synth, name)()
+    idx = ksb.Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals, host_threads=8)
+    assert idx.info.n_updates == s.n_updates and idx.info.n_gram_windows > 100
+    rec = idx.pairwise().records()
+    sizes = np.diff(s.offsets).astype(np.int64)
+    w = s.weights.astype(np.int64)
+    assert int(rec["shared_kmers"].astype(np.int64).sum()) == int((w * sizes * (sizes - 1) // 2).sum())
+    n = int(s.total_ids.max()) + 1
+    per = np.bincount(rec["source_1"], weights=rec["shared_kmers"].astype(np.float64), minlength=n) + \
+        np.bincount(rec["source_2"], weights=rec["shared_kmers"].astype(np.float64), minlength=n)
+    want = np.bincount(s.members, weights=np.repeat((w * (sizes - 1)).astype(np.float64), sizes), minlength=n)
+    assert np.array_equal(per.astype(np.int64), want.astype(np.int64))   # sums < 2^53: exact in float64
+    key = rec["source_1"].astype(np.int64) * (1 << 32) + rec["source_2"].astype(np.int64)
+    assert np.all(np.diff(key) > 0)
+    if name == "cfg3":
+        old = os.environ.get("KSPIDER_GRAM")
+        os.environ["KSPIDER_GRAM"] = "off"
+        try:
+            ref = ksb.Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals, host_threads=8).pairwise().records()
+        finally:
+            if old is None:
+                os.environ.pop("KSPIDER_GRAM", None)
+            else:
+                os.environ["KSPIDER_GRAM"] = old
+        assert_records_equal(rec, ref)
