@@ -32,20 +32,19 @@ static int write_records(const ksb_record* rec, uint64_t n, FILE* f, int threads
         int used = 0;
         parallel_chunks(bn, threads, [&](int t, uint64_t b, uint64_t e) {
             std::string& s = bufs[t];
-            s.clear();
-            s.reserve((e - b) * 64);
-            char line[160];
+            s.resize((e - b) * 128);  // a row is at most 3 x 20 digits + 3 x 16 + 6 separators
+            char* const base = &s[0];
+            char* line = base;
             for (uint64_t i = b; i < e; i++) {
                 const ksb_record& r = rec[b0 + i];
-                int p = 0;
-                p += u64_to_dec(r.source_1, line + p); line[p++] = '\t';
-                p += u64_to_dec(r.source_2, line + p); line[p++] = '\t';
-                p += u64_to_dec(r.shared_kmers, line + p); line[p++] = '\t';
-                p += ksb_format_float(r.min_containment, line + p); line[p++] = '\t';
-                p += ksb_format_float(r.avg_containment, line + p); line[p++] = '\t';
-                p += ksb_format_float(r.max_containment, line + p); line[p++] = '\n';
-                s.append(line, (size_t)p);
+                line += u64_to_dec(r.source_1, line); *line++ = '\t';
+                line += u64_to_dec(r.source_2, line); *line++ = '\t';
+                line += u64_to_dec(r.shared_kmers, line); *line++ = '\t';
+                line += ksb_format_float(r.min_containment, line); *line++ = '\t';
+                line += ksb_format_float(r.avg_containment, line); *line++ = '\t';
+                line += ksb_format_float(r.max_containment, line); *line++ = '\n';
             }
+            s.resize((size_t)(line - base));
         });
         used = (int)std::min<uint64_t>((uint64_t)threads, bn ? bn : 1);
         for (int t = 0; t < used; t++)
@@ -80,7 +79,62 @@ extern "C" {
 
 // ostream<<float with default flags == printf("%g") of the promoted value (libstdc++ num_put uses
 // __convert_from_v with "%.*g", precision 6).  nan/inf come out as "nan"/"-nan"/"inf" either way.
+//
+// Fast exact path for 1e-4 <= v < 1e6 (every containment but the tiniest): v = M * 2^E with a 24-bit
+// M and -38 <= E <= -4, so v * 10^p (p <= 10) is the exact integer M * 10^p shifted right by -E and
+// fits 64 bits; the six significant digits are that quotient rounded half-to-even on the exact
+// remainder -- what glibc prints.  Everything else (0 handled inline) goes through snprintf.
 int ksb_format_float(float v, char* buf) {
+    uint32_t bits;
+    std::memcpy(&bits, &v, 4);
+    if (bits == 0) { buf[0] = '0'; return 1; }
+    const uint32_t ex = (bits >> 23) & 0xFFu;
+    if ((bits >> 31) == 0 && ex >= 113 && ex <= 146) {  // 2^-14 <= v < 2^20, positive, normal
+        const uint64_t M = (bits & 0x7FFFFFu) | 0x800000u;
+        const int sh = 150 - (int)ex;                    // v = M >> sh, 4 <= sh <= 37
+        static const uint64_t P10[12] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull,
+                                         100000000ull, 1000000000ull, 10000000000ull, 100000000000ull};
+        // decimal exponent k: 10^k <= v < 10^(k+1); start from the binary exponent, fix up exactly
+        int k = (int)(((int)ex - 127) * 1233) >> 12;     // floor(log10(2^e)) or one less
+        if (k < -5) k = -5;
+        if (k > 5) k = 5;
+        uint64_t q = 0, rem = 0;
+        for (int it = 0; it < 4; it++) {
+            const int p = 5 - k;                         // 0 <= p <= 10
+            if (p < 0 || p > 10) { k = 99; break; }
+            const uint64_t prod = M * P10[p];            // < 2^24 * 10^10 < 2^58
+            q = prod >> sh;
+            rem = prod & ((1ull << sh) - 1ull);
+            if (q < 100000ull) { k--; continue; }
+            if (q >= 1000000ull) { k++; continue; }
+            break;
+        }
+        if (k >= -4 && k <= 5 && q >= 100000ull && q < 1000000ull) {
+            const uint64_t half = 1ull << (sh - 1);
+            if (rem > half || (rem == half && (q & 1ull))) q++;
+            if (q == 1000000ull) { q = 100000ull; k++; }
+            if (k <= 5) {
+                char d[6];
+                for (int i = 5; i >= 0; i--) { d[i] = (char)('0' + q % 10); q /= 10; }
+                int last = 5;                              // last significant digit kept ("%g" strips trailing zeros)
+                while (last > 0 && d[last] == '0') last--;
+                int n = 0;
+                if (k >= 0) {
+                    for (int i = 0; i <= k; i++) buf[n++] = d[i];
+                    if (last > k) {
+                        buf[n++] = '.';
+                        for (int i = k + 1; i <= last; i++) buf[n++] = d[i];
+                    }
+                } else {
+                    buf[n++] = '0';
+                    buf[n++] = '.';
+                    for (int i = 0; i < -k - 1; i++) buf[n++] = '0';
+                    for (int i = 0; i <= last; i++) buf[n++] = d[i];
+                }
+                return n;
+            }
+        }
+    }
     char tmp[32];
     const int n = snprintf(tmp, sizeof tmp, "%g", (double)v);
     std::memcpy(buf, tmp, (size_t)n);

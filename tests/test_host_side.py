@@ -136,6 +136,35 @@ def test_format_float_matches_printf(built_lib):
         assert format_float(float(v)) == po.format_float(float(v)) == ("%g" % float(v) if np.isfinite(v) else po.format_float(float(v)))
 
 
+def test_fast_format_float_is_exact_on_a_sweep(built_lib):
+    """The writer's integer fast path (1e-4 <= v < 1e6) against printf's correctly rounded "%g":
+    random values, ratios of small integers (what containments are), exact half-way cases and every
+    float next to a power of ten."""
+    import ctypes as C
+    buf = C.create_string_buffer(64)
+
+    def fmt(x):
+        n = built_lib.ksb_format_float(C.c_float(x), buf)
+        return buf.raw[:n].decode()
+    rng = np.random.default_rng(1)
+    a, b = rng.integers(1, 5000, 60000), rng.integers(1, 5000, 60000)
+    vals = [rng.random(60000).astype(np.float32),
+            (rng.random(60000) * 10.0 ** rng.integers(-6, 7, 60000)).astype(np.float32),
+            np.minimum(a, b).astype(np.float32) / np.maximum(a, b).astype(np.float32),
+            np.arange(1, 1024, dtype=np.float32) / np.float32(1024),
+            np.array([999999.0, 999999.5, 999999.4, 123456.5, 123455.5, 0.9999995, 0.99999994, 99999.95, 12345.65], np.float32)]
+    edge = []
+    for c in (1e-4, 1e-3, 1e-2, 0.1, 1.0, 10.0, 1e5, 1e6):
+        for toward in (0.0, 1e9):
+            x = np.float32(c)
+            for _ in range(40):
+                edge.append(x)
+                x = np.nextafter(x, np.float32(toward))
+    vals.append(np.array(edge, dtype=np.float32))
+    for v in np.concatenate(vals):
+        assert fmt(float(v)) == "%g" % float(v), float(v)
+
+
 def test_threshold_float_is_the_exact_boundary(built_lib):
     """c* = smallest float32 whose printed text passes `float(text)*100 >= cutoff*100` (ks_clustering.py:97-105)."""
     from kspider_b200 import threshold_float
