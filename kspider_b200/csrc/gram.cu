@@ -107,6 +107,28 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// explicit shared-space accesses with 32-bit addresses: the generic pointers derived from the aligned
+// dynamic-smem base made the compiler emit LD.E / ST.E with 64-bit address arithmetic in the hot loops
+__device__ __forceinline__ void sts128(uint32_t a, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(x), "r"(y), "r"(z), "r"(w));
+}
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint2 lds64(uint32_t a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t x) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(a), "r"(x) : "memory"); }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const TriGeom& g) {
     if (x - g.rb >= g.nrows) return 0ull;
     return (unsigned long long)g.tri + 8ull * (__ldg(g.rowbase + x) - g.base);
@@ -233,6 +255,7 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* ring = smem + kStages * kStageBytes;
+    const uint32_t smem_a = smem_u32(smem), ring_a = smem_a + kStages * kStageBytes;
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(ring + kRing * kSlotBytes);
     // bars: full[kStages], empty[kStages], done, ready[kRing]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 1 + kRing);
@@ -278,15 +301,15 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                 const uint32_t st = it % kStages, slot = it % kRing;
                 mbar_wait(bar_ready0 + 8u * slot, (it / kRing) & 1u);                                      // bits + weights landed
                 if (it >= kStages) mbar_wait(smem_u32(bars + kStages + st), ((it / kStages) - 1u) & 1u);  // stage drained by the MMAs
-                uint8_t* stage = smem + st * kStageBytes;
-                const uint8_t* rs = ring + slot * kSlotBytes;
+                const uint32_t stage = smem_a + st * kStageBytes;
+                const uint32_t rs = ring_a + slot * kSlotBytes;
 #pragma unroll
                 for (uint32_t k = 0; k < 3; k++) {
                     const uint32_t u = tid + kProducers * k;
                     if (u >= nunits) continue;
                     const uint32_t tsel = u >> 8, r = (u & 255u) >> 1, h = u & 1u, sw = r & 7u;
-                    const uint2 bits = *reinterpret_cast<const uint2*>(rs + u * 8u);  // slot rows are (tile, row, half) ordered
-                    uint8_t* drow = stage + (tsel == 0 ? 0u : (P + tsel - 1) * kTileBytes) + (r >> 3) * 1024u + (r & 7u) * 128u;
+                    const uint2 bits = lds64(rs + u * 8u);  // slot rows are (tile, row, half) ordered
+                    const uint32_t drow = stage + (tsel == 0 ? 0u : (P + tsel - 1) * kTileBytes) + (r >> 3) * 1024u + (r & 7u) * 128u;
 #pragma unroll
                     for (uint32_t wd = 0; wd < 2; wd++) {
                         const uint32_t word = wd ? bits.y : bits.x;
@@ -296,16 +319,15 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
 #pragma unroll
                         for (uint32_t c = 0; c < 2; c++) {
                             const uint32_t chunk = (h * 2 + wd) * 2 + c;  // 16-byte chunk inside the 128-byte row
-                            uint8_t* dst = drow + ((chunk ^ sw) << 4);
+                            const uint32_t dst = drow + ((chunk ^ sw) << 4);
                             if (tsel != 0) {
-                                *reinterpret_cast<uint4*>(dst) = make_uint4(s4[4 * c], s4[4 * c + 1], s4[4 * c + 2], s4[4 * c + 3]);
+                                sts128(dst, s4[4 * c], s4[4 * c + 1], s4[4 * c + 2], s4[4 * c + 3]);
                             } else {
 #pragma unroll
                                 for (int p = 0; p < P; p++) {
-                                    const uint4 w = *reinterpret_cast<const uint4*>(rs + kWOff + p * 128 + chunk * 16);
-                                    *reinterpret_cast<uint4*>(dst + p * kTileBytes) =
-                                        make_uint4((s4[4 * c] * 0xFFu) & w.x, (s4[4 * c + 1] * 0xFFu) & w.y,
-                                                   (s4[4 * c + 2] * 0xFFu) & w.z, (s4[4 * c + 3] * 0xFFu) & w.w);
+                                    const uint4 w = lds128(rs + kWOff + p * 128 + chunk * 16);
+                                    sts128(dst + p * kTileBytes, (s4[4 * c] * 0xFFu) & w.x, (s4[4 * c + 1] * 0xFFu) & w.y,
+                                           (s4[4 * c + 2] * 0xFFu) & w.z, (s4[4 * c + 3] * 0xFFu) & w.w);
                                 }
                             }
                         }
@@ -320,7 +342,7 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                 mbar_wait(bar_done, done_phase);
                 done_phase ^= 1u;
                 tc_fence_after();
-                uint32_t* tp = reinterpret_cast<uint32_t*>(smem) + warp * (32 * 17);  // stage memory is idle now
+                const uint32_t tp = smem_a + warp * (32 * 17 * 4);  // stage memory is idle now
                 const uint32_t lq = warp & 3u, wg = warp >> 2;
                 const uint32_t rsel = lane >> 4, csel = lane & 15u;
                 for (uint32_t ch = wg; ch < ncol * 8u; ch += 4) {
@@ -334,11 +356,11 @@ __global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ G
                         tmem_ld16(tmem + ((32u * lq) << 16) + (p * NB + ct) * kTile + c16 * 16u, v);
                         __syncwarp();
 #pragma unroll
-                        for (uint32_t x = 0; x < 16; x++) tp[lane * 17 + x] = v[x];  // row = lane, column = x
+                        for (uint32_t x = 0; x < 16; x++) sts32(tp + (lane * 17 + x) * 4u, v[x]);  // row = lane, column = x
                         __syncwarp();
 #pragma unroll
                         for (uint32_t y = 0; y < 16; y++)
-                            acc[y] += (unsigned long long)tp[(2 * y + rsel) * 17 + csel] << (8 * p);  // row = 2y + rsel, column = csel
+                            acc[y] += (unsigned long long)lds32(tp + ((2 * y + rsel) * 17 + csel) * 4u) << (8 * p);  // row = 2y + rsel, column = csel
                     }
                     const uint32_t jl = j0 + ct * kTile + c16 * 16u + csel;  // tiles may hang over the window's end:
                     const uint32_t j = win.x0 + jl;                           // those rows / columns hold foreign bits
