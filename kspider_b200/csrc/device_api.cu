@@ -197,6 +197,7 @@ static void build_k1(ksb_device* d) {
     }
     p.n_cls = n;
     p.n_tasks = task;
+    p.weight_bits = (uint32_t)d->desc.weight_bits;
 }
 
 // Row block of `rank` (equal weighted pair-updates per rank), then dense passes under the budget.
@@ -247,6 +248,8 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
                          const ksb_opts* opts) {
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
     if (d->desc.member_bits != 16 && d->desc.member_bits != 32) { set_error("descriptor: member_bits must be 16 or 32"); return KSB_ERR_ARG; }
+    if (d->desc.packed_bits != 12 && d->desc.packed_bits != 16 && d->desc.packed_bits != 32) { set_error("descriptor: packed_bits must be 12, 16 or 32"); return KSB_ERR_ARG; }
+    if (d->desc.weight_bits != 8 && d->desc.weight_bits != 16 && d->desc.weight_bits != 32) { set_error("descriptor: weight_bits must be 8, 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
     if (!d->stream) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     if (!d->stream2) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking));
@@ -401,18 +404,18 @@ static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
     KSB_CUDA(cudaEventRecord(d->ev_copy[1], cs));
     KSB_CUDA(copy(D.off_mid_offsets, D.payload_bytes));
     KSB_CUDA(cudaEventRecord(d->ev_copy[2], cs));
-    const uint64_t mbytes = D.member_bits / 8;
-    const uint64_t small_bytes = mbytes * D.n_small_members + 4 * D.n_small_colors;
+    const uint64_t mbits = D.packed_bits, wbytes = D.weight_bits / 8;
+    const uint64_t small_bytes = mbits * D.n_small_members / 8 + wbytes * D.n_small_colors;
     const uint64_t chunk = std::max<uint64_t>(8ull << 20, small_bytes / 6);
     const K1Params& k1 = d->k1;  // classes in descending size = task order
     for (uint32_t c = 0; c < k1.n_cls;) {
         uint32_t e = c;
         uint64_t bytes = 0;
-        while (e < k1.n_cls && (e == c || bytes < chunk)) { bytes += k1.cls[e].n * (mbytes * k1.cls[e].s + 4); e++; }
+        while (e < k1.n_cls && (e == c || bytes < chunk)) { bytes += k1.cls[e].n * (mbits * k1.cls[e].s + 8 * wbytes) / 8; e++; }
         // classes c..e-1 have descending s, i.e. DEscending offsets: their members / weights are one run each
         const K1Class &hi = k1.cls[c], &lo = k1.cls[e - 1];
-        KSB_CUDA(copy(D.off_small_members + mbytes * lo.member_off, D.off_small_members + mbytes * (hi.member_off + hi.n * hi.s)));
-        KSB_CUDA(copy(D.off_small_weights + 4 * lo.weight_off, D.off_small_weights + 4 * (hi.weight_off + hi.n)));
+        KSB_CUDA(copy(D.off_small_members + mbits * lo.member_off / 8, D.off_small_members + (mbits * (hi.member_off + hi.n * hi.s) + 7) / 8 + 1));
+        KSB_CUDA(copy(D.off_small_weights + wbytes * lo.weight_off, D.off_small_weights + wbytes * (hi.weight_off + hi.n)));
         ksb_device::k1_piece pc;
         pc.ev = nullptr;
         KSB_CUDA(cudaEventCreateWithFlags(&pc.ev, cudaEventDisableTiming));
@@ -656,7 +659,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
     const uint8_t* P = d->d_payload;
     const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
     const void* gmem = P + D.off_gram_members;
-    const uint32_t* gw = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
+    const void* gw = P + D.off_gram_weights;
     bool first = true;
     for (const ksb_gram_chunk& c : plan.chunks) {
         GramParams gp;
@@ -671,7 +674,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
         gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
         cudaStream_t sb = first ? st_build : st;
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
-        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.member_bits, gw, gp.wins, gp.n_wins, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
+        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, gp.wins, gp.n_wins, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
                                  LaunchCfg{d->sms, sb}));
         if (sb != st) {
             KSB_CUDA(cudaEventRecord(ev_built, sb));
@@ -752,8 +755,8 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
             lc1.k1_ctas = (kc && std::atoi(kc) > 0 && std::atoi(kc) <= 8) ? std::atoi(kc) : 8;
         }
         const void* sm_m = P + D.off_small_members;
-        const uint32_t mb = (uint32_t)D.member_bits;
-        const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(P + D.off_small_weights);
+        const uint32_t mb = (uint32_t)D.packed_bits;
+        const void* sm_w = P + D.off_small_weights;
         for (const TriGeom& gs : subs) {
             if (d->copy_pending) {
                 for (const ksb_device::k1_piece& pc : d->k1_pieces) {
@@ -1003,8 +1006,8 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
         SP(cudaMemsetAsync(d_cnt, 0, 16, st));
         SP(cudaEventRecord(e0, st));
         if (ch.kind == 0)
-            SP(launch_k1_spill(d->k1, P + D.off_small_members, (uint32_t)D.member_bits,
-                               reinterpret_cast<const uint32_t*>(P + D.off_small_weights), g, sb, ch.b, ch.e, lc));
+            SP(launch_k1_spill(d->k1, P + D.off_small_members, (uint32_t)D.packed_bits,
+                               P + D.off_small_weights, g, sb, ch.b, ch.e, lc));
         else if (ch.kind == 1)
             SP(launch_k2_spill(reinterpret_cast<const MidItem*>(P + D.off_mid_items), ch.b, ch.e,
                                reinterpret_cast<const unsigned long long*>(P + D.off_mid_offsets),
@@ -1013,11 +1016,11 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, sb, lc));
         else if (ch.kind == 2)
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets),
-                                  P + D.off_gram_members, (uint32_t)D.member_bits,
-                                  reinterpret_cast<const uint32_t*>(P + D.off_gram_weights), g, sb, lc));
+                                  P + D.off_gram_members, (uint32_t)D.packed_bits,
+                                  P + D.off_gram_weights, (uint32_t)D.weight_bits, g, sb, lc));
         else
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_zero_offsets),
-                                  P + D.off_zero_members, (uint32_t)D.member_bits, nullptr, g, sb, lc));
+                                  P + D.off_zero_members, (uint32_t)D.member_bits, nullptr, 32u, g, sb, lc));
         SP(cudaEventRecord(e1, st));
         d->launches++;
         unsigned long long n = 0;

@@ -147,7 +147,7 @@ __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const Tr
 template <class MT>
 __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __restrict__ gram_off,
                                                 const MT* __restrict__ gram_members,
-                                                const uint32_t* __restrict__ gram_weights,
+                                                const void* __restrict__ gram_weights, uint32_t weight_bits,
                                                 const GramWinDev* __restrict__ wins, uint32_t n_wins, uint32_t n_units,
                                                 uint32_t kpad, uint32_t planes, uint32_t* __restrict__ bits,
                                                 uint8_t* __restrict__ wq) {
@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
             x[kk] = 0xFFFFFFFFu;
             if (k < kn) {
                 const unsigned long long o = sm_off[k];
-                if (lane < (uint32_t)(sm_off[k + 1] - o)) x[kk] = __ldg(gram_members + o + lane) - w.x0 - s0;
+                if (lane < (uint32_t)(sm_off[k + 1] - o)) x[kk] = ldm<MT>(gram_members, o + lane) - w.x0 - s0;
             }
         }
 #pragma unroll
@@ -197,12 +197,12 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
             const uint32_t bit = 1u << (k & 31u), word = k >> 5;
 #pragma unroll 4
             for (uint32_t a = 32u + lane; a < s; a += 32) {
-                const uint32_t xx = __ldg(gram_members + o + a) - w.x0 - s0;
+                const uint32_t xx = ldm<MT>(gram_members, o + a) - w.x0 - s0;
                 if (xx < slen) atomicOr(sm + 4u * xx + word, bit);
             }
         }
         if (seg == 0 && tid < kKB) {
-            const uint32_t wt = tid < kn ? __ldg(gram_weights + w.c0 + (unsigned long long)kb * kKB + tid) : 0u;
+            const uint32_t wt = tid < kn ? ldw(gram_weights, weight_bits, w.c0 + (unsigned long long)kb * kKB + tid) : 0u;
             for (uint32_t p = 0; p < planes; p++)
                 wq[(unsigned long long)p * kpad + (unsigned long long)(w.k0 + kb) * kKB + tid] = (uint8_t)(wt >> (8u * p));
         }
@@ -214,15 +214,17 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
 }
 
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
-                            const uint32_t* gram_weights, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
+                            const void* gram_weights, uint32_t weight_bits, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {
     if (n_units == 0) return cudaSuccess;
     const unsigned cap = (unsigned)lc.sms * 6u;  // 32 KB of shared memory per CTA
     const unsigned ctas = n_units < cap ? n_units : cap;
-    if (member_bits == 16)
-        kb_build<uint16_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, wins, n_wins, n_units, kpad, planes, bits, wq);
+    if (member_bits == 12)
+        kb_build<P12><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P12*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
+    else if (member_bits == 16)
+        kb_build<uint16_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
     else
-        kb_build<uint32_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint32_t*>(gram_members), gram_weights, wins, n_wins, n_units, kpad, planes, bits, wq);
+        kb_build<uint32_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint32_t*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
     return cudaGetLastError();
 }
 

@@ -390,6 +390,24 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         d.member_bits = (N <= 65536 && !(mb && std::atoi(mb) == 32)) ? 16 : 32;
     }
     const uint64_t MB = d.member_bits / 8;
+    {   // the small-colour and Gram sections (most of the blob): 12-bit packed members when N <= 4096, and
+        // weights as narrow as the largest one allows.  KSPIDER_MEMBER_BITS=16|32 / KSPIDER_WEIGHT_BITS=32 override.
+        const char* mb = std::getenv("KSPIDER_MEMBER_BITS");
+        d.packed_bits = (N <= 4096 && !(mb && (std::atoi(mb) == 16 || std::atoi(mb) == 32))) ? 12 : d.member_bits;
+        std::vector<uint32_t> tw(T, 0);
+        parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+            uint32_t m = 0;
+            for (uint64_t c = b; c < e; c++)
+                if (raw.off[c + 1] - raw.off[c] >= 2) m = std::max(m, raw.weights[c]);
+            tw[t] = m;
+        });
+        uint32_t wmax = 0;
+        for (uint32_t v : tw) wmax = std::max(wmax, v);
+        const char* wb = std::getenv("KSPIDER_WEIGHT_BITS");
+        d.weight_bits = (wb && std::atoi(wb) == 32) ? 32 : (wmax < (1u << 8) ? 8 : (wmax < (1u << 16) ? 16 : 32));
+    }
+    const uint64_t PB = d.packed_bits, WB = d.weight_bits / 8;
+    auto packed_bytes = [&](uint64_t n) { return (PB * n + 7) / 8 + 8; };
 
     // ---- payload layout
     uint64_t p = 0;
@@ -399,8 +417,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_row_updates = section(8 * N);
     d.off_band_lo = section(4 * N);
     d.off_band_hi = section(4 * N);
-    d.off_small_members = section(MB * d.n_small_members);
-    d.off_small_weights = section(4 * d.n_small_colors);
+    d.off_small_members = section(packed_bytes(d.n_small_members));
+    d.off_small_weights = section(WB * d.n_small_colors);
     d.off_mid_offsets = section(8 * (d.n_mid_colors + 1));
     d.off_mid_sizes = section(4 * d.n_mid_colors);
     d.off_mid_members = section(MB * d.n_mid_members_padded + 64);
@@ -409,8 +427,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
     d.off_zero_members = section(MB * d.n_zero_members);
     d.off_gram_offsets = section(8 * (d.n_gram_colors + 1));
-    d.off_gram_members = section(MB * d.n_gram_members);
-    d.off_gram_weights = section(4 * d.n_gram_colors);
+    d.off_gram_members = section(packed_bytes(d.n_gram_members));
+    d.off_gram_weights = section(WB * d.n_gram_colors);
     d.n_gram_wins = gwins.size();
     for (const GramWin& w : gwins) d.n_gram_macs += (uint64_t)w.n * ((uint64_t)w.width * (w.width - 1) / 2) * gram_planes;
     d.off_gram_wins = section(sizeof(GramWin) * d.n_gram_wins);
@@ -433,7 +451,27 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     uint32_t* band_lo = reinterpret_cast<uint32_t*>(P + d.off_band_lo);
     uint32_t* band_hi = reinterpret_cast<uint32_t*>(P + d.off_band_hi);
     uint8_t* small_m = P + d.off_small_members;  // member sections: u16 or u32 elements
-    uint32_t* small_w = reinterpret_cast<uint32_t*>(P + d.off_small_weights);
+    uint8_t* small_w = P + d.off_small_weights;  // weight sections: u8 / u16 / u32 elements
+    auto put_w = [&](uint8_t* sec, uint64_t i, uint32_t w) {
+        if (WB == 1) sec[i] = (uint8_t)w;
+        else if (WB == 2) reinterpret_cast<uint16_t*>(sec)[i] = (uint16_t)w;
+        else reinterpret_cast<uint32_t*>(sec)[i] = w;
+    };
+    // element i of a small / Gram member section.  12-bit packing: element i = bits [12i, 12i+12); its
+    // full byte is stored plainly, its half byte is OR-ed atomically (the other half may belong to a
+    // neighbouring colour that another thread is writing; the payload starts zeroed)
+    auto put_m = [&](uint8_t* sec, uint64_t i, uint32_t v) {
+        if (PB == 32) { reinterpret_cast<uint32_t*>(sec)[i] = v; return; }
+        if (PB == 16) { reinterpret_cast<uint16_t*>(sec)[i] = (uint16_t)v; return; }
+        uint8_t* p = sec + ((3 * i) >> 1);
+        if ((i & 1) == 0) {
+            p[0] = (uint8_t)v;
+            __atomic_fetch_or(p + 1, (uint8_t)(v >> 8), __ATOMIC_RELAXED);
+        } else {
+            __atomic_fetch_or(p, (uint8_t)((v & 0xFu) << 4), __ATOMIC_RELAXED);
+            p[1] = (uint8_t)(v >> 4);
+        }
+    };
     uint64_t* mid_off = reinterpret_cast<uint64_t*>(P + d.off_mid_offsets);
     uint8_t* mid_m = P + d.off_mid_members;
     uint32_t* mid_w = reinterpret_cast<uint32_t*>(P + d.off_mid_weights);
@@ -443,7 +481,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     uint8_t* zero_m = P + d.off_zero_members;
     uint64_t* gram_off = reinterpret_cast<uint64_t*>(P + d.off_gram_offsets);
     uint8_t* gram_m = P + d.off_gram_members;
-    uint32_t* gram_w = reinterpret_cast<uint32_t*>(P + d.off_gram_weights);
+    uint8_t* gram_w = P + d.off_gram_weights;
 
     std::copy(sample_ids.begin(), sample_ids.end(), sids);
     if (!gwins.empty()) std::memcpy(P + d.off_gram_wins, gwins.data(), sizeof(GramWin) * gwins.size());
@@ -477,9 +515,12 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             const uint64_t s = raw.off[c + 1] - raw.off[c];
             const uint32_t* src = &raw.members[raw.off[c]];
             const uint32_t w = raw.weights[c];
-            uint8_t* dst;  // element 0 of this colour in its member section
+            uint8_t* sec;        // member section of this colour and its first element there
+            uint64_t e0;
+            const bool packed = (k == K_GRAM) || (k != K_MID && k != K_ZERO);
             if (k == K_MID) {
-                dst = mid_m + MB * mat[k];
+                sec = mid_m;
+                e0 = mat[k];
                 mid_off[at[k]] = mat[k];
                 mid_sz[at[k]] = (uint32_t)s;
                 mid_w[at[k]] = w;
@@ -491,23 +532,27 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                         mid_items[iat++] = MidItem{(uint32_t)at[k], (uint32_t)b0, (uint32_t)a0, 0};
                 }
             } else if (k == K_ZERO) {
-                dst = zero_m + MB * mat[k];
+                sec = zero_m;
+                e0 = mat[k];
                 zero_off[at[k]] = mat[k];
             } else if (k == K_GRAM) {
-                dst = gram_m + MB * gram_off[gkey[c]];
-                gram_w[gkey[c]] = w;
+                sec = gram_m;
+                e0 = gram_off[gkey[c]];
+                put_w(gram_w, gkey[c], w);
                 gramu += s * (s - 1) / 2;
             } else {
                 const SmallClass& sc = d.cls[k];
-                dst = small_m + MB * (sc.member_off + at[k] * s);
-                small_w[sc.weight_off + at[k]] = w;
+                sec = small_m;
+                e0 = sc.member_off + at[k] * s;
+                put_w(small_w, sc.weight_off + at[k], w);
             }
             cm.resize(s);
             for (uint64_t i = 0; i < s; i++) {
                 const uint32_t ci = compact(src[i]);
                 cm[i] = ci;
-                if (MB == 2) reinterpret_cast<uint16_t*>(dst)[i] = (uint16_t)ci;
-                else reinterpret_cast<uint32_t*>(dst)[i] = ci;
+                if (packed) put_m(sec, e0 + i, ci);
+                else if (MB == 2) reinterpret_cast<uint16_t*>(sec)[e0 + i] = (uint16_t)ci;
+                else reinterpret_cast<uint32_t*>(sec)[e0 + i] = ci;
                 if (k != K_ZERO) { rows[ci] += s - 1 - i; rowsum[ci] += w; }
             }
             // members are ascending: row cm[i] pairs with columns cm[i+1] .. cm[s-1]
@@ -719,41 +764,49 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     const uint32_t r0 = (uint32_t)cut[rank], r1 = (uint32_t)(rank == world - 1 ? N : cut[rank + 1]);
     const uint32_t* sids = reinterpret_cast<const uint32_t*>(P + D.off_sample_ids);
     const uint32_t* totals = reinterpret_cast<const uint32_t*>(P + D.off_totals);
-    const uint64_t MB = D.member_bits / 8;
-    auto member = [&](const uint8_t* sec, uint64_t i) -> uint32_t {
-        return MB == 2 ? reinterpret_cast<const uint16_t*>(sec)[i] : reinterpret_cast<const uint32_t*>(sec)[i];
+    // element i of a member section of `bits`-wide compact ids (12 = packed), element i of a weight section
+    auto member = [&](const uint8_t* sec, uint64_t bits, uint64_t i) -> uint32_t {
+        if (bits == 32) return reinterpret_cast<const uint32_t*>(sec)[i];
+        if (bits == 16) return reinterpret_cast<const uint16_t*>(sec)[i];
+        const uint8_t* p = sec + ((3 * i) >> 1);
+        return (((uint32_t)p[0] | ((uint32_t)p[1] << 8)) >> ((i & 1) << 2)) & 0xFFFu;
+    };
+    auto weight = [&](const uint8_t* sec, uint64_t i) -> uint32_t {
+        if (D.weight_bits == 8) return sec[i];
+        if (D.weight_bits == 16) return reinterpret_cast<const uint16_t*>(sec)[i];
+        return reinterpret_cast<const uint32_t*>(sec)[i];
     };
     RawIndex raw;
     raw.n_colors_file = D.n_colors_file;
     raw.off.push_back(0);
-    // one colour: sorted compact members sec[b .. b+s)
-    auto take = [&](const uint8_t* sec, uint64_t b, uint64_t s, uint32_t w) {
+    // one colour: sorted compact members sec[b .. b+s) of a `bits`-wide section
+    auto take = [&](const uint8_t* sec, uint64_t bits, uint64_t b, uint64_t s, uint32_t w) {
         uint64_t lo = 0, hi = s;  // first member >= r0
-        while (lo < hi) { const uint64_t mid = (lo + hi) / 2; if (member(sec, b + mid) < r0) lo = mid + 1; else hi = mid; }
-        if (s - lo < 2 || member(sec, b + lo) >= r1) return;  // no owned row with a later column
-        for (uint64_t i = lo; i < s; i++) raw.members.push_back(sids[member(sec, b + i)]);
+        while (lo < hi) { const uint64_t mid = (lo + hi) / 2; if (member(sec, bits, b + mid) < r0) lo = mid + 1; else hi = mid; }
+        if (s - lo < 2 || member(sec, bits, b + lo) >= r1) return;  // no owned row with a later column
+        for (uint64_t i = lo; i < s; i++) raw.members.push_back(sids[member(sec, bits, b + i)]);
         raw.off.push_back(raw.members.size());
         raw.weights.push_back(w);
     };
     for (uint32_t sz = 2; sz <= kSmallMax; sz++) {
         const SmallClass& sc = D.cls[sz];
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(P + D.off_small_weights) + sc.weight_off;
-        for (uint64_t c = 0; c < sc.n; c++) take(P + D.off_small_members, sc.member_off + c * sz, sz, w[c]);
+        for (uint64_t c = 0; c < sc.n; c++)
+            take(P + D.off_small_members, D.packed_bits, sc.member_off + c * sz, sz, weight(P + D.off_small_weights, sc.weight_off + c));
     }
     {
         const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_mid_offsets);
         const uint32_t* szs = reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes);
         const uint32_t* w = reinterpret_cast<const uint32_t*>(P + D.off_mid_weights);
-        for (uint64_t c = 0; c < D.n_mid_colors; c++) take(P + D.off_mid_members, off[c], szs[c], w[c]);
+        for (uint64_t c = 0; c < D.n_mid_colors; c++) take(P + D.off_mid_members, D.member_bits, off[c], szs[c], w[c]);
     }
     {
         const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_zero_offsets);
-        for (uint64_t c = 0; c < D.n_zero_colors; c++) take(P + D.off_zero_members, off[c], off[c + 1] - off[c], 0);
+        for (uint64_t c = 0; c < D.n_zero_colors; c++) take(P + D.off_zero_members, D.member_bits, off[c], off[c + 1] - off[c], 0);
     }
     {
         const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_gram_offsets);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(P + D.off_gram_weights);
-        for (uint64_t c = 0; c < D.n_gram_colors; c++) take(P + D.off_gram_members, off[c], off[c + 1] - off[c], w[c]);
+        for (uint64_t c = 0; c < D.n_gram_colors; c++)
+            take(P + D.off_gram_members, D.packed_bits, off[c], off[c + 1] - off[c], weight(P + D.off_gram_weights, c));
     }
     raw.total_ids.assign(sids, sids + N);
     raw.total_vals.assign(totals, totals + N);

@@ -73,7 +73,7 @@ struct SpillSink {
 template <class Sink, class MT>
 __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params P,
                                                 const MT* __restrict__ members,
-                                                const uint32_t* __restrict__ weights,
+                                                const void* __restrict__ weights,
                                                 const __grid_constant__ TriGeom G, const Sink sink,
                                                 unsigned long long task_begin, unsigned long long task_end) {
     const uint32_t lane = threadIdx.x & 31u;
@@ -88,8 +88,7 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
         const unsigned long long t_in = task - P.cls[lo].task_begin;
         const unsigned long long n = P.cls[lo].n;
         const uint32_t s = P.cls[lo].s;
-        const MT* mcls = members + P.cls[lo].member_off;
-        const uint32_t* wcls = weights + P.cls[lo].weight_off;
+        const unsigned long long moff = P.cls[lo].member_off, woff = P.cls[lo].weight_off;
         if (s <= 32) {
             const uint32_t k = P.cls[lo].k;
             const uint32_t g = lane / s, a = lane - g * s;
@@ -97,8 +96,8 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
             const bool valid = g < k && col0 + g < n;
             uint32_t x = 0, w = 0;
             if (valid) {
-                x = __ldg(mcls + col0 * s + lane);
-                w = __ldg(wcls + col0 + g);
+                x = ldm<MT>(members, moff + col0 * s + lane);
+                w = ldw(weights, P.weight_bits, woff + col0 + g);
             }
             const unsigned long long ra = valid ? Sink::row(x, G) : 0ull;
             const uint32_t own = __ballot_sync(KSB_FULL, ra != 0ull);
@@ -115,11 +114,11 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
                 sink.add(valid && a > ar && r != 0ull, r, cadd, w);
             }
         } else {
-            const MT* m = mcls + t_in * s;
+            const unsigned long long mi = moff + t_in * s;
             const bool v1 = lane + 32 < s;
-            const uint32_t x0 = __ldg(m + lane);
-            const uint32_t x1 = v1 ? __ldg(m + 32 + lane) : 0u;
-            const unsigned long long w = __ldg(wcls + t_in);
+            const uint32_t x0 = ldm<MT>(members, mi + lane);
+            const uint32_t x1 = v1 ? ldm<MT>(members, mi + 32 + lane) : 0u;
+            const unsigned long long w = ldw(weights, P.weight_bits, woff + t_in);
             const unsigned long long ra0 = Sink::row(x0, G);
             const unsigned long long ra1 = v1 ? Sink::row(x1, G) : 0ull;
             if (__ballot_sync(KSB_FULL, (ra0 | ra1) != 0ull) == 0u) continue;
@@ -140,21 +139,23 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
     }
 }
 
-cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
+cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const void* weights, const TriGeom& g,
                             const LaunchCfg& lc, unsigned long long task_begin, unsigned long long task_end) {
     if (task_end <= task_begin) return cudaSuccess;
     const unsigned long long warps_per_cta = 8;
     unsigned long long ctas = (task_end - task_begin + warps_per_cta - 1) / warps_per_cta;
     const unsigned long long cap = (unsigned long long)lc.sms * (unsigned long long)lc.k1_ctas;  // 8 x 256 threads = 2048 resident threads / SM
     if (ctas > cap) ctas = cap;
-    if (member_bits == 16)
+    if (member_bits == 12)
+        k1_small<DenseSink, P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P12*>(members), weights, g, DenseSink{}, task_begin, task_end);
+    else if (member_bits == 16)
         k1_small<DenseSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
     else
         k1_small<DenseSink, uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint32_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
     return cudaGetLastError();
 }
 
-cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
+cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t member_bits, const void* weights, const TriGeom& g,
                             const SpillBuf& sb, unsigned long long task_begin, unsigned long long task_end,
                             const LaunchCfg& lc) {
     if (task_end <= task_begin) return cudaSuccess;
@@ -162,7 +163,9 @@ cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t mem
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
     const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
-    if (member_bits == 16)
+    if (member_bits == 12)
+        k1_small<SpillSink, P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P12*>(members), weights, g, sink, task_begin, task_end);
+    else if (member_bits == 16)
         k1_small<SpillSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, sink, task_begin, task_end);
     else
         k1_small<SpillSink, uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint32_t*>(members), weights, g, sink, task_begin, task_end);
@@ -290,7 +293,7 @@ template <class MT>
 __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, unsigned long long c_end,
                                                    const unsigned long long* __restrict__ off,
                                                    const MT* __restrict__ members,
-                                                   const uint32_t* __restrict__ weights,  // nullptr = weight 0
+                                                   const void* __restrict__ weights, uint32_t weight_bits,  // nullptr = weight 0
                                                    const __grid_constant__ TriGeom G, const SpillSink sink) {
     const uint32_t lane = threadIdx.x & 31u;
     const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -298,30 +301,32 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
     for (unsigned long long c = c_begin + warp; c < c_end; c += nwarps) {
         const unsigned long long o = off[c];
         const uint32_t s = (uint32_t)(off[c + 1] - o);
-        const MT* m = members + o;
-        const unsigned long long w = weights ? __ldg(weights + c) : 0ull;
+        const unsigned long long w = weights ? ldw(weights, weight_bits, c) : 0ull;
         for (uint32_t a = 0; a + 1 < s; a++) {
-            const unsigned long long r = SpillSink::row(__ldg(m + a), G);
+            const unsigned long long r = SpillSink::row(ldm<MT>(members, o + a), G);
             if (r == 0ull) continue;  // warp-uniform
             for (uint32_t b0 = a + 1; b0 < s; b0 += 32) {
                 const uint32_t b = b0 + lane;
-                sink.add(b < s, r, b < s ? __ldg(m + b) : 0u, w);
+                sink.add(b < s, r, b < s ? ldm<MT>(members, o + b) : 0u, w);
             }
         }
     }
 }
 
 cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
-                               uint32_t member_bits, const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc) {
+                               uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb,
+                               const LaunchCfg& lc) {
     if (c_end <= c_begin) return cudaSuccess;
     unsigned long long ctas = (c_end - c_begin + 7) / 8;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
     const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
-    if (member_bits == 16)
-        k3_emit_csr<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint16_t*>(members), weights, g, sink);
+    if (member_bits == 12)
+        k3_emit_csr<P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P12*>(members), weights, weight_bits, g, sink);
+    else if (member_bits == 16)
+        k3_emit_csr<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint16_t*>(members), weights, weight_bits, g, sink);
     else
-        k3_emit_csr<uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint32_t*>(members), weights, g, sink);
+        k3_emit_csr<uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint32_t*>(members), weights, weight_bits, g, sink);
     return cudaGetLastError();
 }
 

@@ -33,6 +33,27 @@ struct TriGeom {
     uint32_t pad;
 };
 
+// Element accessors of the blob's member / weight sections.  Members of the small-colour and Gram
+// sections are u32, u16 (N <= 65536) or 12-bit packed (N <= 4096: element i = bits [12i, 12i+12) of
+// the byte stream); their weights are u8 / u16 / u32, whichever holds the largest.  Narrow sections
+// only shorten the H2D / NVLink copy of the end-to-end path; the kernels widen on load.
+struct P12 { uint8_t b; };
+#ifdef __CUDACC__
+template <class MT>
+__device__ __forceinline__ uint32_t ldm(const MT* base, unsigned long long i) { return __ldg(base + i); }
+template <>
+__device__ __forceinline__ uint32_t ldm<P12>(const P12* base, unsigned long long i) {
+    const uint8_t* p = reinterpret_cast<const uint8_t*>(base) + ((i * 3ull) >> 1);
+    const uint32_t v = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8);
+    return (v >> ((uint32_t)(i & 1ull) << 2)) & 0xFFFu;
+}
+__device__ __forceinline__ uint32_t ldw(const void* base, uint32_t bits, unsigned long long i) {
+    if (bits == 8) return __ldg(static_cast<const uint8_t*>(base) + i);
+    if (bits == 16) return __ldg(static_cast<const uint16_t*>(base) + i);
+    return __ldg(static_cast<const uint32_t*>(base) + i);
+}
+#endif
+
 struct K1Class {
     unsigned long long task_begin;  // first warp task of this class
     unsigned long long n;           // colours in the class
@@ -45,7 +66,7 @@ struct K1Params {
     K1Class cls[kSmallMax];
     unsigned long long n_tasks;
     uint32_t n_cls;
-    uint32_t pad;
+    uint32_t weight_bits;           // 8, 16 or 32: element width of the small-weights section
 };
 
 struct LaunchCfg {
@@ -57,7 +78,7 @@ struct LaunchCfg {
 // launchers (return cudaError_t of the launch)
 // warp tasks [task_begin, task_end) of the K1 task list
 // member sections hold u16 or u32 compact sample ids (IndexDesc::member_bits)
-cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
+cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const void* weights, const TriGeom& g,
                             const LaunchCfg& lc, unsigned long long task_begin, unsigned long long task_end);
 cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned long long* mid_off,
                           const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
@@ -72,14 +93,14 @@ struct SpillBuf {
     unsigned long long* cursor;  // entries appended so far
     uint32_t shift;              // bits of a column index
 };
-cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t member_bits, const uint32_t* weights, const TriGeom& g,
+cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t member_bits, const void* weights, const TriGeom& g,
                             const SpillBuf& sb, unsigned long long task_begin, unsigned long long task_end,
                             const LaunchCfg& lc);
 cudaError_t launch_k2_spill(const MidItem* items, uint64_t item_begin, uint64_t item_end, const unsigned long long* mid_off,
                             const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
                             const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
 cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
-                               uint32_t member_bits, const uint32_t* weights, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
+                               uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
 
 cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
                              const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
@@ -144,7 +165,7 @@ struct GramParams {
 };
 uint32_t gram_cols_per_item(int planes);
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
-                            const uint32_t* gram_weights, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
+                            const void* gram_weights, uint32_t weight_bits, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 

@@ -117,8 +117,11 @@ struct IndexDesc {
     uint64_t n_gram_wins;
     uint64_t n_small_updates;   // pair-updates of the K1 colours
     uint64_t n_gram_macs;       // sum over Gram windows of colours x width(width-1)/2 x planes: the u8 MACs K4 must evaluate
-    uint64_t member_bits;       // 16 or 32: width of the compact sample ids in the four member sections
+    uint64_t member_bits;       // 16 or 32: width of the compact sample ids in the mid / zero member sections
                                 // (u16 when N <= 65536: halves the blob, i.e. the H2D / broadcast time)
+    uint64_t packed_bits;       // 12, 16 or 32: the same for the small-colour and Gram member sections, which can
+                                // also be 12-bit packed (N <= 4096); these two sections are most of the blob
+    uint64_t weight_bits;       // 8, 16 or 32: element width of the small-colour and Gram weight sections
     // row-block shard (ksb_index_shard): this blob holds only what the owner of triangle rows
     // [shard_rb, shard_re) needs -- colours with a member in that range, cut down to their members
     // >= shard_rb.  shard_world == 0: the whole index.
