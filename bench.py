@@ -321,7 +321,7 @@ def main_b200(args):
                 labels, _ = res.cluster(N, "max_cont", args.cutoff)
             d2h = res.info.n_rows * 32 + 4 * N
             tt = res.info.t
-            e2e_lib.update({k: round(float(getattr(tt, k)), 3) for k in ("h2d_ms", "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms")})
+            e2e_lib.update({k: round(float(getattr(tt, k)), 3) for k in ("h2d_ms", "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "host_setup_ms", "host_accumulate_ms", "host_post_ms", "host_free_ms")})
             res.close()
             if world > 1:
                 dv.close()

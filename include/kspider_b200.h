@@ -114,7 +114,10 @@ typedef struct ksb_timings {
     float gram_ms;        /* K4: bitmap build + int8 tcgen05 Gram kernel (inside accumulate_ms) */
     float spill_emit_ms;  /* K3: pair emission into chunk buffers */
     float spill_sort_ms;  /* K3: radix sorts + reduce-by-key + run merges */
-    float reserved[4];
+    float host_setup_ms;  /* ksb_pairwise only, host wall clock: device handle + allocations + copy enqueue */
+    float host_accumulate_ms; /* the ksb_accumulate call(s), including the wait for the pipelined copy */
+    float host_post_ms;   /* the ksb_postpass call(s) */
+    float host_free_ms;   /* releasing the device handle */
 } ksb_timings;
 
 typedef struct ksb_result_info {

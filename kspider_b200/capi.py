@@ -43,8 +43,8 @@ class Record(C.Structure):
 
 class Timings(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("h2d_ms", "zero_ms", "small_ms", "mid_ms", "zero_touch_ms",
-                                         "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "gram_ms", "spill_emit_ms", "spill_sort_ms")] + \
-        [("reserved", C.c_float * 4)]
+                                         "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "gram_ms", "spill_emit_ms", "spill_sort_ms",
+                                         "host_setup_ms", "host_accumulate_ms", "host_post_ms", "host_free_ms")]
 
 
 class ResultInfo(C.Structure):

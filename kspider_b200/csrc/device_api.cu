@@ -1,6 +1,7 @@
 // Device half of the C-ABI (include/kspider_b200.h): resident CSR, owned triangle block(s),
 // accumulation, post-pass, clustering.  No CPU fallback: every entry point here needs a CUDA device.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -140,6 +141,37 @@ struct DevCtx {
 static DevCtx g_ctx[64];
 static std::mutex g_ctx_mu;
 
+// Streams and events are recycled per device: creating ~3 streams and ~25 events per ksb_pairwise call
+// was a measurable part of the end-to-end time of a millisecond-scale run.
+static std::vector<cudaStream_t> g_stream_pool[64];
+static std::vector<cudaEvent_t> g_event_pool[64][2];  // [device][timing disabled?]
+static cudaError_t pool_stream(int dev, cudaStream_t* out) {
+    {
+        std::lock_guard<std::mutex> lk(g_ctx_mu);
+        auto& v = g_stream_pool[dev];
+        if (!v.empty()) { *out = v.back(); v.pop_back(); return cudaSuccess; }
+    }
+    return cudaStreamCreateWithFlags(out, cudaStreamNonBlocking);
+}
+static void unpool_stream(int dev, cudaStream_t s) {  // the stream must be idle
+    if (!s) return;
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    g_stream_pool[dev].push_back(s);
+}
+static cudaError_t pool_event(int dev, cudaEvent_t* out, bool timing = true) {
+    {
+        std::lock_guard<std::mutex> lk(g_ctx_mu);
+        auto& v = g_event_pool[dev][timing ? 0 : 1];
+        if (!v.empty()) { *out = v.back(); v.pop_back(); return cudaSuccess; }
+    }
+    return timing ? cudaEventCreate(out) : cudaEventCreateWithFlags(out, cudaEventDisableTiming);
+}
+static void unpool_event(int dev, cudaEvent_t e, bool timing = true) {
+    if (!e) return;
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    g_event_pool[dev][timing ? 0 : 1].push_back(e);
+}
+
 static int check_device(int device, int* sms) {
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -251,9 +283,9 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
     if (d->desc.packed_bits != 12 && d->desc.packed_bits != 16 && d->desc.packed_bits != 32) { set_error("descriptor: packed_bits must be 12, 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.weight_bits != 8 && d->desc.weight_bits != 16 && d->desc.weight_bits != 32) { set_error("descriptor: weight_bits must be 8, 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
-    if (!d->stream) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
-    if (!d->stream2) KSB_CUDA(cudaStreamCreateWithFlags(&d->stream2, cudaStreamNonBlocking));
-    for (auto& e : d->ev) KSB_CUDA(cudaEventCreate(&e));
+    if (!d->stream) KSB_CUDA(pool_stream(d->device, &d->stream));
+    if (!d->stream2) KSB_CUDA(pool_stream(d->device, &d->stream2));
+    for (auto& e : d->ev) KSB_CUDA(pool_event(d->device, &e));
     { const char* ov = std::getenv("KSPIDER_OVERLAP"); d->overlap = !(ov && ov[0] == '0'); }
     uint64_t budget = opts ? opts->dense_budget_bytes : 0;
     if (budget == 0) {
@@ -368,12 +400,12 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
     if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
     if (fs) cudaStreamSynchronize(fs);
-    for (auto& e : d->ev) if (e) cudaEventDestroy(e);
-    if (d->stream) cudaStreamDestroy(d->stream);
-    if (d->stream2) { cudaStreamSynchronize(d->stream2); cudaStreamDestroy(d->stream2); }
-    if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); cudaStreamDestroy(d->copy_stream); }
-    for (auto& e : d->ev_copy) if (e) cudaEventDestroy(e);
-    for (auto& pc : d->k1_pieces) if (pc.ev) cudaEventDestroy(pc.ev);
+    for (auto& e : d->ev) unpool_event(d->device, e);
+    if (d->stream) { cudaStreamSynchronize(d->stream); unpool_stream(d->device, d->stream); }
+    if (d->stream2) { cudaStreamSynchronize(d->stream2); unpool_stream(d->device, d->stream2); }
+    if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); unpool_stream(d->device, d->copy_stream); }
+    for (auto& e : d->ev_copy) unpool_event(d->device, e);
+    for (auto& pc : d->k1_pieces) unpool_event(d->device, pc.ev, false);
     (void)cudaGetLastError();
     delete d;
 }
@@ -393,8 +425,8 @@ static int opts_common(ksb_device* d, const ksb_opts* opts) {
 // size down in a few chunks -- the order K1 consumes them -- each followed by an event.
 static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
     const IndexDesc& D = d->desc;
-    KSB_CUDA(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
-    for (auto& e : d->ev_copy) KSB_CUDA(cudaEventCreate(&e));
+    KSB_CUDA(pool_stream(d->device, &d->copy_stream));
+    for (auto& e : d->ev_copy) KSB_CUDA(pool_event(d->device, &e));
     cudaStream_t cs = d->copy_stream;
     auto copy = [&](uint64_t b, uint64_t e) -> cudaError_t {
         return e > b ? cudaMemcpyAsync(d->d_payload + b, ix->payload + b, e - b, cudaMemcpyHostToDevice, cs) : cudaSuccess;
@@ -418,7 +450,7 @@ static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
         KSB_CUDA(copy(D.off_small_weights + wbytes * lo.weight_off, D.off_small_weights + wbytes * (hi.weight_off + hi.n)));
         ksb_device::k1_piece pc;
         pc.ev = nullptr;
-        KSB_CUDA(cudaEventCreateWithFlags(&pc.ev, cudaEventDisableTiming));
+        KSB_CUDA(pool_event(d->device, &pc.ev, false));
         KSB_CUDA(cudaEventRecord(pc.ev, cs));
         pc.task_begin = hi.task_begin;
         pc.task_end = e < k1.n_cls ? k1.cls[e].task_begin : k1.n_tasks;
@@ -444,7 +476,7 @@ static int upload_impl(const ksb_index* ix, const ksb_opts* opts, ksb_device** o
     int rc = opts_common(d, opts);
     if (rc) { ksb_device_free(d); return rc; }
     auto fail = [&](int code) { ksb_device_free(d); return code; };
-    cudaError_t e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
+    cudaError_t e = pool_stream(d->device, &d->stream);
     if (e == cudaSuccess) e = cudaMallocAsync(&d->d_payload, d->desc.payload_bytes, d->stream);
     if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
     d->own_payload = true;
@@ -1125,19 +1157,33 @@ done:
 int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     if (!ix || !out) { set_error("ksb_pairwise: null argument"); return KSB_ERR_ARG; }
     *out = nullptr;
+    using Clock = std::chrono::steady_clock;
+    auto ms_since = [](Clock::time_point t) { return std::chrono::duration<float, std::milli>(Clock::now() - t).count(); };
     ksb_device* d = nullptr;
+    auto t0 = Clock::now();
     int rc = upload_impl(ix, opts, &d, true);
     if (rc) return rc;
+    const float setup_ms = ms_since(t0);
+    float acc_ms = 0.f, post_ms = 0.f;
     ksb_result* r = nullptr;
     const int want = opts ? opts->want_records : 1;
     if (d->spill) rc = ksb_device_run_spill(d, want, &r);
     for (int p = 0; !d->spill && p < (int)d->passes.size() && rc == KSB_OK; p++) {
         rc = ksb_device_set_pass(d, p);
+        t0 = Clock::now();
         if (rc == KSB_OK) rc = ksb_accumulate(d, nullptr, 1);
+        acc_ms += ms_since(t0);
+        t0 = Clock::now();
         if (rc == KSB_OK) rc = ksb_postpass(d, want, &r);
+        post_ms += ms_since(t0);
     }
+    t0 = Clock::now();
     ksb_device_free(d);
     if (rc) { ksb_result_free(r); return rc; }
+    r->info.t.host_setup_ms = setup_ms;
+    r->info.t.host_accumulate_ms = acc_ms;
+    r->info.t.host_post_ms = post_ms;
+    r->info.t.host_free_ms = ms_since(t0);
     *out = r;
     return KSB_OK;
 }
