@@ -216,17 +216,20 @@ def main_b200(args):
         shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, U_small, M_small, C_small,
                     inf.payload_bytes, inf.n_gram_colors, inf.gram_planes, inf.n_gram_updates, inf.n_gram_members, inf.n_gram_macs]
         del s
+    cpus = None
     if world > 1:
         t = torch.from_numpy(shape).to(device)
         dist.broadcast(t, 0)
         shape = t.cpu().numpy()
         # every rank receives the row-block shard of its own rows (cut on the host once, part of loading)
         shards = kd.make_shards(idx, world, host_threads=min(32, os.cpu_count() or 1)) if rank == 0 else None
-        desc, d_payload = kd.scatter_shards(shards, device, 0)
-        dev = kd.adopt(desc, d_payload, dense_budget_bytes=budget, spill=args.spill)
-        payload_bytes_rank = torch.tensor([d_payload.numel()], dtype=torch.int64, device=device)
+        cpus = None if os.environ.get("KSPIDER_NO_NUMA_BIND") else kd.bind_to_gpu_numa(local_rank)
+        my = kd.host_shard(shards, device, 0)     # one-off: this rank's shard in its own pinned host memory
+        del shards
+        dev = my.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
+        payload_bytes_rank = torch.tensor([int(my.info.payload_bytes)], dtype=torch.int64, device=device)
         dist.all_reduce(payload_bytes_rank)
-        shape[7] = int(payload_bytes_rank.cpu())  # bytes moved host -> GPUs per e2e step: all shards
+        shape[7] = int(payload_bytes_rank.cpu())  # bytes moved host -> GPUs per e2e step: all shards, each over its rank's link
     else:
         dev = idx.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
     N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram, MAC_gram = (int(v) for v in shape)
@@ -309,12 +312,8 @@ def main_b200(args):
 
         def e2e_step():
             nonlocal d2h
-            if world == 1:
-                res = idx.pairwise(device=local_rank, want_records=True, dense_budget_bytes=budget, spill=args.spill)
-            else:
-                desc2, pay2 = kd.scatter_shards(shards, device, 0)
-                dv = kd.adopt(desc2, pay2, dense_budget_bytes=budget, spill=args.spill)
-                res = dv.run_all_passes(want_records=True)
+            src = idx if world == 1 else my   # N>1: every rank uploads its own row-block shard
+            res = src.pairwise(device=local_rank, want_records=True, dense_budget_bytes=budget, spill=args.spill)
             if world > 1:
                 labels, _ = kd.cluster_merged(res, N, "max_cont", args.cutoff, device, to_host=True)
             else:
@@ -323,8 +322,6 @@ def main_b200(args):
             tt = res.info.t
             e2e_lib.update({k: round(float(getattr(tt, k)), 3) for k in ("h2d_ms", "accumulate_ms", "post_ms", "d2h_ms", "cluster_ms", "host_setup_ms", "host_accumulate_ms", "host_post_ms", "host_free_ms")})
             res.close()
-            if world > 1:
-                dv.close()
 
         e2e_step()
         barrier()
@@ -340,7 +337,8 @@ def main_b200(args):
         e2e = {"value": U / (float(e_ms.cpu()) * 1e-3), "unit": UNIT, "h2d_bytes_per_step": payload_bytes,
                "d2h_bytes_per_step": int(d2h_t.cpu()), "ms_per_step": float(e_ms.cpu()), "steps": n_e2e,
                "timer": "host wall clock around ksb_pairwise + ksb_cluster (synchronous calls)",
-               "library_phases_ms_last_step": e2e_lib}
+               "library_phases_ms_last_step": e2e_lib,
+               "host_numa": (f"rank bound to the {len(cpus)} CPUs next to its GPU before its pinned buffers were allocated" if cpus else "unbound")}
 
     if rank != 0:
         if world > 1:

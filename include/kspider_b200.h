@@ -167,6 +167,11 @@ int ksb_blob_row_cuts(const void* descriptor, uint64_t descriptor_bytes, const v
  * share of the pair-updates instead of the whole colour table.  This is what each GPU of a
  * multi-GPU run receives. */
 int ksb_index_shard(const ksb_index* ix, int rank, int world, int host_threads, ksb_index** out);
+/* Host index from a (descriptor, payload) pair produced by ksb_index_descriptor / ksb_index_payload
+ * on another process or rank: the blob is copied into pinned memory of THIS process, so that every
+ * rank of a multi-GPU run uploads its own shard over its own PCIe link (ksb_pairwise / ksb_upload). */
+int ksb_index_from_blob(const void* descriptor, uint64_t descriptor_bytes, const void* payload, uint64_t payload_bytes,
+                        ksb_index** out);
 int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path);
 void ksb_index_free(ksb_index* ix);
 

@@ -107,6 +107,15 @@ class Index:
         check(lib().ksb_index_shard(self._h, int(rank), int(world), int(host_threads), C.byref(h)))
         return Index(h)
 
+    @classmethod
+    def from_blob(cls, descriptor: bytes, payload: np.ndarray) -> "Index":
+        """Host index of THIS process from another rank's (descriptor(), payload()) — ksb_index_from_blob."""
+        payload = np.ascontiguousarray(payload, dtype=np.uint8)
+        buf = C.create_string_buffer(bytes(descriptor), len(descriptor))
+        h = C.c_void_p()
+        check(lib().ksb_index_from_blob(C.cast(buf, C.c_void_p), len(descriptor), payload.ctypes.data, payload.size, C.byref(h)))
+        return cls(h)
+
     def write_seq_to_kmers(self, path: str) -> None:
         check(lib().ksb_write_seq_to_kmers(self._h, str(path).encode()))
 

@@ -69,6 +69,7 @@ _PROTOS = {
     "ksb_index_bands": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "ksb_blob_row_cuts": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]),
     "ksb_index_shard": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "ksb_index_from_blob": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]),
     "ksb_write_seq_to_kmers": (C.c_int, [C.c_void_p, C.c_char_p]),
     "ksb_index_free": (None, [C.c_void_p]),
     "ksb_upload": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_void_p)]),

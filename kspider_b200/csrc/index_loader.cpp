@@ -887,6 +887,42 @@ int ksb_index_shard(const ksb_index* ix, int rank, int world, int host_threads, 
     }
 }
 
+int ksb_index_from_blob(const void* descriptor, uint64_t descriptor_bytes, const void* payload, uint64_t payload_bytes,
+                        ksb_index** out) {
+    if (!descriptor || !payload || !out) { ksb::set_error("ksb_index_from_blob: null argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    if (descriptor_bytes != sizeof(ksb::IndexDesc)) {
+        ksb::set_error("descriptor is %llu bytes, expected %zu", (unsigned long long)descriptor_bytes, sizeof(ksb::IndexDesc));
+        return KSB_ERR_ARG;
+    }
+    ksb::IndexDesc d;
+    std::memcpy(&d, descriptor, sizeof d);
+    if (d.magic != ksb::kIndexMagic) { ksb::set_error("ksb_index_from_blob: not an index descriptor"); return KSB_ERR_FORMAT; }
+    if (d.payload_bytes != payload_bytes) {
+        ksb::set_error("payload is %llu bytes, descriptor says %llu", (unsigned long long)payload_bytes, (unsigned long long)d.payload_bytes);
+        return KSB_ERR_ARG;
+    }
+    ksb_index* ix = new (std::nothrow) ksb_index();
+    if (!ix) { ksb::set_error("out of memory"); return KSB_ERR_NOMEM; }
+    ix->desc = d;
+    void* mem = nullptr;
+    if (cudaMallocHost(&mem, d.payload_bytes) == cudaSuccess) {
+        ix->pinned = true;
+    } else {
+        (void)cudaGetLastError();
+        if (posix_memalign(&mem, 4096, d.payload_bytes) != 0) { delete ix; ksb::set_error("out of host memory (%llu bytes)", (unsigned long long)d.payload_bytes); return KSB_ERR_NOMEM; }
+    }
+    ix->payload = static_cast<uint8_t*>(mem);
+    std::memcpy(ix->payload, payload, d.payload_bytes);
+    // the totals file order is not part of the blob: slot order (ascending sample id) stands in for it
+    const uint32_t* sid = reinterpret_cast<const uint32_t*>(ix->payload + d.off_sample_ids);
+    const uint32_t* tot = reinterpret_cast<const uint32_t*>(ix->payload + d.off_totals);
+    ix->totals_file_ids.assign(sid, sid + d.n_samples);
+    ix->totals_file_vals.assign(tot, tot + d.n_samples);
+    *out = ix;
+    return KSB_OK;
+}
+
 int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     if (!ix || !info) { ksb::set_error("null argument"); return KSB_ERR_ARG; }
     const ksb::IndexDesc& d = ix->desc;

@@ -83,6 +83,32 @@ def scatter_shards(shards, device: torch.device, src: int = 0) -> Tuple[bytes, t
     return bytes(d_desc.cpu().numpy().tobytes()), d_payload
 
 
+def bind_to_gpu_numa(device_index: int):
+    """Pins the calling process to the CPUs next to GPU `device_index` (NVML's ideal affinity), so that
+    the pinned host buffers it allocates afterwards (first touch) sit on that GPU's NUMA node and the
+    per-rank H2D / D2H copies of a multi-GPU run do not cross the socket interconnect.  Returns the
+    CPU list, or None when NVML or the topology is unavailable (nothing is changed then)."""
+    try:
+        import os
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+        h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        return sorted(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
+def host_shard(shards, device: torch.device, src: int = 0) -> Index:
+    """scatter_shards, then the received shard is kept as an Index in THIS rank's pinned host memory
+    (ksb_index_from_blob).  From there every rank runs the host-facing calls (Index.upload /
+    Index.pairwise) on its own shard, i.e. N uploads over N PCIe links at once — the multi-GPU
+    shape of the reference-facing call, where the one-off distribution is part of loading the index."""
+    desc, payload = scatter_shards(shards, device, src)
+    return Index.from_blob(desc, payload.cpu().numpy())
+
+
 def adopt(desc: bytes, d_payload: torch.Tensor, **opts) -> Device:
     """Device handle of this rank's row block over an already-resident blob (CUDA tensor)."""
     assert d_payload.is_cuda and d_payload.dtype == torch.uint8

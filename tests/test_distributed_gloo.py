@@ -117,6 +117,13 @@ def _worker(rank: int, world: int, port: int, q) -> None:
         sbuf = C.create_string_buffer(sdesc, len(sdesc))
         check(lib().ksb_blob_row_cuts(sbuf, len(sdesc), sp.ctypes.data, sp.size, 1, scuts.ctypes.data))
         assert scuts[0] == 0 and scuts[1] == n
+        # ... and keeps it as a host index of its own (ksb_index_from_blob): same blob, same shard rows
+        mine = kd.host_shard(shards, torch.device("cpu"), 0)
+        assert mine.descriptor() == sdesc and np.array_equal(mine.payload(), sp)
+        assert mine.info.n_samples == n
+        with pytest.raises(Exception):
+            mine.shard(0, 2)
+        mine.close()
         dist.barrier()
         dist.destroy_process_group()
         q.put((rank, "ok"))

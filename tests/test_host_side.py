@@ -266,4 +266,14 @@ def test_row_block_shards_hold_exactly_the_needed_colours(built_lib, world):
         total += inf.n_updates
         with pytest.raises(Exception):
             sh.shard(0, 2)
+        # the (descriptor, payload) pair rebuilds the same host index in another process (ksb_index_from_blob)
+        cp = Index.from_blob(sh.descriptor(), sh.payload())
+        assert cp.descriptor() == sh.descriptor() and np.array_equal(cp.payload(), sh.payload())
+        assert np.array_equal(cp.sample_ids, idx.sample_ids) and cp.info.n_updates == inf.n_updates
+        with pytest.raises(Exception):
+            Index.from_blob(sh.descriptor()[:-8], sh.payload())
+        with pytest.raises(Exception):
+            Index.from_blob(sh.descriptor(), sh.payload()[:-1])
+        with pytest.raises(Exception):
+            Index.from_blob(b"\0" * len(sh.descriptor()), sh.payload())
     assert total == idx.info.n_updates
