@@ -73,14 +73,35 @@ WORKLOAD_DESC = {
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md's clocks line).  The
+    timed region of this bench is tens of milliseconds, shorter than nvidia-smi's start-up, so the
+    sampler reads NVML in-process every ~4 ms (the same counters nvidia-smi prints); nvidia-smi -lms
+    is the fallback when pynvml is missing.  mark() brackets the timed region: the reported median is
+    over the samples inside it (over the whole run, warm-up included, if none fell inside)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+            0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, gpu_index: int):
         self.rows, self.proc, self.gpu = [], None, gpu_index
+        self.samples, self.marks, self.nvml, self.stop_flag, self.t = [], [], None, False, None
+        self.max_mhz = None
 
     def start(self):
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+            self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         if shutil.which("nvidia-smi") is None:
             return
         self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
@@ -88,11 +109,38 @@ class ClockSampler:
         self.t = threading.Thread(target=self._read, daemon=True)
         self.t.start()
 
+    def _poll(self):
+        nv = self.nvml
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                mhz = float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                self.samples.append((time.perf_counter(), mhz, int(get_reasons(self.handle))))
+            except Exception:
+                pass
+            time.sleep(0.004)
+
     def _read(self):
         for line in self.proc.stdout:
             self.rows.append([x.strip() for x in line.split(",")])
 
+    def mark(self):
+        self.marks.append(time.perf_counter())
+
     def stop(self) -> dict:
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.t.join(timeout=2)
+            inside = [x for x in self.samples if len(self.marks) >= 2 and self.marks[0] <= x[0] <= self.marks[1]]
+            use = inside or self.samples
+            reasons = set()
+            for _, _, bits in use:
+                for b, nme in self.BITS.items():
+                    if bits & b:
+                        reasons.add(nme)
+            return {"sm_mhz": float(np.median([x[1] for x in use])) if use else None, "sm_max_mhz": self.max_mhz,
+                    "reasons": sorted(reasons), "samples": len(use), "samples_in_timed_region": len(inside),
+                    "source": "NVML in-process, 4 ms period"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -111,7 +159,7 @@ class ClockSampler:
                 if len(r) > 5 + k and r[5 + k].lower().startswith("active"):
                     reasons.add(nme)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi -lms 20"}
 
 
 # ----------------------------------------------------------------------------- reference / CPU arm
@@ -268,6 +316,7 @@ def main_b200(args):
     barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     host_ms.update({k: 0.0 for k in host_ms})
+    sampler.mark()
     ev0.record()
     w0 = time.perf_counter()
     launches = 0
@@ -277,6 +326,7 @@ def main_b200(args):
     ev1.record()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - w0) * 1e3
+    sampler.mark()
     dev_ms = ev0.elapsed_time(ev1)
     barrier()
     clocks = sampler.stop() if rank == 0 else None

@@ -65,6 +65,8 @@ struct ksb_device {
     cudaEvent_t ev_copy[4] = {};           // copy start, head landed, tail landed, copy end
     struct k1_piece { cudaEvent_t ev; unsigned long long task_begin, task_end; };
     std::vector<k1_piece> k1_pieces;       // K1 task ranges in the order their classes are copied
+    std::vector<cudaEvent_t> gram_ev;      // per K4 chunk of pass 0: the copy piece holding its members has landed
+    std::vector<cudaEvent_t> gram_ev_own;  // the distinct events behind gram_ev (several chunks may share a piece)
     unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
     uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
     uint64_t tri_cells_alloc = 0;
@@ -406,9 +408,12 @@ void ksb_device_free(ksb_device* d) {
     if (d->copy_stream) { cudaStreamSynchronize(d->copy_stream); unpool_stream(d->device, d->copy_stream); }
     for (auto& e : d->ev_copy) unpool_event(d->device, e);
     for (auto& pc : d->k1_pieces) unpool_event(d->device, pc.ev, false);
+    for (auto& e : d->gram_ev_own) unpool_event(d->device, e, false);
     (void)cudaGetLastError();
     delete d;
 }
+
+static int plan_gram(ksb_device* d, uint32_t pass);
 
 static int opts_common(ksb_device* d, const ksb_opts* opts) {
     d->rank = opts ? opts->rank : 0;
@@ -420,22 +425,63 @@ static int opts_common(ksb_device* d, const ksb_opts* opts) {
     return KSB_OK;
 }
 
-// Enqueues the blob copy in pieces on the copy stream: head (totals, ids, bands), tail (mid, zero and
-// Gram sections: K4's bitmap build starts first), then the small-colour classes from the largest
-// size down in a few chunks -- the order K1 consumes them -- each followed by an event.
-static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
+// Enqueues the blob copy in pieces on the copy stream.  Phase A (before the device is planned, so that
+// the planning overlaps the copy): head (totals, ids, bands), then the mid, zero and Gram offset /
+// weight / window sections.  Phase B: the Gram members in one piece per K4 chunk (K4's bitmap build
+// starts first), then the small-colour classes from the largest size down in a few chunks -- the
+// order K1 consumes them -- each followed by an event.
+static int enqueue_copy_head(ksb_device* d, const ksb_index* ix) {
     const IndexDesc& D = d->desc;
     KSB_CUDA(pool_stream(d->device, &d->copy_stream));
     for (auto& e : d->ev_copy) KSB_CUDA(pool_event(d->device, &e));
     cudaStream_t cs = d->copy_stream;
+    cudaEvent_t alloc = nullptr;  // d_payload was allocated in stream order on d->stream
+    KSB_CUDA(pool_event(d->device, &alloc, false));
+    KSB_CUDA(cudaEventRecord(alloc, d->stream));
+    KSB_CUDA(cudaStreamWaitEvent(cs, alloc, 0));
+    unpool_event(d->device, alloc, false);
     auto copy = [&](uint64_t b, uint64_t e) -> cudaError_t {
         return e > b ? cudaMemcpyAsync(d->d_payload + b, ix->payload + b, e - b, cudaMemcpyHostToDevice, cs) : cudaSuccess;
     };
     KSB_CUDA(cudaEventRecord(d->ev_copy[0], cs));
     KSB_CUDA(copy(0, D.off_small_members));
     KSB_CUDA(cudaEventRecord(d->ev_copy[1], cs));
-    KSB_CUDA(copy(D.off_mid_offsets, D.payload_bytes));
+    KSB_CUDA(copy(D.off_mid_offsets, D.off_gram_members));
+    KSB_CUDA(copy(D.off_gram_weights, D.payload_bytes));
     KSB_CUDA(cudaEventRecord(d->ev_copy[2], cs));
+    return KSB_OK;
+}
+
+static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
+    const IndexDesc& D = d->desc;
+    cudaStream_t cs = d->copy_stream;
+    auto copy = [&](uint64_t b, uint64_t e) -> cudaError_t {
+        return e > b ? cudaMemcpyAsync(d->d_payload + b, ix->payload + b, e - b, cudaMemcpyHostToDevice, cs) : cudaSuccess;
+    };
+    // Gram member section (the bulk of the tail) in one piece per K4 chunk of pass 0, so that the bitmap
+    // build of chunk k starts when ITS colours have landed instead of after the whole section
+    const ksb_gram_plan* plan = (D.n_gram_colors && !d->gplan.empty() && d->gplan[0].built && !d->gplan[0].chunks.empty()) ? &d->gplan[0] : nullptr;
+    if (!plan) KSB_CUDA(copy(D.off_gram_members, D.off_gram_weights));  // no K4 launch in pass 0: nobody waits for it
+    if (plan) {
+        const uint64_t* goff = reinterpret_cast<const uint64_t*>(ix->payload + D.off_gram_offsets);
+        const size_t nck = plan->chunks.size();
+        d->gram_ev.assign(nck, nullptr);
+        uint64_t done = D.off_gram_members;
+        size_t first = 0;
+        for (size_t k = 0; k < nck; k++) {
+            const ksb_gram_chunk& c = plan->chunks[k];
+            uint64_t end = D.off_gram_members + ((D.packed_bits * goff[c.c_begin + c.n_colors] + 7) / 8 + 64 + 255) / 256 * 256;
+            if (k + 1 == nck || end > D.off_gram_weights) end = D.off_gram_weights;
+            if (end - done < (4ull << 20) && k + 1 < nck) continue;  // too small for a piece of its own: rides with the next
+            KSB_CUDA(copy(done, end));
+            done = end;
+            cudaEvent_t e = nullptr;
+            KSB_CUDA(pool_event(d->device, &e, false));
+            d->gram_ev_own.push_back(e);
+            KSB_CUDA(cudaEventRecord(e, cs));
+            for (; first <= k; first++) d->gram_ev[first] = e;
+        }
+    }
     const uint64_t mbits = D.packed_bits, wbytes = D.weight_bits / 8;
     const uint64_t small_bytes = mbits * D.n_small_members / 8 + wbytes * D.n_small_colors;
     const uint64_t chunk = std::max<uint64_t>(8ull << 20, small_bytes / 6);
@@ -480,6 +526,11 @@ static int upload_impl(const ksb_index* ix, const ksb_opts* opts, ksb_device** o
     if (e == cudaSuccess) e = cudaMallocAsync(&d->d_payload, d->desc.payload_bytes, d->stream);
     if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
     d->own_payload = true;
+    const bool pipe = pipelined && ix->pinned;
+    if (pipe) {
+        rc = enqueue_copy_head(d, ix);
+        if (rc) return fail(rc);
+    }
     const uint64_t* row_updates = reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_row_updates);
     if (d->desc.n_gram_wins) {
         const GramWin* gw = reinterpret_cast<const GramWin*>(ix->payload + d->desc.off_gram_wins);
@@ -488,7 +539,11 @@ static int upload_impl(const ksb_index* ix, const ksb_opts* opts, ksb_device** o
     rc = finish_device(d, row_updates, reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_lo),
                        reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_hi), opts);
     if (rc) return fail(rc);
-    if (pipelined && ix->pinned && !d->spill) {
+    if (pipe && !d->spill) {
+        if (d->desc.n_gram_colors && !d->passes.empty() && d->passes[0].cells) {
+            rc = plan_gram(d, 0);  // the copy is cut along the K4 chunks of the first pass
+            if (rc) return fail(rc);
+        }
         rc = enqueue_pipelined_copy(d, ix);
         if (rc) return fail(rc);
         *out = d;
@@ -705,6 +760,11 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
         gp.planes = d->g_planes;
         gp.counter = reinterpret_cast<uint32_t*>(d->d_gwq + (uint64_t)d->g_planes * gp.kpad);
         cudaStream_t sb = first ? st_build : st;
+        if (d->copy_pending) {  // first accumulation after a pipelined upload: wait for this chunk's colours
+            const size_t k = &c - plan.chunks.data();
+            cudaEvent_t ce = (d->cur_pass == 0 && k < d->gram_ev.size() && d->gram_ev[k]) ? d->gram_ev[k] : d->ev_copy[3];
+            KSB_CUDA(cudaStreamWaitEvent(sb, ce, 0));
+        }
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
         KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, gp.wins, gp.n_wins, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
                                  LaunchCfg{d->sms, sb}));
