@@ -180,3 +180,31 @@ def test_gram_windows_beyond_max_width(ksb, gram_env):
     sizes = np.diff(csr["offsets"]).astype(object)
     w = csr["weights"].astype(object)
     assert sum(int(v) for v in rec["shared_kmers"]) == sum(int(x) * int(k * (k - 1) // 2) for x, k in zip(w, sizes))
+
+
+def test_gram_pipelined_upload_pieces(ksb, gram_env, monkeypatch):
+    """ksb_pairwise copies the Gram members in one piece per K4 chunk (pieces under 4 MB ride with the
+    next one) and every chunk's bitmap build waits for its own piece: several chunks and several pieces
+    here, result bit-exact; the resident path (upload + run) must agree with it."""
+    gram_env(16)
+    monkeypatch.setenv("KSPIDER_GRAM_CHUNK_MB", "8")
+    rng = np.random.default_rng(71)
+    n, s, nc = 1201, 24, 250_000          # n prime: (a + k b) mod n are s distinct members
+    a = rng.integers(0, n, size=nc)
+    b = rng.integers(1, n, size=nc)
+    members = ((a[:, None] + np.arange(s)[None, :] * b[:, None]) % n + 1).astype(np.uint32).ravel()
+    small = random_csr(seed=72, n_samples=n, n_colors=20000, s_lo=1, s_hi=12, w_hi=255)
+    csr = dict(offsets=np.concatenate([np.arange(nc, dtype=np.uint64) * np.uint64(s), np.uint64(nc * s) + small["offsets"]]),
+               members=np.concatenate([members, small["members"]]),
+               weights=np.concatenate([rng.integers(1, 256, size=nc).astype(np.uint32), small["weights"]]),
+               total_ids=small["total_ids"], total_vals=small["total_vals"])
+    idx = ksb.Index.from_csr(**csr, host_threads=4)
+    inf = idx.info
+    assert inf.n_gram_colors >= nc and inf.n_gram_members * 12 // 8 > (8 << 20)
+    want = oracle_records(csr)
+    for _ in range(2):   # second call: pooled streams / events are reused
+        res = idx.pairwise(device=0)
+        assert_records_equal(res.records(), want)
+        res.close()
+    dev = idx.upload(device=0)
+    assert_records_equal(dev.run_all_passes().records(), want)
