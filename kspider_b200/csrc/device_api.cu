@@ -282,7 +282,7 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
                          const ksb_opts* opts) {
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
     if (d->desc.member_bits != 16 && d->desc.member_bits != 32) { set_error("descriptor: member_bits must be 16 or 32"); return KSB_ERR_ARG; }
-    if (d->desc.packed_bits != 12 && d->desc.packed_bits != 16 && d->desc.packed_bits != 32) { set_error("descriptor: packed_bits must be 12, 16 or 32"); return KSB_ERR_ARG; }
+    if (d->desc.packed_bits != 10 && d->desc.packed_bits != 12 && d->desc.packed_bits != 16 && d->desc.packed_bits != 32) { set_error("descriptor: packed_bits must be 10, 12, 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.weight_bits != 8 && d->desc.weight_bits != 16 && d->desc.weight_bits != 32) { set_error("descriptor: weight_bits must be 8, 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.n_samples > 0x7FFFFFFFull) { set_error("more than 2^31 samples are not supported"); return KSB_ERR_ARG; }
     if (!d->stream) KSB_CUDA(pool_stream(d->device, &d->stream));

@@ -219,7 +219,9 @@ cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram
     if (n_units == 0) return cudaSuccess;
     const unsigned cap = (unsigned)lc.sms * 6u;  // 32 KB of shared memory per CTA
     const unsigned ctas = n_units < cap ? n_units : cap;
-    if (member_bits == 12)
+    if (member_bits == 10)
+        kb_build<P10><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P10*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
+    else if (member_bits == 12)
         kb_build<P12><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P12*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
     else if (member_bits == 16)
         kb_build<uint16_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);

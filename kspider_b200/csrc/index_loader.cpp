@@ -390,10 +390,12 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         d.member_bits = (N <= 65536 && !(mb && std::atoi(mb) == 32)) ? 16 : 32;
     }
     const uint64_t MB = d.member_bits / 8;
-    {   // the small-colour and Gram sections (most of the blob): 12-bit packed members when N <= 4096, and
-        // weights as narrow as the largest one allows.  KSPIDER_MEMBER_BITS=16|32 / KSPIDER_WEIGHT_BITS=32 override.
+    {   // the small-colour and Gram sections (most of the blob): 10-bit packed members when N <= 1024, 12-bit
+        // when N <= 4096, and weights as narrow as the largest one allows.
+        // KSPIDER_MEMBER_BITS=12|16|32 / KSPIDER_WEIGHT_BITS=32 override.
         const char* mb = std::getenv("KSPIDER_MEMBER_BITS");
-        d.packed_bits = (N <= 4096 && !(mb && (std::atoi(mb) == 16 || std::atoi(mb) == 32))) ? 12 : d.member_bits;
+        const int mbv = mb ? std::atoi(mb) : 0;
+        d.packed_bits = (N <= 4096 && mbv != 16 && mbv != 32) ? ((N <= 1024 && mbv != 12) ? 10 : 12) : d.member_bits;
         std::vector<uint32_t> tw(T, 0);
         parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
             uint32_t m = 0;
@@ -459,10 +461,18 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     };
     // element i of a small / Gram member section.  12-bit packing: element i = bits [12i, 12i+12); its
     // full byte is stored plainly, its half byte is OR-ed atomically (the other half may belong to a
-    // neighbouring colour that another thread is writing; the payload starts zeroed)
+    // neighbouring colour that another thread is writing; the payload starts zeroed).  10-bit packing:
+    // element i = bits [10i, 10i+10) — 4 elements per 5 bytes, so an element always lies in 2 bytes.
     auto put_m = [&](uint8_t* sec, uint64_t i, uint32_t v) {
         if (PB == 32) { reinterpret_cast<uint32_t*>(sec)[i] = v; return; }
         if (PB == 16) { reinterpret_cast<uint16_t*>(sec)[i] = (uint16_t)v; return; }
+        if (PB == 10) {
+            uint8_t* p = sec + ((5 * i) >> 2);
+            const uint32_t x = (v & 0x3FFu) << ((i & 3) << 1);
+            __atomic_fetch_or(p, (uint8_t)x, __ATOMIC_RELAXED);
+            __atomic_fetch_or(p + 1, (uint8_t)(x >> 8), __ATOMIC_RELAXED);
+            return;
+        }
         uint8_t* p = sec + ((3 * i) >> 1);
         if ((i & 1) == 0) {
             p[0] = (uint8_t)v;
@@ -768,6 +778,10 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     auto member = [&](const uint8_t* sec, uint64_t bits, uint64_t i) -> uint32_t {
         if (bits == 32) return reinterpret_cast<const uint32_t*>(sec)[i];
         if (bits == 16) return reinterpret_cast<const uint16_t*>(sec)[i];
+        if (bits == 10) {
+            const uint8_t* q = sec + ((5 * i) >> 2);
+            return (((uint32_t)q[0] | ((uint32_t)q[1] << 8)) >> ((i & 3) << 1)) & 0x3FFu;
+        }
         const uint8_t* p = sec + ((3 * i) >> 1);
         return (((uint32_t)p[0] | ((uint32_t)p[1] << 8)) >> ((i & 1) << 2)) & 0xFFFu;
     };

@@ -146,7 +146,9 @@ cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t mem
     unsigned long long ctas = (task_end - task_begin + warps_per_cta - 1) / warps_per_cta;
     const unsigned long long cap = (unsigned long long)lc.sms * (unsigned long long)lc.k1_ctas;  // 8 x 256 threads = 2048 resident threads / SM
     if (ctas > cap) ctas = cap;
-    if (member_bits == 12)
+    if (member_bits == 10)
+        k1_small<DenseSink, P10><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P10*>(members), weights, g, DenseSink{}, task_begin, task_end);
+    else if (member_bits == 12)
         k1_small<DenseSink, P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P12*>(members), weights, g, DenseSink{}, task_begin, task_end);
     else if (member_bits == 16)
         k1_small<DenseSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
@@ -163,7 +165,9 @@ cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t mem
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
     const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
-    if (member_bits == 12)
+    if (member_bits == 10)
+        k1_small<SpillSink, P10><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P10*>(members), weights, g, sink, task_begin, task_end);
+    else if (member_bits == 12)
         k1_small<SpillSink, P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P12*>(members), weights, g, sink, task_begin, task_end);
     else if (member_bits == 16)
         k1_small<SpillSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, sink, task_begin, task_end);
@@ -321,7 +325,9 @@ cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned 
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
     const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
-    if (member_bits == 12)
+    if (member_bits == 10)
+        k3_emit_csr<P10><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P10*>(members), weights, weight_bits, g, sink);
+    else if (member_bits == 12)
         k3_emit_csr<P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P12*>(members), weights, weight_bits, g, sink);
     else if (member_bits == 16)
         k3_emit_csr<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint16_t*>(members), weights, weight_bits, g, sink);

@@ -34,10 +34,12 @@ struct TriGeom {
 };
 
 // Element accessors of the blob's member / weight sections.  Members of the small-colour and Gram
-// sections are u32, u16 (N <= 65536) or 12-bit packed (N <= 4096: element i = bits [12i, 12i+12) of
-// the byte stream); their weights are u8 / u16 / u32, whichever holds the largest.  Narrow sections
+// sections are u32, u16 (N <= 65536), 12-bit packed (N <= 4096: element i = bits [12i, 12i+12) of
+// the byte stream) or 10-bit packed (N <= 1024: bits [10i, 10i+10), 4 elements per 5 bytes, so an
+// element always lies in 2 bytes); their weights are u8 / u16 / u32, whichever holds the largest.  Narrow sections
 // only shorten the H2D / NVLink copy of the end-to-end path; the kernels widen on load.
 struct P12 { uint8_t b; };
+struct P10 { uint8_t b; };
 #ifdef __CUDACC__
 template <class MT>
 __device__ __forceinline__ uint32_t ldm(const MT* base, unsigned long long i) { return __ldg(base + i); }
@@ -46,6 +48,12 @@ __device__ __forceinline__ uint32_t ldm<P12>(const P12* base, unsigned long long
     const uint8_t* p = reinterpret_cast<const uint8_t*>(base) + ((i * 3ull) >> 1);
     const uint32_t v = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8);
     return (v >> ((uint32_t)(i & 1ull) << 2)) & 0xFFFu;
+}
+template <>
+__device__ __forceinline__ uint32_t ldm<P10>(const P10* base, unsigned long long i) {
+    const uint8_t* p = reinterpret_cast<const uint8_t*>(base) + ((i * 5ull) >> 2);
+    const uint32_t v = (uint32_t)__ldg(p) | ((uint32_t)__ldg(p + 1) << 8);
+    return (v >> ((uint32_t)(i & 3ull) << 1)) & 0x3FFu;
 }
 __device__ __forceinline__ uint32_t ldw(const void* base, uint32_t bits, unsigned long long i) {
     if (bits == 8) return __ldg(static_cast<const uint8_t*>(base) + i);

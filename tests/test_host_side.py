@@ -231,12 +231,16 @@ def test_row_bands_are_tight_and_cover_every_pair(built_lib, oracle_lib):
     assert cells == int((whi - wlo).sum()) and cells < n * (n - 1) // 2
 
 
-@pytest.mark.parametrize("world", [2, 5])
-def test_row_block_shards_hold_exactly_the_needed_colours(built_lib, world):
+@pytest.mark.parametrize("world,bits", [(2, None), (5, None), (2, "12"), (2, "16"), (2, "32")])
+def test_row_block_shards_hold_exactly_the_needed_colours(built_lib, world, bits, monkeypatch):
     """ksb_index_shard: rank r's shard = colours with a row in [cut[r], cut[r+1]), cut down to their
-    members >= cut[r]; the owned rows keep their bands, and the shards' updates add up to U."""
+    members >= cut[r]; the owned rows keep their bands, and the shards' updates add up to U.
+    Runs in every member packing of the small / Gram sections (10-bit by default at N = 300; 12-bit,
+    u16, u32 forced): the shard is rebuilt from the PACKED sections, so a wrong pack or unpack shows."""
     from kspider_b200 import Index
     from util import random_csr
+    if bits:
+        monkeypatch.setenv("KSPIDER_MEMBER_BITS", bits)
     csr = random_csr(seed=77, n_samples=300, n_colors=4000, s_lo=1, s_hi=40, big=(70, 150, 290), zero_every=31)
     idx = Index.from_csr(**csr, host_threads=2)
     cuts = idx.row_cuts(world).astype(np.int64)
