@@ -842,9 +842,19 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     }
     if (p.cells) {
         LaunchCfg lc1 = lc;
-        if (has_gram && d->overlap) {  // tuning knob: K4 holds 576 threads and ~37K registers of an SM (measured: no gain from leaving it room, both kernels are issue-bound)
+        if (has_gram && d->overlap) {
+            // K4 (P = 1: 48 registers x 576 threads = 27.6 K registers, capped by __maxnreg__) leaves room for K1
+            // CTAs (32 registers x 256 threads) on every SM: K1 gets 3 per SM (measured on cfg2: 3 -> 2.16 ms/step,
+            // 4 -> 2.23, 8 = K4 waits for K1 to drain -> 2.58) and the max-shared carve-out (LaunchCfg::beside_gram).
+            // Only when K4 is long enough to be worth slowing K1 for: estimated from the measured rates
+            // (5.3e14 u8 MACs/s; 1.9e11 reds/s on an L2-resident block, 2.7e10 otherwise).
             const char* kc = std::getenv("KSPIDER_K1_CTAS");
-            lc1.k1_ctas = (kc && std::atoi(kc) > 0 && std::atoi(kc) <= 8) ? std::atoi(kc) : 8;
+            const double t4 = (double)D.n_gram_macs / 5.3e14;
+            const double t1 = (double)(D.n_updates - D.n_gram_updates) / (8 * p.cells <= (96ull << 20) ? 1.9e11 : 2.7e10);
+            const int fit = t4 >= 0.5 * t1 ? (d->g_planes <= 1 ? 3 : 2) : 8;
+            lc1.k1_ctas = (kc && std::atoi(kc) > 0 && std::atoi(kc) <= 8) ? std::atoi(kc) : fit;
+            const char* cv = std::getenv("KSPIDER_CARVEOUT");
+            lc1.beside_gram = lc1.k1_ctas < 8 && !(cv && std::atoi(cv) == 0);
         }
         const void* sm_m = P + D.off_small_members;
         const uint32_t mb = (uint32_t)D.packed_bits;

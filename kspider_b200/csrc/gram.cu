@@ -250,7 +250,7 @@ cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram
 //             (red.global.add.u64).
 // ------------------------------------------------------------------------------------------------
 template <int P>
-__global__ void __launch_bounds__(kThreads, 1) k4_gram(const __grid_constant__ GramParams prm,
+__global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ GramParams prm,
                                                         const __grid_constant__ TriGeom G) {
     constexpr uint32_t NB = 4 / P;
     constexpr uint32_t kStageBytes = (P + NB) * kTileBytes;

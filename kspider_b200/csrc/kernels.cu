@@ -8,6 +8,8 @@
 // Updates of one step land in ONE row of the triangle, in ascending address order.
 #include "kernels.cuh"
 
+#include <cstdlib>
+
 #include <cub/device/device_scan.cuh>
 
 namespace ksb {
@@ -139,6 +141,103 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
     }
 }
 
+// K1 with 32-bit cell arithmetic (dense sink, owned block < 2^32 cells): a row travels through the
+// shuffle as ONE 32-bit word, the virtual cell index of (row, 0) relative to the block -- wrapping,
+// because rowbase = bandstart - band_lo may be "negative"; (row word + column) mod 2^32 is the real
+// cell index -- and which rows are owned comes from the ballot instead of a 64-bit compare.  The red is
+// predicated, not branched around.  About half the instructions per update of the generic kernel:
+// alone the kernel is bound by L2's red rate either way, but beside K4 the issue slots it no longer
+// takes are K4's.
+// tri[cell] += w on the lanes with pred != 0; address arithmetic and predicate stay inside one asm block
+// so that the red is predicated instead of branched around
+__device__ __forceinline__ void red_cell_if(unsigned long long tri, uint32_t cell, unsigned long long w, uint32_t pred) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %3, 0;\n\tmad.wide.u32 a, %1, 8, %0;\n\t@p red.global.add.u64 [a], %2;\n\t}" ::"l"(tri),
+        "r"(cell), "l"(w), "r"(pred)
+        : "memory");
+}
+
+template <class MT>
+__global__ void __launch_bounds__(256) k1_small_c32(const __grid_constant__ K1Params P,
+                                                    const MT* __restrict__ members,
+                                                    const void* __restrict__ weights,
+                                                    const __grid_constant__ TriGeom G,
+                                                    unsigned long long task_begin, unsigned long long task_end) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    const unsigned long long tri = (unsigned long long)G.tri;
+    for (unsigned long long task = task_begin + warp; task < task_end; task += nwarps) {
+        uint32_t lo = 0, hi = P.n_cls;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (P.cls[mid].task_begin <= task) lo = mid; else hi = mid;
+        }
+        const unsigned long long t_in = task - P.cls[lo].task_begin;
+        const unsigned long long n = P.cls[lo].n;
+        const uint32_t s = P.cls[lo].s;
+        const unsigned long long moff = P.cls[lo].member_off, woff = P.cls[lo].weight_off;
+        if (s <= 32) {
+            const uint32_t k = P.cls[lo].k;
+            const uint32_t g = lane / s, a = lane - g * s;
+            const unsigned long long col0 = t_in * k;
+            const bool valid = g < k && col0 + g < n;
+            uint32_t x = 0, w = 0;
+            if (valid) {
+                x = ldm<MT>(members, moff + col0 * s + lane);
+                w = ldw(weights, P.weight_bits, woff + col0 + g);
+            }
+            const bool owned = valid && (x - G.rb < G.nrows);
+            const uint32_t r32 = owned ? (uint32_t)(__ldg(G.rowbase + x) - G.base) : 0u;
+            const uint32_t own = __ballot_sync(KSB_FULL, owned);
+            if (own == 0u) continue;  // no owned row in this task
+            const uint32_t gb = valid ? g * s : 0u;
+            const uint32_t gm = valid ? (own >> gb) & (0xffffffffu >> (32u - s)) : 0u;  // owned positions of this lane's colour
+            const uint32_t ar0 = __reduce_min_sync(KSB_FULL, gm ? (uint32_t)__ffs(gm) - 1u : s);
+            const uint32_t ar1 = min(__reduce_max_sync(KSB_FULL, gm ? 32u - (uint32_t)__clz(gm) : 0u), s - 1u);
+            const uint32_t act = gm & ((1u << a) - 1u);  // steps (row positions) in which this lane adds: owned rows before its own position
+            const unsigned long long ww = w;
+            // four rows per trip: the four shuffles are issued while the warp is converged, then the four
+            // (branched-around) reds; positions past the colour's end have no bit in `act`
+            for (uint32_t ar = ar0; ar < ar1; ar += 4) {
+                const uint32_t src = gb + ar;
+                const uint32_t q0 = __shfl_sync(KSB_FULL, r32, src);
+                const uint32_t q1 = __shfl_sync(KSB_FULL, r32, src + 1u);
+                const uint32_t q2 = __shfl_sync(KSB_FULL, r32, src + 2u);
+                const uint32_t q3 = __shfl_sync(KSB_FULL, r32, src + 3u);
+                const uint32_t m = act >> ar;  // ar < ar1 <= 31
+                red_cell_if(tri, q0 + x, ww, m & 1u);
+                red_cell_if(tri, q1 + x, ww, m & 2u);
+                red_cell_if(tri, q2 + x, ww, m & 4u);
+                red_cell_if(tri, q3 + x, ww, m & 8u);
+            }
+        } else {
+            const unsigned long long mi = moff + t_in * s;
+            const bool v1 = lane + 32 < s;
+            const uint32_t x0 = ldm<MT>(members, mi + lane);
+            const uint32_t x1 = v1 ? ldm<MT>(members, mi + 32 + lane) : 0u;
+            const unsigned long long w = ldw(weights, P.weight_bits, woff + t_in);
+            const bool o0 = x0 - G.rb < G.nrows, o1 = v1 && (x1 - G.rb < G.nrows);
+            const uint32_t r0 = o0 ? (uint32_t)(__ldg(G.rowbase + x0) - G.base) : 0u;
+            const uint32_t r1 = o1 ? (uint32_t)(__ldg(G.rowbase + x1) - G.base) : 0u;
+            const uint32_t own0 = __ballot_sync(KSB_FULL, o0), own1 = __ballot_sync(KSB_FULL, o1);
+            if ((own0 | own1) == 0u) continue;
+#pragma unroll 4
+            for (uint32_t ar = 0; ar < 32; ar++) {
+                const uint32_t r = __shfl_sync(KSB_FULL, r0, ar);
+                if ((own0 >> ar) & 1u) {  // warp-uniform
+                    red_cell_if(tri, r + x0, w, lane > ar);
+                    red_cell_if(tri, r + x1, w, v1);
+                }
+            }
+            for (uint32_t ar = 32; ar + 1 < s; ar++) {
+                const uint32_t r = __shfl_sync(KSB_FULL, r1, ar - 32);
+                red_cell_if(tri, r + x1, w, ((own1 >> (ar - 32)) & 1u) != 0u && v1 && lane + 32 > ar);
+            }
+        }
+    }
+}
+
 cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t member_bits, const void* weights, const TriGeom& g,
                             const LaunchCfg& lc, unsigned long long task_begin, unsigned long long task_end) {
     if (task_end <= task_begin) return cudaSuccess;
@@ -146,14 +245,23 @@ cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t mem
     unsigned long long ctas = (task_end - task_begin + warps_per_cta - 1) / warps_per_cta;
     const unsigned long long cap = (unsigned long long)lc.sms * (unsigned long long)lc.k1_ctas;  // 8 x 256 threads = 2048 resident threads / SM
     if (ctas > cap) ctas = cap;
-    if (member_bits == 10)
-        k1_small<DenseSink, P10><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P10*>(members), weights, g, DenseSink{}, task_begin, task_end);
-    else if (member_bits == 12)
-        k1_small<DenseSink, P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const P12*>(members), weights, g, DenseSink{}, task_begin, task_end);
-    else if (member_bits == 16)
-        k1_small<DenseSink, uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint16_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
-    else
-        k1_small<DenseSink, uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(p, static_cast<const uint32_t*>(members), weights, g, DenseSink{}, task_begin, task_end);
+    // 32-bit cell arithmetic whenever the owned block allows it (KSPIDER_K1_CELLS=64 forces the generic kernel)
+    static const bool force64 = [] { const char* e = std::getenv("KSPIDER_K1_CELLS"); return e && std::atoi(e) == 64; }();
+    const bool c32 = !force64 && g.cells < (1ull << 32);
+    const int carve = lc.beside_gram ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault;
+    auto go = [&](auto kern64, auto kern32, auto mem) {
+        if (c32) {
+            cudaFuncSetAttribute(kern32, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            kern32<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, mem, weights, g, task_begin, task_end);
+        } else {
+            cudaFuncSetAttribute(kern64, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            kern64<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, mem, weights, g, DenseSink{}, task_begin, task_end);
+        }
+    };
+    if (member_bits == 10) go(k1_small<DenseSink, P10>, k1_small_c32<P10>, static_cast<const P10*>(members));
+    else if (member_bits == 12) go(k1_small<DenseSink, P12>, k1_small_c32<P12>, static_cast<const P12*>(members));
+    else if (member_bits == 16) go(k1_small<DenseSink, uint16_t>, k1_small_c32<uint16_t>, static_cast<const uint16_t*>(members));
+    else go(k1_small<DenseSink, uint32_t>, k1_small_c32<uint32_t>, static_cast<const uint32_t*>(members));
     return cudaGetLastError();
 }
 

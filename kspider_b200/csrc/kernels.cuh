@@ -81,6 +81,11 @@ struct LaunchCfg {
     int sms;
     cudaStream_t stream;
     int k1_ctas = 8;  // K1 CTAs (256 threads) per SM; fewer when K4 runs beside it and needs its slot
+    // K4 (one CTA per SM, ~200 KB of shared memory) runs beside this kernel: ask for the maximum shared-memory
+    // carve-out although the kernel itself uses none.  An SM switches its L1 / shared split only when it is
+    // idle, so a K1 grid that got there first with the default (all-L1) split keeps every K4 CTA waiting
+    // until K1 has drained -- the two kernels then run back to back instead of side by side.
+    bool beside_gram = false;
 };
 
 // launchers (return cudaError_t of the launch)
