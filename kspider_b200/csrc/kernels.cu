@@ -158,7 +158,7 @@ __device__ __forceinline__ void red_cell_if(unsigned long long tri, uint32_t cel
 }
 
 template <class MT>
-__global__ void __launch_bounds__(256) k1_small_c32(const __grid_constant__ K1Params P,
+__global__ void __launch_bounds__(256, 6) k1_small_c32(const __grid_constant__ K1Params P,
                                                     const MT* __restrict__ members,
                                                     const void* __restrict__ weights,
                                                     const __grid_constant__ TriGeom G,
@@ -167,19 +167,36 @@ __global__ void __launch_bounds__(256) k1_small_c32(const __grid_constant__ K1Pa
     const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
     const unsigned long long tri = (unsigned long long)G.tri;
-    for (unsigned long long task = task_begin + warp; task < task_end; task += nwarps) {
-        uint32_t lo = 0, hi = P.n_cls;
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (P.cls[mid].task_begin <= task) lo = mid; else hi = mid;
+    unsigned long long task = task_begin + warp;
+    if (task >= task_end) return;
+    // The class of a task is looked up once and then followed: a warp's tasks only move forward through
+    // the class list.  Per class the lane's group / position and the validity of its group are fixed.
+    uint32_t ci = 0;
+    {
+        uint32_t hi = P.n_cls;
+        while (hi - ci > 1) {
+            const uint32_t mid = (ci + hi) >> 1;
+            if (P.cls[mid].task_begin <= task) ci = mid; else hi = mid;
         }
-        const unsigned long long t_in = task - P.cls[lo].task_begin;
-        const unsigned long long n = P.cls[lo].n;
-        const uint32_t s = P.cls[lo].s;
-        const unsigned long long moff = P.cls[lo].member_off, woff = P.cls[lo].weight_off;
+    }
+    unsigned long long c_end = 0;  // first task of the next class; 0 forces the first load below
+    unsigned long long c_begin = 0, n = 0, moff = 0, woff = 0;
+    uint32_t s = 2, k = 1, g = 0, a = 0, gb = 0, smask = 0, below = 0;
+    for (; task < task_end; task += nwarps) {
+        if (task >= c_end) {
+            while (ci + 1 < P.n_cls && P.cls[ci + 1].task_begin <= task) ci++;
+            const K1Class& c = P.cls[ci];
+            c_begin = c.task_begin;
+            c_end = ci + 1 < P.n_cls ? P.cls[ci + 1].task_begin : ~0ull;
+            n = c.n; moff = c.member_off; woff = c.weight_off; s = c.s; k = c.k;
+            g = (lane * (65536u / s + 1u)) >> 16;  // = lane / s for lane < 32, s <= 32 (s > 32: unused)
+            a = lane - g * s;
+            gb = g * s;
+            smask = 0xffffffffu >> (32u - min(s, 32u));
+            below = (1u << a) - 1u;
+        }
+        const unsigned long long t_in = task - c_begin;
         if (s <= 32) {
-            const uint32_t k = P.cls[lo].k;
-            const uint32_t g = lane / s, a = lane - g * s;
             const unsigned long long col0 = t_in * k;
             const bool valid = g < k && col0 + g < n;
             uint32_t x = 0, w = 0;
@@ -191,16 +208,16 @@ __global__ void __launch_bounds__(256) k1_small_c32(const __grid_constant__ K1Pa
             const uint32_t r32 = owned ? (uint32_t)(__ldg(G.rowbase + x) - G.base) : 0u;
             const uint32_t own = __ballot_sync(KSB_FULL, owned);
             if (own == 0u) continue;  // no owned row in this task
-            const uint32_t gb = valid ? g * s : 0u;
-            const uint32_t gm = valid ? (own >> gb) & (0xffffffffu >> (32u - s)) : 0u;  // owned positions of this lane's colour
+            const uint32_t gm = valid ? (own >> gb) & smask : 0u;  // owned positions of this lane's colour
             const uint32_t ar0 = __reduce_min_sync(KSB_FULL, gm ? (uint32_t)__ffs(gm) - 1u : s);
             const uint32_t ar1 = min(__reduce_max_sync(KSB_FULL, gm ? 32u - (uint32_t)__clz(gm) : 0u), s - 1u);
-            const uint32_t act = gm & ((1u << a) - 1u);  // steps (row positions) in which this lane adds: owned rows before its own position
+            const uint32_t act = gm & below;  // steps (row positions) in which this lane adds: owned rows before its own position
+            const uint32_t sb = valid ? gb : 0u;
             const unsigned long long ww = w;
             // four rows per trip: the four shuffles are issued while the warp is converged, then the four
             // (branched-around) reds; positions past the colour's end have no bit in `act`
             for (uint32_t ar = ar0; ar < ar1; ar += 4) {
-                const uint32_t src = gb + ar;
+                const uint32_t src = sb + ar;
                 const uint32_t q0 = __shfl_sync(KSB_FULL, r32, src);
                 const uint32_t q1 = __shfl_sync(KSB_FULL, r32, src + 1u);
                 const uint32_t q2 = __shfl_sync(KSB_FULL, r32, src + 2u);
@@ -252,6 +269,8 @@ cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t mem
     auto go = [&](auto kern64, auto kern32, auto mem) {
         if (c32) {
             cudaFuncSetAttribute(kern32, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            const unsigned long long cap32 = (unsigned long long)lc.sms * (unsigned long long)(lc.k1_ctas < 6 ? lc.k1_ctas : 6);  // 40 registers: 6 resident CTAs / SM
+            if (ctas > cap32) ctas = cap32;  // persistent grid: every CTA must be resident from the start (tasks are strided statically)
             kern32<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, mem, weights, g, task_begin, task_end);
         } else {
             cudaFuncSetAttribute(kern64, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
