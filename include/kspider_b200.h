@@ -270,6 +270,18 @@ void ksb_colors_free(ksb_colors* c);
 /* ostream<<float of the reference = "%g": writes at most 16 bytes, returns length (no NUL). */
 int ksb_format_float(float v, char* buf);
 
+/* ---- ANI column: `kSpider pairwise --estimate-ani` (pykSpider/kSpider2/ks_pairwise.py:29-82) ----------
+ * ksb_ani_column: avg_ani of every record of `r`, in record order, computed on r's device (K8) from the
+ * device-resident records: per row the PRINTED min / max containment (6 significant digits, as the
+ * reference re-reads its own TSV) -> sourmash containment_to_distance(...).ani = 1 - (1 - c ** (1/ksize))
+ * (0 -> 0.0, 1 -> 1.0) -> mean of the two.  ani_out: host, n_rows doubles.  n_invalid: rows where the
+ * reference would raise (printed containment > 1, inf, nan); their value is NaN or out of range.
+ * ksb_format_double_repr: Python's repr(float) (the text ks_pairwise.py:79 writes); buf >= 32 bytes.
+ * ksb_write_ani_column: `P_kSpider_pairwise.ani_col.tsv` -- "avg_ani" header, one repr per row. */
+int ksb_ani_column(const ksb_result* r, int ksize, double* ani_out, uint64_t* n_invalid);
+int ksb_format_double_repr(double v, char* buf);
+int ksb_write_ani_column(const double* ani, uint64_t n, const char* path, int host_threads);
+
 /* ---- synthetic index files (bench / tests): real phmap dump bytes ------------------------- */
 int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uint64_t* color_ids,
                           const uint64_t* offsets, const uint32_t* members, uint64_t n_counts,

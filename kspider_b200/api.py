@@ -255,6 +255,15 @@ class Result:
             check(lib().ksb_cluster_pct(self._h, DIST_COL[dist_type], float(cut_pct), labels.ctypes.data, C.byref(ne)))
         return labels, ne.value
 
+    def ani_column(self, ksize: int):
+        """avg_ani of every record, in record order (K8 on the result's device; ks_pairwise.py:29-82).
+        Returns (float64[n_rows], number of rows for which the reference would raise)."""
+        n = int(self.info.n_rows)
+        out = np.empty(n, dtype=np.float64)
+        bad = C.c_uint64()
+        check(lib().ksb_ani_column(self._h, int(ksize), out.ctypes.data, C.byref(bad)))
+        return out, bad.value
+
     def cluster_into(self, d_labels_ptr: int, dist_type: str = "max_cont", cutoff01: float = 0.0) -> int:
         """Same as cluster(), labels written to DEVICE memory at `d_labels_ptr` (uint32[N] on this result's
         device; e.g. a torch tensor's data_ptr()).  Returns the number of kept edges."""
@@ -282,6 +291,17 @@ def format_float(v: float) -> str:
     buf = C.create_string_buffer(32)
     n = lib().ksb_format_float(C.c_float(v), buf)
     return buf.raw[:n].decode()
+
+
+def format_double_repr(v: float) -> str:
+    buf = C.create_string_buffer(40)
+    n = lib().ksb_format_double_repr(C.c_double(v), buf)
+    return buf.raw[:n].decode()
+
+
+def write_ani_column(ani: np.ndarray, path: str, host_threads: int = 1) -> None:
+    a = np.ascontiguousarray(ani, dtype=np.float64)
+    check(lib().ksb_write_ani_column(a.ctypes.data, a.size, str(path).encode(), int(host_threads)))
 
 
 def cluster_merge(labels_a: np.ndarray, labels_b: np.ndarray) -> np.ndarray:

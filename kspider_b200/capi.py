@@ -111,6 +111,9 @@ _PROTOS = {
     "ksb_colors_device_ms": (C.c_float, [C.c_void_p]),
     "ksb_colors_free": (None, [C.c_void_p]),
     "ksb_format_float": (C.c_int, [C.c_float, C.c_char_p]),
+    "ksb_ani_column": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "ksb_format_double_repr": (C.c_int, [C.c_double, C.c_char_p]),
+    "ksb_write_ani_column": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_int]),
     "ksb_write_index_files": (C.c_int, [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
                                         C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "ksb_bench_red": (C.c_int, [C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),

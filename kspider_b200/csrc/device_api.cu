@@ -1386,6 +1386,49 @@ static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint3
     return rc;
 }
 
+// ANI column (`kSpider pairwise --estimate-ani`, ks_pairwise.py:29-82): avg_ani of every record, in record
+// order, computed on the result's device from the device-resident records (K8) and copied to ani_out.
+// n_invalid = rows for which the reference would raise (containment text > 1, inf or nan).
+int ksb_ani_column(const ksb_result* r, int ksize, double* ani_out, uint64_t* n_invalid) {
+    if (!r || (!ani_out && r->info.n_rows)) { set_error("ksb_ani_column: null argument"); return KSB_ERR_ARG; }
+    if (ksize < 1) { set_error("ksb_ani_column: ksize must be positive"); return KSB_ERR_ARG; }
+    if (n_invalid) *n_invalid = 0;
+    uint64_t total = 0;
+    for (const ksb_segment& sg : r->seg) total += sg.n;
+    if (total == 0) return KSB_OK;
+    int sms = 0;
+    const int dev = check_device(r->device, &sms);
+    if (dev < 0) return dev;
+    cudaStream_t st = g_ctx[dev].stream;
+    double* d_out = nullptr;
+    unsigned long long* d_bad = nullptr;
+    cudaError_t e = cudaSuccess;
+    int rc = KSB_OK;
+    do {
+        if ((e = cudaMallocAsync(&d_out, 8 * total, st)) != cudaSuccess) break;
+        if ((e = cudaMallocAsync(&d_bad, 8, st)) != cudaSuccess) break;
+        if ((e = cudaMemsetAsync(d_bad, 0, 8, st)) != cudaSuccess) break;
+        const LaunchCfg lc{sms, st};
+        uint64_t at = 0;
+        for (const ksb_segment& sg : r->seg) {
+            if (!sg.d_records && sg.n) { e = cudaErrorInvalidValue; break; }
+            if ((e = launch_k8_ani(sg.d_records, sg.n, 1.0 / (double)ksize, d_out + at, d_bad, lc)) != cudaSuccess) break;
+            at += sg.n;
+        }
+        if (e != cudaSuccess) break;
+        unsigned long long nb = 0;
+        if ((e = cudaMemcpyAsync(ani_out, d_out, 8 * total, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+        if ((e = cudaMemcpyAsync(&nb, d_bad, 8, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+        if ((e = cudaStreamSynchronize(st)) != cudaSuccess) break;
+        if (n_invalid) *n_invalid = nb;
+        const_cast<ksb_result*>(r)->info.gpu_launches += r->seg.size();
+    } while (0);
+    if (e != cudaSuccess) { set_error("ksb_ani_column: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); rc = KSB_ERR_CUDA; }
+    if (d_out) cudaFreeAsync(d_out, st);
+    if (d_bad) cudaFreeAsync(d_bad, st);
+    return rc;
+}
+
 }  // extern "C"
 
 // ------------------------------------------------------- multi-GPU label merge + red micro-benchmark

@@ -304,6 +304,77 @@ cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t mem
 }
 
 // ------------------------------------------------------------------------------------------------
+// K8: ANI column (pykSpider/kSpider2/ks_pairwise.py:29-82, `pairwise --estimate-ani`).  Per TSV row the
+// reference parses the PRINTED min / max containment (6 significant digits of the float32) back to a
+// double, runs sourmash.distance_utils.containment_to_distance(c, ksize, scale, n_unique_kmers).ani on
+// each -- c == 0 -> 0.0, c == 1 -> 1.0, else 1 - (1 - c ** (1.0 / ksize)); a distance outside [0, 1]
+// raises -- and writes their mean.  The text round trip is reproduced exactly (text6 below); pow() is
+// CUDA's (<= 2 ulp) where CPython calls glibc's (< 1 ulp), so the column agrees to a few ulp, not bit
+// for bit (tests state the tolerance).
+// ------------------------------------------------------------------------------------------------
+__constant__ double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                  1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+
+// strtod(printf("%g", c)) for a finite float 0 <= c < 10: the six significant decimal digits of the
+// exact binary value, rounded half-to-even on the exact remainder as glibc does (x * 10^k is split
+// exactly into p + err by an fma), then digits / 10^k in ONE correctly rounded division (digits < 2^53
+// and 10^k exact for k <= 22: the classic exact strtod path).  NaN for anything else.
+__device__ double text6(float c) {
+    if (c == 0.0f) return 0.0;
+    if (!(c > 0.0f) || !(c < 10.0f)) return __longlong_as_double(0x7ff8000000000000ll);
+    const double x = (double)c;
+    int e10 = (int)floor(log10(x));
+    double P = 1.0, p = 0.0, err = 0.0;
+    for (int it = 0; it < 4; it++) {
+        const int k = 5 - e10;
+        if (k < 5 || k > 22) return __longlong_as_double(0x7ff8000000000000ll);
+        P = kPow10[k];
+        p = __dmul_rn(x, P);
+        err = __fma_rn(x, P, -p);
+        if (p < 1e5 || (p == 1e5 && err < 0.0)) { e10--; continue; }
+        if (p > 1e6 || (p == 1e6 && err >= 0.0)) { e10++; continue; }
+        break;
+    }
+    const double ip = floor(p);
+    const double t = __dsub_rn(__dsub_rn(p, ip), 0.5);  // exact: p < 2^20, so the fraction is a multiple of ulp(p) >= 2^-36
+    // |err| <= ulp(p)/2 < |t| unless t == 0: the sign of (t + err) is t's, or err's on a tie of p
+    const bool up = t > 0.0 || (t == 0.0 && (err > 0.0 || (err == 0.0 && (((long long)ip) & 1ll))));
+    return __ddiv_rn(up ? ip + 1.0 : ip, P);
+}
+
+__device__ __forceinline__ double ani_of(double c, double inv_k, bool* bad) {
+    if (c == 0.0) return 0.0;   // 1 - 1.0
+    if (c == 1.0) return 1.0;   // 1 - 0.0
+    const double dist = __dsub_rn(1.0, inv_k == 1.0 ? c : pow(c, inv_k));  // ksize 1: c ** 1.0 is c exactly (CUDA pow(c, 1.0) is not always)
+    if (!(dist >= 0.0 && dist <= 1.0)) { *bad = true; return dist; }  // sourmash: ValueError (also NaN from text6)
+    return __dsub_rn(1.0, dist);
+}
+
+__global__ void __launch_bounds__(256) k8_ani(const ksb_record* __restrict__ records, unsigned long long n_rows, double inv_k,
+                                              double* __restrict__ out, unsigned long long* n_bad) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    uint32_t nb = 0;
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+        const float cmin = __ldg(&records[r].min_containment), cmax = __ldg(&records[r].max_containment);
+        bool bad = false;
+        const double a1 = ani_of(text6(cmin), inv_k, &bad);
+        const double a2 = ani_of(text6(cmax), inv_k, &bad);
+        out[r] = __ddiv_rn(__dadd_rn(a1, a2), 2.0);
+        nb += bad ? 1u : 0u;
+    }
+    nb = __reduce_add_sync(KSB_FULL, nb);
+    if ((threadIdx.x & 31u) == 0 && nb) atomicAdd(n_bad, (unsigned long long)nb);
+}
+
+cudaError_t launch_k8_ani(const ksb_record* records, uint64_t n_rows, double inv_k, double* out, unsigned long long* n_bad,
+                          const LaunchCfg& lc) {
+    if (n_rows == 0) return cudaSuccess;
+    const uint64_t want = (n_rows + 255) / 256, cap = (uint64_t)lc.sms * 8;
+    k8_ani<<<(unsigned)(want < cap ? want : cap), 256, 0, lc.stream>>>(records, n_rows, inv_k, out, n_bad);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
 // K2: block-tiled mid/large colours (s > 64).  One CTA item = 256 columns (one per thread, kept in
 // a register) x up to 512 rows.  The rows' member ids are staged into shared memory with one TMA
 // bulk copy (cp.async.bulk + mbarrier), converted once to row addresses, then every warp sweeps the

@@ -145,6 +145,10 @@ cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 
+// K8: ANI column of the records (ks_pairwise.py:29-82); n_bad counts rows whose distance left [0, 1]
+cudaError_t launch_k8_ani(const ksb_record* records, uint64_t n_rows, double inv_k, double* out, unsigned long long* n_bad,
+                          const LaunchCfg& lc);
+
 // K4: int8 tcgen05 Gram path (gram.cu).  One launch handles a CHUNK: a list of (sub-)windows whose
 // bitmaps share one buffer, and a list of work items over them.
 struct GramWinDev {

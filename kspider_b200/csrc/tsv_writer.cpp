@@ -1,6 +1,8 @@
 // Host text side of the path: the pairwise TSV (src/pairwise.cpp:242-275), "%g" float text
 // (ostream<<float with default flags), and the synthetic index-file writer used by tests / bench.
 #include <cerrno>
+#include <charconv>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -139,6 +141,81 @@ int ksb_format_float(float v, char* buf) {
     const int n = snprintf(tmp, sizeof tmp, "%g", (double)v);
     std::memcpy(buf, tmp, (size_t)n);
     return n;
+}
+
+// Python's repr(float) (what ks_pairwise.py:79 writes with f"{avg_ani}"): the shortest digit string that
+// round-trips (std::to_chars), laid out by CPython's rule for format code 'r' -- fixed notation when
+// 1e-4 <= |v| < 1e16 (with ".0" appended to integers), otherwise d[.ddd]e+XX with at least two exponent
+// digits.  buf needs 32 bytes; returns the length.
+int ksb_format_double_repr(double v, char* buf) {
+    if (std::isnan(v)) { std::memcpy(buf, "nan", 3); return 3; }
+    int n = 0;
+    if (std::signbit(v)) { buf[n++] = '-'; v = -v; }
+    if (std::isinf(v)) { std::memcpy(buf + n, "inf", 3); return n + 3; }
+    if (v == 0.0) { std::memcpy(buf + n, "0.0", 3); return n + 3; }
+    char sci[40];
+    const auto res = std::to_chars(sci, sci + sizeof sci, v, std::chars_format::scientific);  // d[.ddd]e[+-]XX, shortest
+    char digits[24];
+    int nd = 0, e10 = 0;
+    const char* q = sci;
+    for (; q < res.ptr && *q != 'e'; q++)
+        if (*q != '.') digits[nd++] = *q;
+    if (q < res.ptr) {
+        q++;
+        const bool neg = *q == '-';
+        if (*q == '+' || *q == '-') q++;
+        for (; q < res.ptr; q++) e10 = e10 * 10 + (*q - '0');
+        if (neg) e10 = -e10;
+    }
+    if (e10 < -4 || e10 >= 16) {  // CPython: decpt <= -4 || decpt > 16, decpt = e10 + 1
+        buf[n++] = digits[0];
+        if (nd > 1) { buf[n++] = '.'; std::memcpy(buf + n, digits + 1, (size_t)nd - 1); n += nd - 1; }
+        buf[n++] = 'e';
+        buf[n++] = e10 < 0 ? '-' : '+';
+        const int ae = e10 < 0 ? -e10 : e10;
+        if (ae >= 100) buf[n++] = (char)('0' + ae / 100);
+        buf[n++] = (char)('0' + (ae / 10) % 10);
+        buf[n++] = (char)('0' + ae % 10);
+    } else if (e10 < 0) {
+        buf[n++] = '0'; buf[n++] = '.';
+        for (int i = 0; i < -e10 - 1; i++) buf[n++] = '0';
+        std::memcpy(buf + n, digits, (size_t)nd); n += nd;
+    } else {
+        for (int i = 0; i <= e10; i++) buf[n++] = i < nd ? digits[i] : '0';
+        buf[n++] = '.';
+        if (nd > e10 + 1) { std::memcpy(buf + n, digits + e10 + 1, (size_t)(nd - e10 - 1)); n += nd - e10 - 1; }
+        else buf[n++] = '0';
+    }
+    return n;
+}
+
+// `P_kSpider_pairwise.ani_col.tsv` (ks_pairwise.py:33,64-80): header "avg_ani", one repr(float) per row.
+int ksb_write_ani_column(const double* ani, uint64_t n, const char* path, int host_threads) {
+    if ((!ani && n) || !path) { ksb::set_error("ksb_write_ani_column: null argument"); return KSB_ERR_ARG; }
+    FILE* f = fopen(path, "wb");
+    if (!f) { ksb::set_error("cannot write %s: %s", path, strerror(errno)); return KSB_ERR_IO; }
+    int rc = fputs("avg_ani\n", f) < 0 ? KSB_ERR_IO : KSB_OK;
+    const int threads = host_threads < 1 ? 1 : host_threads;
+    std::vector<std::string> bufs(threads);
+    const uint64_t kBatch = 1ull << 21;
+    for (uint64_t b0 = 0; b0 < n && rc == KSB_OK; b0 += kBatch) {
+        const uint64_t bn = std::min(kBatch, n - b0);
+        ksb::parallel_chunks(bn, threads, [&](int t, uint64_t b, uint64_t e) {
+            std::string& s = bufs[t];
+            s.resize((e - b) * 32);
+            char* const base = &s[0];
+            char* line = base;
+            for (uint64_t i = b; i < e; i++) { line += ksb_format_double_repr(ani[b0 + i], line); *line++ = '\n'; }
+            s.resize((size_t)(line - base));
+        });
+        for (auto& s : bufs) {
+            if (!s.empty() && fwrite(s.data(), 1, s.size(), f) != s.size()) rc = KSB_ERR_IO;
+            s.clear();
+        }
+    }
+    if (fclose(f) != 0) rc = KSB_ERR_IO;
+    if (rc == KSB_ERR_IO) ksb::set_error("write error on %s", path);
+    return rc;
 }
 
 int ksb_write_tsv(const ksb_result* r, const char* path, int host_threads) { return ksb::write_tsv_impl(r, path, host_threads, false); }
