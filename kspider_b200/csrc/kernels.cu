@@ -263,7 +263,8 @@ cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t mem
     const unsigned long long cap = (unsigned long long)lc.sms * (unsigned long long)lc.k1_ctas;  // 8 x 256 threads = 2048 resident threads / SM
     if (ctas > cap) ctas = cap;
     // 32-bit cell arithmetic whenever the owned block allows it (KSPIDER_K1_CELLS=64 forces the generic kernel)
-    static const bool force64 = [] { const char* e = std::getenv("KSPIDER_K1_CELLS"); return e && std::atoi(e) == 64; }();
+    const char* k1c = std::getenv("KSPIDER_K1_CELLS");
+    const bool force64 = k1c && std::atoi(k1c) == 64;
     const bool c32 = !force64 && g.cells < (1ull << 32);
     const int carve = lc.beside_gram ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault;
     auto go = [&](auto kern64, auto kern32, auto mem) {

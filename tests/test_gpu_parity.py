@@ -279,6 +279,28 @@ def test_banded_accumulator_on_clade_structured_index(ksb):
     assert_records_equal(dev.run_all_passes().records(), want)
 
 
+@pytest.mark.parametrize("cells", ["32", "64"])
+@pytest.mark.parametrize("bits", ["10", "12", "16", "32"])
+def test_k1_kernels_and_member_packings_agree(ksb, cells, bits, monkeypatch):
+    """K1 has two kernels (k1_small_c32: 32-bit cell arithmetic, the default below 2^32 owned cells;
+    k1_small: 64-bit row addresses, also the spill sink's) and the small / Gram member sections four
+    packings (10-bit <= 1024 samples, 12-bit <= 4096, u16, u32).  Every combination, on the whole
+    triangle and on row blocks (where the owned-row runs and the ballot masks matter), against the
+    oracle.  No Gram routing, so that all colours <= 64 go through K1."""
+    monkeypatch.setenv("KSPIDER_K1_CELLS", cells)
+    monkeypatch.setenv("KSPIDER_GRAM", "off")
+    if bits != "10":
+        monkeypatch.setenv("KSPIDER_MEMBER_BITS", bits)
+    csr = random_csr(seed=123, n_samples=700, n_colors=9000, s_lo=1, s_hi=64, big=(31, 32, 33, 63, 64), zero_every=37)
+    want = oracle_records(csr)
+    idx = ksb.Index.from_csr(**csr, host_threads=2)
+    assert_records_equal(idx.pairwise().records(), want)
+    parts = [idx.pairwise(rank=r, world=3).records() for r in range(3)]
+    assert_records_equal(np.concatenate(parts), want)
+    parts = [idx.shard(r, 5).pairwise().records() for r in range(5)]
+    assert_records_equal(np.concatenate(parts), want)
+
+
 @pytest.mark.parametrize("world", [2, 3, 7])
 def test_row_block_shards_equal_row_blocks(ksb, world):
     """A device made from rank r's shard produces the same records as the whole index run with
