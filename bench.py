@@ -465,6 +465,9 @@ def main_b200(args):
             red[nm + "_ops_per_s"] = n_ops / (bench_red(cells, n_ops, 64, pat, 3) * 1e-3)
         red["cells"] = cells
         red["kernel_frac_of_warp_contiguous"] = k_upd / (k_ms * 1e-3) / red["warp_contiguous_ops_per_s"] if k_ms > 0 else None
+        # the atomic kernel's updates land on member-random columns of a row: its honest ceiling is the RANDOM rate
+        red["kernel_frac_of_random"] = k_upd / (k_ms * 1e-3) / red["random_ops_per_s"] if k_ms > 0 else None
+        red["kernel"] = kname
     except Exception as e:  # the micro-benchmark is informative only
         red = {"error": str(e)}
 
