@@ -77,6 +77,17 @@ def test_oracle_restates_the_sourmash_formula():
         containment_to_ani(float("inf"), 21)
 
 
+def test_estimate_ani_preconditions_need_no_device(built_lib, tmp_path):
+    """ks_pairwise.py:35-36,44-45: the TSV must exist and a scale must be given -- checked before any GPU work"""
+    from kspider_b200.ani import estimate_ani
+    prefix = str(tmp_path / "nothing")
+    with pytest.raises(FileNotFoundError):
+        estimate_ani(prefix, 1000)
+    open(prefix + "_kSpider_pairwise.tsv", "w").write("source_1\tsource_2\tshared_kmers\tmin_containment\tavg_containment\tmax_containment\n")
+    with pytest.raises(ValueError):
+        estimate_ani(prefix, 0)
+
+
 @pytest.fixture(scope="module")
 def ksb(built_lib):
     from kspider_b200.capi import check
