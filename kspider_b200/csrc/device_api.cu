@@ -1366,6 +1366,12 @@ static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint3
         cudaEventRecord(e0, st);
         if ((e = cudaMemsetAsync(d_edges, 0, 8, st)) != cudaSuccess) break;
         if ((e = launch_k7_init(d_parent, N, lc)) != cudaSuccess) break;
+        const bool hook = !(std::getenv("KSPIDER_HOOK_MIN") && std::atoi(std::getenv("KSPIDER_HOOK_MIN")) == 0);
+        if (hook) {
+            for (const ksb_segment& s : r->seg)
+                if ((e = launch_k6_hook_min(s.d_records, s.d_pairs, dist_col == 5 ? reinterpret_cast<const float*>(s.d_pairs + s.n) : nullptr, s.n, dist_col, cstar, d_parent, lc)) != cudaSuccess) break;
+            if (e != cudaSuccess) break;
+        }
         for (const ksb_segment& s : r->seg)
             if ((e = launch_k67_union(s.d_records, s.d_pairs, dist_col == 5 ? reinterpret_cast<const float*>(s.d_pairs + s.n) : nullptr, s.n, dist_col, cstar, d_parent, d_edges, lc)) != cudaSuccess) break;
         if (e != cudaSuccess) break;
@@ -1378,7 +1384,7 @@ static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint3
         if (n_edges) *n_edges = ne;
         ksb_result* rw = const_cast<ksb_result*>(r);
         rw->info.t.cluster_ms = ev_ms(e0, e1);
-        rw->info.gpu_launches += 2 + r->seg.size();
+        rw->info.gpu_launches += 2 + (hook ? 2 : 1) * r->seg.size();
     } while (0);
     if (e != cudaSuccess) { set_error("ksb_cluster: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); rc = KSB_ERR_CUDA; }
     if (d_parent && d_parent != d_labels_out) cudaFreeAsync(d_parent, st);

@@ -809,12 +809,43 @@ __device__ __forceinline__ void uf_union(uint32_t* parent, uint32_t a, uint32_t 
     }
 }
 
+// K6a: before any union, every kept edge (i < j) lowers parent[j] to i with one fire-and-forget
+// atomicMin.  Each link joins two samples that ARE connected and keeps parent[x] <= x, so the result is a
+// valid union-find forest whose roots are the minima of their trees; in clique-like components (a clade:
+// 50 samples, 1225 kept edges) it already is the final star, and the unions of K6b -- which still process
+// EVERY edge, so nothing depends on this pass for correctness -- find equal roots after two loads instead
+// of fighting over the same few roots with CAS retries.  Must run over all segments before the first union.
+__global__ void __launch_bounds__(256) k6_hook_min(const ksb_record* __restrict__ records,
+                                                   const unsigned long long* __restrict__ pairs,
+                                                   const float* __restrict__ colvals, unsigned long long n_rows,
+                                                   int dist_col, float cstar, uint32_t* parent) {
+    // 8 independent coalesced loads per thread: with one load in flight per thread the scan ran at 2.3 TB/s
+    constexpr uint32_t R = 8;
+    const unsigned long long span = 256ull * R;
+    for (unsigned long long base = (unsigned long long)blockIdx.x * span; base < n_rows; base += (unsigned long long)gridDim.x * span) {
+        float c[R];
+#pragma unroll
+        for (uint32_t k = 0; k < R; k++) {
+            const unsigned long long r = base + k * 256u + threadIdx.x;
+            c[k] = -INFINITY;
+            if (r < n_rows) c[k] = colvals ? __ldg(colvals + r) : __ldg(&records[r].min_containment + (dist_col - 3));
+        }
+#pragma unroll
+        for (uint32_t k = 0; k < R; k++) {
+            const unsigned long long r = base + k * 256u + threadIdx.x;
+            if (r >= n_rows || c[k] < cstar) continue;  // NaN is kept
+            const unsigned long long ij = __ldg(pairs + r);
+            atomicMin(parent + (uint32_t)ij, (uint32_t)(ij >> 32));
+        }
+    }
+}
+
 // Threshold and union are decoupled inside the CTA: a pass over 4 x 256 rows (four independent coalesced
 // loads per thread) appends the kept edges to a shared-memory queue, and the unions are run 256 at a time,
 // one per thread, only when the queue holds a full round (the rest is carried to the next pass).  With the
 // union done in place (`if (keep) uf_union`) a warp waited ~2.5 us of dependent L2 accesses for the two or
 // three lanes that had an edge before it could test its next 32 rows: cfg4 (5e7 rows, 5 % kept) 0.37 ms.
-constexpr uint32_t kUnionRows = 4;  // rows per thread and pass
+constexpr uint32_t kUnionRows = 8;  // rows per thread and pass
 __global__ void __launch_bounds__(256) k67_union(const ksb_record* __restrict__ records,
                                                  const unsigned long long* __restrict__ pairs,
                                                  const float* __restrict__ colvals,  // dense copy of the column, or null
@@ -889,6 +920,15 @@ cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
     k67_union<<<(unsigned)ctas, 256, 0, lc.stream>>>(records, pairs, colvals, n_rows, dist_col, cstar, parent, n_edges);
+    return cudaGetLastError();
+}
+cudaError_t launch_k6_hook_min(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
+                               int dist_col, float cstar, uint32_t* parent, const LaunchCfg& lc) {
+    if (n_rows == 0) return cudaSuccess;
+    unsigned long long ctas = (n_rows + 2047) / 2048;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    k6_hook_min<<<(unsigned)ctas, 256, 0, lc.stream>>>(records, pairs, colvals, n_rows, dist_col, cstar, parent);
     return cudaGetLastError();
 }
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc) {

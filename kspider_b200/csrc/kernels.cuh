@@ -142,6 +142,8 @@ cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const
 // K6+K7
 cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
                              int dist_col, float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc);
+cudaError_t launch_k6_hook_min(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
+                               int dist_col, float cstar, uint32_t* parent, const LaunchCfg& lc);
 cudaError_t launch_k7_init(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 cudaError_t launch_k7_compress(uint32_t* parent, uint32_t n, const LaunchCfg& lc);
 
