@@ -84,6 +84,7 @@ struct ksb_device {
     void* d_scan_tmp = nullptr;
     size_t scan_tmp_bytes = 0;
     uint64_t post_blocks_alloc = 0;
+    int block_rows_pass = -1;  // pass whose K5 block rows sit behind the two scan arrays of d_block_counts (-1: none)
     // K4 (Gram) scratch: bitmap of one chunk of colours + weight byte planes
     uint32_t* d_gbits = nullptr;
     uint8_t* d_gwq = nullptr;
@@ -324,7 +325,8 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
     KSB_CUDA(cudaMallocAsync(&d->d_tri, 8 * (cells + 8), d->stream));
     if (d->desc.n_zero_colors) KSB_CUDA(cudaMallocAsync(&d->d_touched, 4 * (cells / 32 + 2), d->stream));
     d->post_blocks_alloc = post_blocks(cells) + 1;
-    KSB_CUDA(cudaMallocAsync(&d->d_block_counts, 8 * d->post_blocks_alloc * 2, d->stream));
+    KSB_CUDA(cudaMallocAsync(&d->d_block_counts, 8 * d->post_blocks_alloc * 3, d->stream));  // counts, offsets, u32 block rows
+    d->block_rows_pass = -1;
     d->scan_tmp_bytes = 0;
     KSB_CUDA(scan_block_counts(nullptr, &d->scan_tmp_bytes, d->d_block_counts, d->d_block_counts + d->post_blocks_alloc,
                                d->post_blocks_alloc, d->stream));
@@ -1008,7 +1010,13 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
             seg.n = n_rows;
             r->seg.push_back(seg);
             const uint8_t* P = d->d_payload;
-            KSB_CUDA_R(launch_k5_emit(g, d->d_touched, offsets, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals),
+            uint32_t* block_rows = reinterpret_cast<uint32_t*>(d->d_block_counts + 2 * d->post_blocks_alloc);
+            if (d->block_rows_pass != d->cur_pass) {  // geometry of the pass: computed once, reused by every later post pass
+                KSB_CUDA_R(launch_k5_block_rows(g, block_rows, lc));
+                d->block_rows_pass = d->cur_pass;
+                d->launches++;
+            }
+            KSB_CUDA_R(launch_k5_emit(g, d->d_touched, offsets, block_rows, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals),
                                       reinterpret_cast<const uint32_t*>(P + d->desc.off_sample_ids), seg.d_records, seg.d_pairs, reinterpret_cast<float*>(seg.d_pairs + n_rows), lc));
             d->launches++;
         }

@@ -637,12 +637,29 @@ __device__ __forceinline__ void containment(unsigned long long shared, uint32_t 
     cavg = canon_nan(__double2float_rn(__ddiv_rn((double)sum, 2.0)));
 }
 
+// Row of the first cell of every K5 block (2048 cells) of the owned block: static geometry, computed once
+// per pass.  k5_emit starts its per-lane row search from it -- between this block's row and the next
+// block's, a handful of rows -- instead of running 17 dependent bandstart loads over all N rows per warp.
+__global__ void __launch_bounds__(256) k5_block_rows(const __grid_constant__ TriGeom G, unsigned long long n_blocks,
+                                                     uint32_t* __restrict__ block_rows) {
+    const unsigned long long b = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    const unsigned long long g0 = G.base + b * kPostChunk;
+    uint32_t lo = G.rb, hi = G.rb + G.nrows;  // last row with bandstart <= g0
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(G.bandstart + mid) <= g0) lo = mid; else hi = mid;
+    }
+    block_rows[b] = lo;
+}
+
 // Emit pass.  A warp owns 256 consecutive cells and takes them 32 at a time (lane = cell), so the
 // flagged lanes of one step write CONSECUTIVE records: the record stores of a warp instruction fill
 // whole 32-byte sectors instead of one scattered sector per lane.
 __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ TriGeom G,
                                                         const uint32_t* __restrict__ touched,
                                                         const unsigned long long* __restrict__ block_offsets,
+                                                        const uint32_t* __restrict__ block_rows,
                                                         const uint32_t* __restrict__ totals,
                                                         const uint32_t* __restrict__ sample_ids,
                                                         ksb_record* __restrict__ records,
@@ -678,7 +695,10 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
     unsigned long long out = block_offsets[blockIdx.x] + wbase;
     // decode (i,j) of this lane's first cell, then walk 32 cells per step
     const unsigned long long g0 = G.base + wcell0 + lane;
-    uint32_t lo = G.rb, hi = G.rb + G.nrows;  // last row with bandstart <= g0 (rows with an empty band share their start)
+    // last row with bandstart <= g0 (rows with an empty band share their start): it lies between the row of
+    // this block's first cell and the row of the next block's first cell (k5_block_rows)
+    uint32_t lo = __ldg(block_rows + blockIdx.x);
+    uint32_t hi = blockIdx.x + 1u < gridDim.x ? __ldg(block_rows + blockIdx.x + 1u) + 1u : G.rb + G.nrows;
     while (hi - lo > 1) {
         const uint32_t mid = (lo + hi) >> 1;
         if (__ldg(G.bandstart + mid) <= g0) lo = mid; else hi = mid;
@@ -729,12 +749,19 @@ cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsi
     return cudaGetLastError();
 }
 
+cudaError_t launch_k5_block_rows(const TriGeom& g, uint32_t* block_rows, const LaunchCfg& lc) {
+    const uint64_t nb = post_blocks(g.cells);
+    if (nb == 0) return cudaSuccess;
+    k5_block_rows<<<(unsigned)((nb + 255) / 256), 256, 0, lc.stream>>>(g, nb, block_rows);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const unsigned long long* block_offsets,
-                           const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
+                           const uint32_t* block_rows, const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
                            unsigned long long* pairs, float* cmax, const LaunchCfg& lc) {
     const uint64_t nb = post_blocks(g.cells);
     if (nb == 0) return cudaSuccess;
-    k5_emit<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_offsets, totals, sample_ids, records,
+    k5_emit<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_offsets, block_rows, totals, sample_ids, records,
                                                          pairs, cmax);
     return cudaGetLastError();
 }

@@ -135,8 +135,10 @@ constexpr uint32_t kPostChunk = kPostThreads * kPostPerThread;
 inline uint64_t post_blocks(uint64_t cells) { return (cells + kPostChunk - 1) / kPostChunk; }
 cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsigned long long* block_counts,
                             const LaunchCfg& lc);
+// block_rows[b] = row of the first cell of K5 block b (post_blocks(cells) entries): static per pass
+cudaError_t launch_k5_block_rows(const TriGeom& g, uint32_t* block_rows, const LaunchCfg& lc);
 cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const unsigned long long* block_offsets,
-                           const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
+                           const uint32_t* block_rows, const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
                            unsigned long long* pairs, float* cmax, const LaunchCfg& lc);
 
 // K6+K7
