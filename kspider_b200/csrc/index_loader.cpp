@@ -260,34 +260,49 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             // per window: keep it only if the tensor path wins (bitmap build + MMAs + per-item overhead + one pass of reds)
             double gain = 0.0;
             std::vector<std::pair<uint64_t, uint64_t>> kept;  // [begin, end) ranges of cand
+            std::vector<std::pair<uint64_t, uint64_t>> kept_span;  // (first sample, width) of the kept windows
             for (uint64_t b = 0; b < cand.size();) {
-                uint64_t e = b, upd = 0, mem = 0;
+                uint64_t e = b, upd = 0, mem = 0, lo = ~0ull, hi = 0;
                 while (e < cand.size() && cand[e].first == cand[b].first) {
-                    const uint64_t sz = raw.off[cand[e].second + 1] - raw.off[cand[e].second];
+                    const uint64_t c = cand[e].second, sz = raw.off[c + 1] - raw.off[c];
                     upd += sz * (sz - 1) / 2;
                     mem += sz;
+                    lo = std::min<uint64_t>(lo, compact(raw.members[raw.off[c]]));
+                    hi = std::max<uint64_t>(hi, (uint64_t)compact(raw.members[raw.off[c + 1] - 1]) + 1);
                     e++;
                 }
                 const Level& lv = levels[cand[b].first & 0xFF];
-                const double width = (double)lv.width, tiles = width / kGramTile;
+                // The grid window only decides which colours go together; the window K4 works on is the range
+                // of samples its colours really touch, from the first one (tiles may start at any sample) to the
+                // last, rounded up to whole tiles.  A 1000-sample family that the grid puts into a 2048-wide window
+                // (span <= width / 2) needs 8 x 8 tiles, not 16 x 16: 36 tile pairs instead of 136.
+                const uint64_t span_w = std::min<uint64_t>(lv.width, (hi - lo + kGramTile - 1) / kGramTile * kGramTile);
+                const double width = (double)span_w, tiles = width / kGramTile;
                 const double kpad = (double)((e - b + kGramKBlock - 1) / kGramKBlock * kGramKBlock);
                 const double rate = lv.width >= 4 * kGramTile ? kGramMacRate : 0.5 * kGramMacRate;
                 const double t_gram = width * width * kpad * (double)planes / rate + (double)mem / 1.0e11 +
                                       tiles * (tiles + 1) / 2 / (double)(4 / planes) * 30e-9 + width * width / 2 / kGramRedRate;
                 const double t_red = (double)upd / kGramRedRate;
-                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); gain += t_red - t_gram; }
+                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); kept_span.emplace_back(lo, span_w); gain += t_red - t_gram; }
                 b = e;
             }
-            if (forced < 2 && gain < 30e-6) kept.clear();  // launches + memsets of the path itself
+            if (forced < 2 && gain < 30e-6) { kept.clear(); kept_span.clear(); }  // launches + memsets of the path itself
             std::fill(gkey.begin(), gkey.end(), NOKEY);
             uint64_t smallest = ~0ull;
-            for (auto& r : kept) {
+            const bool shrink = !(std::getenv("KSPIDER_GRAM_SHRINK") && std::atoi(std::getenv("KSPIDER_GRAM_SHRINK")) == 0);
+            for (size_t ki = 0; ki < kept.size(); ki++) {
+                auto& r = kept[ki];
                 const Level& lv = levels[cand[r.first].first & 0xFF];
                 GramWin w;
                 w.c0 = gram_list.size();
                 w.n = (uint32_t)(r.second - r.first);
-                w.x0 = (uint32_t)(cand[r.first].first >> 8);
-                w.width = (uint32_t)std::min<uint64_t>(lv.width, (npad - w.x0 + kGramTile - 1) / kGramTile * kGramTile);
+                if (shrink) {
+                    w.x0 = (uint32_t)kept_span[ki].first;
+                    w.width = (uint32_t)kept_span[ki].second;
+                } else {
+                    w.x0 = (uint32_t)(cand[r.first].first >> 8);
+                    w.width = (uint32_t)std::min<uint64_t>(lv.width, (npad - w.x0 + kGramTile - 1) / kGramTile * kGramTile);
+                }
                 w.pad = 0;
                 gwins.push_back(w);
                 for (uint64_t i = r.first; i < r.second; i++) {
