@@ -195,10 +195,25 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
             const unsigned long long o = sm_off[k];
             const uint32_t s = (uint32_t)(sm_off[k + 1] - o);
             const uint32_t bit = 1u << (k & 31u), word = k >> 5;
-#pragma unroll 4
-            for (uint32_t a = 32u + lane; a < s; a += 32) {
-                const uint32_t xx = ldm<MT>(gram_members, o + a) - w.x0 - s0;
-                if (xx < slen) atomicOr(sm + 4u * xx + word, bit);
+            if (s <= 96u) {  // one or two more members per lane: the plain loop (the batched one costs cfg2's s <= 64 colours 8 %)
+                for (uint32_t a = 32u + lane; a < s; a += 32) {
+                    const uint32_t xx = ldm<MT>(gram_members, o + a) - w.x0 - s0;
+                    if (xx < slen) atomicOr(sm + 4u * xx + word, bit);
+                }
+                continue;
+            }
+            // eight independent loads per lane before the first atomic: a 500-member colour is two memory
+            // latencies instead of fifteen dependent load -> atomicOr steps
+            for (uint32_t a0 = 32u + lane; a0 < s; a0 += 256u) {
+                uint32_t xs[8];
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) {
+                    const uint32_t a = a0 + 32u * u;
+                    xs[u] = a < s ? ldm<MT>(gram_members, o + a) - w.x0 - s0 : 0xFFFFFFFFu;
+                }
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++)
+                    if (xs[u] < slen) atomicOr(sm + 4u * xs[u] + word, bit);
             }
         }
         if (seg == 0 && tid < kKB) {
