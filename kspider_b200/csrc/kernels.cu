@@ -7,6 +7,7 @@
 // when this GPU does not own the row), so one update is: add 8*column, red.global.add.u64.
 // Updates of one step land in ONE row of the triangle, in ascending address order.
 #include "kernels.cuh"
+#include "ddpow.hpp"
 
 #include <cstdlib>
 
@@ -309,9 +310,10 @@ cudaError_t launch_k1_spill(const K1Params& p, const void* members, uint32_t mem
 // reference parses the PRINTED min / max containment (6 significant digits of the float32) back to a
 // double, runs sourmash.distance_utils.containment_to_distance(c, ksize, scale, n_unique_kmers).ani on
 // each -- c == 0 -> 0.0, c == 1 -> 1.0, else 1 - (1 - c ** (1.0 / ksize)); a distance outside [0, 1]
-// raises -- and writes their mean.  The text round trip is reproduced exactly (text6 below); pow() is
-// CUDA's (<= 2 ulp) where CPython calls glibc's (< 1 ulp), so the column agrees to a few ulp, not bit
-// for bit (tests state the tolerance).
+// raises -- and writes their mean.  The text round trip is reproduced exactly (text6 below); the power is
+// a double-double pow (ddpow.hpp, correctly rounded in practice) where CPython calls glibc's (< 1 ulp, not
+// always correctly rounded), so ~99.9 % of the values are bit-identical and the rest differ by one ulp
+// (tests state the tolerance).
 // ------------------------------------------------------------------------------------------------
 __constant__ double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
                                   1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
@@ -346,7 +348,10 @@ __device__ double text6(float c) {
 __device__ __forceinline__ double ani_of(double c, double inv_k, bool* bad) {
     if (c == 0.0) return 0.0;   // 1 - 1.0
     if (c == 1.0) return 1.0;   // 1 - 0.0
-    const double dist = __dsub_rn(1.0, inv_k == 1.0 ? c : pow(c, inv_k));  // ksize 1: c ** 1.0 is c exactly (CUDA pow(c, 1.0) is not always)
+    // c ** (1.0 / ksize): ksize 1 -> c exactly; otherwise the double-double pow of ddpow.hpp (correctly rounded but for
+    // ~2^-45 of the cases; CUDA's pow() is <= 2 ulp, CPython's is glibc's < 1 ulp)
+    const double pw = inv_k == 1.0 ? c : ((c > 0.0 && c < 1.0) ? dd_pow(c, inv_k) : pow(c, inv_k));
+    const double dist = __dsub_rn(1.0, pw);
     if (!(dist >= 0.0 && dist <= 1.0)) { *bad = true; return dist; }  // sourmash: ValueError (also NaN from text6)
     return __dsub_rn(1.0, dist);
 }

@@ -4,8 +4,10 @@ CPU: the repr(float) formatter against Python's own, the column writer, the orac
 hand-computed values.  GPU (-m gpu): K8 through the C-ABI against oracle/ani_oracle.py —
   * ksize = 1: pow(c, 1.0) is exact, so the column must be BIT-IDENTICAL; this pins the text round
     trip float32 -> "%g" -> double (text6) on every row;
-  * ksize = 21 / 31: CUDA's pow (<= 2 ulp) against CPython's (glibc, < 1 ulp) on values in (0, 1]:
-    tolerance 4 ulp of 1.0 = 4 * 2**-53 absolute, stated here as the bar for this floating-point column.
+  * ksize = 21 / 31: the device's double-double pow (csrc/ddpow.hpp, correctly rounded in practice) against
+    CPython's (glibc, < 1 ulp but not always correctly rounded) on values in (0, 1]: tolerance 2 ulp of 1.0 =
+    2 * 2**-53 absolute, and at least 99 % of the rows bit-identical, stated here as the bar for this
+    floating-point column (a CPU check of the same header against glibc: 0.09 % of 2e6 values differ, by 1 ulp).
 """
 import math
 import os
@@ -17,7 +19,7 @@ import pytest
 
 from util import random_csr
 
-TOL = 4 * 2.0 ** -53
+TOL = 2 * 2.0 ** -53
 
 
 def consistent_totals(csr):
@@ -112,7 +114,7 @@ def test_ani_column_against_oracle(ksb, ksize):
         assert np.array_equal(got.view(np.uint64), want.view(np.uint64))
     else:
         assert np.max(np.abs(got - want)) <= TOL
-        assert np.mean(got == want) > 0.5  # most rows are bit-identical; the rest differ in the last place
+        assert np.mean(got == want) > 0.99  # the rest differ in the last place
     res.close()
     idx.close()
 
