@@ -90,6 +90,50 @@ def test_estimate_ani_preconditions_need_no_device(built_lib, tmp_path):
         estimate_ani(prefix, 0)
 
 
+DDPOW_CHECK = r"""
+#include "ddpow.hpp"
+#include <cstdio>
+#include <cstdlib>
+#include <random>
+int main() {
+    std::mt19937_64 rng(7);
+    long bad = 0, n = 0, worse = 0;
+    const int ks[5] = {21, 31, 51, 2, 7};
+    for (int ki = 0; ki < 5; ki++) {
+        const double e = 1.0 / ks[ki];
+        for (int i = 0; i < 60000; i++) {
+            char buf[64];  // six-digit decimals like the TSV text, over the range of containments
+            snprintf(buf, sizeof buf, "%.0fe%d", (double)(100000 + rng() % 900000), -6 - (int)(rng() % 10));
+            const double x = strtod(buf, nullptr);
+            if (!(x > 0 && x < 1)) continue;
+            const double a = ksb::dd_pow(x, e), b = pow(x, e);
+            n++;
+            if (a != b) { bad++; if (a != nextafter(b, 0.0) && a != nextafter(b, 2.0)) worse++; }
+        }
+    }
+    printf("%ld %ld %ld\n", n, bad, worse);
+    return 0;
+}
+"""
+
+
+def test_ddpow_host_build_agrees_with_glibc(tmp_path):
+    """K8's power function (csrc/ddpow.hpp, every step an explicit IEEE operation) compiled for the host with
+    contraction off: against glibc's pow -- what CPython's float ** float calls -- on 3e5 six-digit inputs it may
+    differ on a fraction of a per cent (glibc is < 1 ulp, not correctly rounded), and never by more than one ulp."""
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    src = tmp_path / "ddpow_check.cpp"
+    src.write_text(DDPOW_CHECK)
+    exe = tmp_path / "ddpow_check"
+    inc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "kspider_b200", "csrc")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-I", inc, str(src), "-o", str(exe)], check=True)
+    n, bad, worse = (int(v) for v in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split())
+    assert n > 250000 and worse == 0 and bad / n < 0.003, (n, bad, worse)
+
+
 @pytest.fixture(scope="module")
 def ksb(built_lib):
     from kspider_b200.capi import check
