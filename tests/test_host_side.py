@@ -281,3 +281,30 @@ def test_row_block_shards_hold_exactly_the_needed_colours(built_lib, world, bits
         with pytest.raises(Exception):
             Index.from_blob(b"\0" * len(sh.descriptor()), sh.payload())
     assert total == idx.info.n_updates
+
+
+def test_gram_windows_shrink_to_the_touched_samples(built_lib, monkeypatch):
+    """Loader: the grid window of a Gram-routed colour only groups colours; the window K4 works on is the range
+    of samples they touch.  Same routed colours either way, never more MACs, and far fewer when a clade-local
+    family straddles the grid (700 samples inside a 2048-wide grid window: 6 x 6 tiles instead of 16 x 16)."""
+    from kspider_b200 import Index
+    rng = np.random.default_rng(5)
+    n, fam0, fam = 6000, 900, 700  # samples 900..1599 fit no 1024-wide grid window (stride 512): the 2048 level
+    ids = np.arange(1, n + 1, dtype=np.uint32)
+    members, offsets = [], [0]
+    for _ in range(400):
+        m = np.sort(rng.choice(fam, size=350, replace=False)) + fam0
+        members.append(ids[m])
+        offsets.append(offsets[-1] + m.size)
+    csr = dict(offsets=np.array(offsets, dtype=np.uint64), members=np.concatenate(members).astype(np.uint32),
+               weights=rng.integers(1, 200, size=400).astype(np.uint32), total_ids=ids, total_vals=np.full(n, 10 ** 6, dtype=np.uint32))
+    monkeypatch.setenv("KSPIDER_GRAM", "16")
+    info = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("KSPIDER_GRAM_SHRINK", mode)
+        idx = Index.from_csr(**csr, host_threads=2)
+        info[mode] = (idx.info.n_gram_colors, idx.info.n_gram_macs, idx.info.n_updates)
+        idx.close()
+    assert info["0"][0] == info["1"][0] == 400 and info["0"][2] == info["1"][2]
+    assert info["1"][1] == 400 * (768 * 767 // 2)           # 700 samples -> six tiles of 128
+    assert info["0"][1] == 400 * (2048 * 2047 // 2)         # the grid window itself
