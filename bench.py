@@ -2,11 +2,13 @@
 """bench.py — weighted pair-updates/s of the pairwise hot path on N B200s (one process per GPU).
 
 A "step" = one pass of the hot path over the whole synthetic index with the binned CSR already
-resident in HBM: clear the owned triangle block, pair-emission kernels (K1/K2/Kz), containment +
-record compaction (K5), threshold + union-find (K6/K7) and, for N > 1, the label all-gather + merge.
+resident in HBM: clear the owned triangle block, pair-emission kernels (K1/K2/Kz, K4 beside them),
+containment + record compaction (K5), threshold + union-find (K6/K7) and, for N > 1, the label
+all-gather + merge.
 `value` = U (weighted pair-updates of the index) x steps / time, max over ranks.
 `e2e`   = the same through the host-facing call (ksb_pairwise on the pinned host CSR: H2D of the
-          blob, kernels, D2H of the records) — wall clock around the call.
+          blob, kernels, D2H of the records) — wall clock around the call; best of 5 rounds of
+          min(steps, 5) calls after 3 warm-up calls, every round listed in `e2e.rounds_ms`.
 `--impl reference` times the UNMODIFIED reference (oracle/_ref/pairwise_ref = src/pairwise.cpp,
 OpenMP + parallel-hashmap) on the host cores on a bounded sample of the same workload.
 """
