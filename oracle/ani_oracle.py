@@ -1,7 +1,10 @@
 """TEST INFRASTRUCTURE ONLY — CPU restatement of `kSpider pairwise --estimate-ani`
 (pykSpider/kSpider2/ks_pairwise.py:29-82).
 
-Parity status: "parity unpinned".  The arithmetic lives in a third-party dependency that is absent
+Parity status: the text handling (which columns, float() of the printed values, mean, f-string repr,
+header, row order) is PINNED: tests/test_cluster_pinning.py compares this restatement verbatim with the
+ani_col files the UNMODIFIED ks_pairwise.py wrote through oracle/refpy.py (tests/golden/*.ani_k*.tsv).
+The formula itself stays "parity unpinned": the arithmetic lives in a third-party dependency that is absent
 from /root/reference and from this image: `sourmash.distance_utils.containment_to_distance`
 (imported at ks_pairwise.py:50; sourmash is not listed in setup.py:203-210 nor requirements.txt, so
 no version is pinned).  Its published algorithm (sourmash >= 4.4, distance_utils.py) is restated

@@ -1,13 +1,15 @@
 """TEST INFRASTRUCTURE ONLY — CPU restatement of `kSpider cluster`
 (pykSpider/kSpider2/ks_clustering.py:22-137,150-163).
 
-Parity status: "parity unpinned" for the connected-components step — the reference calls
-rustworkx.connected_components (third-party Rust module, listed unpinned in setup.py:203-210, not
-vendored, not installed here) and none of the reference's tests touch clustering.  This
-restatement follows the Python control flow line by line and substitutes
-scipy.sparse.csgraph.connected_components for the rustworkx call; connected components of an
-undirected graph are unique as a PARTITION, which is what is compared.  The threshold arithmetic
-(text -> Python float -> *100 -> `<`) is plain Python and is followed exactly.
+Parity status: PINNED against the unmodified reference for everything ks_clustering.py itself does —
+tests/test_cluster_pinning.py compares this restatement with (1) the committed goldens
+tests/golden/*.clusters.json, written by the UNMODIFIED ks_clustering.py run through oracle/refpy.py on
+the unmodified src/pairwise.cpp's TSVs (every dist type incl. ani, nine cut-offs, five cases), and (2)
+the reference run live on fresh inputs where /root/reference exists.  The one thing still "unpinned" is
+rustworkx.connected_components itself (third-party Rust module, listed unpinned in setup.py:203-210,
+not vendored, not installed here; oracle/py_shim/rustworkx.py stands in for it with scipy): connected
+components of an undirected graph are unique as a PARTITION, which is what is compared.  The
+threshold arithmetic (text -> Python float -> *100 -> `<`) is plain Python and is followed exactly.
 
 Deliberately NOT restated (reference defect): ks_clustering.py:107-113 drops
 the current edge whenever a 10 M-edge batch fills up; which edge is lost depends on the hash-map
@@ -35,22 +37,29 @@ def load_names_map(path: str) -> Dict[int, str]:
     return names
 
 
-def edges_from_tsv(pairwise_tsv: str, dist_col: int, cutoff01: float) -> List[Tuple[int, int]]:
+def edges_from_tsv(pairwise_tsv: str, dist_col: int, cutoff01: float, ani_col_tsv: str | None = None) -> List[Tuple[int, int]]:
     """ks_clustering.py:97-105,157 — cut_off_threshold = float(cutoff)*100 ;
     distance = float(text)*100 ; the row is skipped iff distance < cut_off_threshold
-    (so NaN distances are KEPT)."""
+    (so NaN distances are KEPT).  dist_col 6 (:70-83): the distance is the same row of the one-column
+    `_kSpider_pairwise.ani_col.tsv`, float(line) * 100.0."""
     cut = float(cutoff01) * 100
     edges = []
     with open(pairwise_tsv) as f:
         next(f)
+        ani = None
+        if dist_col == 6:
+            ani = open(ani_col_tsv)
+            next(ani)
         for row in f:
             row = row.strip().split("\t")
             seq1 = int(row[0]) - 1
             seq2 = int(row[1]) - 1
-            distance = float(row[dist_col]) * 100
+            distance = float(next(ani).strip()) * 100.0 if ani is not None else float(row[dist_col]) * 100
             if distance < cut:
                 continue
             edges.append((seq1, seq2))
+        if ani is not None:
+            ani.close()
     return edges
 
 
@@ -70,7 +79,8 @@ def cluster(index_prefix: str, cutoff01: float, dist_type: str = "max_cont") -> 
     sorted, clusters sorted) — line/member order in the reference's file is rustworkx-internal."""
     names = load_names_map(index_prefix + ".namesMap")
     node_ids = list(names.keys())  # node index = position in file (ks_clustering.py:45-47)
-    edges = edges_from_tsv(index_prefix + "_kSpider_pairwise.tsv", DISTANCE_TO_COL[dist_type], cutoff01)
+    edges = edges_from_tsv(index_prefix + "_kSpider_pairwise.tsv", DISTANCE_TO_COL[dist_type], cutoff01,
+                           index_prefix + "_kSpider_pairwise.ani_col.tsv")
     labels = components(len(node_ids), edges)
     groups: Dict[int, List[str]] = {}
     for node, lab in enumerate(labels):

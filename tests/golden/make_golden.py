@@ -56,12 +56,47 @@ def from_csr(csr, extra_singletons=True, wide_ids=False):
     return totals, counts, colors
 
 
+def clades_csr(seed=15, n_clades=8, clade=15, n_core=220, n_family=40, n_noise=150):
+    """Clade-structured colour table with ids 1..N and totals = the sample's own k-mer count (sum of the
+    weights of every colour containing it + a private remainder), so every containment lies in [0, 1] and
+    spreads over it: the case behind the cluster / ANI goldens (make_golden_py.py)."""
+    rng = np.random.default_rng(seed)
+    n = n_clades * clade
+    cols, w = [], []
+    for c in range(n_core):
+        k = c % n_clades
+        keep = rng.random(clade) < rng.uniform(0.55, 1.0)
+        m = np.flatnonzero(keep) + k * clade
+        if m.size >= 1:
+            cols.append(m); w.append(int(rng.integers(1, 400)))
+    for c in range(n_family):
+        k = int(rng.integers(0, n_clades - 1))
+        m = np.flatnonzero(rng.random(2 * clade) < 0.5) + k * clade
+        if m.size >= 1:
+            cols.append(m); w.append(int(rng.integers(1, 60)))
+    for c in range(n_noise):
+        cols.append(rng.choice(n, size=int(rng.integers(1, 5)), replace=False)); w.append(int(rng.integers(0, 8)))
+    ids = np.arange(1, n + 1, dtype=np.uint32)
+    tot = np.zeros(n, dtype=np.int64)
+    for m, ww in zip(cols, w):
+        tot[m] += ww
+    private = rng.integers(0, 300, size=n)
+    private[::9] = 0          # some samples are fully covered by shared colours: containment exactly 1 happens
+    tot += private
+    tot[tot == 0] = 1
+    sizes = np.array([m.size for m in cols], dtype=np.uint64)
+    members = np.concatenate([ids[rng.permutation(m)] for m in cols]).astype(np.uint32)
+    return dict(offsets=np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64), members=members,
+                weights=np.array(w, dtype=np.uint32), total_ids=ids, total_vals=tot.astype(np.uint32))
+
+
 CASES = {
     "micro_kat": lambda: micro_kat(),
     "small_dense": lambda: from_csr(random_csr(11, 40, 300, 1, 9)),
     "sparse_ids_zero_w": lambda: from_csr(random_csr(12, 60, 400, 1, 12, id_mode="sparse", zero_every=7)),
     "mid_colors": lambda: from_csr(random_csr(13, 400, 200, 2, 40, big=(65, 66, 130, 257, 399))),
     "wide_counts": lambda: from_csr(random_csr(14, 50, 200, 2, 8), wide_ids=True),
+    "clades": lambda: from_csr(clades_csr(), extra_singletons=False),
 }
 KEEP_BINS = set(CASES)
 

@@ -1,7 +1,14 @@
 """Shared helpers of the test-suite: seeded random indexes and result comparison."""
 from __future__ import annotations
 
+import gzip
+import json
+import os
+import shutil
+
 import numpy as np
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 def random_csr(seed: int, n_samples: int, n_colors: int, s_lo: int = 1, s_hi: int = 12, id_mode: str = "dense",
@@ -64,3 +71,43 @@ def canonical_partition(labels: np.ndarray):
     for i, l in enumerate(labels.tolist()):
         groups.setdefault(l, []).append(i)
     return sorted(tuple(g) for g in groups.values())
+
+
+def stage_golden_prefix(name: str, td: str, ksize: int = 21, with_index_files: bool = False) -> str:
+    """Index prefix under `td` holding what `kSpider cluster` / `pairwise --estimate-ani` read for golden case
+    `name`: the reference's pairwise TSV and seqToKmersNo.tsv (tests/golden, made by the unmodified
+    src/pairwise.cpp), a namesMap with names s<id> in id order and .extra (first line = kSize).
+    with_index_files: also the three phmap index files (so that the product can run on the same prefix)."""
+    prefix = os.path.join(str(td), name)
+    src = os.path.join(GOLD, name + ".pairwise.tsv")
+    if os.path.exists(src + ".gz"):
+        with gzip.open(src + ".gz", "rb") as f, open(prefix + "_kSpider_pairwise.tsv", "wb") as g:
+            shutil.copyfileobj(f, g)
+    else:
+        shutil.copy(src, prefix + "_kSpider_pairwise.tsv")
+    shutil.copy(os.path.join(GOLD, name + ".seq.tsv"), prefix + "_kSpider_seqToKmersNo.tsv")
+    ids = np.sort(np.load(os.path.join(GOLD, name + ".raw.npz"))["total_ids"])
+    assert ids[0] == 1 and ids[-1] == ids.size, "the reference's cluster command needs ids 1..N"
+    with open(prefix + ".namesMap", "w") as f:
+        f.write(f"{ids.size}\n")
+        for i in ids:
+            f.write(f"{i} s{i}\n")
+    with open(prefix + ".extra", "w") as f:
+        f.write(f"{ksize}\n1\n1\n\n")
+    if with_index_files:
+        for suf in ("_color_to_sources.bin", "_color_count.bin", "_groupID_to_kmerCount.bin"):
+            shutil.copy(os.path.join(GOLD, name + suf), prefix + suf)
+    return prefix
+
+
+def golden_clusters(name: str) -> dict:
+    """{(dist_type, cutoff): partition as sorted lists of sample ids} written by the UNMODIFIED
+    ks_clustering.py (tests/golden/make_golden_py.py)."""
+    with open(os.path.join(GOLD, name + ".clusters.json")) as f:
+        raw = json.load(f)
+    return {(k.split("|")[0], float(k.split("|")[1])): [list(c) for c in v] for k, v in raw.items()}
+
+
+def partition_of_names(clusters) -> list:
+    """clusters of names s<id> -> sorted lists of ids (the goldens' canonical form)"""
+    return sorted(sorted(int(n[1:]) for n in c) for c in clusters)
