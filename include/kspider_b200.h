@@ -282,6 +282,44 @@ int ksb_ani_column(const ksb_result* r, int ksize, double* ani_out, uint64_t* n_
 int ksb_format_double_repr(double v, char* buf);
 int ksb_write_ani_column(const double* ani, uint64_t n, const char* path, int host_threads);
 
+/* ---- the pairwise TSV ON DISK as input: `kSpider cluster` and `pairwise --estimate-ani` -------------------
+ * The reference's two consumers of the pairwise TSV read the FILE (pykSpider/kSpider2/ks_clustering.py:63-117,
+ * ks_pairwise.py:64-73).  A ksb_table holds its parsed rows:
+ *   ksb_table_read_tsv      multithreaded parse; per data line int(row[0]), int(row[1]) and float(row[dist_col])
+ *                           exactly as Python parses them (correctly rounded; "inf", "nan", "-nan" accepted).
+ *                           dist_col 3 = min, 4 = avg, 5 = max containment; 6 = "ani": the value of the same line
+ *                           of the one-column file ani_col_tsv (ks_clustering.py:70-79).  dist_col2 (0 = none,
+ *                           else 3..5) parses a second column (the ANI estimate needs min and max).
+ *   ksb_write_sidecar       binary side-car of a result: the 32-byte records in the row order
+ *                           of the TSV ksb_write_tsv writes, plus that TSV's size and modification time.  ksb_dropin_pairwise writes it
+ *                           as <prefix>_kSpider_pairwise.ksb unless KSPIDER_SIDECAR=0.  tsv_path: the TSV it
+ *                           belongs to (its size is recorded); append != 0 adds the rows of a further row block.
+ *   ksb_sidecar_matches     1 if `sidecar` is intact and was written for exactly this pairwise_tsv (same size, same
+ *                           modification time: a TSV rewritten later by any tool invalidates it), else 0.
+ *   ksb_table_read_sidecar  the same table from the side-car: no text is parsed; values stay float32 and the
+ *                           consumers apply the text rule through ksb_threshold_float_pct / the exact "%g" round trip.
+ *   ksb_cluster_table       ks_clustering.py:45-47,63-120 on the GPU: n_nodes nodes (one per namesMap entry),
+ *                           node = id - 1, row dropped iff float(text) * 100 < cut_pct (NaN kept), lock-free
+ *                           union-find.  labels_out[n_nodes]: smallest node index of the node's component.
+ *                           A KEPT row naming a node >= n_nodes fails with KSB_ERR_FORMAT (rustworkx raises).
+ *   ksb_ani_table           ks_pairwise.py:64-80 on the GPU for a table holding columns 3 and 5
+ *                           (ksb_table_read_*(.., 3, 5, ..)): ani_out[n_rows] in table (= file) order. */
+typedef struct ksb_table ksb_table;
+int ksb_table_read_tsv(const char* pairwise_tsv, int dist_col, int dist_col2, const char* ani_col_tsv, int host_threads,
+                       ksb_table** out);
+int ksb_table_read_sidecar(const char* sidecar, int dist_col, int dist_col2, int host_threads, ksb_table** out);
+/* views into the table (valid until ksb_table_free); dist is NULL for side-car tables, cont for TSV tables */
+int ksb_table_get(const ksb_table* t, uint64_t* n_rows, const uint32_t** source_1, const uint32_t** source_2,
+                  const double** dist, const float** cont);
+void ksb_table_free(ksb_table* t);
+int ksb_write_sidecar(const ksb_result* r, const char* path, const char* tsv_path, int append);
+int ksb_write_sidecar_records(const ksb_record* records, uint64_t n_rows, const char* path, uint64_t tsv_bytes,
+                              uint64_t tsv_mtime_ns, int append);
+int ksb_sidecar_matches(const char* sidecar, const char* pairwise_tsv);
+int ksb_cluster_table(const ksb_table* t, uint64_t n_nodes, double cut_pct, int device, uint32_t* labels_out,
+                      uint64_t* n_edges);
+int ksb_ani_table(const ksb_table* t, int ksize, int device, double* ani_out, uint64_t* n_invalid);
+
 /* ---- synthetic index files (bench / tests): real phmap dump bytes ------------------------- */
 int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uint64_t* color_ids,
                           const uint64_t* offsets, const uint32_t* members, uint64_t n_counts,

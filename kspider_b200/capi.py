@@ -114,6 +114,16 @@ _PROTOS = {
     "ksb_ani_column": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_format_double_repr": (C.c_int, [C.c_double, C.c_char_p]),
     "ksb_write_ani_column": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_int]),
+    "ksb_table_read_tsv": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "ksb_table_read_sidecar": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "ksb_table_get": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
+    "ksb_table_free": (None, [C.c_void_p]),
+    "ksb_write_sidecar": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int]),
+    "ksb_write_sidecar_records": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_uint64, C.c_uint64, C.c_int]),
+    "ksb_sidecar_matches": (C.c_int, [C.c_char_p, C.c_char_p]),
+    "ksb_cluster_table": (C.c_int, [C.c_void_p, C.c_uint64, C.c_double, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "ksb_ani_table": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_write_index_files": (C.c_int, [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
                                         C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "ksb_bench_red": (C.c_int, [C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]),

@@ -175,7 +175,7 @@ static void unpool_event(int dev, cudaEvent_t e, bool timing = true) {
     g_event_pool[dev][timing ? 0 : 1].push_back(e);
 }
 
-static int check_device(int device, int* sms) {
+int check_device(int device, int* sms) {
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) {
@@ -211,6 +211,8 @@ static int check_device(int device, int* sms) {
     if (sms) *sms = c.sms;
     return device;
 }
+
+cudaStream_t service_stream(int dev) { return g_ctx[dev].stream; }
 
 static void build_k1(ksb_device* d) {
     K1Params& p = d->k1;

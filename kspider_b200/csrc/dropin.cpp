@@ -79,6 +79,12 @@ void pairwise(std::string index_prefix, int user_threads) {
     int rc = KSB_OK;
     for (int g = 0; g < gpus && rc == KSB_OK; g++)
         rc = g == 0 ? ksb_write_tsv(res[g], out.c_str(), threads) : ksb_append_tsv(res[g], out.c_str(), threads);
+    // binary side-car for `cluster` / `--estimate-ani` (they then skip the text): the same rows, 32 bytes each
+    const char* sc = std::getenv("KSPIDER_SIDECAR");
+    if (rc == KSB_OK && !(sc && sc[0] == '0')) {
+        const std::string side = index_prefix + "_kSpider_pairwise.ksb";
+        for (int g = 0; g < gpus && rc == KSB_OK; g++) rc = ksb_write_sidecar(res[g], side.c_str(), out.c_str(), g != 0);
+    }
     const std::string err = rc == KSB_OK ? "" : ksb_last_error();
     for (auto* r : res) ksb_result_free(r);
     ksb_index_free(ix);

@@ -380,6 +380,35 @@ cudaError_t launch_k8_ani(const ksb_record* records, uint64_t n_rows, double inv
     return cudaGetLastError();
 }
 
+// The same column from two parsed columns of the TSV on disk (ksb_ani_table): doubles = float(text) as the
+// reference parses them (no text6 needed), or float32 from the binary side-car (text6 recovers the text value).
+__global__ void __launch_bounds__(256) k8_ani_cols(const double* __restrict__ dmin, const double* __restrict__ dmax,
+                                                   const float* __restrict__ fmin, const float* __restrict__ fmax,
+                                                   unsigned long long n_rows, double inv_k, double* __restrict__ out,
+                                                   unsigned long long* n_bad) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    uint32_t nb = 0;
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += stride) {
+        const double c1 = dmin ? __ldg(dmin + r) : text6(__ldg(fmin + r));
+        const double c2 = dmax ? __ldg(dmax + r) : text6(__ldg(fmax + r));
+        bool bad = false;
+        const double a1 = ani_of(c1, inv_k, &bad);
+        const double a2 = ani_of(c2, inv_k, &bad);
+        out[r] = __ddiv_rn(__dadd_rn(a1, a2), 2.0);
+        nb += bad ? 1u : 0u;
+    }
+    nb = __reduce_add_sync(KSB_FULL, nb);
+    if ((threadIdx.x & 31u) == 0 && nb) atomicAdd(n_bad, (unsigned long long)nb);
+}
+
+cudaError_t launch_k8_ani_cols(const double* dmin, const double* dmax, const float* fmin, const float* fmax, uint64_t n_rows,
+                               double inv_k, double* out, unsigned long long* n_bad, const LaunchCfg& lc) {
+    if (n_rows == 0) return cudaSuccess;
+    const uint64_t want = (n_rows + 255) / 256, cap = (uint64_t)lc.sms * 8;
+    k8_ani_cols<<<(unsigned)(want < cap ? want : cap), 256, 0, lc.stream>>>(dmin, dmax, fmin, fmax, n_rows, inv_k, out, n_bad);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------
 // K2: block-tiled mid/large colours (s > 64).  One CTA item = 256 columns (one per thread, kept in
 // a register) x up to 512 rows.  The rows' member ids are staged into shared memory with one TMA
@@ -820,27 +849,6 @@ cudaError_t scan_block_counts(void* temp, size_t* temp_bytes, const unsigned lon
 // K6 + K7: threshold on the selected containment column and lock-free union-find (smaller root wins,
 // so the final label of a component is its smallest compact sample index).
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t uf_find(uint32_t* parent, uint32_t x) {
-    volatile uint32_t* p = parent;
-    for (;;) {
-        const uint32_t px = p[x];
-        if (px == x) return x;
-        const uint32_t ppx = p[px];
-        if (ppx != px) p[x] = ppx;  // path halving
-        x = px;
-    }
-}
-
-__device__ __forceinline__ void uf_union(uint32_t* parent, uint32_t a, uint32_t b) {
-    for (;;) {
-        a = uf_find(parent, a);
-        b = uf_find(parent, b);
-        if (a == b) return;
-        if (a < b) { const uint32_t t = a; a = b; b = t; }
-        if (atomicCAS(parent + a, a, b) == a) return;
-    }
-}
-
 // K6a: before any union, every kept edge (i < j) lowers parent[j] to i with one fire-and-forget
 // atomicMin.  Each link joins two samples that ARE connected and keeps parent[x] <= x, so the result is a
 // valid union-find forest whose roots are the minima of their trees; in clique-like components (a clade:

@@ -190,6 +190,35 @@ cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 
+// device handle shared by the translation units of the C-ABI (device_api.cu): validates / selects the ordinal
+// (-1 = current), returns it or a negative KSB_ERR_*; the per-device service stream results and tables use
+int check_device(int device, int* sms);
+cudaStream_t service_stream(int dev);
+
+#ifdef __CUDACC__
+// lock-free union-find shared by K6/K7 (kernels.cu) and the table kernels (table.cu): smaller root wins
+__device__ __forceinline__ uint32_t uf_find(uint32_t* parent, uint32_t x) {
+    volatile uint32_t* p = parent;
+    for (;;) {
+        const uint32_t px = p[x];
+        if (px == x) return x;
+        const uint32_t ppx = p[px];
+        if (ppx != px) p[x] = ppx;  // path halving
+        x = px;
+    }
+}
+
+__device__ __forceinline__ void uf_union(uint32_t* parent, uint32_t a, uint32_t b) {
+    for (;;) {
+        a = uf_find(parent, a);
+        b = uf_find(parent, b);
+        if (a == b) return;
+        if (a < b) { const uint32_t t = a; a = b; b = t; }
+        if (atomicCAS(parent + a, a, b) == a) return;
+    }
+}
+#endif
+
 // red micro-benchmark
 cudaError_t launch_bench_red(void* buf, uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, const LaunchCfg& lc);
 

@@ -222,9 +222,14 @@ def test_cluster_partition_vs_oracle(ksb, dist, cutoff, tmp_path):
     assert all(labels[g[0]] == g[0] for g in canonical_partition(labels)), "label = smallest member"
     # the mirrored command writes the reference's file name and the same partition
     from kspider_b200 import clustering
-    out = clustering.cluster(prefix, cutoff, dist, index=idx, result=res)
+    idx.write_seq_to_kmers(prefix + "_kSpider_seqToKmersNo.tsv")
+    want = cluster_oracle.cluster(prefix, cutoff, dist)
+    out = clustering.cluster(prefix, cutoff, dist)  # file-driven, like the reference: parses the TSV on disk
     assert out == cluster_oracle.output_name(prefix, cutoff)
-    assert cluster_oracle.read_clusters_file(out) == cluster_oracle.cluster(prefix, cutoff, dist)
+    assert cluster_oracle.read_clusters_file(out) == want
+    live = str(tmp_path / "live.tsv")                # and from the live result, nothing read back from disk
+    clustering.cluster_result(idx, res, cluster_oracle.load_names_map(prefix + ".namesMap"), live, cutoff, dist)
+    assert cluster_oracle.read_clusters_file(live) == want
 
 
 def test_cluster_merge_of_row_blocks(ksb):
