@@ -141,6 +141,14 @@ int ksb_index_load(const char* index_prefix, int host_threads, ksb_index** out);
 int ksb_index_from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members,
                        const uint32_t* weights, uint64_t n_totals, const uint32_t* total_ids,
                        const uint32_t* total_vals, int host_threads, ksb_index** out);
+/* The same index from a kProcessor `colored_kDataFrame` file set -- what index_kmers /
+ * index_skipmers / index_protein leave (src/index.cpp:53-80 -> colored_kDataFrame::save,
+ * lib/kProcessor/src/kDataFrames/colored_kDataFrame.cpp:101-113): <prefix>.phmap (k-mer -> colour,
+ * kDataFramePHMAP.cpp:208-224), <prefix>colors.intvectors (colour -> samples, colorTable.cpp:256-282) and
+ * <prefix>.namesMap.  Per-colour counts = histogram of the k-mer map's values, computed on `device` (-1 = current);
+ * per-sample totals = sum of the counts of the colours holding the sample; counts / totals narrowed to u32 as
+ * src/pairwise.cpp:118-120 does.  KSB_ERR_FORMAT when a k-mer carries a colour the table does not list. */
+int ksb_index_load_colored(const char* index_prefix, int host_threads, int device, ksb_index** out);
 int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info);
 /* compact index -> original sample id (ascending), and per-sample totals in the same order */
 const uint32_t* ksb_index_sample_ids(const ksb_index* ix);

@@ -49,6 +49,14 @@ class Index:
         return cls(h)
 
     @classmethod
+    def load_colored(cls, index_prefix: str, host_threads: int = 1, device: int = -1) -> "Index":
+        """From a kProcessor colored_kDataFrame file set (<prefix>.phmap, <prefix>colors.intvectors, <prefix>.namesMap):
+        ksb_index_load_colored -- per-colour counts by a histogram of the k-mer map on the device."""
+        h = C.c_void_p()
+        check(lib().ksb_index_load_colored(str(index_prefix).encode(), int(host_threads), int(device), C.byref(h)))
+        return cls(h)
+
+    @classmethod
     def from_csr(cls, offsets, members, weights, total_ids, total_vals, host_threads: int = 1) -> "Index":
         offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
         members = np.ascontiguousarray(members, dtype=np.uint32)

@@ -58,6 +58,7 @@ _PROTOS = {
     "ksb_abi_version": (C.c_int, []),
     "ksb_cuda_available": (C.c_int, []),
     "ksb_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "ksb_index_load_colored": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
     "ksb_index_from_csr": (C.c_int, [C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                      C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
     "ksb_index_get_info": (C.c_int, [C.c_void_p, C.POINTER(IndexInfo)]),

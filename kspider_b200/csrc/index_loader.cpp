@@ -776,6 +776,11 @@ static int from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* 
     return build_index(raw, threads, out);
 }
 
+int from_csr_owned(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members, const uint32_t* weights,
+                   uint64_t n_totals, const uint32_t* total_ids, const uint32_t* total_vals, int threads, ksb_index** out) {
+    return from_csr(n_colors, offsets, members, weights, n_totals, total_ids, total_vals, threads, out);
+}
+
 // Row-block shard: walks every colour of the binned blob, keeps those with a member in rows
 // [r0, r1) (as a ROW, i.e. not as the colour's last member), cut down to their members >= r0, and
 // bins the result again.  Sample ids / totals are passed through unchanged so the compaction (and
