@@ -100,3 +100,41 @@ def read_clusters_file(path: str) -> List[List[str]]:
 def output_name(index_prefix: str, cutoff01: float) -> str:
     """ks_clustering.py:31-32,157 — f"_kSpider_clusters_{float(cutoff)*100}%.tsv"."""
     return index_prefix + f"_kSpider_clusters_{float(cutoff01) * 100}%.tsv"
+
+
+# ---- the same decisions on float32 columns (for BASELINE-size results, where formatting 5e7 rows in Python
+# ---- is not an option): pinned against the text rule above in tests/test_cluster_pinning.py
+
+def threshold_float32(cut_pct: float) -> float:
+    """Smallest float32 c >= 0 whose printed text the reference keeps: float("%g" % c) * 100 >= cut_pct
+    (ks_clustering.py:101-105 on src/pairwise.cpp:266-273's text).  "%g" and float() are monotone, so the
+    kept set is {c >= c*} (plus NaN): binary search over the bit patterns +0 .. +inf.  cut_pct above every
+    finite value returns inf (only inf / NaN rows survive)."""
+    def kept(bits: int) -> bool:
+        c = float(np.array([bits], dtype=np.uint32).view(np.float32)[0])
+        return not (float("%g" % c) * 100 < cut_pct)
+    lo, hi = 0, 0x7F800000
+    if kept(lo):
+        return 0.0
+    while hi - lo > 1:
+        mid = (lo + hi) // 2
+        if kept(mid):
+            hi = mid
+        else:
+            lo = mid
+    return float(np.array([hi], dtype=np.uint32).view(np.float32)[0])
+
+
+def kept_mask(col: np.ndarray, cut_pct: float) -> np.ndarray:
+    """rows of a float32 containment column the reference keeps at cut_off_threshold = cut_pct"""
+    cstar = np.float32(threshold_float32(cut_pct))
+    return ~(np.asarray(col, dtype=np.float32) < cstar)
+
+
+def min_labels(n_nodes: int, a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    """label[v] = smallest node of v's component (the form ksb_cluster returns) for the edge list (a, b)"""
+    g = coo_matrix((np.ones(a.size, dtype=np.int8), (a, b)), shape=(n_nodes, n_nodes))
+    _, lab = connected_components(g, directed=False)
+    first = np.full(lab.max() + 1 if lab.size else 0, n_nodes, dtype=np.int64)
+    np.minimum.at(first, lab, np.arange(n_nodes))
+    return first[lab].astype(np.uint32)

@@ -20,6 +20,12 @@
  *                          insert_or_assign = last one wins) and :166-170 (totals)
  *   ko_pairwise_csr        src/pairwise.cpp:209-225 (all member pairs of each colour, ascending(),
  *                          edges[(i,j)] += (uint32_t)count, inserted even when count == 0)
+ *   ko_pairwise_csr_banded the same sums for indexes of BASELINE size (10^9..10^10 updates), where a
+ *                          single-threaded hash map takes hours: per smaller sample i the cells (i, j) of
+ *                          the columns j it is ever paired with, accumulated by all host threads with
+ *                          atomic adds (OpenMP), a byte per cell for "touched" (count 0 still makes a row).
+ *                          Another container, the same arithmetic; pinned against ko_pairwise_csr on every
+ *                          golden case and on seeded inputs (tests/test_oracle_pinning.py).
  *   ko_containment         src/pairwise.cpp:257-264 (float32 math)
  *   ko_write_tsv           src/pairwise.cpp:242-275 (header, columns, ostream<<float == "%g")
  *   ko_write_seq_to_kmers  src/pairwise.cpp:173-180
@@ -375,6 +381,146 @@ int ko_pairwise_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* 
     }
     ko_map32_free(&tm);
     free(kv);
+    *out = r;
+    return KO_OK;
+}
+
+/* u32 ascending */
+static int ko_u32_cmp(const void* a, const void* b) {
+    uint32_t x = *(const uint32_t*)a, y = *(const uint32_t*)b;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+static void ko_isort_u32(uint32_t* a, uint64_t n) {
+    if (n > 48) { qsort(a, n, 4, ko_u32_cmp); return; }
+    for (uint64_t i = 1; i < n; i++) {
+        uint32_t v = a[i];
+        uint64_t j = i;
+        while (j > 0 && a[j - 1] > v) { a[j] = a[j - 1]; j--; }
+        a[j] = v;
+    }
+}
+
+/* Large-index variant of ko_pairwise_csr (see the header): same result, rows in (source_1, source_2) order. */
+int ko_pairwise_csr_banded(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members,
+                           const uint32_t* weights, uint64_t n_totals, const uint32_t* total_ids,
+                           const uint32_t* total_vals, int threads, ko_result** out) {
+    const uint64_t M = offsets[n_colors];
+    if (threads < 1) threads = 1;
+    /* compact sample index = rank among the distinct member ids */
+    uint32_t* ids = (uint32_t*)malloc((M + 1) * 4);
+    if (!ids) return KO_ERR_NOMEM;
+    uint64_t N = 0;
+    uint32_t max_id = 0;
+    for (uint64_t i = 0; i < M; i++) if (members[i] > max_id) max_id = members[i];
+    uint32_t* rank = NULL; /* dense ids: id -> compact index by table instead of by search */
+    if (M && (uint64_t)max_id < (1ull << 28)) {
+        rank = (uint32_t*)calloc((uint64_t)max_id + 1, 4);
+        if (!rank) return KO_ERR_NOMEM;
+        for (uint64_t i = 0; i < M; i++) rank[members[i]] = 1;
+        for (uint64_t v = 0; v <= max_id; v++)
+            if (rank[v]) { rank[v] = (uint32_t)N; ids[N++] = (uint32_t)v; }
+    } else {
+        memcpy(ids, members, M * 4);
+        qsort(ids, M, 4, ko_u32_cmp);
+        for (uint64_t i = 0; i < M; i++)
+            if (i == 0 || ids[i] != ids[i - 1]) ids[N++] = ids[i];
+    }
+    /* sorted compact members per colour */
+    uint32_t* cm = (uint32_t*)malloc((M + 1) * 4);
+    uint32_t* lo = (uint32_t*)malloc((N + 1) * 4);
+    uint32_t* hi = (uint32_t*)calloc(N + 1, 4);
+    uint64_t* start = (uint64_t*)calloc(N + 2, 8);
+    if (!cm || !lo || !hi || !start) return KO_ERR_NOMEM;
+    for (uint64_t i = 0; i < N; i++) lo[i] = 0xFFFFFFFFu;
+    int zero_w = 0;
+#pragma omp parallel for schedule(dynamic, 4096) num_threads(threads) reduction(| : zero_w)
+    for (uint64_t c = 0; c < n_colors; c++) {
+        const uint64_t b = offsets[c], s = offsets[c + 1] - b;
+        for (uint64_t a = 0; a < s; a++) {
+            const uint32_t v = members[b + a];
+            if (rank) { cm[b + a] = rank[v]; continue; }
+            uint64_t l = 0, h = N;
+            while (h - l > 1) { const uint64_t m = (l + h) >> 1; if (ids[m] <= v) l = m; else h = m; }
+            cm[b + a] = (uint32_t)l;
+        }
+        ko_isort_u32(cm + b, s);
+        if (s >= 2 && weights[c] == 0) zero_w = 1;
+    }
+    /* bands: row m[p] is paired with the columns m[p+1] .. m[s-1] */
+    for (uint64_t c = 0; c < n_colors; c++) {
+        const uint64_t b = offsets[c], s = offsets[c + 1] - b;
+        for (uint64_t p = 0; p + 1 < s; p++) {
+            const uint32_t r = cm[b + p];
+            if (cm[b + p + 1] < lo[r]) lo[r] = cm[b + p + 1];
+            if (cm[b + s - 1] + 1 > hi[r]) hi[r] = cm[b + s - 1] + 1;
+        }
+    }
+    for (uint64_t i = 0; i < N; i++) {
+        if (lo[i] == 0xFFFFFFFFu) lo[i] = hi[i] = 0;
+        start[i + 1] = start[i] + (hi[i] - lo[i]);
+    }
+    const uint64_t cells = start[N];
+    uint64_t* acc = (uint64_t*)calloc(cells + 1, 8);
+    uint8_t* touched = (uint8_t*)calloc(cells + 1, 1);
+    if (!acc || !touched) return KO_ERR_NOMEM;
+#pragma omp parallel for schedule(dynamic, 1024) num_threads(threads)
+    for (uint64_t c = 0; c < n_colors; c++) {
+        const uint64_t b = offsets[c], s = offsets[c + 1] - b;
+        const uint64_t w = weights[c];
+        for (uint64_t p = 0; p + 1 < s; p++) {
+            const uint32_t r = cm[b + p];
+            uint64_t* row = acc + start[r] - lo[r];
+            uint8_t* trow = touched + start[r] - lo[r];
+            for (uint64_t q = p + 1; q < s; q++) {
+                const uint32_t j = cm[b + q];
+                if (j == r) continue; /* cannot happen: member lists are sets */
+                if (w) __atomic_fetch_add(&row[j], w, __ATOMIC_RELAXED);      /* v.second += ccount */
+                if (zero_w || !w) trow[j] = 1;                                 /* inserted even when count == 0 */
+            }
+        }
+    }
+    /* rows per sample, prefix, emit */
+    uint64_t* rfirst = (uint64_t*)calloc(N + 2, 8);
+    if (!rfirst) return KO_ERR_NOMEM;
+#pragma omp parallel for schedule(static) num_threads(threads)
+    for (uint64_t i = 0; i < N; i++) {
+        uint64_t n = 0;
+        for (uint64_t k = start[i]; k < start[i + 1]; k++) n += (acc[k] != 0 || touched[k]);
+        rfirst[i + 1] = n;
+    }
+    for (uint64_t i = 0; i < N; i++) rfirst[i + 1] += rfirst[i];
+    const uint64_t n = rfirst[N];
+    ko_map32 tm;
+    if (ko_map32_init(&tm, n_totals)) return KO_ERR_NOMEM;
+    for (uint64_t i = 0; i < n_totals; i++) {
+        int found; uint64_t sl = ko_map32_slot(&tm, total_ids[i], &found);
+        if (!found) { tm.used[sl] = 1; tm.keys[sl] = total_ids[i]; tm.n++; }
+        tm.vals[sl] = total_vals[i];
+    }
+    uint32_t* tot = (uint32_t*)calloc(N + 1, 4);
+    for (uint64_t i = 0; i < N; i++) {
+        int f; uint64_t sl = ko_map32_slot(&tm, ids[i], &f);
+        tot[i] = f ? (uint32_t)tm.vals[sl] : 0;  /* operator[] default 0 (pairwise.cpp:257-258) */
+    }
+    ko_map32_free(&tm);
+    ko_result* r = (ko_result*)calloc(1, sizeof(ko_result));
+    r->n_rows = n;
+    r->src1 = (uint32_t*)malloc((n + 1) * 4); r->src2 = (uint32_t*)malloc((n + 1) * 4);
+    r->shared = (uint64_t*)malloc((n + 1) * 8);
+    r->cmin = (float*)malloc((n + 1) * 4); r->cavg = (float*)malloc((n + 1) * 4); r->cmax = (float*)malloc((n + 1) * 4);
+    if (!r->src1 || !r->src2 || !r->shared || !r->cmin || !r->cavg || !r->cmax) return KO_ERR_NOMEM;
+#pragma omp parallel for schedule(dynamic, 64) num_threads(threads)
+    for (uint64_t i = 0; i < N; i++) {
+        uint64_t x = rfirst[i];
+        for (uint64_t k = start[i]; k < start[i + 1]; k++) {
+            if (acc[k] == 0 && !touched[k]) continue;
+            const uint32_t j = lo[i] + (uint32_t)(k - start[i]);
+            r->src1[x] = ids[i]; r->src2[x] = ids[j]; r->shared[x] = acc[k];
+            ko_containment(acc[k], tot[i], tot[j], &r->cmin[x], &r->cavg[x], &r->cmax[x]);
+            x++;
+        }
+    }
+    free(rank); free(ids); free(cm); free(lo); free(hi); free(start); free(acc); free(touched); free(rfirst); free(tot);
     *out = r;
     return KO_OK;
 }

@@ -32,6 +32,7 @@ def lib():
         L.ko_index_free.argtypes = [vp]
         L.ko_pairwise.argtypes = [vp, C.POINTER(vp)]
         L.ko_pairwise_csr.argtypes = [u64, vp, vp, vp, u64, vp, vp, C.POINTER(vp)]
+        L.ko_pairwise_csr_banded.argtypes = [u64, vp, vp, vp, u64, vp, vp, C.c_int, C.POINTER(vp)]
         L.ko_result_free.argtypes = [vp]
         L.ko_write_tsv.argtypes = [vp, cp]
         L.ko_write_seq_to_kmers.argtypes = [vp, cp]
@@ -127,6 +128,22 @@ def pairwise_csr(offsets, members, weights, total_ids, total_vals) -> OracleResu
                                total_vals.ctypes.data, C.byref(h))
     if rc != 0:
         raise RuntimeError(f"oracle: ko_pairwise_csr rc={rc}")
+    return OracleResult(h)
+
+
+def pairwise_csr_banded(offsets, members, weights, total_ids, total_vals, threads: int = 0) -> OracleResult:
+    """ko_pairwise_csr_banded: the same rows for indexes of BASELINE size (all host threads, banded accumulator)."""
+    offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+    members = np.ascontiguousarray(members, dtype=np.uint32)
+    weights = np.ascontiguousarray(weights, dtype=np.uint32)
+    total_ids = np.ascontiguousarray(total_ids, dtype=np.uint32)
+    total_vals = np.ascontiguousarray(total_vals, dtype=np.uint32)
+    h = C.c_void_p()
+    rc = lib().ko_pairwise_csr_banded(offsets.size - 1, offsets.ctypes.data, members.ctypes.data,
+                                      weights.ctypes.data, total_ids.size, total_ids.ctypes.data,
+                                      total_vals.ctypes.data, int(threads) or (os.cpu_count() or 1), C.byref(h))
+    if rc != 0:
+        raise RuntimeError(f"oracle: ko_pairwise_csr_banded rc={rc}")
     return OracleResult(h)
 
 

@@ -86,3 +86,28 @@ def test_oracles_match_live_reference(tmp_path):
         want = cluster_oracle.read_clusters_file(path)
         assert 1 < len(want) < n
         assert cluster_oracle.cluster(prefix, cutoff, dist) == want
+
+
+@pytest.mark.parametrize("name", ["clades", "mid_colors", "small_dense"])
+def test_float32_threshold_rule_equals_the_text_rule(name, tmp_path):
+    """cluster_oracle.kept_mask (used at BASELINE sizes) against ks_clustering.py's text rule row by row"""
+    prefix = stage_golden_prefix(name, tmp_path)
+    rows = [l.split("\t") for l in open(prefix + "_kSpider_pairwise.tsv").read().splitlines()[1:]]
+    for col in (3, 4, 5):
+        text = [r[col] for r in rows]
+        f32 = np.array([float(t) for t in text], dtype=np.float64).astype(np.float32)
+        assert ["%g" % float(v) for v in f32] == text            # the float32 the text came from
+        for cutoff in (0.0, 0.004, 0.3, 0.333333, 0.5, 0.95, 1.0, 2.0):
+            cut = float(cutoff) * 100
+            want = np.array([not (float(t) * 100 < cut) for t in text])
+            assert np.array_equal(cluster_oracle.kept_mask(f32, cut), want), (name, col, cutoff)
+
+
+def test_min_labels_is_the_partition_of_components():
+    rng = np.random.default_rng(5)
+    a, b = rng.integers(0, 500, 300), rng.integers(0, 500, 300)
+    lab = cluster_oracle.min_labels(500, a, b)
+    ref = cluster_oracle.components(500, list(zip(a.tolist(), b.tolist())))
+    for g in np.unique(ref):
+        mem = np.flatnonzero(ref == g)
+        assert np.all(lab[mem] == mem.min())

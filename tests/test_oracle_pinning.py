@@ -147,3 +147,29 @@ def test_cluster_oracle_threshold_and_components(tmp_path):
     assert cluster_oracle.cluster(prefix, 0.0) == [["a", "b", "c"], ["d"]]
     assert cluster_oracle.cluster(prefix, 0.5, "min_cont") == [["a"], ["b"], ["c"], ["d"]]
     assert cluster_oracle.output_name(prefix, 0.95).endswith("_kSpider_clusters_95.0%.tsv")
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_banded_oracle_equals_hash_map_oracle_on_goldens(name):
+    """ko_pairwise_csr_banded (the BASELINE-size checker) against the pinned ko_pairwise_csr"""
+    csr = golden_input(name)
+    a, b = po.pairwise_csr(**csr), po.pairwise_csr_banded(**csr, threads=3)
+    for f in ("src1", "src2", "shared"):
+        assert np.array_equal(getattr(a, f), getattr(b, f)), f
+    for f in ("cmin", "cavg", "cmax"):
+        assert np.array_equal(getattr(a, f).view(np.uint32), getattr(b, f).view(np.uint32)), f
+
+
+@pytest.mark.parametrize("seed,kw", [
+    (201, dict(n_samples=300, n_colors=4000, s_lo=1, s_hi=40, big=(70, 150, 290), zero_every=97)),
+    (202, dict(n_samples=70, n_colors=900, s_lo=1, s_hi=9, id_mode="sparse", zero_every=5)),
+    (203, dict(n_samples=1000, n_colors=20000, s_lo=2, s_hi=6)),
+])
+def test_banded_oracle_equals_hash_map_oracle_on_seeded_inputs(seed, kw):
+    csr = random_csr(seed, **kw)
+    a, b = po.pairwise_csr(**csr), po.pairwise_csr_banded(**csr, threads=4)
+    assert a.src1.size == b.src1.size
+    for f in ("src1", "src2", "shared"):
+        assert np.array_equal(getattr(a, f), getattr(b, f)), f
+    for f in ("cmin", "cavg", "cmax"):
+        assert np.array_equal(getattr(a, f).view(np.uint32), getattr(b, f).view(np.uint32)), f
