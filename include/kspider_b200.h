@@ -338,6 +338,10 @@ int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uin
 /* n_ops random (pattern 0) / warp-contiguous (pattern 1) red.global.add.{u64,u32} into a buffer of
  * `cells` cells; returns the best-of-`reps` milliseconds. */
 int ksb_bench_red(uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, int reps, float* best_ms);
+/* int8 tensor-pipe ceiling in K4's own instruction shape (tcgen05.mma kind::i8, cta_group::1, M = 128, N = 256,
+ * K = 32; one CTA per SM issuing `iters` K-blocks of 8 instructions on resident tiles): best-of-`reps`
+ * milliseconds of one launch and the u8 multiply-adds it performs. */
+int ksb_bench_imma(uint32_t iters, int reps, float* best_ms, double* macs_per_launch);
 
 #ifdef __cplusplus
 }

@@ -337,3 +337,10 @@ def bench_red(cells: int, n_ops: int, cell_bits: int = 64, pattern: int = 0, rep
     ms = C.c_float()
     check(lib().ksb_bench_red(int(cells), int(n_ops), cell_bits, pattern, reps, C.byref(ms)))
     return ms.value
+
+
+def bench_imma(iters: int = 2048, reps: int = 5):
+    """(best ms, u8 MACs per launch) of the int8 tcgen05 peak kernel in K4's instruction shape"""
+    ms, macs = C.c_float(), C.c_double()
+    check(lib().ksb_bench_imma(int(iters), int(reps), C.byref(ms), C.byref(macs)))
+    return ms.value, macs.value

@@ -1494,6 +1494,31 @@ int ksb_cluster_merge(uint64_t n, const uint32_t* labels_a, const uint32_t* labe
     return rc;
 }
 
+int ksb_bench_imma(uint32_t iters, int reps, float* best_ms, double* macs_per_launch) {
+    if (!best_ms || !macs_per_launch || iters == 0 || reps < 1) { set_error("ksb_bench_imma: bad argument"); return KSB_ERR_ARG; }
+    int sms = 0;
+    const int dev = check_device(-1, &sms);
+    if (dev < 0) return dev;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    const LaunchCfg lc{sms, nullptr};
+    float best = 1e30f;
+    cudaError_t e = cudaSuccess;
+    for (int i = 0; i < reps + 1 && e == cudaSuccess; i++) {  // first launch = warm-up
+        cudaEventRecord(a, nullptr);
+        e = launch_imma_peak(iters, nullptr, macs_per_launch, lc);
+        cudaEventRecord(b, nullptr);
+        if (e == cudaSuccess) e = cudaEventSynchronize(b);
+        if (i > 0 && e == cudaSuccess) best = std::min(best, ev_ms(a, b));
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    if (e != cudaSuccess) { set_error("ksb_bench_imma: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return KSB_ERR_CUDA; }
+    *best_ms = best;
+    return KSB_OK;
+}
+
 int ksb_bench_red(uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, int reps, float* best_ms) {
     if (!best_ms || cells < 64 || (cell_bits != 32 && cell_bits != 64) || reps < 1) { set_error("ksb_bench_red: bad argument"); return KSB_ERR_ARG; }
     int sms = 0;

@@ -454,6 +454,66 @@ __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ Gr
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_imma_peak: the tensor-pipe ceiling K4 is measured against, in K4's own instruction shape.  One CTA per SM
+// fills one A tile and two pairs of B tiles with bytes ONCE and then issues `iters` K-blocks of exactly the
+// UMMAs k4_gram<1> issues per K-block (4 K-steps x 2 N = 256 instructions, kind::i8, cta_group::1, M = 128,
+// accumulators in the 512 TMEM columns) back to back: no expansion, no loads, no epilogue.  bench.py divides
+// K4's u8 MAC rate by this rate ("int8 tensor peak ... must be measured in the same run").
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) k_imma_peak(uint32_t iters, uint32_t* sink) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + 5 * kTileBytes);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    for (uint32_t i = tid; i < 5 * kTileBytes / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x01010101u * ((i * 2654435761u) >> 30);
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 32) {
+        mbar_init(smem_u32(bar), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    if (tid == 0) {
+        const uint32_t sbase = smem_u32(smem);
+        const uint64_t adesc = umma_desc_sw128(sbase);
+        const uint64_t bdesc0 = umma_desc_sw128(sbase + kTileBytes), bdesc1 = umma_desc_sw128(sbase + 3 * kTileBytes);
+        for (uint32_t it = 0; it < iters; it++) {
+#pragma unroll
+            for (uint32_t k = 0; k < 4; k++) {
+                const uint32_t acc = (it > 0 || k > 0) ? 1u : 0u;
+                umma_i8(tmem, adesc + 2 * k, bdesc0 + 2 * k, umma_idesc(256), acc);
+                umma_i8(tmem + 256, adesc + 2 * k, bdesc1 + 2 * k, umma_idesc(256), acc);
+            }
+        }
+        umma_commit(smem_u32(bar));
+    }
+    mbar_wait(smem_u32(bar), 0);
+    tc_fence_after();
+    uint32_t v[16];
+    tmem_ld16(tmem + ((32u * warp) << 16), v);   // one read so that the accumulators are observable
+    if (v[0] == 0xFFFFFFFFu && sink) sink[0] = v[1];
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
+}
+
+cudaError_t launch_imma_peak(uint32_t iters, uint32_t* sink, double* macs, const LaunchCfg& lc) {
+    const size_t smem = 1024 + 5 * (size_t)kTileBytes + 64;
+    cudaError_t e = cudaFuncSetAttribute(k_imma_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_imma_peak<<<(unsigned)lc.sms, 128, smem, lc.stream>>>(iters, sink);
+    if (macs) *macs = (double)lc.sms * (double)iters * 8.0 * 128.0 * 256.0 * 32.0;
+    return cudaGetLastError();
+}
+
 uint32_t gram_cols_per_item(int planes) { return planes <= 1 ? 4u : (planes == 2 ? 2u : 1u); }
 
 static size_t gram_smem_bytes(int P) {

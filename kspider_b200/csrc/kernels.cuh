@@ -219,6 +219,9 @@ __device__ __forceinline__ void uf_union(uint32_t* parent, uint32_t a, uint32_t 
 }
 #endif
 
+// tensor-pipe ceiling in K4's instruction shape (gram.cu); *macs = u8 multiply-adds of one launch
+cudaError_t launch_imma_peak(uint32_t iters, uint32_t* sink, double* macs, const LaunchCfg& lc);
+
 // red micro-benchmark
 cudaError_t launch_bench_red(void* buf, uint64_t cells, uint64_t n_ops, int cell_bits, int pattern, const LaunchCfg& lc);
 

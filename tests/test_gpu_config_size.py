@@ -71,7 +71,7 @@ def run_config(ksb, s, cutoffs, **opts):
 
 def test_cfg2_full_size_rows_and_labels(ksb):
     s = synth.zipf_index(1000, 10_000_000, seed=12345, name="cfg2")
-    idx, res, want = run_config(ksb, s, (0.0, 0.0103, 0.0125, 0.3, 0.95, 1.0))
+    idx, res, want = run_config(ksb, s, (0.0, 0.0257, 0.0258, 0.3, 0.95, 1.0))
     assert idx.info.n_gram_colors > 0 and idx.info.n_small_colors > 0   # K1 and K4 both carried the result
 
 
@@ -102,7 +102,7 @@ def test_cfg2_full_size_through_the_files(ksb, tmp_path, capfd):
         def INFO(self, m): pass
         def ERROR(self, m): raise SystemExit(1)
     a, b = (want.src1 - 1).astype(np.int64), (want.src2 - 1).astype(np.int64)
-    for dist, cutoff in (("max_cont", 0.0125), ("min_cont", 0.0103), ("avg_cont", 0.3)):
+    for dist, cutoff in (("max_cont", 0.0258), ("min_cont", 0.0257), ("avg_cont", 0.3)):
         kcl = Clusters(logger_obj=Log(), index_prefix=prefix, cut_off_threshold=float(cutoff) * 100, dist_type=dist)
         kcl.construct_graph()
         kcl.cluster_graph()
