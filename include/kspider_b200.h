@@ -216,6 +216,18 @@ int ksb_device_get_info(const ksb_device* dev, ksb_result_info* info);
  * creates the result, otherwise the rows are appended to it.  Records also land on the host if
  * want_records (the flag of the creating call decides). */
 int ksb_postpass(ksb_device* dev, int want_records, ksb_result** inout);
+/* Cluster-only step (north_star (3): "only the edge list or cluster labels return to the host"): every dense pass
+ * is accumulated and its block scanned ONCE by K56 -- float32 containment of column dist_col (3 = min, 4 = avg,
+ * 5 = max) exactly as ksb_postpass computes it (src/pairwise.cpp:253-264), the reference's threshold on the
+ * printed text (ks_clustering.py:97-105; cut_pct = float(cutoff) * 100), and ONLY the kept pairs are appended
+ * (8 bytes each) to an edge list -- then lock-free union-find over that list.  No records are built, nothing is
+ * read twice.  Everything is enqueued on `stream` (a cudaStream_t as void*; NULL = the library's own) and the
+ * call synchronises once, at the end.  labels_out (host, N entries) and / or d_labels_out (device, N entries)
+ * receive label = smallest compact sample index of the component, restricted to the edges of the rows this
+ * device owns (merge row blocks with ksb_cluster_merge_device).  n_rows = touched pairs (the TSV rows the
+ * reference would write), n_edges = kept edges.  Same labels as ksb_postpass + ksb_cluster. */
+int ksb_device_cluster(ksb_device* dev, int dist_col, double cut_pct, void* stream, uint32_t* labels_out,
+                       uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows);
 void ksb_device_free(ksb_device* dev);
 
 /* upload + accumulate + postpass in one call (the end-to-end path) */

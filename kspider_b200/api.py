@@ -220,6 +220,19 @@ class Device:
             res = self.postpass(want_records, into=res)
         return res
 
+    def cluster(self, n_samples: int, dist_type: str = "max_cont", cutoff01: float = 0.0, cut_pct=None, stream: int = 0,
+                d_labels_ptr: int = 0, to_host: bool = True):
+        """Cluster-only step (ksb_device_cluster): accumulate + one fused scan per pass + unions; no records.
+        Returns (labels[N] or None, kept edges, touched pairs).  d_labels_ptr: device uint32[N] that also receives
+        the labels (multi-GPU merge); stream: a cudaStream_t to enqueue on (0 = the library's)."""
+        labels = np.empty(n_samples, dtype=np.uint32) if to_host else None
+        ne, nr = C.c_uint64(), C.c_uint64()
+        cut = float(cutoff01) * 100 if cut_pct is None else float(cut_pct)
+        check(lib().ksb_device_cluster(self._h, DIST_COL[dist_type], cut, C.c_void_p(stream) if stream else None,
+                                       labels.ctypes.data if to_host else None,
+                                       C.c_void_p(d_labels_ptr) if d_labels_ptr else None, C.byref(ne), C.byref(nr)))
+        return labels, ne.value, nr.value
+
     def close(self) -> None:
         if self._h:
             lib().ksb_device_free(self._h)

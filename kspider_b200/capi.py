@@ -87,6 +87,8 @@ _PROTOS = {
     "ksb_device_set_pass": (C.c_int, [C.c_void_p, C.c_int]),
     "ksb_device_get_info": (C.c_int, [C.c_void_p, C.POINTER(ResultInfo)]),
     "ksb_postpass": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "ksb_device_cluster": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "ksb_device_free": (None, [C.c_void_p]),
     "ksb_pairwise": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_void_p)]),
     "ksb_result_get_info": (C.c_int, [C.c_void_p, C.POINTER(ResultInfo)]),

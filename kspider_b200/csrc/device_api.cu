@@ -95,6 +95,13 @@ struct ksb_device {
     // K3 (spill)
     uint64_t spill_mode = 0, budget = 0;
     bool spill = false;
+    // cluster-only step (ksb_device_cluster): union-find forest, kept-edge list, counters, pinned staging
+    uint32_t* d_parent = nullptr;
+    unsigned long long* d_cl_counters = nullptr;  // [0] touched cells (rows), [1] kept edges appended (may exceed edge_cap)
+    unsigned long long* d_edges = nullptr;
+    uint64_t edge_cap = 0;
+    uint8_t* h_stage = nullptr;                    // pinned: labels[N] then 2 x u64 counters
+    uint64_t h_stage_bytes = 0;
 };
 
 struct ksb_segment {
@@ -405,7 +412,11 @@ void ksb_device_free(ksb_device* d) {
     }
     if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
     if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
+    if (d->d_parent) cudaFreeAsync(d->d_parent, fs);
+    if (d->d_cl_counters) cudaFreeAsync(d->d_cl_counters, fs);
+    if (d->d_edges) cudaFreeAsync(d->d_edges, fs);
     if (fs) cudaStreamSynchronize(fs);
+    if (d->h_stage) pinned_release(d->h_stage, d->h_stage_bytes);
     for (auto& e : d->ev) unpool_event(d->device, e);
     if (d->stream) { cudaStreamSynchronize(d->stream); unpool_stream(d->device, d->stream); }
     if (d->stream2) { cudaStreamSynchronize(d->stream2); unpool_stream(d->device, d->stream2); }
@@ -783,6 +794,16 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
     return KSB_OK;
 }
 
+// phase timers of the accumulation whose events were recorded last; the stream must have been synchronised
+static void harvest_accumulate_timers(ksb_device* d) {
+    d->t.zero_ms += ev_ms(d->ev[0], d->ev[1]);
+    d->t.small_ms += ev_ms(d->ev[1], d->ev[2]);
+    d->t.mid_ms += ev_ms(d->ev[2], d->ev[3]);
+    d->t.zero_touch_ms += ev_ms(d->ev[3], d->ev[4]);
+    d->t.gram_ms += ev_ms(d->ev[9], d->ev[10]);  // overlaps small_ms/mid_ms unless KSPIDER_OVERLAP=0
+    d->t.accumulate_ms += ev_ms(d->ev[0], d->ev[8]);
+}
+
 int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     if (!d) { set_error("ksb_accumulate: null device"); return KSB_ERR_ARG; }
     if (d->spill) { set_error("ksb_accumulate: this device runs the spill path (ksb_device_run_spill)"); return KSB_ERR_ARG; }
@@ -910,12 +931,7 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     }
     if (sync) {
         KSB_CUDA(cudaStreamSynchronize(st));
-        d->t.zero_ms += ev_ms(d->ev[0], d->ev[1]);
-        d->t.small_ms += ev_ms(d->ev[1], d->ev[2]);
-        d->t.mid_ms += ev_ms(d->ev[2], d->ev[3]);
-        d->t.zero_touch_ms += ev_ms(d->ev[3], d->ev[4]);
-        d->t.gram_ms += ev_ms(d->ev[9], d->ev[10]);  // overlaps small_ms/mid_ms unless KSPIDER_OVERLAP=0
-        d->t.accumulate_ms += ev_ms(d->ev[0], d->ev[8]);
+        harvest_accumulate_timers(d);
     }
     return KSB_OK;
 }
@@ -1231,6 +1247,96 @@ done:
     cudaStreamSynchronize(st);
     if (rc != KSB_OK) { if (r) ksb_result_free(r); return rc; }
     *out = r;
+    return KSB_OK;
+}
+
+float ksb_threshold_float_pct(double cut);
+
+// Cluster-only step (north_star 3): for every dense pass, accumulate and scan its block ONCE (K56: containment,
+// threshold, append of the kept pairs only), then the unions over the kept-edge list and the label compression --
+// everything enqueued on one stream without a host round trip; a single synchronisation at the end brings the
+// labels (and the two counters) to the host.  No records are built.  The edge list has a capacity (an eighth of
+// the owned cells at first); when a step keeps more edges than fit, the list is grown to the exact need and the
+// step is repeated -- the only case with a second synchronisation.
+int ksb_device_cluster(ksb_device* d, int dist_col, double cut_pct, void* stream_v, uint32_t* labels_out,
+                       uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows) {
+    if (!d) { set_error("ksb_device_cluster: null device"); return KSB_ERR_ARG; }
+    if (d->spill) { set_error("ksb_device_cluster: this device runs the spill path (ksb_device_run_spill + ksb_cluster)"); return KSB_ERR_ARG; }
+    if (dist_col < 3 || dist_col > 5) { set_error("ksb_device_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t st = stream_v ? static_cast<cudaStream_t>(stream_v) : d->stream;
+    const uint32_t N = (uint32_t)d->desc.n_samples;
+    if (n_edges) *n_edges = 0;
+    if (n_rows) *n_rows = 0;
+    if (N == 0) return KSB_OK;
+    float cstar = ksb_threshold_float_pct(cut_pct);
+    if (cstar != cstar) cstar = INFINITY;
+    const LaunchCfg lc{d->sms, st};
+    if (!d->d_parent) {
+        KSB_CUDA(cudaMallocAsync(&d->d_parent, 4ull * N, st));
+        KSB_CUDA(cudaMallocAsync(&d->d_cl_counters, 32, st));
+        uint64_t got = 4ull * N + 16;
+        void* hp = nullptr;
+        KSB_CUDA(pinned_acquire(&hp, &got));
+        d->h_stage = static_cast<uint8_t*>(hp);
+        d->h_stage_bytes = got;
+    }
+    const uint8_t* P = d->d_payload;
+    uint32_t* block_rows = reinterpret_cast<uint32_t*>(d->d_block_counts + 2 * d->post_blocks_alloc);
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if (!d->d_edges) {
+            if (d->edge_cap == 0) {
+                const char* ec = std::getenv("KSPIDER_EDGE_CAP");  // test knob: a short list forces the grow-and-repeat path
+                d->edge_cap = (ec && std::atoll(ec) > 0) ? (uint64_t)std::atoll(ec) : std::max<uint64_t>(1ull << 16, d->owned_cells / 8);
+            }
+            KSB_CUDA(cudaMallocAsync(&d->d_edges, 8 * d->edge_cap, st));
+        }
+        KSB_CUDA(cudaMemsetAsync(d->d_cl_counters, 0, 32, st));
+        KSB_CUDA(launch_k7_init(d->d_parent, N, lc));
+        d->launches++;
+        for (uint32_t p = 0; p < d->passes.size(); p++) {
+            d->cur_pass = p;
+            const int rc = ksb_accumulate(d, st, 0);
+            if (rc) return rc;
+            const ksb_pass& ps = d->passes[p];
+            if (ps.cells == 0) continue;
+            const TriGeom g = geom_of(d, ps);
+            if (d->block_rows_pass != (int)p) {
+                KSB_CUDA(launch_k5_block_rows(g, block_rows, lc));
+                d->block_rows_pass = (int)p;
+                d->launches++;
+            }
+            KSB_CUDA(cudaEventRecord(d->ev[5], st));
+            KSB_CUDA(launch_k56_scan(g, d->d_touched, block_rows, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals), dist_col, cstar,
+                                     d->d_edges, d->edge_cap, d->d_cl_counters, lc));
+            KSB_CUDA(cudaEventRecord(d->ev[6], st));
+            d->launches++;
+        }
+        KSB_CUDA(launch_k6_edges(d->d_edges, d->edge_cap, d->d_cl_counters, d->d_parent, d->edge_cap, lc));
+        KSB_CUDA(launch_k7_compress(d->d_parent, N, lc));
+        KSB_CUDA(cudaEventRecord(d->ev[7], st));
+        d->launches += 3;
+        if (d_labels_out) KSB_CUDA(cudaMemcpyAsync(d_labels_out, d->d_parent, 4ull * N, cudaMemcpyDeviceToDevice, st));
+        if (labels_out) KSB_CUDA(cudaMemcpyAsync(d->h_stage, d->d_parent, 4ull * N, cudaMemcpyDeviceToHost, st));
+        KSB_CUDA(cudaMemcpyAsync(d->h_stage + 4ull * N, d->d_cl_counters, 16, cudaMemcpyDeviceToHost, st));
+        KSB_CUDA(cudaStreamSynchronize(st));
+        unsigned long long cnt[2];
+        std::memcpy(cnt, d->h_stage + 4ull * N, 16);
+        if (cnt[1] > d->edge_cap) {  // the list was too short: now the need is known exactly
+            if (attempt == 1) { set_error("ksb_device_cluster: edge list overflow after growing"); return KSB_ERR_CUDA; }
+            KSB_CUDA(cudaFreeAsync(d->d_edges, st));
+            d->d_edges = nullptr;
+            d->edge_cap = cnt[1] + cnt[1] / 16 + 1024;
+            continue;
+        }
+        harvest_accumulate_timers(d);  // of the last pass
+        d->t.post_ms += ev_ms(d->ev[5], d->ev[6]);
+        d->t.cluster_ms += ev_ms(d->ev[6], d->ev[7]);
+        if (labels_out) std::memcpy(labels_out, d->h_stage, 4ull * N);
+        if (n_rows) *n_rows = cnt[0];
+        if (n_edges) *n_edges = cnt[1];
+        return KSB_OK;
+    }
     return KSB_OK;
 }
 

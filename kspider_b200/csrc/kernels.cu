@@ -9,6 +9,7 @@
 #include "kernels.cuh"
 #include "ddpow.hpp"
 
+#include <algorithm>
 #include <cstdlib>
 
 #include <cub/device/device_scan.cuh>
@@ -773,6 +774,134 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
         out += __popc(ball[q]);
         j += 32;
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K56: cluster-only post-pass (north_star 3: "only the edge list or cluster labels return to the host").
+// ONE scan of the owned block replaces k5_count + k5_emit + the threshold scan of K6: a warp takes 32
+// consecutive cells per step (lane = cell), every touched cell gets its (i, j) and the float32 containment of
+// the selected column exactly as K5 computes it (src/pairwise.cpp:253-264), the reference's threshold on the
+// printed text is the comparison with c* (ks_clustering.py:97-105, ksb_threshold_float_pct), and only the KEPT
+// pairs are appended -- 8 bytes each, (i << 32) | j in compact indices -- to an edge list through a per-CTA
+// queue (one global atomicAdd per CTA flush).  No records, no pair array, no column copy, no second read of
+// the block.  counters: [0] touched cells (= TSV rows), [1] kept edges (may exceed the list's capacity: the
+// host then grows the list and repeats the step), both accumulated over the passes of a step.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kScanQueue = 2048;
+__global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__ TriGeom G,
+                                                         const uint32_t* __restrict__ touched,
+                                                         const uint32_t* __restrict__ block_rows,
+                                                         const uint32_t* __restrict__ totals, int dist_col, float cstar,
+                                                         unsigned long long* __restrict__ edges, unsigned long long cap,
+                                                         unsigned long long* counters) {
+    __shared__ unsigned long long q[kScanQueue];
+    __shared__ uint32_t qn, rows_cta;
+    __shared__ unsigned long long qbase;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { qn = 0; rows_cta = 0; }
+    __syncthreads();
+    const unsigned long long wcell0 = (unsigned long long)blockIdx.x * kPostChunk + wid * (32u * kPostPerThread);
+    unsigned long long v[kPostPerThread];
+    uint32_t mine = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < kPostPerThread; k++) {
+        const unsigned long long cell = wcell0 + 32u * k + lane;
+        bool f = false;
+        v[k] = 0ull;
+        if (cell < G.cells) {
+            v[k] = G.tri[cell];
+            f = v[k] != 0ull;
+            if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
+        }
+        mine |= (uint32_t)f << k;
+    }
+    uint32_t nrows = __reduce_add_sync(KSB_FULL, (uint32_t)__popc(mine));
+    if (lane == 0 && nrows) atomicAdd(&rows_cta, nrows);
+    if (mine != 0u) {
+        const unsigned long long g0 = G.base + wcell0 + lane;
+        uint32_t lo = __ldg(block_rows + blockIdx.x);
+        uint32_t hi = blockIdx.x + 1u < gridDim.x ? __ldg(block_rows + blockIdx.x + 1u) + 1u : G.rb + G.nrows;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(G.bandstart + mid) <= g0) lo = mid; else hi = mid;
+        }
+        uint32_t i = lo;
+        uint32_t j = __ldg(G.band_lo + i) + (uint32_t)(g0 - __ldg(G.bandstart + i));
+        uint32_t jend = __ldg(G.band_hi + i);
+        uint32_t ti = __ldg(totals + i);
+#pragma unroll
+        for (uint32_t k = 0; k < kPostPerThread; k++) {
+            if ((mine >> k) == 0u) break;
+            while (j >= jend) {
+                const uint32_t over = j - jend;
+                i++;
+                jend = __ldg(G.band_hi + i);
+                j = __ldg(G.band_lo + i) + over;
+                ti = __ldg(totals + i);
+            }
+            if ((mine >> k) & 1u) {
+                float cmin, cavg, cmax;
+                containment(v[k], ti, __ldg(totals + j), cmin, cavg, cmax);
+                const float c = dist_col == 3 ? cmin : (dist_col == 4 ? cavg : cmax);
+                if (!(c < cstar)) {  // NaN is kept, as in `if distance < cutoff: continue`
+                    const uint32_t pos = atomicAdd(&qn, 1u);
+                    if (pos < kScanQueue) q[pos] = ((unsigned long long)i << 32) | j;
+                    else {  // queue full (a dense clade at a low cut-off): straight to the list
+                        const unsigned long long o = atomicAdd(counters + 1, 1ull);
+                        if (o < cap) edges[o] = ((unsigned long long)i << 32) | j;
+                    }
+                }
+            }
+            j += 32;
+        }
+    }
+    __syncthreads();
+    const uint32_t n = min(qn, kScanQueue);
+    if (threadIdx.x == 0) {
+        qbase = n ? atomicAdd(counters + 1, (unsigned long long)n) : 0ull;
+        if (rows_cta) atomicAdd(counters, (unsigned long long)rows_cta);
+    }
+    __syncthreads();
+    const unsigned long long base = qbase;
+    for (uint32_t k = threadIdx.x; k < n; k += kPostThreads)
+        if (base + k < cap) edges[base + k] = q[k];
+}
+
+// hook (atomicMin accelerator, see k6_hook_min) and union over a compact edge list whose length lives on the device
+__global__ void __launch_bounds__(256) k6_edges_hook(const unsigned long long* __restrict__ edges, unsigned long long cap,
+                                                     const unsigned long long* __restrict__ counters, uint32_t* parent) {
+    const unsigned long long n = min(__ldg(counters + 1), cap);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
+        const unsigned long long ij = __ldg(edges + r);
+        atomicMin(parent + (uint32_t)ij, (uint32_t)(ij >> 32));
+    }
+}
+__global__ void __launch_bounds__(256) k6_edges_union(const unsigned long long* __restrict__ edges, unsigned long long cap,
+                                                      const unsigned long long* __restrict__ counters, uint32_t* parent) {
+    const unsigned long long n = min(__ldg(counters + 1), cap);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
+        const unsigned long long ij = __ldg(edges + r);
+        uf_union(parent, (uint32_t)(ij >> 32), (uint32_t)ij);
+    }
+}
+
+cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, const uint32_t* block_rows, const uint32_t* totals,
+                            int dist_col, float cstar, unsigned long long* edges, unsigned long long cap,
+                            unsigned long long* counters, const LaunchCfg& lc) {
+    const uint64_t nb = post_blocks(g.cells);
+    if (nb == 0) return cudaSuccess;
+    k56_scan<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_rows, totals, dist_col, cstar, edges, cap, counters);
+    return cudaGetLastError();
+}
+cudaError_t launch_k6_edges(const unsigned long long* edges, unsigned long long cap, const unsigned long long* counters,
+                            uint32_t* parent, uint64_t expect, const LaunchCfg& lc) {
+    const unsigned long long want = (std::max<uint64_t>(expect, 1) + 255) / 256, capc = (unsigned long long)lc.sms * 8ull;
+    const unsigned ctas = (unsigned)(want < capc ? want : capc);
+    k6_edges_hook<<<ctas, 256, 0, lc.stream>>>(edges, cap, counters, parent);
+    k6_edges_union<<<ctas, 256, 0, lc.stream>>>(edges, cap, counters, parent);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_k5_count(const TriGeom& g, const uint32_t* touched_bits, unsigned long long* block_counts,

@@ -141,6 +141,13 @@ cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const
                            const uint32_t* block_rows, const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
                            unsigned long long* pairs, float* cmax, const LaunchCfg& lc);
 
+// K56: cluster-only scan (containment + threshold + append of the kept pairs only) and the edge-list unions
+cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, const uint32_t* block_rows, const uint32_t* totals,
+                            int dist_col, float cstar, unsigned long long* edges, unsigned long long cap,
+                            unsigned long long* counters, const LaunchCfg& lc);
+cudaError_t launch_k6_edges(const unsigned long long* edges, unsigned long long cap, const unsigned long long* counters,
+                            uint32_t* parent, uint64_t expect, const LaunchCfg& lc);
+
 // K6+K7
 cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
                              int dist_col, float cstar, uint32_t* parent, unsigned long long* n_edges, const LaunchCfg& lc);

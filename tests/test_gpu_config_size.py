@@ -59,6 +59,18 @@ def check_clusters(res, n, want, cutoffs):
     assert seen_nontrivial, "no cut-off produced a partition between one cluster and all singletons"
 
 
+def check_fused(idx, n, want, cutoffs, **opts):
+    """the cluster-only step (ksb_device_cluster: K56 fused scan, no records) on the same index"""
+    a, b = (want.src1 - 1).astype(np.int64), (want.src2 - 1).astype(np.int64)
+    dev = idx.upload(**opts)
+    for dist, cutoff in [("max_cont", c) for c in cutoffs] + [("min_cont", cutoffs[1]), ("avg_cont", cutoffs[2])]:
+        keep = cluster_oracle.kept_mask(getattr(want, DIST[dist]), float(cutoff) * 100)
+        labels, ne, nr = dev.cluster(n, dist, cutoff)
+        assert (ne, nr) == (int(keep.sum()), want.src1.size), (dist, cutoff)
+        assert np.array_equal(labels, cluster_oracle.min_labels(n, a[keep], b[keep])), (dist, cutoff)
+    dev.close()
+
+
 def run_config(ksb, s, cutoffs, **opts):
     want = oracle_of(s)
     idx = ksb.Index.from_csr(s.offsets, s.members, s.weights, s.total_ids, s.total_vals, host_threads=min(32, os.cpu_count() or 1))
@@ -66,6 +78,8 @@ def run_config(ksb, s, cutoffs, **opts):
     res = idx.pairwise(want_records=True, **opts)
     assert_rows_equal(res.records(), want)
     check_clusters(res, s.n_samples, want, cutoffs)
+    res.close()
+    check_fused(idx, s.n_samples, want, cutoffs, **opts)
     return idx, res, want
 
 
