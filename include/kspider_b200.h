@@ -233,6 +233,13 @@ void ksb_device_free(ksb_device* dev);
 /* upload + accumulate + postpass in one call (the end-to-end path) */
 int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out);
 
+/* upload + ksb_device_cluster + release in one call: host index in, cluster labels out -- the end-to-end path
+ * when only the labels are wanted (H2D: the blob; D2H: 4 N + 16 bytes).  labels_out: host, d_labels_out: device
+ * memory of opts->device (either may be NULL; the multi-GPU path merges the device copies).  info_out (optional): rows, updates,
+ * launches, timings of the run.  A device that must spill runs the sort-reduce path and clusters its records. */
+int ksb_pairwise_cluster(const ksb_index* ix, const ksb_opts* opts, int dist_col, double cut_pct, uint32_t* labels_out,
+                         uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows, ksb_result_info* info_out);
+
 /* ---- results ---------------------------------------------------------------------------------- */
 int ksb_result_get_info(const ksb_result* r, ksb_result_info* info);
 const ksb_record* ksb_result_records(const ksb_result* r, uint64_t* n_rows);

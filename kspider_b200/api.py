@@ -139,6 +139,18 @@ class Index:
         check(lib().ksb_pairwise(self._h, C.byref(o), C.byref(h)))
         return Result(h)
 
+    def pairwise_cluster(self, dist_type: str = "max_cont", cutoff01: float = 0.0, cut_pct=None, d_labels_ptr: int = 0,
+                         to_host: bool = True, **kw):
+        """ksb_pairwise_cluster: upload + cluster-only step + release.  Returns (labels[N] or None, kept edges,
+        touched pairs, info).  d_labels_ptr: device uint32[N] that also receives the labels."""
+        o = make_opts(**{**kw, "want_records": False})
+        labels = np.empty(int(self.info.n_samples), dtype=np.uint32) if to_host else None
+        ne, nr, inf = C.c_uint64(), C.c_uint64(), ResultInfo()
+        cut = float(cutoff01) * 100 if cut_pct is None else float(cut_pct)
+        check(lib().ksb_pairwise_cluster(self._h, C.byref(o), DIST_COL[dist_type], cut, labels.ctypes.data if to_host else None,
+                                         C.c_void_p(d_labels_ptr) if d_labels_ptr else None, C.byref(ne), C.byref(nr), C.byref(inf)))
+        return labels, ne.value, nr.value, inf
+
     def close(self) -> None:
         if self._h:
             lib().ksb_index_free(self._h)

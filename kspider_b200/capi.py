@@ -91,6 +91,8 @@ _PROTOS = {
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "ksb_device_free": (None, [C.c_void_p]),
     "ksb_pairwise": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_void_p)]),
+    "ksb_pairwise_cluster": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64),
+                                       C.POINTER(C.c_uint64), C.POINTER(ResultInfo)]),
     "ksb_result_get_info": (C.c_int, [C.c_void_p, C.POINTER(ResultInfo)]),
     "ksb_result_records": (C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_write_tsv": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),

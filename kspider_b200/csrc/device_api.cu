@@ -1251,6 +1251,9 @@ done:
 }
 
 float ksb_threshold_float_pct(double cut);
+int ksb_cluster_pct(const ksb_result* r, int dist_col, double cut_pct, uint32_t* labels_out, uint64_t* n_edges);
+int ksb_cluster_pct_device(const ksb_result* r, int dist_col, double cut_pct, uint32_t* d_labels_out, uint64_t* n_edges);
+int ksb_device_get_info(const ksb_device* d, ksb_result_info* info);
 
 // Cluster-only step (north_star 3): for every dense pass, accumulate and scan its block ONCE (K56: containment,
 // threshold, append of the kept pairs only), then the unions over the kept-edge list and the label compression --
@@ -1371,6 +1374,49 @@ int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     r->info.t.host_post_ms = post_ms;
     r->info.t.host_free_ms = ms_since(t0);
     *out = r;
+    return KSB_OK;
+}
+
+// upload + cluster-only step + release in one call: the end-to-end path when only the labels are wanted
+// (host index in, N labels out; H2D = the blob, D2H = 4 N + 16 bytes).  A device that has to spill falls back to
+// the record path on the device (sort-reduce run, then K6 + K7 over its records).
+int ksb_pairwise_cluster(const ksb_index* ix, const ksb_opts* opts, int dist_col, double cut_pct, uint32_t* labels_out,
+                         uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows, ksb_result_info* info_out) {
+    if (!ix || (!labels_out && !d_labels_out)) { set_error("ksb_pairwise_cluster: null argument"); return KSB_ERR_ARG; }
+    using Clock = std::chrono::steady_clock;
+    auto ms_since = [](Clock::time_point t) { return std::chrono::duration<float, std::milli>(Clock::now() - t).count(); };
+    ksb_device* d = nullptr;
+    auto t0 = Clock::now();
+    int rc = upload_impl(ix, opts, &d, true);
+    if (rc) return rc;
+    const float setup_ms = ms_since(t0);
+    t0 = Clock::now();
+    ksb_result_info info;
+    std::memset(&info, 0, sizeof info);
+    if (d->spill) {
+        ksb_result* r = nullptr;
+        rc = ksb_device_run_spill(d, 0, &r);
+        if (rc == KSB_OK && labels_out) rc = ksb_cluster_pct(r, dist_col, cut_pct, labels_out, n_edges);
+        if (rc == KSB_OK && d_labels_out) rc = ksb_cluster_pct_device(r, dist_col, cut_pct, d_labels_out, n_edges);
+        if (rc == KSB_OK) { info = r->info; if (n_rows) *n_rows = r->info.n_rows; }
+        ksb_result_free(r);
+    } else {
+        uint64_t nr = 0;
+        rc = ksb_device_cluster(d, dist_col, cut_pct, nullptr, labels_out, d_labels_out, n_edges, &nr);
+        if (rc == KSB_OK) {
+            ksb_device_get_info(d, &info);
+            info.n_rows = nr;
+            if (n_rows) *n_rows = nr;
+        }
+    }
+    const float step_ms = ms_since(t0);
+    t0 = Clock::now();
+    ksb_device_free(d);
+    if (rc) return rc;
+    info.t.host_setup_ms = setup_ms;
+    info.t.host_accumulate_ms = step_ms;
+    info.t.host_free_ms = ms_since(t0);
+    if (info_out) *info_out = info;
     return KSB_OK;
 }
 

@@ -27,17 +27,22 @@ void pairwise(std::string index_prefix, int user_threads) {
     const int dev0 = (int)env_long("KSPIDER_DEVICE", 0);
     const double budget_gb = std::getenv("KSPIDER_DENSE_BUDGET_GB") ? std::atof(std::getenv("KSPIDER_DENSE_BUDGET_GB")) : 0.0;
 
+    // KSPIDER_VERBOSE=1: one extra line on STDERR with the phases of this call (the five stdout lines stay the reference's)
+    const bool verbose = env_long("KSPIDER_VERBOSE", 0) != 0;
+    double t_load = 0, t_seq = 0, t_gpu = 0, t_tsv = 0, t_side = 0;
     // the reference prints three load timers (src/pairwise.cpp:133,155,181); the loader does the
     // three loads in one call, so the first line carries the time and the other two are ~0
     auto t0 = Clock::now();
     ksb_index* ix = nullptr;
     if (ksb_index_load(index_prefix.c_str(), threads, &ix) != KSB_OK) fail("loading the index");
-    std::cout << "mapping colors to groups: " << secs_since(t0) << " secs" << std::endl;
+    t_load = secs_since(t0);
+    std::cout << "mapping colors to groups: " << t_load << " secs" << std::endl;
     t0 = Clock::now();
     std::cout << "parsing index colors: " << secs_since(t0) << " secs" << std::endl;
     t0 = Clock::now();
     if (ksb_write_seq_to_kmers(ix, (index_prefix + "_kSpider_seqToKmersNo.tsv").c_str()) != KSB_OK) { ksb_index_free(ix); fail("writing seqToKmersNo.tsv"); }
-    std::cout << "kmer counting: " << secs_since(t0) << " secs" << std::endl;
+    t_seq = secs_since(t0);
+    std::cout << "kmer counting: " << t_seq << " secs" << std::endl;
 
     t0 = Clock::now();
     std::vector<ksb_result*> res(gpus, nullptr);
@@ -73,18 +78,25 @@ void pairwise(std::string index_prefix, int user_threads) {
             ksb_index_free(ix);
             throw std::runtime_error(msg);
         }
-    std::cout << "pairwise hashmap construction: " << secs_since(t0) << " secs" << std::endl;
+    t_gpu = secs_since(t0);
+    std::cout << "pairwise hashmap construction: " << t_gpu << " secs" << std::endl;
     const std::string out = index_prefix + "_kSpider_pairwise.tsv";
     std::cout << "writing pairwise matrix to " << out << std::endl;
     int rc = KSB_OK;
+    t0 = Clock::now();
     for (int g = 0; g < gpus && rc == KSB_OK; g++)
         rc = g == 0 ? ksb_write_tsv(res[g], out.c_str(), threads) : ksb_append_tsv(res[g], out.c_str(), threads);
+    t_tsv = secs_since(t0);
+    t0 = Clock::now();
     // binary side-car for `cluster` / `--estimate-ani` (they then skip the text): the same rows, 32 bytes each
     const char* sc = std::getenv("KSPIDER_SIDECAR");
     if (rc == KSB_OK && !(sc && sc[0] == '0')) {
         const std::string side = index_prefix + "_kSpider_pairwise.ksb";
         for (int g = 0; g < gpus && rc == KSB_OK; g++) rc = ksb_write_sidecar(res[g], side.c_str(), out.c_str(), g != 0);
     }
+    t_side = secs_since(t0);
+    if (verbose) std::cerr << "ksb_phases load_s=" << t_load << " seq_to_kmers_s=" << t_seq << " gpu_s=" << t_gpu << " tsv_s=" << t_tsv
+                           << " sidecar_s=" << t_side << std::endl;
     const std::string err = rc == KSB_OK ? "" : ksb_last_error();
     for (auto* r : res) ksb_result_free(r);
     ksb_index_free(ix);

@@ -147,6 +147,62 @@ def cluster_merged(result, n_samples: int, dist_type: str, cutoff01: float, devi
 _LABEL_BUFFERS = {}
 
 
+def _label_buffers(n_samples: int, world: int, device: torch.device):
+    key = (n_samples, world, device.index)
+    buf = _LABEL_BUFFERS.get(key)
+    if buf is None:  # allocated once per shape: a step must not pay for allocator calls
+        buf = (torch.empty(n_samples, dtype=torch.int32, device=device),
+               torch.empty(world * n_samples, dtype=torch.int32, device=device),
+               torch.empty(n_samples, dtype=torch.int32, device=device),
+               torch.empty(n_samples, dtype=torch.int32, pin_memory=True))
+        _LABEL_BUFFERS.clear()
+        _LABEL_BUFFERS[key] = buf
+    return buf
+
+
+def pairwise_cluster_step(shard: Index, n_samples: int, dist_type: str, cutoff01: float, device: torch.device, **opts):
+    """The multi-GPU END-TO-END cluster-only step: every rank uploads its own row-block shard from its pinned host
+    memory (ksb_pairwise_cluster: pipelined H2D, accumulate, fused scan, unions; labels left on the GPU), then the
+    label all-gather, the K7 merge kernel and one pinned D2H.  Returns (labels, kept edges, touched pairs, info)."""
+    world = dist.get_world_size()
+    mine, allv, out, host = _label_buffers(n_samples, world, device)
+    _, n_edges, n_rows, info = shard.pairwise_cluster(dist_type, cutoff01, d_labels_ptr=mine.data_ptr(), to_host=False,
+                                                      device=device.index, **opts)
+    dist.all_gather_into_tensor(allv, mine)
+    stream = torch.cuda.current_stream(device).cuda_stream
+    check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
+                                         C.c_void_p(stream)))
+    host.copy_(out, non_blocking=True)
+    torch.cuda.current_stream(device).synchronize()
+    return host.numpy().view(np.uint32), n_edges, n_rows, info
+
+
+def cluster_step(dev: Device, n_samples: int, dist_type: str, cutoff01: float, device: torch.device):
+    """The multi-GPU cluster-only step: ksb_device_cluster on this rank's row block (accumulate + fused scan +
+    unions, labels left on the GPU), all-gather of every rank's labels over NVLink, K7 merge kernel, one pinned
+    D2H.  Returns (global labels as a numpy view of a pinned buffer the next call overwrites, this rank's kept
+    edges, this rank's touched pairs)."""
+    world = dist.get_world_size()
+    key = (n_samples, world, device.index)
+    buf = _LABEL_BUFFERS.get(key)
+    if buf is None:
+        buf = (torch.empty(n_samples, dtype=torch.int32, device=device),
+               torch.empty(world * n_samples, dtype=torch.int32, device=device),
+               torch.empty(n_samples, dtype=torch.int32, device=device),
+               torch.empty(n_samples, dtype=torch.int32, pin_memory=True))
+        _LABEL_BUFFERS.clear()
+        _LABEL_BUFFERS[key] = buf
+    mine, allv, out, host = buf
+    stream = torch.cuda.current_stream(device).cuda_stream
+    _, n_edges, n_rows = dev.cluster(n_samples, dist_type, cutoff01, stream=stream, d_labels_ptr=mine.data_ptr(), to_host=False)
+    dist.all_gather_into_tensor(allv, mine)
+    check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
+                                         C.c_void_p(stream)))
+    host.copy_(out, non_blocking=True)
+    torch.cuda.current_stream(device).synchronize()
+    return host.numpy().view(np.uint32), n_edges, n_rows
+
+
 def merge_labels(labels: np.ndarray, device: torch.device) -> np.ndarray:
     """all-gather of every rank's label array + K7 merge kernel (on CUDA); on a CPU `device` the
     gathered arrays are returned unmerged-by-kernel, merged with a host union-find used only by the

@@ -53,6 +53,7 @@ def write_raw_arrays(path: str, total_ids: np.ndarray, total_vals: np.ndarray,
                      color_ids: np.ndarray, offsets: np.ndarray, members: np.ndarray) -> None:
     """Vectorised KSBRAW01 writer for large synthetic indexes (CSR form)."""
     n_col = int(color_ids.size)
+    offsets = np.asarray(offsets).astype(np.int64)
     sizes = np.diff(offsets).astype("<u4")
     with open(path, "wb") as f:
         f.write(struct.pack("<Q", RAW_MAGIC))
