@@ -40,12 +40,14 @@ struct ksb_gram_chunk {
     uint32_t item_begin = 0, n_items = 0; // into the plan's item array
     uint32_t kblocks = 0;                 // K-blocks of all windows = pitch of the weight planes / 128
     uint32_t n_units = 0;                 // bitmap-build units (K-block x sample segment)
+    uint32_t unit_begin = 0;              // into the plan's unit array
 };
 struct ksb_gram_plan {
     bool built = false;
     std::vector<ksb_gram_chunk> chunks;
     ksb::GramWinDev* d_wins = nullptr;
     ksb::GramItem* d_items = nullptr;
+    ksb::GramUnit* d_units = nullptr;
 };
 
 struct ksb_device {
@@ -409,6 +411,7 @@ void ksb_device_free(ksb_device* d) {
     for (ksb_gram_plan& gp : d->gplan) {
         if (gp.d_wins) cudaFreeAsync(gp.d_wins, fs);
         if (gp.d_items) cudaFreeAsync(gp.d_items, fs);
+        if (gp.d_units) cudaFreeAsync(gp.d_units, fs);
     }
     if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
     if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
@@ -609,6 +612,7 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
         d->gwins.resize(d->desc.n_gram_wins);
         cudaError_t e = cudaMemcpy(d->gwins.data(), d->d_payload + d->desc.off_gram_wins, sizeof(GramWin) * d->desc.n_gram_wins, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { set_error("reading Gram windows from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
+
     }
     rc = finish_device(d, row_updates.data(), blo.data(), bhi.data(), opts);
     if (rc) { ksb_device_free(d); return rc; }
@@ -647,6 +651,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     const uint64_t waves = (wv && std::atoi(wv) > 0) ? (uint64_t)std::atoi(wv) : 4;
     std::vector<GramWinDev> wins;
     std::vector<GramItem> items;
+    std::vector<GramUnit> units;
     struct Rows { uint32_t ilo, ihi; };  // owned rows of a window, as offsets inside it
     std::vector<Rows> wrows;
     ksb_gram_chunk cur;
@@ -675,6 +680,26 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
                     }
         }
         cur.n_items = (uint32_t)items.size() - cur.item_begin;
+        // bitmap-build units of the chunk, the heaviest (most members to place) first
+        cur.unit_begin = (uint32_t)units.size();
+        for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) {
+            const uint32_t kblocks = (wins[w].n + kGramKBlock - 1) / kGramKBlock, segs = (wins[w].width + kGramSeg - 1) / kGramSeg;
+            for (uint32_t kb = 0; kb < kblocks; kb++)
+                for (uint32_t sg = 0; sg < segs; sg++) {
+                    GramUnit u;
+                    u.c0k = wins[w].c0 + (uint64_t)kb * kGramKBlock;
+                    u.kn = (uint32_t)std::min<uint64_t>(kGramKBlock, wins[w].n - (uint64_t)kb * kGramKBlock);
+                    u.xbase = wins[w].x0 + sg * kGramSeg;
+                    u.slen = std::min<uint32_t>(kGramSeg, wins[w].width - sg * kGramSeg);
+                    u.bits_row = wins[w].bits_off + (uint64_t)kb * wins[w].width + (uint64_t)sg * kGramSeg;
+                    u.wq_off = sg == 0 ? (wins[w].k0 + kb) * kGramKBlock : 0xFFFFFFFFu;
+                    units.push_back(u);
+                }
+        }
+        // proxy for the members a unit places: colours of the K-block x samples of the segment (wide windows hold long colours)
+        std::stable_sort(units.begin() + cur.unit_begin, units.end(),
+                         [&](const GramUnit& a, const GramUnit& b) { return (uint64_t)a.kn * a.slen > (uint64_t)b.kn * b.slen; });
+        if ((uint32_t)units.size() - cur.unit_begin != cur.n_units) cur.n_units = (uint32_t)units.size() - cur.unit_begin;
         auto cost = [&](const GramItem& it) {
             return (uint64_t)(it.kb1 - it.kb0) * (1 + std::min<uint32_t>(NB, (wins[cur.win_begin + it.win].width - it.j0 + kGramTile - 1) / kGramTile));
         };
@@ -742,6 +767,8 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         KSB_CUDA(cudaMallocAsync(&plan.d_items, sizeof(GramItem) * items.size(), d->stream));
         KSB_CUDA(cudaMemcpyAsync(plan.d_wins, wins.data(), sizeof(GramWinDev) * wins.size(), cudaMemcpyHostToDevice, d->stream));
         KSB_CUDA(cudaMemcpyAsync(plan.d_items, items.data(), sizeof(GramItem) * items.size(), cudaMemcpyHostToDevice, d->stream));
+        KSB_CUDA(cudaMallocAsync(&plan.d_units, sizeof(GramUnit) * std::max<size_t>(units.size(), 1), d->stream));
+        KSB_CUDA(cudaMemcpyAsync(plan.d_units, units.data(), sizeof(GramUnit) * units.size(), cudaMemcpyHostToDevice, d->stream));
         KSB_CUDA(cudaStreamSynchronize(d->stream));  // wins / items are locals
     }
     plan.built = true;
@@ -781,7 +808,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
             KSB_CUDA(cudaStreamWaitEvent(sb, ce, 0));
         }
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
-        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, gp.wins, gp.n_wins, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
+        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
                                  LaunchCfg{d->sms, sb}));
         if (sb != st) {
             KSB_CUDA(cudaEventRecord(ev_built, sb));

@@ -140,7 +140,7 @@ __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const Tr
 // kb_build: one CTA per build unit = (sub-window, K-block of 128 colours, segment of kGramSeg
 // samples).  The unit's piece of the K-block-major bitmap
 //     bits[(bits_off + kblock * width + sample - x0) * 4 + word]      bit (colour % 128) of the sample
-// is assembled in shared memory (shared atomicOr, 16 colours per warp with their loads batched) and written out once,
+// is assembled in shared memory (shared atomicOr over the K-block's contiguous member array) and written out once,
 // coalesced -- zeros included, so the bitmap needs no memset and no global atomics.  Segment 0 also
 // writes the byte planes of the weights to wq[plane * kpad + (k0 + kblock) * 128 + k].
 // ------------------------------------------------------------------------------------------------
@@ -148,100 +148,72 @@ template <class MT>
 __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __restrict__ gram_off,
                                                 const MT* __restrict__ gram_members,
                                                 const void* __restrict__ gram_weights, uint32_t weight_bits,
-                                                const GramWinDev* __restrict__ wins, uint32_t n_wins, uint32_t n_units,
+                                                const GramUnit* __restrict__ units, uint32_t n_units,
                                                 uint32_t kpad, uint32_t planes, uint32_t* __restrict__ bits,
                                                 uint8_t* __restrict__ wq) {
     __shared__ __align__(16) uint32_t sm[kGramSeg * 4];
     __shared__ unsigned long long sm_off[kKB + 1];
-    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const uint32_t tid = threadIdx.x;
+    if (blockIdx.x >= n_units) return;
+    GramUnit nxt = units[blockIdx.x];
     for (uint32_t unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-        uint32_t lo = 0, hi = n_wins;  // last window with u0 <= unit
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (__ldg(&wins[mid].u0) <= unit) lo = mid; else hi = mid;
-        }
-        const GramWinDev w = wins[lo];
-        const uint32_t segs = (w.width + kGramSeg - 1) / kGramSeg;
-        const uint32_t kb = (unit - w.u0) / segs, seg = (unit - w.u0) - kb * segs;
-        const uint32_t s0 = seg * kGramSeg, slen = min(kGramSeg, w.width - s0);
+        // the plan's table says everything about the unit (heaviest units first); the NEXT unit's entry is loaded now
+        const GramUnit gu = nxt;
+        if (unit + gridDim.x < n_units) nxt = units[unit + gridDim.x];
+        const uint32_t slen = gu.slen, kn = gu.kn;
         uint4* sm4 = reinterpret_cast<uint4*>(sm);
         for (uint32_t r = tid; r < slen; r += 256) sm4[r] = make_uint4(0u, 0u, 0u, 0u);
+        if (tid <= kn) sm_off[tid] = gram_off[gu.c0k + tid];
         __syncthreads();
-        const uint32_t kn = min(kKB, w.n - kb * kKB);  // colours of this K-block
-        // offsets of the K-block's colours staged once; then every warp takes 16 colours and issues the
-        // loads of all of them before the first shared atomic (the loads are independent: one memory
-        // latency per unit instead of one per colour)
-        const unsigned long long c0k = w.c0 + (unsigned long long)kb * kKB;
-        if (tid <= kn) sm_off[tid] = gram_off[c0k + tid];
-        __syncthreads();
-        uint32_t x[16];
+        // The colours of a K-block are consecutive in the Gram CSR, so their member lists are ONE contiguous array:
+        // every thread takes elements tid, tid + 256, ... of it, sixteen independent (coalesced) loads in flight before
+        // the first shared atomic, and follows the colour of its element through the staged offsets (its elements
+        // only move forward).  One memory latency per 4096 members instead of one per colour.
+        const unsigned long long o0 = sm_off[0];
+        const uint32_t L = (uint32_t)(sm_off[kn] - o0);
+        const uint32_t xbase = gu.xbase;
+        uint32_t k = 0;
+        for (uint32_t e0 = tid; e0 < L; e0 += 256u * 16u) {
+            uint32_t xs[16];
 #pragma unroll
-        for (uint32_t kk = 0; kk < 16; kk++) {
-            const uint32_t k = warp + 8u * kk;
-            x[kk] = 0xFFFFFFFFu;
-            if (k < kn) {
-                const unsigned long long o = sm_off[k];
-                if (lane < (uint32_t)(sm_off[k + 1] - o)) x[kk] = ldm<MT>(gram_members, o + lane) - w.x0 - s0;
+            for (uint32_t u = 0; u < 16; u++) {
+                const uint32_t e = e0 + 256u * u;
+                xs[u] = e < L ? ldm<MT>(gram_members, o0 + e) - xbase : 0xFFFFFFFFu;  // members outside the segment wrap to >= slen
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < 16; u++) {
+                const uint32_t e = e0 + 256u * u;
+                if (e >= L) break;
+                while (sm_off[k + 1] <= o0 + e) k++;
+                if (xs[u] < slen) atomicOr(sm + 4u * xs[u] + (k >> 5), 1u << (k & 31u));
             }
         }
-#pragma unroll
-        for (uint32_t kk = 0; kk < 16; kk++) {
-            const uint32_t k = warp + 8u * kk;
-            if (x[kk] < slen) atomicOr(sm + 4u * x[kk] + (k >> 5), 1u << (k & 31u));  // members outside the segment wrap to >= slen
-        }
-        for (uint32_t kk = 0; kk < 16; kk++) {  // colours with more than 32 members
-            const uint32_t k = warp + 8u * kk;
-            if (k >= kn) break;
-            const unsigned long long o = sm_off[k];
-            const uint32_t s = (uint32_t)(sm_off[k + 1] - o);
-            const uint32_t bit = 1u << (k & 31u), word = k >> 5;
-            if (s <= 96u) {  // one or two more members per lane: the plain loop (the batched one costs cfg2's s <= 64 colours 8 %)
-                for (uint32_t a = 32u + lane; a < s; a += 32) {
-                    const uint32_t xx = ldm<MT>(gram_members, o + a) - w.x0 - s0;
-                    if (xx < slen) atomicOr(sm + 4u * xx + word, bit);
-                }
-                continue;
-            }
-            // eight independent loads per lane before the first atomic: a 500-member colour is two memory
-            // latencies instead of fifteen dependent load -> atomicOr steps
-            for (uint32_t a0 = 32u + lane; a0 < s; a0 += 256u) {
-                uint32_t xs[8];
-#pragma unroll
-                for (uint32_t u = 0; u < 8; u++) {
-                    const uint32_t a = a0 + 32u * u;
-                    xs[u] = a < s ? ldm<MT>(gram_members, o + a) - w.x0 - s0 : 0xFFFFFFFFu;
-                }
-#pragma unroll
-                for (uint32_t u = 0; u < 8; u++)
-                    if (xs[u] < slen) atomicOr(sm + 4u * xs[u] + word, bit);
-            }
-        }
-        if (seg == 0 && tid < kKB) {
-            const uint32_t wt = tid < kn ? ldw(gram_weights, weight_bits, w.c0 + (unsigned long long)kb * kKB + tid) : 0u;
+        if (gu.wq_off != 0xFFFFFFFFu && tid < kKB) {
+            const uint32_t wt = tid < kn ? ldw(gram_weights, weight_bits, gu.c0k + tid) : 0u;
             for (uint32_t p = 0; p < planes; p++)
-                wq[(unsigned long long)p * kpad + (unsigned long long)(w.k0 + kb) * kKB + tid] = (uint8_t)(wt >> (8u * p));
+                wq[(unsigned long long)p * kpad + (unsigned long long)gu.wq_off + tid] = (uint8_t)(wt >> (8u * p));
         }
         __syncthreads();
-        uint4* dst = reinterpret_cast<uint4*>(bits) + w.bits_off + (unsigned long long)kb * w.width + s0;
+        uint4* dst = reinterpret_cast<uint4*>(bits) + gu.bits_row;
         for (uint32_t r = tid; r < slen; r += 256) dst[r] = sm4[r];
         __syncthreads();
     }
 }
 
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
-                            const void* gram_weights, uint32_t weight_bits, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
+                            const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {
     if (n_units == 0) return cudaSuccess;
     const unsigned cap = (unsigned)lc.sms * 6u;  // 32 KB of shared memory per CTA
     const unsigned ctas = n_units < cap ? n_units : cap;
     if (member_bits == 10)
-        kb_build<P10><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P10*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
+        kb_build<P10><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P10*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
     else if (member_bits == 12)
-        kb_build<P12><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P12*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
+        kb_build<P12><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const P12*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
     else if (member_bits == 16)
-        kb_build<uint16_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
+        kb_build<uint16_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
     else
-        kb_build<uint32_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint32_t*>(gram_members), gram_weights, weight_bits, wins, n_wins, n_units, kpad, planes, bits, wq);
+        kb_build<uint32_t><<<ctas, 256, 0, lc.stream>>>(gram_off, static_cast<const uint32_t*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
     return cudaGetLastError();
 }
 

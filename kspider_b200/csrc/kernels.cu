@@ -787,84 +787,130 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
 // the block.  counters: [0] touched cells (= TSV rows), [1] kept edges (may exceed the list's capacity: the
 // host then grows the list and repeats the step), both accumulated over the passes of a step.
 // ------------------------------------------------------------------------------------------------
-constexpr uint32_t kScanQueue = 2048;
+constexpr uint32_t kScanQueue = 1024;  // kept pairs of one block queued in shared memory; a denser block appends the rest directly
+constexpr uint32_t kScanCtasPerSm = 4;  // 48 KB of shared memory per CTA
 __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__ TriGeom G,
                                                          const uint32_t* __restrict__ touched,
                                                          const uint32_t* __restrict__ block_rows,
                                                          const uint32_t* __restrict__ totals, int dist_col, float cstar,
                                                          unsigned long long* __restrict__ edges, unsigned long long cap,
-                                                         unsigned long long* counters) {
+                                                         unsigned long long* counters, uint32_t n_blocks) {
+    // Persistent CTAs over the 2048-cell blocks of the owned block; the cells of the NEXT block are in flight (one
+    // TMA bulk copy into the other half of a shared double buffer, mbarrier complete_tx) while this block is
+    // decoded: the scan is a stream of 16 KB copies instead of a load -> wait -> compute chain per CTA.
+    __shared__ __align__(128) unsigned long long buf[2][kPostChunk];
     __shared__ unsigned long long q[kScanQueue];
+    __shared__ __align__(8) unsigned long long bars[2];
     __shared__ uint32_t qn, rows_cta;
     __shared__ unsigned long long qbase;
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-    if (threadIdx.x == 0) { qn = 0; rows_cta = 0; }
-    __syncthreads();
-    const unsigned long long wcell0 = (unsigned long long)blockIdx.x * kPostChunk + wid * (32u * kPostPerThread);
-    unsigned long long v[kPostPerThread];
-    uint32_t mine = 0;
-#pragma unroll
-    for (uint32_t k = 0; k < kPostPerThread; k++) {
-        const unsigned long long cell = wcell0 + 32u * k + lane;
-        bool f = false;
-        v[k] = 0ull;
-        if (cell < G.cells) {
-            v[k] = G.tri[cell];
-            f = v[k] != 0ull;
-            if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
-        }
-        mine |= (uint32_t)f << k;
+    const uint32_t bar0 = smem_u32(&bars[0]);
+    auto fetch = [&](uint32_t blk, uint32_t slot) {  // thread 0 only
+        const unsigned long long c0 = (unsigned long long)blk * kPostChunk;
+        const unsigned long long left = G.cells - c0;
+        const uint32_t bytes = (uint32_t)(((left < kPostChunk ? left : (unsigned long long)kPostChunk) * 8ull + 15ull) & ~15ull);  // the block is padded by 8 cells
+        mbar_expect_tx(bar0 + 8u * slot, bytes);
+        tma_load_1d(smem_u32(&buf[slot][0]), G.tri + c0, bytes, bar0 + 8u * slot);
+    };
+    if (threadIdx.x == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8u, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        qn = 0;
+        rows_cta = 0;
+        if (blockIdx.x < n_blocks) fetch(blockIdx.x, 0);
     }
-    uint32_t nrows = __reduce_add_sync(KSB_FULL, (uint32_t)__popc(mine));
-    if (lane == 0 && nrows) atomicAdd(&rows_cta, nrows);
-    if (mine != 0u) {
-        const unsigned long long g0 = G.base + wcell0 + lane;
-        uint32_t lo = __ldg(block_rows + blockIdx.x);
-        uint32_t hi = blockIdx.x + 1u < gridDim.x ? __ldg(block_rows + blockIdx.x + 1u) + 1u : G.rb + G.nrows;
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (__ldg(G.bandstart + mid) <= g0) lo = mid; else hi = mid;
+    __syncthreads();
+    uint32_t it = 0;
+    for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x, it++) {
+        const uint32_t slot = it & 1u;
+        if (threadIdx.x == 0 && blk + gridDim.x < n_blocks) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the other half was read (generic proxy) in the previous trip
+            fetch(blk + gridDim.x, slot ^ 1u);
         }
-        uint32_t i = lo;
-        uint32_t j = __ldg(G.band_lo + i) + (uint32_t)(g0 - __ldg(G.bandstart + i));
-        uint32_t jend = __ldg(G.band_hi + i);
-        uint32_t ti = __ldg(totals + i);
+        mbar_wait(bar0 + 8u * slot, (it >> 1) & 1u);
+        const unsigned long long wcell0 = (unsigned long long)blk * kPostChunk + wid * (32u * kPostPerThread);
+        unsigned long long v[kPostPerThread];
+        uint32_t mine = 0;
 #pragma unroll
         for (uint32_t k = 0; k < kPostPerThread; k++) {
-            if ((mine >> k) == 0u) break;
-            while (j >= jend) {
-                const uint32_t over = j - jend;
-                i++;
-                jend = __ldg(G.band_hi + i);
-                j = __ldg(G.band_lo + i) + over;
-                ti = __ldg(totals + i);
+            const unsigned long long cell = wcell0 + 32u * k + lane;
+            bool f = false;
+            v[k] = 0ull;
+            if (cell < G.cells) {
+                v[k] = buf[slot][wid * (32u * kPostPerThread) + 32u * k + lane];
+                f = v[k] != 0ull;
+                if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
             }
-            if ((mine >> k) & 1u) {
-                float cmin, cavg, cmax;
-                containment(v[k], ti, __ldg(totals + j), cmin, cavg, cmax);
-                const float c = dist_col == 3 ? cmin : (dist_col == 4 ? cavg : cmax);
-                if (!(c < cstar)) {  // NaN is kept, as in `if distance < cutoff: continue`
-                    const uint32_t pos = atomicAdd(&qn, 1u);
-                    if (pos < kScanQueue) q[pos] = ((unsigned long long)i << 32) | j;
-                    else {  // queue full (a dense clade at a low cut-off): straight to the list
-                        const unsigned long long o = atomicAdd(counters + 1, 1ull);
-                        if (o < cap) edges[o] = ((unsigned long long)i << 32) | j;
+            mine |= (uint32_t)f << k;
+        }
+        const uint32_t nrows = __reduce_add_sync(KSB_FULL, (uint32_t)__popc(mine));
+        if (lane == 0 && nrows) atomicAdd(&rows_cta, nrows);
+        if (mine != 0u) {
+            const unsigned long long g0 = G.base + wcell0 + lane;
+            uint32_t lo = __ldg(block_rows + blk);
+            uint32_t hi = blk + 1u < n_blocks ? __ldg(block_rows + blk + 1u) + 1u : G.rb + G.nrows;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (__ldg(G.bandstart + mid) <= g0) lo = mid; else hi = mid;
+            }
+            uint32_t i = lo;
+            uint32_t j = __ldg(G.band_lo + i) + (uint32_t)(g0 - __ldg(G.bandstart + i));
+            uint32_t jend = __ldg(G.band_hi + i);
+            uint32_t ti = __ldg(totals + i);
+#pragma unroll
+            for (uint32_t k = 0; k < kPostPerThread; k++) {
+                if ((mine >> k) == 0u) break;
+                while (j >= jend) {
+                    const uint32_t over = j - jend;
+                    i++;
+                    jend = __ldg(G.band_hi + i);
+                    j = __ldg(G.band_lo + i) + over;
+                    ti = __ldg(totals + i);
+                }
+                if ((mine >> k) & 1u) {
+                    const uint32_t tj = __ldg(totals + j);
+                    float c;
+                    if (dist_col != 4 && ti != 0u && tj != 0u) {
+                        // min / max of the two quotients = the quotient by the larger / smaller total: correctly rounded
+                        // division is monotone in the divisor, so this IS std::min / std::max of the two float32 values
+                        // (src/pairwise.cpp:260-264) -- with one division.  A zero total (inf / NaN) takes the full path.
+                        c = __fdiv_rn(__ull2float_rn(v[k]), __uint2float_rn(dist_col == 3 ? max(ti, tj) : min(ti, tj)));
+                    } else {
+                        float cmin, cavg, cmax;
+                        containment(v[k], ti, tj, cmin, cavg, cmax);
+                        c = dist_col == 3 ? cmin : (dist_col == 4 ? cavg : cmax);
+                    }
+                    if (!(c < cstar)) {  // NaN is kept, as in `if distance < cutoff: continue`
+                        const uint32_t pos = atomicAdd(&qn, 1u);
+                        if (pos < kScanQueue) q[pos] = ((unsigned long long)i << 32) | j;
+                        else {  // queue full: straight to the list
+                            const unsigned long long o = atomicAdd(counters + 1, 1ull);
+                            if (o < cap) edges[o] = ((unsigned long long)i << 32) | j;
+                        }
                     }
                 }
+                j += 32;
             }
-            j += 32;
+        }
+        __syncthreads();
+        const uint32_t n = min(qn, kScanQueue);
+        // the block's kept pairs go to the list with ONE global atomicAdd; the row counter once, at the end
+        const bool last = blk + gridDim.x >= n_blocks;
+        if (n != 0u || last) {
+            if (threadIdx.x == 0) {
+                qbase = n ? atomicAdd(counters + 1, (unsigned long long)n) : 0ull;
+                if (last && rows_cta) atomicAdd(counters, (unsigned long long)rows_cta);
+            }
+            __syncthreads();
+            const unsigned long long base = qbase;
+            for (uint32_t k = threadIdx.x; k < n; k += kPostThreads)
+                if (base + k < cap) edges[base + k] = q[k];
+            __syncthreads();
+            if (threadIdx.x == 0) qn = 0;
+            __syncthreads();
         }
     }
-    __syncthreads();
-    const uint32_t n = min(qn, kScanQueue);
-    if (threadIdx.x == 0) {
-        qbase = n ? atomicAdd(counters + 1, (unsigned long long)n) : 0ull;
-        if (rows_cta) atomicAdd(counters, (unsigned long long)rows_cta);
-    }
-    __syncthreads();
-    const unsigned long long base = qbase;
-    for (uint32_t k = threadIdx.x; k < n; k += kPostThreads)
-        if (base + k < cap) edges[base + k] = q[k];
 }
 
 // hook (atomicMin accelerator, see k6_hook_min) and union over a compact edge list whose length lives on the device
@@ -892,7 +938,9 @@ cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, cons
                             unsigned long long* counters, const LaunchCfg& lc) {
     const uint64_t nb = post_blocks(g.cells);
     if (nb == 0) return cudaSuccess;
-    k56_scan<<<(unsigned)nb, kPostThreads, 0, lc.stream>>>(g, touched_bits, block_rows, totals, dist_col, cstar, edges, cap, counters);
+    const uint64_t capc = (uint64_t)lc.sms * kScanCtasPerSm;
+    k56_scan<<<(unsigned)(nb < capc ? nb : capc), kPostThreads, 0, lc.stream>>>(g, touched_bits, block_rows, totals, dist_col, cstar, edges, cap,
+                                                                                counters, (uint32_t)nb);
     return cudaGetLastError();
 }
 cudaError_t launch_k6_edges(const unsigned long long* edges, unsigned long long cap, const unsigned long long* counters,

@@ -173,6 +173,15 @@ struct GramWinDev {
     uint32_t u0;                  // first bitmap-build unit (K-block x segment of kGramSeg samples) of the window
 };
 constexpr uint32_t kGramSeg = 2048;  // samples per bitmap-build unit: 32 KB of shared memory
+struct GramUnit {                    // one bitmap-build unit of a chunk (plan_gram lists them, heaviest first): a K-block
+                                     // of <= 128 colours of a window x a segment of <= kGramSeg samples
+    unsigned long long c0k;          // first colour of the K-block in the Gram CSR
+    unsigned long long bits_row;     // first 16-byte row of the unit in the chunk's bitmap buffer
+    uint32_t kn;                     // colours in the K-block
+    uint32_t xbase;                  // first sample of the segment
+    uint32_t slen;                   // samples in the segment
+    uint32_t wq_off;                 // offset of the K-block in a weight byte plane, 0xFFFFFFFF when another unit writes it
+};
 struct GramItem {
     uint32_t win;                 // index into the chunk's window list
     uint16_t i0, j0;              // first row of the 128-row tile and first column of its (up to NB) 128-column
@@ -193,7 +202,7 @@ struct GramParams {
 };
 uint32_t gram_cols_per_item(int planes);
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
-                            const void* gram_weights, uint32_t weight_bits, const GramWinDev* wins, uint32_t n_wins, uint32_t n_units,
+                            const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 
