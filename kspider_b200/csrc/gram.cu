@@ -161,8 +161,12 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         const GramUnit gu = nxt;
         if (unit + gridDim.x < n_units) nxt = units[unit + gridDim.x];
         const uint32_t slen = gu.slen, kn = gu.kn;
-        uint4* sm4 = reinterpret_cast<uint4*>(sm);
-        for (uint32_t r = tid; r < slen; r += 256) sm4[r] = make_uint4(0u, 0u, 0u, 0u);
+        // shared layout is WORD-major -- sm[word][sample], word = 32 colours -- so that the atomics of a warp, whose
+        // lanes hold consecutive (ascending) members of a colour, fall into different banks; the 16-byte rows of the
+        // bitmap are put together when the unit is written out
+#pragma unroll
+        for (uint32_t wd = 0; wd < 4; wd++)
+            for (uint32_t r = tid; r < slen; r += 256) sm[wd * kGramSeg + r] = 0u;
         if (tid <= kn) sm_off[tid] = gram_off[gu.c0k + tid];
         __syncthreads();
         // The colours of a K-block are consecutive in the Gram CSR, so their member lists are ONE contiguous array:
@@ -185,7 +189,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
                 const uint32_t e = e0 + 256u * u;
                 if (e >= L) break;
                 while (sm_off[k + 1] <= o0 + e) k++;
-                if (xs[u] < slen) atomicOr(sm + 4u * xs[u] + (k >> 5), 1u << (k & 31u));
+                if (xs[u] < slen) atomicOr(sm + (k >> 5) * kGramSeg + xs[u], 1u << (k & 31u));
             }
         }
         if (gu.wq_off != 0xFFFFFFFFu && tid < kKB) {
@@ -195,7 +199,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         }
         __syncthreads();
         uint4* dst = reinterpret_cast<uint4*>(bits) + gu.bits_row;
-        for (uint32_t r = tid; r < slen; r += 256) dst[r] = sm4[r];
+        for (uint32_t r = tid; r < slen; r += 256) dst[r] = make_uint4(sm[r], sm[kGramSeg + r], sm[2u * kGramSeg + r], sm[3u * kGramSeg + r]);
         __syncthreads();
     }
 }

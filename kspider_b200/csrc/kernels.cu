@@ -10,7 +10,9 @@
 #include "ddpow.hpp"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 #include <cub/device/device_scan.cuh>
 
@@ -789,10 +791,12 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kScanQueue = 1024;  // kept pairs of one block queued in shared memory; a denser block appends the rest directly
 constexpr uint32_t kScanCtasPerSm = 4;  // 48 KB of shared memory per CTA
+struct ScanCut { uint32_t mode, use_max, m, shift, tie_keeps; };
 __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__ TriGeom G,
                                                          const uint32_t* __restrict__ touched,
                                                          const uint32_t* __restrict__ block_rows,
                                                          const uint32_t* __restrict__ totals, int dist_col, float cstar,
+                                                         const ScanCut cut,
                                                          unsigned long long* __restrict__ edges, unsigned long long cap,
                                                          unsigned long long* counters, uint32_t n_blocks) {
     // Persistent CTAs over the 2048-cell blocks of the owned block; the cells of the NEXT block are in flight (one
@@ -832,17 +836,26 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
         const unsigned long long wcell0 = (unsigned long long)blk * kPostChunk + wid * (32u * kPostPerThread);
         unsigned long long v[kPostPerThread];
         uint32_t mine = 0;
+        const bool whole = (unsigned long long)(blk + 1u) * kPostChunk <= G.cells && touched == nullptr;  // CTA-uniform
+        if (whole) {
 #pragma unroll
-        for (uint32_t k = 0; k < kPostPerThread; k++) {
-            const unsigned long long cell = wcell0 + 32u * k + lane;
-            bool f = false;
-            v[k] = 0ull;
-            if (cell < G.cells) {
+            for (uint32_t k = 0; k < kPostPerThread; k++) {
                 v[k] = buf[slot][wid * (32u * kPostPerThread) + 32u * k + lane];
-                f = v[k] != 0ull;
-                if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
+                mine |= (uint32_t)(v[k] != 0ull) << k;
             }
-            mine |= (uint32_t)f << k;
+        } else {
+#pragma unroll
+            for (uint32_t k = 0; k < kPostPerThread; k++) {
+                const unsigned long long cell = wcell0 + 32u * k + lane;
+                bool f = false;
+                v[k] = 0ull;
+                if (cell < G.cells) {
+                    v[k] = buf[slot][wid * (32u * kPostPerThread) + 32u * k + lane];
+                    f = v[k] != 0ull;
+                    if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
+                }
+                mine |= (uint32_t)f << k;
+            }
         }
         const uint32_t nrows = __reduce_add_sync(KSB_FULL, (uint32_t)__popc(mine));
         if (lane == 0 && nrows) atomicAdd(&rows_cta, nrows);
@@ -871,6 +884,24 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
                 if ((mine >> k) & 1u) {
                     const uint32_t tj = __ldg(totals + j);
                     float c;
+                    const uint32_t T = cut.use_max ? max(ti, tj) : min(ti, tj);
+                    if (cut.mode == 1u && v[k] < (1ull << 24) && T - 1u < (1u << 24) - 1u && min(ti, tj) != 0u) {
+                        // EXACT integer form of `float32 quotient >= c*` (no conversion, no division): the correctly
+                        // rounded quotient S / T reaches c* iff the real quotient reaches the midpoint M * 2^-shift
+                        // between c* and its predecessor (ties go to the even one of the two), i.e. iff
+                        // S << shift >= M * T.  S < 2^24 and T < 2^24 are exact as float32, M < 2^26, shift <= 39.
+                        const unsigned long long lhs = v[k] << cut.shift, rhs = (unsigned long long)cut.m * T;
+                        if (lhs > rhs || (lhs == rhs && cut.tie_keeps)) {
+                            const uint32_t pos = atomicAdd(&qn, 1u);
+                            if (pos < kScanQueue) q[pos] = ((unsigned long long)i << 32) | j;
+                            else {
+                                const unsigned long long o = atomicAdd(counters + 1, 1ull);
+                                if (o < cap) edges[o] = ((unsigned long long)i << 32) | j;
+                            }
+                        }
+                        j += 32;
+                        continue;
+                    }
                     if (dist_col != 4 && ti != 0u && tj != 0u) {
                         // min / max of the two quotients = the quotient by the larger / smaller total: correctly rounded
                         // division is monotone in the divisor, so this IS std::min / std::max of the two float32 values
@@ -933,14 +964,42 @@ __global__ void __launch_bounds__(256) k6_edges_union(const unsigned long long* 
     }
 }
 
+// Integer form of the threshold for the min / max column (see k56_scan): c* = m24 * 2^E; the midpoint between c* and its
+// predecessor is M * 2^-shift with M < 2^26.  mode 0 = use the float path (avg column, c* of 0 / inf / NaN, or a c* so
+// small that S << shift could overflow).
+static ScanCut make_scan_cut(int dist_col, float cstar) {
+    ScanCut c{};
+    c.mode = 0;
+    c.use_max = dist_col == 3 ? 1u : 0u;  // min containment = quotient by the LARGER total
+    if (dist_col == 4 || !(cstar > 0.0f) || !std::isfinite(cstar)) return c;
+    uint32_t bits;
+    std::memcpy(&bits, &cstar, 4);
+    if ((bits >> 23) == 0u) return c;  // subnormal c*
+    uint32_t pb = bits - 1u;           // predecessor (c* > 0 and normal, so this is the next float below)
+    float pred;
+    std::memcpy(&pred, &pb, 4);
+    const double mid = ((double)pred + (double)cstar) * 0.5;  // exact: <= 25 significant bits
+    int e = 0;
+    const double fr = std::frexp(mid, &e);                    // mid = fr * 2^e, 0.5 <= fr < 1
+    const double M = std::ldexp(fr, 26);                      // integer < 2^26
+    const int shift = 26 - e;
+    if (M != std::floor(M) || shift < 0 || shift > 39) return c;
+    c.m = (uint32_t)M;
+    c.shift = (uint32_t)shift;
+    c.tie_keeps = (bits & 1u) == 0u ? 1u : 0u;  // round-half-to-even lands on c* iff its mantissa is even
+    c.mode = 1;
+    return c;
+}
+
 cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, const uint32_t* block_rows, const uint32_t* totals,
                             int dist_col, float cstar, unsigned long long* edges, unsigned long long cap,
                             unsigned long long* counters, const LaunchCfg& lc) {
     const uint64_t nb = post_blocks(g.cells);
     if (nb == 0) return cudaSuccess;
+    const ScanCut cut = make_scan_cut(dist_col, cstar);
     const uint64_t capc = (uint64_t)lc.sms * kScanCtasPerSm;
-    k56_scan<<<(unsigned)(nb < capc ? nb : capc), kPostThreads, 0, lc.stream>>>(g, touched_bits, block_rows, totals, dist_col, cstar, edges, cap,
-                                                                                counters, (uint32_t)nb);
+    k56_scan<<<(unsigned)(nb < capc ? nb : capc), kPostThreads, 0, lc.stream>>>(g, touched_bits, block_rows, totals, dist_col, cstar, cut, edges,
+                                                                                cap, counters, (uint32_t)nb);
     return cudaGetLastError();
 }
 cudaError_t launch_k6_edges(const unsigned long long* edges, unsigned long long cap, const unsigned long long* counters,
