@@ -41,6 +41,7 @@ struct ksb_gram_chunk {
     uint32_t kblocks = 0;                 // K-blocks of all windows = pitch of the weight planes / 128
     uint32_t n_units = 0;                 // bitmap-build units (K-block x sample segment)
     uint32_t unit_begin = 0;              // into the plan's unit array
+    bool pipe = false;                    // short items: k4_gram_pipe (static schedule, double-buffered accumulators)
 };
 struct ksb_gram_plan {
     bool built = false;
@@ -644,7 +645,12 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     ksb_gram_plan& plan = d->gplan[pass];
     if (plan.built) return KSB_OK;
     const ksb_pass& p = d->passes[pass];
-    const uint32_t NB = gram_cols_per_item((int)d->g_planes);
+    const uint32_t NB_long = gram_cols_per_item((int)d->g_planes);
+    uint32_t NB = NB_long;
+    // chunks whose windows are all short in K (a clade / family window: a few K-blocks per tile pair) run the
+    // pipelined variant; KSPIDER_GRAM_PIPE=0 keeps everything on k4_gram, =<n> moves the K-block limit
+    const char* gpe = std::getenv("KSPIDER_GRAM_PIPE");
+    const uint32_t pipe_max_kb = d->g_planes > 2 ? 0u : (gpe ? (uint32_t)std::atoi(gpe) : 64u);
     const char* cm = std::getenv("KSPIDER_GRAM_CHUNK_MB");  // tuning knob; default keeps a chunk's bitmap L2-resident
     const uint64_t chunk_rows = ((cm && std::atoi(cm) > 0) ? (uint64_t)std::atoi(cm) : 64) << 16;  // MB -> 16-byte rows
     const char* wv = std::getenv("KSPIDER_GRAM_WAVES");     // tuning knob
@@ -657,6 +663,10 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     ksb_gram_chunk cur;
     auto close_chunk = [&]() {
         if (cur.n_wins == 0) return;
+        uint32_t max_kb = 0;
+        for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) max_kb = std::max<uint32_t>(max_kb, (wins[w].n + kGramKBlock - 1) / kGramKBlock);
+        cur.pipe = max_kb <= pipe_max_kb;
+        NB = cur.pipe ? gram_cols_per_item_pipe((int)d->g_planes) : NB_long;
         // base items, then K splits so that there are ~`waves` items per SM
         uint64_t base = 0;
         for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++)
@@ -735,7 +745,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
             wd.width = w.width;
             wd.tiles = tiles;
             wd.k0 = cur.kblocks;
-            wd.u0 = cur.n_units;
+            wd.extent = w.extent ? (uint32_t)std::min<uint64_t>(w.extent, w.width) : 0u;
             cur.n_units += (uint32_t)kbs * ((w.width + kGramSeg - 1) / kGramSeg);
             wins.push_back(wd);
             wrows.push_back(rows);
@@ -814,7 +824,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
             KSB_CUDA(cudaEventRecord(ev_built, sb));
             KSB_CUDA(cudaStreamWaitEvent(st, ev_built, 0));
         }
-        KSB_CUDA(launch_k4_gram(gp, g, LaunchCfg{d->sms, st}));
+        KSB_CUDA(c.pipe ? launch_k4_gram_pipe(gp, g, LaunchCfg{d->sms, st}) : launch_k4_gram(gp, g, LaunchCfg{d->sms, st}));
         d->launches += 2;
         first = false;
     }

@@ -153,6 +153,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
                                                 uint8_t* __restrict__ wq) {
     __shared__ __align__(16) uint32_t sm[kGramSeg * 4];
     __shared__ unsigned long long sm_off[kKB + 1];
+    __shared__ uint32_t sm_rel[kKB + 1];
     const uint32_t tid = threadIdx.x;
     if (blockIdx.x >= n_units) return;
     GramUnit nxt = units[blockIdx.x];
@@ -169,26 +170,40 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
             for (uint32_t r = tid; r < slen; r += 256) sm[wd * kGramSeg + r] = 0u;
         if (tid <= kn) sm_off[tid] = gram_off[gu.c0k + tid];
         __syncthreads();
-        // The colours of a K-block are consecutive in the Gram CSR, so their member lists are ONE contiguous array:
-        // every thread takes elements tid, tid + 256, ... of it, sixteen independent (coalesced) loads in flight before
-        // the first shared atomic, and follows the colour of its element through the staged offsets (its elements
-        // only move forward).  One memory latency per 4096 members instead of one per colour.
+        // The colours of a K-block are consecutive in the Gram CSR, so their member lists are ONE contiguous array.
+        // Every warp takes a contiguous eighth of it, 32 elements per load instruction (coalesced), sixteen
+        // independent loads in flight per lane before the first shared atomic; the colour of a lane's element is
+        // followed through the staged offsets (relative, 32-bit) -- consecutive elements of a lane are 32 apart, so
+        // the colour index advances by at most one or two per element.
         const unsigned long long o0 = sm_off[0];
         const uint32_t L = (uint32_t)(sm_off[kn] - o0);
+        __syncthreads();
+        if (tid <= kn) sm_rel[tid] = (uint32_t)(sm_off[tid] - o0);
+        __syncthreads();
         const uint32_t xbase = gu.xbase;
+        const uint32_t per_warp = ((L + 8u * 32u - 1u) / (8u * 32u)) * 32u;   // multiple of 32
+        const uint32_t wb = (tid >> 5) * per_warp, we = min(L, wb + per_warp);
         uint32_t k = 0;
-        for (uint32_t e0 = tid; e0 < L; e0 += 256u * 16u) {
+        if (wb < we) {  // first colour of the warp's slice: binary search once
+            uint32_t lo = 0, hi = kn;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (sm_rel[mid] <= wb) lo = mid; else hi = mid;
+            }
+            k = lo;
+        }
+        for (uint32_t e0 = wb + (tid & 31u); e0 < we; e0 += 32u * 16u) {
             uint32_t xs[16];
 #pragma unroll
             for (uint32_t u = 0; u < 16; u++) {
-                const uint32_t e = e0 + 256u * u;
-                xs[u] = e < L ? ldm<MT>(gram_members, o0 + e) - xbase : 0xFFFFFFFFu;  // members outside the segment wrap to >= slen
+                const uint32_t e = e0 + 32u * u;
+                xs[u] = e < we ? ldm<MT>(gram_members, o0 + e) - xbase : 0xFFFFFFFFu;  // members outside the segment wrap to >= slen
             }
 #pragma unroll
             for (uint32_t u = 0; u < 16; u++) {
-                const uint32_t e = e0 + 256u * u;
-                if (e >= L) break;
-                while (sm_off[k + 1] <= o0 + e) k++;
+                const uint32_t e = e0 + 32u * u;
+                if (e >= we) break;
+                while (sm_rel[k + 1] <= e) k++;
                 if (xs[u] < slen) atomicOr(sm + (k >> 5) * kGramSeg + xs[u], 1u << (k & 31u));
             }
         }
@@ -489,6 +504,252 @@ cudaError_t launch_imma_peak(uint32_t iters, uint32_t* sink, double* macs, const
     if (macs) *macs = (double)lc.sms * (double)iters * 8.0 * 128.0 * 256.0 * 32.0;
     return cudaGetLastError();
 }
+
+// ------------------------------------------------------------------------------------------------
+// k4_gram_pipe<P> (P = 1, 2): the same Gram product for chunks whose items are SHORT (a handful of K-blocks per
+// tile pair: clade / family windows of a FracMinHash index).  There the time of k4_gram goes to the per-item
+// serial chain -- fetch the item, fill the pipeline, wait for the last MMA, run the epilogue, CTA-wide barrier --
+// not to the tensor pipe.  This variant removes the chain:
+//   * static schedule: CTA c takes items c, c + gridDim, ... of the plan's cost-sorted list, so every role walks
+//     the same item sequence on its own -- no counter, no CTA-wide barrier between items;
+//   * the accumulators are DOUBLE-BUFFERED in TMEM (2 x 256 columns: an item covers NB = 2 / P column tiles), the
+//     MMA warp starts item n + 1 in the other buffer as soon as its operands arrive;
+//   * the producer warps expand item n + 1 BEFORE they run the epilogue of item n, so the tensor core works on
+//     n + 1 (and the loader is already fetching n + 2) while TMEM -> red of item n runs;
+//   * three operand stages, the loader's 4-slot ring freed by its own mbarrier, epilogue transposes in their own
+//     shared scratch (the stages stay busy).
+// Roles and operand expansion as in k4_gram.  `extent` of a window (samples really touched) lets the epilogue skip
+// the row / column groups that are padding, and groups entirely below the diagonal are skipped.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kPipeStages = 3;
+template <int P>
+__global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams prm, const __grid_constant__ TriGeom G) {
+    constexpr uint32_t NB = 2 / P;
+    constexpr uint32_t kStageBytes = (P + NB) * kTileBytes;
+    constexpr uint32_t kSlotBytes = (1 + NB) * 2048 + P * 128;
+    constexpr uint32_t kWOff = (1 + NB) * 2048;
+    constexpr uint32_t kScratch = kProducerWarps * 32 * 17 * 4;
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* ring = smem + kPipeStages * kStageBytes;
+    const uint32_t smem_a = smem_u32(smem), ring_a = smem_a + kPipeStages * kStageBytes;
+    const uint32_t scratch_a = ring_a + kRing * kSlotBytes;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(ring + kRing * kSlotBytes + kScratch);
+    // bars: full[3], empty[3], ready[4], ring_free[4], acc_full[2], acc_free[2]
+    const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8u * kPipeStages, bar_ready = bar_empty + 8u * kPipeStages;
+    const uint32_t bar_rfree = bar_ready + 8u * kRing, bar_afull = bar_rfree + 8u * kRing, bar_afree = bar_afull + 16u;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kPipeStages + 2 * kRing + 4);
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 32) {
+        for (uint32_t s = 0; s < kPipeStages; s++) { mbar_init(bar_full + 8u * s, kProducerWarps); mbar_init(bar_empty + 8u * s, 1); }
+        for (uint32_t s = 0; s < kRing; s++) { mbar_init(bar_ready + 8u * s, 1); mbar_init(bar_rfree + 8u * s, kProducerWarps); }
+        for (uint32_t s = 0; s < 2; s++) { mbar_init(bar_afull + 8u * s, 1); mbar_init(bar_afree + 8u * s, kProducerWarps); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < kProducerWarps) {
+        // ---------------- producers: expand item n + 1, then the epilogue of item n
+        uint32_t it = 0, n = 0;
+        GramItem pgi{};          // the item whose epilogue is pending
+        GramWinDev pwin{};
+        bool pending = false;
+        auto epilogue = [&](const GramItem& gi, const GramWinDev& win, uint32_t m) {
+            const uint32_t b = m & 1u;
+            mbar_wait(bar_afull + 8u * b, (m >> 1) & 1u);
+            tc_fence_after();
+            const uint32_t i0 = gi.i0, j0 = gi.j0;
+            const uint32_t ncol = min(NB, (win.width - j0 + kTile - 1) / kTile);
+            const uint32_t ext = win.extent ? win.extent : win.width;
+            const uint32_t tp = scratch_a + warp * (32 * 17 * 4);
+            const uint32_t lq = warp & 3u, wg = warp >> 2;
+            const uint32_t rsel = lane >> 4, csel = lane & 15u;
+            const uint32_t row0 = i0 + 32u * lq;            // first row of this warp's 32-row group
+            if (row0 < ext) {
+                for (uint32_t ch = wg; ch < ncol * 8u; ch += 4) {
+                    const uint32_t ct = ch >> 3, c16 = ch & 7u;
+                    const uint32_t col0 = j0 + ct * kTile + c16 * 16u;
+                    if (col0 >= ext || col0 + 15u <= row0) continue;  // padding columns, or every cell on / below the diagonal (warp-uniform)
+                    unsigned long long acc[16];
+#pragma unroll
+                    for (uint32_t y = 0; y < 16; y++) acc[y] = 0ull;
+#pragma unroll
+                    for (int p = 0; p < P; p++) {
+                        uint32_t v[16];
+                        tmem_ld16(tmem + ((32u * lq) << 16) + b * 256u + (p * NB + ct) * kTile + c16 * 16u, v);
+                        __syncwarp();
+#pragma unroll
+                        for (uint32_t x = 0; x < 16; x++) sts32(tp + (lane * 17 + x) * 4u, v[x]);
+                        __syncwarp();
+#pragma unroll
+                        for (uint32_t y = 0; y < 16; y++)
+                            acc[y] += (unsigned long long)lds32(tp + ((2 * y + rsel) * 17 + csel) * 4u) << (8 * p);
+                    }
+                    const uint32_t jl = col0 + csel;
+                    const uint32_t j = win.x0 + jl;
+#pragma unroll
+                    for (uint32_t y = 0; y < 16; y++) {
+                        const uint32_t il = row0 + 2 * y + rsel;
+                        const uint32_t i = win.x0 + il;
+                        if (il < jl && jl < win.width && j < G.n && acc[y] != 0ull) {
+                            const unsigned long long ra = gram_row_addr(i, G);
+                            if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_afree + 8u * b);
+        };
+        for (uint32_t item = blockIdx.x; item < prm.n_items; item += gridDim.x, n++) {
+            const GramItem gi = prm.items[item];
+            const GramWinDev win = prm.wins[gi.win];
+            const uint32_t ncol = min(NB, (win.width - gi.j0 + kTile - 1) / kTile);
+            const uint32_t nunits = (1u + ncol) * 256u;  // (tile, row, half K-block)
+            for (uint32_t kb = gi.kb0; kb < gi.kb1; kb++, it++) {
+                const uint32_t st = it % kPipeStages, slot = it % kRing;
+                mbar_wait(bar_ready + 8u * slot, (it / kRing) & 1u);
+                if (it >= kPipeStages) mbar_wait(bar_empty + 8u * st, ((it / kPipeStages) - 1u) & 1u);
+                const uint32_t stage = smem_a + st * kStageBytes;
+                const uint32_t rs = ring_a + slot * kSlotBytes;
+#pragma unroll
+                for (uint32_t k = 0; k < 2; k++) {
+                    const uint32_t u = tid + kProducers * k;
+                    if (u >= nunits) continue;
+                    const uint32_t tsel = u >> 8, r = (u & 255u) >> 1, h = u & 1u, sw = r & 7u;
+                    const uint2 bits = lds64(rs + u * 8u);
+                    const uint32_t drow = stage + (tsel == 0 ? 0u : (P + tsel - 1) * kTileBytes) + (r >> 3) * 1024u + (r & 7u) * 128u;
+#pragma unroll
+                    for (uint32_t wd = 0; wd < 2; wd++) {
+                        const uint32_t word = wd ? bits.y : bits.x;
+                        uint32_t s4[8];
+#pragma unroll
+                        for (uint32_t q = 0; q < 8; q++) s4[q] = (((word >> (4 * q)) & 0xFu) * 0x00204081u) & 0x01010101u;
+#pragma unroll
+                        for (uint32_t c = 0; c < 2; c++) {
+                            const uint32_t chunk = (h * 2 + wd) * 2 + c;
+                            const uint32_t dst = drow + ((chunk ^ sw) << 4);
+                            if (tsel != 0) {
+                                sts128(dst, s4[4 * c], s4[4 * c + 1], s4[4 * c + 2], s4[4 * c + 3]);
+                            } else {
+#pragma unroll
+                                for (int p = 0; p < P; p++) {
+                                    const uint4 w = lds128(rs + kWOff + p * 128 + chunk * 16);
+                                    sts128(dst + p * kTileBytes, (s4[4 * c] * 0xFFu) & w.x, (s4[4 * c + 1] * 0xFFu) & w.y,
+                                           (s4[4 * c + 2] * 0xFFu) & w.z, (s4[4 * c + 3] * 0xFFu) & w.w);
+                                }
+                            }
+                        }
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) { mbar_arrive(bar_full + 8u * st); mbar_arrive(bar_rfree + 8u * slot); }
+            }
+            if (pending) epilogue(pgi, pwin, n - 1u);
+            pgi = gi;
+            pwin = win;
+            pending = true;
+        }
+        if (pending) epilogue(pgi, pwin, n - 1u);
+    } else if (warp == kProducerWarps) {
+        // ---------------- MMA issuer (one thread)
+        if (lane == 0) {
+            uint32_t it = 0, n = 0;
+            for (uint32_t item = blockIdx.x; item < prm.n_items; item += gridDim.x, n++) {
+                const GramItem gi = prm.items[item];
+                const GramWinDev win = prm.wins[gi.win];
+                const uint32_t ncol = min(NB, (win.width - gi.j0 + kTile - 1) / kTile);
+                const uint32_t b = n & 1u;
+                if (n >= 2u) { mbar_wait(bar_afree + 8u * b, ((n >> 1) - 1u) & 1u); tc_fence_after(); }
+                const uint32_t nn = kTile * ncol;
+                for (uint32_t kb = gi.kb0; kb < gi.kb1; kb++, it++) {
+                    const uint32_t st = it % kPipeStages;
+                    mbar_wait(bar_full + 8u * st, (it / kPipeStages) & 1u);
+                    tc_fence_after();
+                    const uint32_t sbase = smem_a + st * kStageBytes;
+                    const uint64_t bdesc = umma_desc_sw128(sbase + P * kTileBytes);
+#pragma unroll
+                    for (int p = 0; p < P; p++) {
+                        const uint64_t adesc = umma_desc_sw128(sbase + p * kTileBytes);
+#pragma unroll
+                        for (uint32_t k = 0; k < 4; k++)
+                            umma_i8(tmem + b * 256u + (p * NB) * kTile, adesc + 2 * k, bdesc + 2 * k, umma_idesc(nn), (kb > gi.kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(bar_empty + 8u * st);
+                    if (kb + 1 == gi.kb1) umma_commit(bar_afull + 8u * b);
+                }
+            }
+        }
+    } else {
+        // ---------------- TMA loader (one thread)
+        if (lane == 0) {
+            uint32_t it = 0;
+            const uint8_t* gbits = reinterpret_cast<const uint8_t*>(prm.bits);
+            for (uint32_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+                const GramItem gi = prm.items[item];
+                const GramWinDev win = prm.wins[gi.win];
+                const uint32_t ncol = min(NB, (win.width - gi.j0 + kTile - 1) / kTile);
+                const uint32_t bytes = (1u + ncol) * 2048u + P * 128u;
+                for (uint32_t kb = gi.kb0; kb < gi.kb1; kb++, it++) {
+                    const uint32_t slot = it % kRing;
+                    if (it >= kRing) mbar_wait(bar_rfree + 8u * slot, ((it / kRing) - 1u) & 1u);
+                    const uint32_t bar = bar_ready + 8u * slot;
+                    const uint32_t dst = ring_a + slot * kSlotBytes;
+                    const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.width) * 16ull;
+                    mbar_expect_tx(bar, bytes);
+                    tma_load_1d(dst, kbase + (unsigned long long)gi.i0 * 16ull, 2048u, bar);
+                    tma_load_1d(dst + 2048u, kbase + (unsigned long long)gi.j0 * 16ull, ncol * 2048u, bar);
+#pragma unroll
+                    for (int p = 0; p < P; p++)
+                        tma_load_1d(dst + kWOff + p * 128, prm.wq + (unsigned long long)p * prm.kpad + (unsigned long long)(win.k0 + kb) * kKB, 128u, bar);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
+    }
+}
+
+static size_t gram_pipe_smem_bytes(int P) {
+    const size_t nb = 2 / P;
+    return 1024 + kPipeStages * (P + nb) * (size_t)kTileBytes + kRing * ((1 + nb) * 2048 + P * 128) + kProducerWarps * 32 * 17 * 4 +
+           8 * (2 * kPipeStages + 2 * kRing + 4) + 16;
+}
+
+template <int P>
+static cudaError_t launch_gram_pipe_p(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc) {
+    const size_t smem = gram_pipe_smem_bytes(P);
+    cudaError_t e = cudaFuncSetAttribute(k4_gram_pipe<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    unsigned long long ctas = prm.n_items < (unsigned long long)lc.sms ? prm.n_items : (unsigned long long)lc.sms;
+    k4_gram_pipe<P><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_k4_gram_pipe(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc) {
+    if (prm.n_items == 0) return cudaSuccess;
+    switch (prm.planes) {
+        case 1: return launch_gram_pipe_p<1>(prm, g, lc);
+        case 2: return launch_gram_pipe_p<2>(prm, g, lc);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+uint32_t gram_cols_per_item_pipe(int planes) { return planes <= 1 ? 2u : 1u; }
 
 uint32_t gram_cols_per_item(int planes) { return planes <= 1 ? 4u : (planes == 2 ? 2u : 1u); }
 

@@ -261,6 +261,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             double gain = 0.0;
             std::vector<std::pair<uint64_t, uint64_t>> kept;  // [begin, end) ranges of cand
             std::vector<std::pair<uint64_t, uint64_t>> kept_span;  // (first sample, width) of the kept windows
+            std::vector<uint64_t> kept_extent;                      // samples from the first to the last touched one
             for (uint64_t b = 0; b < cand.size();) {
                 uint64_t e = b, upd = 0, mem = 0, lo = ~0ull, hi = 0;
                 while (e < cand.size() && cand[e].first == cand[b].first) {
@@ -283,10 +284,10 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 const double t_gram = width * width * kpad * (double)planes / rate + (double)mem / 1.0e11 +
                                       tiles * (tiles + 1) / 2 / (double)(4 / planes) * 30e-9 + width * width / 2 / kGramRedRate;
                 const double t_red = (double)upd / kGramRedRate;
-                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); kept_span.emplace_back(lo, span_w); gain += t_red - t_gram; }
+                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); kept_span.emplace_back(lo, span_w); kept_extent.push_back(hi - lo); gain += t_red - t_gram; }
                 b = e;
             }
-            if (forced < 2 && gain < 30e-6) { kept.clear(); kept_span.clear(); }  // launches + memsets of the path itself
+            if (forced < 2 && gain < 30e-6) { kept.clear(); kept_span.clear(); kept_extent.clear(); }  // launches + memsets of the path itself
             std::fill(gkey.begin(), gkey.end(), NOKEY);
             uint64_t smallest = ~0ull;
             const bool shrink = !(std::getenv("KSPIDER_GRAM_SHRINK") && std::atoi(std::getenv("KSPIDER_GRAM_SHRINK")) == 0);
@@ -299,11 +300,12 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 if (shrink) {
                     w.x0 = (uint32_t)kept_span[ki].first;
                     w.width = (uint32_t)kept_span[ki].second;
+                    w.extent = (uint32_t)std::min<uint64_t>(kept_extent[ki], w.width);
                 } else {
                     w.x0 = (uint32_t)(cand[r.first].first >> 8);
                     w.width = (uint32_t)std::min<uint64_t>(lv.width, (npad - w.x0 + kGramTile - 1) / kGramTile * kGramTile);
+                    w.extent = 0;
                 }
-                w.pad = 0;
                 gwins.push_back(w);
                 for (uint64_t i = r.first; i < r.second; i++) {
                     gkey[cand[i].second] = gram_list.size();

@@ -790,7 +790,7 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
 // host then grows the list and repeats the step), both accumulated over the passes of a step.
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kScanQueue = 1024;  // kept pairs of one block queued in shared memory; a denser block appends the rest directly
-constexpr uint32_t kScanCtasPerSm = 4;  // 48 KB of shared memory per CTA
+constexpr uint32_t kScanCtasPerSm = 6;  // 24 KB of shared memory, 42 registers x 256 threads per CTA
 struct ScanCut { uint32_t mode, use_max, m, shift, tie_keeps; };
 __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__ TriGeom G,
                                                          const uint32_t* __restrict__ touched,
@@ -799,10 +799,11 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
                                                          const ScanCut cut,
                                                          unsigned long long* __restrict__ edges, unsigned long long cap,
                                                          unsigned long long* counters, uint32_t n_blocks) {
-    // Persistent CTAs over the 2048-cell blocks of the owned block; the cells of the NEXT block are in flight (one
-    // TMA bulk copy into the other half of a shared double buffer, mbarrier complete_tx) while this block is
-    // decoded: the scan is a stream of 16 KB copies instead of a load -> wait -> compute chain per CTA.
-    __shared__ __align__(128) unsigned long long buf[2][kPostChunk];
+    // Persistent CTAs over the 2048-cell blocks of the owned block.  A block is staged by ONE TMA bulk copy (16 KB,
+    // mbarrier complete_tx) and moved to registers at once; the copy of the NEXT block is issued right after that,
+    // so it is in flight while this block is decoded: a stream of 16 KB copies instead of a load -> wait -> compute
+    // chain per CTA, with one 16 KB staging buffer (24 KB of shared memory per CTA, 6 CTAs per SM).
+    __shared__ __align__(128) unsigned long long buf[1][kPostChunk];
     __shared__ unsigned long long q[kScanQueue];
     __shared__ __align__(8) unsigned long long bars[2];
     __shared__ uint32_t qn, rows_cta;
@@ -818,7 +819,6 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
     };
     if (threadIdx.x == 0) {
         mbar_init(bar0, 1);
-        mbar_init(bar0 + 8u, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         qn = 0;
         rows_cta = 0;
@@ -827,12 +827,8 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
     __syncthreads();
     uint32_t it = 0;
     for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x, it++) {
-        const uint32_t slot = it & 1u;
-        if (threadIdx.x == 0 && blk + gridDim.x < n_blocks) {
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the other half was read (generic proxy) in the previous trip
-            fetch(blk + gridDim.x, slot ^ 1u);
-        }
-        mbar_wait(bar0 + 8u * slot, (it >> 1) & 1u);
+        const uint32_t slot = 0u;
+        mbar_wait(bar0, it & 1u);
         const unsigned long long wcell0 = (unsigned long long)blk * kPostChunk + wid * (32u * kPostPerThread);
         unsigned long long v[kPostPerThread];
         uint32_t mine = 0;
@@ -856,6 +852,11 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
                 }
                 mine |= (uint32_t)f << k;
             }
+        }
+        __syncthreads();  // every thread holds its cells: the staging buffer is free
+        if (threadIdx.x == 0 && blk + gridDim.x < n_blocks) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy reads before the async-proxy write
+            fetch(blk + gridDim.x, 0u);
         }
         const uint32_t nrows = __reduce_add_sync(KSB_FULL, (uint32_t)__popc(mine));
         if (lane == 0 && nrows) atomicAdd(&rows_cta, nrows);

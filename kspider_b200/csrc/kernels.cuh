@@ -170,7 +170,8 @@ struct GramWinDev {
     uint32_t width;               // samples (multiple of kGramTile)
     uint32_t tiles;               // width / kGramTile
     uint32_t k0;                  // first K-block of the window in the chunk's weight planes
-    uint32_t u0;                  // first bitmap-build unit (K-block x segment of kGramSeg samples) of the window
+    uint32_t extent;              // samples from x0 to the last one a colour of the window touches (<= width; 0 = unknown):
+                                  // rows / columns beyond it are padding of the last tile and hold no update
 };
 constexpr uint32_t kGramSeg = 2048;  // samples per bitmap-build unit: 32 KB of shared memory
 struct GramUnit {                    // one bitmap-build unit of a chunk (plan_gram lists them, heaviest first): a K-block
@@ -201,6 +202,10 @@ struct GramParams {
     uint32_t* counter;            // work counter, zeroed before the launch
 };
 uint32_t gram_cols_per_item(int planes);
+// the variant for chunks of SHORT items (few K-blocks per tile pair): static schedule, double-buffered TMEM
+// accumulators, expansion of item n + 1 before the epilogue of item n; planes 1 or 2, NB = 2 / planes
+uint32_t gram_cols_per_item_pipe(int planes);
+cudaError_t launch_k4_gram_pipe(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
                             const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
