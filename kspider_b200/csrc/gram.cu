@@ -181,30 +181,79 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         if (tid <= kn) sm_rel[tid] = (uint32_t)(sm_off[tid] - o0);
         __syncthreads();
         const uint32_t xbase = gu.xbase;
-        const uint32_t per_warp = ((L + 8u * 32u - 1u) / (8u * 32u)) * 32u;   // multiple of 32
-        const uint32_t wb = (tid >> 5) * per_warp, we = min(L, wb + per_warp);
-        uint32_t k = 0;
-        if (wb < we) {  // first colour of the warp's slice: binary search once
-            uint32_t lo = 0, hi = kn;
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (sm_rel[mid] <= wb) lo = mid; else hi = mid;
+        const uint32_t lane = tid & 31u, wrp = tid >> 5;
+        if constexpr (sizeof(MT) == 4 || sizeof(MT) == 2) {
+            // plain u32 / u16 members: 16-byte loads (4 / 8 members per lane and instruction) over the ALIGNED vectors
+            // that cover the array; elements before its start or past its end are masked
+            constexpr uint32_t VEC = 16 / sizeof(MT);
+            const unsigned long long v_begin = o0 / VEC, v_end = (o0 + L + VEC - 1) / VEC;
+            const uint32_t nvec = (uint32_t)(v_end - v_begin);
+            const uint32_t per_warp = ((nvec + 8u * 32u - 1u) / (8u * 32u)) * 32u;
+            const uint32_t wb = wrp * per_warp, we = min(nvec, wb + per_warp);
+            const uint32_t head = (uint32_t)(o0 - v_begin * VEC);      // elements of the first vector that belong to the previous colours
+            uint32_t k = 0, next = 0;
+            if (wb < we) {  // colour of the first element of the warp's slice: one binary search
+                const uint32_t e_first = wb * VEC > head ? wb * VEC - head : 0u;
+                uint32_t lo = 0, hi = kn;
+                while (hi - lo > 1) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (sm_rel[mid] <= e_first) lo = mid; else hi = mid;
+                }
+                k = lo;
+                next = sm_rel[k + 1];
             }
-            k = lo;
-        }
-        for (uint32_t e0 = wb + (tid & 31u); e0 < we; e0 += 32u * 16u) {
-            uint32_t xs[16];
+            const uint4* vbase = reinterpret_cast<const uint4*>(gram_members) + v_begin;
+            for (uint32_t v0 = wb + lane; v0 < we; v0 += 32u * 4u) {
+                uint4 q[4];
 #pragma unroll
-            for (uint32_t u = 0; u < 16; u++) {
-                const uint32_t e = e0 + 32u * u;
-                xs[u] = e < we ? ldm<MT>(gram_members, o0 + e) - xbase : 0xFFFFFFFFu;  // members outside the segment wrap to >= slen
+                for (uint32_t u = 0; u < 4; u++) {
+                    const uint32_t v = v0 + 32u * u;
+                    q[u] = v < we ? __ldg(vbase + v) : make_uint4(0u, 0u, 0u, 0u);
+                }
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    const uint32_t v = v0 + 32u * u;
+                    if (v >= we) break;
+                    const uint32_t w4[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+#pragma unroll
+                    for (uint32_t t = 0; t < VEC; t++) {
+                        const uint32_t e = v * VEC + t - head;  // wraps (>= L) for the elements in front of the array
+                        if (e >= L) continue;
+                        while (next <= e) { k++; next = sm_rel[k + 1]; }
+                        const uint32_t m = sizeof(MT) == 4 ? w4[t] : ((w4[t >> 1] >> ((t & 1u) * 16u)) & 0xFFFFu);
+                        const uint32_t x = m - xbase;           // members outside the segment wrap to >= slen
+                        if (x < slen) atomicOr(sm + (k >> 5) * kGramSeg + x, 1u << (k & 31u));
+                    }
+                }
             }
+        } else {
+            // packed members (10 / 12 bits): element-wise loads, sixteen in flight per lane
+            const uint32_t per_warp = ((L + 8u * 32u - 1u) / (8u * 32u)) * 32u;   // multiple of 32
+            const uint32_t wb = wrp * per_warp, we = min(L, wb + per_warp);
+            uint32_t k = 0, next = 0;
+            if (wb < we) {
+                uint32_t lo = 0, hi = kn;
+                while (hi - lo > 1) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (sm_rel[mid] <= wb) lo = mid; else hi = mid;
+                }
+                k = lo;
+                next = sm_rel[k + 1];
+            }
+            for (uint32_t e0 = wb + lane; e0 < we; e0 += 32u * 16u) {
+                uint32_t xs[16];
 #pragma unroll
-            for (uint32_t u = 0; u < 16; u++) {
-                const uint32_t e = e0 + 32u * u;
-                if (e >= we) break;
-                while (sm_rel[k + 1] <= e) k++;
-                if (xs[u] < slen) atomicOr(sm + (k >> 5) * kGramSeg + xs[u], 1u << (k & 31u));
+                for (uint32_t u = 0; u < 16; u++) {
+                    const uint32_t e = e0 + 32u * u;
+                    xs[u] = e < we ? ldm<MT>(gram_members, o0 + e) - xbase : 0xFFFFFFFFu;
+                }
+#pragma unroll
+                for (uint32_t u = 0; u < 16; u++) {
+                    const uint32_t e = e0 + 32u * u;
+                    if (e >= we) break;
+                    while (next <= e) { k++; next = sm_rel[k + 1]; }
+                    if (xs[u] < slen) atomicOr(sm + (k >> 5) * kGramSeg + xs[u], 1u << (k & 31u));
+                }
             }
         }
         if (gu.wq_off != 0xFFFFFFFFu && tid < kKB) {
@@ -574,6 +623,10 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
             const uint32_t rsel = lane >> 4, csel = lane & 15u;
             const uint32_t row0 = i0 + 32u * lq;            // first row of this warp's 32-row group
             if (row0 < ext) {
+                // address of the virtual cell (row, 0) of the warp's 32 rows, one per lane: the chunk loop takes
+                // them by shuffle instead of a dependent global load in front of every red
+                const unsigned long long ra_lane = (row0 + lane < win.width) ? gram_row_addr(win.x0 + row0 + lane, G) : 0ull;
+                const uint32_t ra_lo = (uint32_t)ra_lane, ra_hi = (uint32_t)(ra_lane >> 32);
                 for (uint32_t ch = wg; ch < ncol * 8u; ch += 4) {
                     const uint32_t ct = ch >> 3, c16 = ch & 7u;
                     const uint32_t col0 = j0 + ct * kTile + c16 * 16u;
@@ -595,14 +648,13 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
                     }
                     const uint32_t jl = col0 + csel;
                     const uint32_t j = win.x0 + jl;
+                    const bool col_ok = jl < win.width && j < G.n;
 #pragma unroll
                     for (uint32_t y = 0; y < 16; y++) {
-                        const uint32_t il = row0 + 2 * y + rsel;
-                        const uint32_t i = win.x0 + il;
-                        if (il < jl && jl < win.width && j < G.n && acc[y] != 0ull) {
-                            const unsigned long long ra = gram_row_addr(i, G);
-                            if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
-                        }
+                        const uint32_t src = 2 * y + rsel;
+                        const unsigned long long ra = ((unsigned long long)__shfl_sync(0xffffffffu, ra_hi, src) << 32) | __shfl_sync(0xffffffffu, ra_lo, src);
+                        if (row0 + src < jl && col_ok && acc[y] != 0ull && ra != 0ull)
+                            asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
                     }
                 }
             }
