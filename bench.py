@@ -463,27 +463,39 @@ def main_b200(args):
     dev_ms = ev0.elapsed_time(ev1)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    after = timers()
-    phase = {k: (after[k] - before[k]) / args.steps for k in PHASES}
+    # the timed steps replay ONE CUDA graph per step (events inside a graph carry no timestamps), so the per-phase
+    # timers come from two extra legs of the same step enqueued kernel by kernel:
+    #   phases leg   -- K4 beside K1/K2 on its own stream, as in the timed steps;
+    #   roofline leg -- K4 serialised after K1/K2, so that each kernel's timer is that kernel running alone
     per_step_launches = (dev.info.gpu_launches - l_before) / args.steps + (2 if world > 1 else 0)  # + the K7 merge kernels
     labels_step = np.array(last["labels"], copy=True)
     rows_l = torch.tensor([int(last["rows"]), int(last["edges"])], dtype=torch.int64, device=device)
     if world > 1:
         dist.all_reduce(rows_l)
     rows, n_edges = (int(v) for v in rows_l.cpu())
-    # roofline leg: the same step with K4 serialised after K1/K2, so that each kernel's library timer is that
-    # kernel running alone (in the timed steps above K4 runs beside K1/K2 on a 2nd stream)
+    phase = {k: 0.0 for k in PHASES}
     alone = {k: 0.0 for k in PHASES}
-    if not spill:
-        n_alone = 3
+    if spill:
+        after = timers()
+        phase = {k: (after[k] - before[k]) / args.steps for k in PHASES}
+    else:
+        n_leg = 3
+        dev.set_graph(False)
+        step()
+        b0 = timers()
+        for _ in range(n_leg):
+            step()
+        b1 = timers()
+        phase = {k: (b1[k] - b0[k]) / n_leg for k in PHASES}
         dev.set_overlap(False)
         step()
         b0 = timers()
-        for _ in range(n_alone):
+        for _ in range(n_leg):
             step()
         b1 = timers()
-        alone = {k: (b1[k] - b0[k]) / n_alone for k in PHASES}
+        alone = {k: (b1[k] - b0[k]) / n_leg for k in PHASES}
         dev.set_overlap(True)
+        dev.set_graph(True)
     ms = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -676,11 +688,11 @@ def main_b200(args):
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "name": args.workload, "samples": N, "colors": C_,
                        "members": M, "pair_updates": U, "rows": rows, "edges": n_edges, "cutoff": args.cutoff,
-                       "clusters": int(np.unique(labels_step).size), "step": "cluster-only (ksb_device_cluster)" if not spill else "spill: sort-reduce records + K6/K7",
+                       "clusters": int(np.unique(labels_step).size), "step": "cluster-only (ksb_device_cluster), one CUDA graph launch per step" if not spill else "spill: sort-reduce records + K6/K7",
                        "parallelism": f"row-blocks x{world}", "passes": dev.n_passes, "spill": spill,
                        "index_build_s": t_build,
                        "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the owned block of the triangle ({owned_cells * 8 / 1e6:.0f} MB) is cleared every step)"},
-            "phases_ms": phase, "kernels_alone_ms": alone, "host_ms_per_step": host_ms["step"] / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+            "phases_ms": phase, "phases_note": "per-kernel timers of extra legs run kernel by kernel (the timed steps are graph replays)", "kernels_alone_ms": alone, "host_ms_per_step": host_ms["step"] / args.steps, "wall_ms_per_step": wall_ms / args.steps,
             "timer": "torch.cuda.Event pair on the current stream around the K steps (every step ends with a stream synchronisation); phases: library CUDA events on the launching stream",
             "clocks": clocks, "e2e": e2e, "e2e_records": e2e_rec, "check": check_blk, "wall": wall,
             "gpu_launches": int(round(per_step_launches * args.steps)),

@@ -228,6 +228,16 @@ int ksb_postpass(ksb_device* dev, int want_records, ksb_result** inout);
  * reference would write), n_edges = kept edges.  Same labels as ksb_postpass + ksb_cluster. */
 int ksb_device_cluster(ksb_device* dev, int dist_col, double cut_pct, void* stream, uint32_t* labels_out,
                        uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows);
+/* The same step in two halves, for callers that put more work behind it on the same stream before they wait (the
+ * multi-GPU step: label all-gather + merge): _enqueue returns without synchronising -- the step is replayed as ONE
+ * CUDA graph launch (captured at the first call for a given column / threshold / output; KSPIDER_GRAPH=0 or
+ * ksb_device_set_graph(dev, 0) enqueue it kernel by kernel, which also keeps the per-kernel timers alive) --
+ * and _collect waits for it and hands out the labels (if host_labels was set) and the counters.
+ * _collect returns KSB_ERR_BUDGET when the kept-edge list was too short: it has been grown, enqueue again. */
+int ksb_device_cluster_enqueue(ksb_device* dev, int dist_col, double cut_pct, void* stream, uint32_t* d_labels_out,
+                               int host_labels);
+int ksb_device_cluster_collect(ksb_device* dev, uint32_t* labels_out, uint64_t* n_edges, uint64_t* n_rows);
+int ksb_device_set_graph(ksb_device* dev, int on);
 void ksb_device_free(ksb_device* dev);
 
 /* upload + accumulate + postpass in one call (the end-to-end path) */

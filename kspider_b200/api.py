@@ -167,6 +167,7 @@ class Device:
     def __init__(self, handle: C.c_void_p, keepalive=None):
         self._h = handle
         self._keep = keepalive  # e.g. the torch tensor holding an adopted payload
+        self._first_steps_left = 2  # distributed.cluster_step: steps during which the ranks agree on a repeat
 
     @classmethod
     def adopt(cls, descriptor: bytes, d_payload_ptr: int, payload_bytes: int, keepalive=None, **kw) -> "Device":
@@ -243,6 +244,21 @@ class Device:
         check(lib().ksb_device_cluster(self._h, DIST_COL[dist_type], cut, C.c_void_p(stream) if stream else None,
                                        labels.ctypes.data if to_host else None,
                                        C.c_void_p(d_labels_ptr) if d_labels_ptr else None, C.byref(ne), C.byref(nr)))
+        return labels, ne.value, nr.value
+
+    def set_graph(self, on: bool) -> None:
+        """the cluster-only step as one CUDA graph launch (default) or kernel by kernel (keeps the per-kernel timers)"""
+        check(lib().ksb_device_set_graph(self._h, 1 if on else 0))
+
+    def cluster_enqueue(self, dist_type: str, cutoff01: float, stream: int = 0, d_labels_ptr: int = 0, host_labels: bool = False) -> None:
+        check(lib().ksb_device_cluster_enqueue(self._h, DIST_COL[dist_type], float(cutoff01) * 100, C.c_void_p(stream) if stream else None,
+                                               C.c_void_p(d_labels_ptr) if d_labels_ptr else None, 1 if host_labels else 0))
+
+    def cluster_collect(self, n_samples: int = 0, want_labels: bool = False):
+        """(labels or None, kept edges, touched pairs); raises KsbError(KSB_ERR_BUDGET) when the step must be repeated"""
+        labels = np.empty(n_samples, dtype=np.uint32) if want_labels else None
+        ne, nr = C.c_uint64(), C.c_uint64()
+        check(lib().ksb_device_cluster_collect(self._h, labels.ctypes.data if want_labels else None, C.byref(ne), C.byref(nr)))
         return labels, ne.value, nr.value
 
     def close(self) -> None:

@@ -89,6 +89,9 @@ _PROTOS = {
     "ksb_postpass": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]),
     "ksb_device_cluster": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "ksb_device_cluster_enqueue": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_int]),
+    "ksb_device_cluster_collect": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "ksb_device_set_graph": (C.c_int, [C.c_void_p, C.c_int]),
     "ksb_device_free": (None, [C.c_void_p]),
     "ksb_pairwise": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.POINTER(C.c_void_p)]),
     "ksb_pairwise_cluster": (C.c_int, [C.c_void_p, C.POINTER(Opts), C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64),

@@ -105,6 +105,14 @@ struct ksb_device {
     uint64_t edge_cap = 0;
     uint8_t* h_stage = nullptr;                    // pinned: labels[N] then 2 x u64 counters
     uint64_t h_stage_bytes = 0;
+    // the step as a CUDA graph: captured once per (column, threshold, outputs), replayed by one launch
+    struct graph_key { int dist_col; uint32_t cstar_bits; uint32_t* d_labels_out; bool host_labels, overlap; uint64_t edge_cap; void* d_edges; };
+    bool use_graph = true;                         // KSPIDER_GRAPH=0 / ksb_device_set_graph(dev, 0): enqueue every step kernel by kernel
+    cudaGraphExec_t cl_graph = nullptr;
+    graph_key cl_key{};
+    uint64_t cl_graph_launches = 0;
+    cudaStream_t cl_stream = nullptr;              // stream of the step enqueued last
+    bool cl_host_labels = false, cl_was_graph = false;
 };
 
 struct ksb_segment {
@@ -302,6 +310,7 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
     if (!d->stream2) KSB_CUDA(pool_stream(d->device, &d->stream2));
     for (auto& e : d->ev) KSB_CUDA(pool_event(d->device, &e));
     { const char* ov = std::getenv("KSPIDER_OVERLAP"); d->overlap = !(ov && ov[0] == '0'); }
+    { const char* gv = std::getenv("KSPIDER_GRAPH"); d->use_graph = !(gv && gv[0] == '0'); }
     uint64_t budget = opts ? opts->dense_budget_bytes : 0;
     if (budget == 0) {
         size_t fr = 0, tot = 0;
@@ -421,6 +430,7 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_edges) cudaFreeAsync(d->d_edges, fs);
     if (fs) cudaStreamSynchronize(fs);
     if (d->h_stage) pinned_release(d->h_stage, d->h_stage_bytes);
+    if (d->cl_graph) cudaGraphExecDestroy(d->cl_graph);
     for (auto& e : d->ev) unpool_event(d->device, e);
     if (d->stream) { cudaStreamSynchronize(d->stream); unpool_stream(d->device, d->stream); }
     if (d->stream2) { cudaStreamSynchronize(d->stream2); unpool_stream(d->device, d->stream2); }
@@ -1298,20 +1308,11 @@ int ksb_device_get_info(const ksb_device* d, ksb_result_info* info);
 // labels (and the two counters) to the host.  No records are built.  The edge list has a capacity (an eighth of
 // the owned cells at first); when a step keeps more edges than fit, the list is grown to the exact need and the
 // step is repeated -- the only case with a second synchronisation.
-int ksb_device_cluster(ksb_device* d, int dist_col, double cut_pct, void* stream_v, uint32_t* labels_out,
-                       uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows) {
-    if (!d) { set_error("ksb_device_cluster: null device"); return KSB_ERR_ARG; }
-    if (d->spill) { set_error("ksb_device_cluster: this device runs the spill path (ksb_device_run_spill + ksb_cluster)"); return KSB_ERR_ARG; }
-    if (dist_col < 3 || dist_col > 5) { set_error("ksb_device_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
-    KSB_CUDA(cudaSetDevice(d->device));
-    cudaStream_t st = stream_v ? static_cast<cudaStream_t>(stream_v) : d->stream;
+// The enqueued work of a step is captured ONCE into a CUDA graph (both streams of the accumulation, the memsets,
+// every kernel, the label / counter copies) and replayed by one cudaGraphLaunch per step: at 8 GPUs the kernels of
+// a step are ~20 us each and ~14 launches + ~20 event records of host API time would otherwise BE the step.
+static int cluster_prepare(ksb_device* d, cudaStream_t st) {
     const uint32_t N = (uint32_t)d->desc.n_samples;
-    if (n_edges) *n_edges = 0;
-    if (n_rows) *n_rows = 0;
-    if (N == 0) return KSB_OK;
-    float cstar = ksb_threshold_float_pct(cut_pct);
-    if (cstar != cstar) cstar = INFINITY;
-    const LaunchCfg lc{d->sms, st};
     if (!d->d_parent) {
         KSB_CUDA(cudaMallocAsync(&d->d_parent, 4ull * N, st));
         KSB_CUDA(cudaMallocAsync(&d->d_cl_counters, 32, st));
@@ -1321,62 +1322,152 @@ int ksb_device_cluster(ksb_device* d, int dist_col, double cut_pct, void* stream
         d->h_stage = static_cast<uint8_t*>(hp);
         d->h_stage_bytes = got;
     }
+    if (!d->d_edges) {
+        if (d->edge_cap == 0) {
+            const char* ec = std::getenv("KSPIDER_EDGE_CAP");  // test knob: a short list forces the grow-and-repeat path
+            d->edge_cap = (ec && std::atoll(ec) > 0) ? (uint64_t)std::atoll(ec) : std::max<uint64_t>(1ull << 16, d->owned_cells / 8);
+        }
+        KSB_CUDA(cudaMallocAsync(&d->d_edges, 8 * d->edge_cap, st));
+    }
+    if (d->desc.n_gram_colors)
+        for (uint32_t p = 0; p < d->passes.size(); p++)
+            if (d->passes[p].cells) { const int rc = plan_gram(d, p); if (rc) return rc; }  // allocates and copies: never inside a capture
+    return KSB_OK;
+}
+
+static int cluster_body(ksb_device* d, int dist_col, float cstar, cudaStream_t st, uint32_t* d_labels_out, bool host_labels) {
+    const uint32_t N = (uint32_t)d->desc.n_samples;
+    const LaunchCfg lc{d->sms, st};
     const uint8_t* P = d->d_payload;
     uint32_t* block_rows = reinterpret_cast<uint32_t*>(d->d_block_counts + 2 * d->post_blocks_alloc);
-    for (int attempt = 0; attempt < 2; attempt++) {
-        if (!d->d_edges) {
-            if (d->edge_cap == 0) {
-                const char* ec = std::getenv("KSPIDER_EDGE_CAP");  // test knob: a short list forces the grow-and-repeat path
-                d->edge_cap = (ec && std::atoll(ec) > 0) ? (uint64_t)std::atoll(ec) : std::max<uint64_t>(1ull << 16, d->owned_cells / 8);
-            }
-            KSB_CUDA(cudaMallocAsync(&d->d_edges, 8 * d->edge_cap, st));
-        }
-        KSB_CUDA(cudaMemsetAsync(d->d_cl_counters, 0, 32, st));
-        KSB_CUDA(launch_k7_init(d->d_parent, N, lc));
-        d->launches++;
-        for (uint32_t p = 0; p < d->passes.size(); p++) {
-            d->cur_pass = p;
-            const int rc = ksb_accumulate(d, st, 0);
-            if (rc) return rc;
-            const ksb_pass& ps = d->passes[p];
-            if (ps.cells == 0) continue;
-            const TriGeom g = geom_of(d, ps);
-            if (d->block_rows_pass != (int)p) {
-                KSB_CUDA(launch_k5_block_rows(g, block_rows, lc));
-                d->block_rows_pass = (int)p;
-                d->launches++;
-            }
-            KSB_CUDA(cudaEventRecord(d->ev[5], st));
-            KSB_CUDA(launch_k56_scan(g, d->d_touched, block_rows, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals), dist_col, cstar,
-                                     d->d_edges, d->edge_cap, d->d_cl_counters, lc));
-            KSB_CUDA(cudaEventRecord(d->ev[6], st));
+    KSB_CUDA(cudaMemsetAsync(d->d_cl_counters, 0, 32, st));
+    KSB_CUDA(launch_k7_init(d->d_parent, N, lc));
+    d->launches++;
+    for (uint32_t p = 0; p < d->passes.size(); p++) {
+        d->cur_pass = p;
+        const int rc = ksb_accumulate(d, st, 0);
+        if (rc) return rc;
+        const ksb_pass& ps = d->passes[p];
+        if (ps.cells == 0) continue;
+        const TriGeom g = geom_of(d, ps);
+        if (d->block_rows_pass != (int)p || d->passes.size() > 1) {
+            KSB_CUDA(launch_k5_block_rows(g, block_rows, lc));
+            d->block_rows_pass = (int)p;
             d->launches++;
         }
-        KSB_CUDA(launch_k6_edges(d->d_edges, d->edge_cap, d->d_cl_counters, d->d_parent, d->edge_cap, lc));
-        KSB_CUDA(launch_k7_compress(d->d_parent, N, lc));
-        KSB_CUDA(cudaEventRecord(d->ev[7], st));
-        d->launches += 3;
-        if (d_labels_out) KSB_CUDA(cudaMemcpyAsync(d_labels_out, d->d_parent, 4ull * N, cudaMemcpyDeviceToDevice, st));
-        if (labels_out) KSB_CUDA(cudaMemcpyAsync(d->h_stage, d->d_parent, 4ull * N, cudaMemcpyDeviceToHost, st));
-        KSB_CUDA(cudaMemcpyAsync(d->h_stage + 4ull * N, d->d_cl_counters, 16, cudaMemcpyDeviceToHost, st));
-        KSB_CUDA(cudaStreamSynchronize(st));
-        unsigned long long cnt[2];
-        std::memcpy(cnt, d->h_stage + 4ull * N, 16);
-        if (cnt[1] > d->edge_cap) {  // the list was too short: now the need is known exactly
-            if (attempt == 1) { set_error("ksb_device_cluster: edge list overflow after growing"); return KSB_ERR_CUDA; }
-            KSB_CUDA(cudaFreeAsync(d->d_edges, st));
-            d->d_edges = nullptr;
-            d->edge_cap = cnt[1] + cnt[1] / 16 + 1024;
-            continue;
+        KSB_CUDA(cudaEventRecord(d->ev[5], st));
+        KSB_CUDA(launch_k56_scan(g, d->d_touched, block_rows, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals), dist_col, cstar,
+                                 d->d_edges, d->edge_cap, d->d_cl_counters, lc));
+        KSB_CUDA(cudaEventRecord(d->ev[6], st));
+        d->launches++;
+    }
+    KSB_CUDA(launch_k6_edges(d->d_edges, d->edge_cap, d->d_cl_counters, d->d_parent, d->edge_cap, lc));
+    KSB_CUDA(launch_k7_compress(d->d_parent, N, lc));
+    KSB_CUDA(cudaEventRecord(d->ev[7], st));
+    d->launches += 3;
+    if (d_labels_out) KSB_CUDA(cudaMemcpyAsync(d_labels_out, d->d_parent, 4ull * N, cudaMemcpyDeviceToDevice, st));
+    if (host_labels) KSB_CUDA(cudaMemcpyAsync(d->h_stage, d->d_parent, 4ull * N, cudaMemcpyDeviceToHost, st));
+    KSB_CUDA(cudaMemcpyAsync(d->h_stage + 4ull * N, d->d_cl_counters, 16, cudaMemcpyDeviceToHost, st));
+    return KSB_OK;
+}
+
+int ksb_device_cluster_enqueue(ksb_device* d, int dist_col, double cut_pct, void* stream_v, uint32_t* d_labels_out, int host_labels) {
+    if (!d) { set_error("ksb_device_cluster: null device"); return KSB_ERR_ARG; }
+    if (d->spill) { set_error("ksb_device_cluster: this device runs the spill path (ksb_device_run_spill + ksb_cluster)"); return KSB_ERR_ARG; }
+    if (dist_col < 3 || dist_col > 5) { set_error("ksb_device_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(d->device));
+    cudaStream_t st = stream_v ? static_cast<cudaStream_t>(stream_v) : d->stream;
+    if (d->desc.n_samples == 0) return KSB_OK;
+    float cstar = ksb_threshold_float_pct(cut_pct);
+    if (cstar != cstar) cstar = INFINITY;
+    int rc = cluster_prepare(d, st);
+    if (rc) return rc;
+    d->cl_stream = st;
+    d->cl_host_labels = host_labels != 0;
+    d->cl_was_graph = false;
+    const bool can_graph = d->use_graph && !d->copy_pending;
+    if (!can_graph) return cluster_body(d, dist_col, cstar, st, d_labels_out, host_labels != 0);
+    uint32_t cbits;
+    std::memcpy(&cbits, &cstar, 4);
+    const ksb_device::graph_key key{dist_col, cbits, d_labels_out, host_labels != 0, d->overlap, d->edge_cap, d->d_edges};
+    if (!d->cl_graph || std::memcmp(&key, &d->cl_key, sizeof key) != 0) {
+        if (d->cl_graph) { cudaGraphExecDestroy(d->cl_graph); d->cl_graph = nullptr; }
+        const uint64_t launches_before = d->launches;
+        KSB_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        rc = cluster_body(d, dist_col, cstar, st, d_labels_out, host_labels != 0);
+        cudaGraph_t graph = nullptr;
+        cudaError_t e = cudaStreamEndCapture(st, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); (void)cudaGetLastError(); return rc; }
+        if (e != cudaSuccess || !graph) {
+            // capture refused (an API call inside the step is not capturable on this driver): run the step eagerly from now on
+            (void)cudaGetLastError();
+            if (graph) cudaGraphDestroy(graph);
+            d->use_graph = false;
+            d->launches = launches_before;
+            return cluster_body(d, dist_col, cstar, st, d_labels_out, host_labels != 0);
         }
+        e = cudaGraphInstantiate(&d->cl_graph, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) { (void)cudaGetLastError(); d->cl_graph = nullptr; d->use_graph = false; d->launches = launches_before; return cluster_body(d, dist_col, cstar, st, d_labels_out, host_labels != 0); }
+        d->cl_key = key;
+        d->cl_graph_launches = d->launches - launches_before;
+        d->launches = launches_before;
+    }
+    KSB_CUDA(cudaGraphLaunch(d->cl_graph, st));
+    d->launches += d->cl_graph_launches;
+    d->cl_was_graph = true;
+    return KSB_OK;
+}
+
+// Waits for the step enqueued last and hands out its result.  KSB_ERR_BUDGET: the kept-edge list was too short; it
+// has been grown to the exact need -- enqueue the step again.
+int ksb_device_cluster_collect(ksb_device* d, uint32_t* labels_out, uint64_t* n_edges, uint64_t* n_rows) {
+    if (!d) { set_error("ksb_device_cluster_collect: null device"); return KSB_ERR_ARG; }
+    const uint32_t N = (uint32_t)d->desc.n_samples;
+    if (n_edges) *n_edges = 0;
+    if (n_rows) *n_rows = 0;
+    if (N == 0) return KSB_OK;
+    if (!d->cl_stream || !d->h_stage) { set_error("ksb_device_cluster_collect: no step was enqueued"); return KSB_ERR_ARG; }
+    KSB_CUDA(cudaSetDevice(d->device));
+    KSB_CUDA(cudaStreamSynchronize(d->cl_stream));
+    unsigned long long cnt[2];
+    std::memcpy(cnt, d->h_stage + 4ull * N, 16);
+    if (cnt[1] > d->edge_cap) {  // the list was too short: now the need is known exactly
+        KSB_CUDA(cudaFreeAsync(d->d_edges, d->cl_stream));
+        d->d_edges = nullptr;
+        d->edge_cap = cnt[1] + cnt[1] / 16 + 1024;
+        set_error("ksb_device_cluster: the kept-edge list was too short (%llu edges); it has been grown, repeat the step", cnt[1]);
+        return KSB_ERR_BUDGET;
+    }
+    if (!d->cl_was_graph) {  // events recorded inside a graph carry no timestamps
         harvest_accumulate_timers(d);  // of the last pass
         d->t.post_ms += ev_ms(d->ev[5], d->ev[6]);
         d->t.cluster_ms += ev_ms(d->ev[6], d->ev[7]);
-        if (labels_out) std::memcpy(labels_out, d->h_stage, 4ull * N);
-        if (n_rows) *n_rows = cnt[0];
-        if (n_edges) *n_edges = cnt[1];
-        return KSB_OK;
     }
+    if (labels_out) {
+        if (!d->cl_host_labels) { set_error("ksb_device_cluster_collect: the step was enqueued without host labels"); return KSB_ERR_ARG; }
+        std::memcpy(labels_out, d->h_stage, 4ull * N);
+    }
+    if (n_rows) *n_rows = cnt[0];
+    if (n_edges) *n_edges = cnt[1];
+    return KSB_OK;
+}
+
+int ksb_device_cluster(ksb_device* d, int dist_col, double cut_pct, void* stream_v, uint32_t* labels_out,
+                       uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows) {
+    for (int attempt = 0; attempt < 2; attempt++) {
+        int rc = ksb_device_cluster_enqueue(d, dist_col, cut_pct, stream_v, d_labels_out, labels_out != nullptr);
+        if (rc) return rc;
+        rc = ksb_device_cluster_collect(d, labels_out, n_edges, n_rows);
+        if (rc != KSB_ERR_BUDGET) return rc;
+    }
+    set_error("ksb_device_cluster: edge list overflow after growing");
+    return KSB_ERR_CUDA;
+}
+
+int ksb_device_set_graph(ksb_device* d, int on) {
+    if (!d) { set_error("ksb_device_set_graph: null device"); return KSB_ERR_ARG; }
+    d->use_graph = on != 0;
     return KSB_OK;
 }
 
@@ -1641,6 +1732,7 @@ int ksb_ani_column(const ksb_result* r, int ksize, double* ani_out, uint64_t* n_
 namespace ksb {
 // union(v, other[v]) for every v: merges the partition `other` into `parent`
 cudaError_t launch_k7_merge(uint32_t* parent, const uint32_t* other, uint32_t n, const LaunchCfg& lc);
+cudaError_t launch_k7_merge_all(uint32_t* parent, const uint32_t* others, uint32_t n, uint32_t n_other, const LaunchCfg& lc);
 }  // namespace ksb
 
 extern "C" {
@@ -1656,7 +1748,7 @@ int ksb_cluster_merge_device(uint64_t n, int world, const uint32_t* d_labels_all
     cudaStream_t st = static_cast<cudaStream_t>(stream_v);
     const LaunchCfg lc{sms, st};
     KSB_CUDA(cudaMemcpyAsync(d_out, d_labels_all, 4 * n, cudaMemcpyDeviceToDevice, st));
-    for (int w = 1; w < world; w++) KSB_CUDA(launch_k7_merge(d_out, d_labels_all + (uint64_t)w * n, (uint32_t)n, lc));
+    KSB_CUDA(launch_k7_merge_all(d_out, d_labels_all + n, (uint32_t)n, (uint32_t)(world - 1), lc));  // every other rank's labels, one launch
     KSB_CUDA(launch_k7_compress(d_out, (uint32_t)n, lc));
     return KSB_OK;
 }

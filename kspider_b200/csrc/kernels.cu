@@ -1263,6 +1263,20 @@ __global__ void __launch_bounds__(256) k7_merge(uint32_t* parent, const uint32_t
         if (o != v) uf_union(parent, v, o);
     }
 }
+// all the other ranks' label arrays in one launch: others = [n_other][n]
+__global__ void __launch_bounds__(256) k7_merge_all(uint32_t* parent, const uint32_t* __restrict__ others, uint32_t n, uint32_t n_other) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    for (uint32_t w = 0; w < n_other; w++) {
+        const uint32_t o = __ldg(others + (unsigned long long)w * n + v);
+        if (o != v) uf_union(parent, v, o);
+    }
+}
+cudaError_t launch_k7_merge_all(uint32_t* parent, const uint32_t* others, uint32_t n, uint32_t n_other, const LaunchCfg& lc) {
+    if (n == 0 || n_other == 0) return cudaSuccess;
+    k7_merge_all<<<(n + 255) / 256, 256, 0, lc.stream>>>(parent, others, n, n_other);
+    return cudaGetLastError();
+}
 cudaError_t launch_k7_merge(uint32_t* parent, const uint32_t* other, uint32_t n, const LaunchCfg& lc) {
     if (n == 0) return cudaSuccess;
     k7_merge<<<(n + 255) / 256, 256, 0, lc.stream>>>(parent, other, n);

@@ -178,44 +178,37 @@ def pairwise_cluster_step(shard: Index, n_samples: int, dist_type: str, cutoff01
 
 
 def cluster_step(dev: Device, n_samples: int, dist_type: str, cutoff01: float, device: torch.device):
-    """The multi-GPU cluster-only step: ksb_device_cluster on this rank's row block (accumulate + fused scan +
-    unions, labels left on the GPU), all-gather of every rank's labels over NVLink, K7 merge kernel, one pinned
-    D2H.  Returns (global labels as a numpy view of a pinned buffer the next call overwrites, this rank's kept
-    edges, this rank's touched pairs)."""
+    """The multi-GPU cluster-only step, ONE host synchronisation: ksb_device_cluster_enqueue on this rank's row block
+    (one CUDA graph launch: accumulate + fused scan + unions, labels left on the GPU), all-gather of every rank's
+    labels over NVLink, K7 merge kernel, one pinned D2H, stream synchronise.  Returns (global labels as a numpy view
+    of a pinned buffer the next call overwrites, this rank's kept edges, this rank's touched pairs)."""
+    from .capi import KSB_ERR_BUDGET, KsbError
     world = dist.get_world_size()
-    key = (n_samples, world, device.index)
-    buf = _LABEL_BUFFERS.get(key)
-    if buf is None:
-        buf = (torch.empty(n_samples, dtype=torch.int32, device=device),
-               torch.empty(world * n_samples, dtype=torch.int32, device=device),
-               torch.empty(n_samples, dtype=torch.int32, device=device),
-               torch.empty(n_samples, dtype=torch.int32, pin_memory=True))
-        _LABEL_BUFFERS.clear()
-        _LABEL_BUFFERS[key] = buf
-    mine, allv, out, host = buf
+    mine, allv, out, host = _label_buffers(n_samples, world, device)
     stream = torch.cuda.current_stream(device).cuda_stream
-    _, n_edges, n_rows = dev.cluster(n_samples, dist_type, cutoff01, stream=stream, d_labels_ptr=mine.data_ptr(), to_host=False)
-    dist.all_gather_into_tensor(allv, mine)
-    check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
-                                         C.c_void_p(stream)))
-    host.copy_(out, non_blocking=True)
-    torch.cuda.current_stream(device).synchronize()
-    return host.numpy().view(np.uint32), n_edges, n_rows
-
-
-def merge_labels(labels: np.ndarray, device: torch.device) -> np.ndarray:
-    """all-gather of every rank's label array + K7 merge kernel (on CUDA); on a CPU `device` the
-    gathered arrays are returned unmerged-by-kernel, merged with a host union-find used only by the
-    gloo tests."""
-    world = dist.get_world_size()
-    mine = torch.from_numpy(labels.astype(np.int32, copy=False).view(np.int32)).to(device)
-    allv = torch.empty(world * mine.numel(), dtype=torch.int32, device=device)
-    dist.all_gather_into_tensor(allv, mine) if device.type == "cuda" else \
-        dist.all_gather(list(allv.view(world, -1).unbind(0)), mine)
-    if device.type == "cuda":
-        out = torch.empty_like(mine)
-        stream = torch.cuda.current_stream(device).cuda_stream
-        check(lib().ksb_cluster_merge_device(mine.numel(), world, C.c_void_p(allv.data_ptr()),
-                                             C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
-        return out.cpu().numpy().view(np.uint32)
-    return allv.view(world, -1).numpy().view(np.uint32)
+    while True:
+        dev.cluster_enqueue(dist_type, cutoff01, stream=stream, d_labels_ptr=mine.data_ptr())
+        dist.all_gather_into_tensor(allv, mine)
+        check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
+                                             C.c_void_p(stream)))
+        host.copy_(out, non_blocking=True)
+        torch.cuda.current_stream(device).synchronize()
+        # every rank must take the same branch (the all-gather is collective): a rank whose edge list was too short
+        # grows it inside collect; all ranks then repeat the step
+        again = torch.zeros(1, dtype=torch.int32, device=device)
+        try:
+            _, n_edges, n_rows = dev.cluster_collect()
+        except KsbError as e:
+            if e.code != KSB_ERR_BUDGET:
+                raise
+            again += 1
+            n_edges = n_rows = 0
+        if dev._first_steps_left > 0:   # overflow can only happen while the list is still at its initial size
+            dist.all_reduce(again)
+            dev._first_steps_left -= 1
+            if int(again.item()):
+                dev._first_steps_left = 2
+                continue
+        elif int(again.item()):
+            raise RuntimeError("kept-edge list overflow after the warm-up steps (the cut-off changed?): call Device.cluster once first")
+        return host.numpy().view(np.uint32), n_edges, n_rows

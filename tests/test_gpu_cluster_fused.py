@@ -94,3 +94,23 @@ def test_spill_device_refuses(ksb):
     dev = ksb.Index.from_csr(**csr).upload(spill="always", dense_budget_bytes=50_000_000)
     with pytest.raises(KsbError):
         dev.cluster(100, "max_cont", 0.0)
+
+
+def test_graph_replay_equals_kernel_by_kernel(ksb):
+    """the step as one CUDA graph launch (captured once per column / threshold, replayed afterwards) against the
+    same step enqueued kernel by kernel; a change of threshold re-captures"""
+    csr = spread_totals(random_csr(seed=48, n_samples=400, n_colors=1500, s_lo=2, s_hi=30, big=(70, 150, 390)), 48)
+    idx = ksb.Index.from_csr(**csr)
+    dev = idx.upload()
+    for cutoff in (0.1, 0.4, 0.1):
+        dev.set_graph(False)
+        want = dev.cluster(400, "max_cont", cutoff)
+        dev.set_graph(True)
+        launches0 = dev.info.gpu_launches
+        for rep in range(3):   # capture, then two replays
+            got = dev.cluster(400, "max_cont", cutoff)
+            assert np.array_equal(got[0], want[0]) and got[1:] == want[1:], (cutoff, rep)
+        assert dev.info.gpu_launches - launches0 >= 3 * 5   # replays count their kernels
+    lab, ne, nr = dev.cluster(400, "min_cont", 0.1)
+    ref, ref_ne, ref_rows = oracle_labels(csr, idx.sample_ids, "min_cont", 0.1)
+    assert (ne, nr) == (ref_ne, ref_rows) and np.array_equal(lab, ref)
