@@ -459,6 +459,7 @@ def main_b200(args):
     ev1.record()
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - w0) * 1e3
+    host_step_ms = host_ms["step"] / args.steps
     sampler.mark()
     dev_ms = ev0.elapsed_time(ev1)
     barrier()
@@ -692,7 +693,7 @@ def main_b200(args):
                        "parallelism": f"row-blocks x{world}", "passes": dev.n_passes, "spill": spill,
                        "index_build_s": t_build,
                        "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the owned block of the triangle ({owned_cells * 8 / 1e6:.0f} MB) is cleared every step)"},
-            "phases_ms": phase, "phases_note": "per-kernel timers of extra legs run kernel by kernel (the timed steps are graph replays)", "kernels_alone_ms": alone, "host_ms_per_step": host_ms["step"] / args.steps, "wall_ms_per_step": wall_ms / args.steps,
+            "phases_ms": phase, "phases_note": "per-kernel timers of extra legs run kernel by kernel (the timed steps are graph replays)", "kernels_alone_ms": alone, "host_ms_per_step": host_step_ms, "wall_ms_per_step": wall_ms / args.steps,
             "timer": "torch.cuda.Event pair on the current stream around the K steps (every step ends with a stream synchronisation); phases: library CUDA events on the launching stream",
             "clocks": clocks, "e2e": e2e, "e2e_records": e2e_rec, "check": check_blk, "wall": wall,
             "gpu_launches": int(round(per_step_launches * args.steps)),
