@@ -145,6 +145,7 @@ def cluster_merged(result, n_samples: int, dist_type: str, cutoff01: float, devi
 
 
 _LABEL_BUFFERS = {}
+_STEP_STREAMS = {}
 
 
 def _label_buffers(n_samples: int, world: int, device: torch.device):
@@ -185,30 +186,37 @@ def cluster_step(dev: Device, n_samples: int, dist_type: str, cutoff01: float, d
     from .capi import KSB_ERR_BUDGET, KsbError
     world = dist.get_world_size()
     mine, allv, out, host = _label_buffers(n_samples, world, device)
-    stream = torch.cuda.current_stream(device).cuda_stream
+    # Everything of the step is ordered on ONE non-default stream: torch's default stream has handle 0, which the C-ABI
+    # reads as "the library's own stream" -- the all-gather would then not wait for the labels.
+    side = _STEP_STREAMS.get(device.index)
+    if side is None:
+        side = _STEP_STREAMS[device.index] = torch.cuda.Stream(device)
+    stream = side.cuda_stream
     while True:
-        dev.cluster_enqueue(dist_type, cutoff01, stream=stream, d_labels_ptr=mine.data_ptr())
-        dist.all_gather_into_tensor(allv, mine)
-        check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
-                                             C.c_void_p(stream)))
-        host.copy_(out, non_blocking=True)
-        torch.cuda.current_stream(device).synchronize()
+        with torch.cuda.stream(side):
+            dev.cluster_enqueue(dist_type, cutoff01, stream=stream, d_labels_ptr=mine.data_ptr())
+            dist.all_gather_into_tensor(allv, mine)
+            check(lib().ksb_cluster_merge_device(n_samples, world, C.c_void_p(allv.data_ptr()), C.c_void_p(out.data_ptr()),
+                                                 C.c_void_p(stream)))
+            host.copy_(out, non_blocking=True)
+        side.synchronize()
         # every rank must take the same branch (the all-gather is collective): a rank whose edge list was too short
         # grows it inside collect; all ranks then repeat the step
-        again = torch.zeros(1, dtype=torch.int32, device=device)
+        short = False
         try:
             _, n_edges, n_rows = dev.cluster_collect()
         except KsbError as e:
             if e.code != KSB_ERR_BUDGET:
                 raise
-            again += 1
+            short = True
             n_edges = n_rows = 0
         if dev._first_steps_left > 0:   # overflow can only happen while the list is still at its initial size
+            again = torch.tensor([1 if short else 0], dtype=torch.int32, device=device)
             dist.all_reduce(again)
             dev._first_steps_left -= 1
             if int(again.item()):
                 dev._first_steps_left = 2
                 continue
-        elif int(again.item()):
+        elif short:
             raise RuntimeError("kept-edge list overflow after the warm-up steps (the cut-off changed?): call Device.cluster once first")
         return host.numpy().view(np.uint32), n_edges, n_rows
