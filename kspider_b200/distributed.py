@@ -220,3 +220,21 @@ def cluster_step(dev: Device, n_samples: int, dist_type: str, cutoff01: float, d
         elif short:
             raise RuntimeError("kept-edge list overflow after the warm-up steps (the cut-off changed?): call Device.cluster once first")
         return host.numpy().view(np.uint32), n_edges, n_rows
+
+
+def merge_labels(labels: np.ndarray, device: torch.device) -> np.ndarray:
+    """all-gather of every rank's label array + K7 merge kernel (on CUDA); on a CPU `device` the
+    gathered arrays are returned unmerged-by-kernel, merged with a host union-find used only by the
+    gloo tests."""
+    world = dist.get_world_size()
+    mine = torch.from_numpy(labels.astype(np.int32, copy=False).view(np.int32)).to(device)
+    allv = torch.empty(world * mine.numel(), dtype=torch.int32, device=device)
+    dist.all_gather_into_tensor(allv, mine) if device.type == "cuda" else \
+        dist.all_gather(list(allv.view(world, -1).unbind(0)), mine)
+    if device.type == "cuda":
+        out = torch.empty_like(mine)
+        stream = torch.cuda.current_stream(device).cuda_stream
+        check(lib().ksb_cluster_merge_device(mine.numel(), world, C.c_void_p(allv.data_ptr()),
+                                             C.c_void_p(out.data_ptr()), C.c_void_p(stream)))
+        return out.cpu().numpy().view(np.uint32)
+    return allv.view(world, -1).numpy().view(np.uint32)
