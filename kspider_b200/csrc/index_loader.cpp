@@ -12,6 +12,7 @@
 // (ascending(), Combo enumeration order) is folded in here: members are sorted once.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -105,6 +106,8 @@ public:
         }
         return false;
     }
+    bool dense() const { return dense_; }
+    void prefetch(uint32_t k) const { if (dense_ && k < val_.size()) { __builtin_prefetch(&val_[k]); __builtin_prefetch(&used_[k]); } }
 private:
     static uint64_t mix(uint64_t x) { x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; return x; }
     uint64_t slot(uint32_t k) const {
@@ -142,7 +145,20 @@ struct RawIndex {
     uint64_t n_colors_file = 0;
 };
 
+// KSPIDER_LOAD_TIMERS=1: phases of the loader on stderr
+struct LoadTimer {
+    bool on = std::getenv("KSPIDER_LOAD_TIMERS") && std::atoi(std::getenv("KSPIDER_LOAD_TIMERS")) != 0;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "ksb_load %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 static int build_index(RawIndex& raw, int threads, ksb_index** out) {
+    LoadTimer bt;
     std::unique_ptr<ksb_index> ix(new ksb_index());
     IndexDesc& d = ix->desc;
     std::memset(&d, 0, sizeof d);
@@ -169,7 +185,9 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         std::vector<uint8_t> present((uint64_t)max_id + 1, 0);
         for (uint32_t v : raw.total_ids) present[v] = 1;
         parallel_chunks(raw.members.size(), threads, [&](int, uint64_t b, uint64_t e) {
-            for (uint64_t i = b; i < e; i++) present[raw.members[i]] = 1;  // benign same-value race
+            // benign same-value race; read before write: with few samples the flags share a handful of cache lines, and
+            // unconditional stores from every thread made this loop the slowest phase of the loader
+            for (uint64_t i = b; i < e; i++) { const uint32_t m = raw.members[i]; if (!present[m]) present[m] = 1; }
         });
         remap.assign((uint64_t)max_id + 1, 0);
         for (uint64_t v = 0; v <= max_id; v++)
@@ -189,6 +207,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
     const int T = std::max(1, threads);
 
+    bt.lap("  compaction");
     // ---- routing of the int8 Gram path (K4), per sample window.  A colour whose members all lie in a
     // window of `width` samples costs ~width^2 * planes tensor MACs there against s^2/2 reds on K1/K2,
     // so it is a candidate when s >= kGramCrossover * width * sqrt(planes) (and >= kGramMinSize) for
@@ -320,6 +339,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.gram_min_size = gram_min;
     d.gram_planes = gram_planes;
 
+    bt.lap("  gram routing");
     // ---- locality order: when the accumulator cannot be L2-resident, colours are placed in the blob
     // by ascending first member (= the triangle row of their first updates), so the colours the SMs
     // work on at the same time hit the same neighbourhood of rows and the reds stay in L2 instead of
@@ -341,6 +361,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     }
     auto ord = [&](uint64_t ci) -> uint64_t { return order.empty() ? ci : order[ci]; };
 
+    bt.lap("  locality order");
     // ---- classify colours; per-chunk class counts so the fill can run in parallel, in blob order
     const uint32_t K_MID = kSmallMax + 1, K_ZERO = kSmallMax + 2, K_GRAM = kSmallMax + 3, K_N = kSmallMax + 4;
     std::vector<std::vector<uint64_t>> cnt(T, std::vector<uint64_t>(K_N, 0));      // colours per class
@@ -400,6 +421,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.n_gram_members = mtot[K_GRAM];
     d.n_colors = d.n_small_colors + d.n_mid_colors + d.n_zero_colors + d.n_gram_colors;
 
+    bt.lap("  classify");
     // ---- member width: u16 when every compact id fits (halves the blob = the H2D / broadcast time);
     // KSPIDER_MEMBER_BITS=32 forces u32 (tests)
     {
@@ -428,6 +450,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     const uint64_t PB = d.packed_bits, WB = d.weight_bits / 8;
     auto packed_bytes = [&](uint64_t n) { return (PB * n + 7) / 8 + 8; };
 
+    bt.lap("  member width");
     // ---- payload layout
     uint64_t p = 0;
     auto section = [&](uint64_t bytes) { const uint64_t o = p; p = align256(p + bytes); return o; };
@@ -519,6 +542,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     // groupID_to_kmerCount[id]: a map, so one value per id; missing -> 0 (operator[] default)
     for (size_t i = 0; i < raw.total_ids.size(); i++) totals[compact(raw.total_ids[i])] = raw.total_vals[i];
 
+    bt.lap("  layout + alloc + memset");
     // ---- fill (parallel, deterministic placement = input order within each class)
     std::vector<std::vector<uint64_t>> t_rows(T), t_rowsum(T);
     std::vector<std::vector<uint32_t>> t_lo(T), t_hi(T);  // per row: columns it is ever paired with, [lo, hi)
@@ -619,6 +643,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         for (int t = 0; t < T; t++) if (!t_rowsum[t].empty()) r += t_rowsum[t][i];
         d.max_row_sum = std::max(d.max_row_sum, r);
     }
+    bt.lap("  fill");
     // ---- row bands: cell (i, j) can only be touched for band_lo[i] <= j < band_hi[i]; the accumulator
     // stores exactly these cells, row after row (the full triangle when the colours have no locality)
     d.band_cells = 0;
@@ -639,6 +664,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
 static int load_files(const char* prefix, int threads, ksb_index** out) {
     const std::string P(prefix);
+    LoadTimer lt;
     RawIndex raw;
     MappedFile fs, fc, ft;
     if (!fs.open(P + "_color_to_sources.bin")) return KSB_ERR_IO;
@@ -669,10 +695,14 @@ static int load_files(const char* prefix, int threads, ksb_index** out) {
             pos += 8 + v.bytes;
         }
         // int_vec_map key is uint32_t: insert_or_assign keeps the last record per narrowed id
+        // (the writers iterate a map, so the u64 ids are distinct: two records can only share a NARROWED id when some id
+        // does not fit 32 bits -- only then is the table of last records needed)
         IdTable last;
-        last.init(n_rec, max_id);
         bool dup = false;
-        for (uint64_t r = 0; r < n_rec; r++) dup |= last.put(recs[r].id, (uint32_t)std::min<uint64_t>(r, 0xFFFFFFFFull));
+        if (wide) {
+            last.init(n_rec, max_id);
+            for (uint64_t r = 0; r < n_rec; r++) dup |= last.put(recs[r].id, (uint32_t)std::min<uint64_t>(r, 0xFFFFFFFFull));
+        }
         if (dup) {
             if (n_rec > 0xFFFFFFFFull) { set_error("duplicate colour ids with more than 2^32 records are not supported"); return KSB_ERR_FORMAT; }
             std::vector<Rec> kept;
@@ -688,6 +718,7 @@ static int load_files(const char* prefix, int threads, ksb_index** out) {
     }
     const uint64_t C = recs.size();
     raw.n_colors_file = C;
+    lt.lap("record boundaries");
 
     // ---- colour counts: narrowed key -> narrowed value, slot order, last wins
     IdTable wt;
@@ -695,20 +726,40 @@ static int load_files(const char* prefix, int threads, ksb_index** out) {
         DumpView v;
         if (!open_dump(fc.data, fc.size, 16, &v)) return KSB_ERR_FORMAT;
         if (v.size == 0) { set_error("%s_color_count.bin is empty (reference: assert(tmpMap.size()), src/pairwise.cpp:117)", prefix); return KSB_ERR_FORMAT; }
+        // two parallel sweeps over the slots: (1) largest narrowed id, live slots, any id above 2^32;
+        // (2) the table itself -- distinct u64 keys narrow to distinct u32 keys unless an id is wide, so the direct
+        // table takes concurrent puts; otherwise slot order decides which duplicate wins and the sweep stays serial
+        const int TC = std::max(1, threads);
+        std::vector<uint32_t> tmax(TC, 0);
+        std::vector<uint64_t> tlive(TC, 0);
+        std::vector<uint8_t> twide(TC, 0);
+        parallel_chunks(v.capacity, TC, [&](int t, uint64_t b, uint64_t e) {
+            uint32_t mx = 0;
+            uint64_t lv = 0;
+            bool wd = false;
+            for (uint64_t i = b; i < e; i++)
+                if (v.ctrl[i] >= 0) { uint64_t k; std::memcpy(&k, v.slots + 16 * i, 8); mx = std::max(mx, (uint32_t)k); wd |= (k >> 32) != 0; lv++; }
+            tmax[t] = mx; tlive[t] = lv; twide[t] = wd;
+        });
         uint32_t max_id = 0;
         uint64_t live = 0;
-        for (uint64_t i = 0; i < v.capacity; i++)
-            if (v.ctrl[i] >= 0) { uint64_t k; std::memcpy(&k, v.slots + 16 * i, 8); max_id = std::max(max_id, (uint32_t)k); live++; }
+        bool wide_ids = false;
+        for (int t = 0; t < TC; t++) { max_id = std::max(max_id, tmax[t]); live += tlive[t]; wide_ids |= twide[t] != 0; }
         if (live != v.size) { set_error("%s_color_count.bin: %llu live slots, header says %llu", prefix, (unsigned long long)live, (unsigned long long)v.size); return KSB_ERR_FORMAT; }
         wt.init(v.size, max_id);
-        for (uint64_t i = 0; i < v.capacity; i++)
-            if (v.ctrl[i] >= 0) {
-                uint64_t kv[2];
-                std::memcpy(kv, v.slots + 16 * i, 16);
-                wt.put((uint32_t)kv[0], (uint32_t)kv[1]);
-            }
+        auto sweep = [&](int, uint64_t b, uint64_t e) {
+            for (uint64_t i = b; i < e; i++)
+                if (v.ctrl[i] >= 0) {
+                    uint64_t kv[2];
+                    std::memcpy(kv, v.slots + 16 * i, 16);
+                    wt.put((uint32_t)kv[0], (uint32_t)kv[1]);
+                }
+        };
+        if (wt.dense() && !wide_ids) parallel_chunks(v.capacity, TC, sweep);
+        else sweep(0, 0, v.capacity);
     }
 
+    lt.lap("colour counts");
     // ---- totals, slot order
     {
         DumpView v;
@@ -732,23 +783,53 @@ static int load_files(const char* prefix, int threads, ksb_index** out) {
     raw.members.resize(raw.off[C]);
     raw.weights.resize(C);
     std::atomic<int> bad{0};
-    parallel_chunks(C, threads, [&](int, uint64_t b, uint64_t e) {
-        for (uint64_t c = b; c < e; c++) {
+    // chunks of equal FILE BYTES, not of equal colour counts: indexers write colours of very different sizes in runs
+    // (500-member family colours after 45-member clade colours), and equal counts left one thread with most of the work
+    const int TT = std::max(1, threads);
+    std::vector<uint64_t> cstart(TT + 1, C);
+    cstart[0] = 0;
+    for (int t = 1; t < TT && C; t++) {
+        const uint64_t target = 8 + (fs.size - 8) * (uint64_t)t / (uint64_t)TT;
+        cstart[t] = (uint64_t)(std::lower_bound(recs.begin(), recs.end(), target, [](const Rec& r, uint64_t pos) { return r.pos < pos; }) - recs.begin());
+    }
+    parallel_chunks((uint64_t)TT, TT, [&](int, uint64_t tb, uint64_t te) {
+      for (uint64_t t = tb; t < te; t++)
+        for (uint64_t c = cstart[t]; c < cstart[t + 1]; c++) {
+            if (c + 16 < cstart[t + 1]) wt.prefetch(recs[c + 16].id);  // the count lookup is a cache miss per colour
             DumpView v;
             open_dump(fs.data + recs[c].pos, fs.size - recs[c].pos, 4, &v);  // validated in pass 1
             uint32_t* dst = &raw.members[raw.off[c]];
             uint64_t k = 0;
-            for (uint64_t i = 0; i < v.capacity && v.size; i++)
-                if (v.ctrl[i] >= 0) { if (k < v.size) std::memcpy(&dst[k], v.slots + 4 * i, 4); k++; }
+            if (v.size) {
+                // eight control bytes at a time: a FULL slot has the top bit of its byte clear
+                uint64_t i = 0;
+                for (; i + 8 <= v.capacity; i += 8) {
+                    uint64_t w8;
+                    std::memcpy(&w8, v.ctrl + i, 8);
+                    uint64_t full = ~w8 & 0x8080808080808080ull;
+                    while (full) {
+                        const unsigned b = (unsigned)__builtin_ctzll(full) >> 3;
+                        if (k < v.size) std::memcpy(&dst[k], v.slots + 4 * (i + b), 4);
+                        k++;
+                        full &= full - 1;
+                    }
+                }
+                for (; i < v.capacity; i++)
+                    if (v.ctrl[i] >= 0) { if (k < v.size) std::memcpy(&dst[k], v.slots + 4 * i, 4); k++; }
+            }
             if (k != v.size) { bad = 1; continue; }
-            std::sort(dst, dst + k);
+            if (k == 2) { if (dst[0] > dst[1]) std::swap(dst[0], dst[1]); }
+            else std::sort(dst, dst + k);
             uint32_t w = 0;
             wt.get(recs[c].id, &w);  // colorsCount[id] default-inserts 0 when absent
             raw.weights[c] = w;
         }
     });
     if (bad) { set_error("%s_color_to_sources.bin: a member set has live slots != size", prefix); return KSB_ERR_FORMAT; }
-    return build_index(raw, threads, out);
+    lt.lap("members extract + sort");
+    const int rc = build_index(raw, threads, out);
+    lt.lap("build_index (bin, route, blob)");
+    return rc;
 }
 
 static int from_csr(uint64_t n_colors, const uint64_t* offsets, const uint32_t* members, const uint32_t* weights,
