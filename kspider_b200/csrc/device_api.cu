@@ -702,23 +702,37 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         cur.n_items = (uint32_t)items.size() - cur.item_begin;
         // bitmap-build units of the chunk, the heaviest (most members to place) first
         cur.unit_begin = (uint32_t)units.size();
+        // with few units per CTA slot (a rank's share of a multi-GPU run) the long units of wide windows are the critical
+        // path of the build: they are split; with many units the whole-row stores of unsplit units are cheaper
+        const bool split_wide = cur.n_units < 3u * 6u * (uint32_t)d->sms;
         for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) {
             const uint32_t kblocks = (wins[w].n + kGramKBlock - 1) / kGramKBlock, segs = (wins[w].width + kGramSeg - 1) / kGramSeg;
             for (uint32_t kb = 0; kb < kblocks; kb++)
                 for (uint32_t sg = 0; sg < segs; sg++) {
                     GramUnit u;
                     u.c0k = wins[w].c0 + (uint64_t)kb * kGramKBlock;
-                    u.kn = (uint32_t)std::min<uint64_t>(kGramKBlock, wins[w].n - (uint64_t)kb * kGramKBlock);
+                    u.kn = (uint16_t)std::min<uint64_t>(kGramKBlock, wins[w].n - (uint64_t)kb * kGramKBlock);
                     u.xbase = wins[w].x0 + sg * kGramSeg;
                     u.slen = std::min<uint32_t>(kGramSeg, wins[w].width - sg * kGramSeg);
                     u.bits_row = wins[w].bits_off + (uint64_t)kb * wins[w].width + (uint64_t)sg * kGramSeg;
                     u.wq_off = sg == 0 ? (wins[w].k0 + kb) * kGramKBlock : 0xFFFFFFFFu;
+                    u.w0 = 0;
+                    u.nw = 4;
+                    if (u.slen >= 512 && split_wide) {  // a wide window holds long colours: four one-word units instead of one long one
+                        for (uint8_t wd = 0; wd < 4; wd++) {
+                            GramUnit q = u;
+                            q.w0 = wd;
+                            q.nw = 1;
+                            if (wd) q.wq_off = 0xFFFFFFFFu;
+                            if (wd < 3) units.push_back(q); else u = q;
+                        }
+                    }
                     units.push_back(u);
                 }
         }
         // proxy for the members a unit places: colours of the K-block x samples of the segment (wide windows hold long colours)
         std::stable_sort(units.begin() + cur.unit_begin, units.end(),
-                         [&](const GramUnit& a, const GramUnit& b) { return (uint64_t)a.kn * a.slen > (uint64_t)b.kn * b.slen; });
+                         [&](const GramUnit& a, const GramUnit& b) { return (uint64_t)a.kn * a.slen * a.nw > (uint64_t)b.kn * b.slen * b.nw; });
         if ((uint32_t)units.size() - cur.unit_begin != cur.n_units) cur.n_units = (uint32_t)units.size() - cur.unit_begin;
         auto cost = [&](const GramItem& it) {
             return (uint64_t)(it.kb1 - it.kb0) * (1 + std::min<uint32_t>(NB, (wins[cur.win_begin + it.win].width - it.j0 + kGramTile - 1) / kGramTile));

@@ -162,11 +162,11 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         const GramUnit gu = nxt;
         if (unit + gridDim.x < n_units) nxt = units[unit + gridDim.x];
         const uint32_t slen = gu.slen, kn = gu.kn;
+        const uint32_t k0 = min(kn, 32u * gu.w0), k1 = min(kn, 32u * (gu.w0 + gu.nw));  // colours of this unit's words
         // shared layout is WORD-major -- sm[word][sample], word = 32 colours -- so that the atomics of a warp, whose
         // lanes hold consecutive (ascending) members of a colour, fall into different banks; the 16-byte rows of the
         // bitmap are put together when the unit is written out
-#pragma unroll
-        for (uint32_t wd = 0; wd < 4; wd++)
+        for (uint32_t wd = gu.w0; wd < (uint32_t)gu.w0 + gu.nw; wd++)
             for (uint32_t r = tid; r < slen; r += 256) sm[wd * kGramSeg + r] = 0u;
         if (tid <= kn) sm_off[tid] = gram_off[gu.c0k + tid];
         __syncthreads();
@@ -175,10 +175,10 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         // independent loads in flight per lane before the first shared atomic; the colour of a lane's element is
         // followed through the staged offsets (relative, 32-bit) -- consecutive elements of a lane are 32 apart, so
         // the colour index advances by at most one or two per element.
-        const unsigned long long o0 = sm_off[0];
-        const uint32_t L = (uint32_t)(sm_off[kn] - o0);
+        const unsigned long long o0 = sm_off[k0];
+        const uint32_t L = (uint32_t)(sm_off[k1] - o0);
         __syncthreads();
-        if (tid <= kn) sm_rel[tid] = (uint32_t)(sm_off[tid] - o0);
+        if (tid >= k0 && tid <= k1) sm_rel[tid] = (uint32_t)(sm_off[tid] - o0);
         __syncthreads();
         const uint32_t xbase = gu.xbase;
         const uint32_t lane = tid & 31u, wrp = tid >> 5;
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
             uint32_t k = 0, next = 0;
             if (wb < we) {  // colour of the first element of the warp's slice: one binary search
                 const uint32_t e_first = wb * VEC > head ? wb * VEC - head : 0u;
-                uint32_t lo = 0, hi = kn;
+                uint32_t lo = k0, hi = k1;
                 while (hi - lo > 1) {
                     const uint32_t mid = (lo + hi) >> 1;
                     if (sm_rel[mid] <= e_first) lo = mid; else hi = mid;
@@ -232,7 +232,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
             const uint32_t wb = wrp * per_warp, we = min(L, wb + per_warp);
             uint32_t k = 0, next = 0;
             if (wb < we) {
-                uint32_t lo = 0, hi = kn;
+                uint32_t lo = k0, hi = k1;
                 while (hi - lo > 1) {
                     const uint32_t mid = (lo + hi) >> 1;
                     if (sm_rel[mid] <= wb) lo = mid; else hi = mid;
@@ -263,7 +263,13 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         }
         __syncthreads();
         uint4* dst = reinterpret_cast<uint4*>(bits) + gu.bits_row;
-        for (uint32_t r = tid; r < slen; r += 256) dst[r] = make_uint4(sm[r], sm[kGramSeg + r], sm[2u * kGramSeg + r], sm[3u * kGramSeg + r]);
+        if (gu.nw == 4) {
+            for (uint32_t r = tid; r < slen; r += 256) dst[r] = make_uint4(sm[r], sm[kGramSeg + r], sm[2u * kGramSeg + r], sm[3u * kGramSeg + r]);
+        } else {
+            uint32_t* dw = reinterpret_cast<uint32_t*>(dst);
+            for (uint32_t wd = gu.w0; wd < (uint32_t)gu.w0 + gu.nw; wd++)
+                for (uint32_t r = tid; r < slen; r += 256) dw[4u * r + wd] = sm[wd * kGramSeg + r];
+        }
         __syncthreads();
     }
 }

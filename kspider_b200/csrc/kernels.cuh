@@ -178,7 +178,9 @@ struct GramUnit {                    // one bitmap-build unit of a chunk (plan_g
                                      // of <= 128 colours of a window x a segment of <= kGramSeg samples
     unsigned long long c0k;          // first colour of the K-block in the Gram CSR
     unsigned long long bits_row;     // first 16-byte row of the unit in the chunk's bitmap buffer
-    uint32_t kn;                     // colours in the K-block
+    uint16_t kn;                     // colours in the K-block
+    uint8_t w0, nw;                  // the unit builds the 32-colour words [w0, w0 + nw) of the bitmap rows (nw = 4: whole rows);
+                                     // K-blocks of wide windows (long colours) are split into four one-word units
     uint32_t xbase;                  // first sample of the segment
     uint32_t slen;                   // samples in the segment
     uint32_t wq_off;                 // offset of the K-block in a weight byte plane, 0xFFFFFFFF when another unit writes it
