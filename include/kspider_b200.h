@@ -83,8 +83,13 @@ typedef struct ksb_opts {
     int32_t device;              /* CUDA ordinal; -1 = current device */
     int32_t rank;                /* this process owns row block `rank` of `world` (balanced by updates) */
     int32_t world;               /* 0 or 1 = whole triangle */
-    int32_t want_records;        /* 1: build the {i,j,shared,min,avg,max} records and bring them to the host */
-    uint64_t dense_budget_bytes; /* 0 = library default (80% of free HBM) */
+    int32_t want_records;        /* 1: build the {i,j,shared,min,avg,max} records and bring them to the host;
+                                    2: the same, HOST ONLY -- the device copies of a pass (44 bytes per row) are released as
+                                       soon as its rows are on the host (what the TSV-writing drop-in wants; such a result
+                                       cannot be clustered on the device); 0: no host copy */
+    uint64_t dense_budget_bytes; /* 0 = library default: 80% of the free HBM for a pass, i.e. its cells AND (when records
+                                    are wanted) the rows it can emit.  When a pass still runs out of device memory,
+                                    ksb_pairwise repeats the run with a quarter of the budget (more, smaller passes). */
     uint64_t spill_mode;         /* K3 sort-reduce path: 0 = auto (only when the owned block would need more than
                                     16 dense passes under the budget), 1 = always, 2 = never */
     uint64_t reserved[3];

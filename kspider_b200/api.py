@@ -30,7 +30,7 @@ def make_opts(device: int = -1, rank: int = 0, world: int = 1, want_records: boo
               dense_budget_bytes: int = 0, spill: str = "auto") -> Opts:
     o = Opts()
     o.device, o.rank, o.world = device, rank, world
-    o.want_records = 1 if want_records else 0
+    o.want_records = 2 if want_records == "host" else (1 if want_records else 0)  # "host": host records only (ksb_opts.want_records = 2)
     o.dense_budget_bytes = int(dense_budget_bytes)
     o.spill_mode = {"auto": 0, "always": 1, "never": 2}[spill]
     return o

@@ -128,6 +128,7 @@ struct ksb_result {
     ksb_record* h_records = nullptr;  // pinned, all segments concatenated (only when want_records)
     uint64_t h_capacity = 0;
     bool have_host = false;
+    bool host_only = false;           // want_records == 2: the device copies of a pass are released once its rows are on the host
     ksb_result_info info;
 };
 
@@ -313,9 +314,12 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
     { const char* gv = std::getenv("KSPIDER_GRAPH"); d->use_graph = !(gv && gv[0] == '0'); }
     uint64_t budget = opts ? opts->dense_budget_bytes : 0;
     if (budget == 0) {
+        // default: 80 % of the free memory for a pass -- its cells (8 bytes each) AND, when records are wanted, the rows it
+        // can emit (32-byte record + 12 bytes of pair / column per touched cell, every cell in the worst case)
         size_t fr = 0, tot = 0;
         KSB_CUDA(cudaMemGetInfo(&fr, &tot));
-        budget = (uint64_t)((double)fr * 0.8);
+        const bool rows = opts && opts->want_records != 0;
+        budget = (uint64_t)((double)fr * 0.8 * (rows ? 8.0 / 52.0 : 1.0));
     }
     {   // banded accumulator: prefix of the band lengths, and the per-row base the kernels add columns to
         const uint64_t N = d->desc.n_samples;
@@ -1052,6 +1056,7 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
         r->info.row_end = d->row_end;
         r->info.owned_cells = d->owned_cells;
         r->have_host = want_records != 0;
+        r->host_only = want_records == 2;
     }
     auto fail = [&](int code) { if (created) ksb_result_free(r); return code; };
 #define KSB_CUDA_R(call)                                                                              \
@@ -1083,9 +1088,16 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
         d->launches += 2;  // k5_count + the scan
         n_rows = total;
         if (n_rows) {
-            KSB_CUDA_R(cudaMallocAsync(&seg.d_records, sizeof(ksb_record) * n_rows, d->stream));
-            cudaError_t e = cudaMallocAsync(&seg.d_pairs, 12 * n_rows, d->stream);
-            if (e != cudaSuccess) { cudaFreeAsync(seg.d_records, d->stream); set_error("cudaMalloc pairs: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
+            cudaError_t e = cudaMallocAsync(&seg.d_records, sizeof(ksb_record) * n_rows, d->stream);
+            if (e == cudaSuccess) {
+                e = cudaMallocAsync(&seg.d_pairs, 12 * n_rows, d->stream);
+                if (e != cudaSuccess) { cudaFreeAsync(seg.d_records, d->stream); seg.d_records = nullptr; }
+            }
+            if (e != cudaSuccess) {
+                set_error("device memory for %llu rows of this pass (44 bytes each): %s", (unsigned long long)n_rows, cudaGetErrorString(e));
+                (void)cudaGetLastError();
+                return fail(e == cudaErrorMemoryAllocation ? KSB_ERR_NOMEM : KSB_ERR_CUDA);
+            }
             seg.n = n_rows;
             r->seg.push_back(seg);
             const uint8_t* P = d->d_payload;
@@ -1118,6 +1130,13 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
     }
     KSB_CUDA_R(cudaEventRecord(d->ev[7], d->stream));
     KSB_CUDA_R(cudaStreamSynchronize(d->stream));
+    if (r->host_only && n_rows) {  // the rows are on the host: 44 bytes per row of device memory go back to the pool
+        ksb_segment& sg = r->seg.back();
+        cudaFreeAsync(sg.d_records, d->stream);
+        cudaFreeAsync(sg.d_pairs, d->stream);
+        sg.d_records = nullptr;
+        sg.d_pairs = nullptr;
+    }
 #undef KSB_CUDA_R
     d->t.post_ms += ev_ms(d->ev[5], d->ev[6]);
     d->t.d2h_ms += ev_ms(d->ev[6], d->ev[7]);
@@ -1485,9 +1504,7 @@ int ksb_device_set_graph(ksb_device* d, int on) {
     return KSB_OK;
 }
 
-int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
-    if (!ix || !out) { set_error("ksb_pairwise: null argument"); return KSB_ERR_ARG; }
-    *out = nullptr;
+static int pairwise_once(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     using Clock = std::chrono::steady_clock;
     auto ms_since = [](Clock::time_point t) { return std::chrono::duration<float, std::milli>(Clock::now() - t).count(); };
     ksb_device* d = nullptr;
@@ -1517,6 +1534,29 @@ int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
     r->info.t.host_free_ms = ms_since(t0);
     *out = r;
     return KSB_OK;
+}
+
+// One retry policy for the whole call: when a pass runs out of device memory (its rows did not fit beside its cells), the
+// run is repeated with a quarter of the dense budget -- more, smaller passes -- instead of failing where the reference,
+// which only needs host memory, succeeds.
+int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
+    if (!ix || !out) { set_error("ksb_pairwise: null argument"); return KSB_ERR_ARG; }
+    *out = nullptr;
+    ksb_opts o{};
+    if (opts) o = *opts; else { o.device = -1; o.want_records = 1; }
+    int rc = pairwise_once(ix, &o, out);
+    for (int attempt = 0; rc == KSB_ERR_NOMEM && attempt < 3; attempt++) {
+        if (o.dense_budget_bytes == 0) {
+            int dev = o.device;
+            if (dev >= 0) cudaSetDevice(dev);
+            size_t fr = 0, tot = 0;
+            if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) { (void)cudaGetLastError(); break; }
+            o.dense_budget_bytes = (uint64_t)((double)fr * 0.8 * 8.0 / 52.0);
+        }
+        o.dense_budget_bytes = std::max<uint64_t>(o.dense_budget_bytes / 4, 1ull << 20);
+        rc = pairwise_once(ix, &o, out);
+    }
+    return rc;
 }
 
 // upload + cluster-only step + release in one call: the end-to-end path when only the labels are wanted
@@ -1648,6 +1688,7 @@ static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint3
                         uint64_t* n_edges) {
     if (!r) { set_error("ksb_cluster: null argument"); return KSB_ERR_ARG; }
     if (dist_col < 3 || dist_col > 5) { set_error("ksb_cluster: dist_col must be 3 (min), 4 (avg) or 5 (max)"); return KSB_ERR_ARG; }
+    if (r->host_only) { set_error("ksb_cluster: this result was made with want_records = 2 (host records only); its device copies are gone"); return KSB_ERR_ARG; }
     int sms = 0;
     const int dev = check_device(r->device, &sms);
     if (dev < 0) return dev;
@@ -1701,6 +1742,7 @@ static int cluster_core(const ksb_result* r, int dist_col, double cut_pct, uint3
 // n_invalid = rows for which the reference would raise (containment text > 1, inf or nan).
 int ksb_ani_column(const ksb_result* r, int ksize, double* ani_out, uint64_t* n_invalid) {
     if (!r || (!ani_out && r->info.n_rows)) { set_error("ksb_ani_column: null argument"); return KSB_ERR_ARG; }
+    if (r->host_only) { set_error("ksb_ani_column: this result was made with want_records = 2 (host records only)"); return KSB_ERR_ARG; }
     if (ksize < 1) { set_error("ksb_ani_column: ksize must be positive"); return KSB_ERR_ARG; }
     if (n_invalid) *n_invalid = 0;
     uint64_t total = 0;

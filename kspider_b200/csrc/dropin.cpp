@@ -51,7 +51,7 @@ void pairwise(std::string index_prefix, int user_threads) {
     auto work = [&](int g) {
         ksb_opts o{};
         o.device = dev0 + g;
-        o.want_records = 1;
+        o.want_records = 2;  // rows go to the TSV: no device copy is kept once a pass is on the host
         o.dense_budget_bytes = (uint64_t)(budget_gb * 1e9);
         if (gpus == 1) {
             rcs[g] = ksb_pairwise(ix, &o, &res[g]);

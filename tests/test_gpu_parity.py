@@ -419,3 +419,19 @@ def test_full_size_properties_clade_structured(ksb, name):
             else:
                 os.environ["KSPIDER_GRAM"] = old
         assert_records_equal(rec, ref)
+
+
+def test_host_only_records_release_the_device_copies(ksb):
+    """ksb_opts.want_records = 2 (what the TSV-writing drop-in uses): the same rows on the host, pass by pass, and the
+    device copies are gone -- clustering such a result is refused loudly (44 B per row stayed resident)"""
+    from kspider_b200.capi import KsbError
+    csr = random_csr(seed=61, n_samples=400, n_colors=3000, s_lo=2, s_hi=6)
+    idx = ksb.Index.from_csr(**csr)
+    want = oracle_records(csr)
+    res = idx.pairwise(want_records="host", dense_budget_bytes=200_000)   # several passes
+    assert_records_equal(res.records(), want)
+    with pytest.raises(KsbError, match="host records only"):
+        res.cluster(400, "max_cont", 0.1)
+    res2 = idx.pairwise(want_records=True)   # default budget: cells and rows of a pass both fit
+    assert_records_equal(res2.records(), want)
+    assert res2.cluster(400, "max_cont", 0.1)[1] >= 0
