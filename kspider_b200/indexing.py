@@ -18,7 +18,7 @@ import gzip
 import json
 import os
 from dataclasses import dataclass
-from typing import List, Sequence
+from typing import Optional, List, Sequence
 
 import numpy as np
 
@@ -66,8 +66,11 @@ def index_from_colors(colors: Colors, sample_ids: np.ndarray, host_threads: int 
                           ids, (colors.totals & np.uint64(0xFFFFFFFF)).astype(np.uint32), host_threads=host_threads)
 
 
-def write_index(prefix: str, colors: Colors, sample_ids: np.ndarray, names: Sequence[str], ksize: int) -> None:
-    """The reference's index file set for `prefix` (src/sourmash_indexing.cpp:281-327)."""
+def write_index(prefix: str, colors: Colors, sample_ids: np.ndarray, names: Sequence[str], ksize: int,
+                has_total: Optional[np.ndarray] = None) -> None:
+    """The reference's index file set for `prefix` (src/sourmash_indexing.cpp:281-327).  has_total[s] False: sample s
+    gets no entry in _groupID_to_kmerCount.bin (the reference only records a k-mer count for a signature it parsed
+    with the requested ksize, :205,282-285)."""
     ids = np.ascontiguousarray(sample_ids, dtype=np.uint32)
     n = ids.size
     sizes = np.diff(colors.offsets).astype(np.int64)
@@ -82,8 +85,9 @@ def write_index(prefix: str, colors: Colors, sample_ids: np.ndarray, names: Sequ
     extra = np.array([int(v) for v in ids if int(v) not in have], dtype=np.uint64)
     count_ids = np.concatenate([color_ids, extra])
     count_vals = np.concatenate([colors.counts.astype(np.uint64), np.zeros(extra.size, dtype=np.uint64)])
+    keep = np.ones(n, dtype=bool) if has_total is None else np.asarray(has_total, dtype=bool)
     write_index_files(prefix, color_ids, colors.offsets, ids[colors.members], count_ids, count_vals,
-                      ids, (colors.totals & np.uint64(0xFFFFFFFF)).astype(np.uint32))
+                      ids[keep], (colors.totals & np.uint64(0xFFFFFFFF)).astype(np.uint32)[keep])
     with open(prefix + ".namesMap", "w") as f:           # :313-319
         f.write(f"{n}\n")
         for i, nm in zip(ids, names):
@@ -108,16 +112,30 @@ def sourmash_sigs_indexing(sigs_dir: str, kSize: int, device: int = -1, out_dir:
     with prefix basename(sigs_dir) (in the working directory like the reference, or `out_dir`)."""
     sigs_dir = sigs_dir.rstrip("/")
     prefix = os.path.join(out_dir, os.path.basename(sigs_dir))
+    # First loop of the reference (:85-117): EVERY file whose last extension is "sig" or "gz" names a group (the file name
+    # without that extension) and gets the next id, in glob(3) order = byte order of the paths; a name seen twice keeps
+    # its id.  Second loop (:140-275): only files whose last extension is "sig" are parsed (plain or gzip JSON, zstr).
     names: List[str] = []
+    index_of = {}
     sketches: List[np.ndarray] = []
-    for path in sorted(glob.glob(sigs_dir + "/*")):          # glob(3) returns sorted paths (:27-47)
+    parsed: List[bool] = []
+    for path in sorted(glob.glob(sigs_dir + "/*")):
         root, ext = os.path.splitext(path)
-        if ext != ".sig":                                    # second loop of the reference: extension must be "sig" (:152)
+        if ext not in (".sig", ".gz"):
+            continue
+        name = os.path.basename(root)
+        if name not in index_of:
+            index_of[name] = len(names)
+            names.append(name)
+            sketches.append(np.zeros(0, dtype=np.uint64))
+            parsed.append(False)
+        if ext != ".sig":
             continue
         mins = read_signature_mins(path, int(kSize))
-        names.append(os.path.basename(root))
-        sketches.append(mins if mins is not None else np.zeros(0, dtype=np.uint64))
+        if mins is not None:                                 # no signature of this ksize: no k-mer count for the sample (:176-178)
+            sketches[index_of[name]] = mins
+            parsed[index_of[name]] = True
     ids = np.arange(1, len(names) + 1, dtype=np.uint32)      # groupID counter starts at 1 (:74)
     colors = build_colors(sketches, device=device)
-    write_index(prefix, colors, ids, names, int(kSize))
+    write_index(prefix, colors, ids, names, int(kSize), has_total=np.array(parsed, dtype=bool))
     return prefix

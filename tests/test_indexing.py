@@ -162,3 +162,30 @@ def test_signatures_to_pairwise_against_the_reference_golden_procedure(built_lib
     assert os.path.basename(out) == "sigs_kSpider_clusters_20.0%.tsv"
     seen = [n for line in open(out) for n in line.strip().split(",")]
     assert sorted(seen) == sorted(names)
+
+
+@pytest.mark.gpu
+def test_mixed_directory_numbers_samples_like_the_reference(built_lib, tmp_path, monkeypatch):
+    """src/sourmash_indexing.cpp:85-117 gives an id (and a namesMap line) to EVERY *.sig and *.gz file, in glob order,
+    but parses only *.sig (:152); a .sig without a signature of the requested ksize gets no k-mer count (:176-178,282-285)."""
+    from kspider_b200 import kSpider_internal
+    sk = _sketches(31, n=6, pools=2, pool_size=200, own=40)
+    d = tmp_path / "mix"
+    d.mkdir()
+    _write_sigs(str(d), sk)                                     # genome_000.sig .. genome_005.sig (+ README.txt)
+    with gzip.open(str(d / "genome_002b.sig.gz"), "wt") as f:   # extension "gz": named "genome_002b.sig", numbered, never parsed
+        json.dump([{"signatures": [{"ksize": 25, "mins": [1, 2, 3]}]}], f)
+    with open(str(d / "genome_004b.sig"), "w") as f:            # parsed, but holds no ksize-25 signature
+        json.dump([{"signatures": [{"ksize": 31, "mins": [7, 8]}]}], f)
+    monkeypatch.chdir(tmp_path)
+    kSpider_internal.sourmash_sigs_indexing(str(d), 25)
+    prefix = str(tmp_path / "mix")
+    lines = open(prefix + ".namesMap").read().splitlines()
+    want_names = ["genome_000", "genome_001", "genome_002", "genome_002b.sig", "genome_003", "genome_004", "genome_004b", "genome_005"]
+    assert lines[0] == "8" and [l.split() for l in lines[1:]] == [[str(i + 1), n] for i, n in enumerate(want_names)]
+    kSpider_internal.pairwise(index_prefix=prefix, user_threads=2)
+    seq = [l.split("\t") for l in open(prefix + "_kSpider_seqToKmersNo.tsv").read().splitlines()[1:]]
+    got = {int(r[1]): int(r[2]) for r in seq}
+    assert got == {1: sk[0].size, 2: sk[1].size, 3: sk[2].size, 5: sk[3].size, 6: sk[4].size, 8: sk[5].size}  # ids 4 and 7: no count
+    pairs = {(int(l.split("\t")[0]), int(l.split("\t")[1])) for l in open(prefix + "_kSpider_pairwise.tsv").read().splitlines()[1:]}
+    assert pairs and all(a not in (4, 7) and b not in (4, 7) for a, b in pairs)
