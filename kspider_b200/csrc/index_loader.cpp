@@ -1004,6 +1004,78 @@ int ksb_index_shard(const ksb_index* ix, int rank, int world, int host_threads, 
     }
 }
 
+namespace ksb {
+// A (descriptor, payload) pair that came from another process or rank (NCCL / gloo / a file) is checked before it is
+// trusted: the section offsets must be exactly the layout build_index derives from the descriptor's own counts, the
+// class table must add up, and the CSR offset arrays and window list inside the payload must stay inside their
+// sections.  (Member VALUES are not scanned: that is O(M); a sample index >= N inside a section can still not leave
+// the accumulator, because every kernel checks rows against the owned block and columns against the bands' extent.)
+static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t payload_bytes) {
+    if (d.magic != kIndexMagic) return "wrong magic";
+    if (d.n_samples > 0x7FFFFFFFull) return "more than 2^31 samples";
+    if (d.member_bits != 16 && d.member_bits != 32) return "member_bits";
+    if (d.packed_bits != 10 && d.packed_bits != 12 && d.packed_bits != 16 && d.packed_bits != 32) return "packed_bits";
+    if (d.weight_bits != 8 && d.weight_bits != 16 && d.weight_bits != 32) return "weight_bits";
+    const uint64_t lim = 1ull << 40;
+    for (uint64_t v : {d.n_small_members, d.n_small_colors, d.n_mid_colors, d.n_mid_members_padded, d.n_mid_items, d.n_zero_colors,
+                       d.n_zero_members, d.n_gram_colors, d.n_gram_members, d.n_gram_wins})
+        if (v > lim) return "a count is absurd";
+    const uint64_t N = d.n_samples, MB = d.member_bits / 8, PB = d.packed_bits, WB = d.weight_bits / 8;
+    auto packed_bytes = [&](uint64_t n) { return (PB * n + 7) / 8 + 8; };
+    uint64_t p = 0;
+    bool ok = true;
+    auto section = [&](uint64_t off, uint64_t bytes) { if (off != p) ok = false; p = align256(p + bytes); };
+    section(d.off_totals, 4 * N);
+    section(d.off_sample_ids, 4 * N);
+    section(d.off_row_updates, 8 * N);
+    section(d.off_band_lo, 4 * N);
+    section(d.off_band_hi, 4 * N);
+    section(d.off_small_members, packed_bytes(d.n_small_members));
+    section(d.off_small_weights, WB * d.n_small_colors);
+    section(d.off_mid_offsets, 8 * (d.n_mid_colors + 1));
+    section(d.off_mid_sizes, 4 * d.n_mid_colors);
+    section(d.off_mid_members, MB * d.n_mid_members_padded + 64);
+    section(d.off_mid_weights, 4 * d.n_mid_colors);
+    section(d.off_mid_items, sizeof(MidItem) * d.n_mid_items);
+    section(d.off_zero_offsets, 8 * (d.n_zero_colors + 1));
+    section(d.off_zero_members, MB * d.n_zero_members);
+    section(d.off_gram_offsets, 8 * (d.n_gram_colors + 1));
+    section(d.off_gram_members, packed_bytes(d.n_gram_members));
+    section(d.off_gram_weights, WB * d.n_gram_colors);
+    section(d.off_gram_wins, sizeof(GramWin) * d.n_gram_wins);
+    if (!ok) return "section offsets do not match the layout of this build";
+    if (std::max<uint64_t>(p, 256) != d.payload_bytes || d.payload_bytes != payload_bytes) return "payload size does not match the layout";
+    uint64_t nc = 0, nm = 0;
+    for (uint32_t s = 2; s <= kSmallMax; s++) {
+        const SmallClass& c = d.cls[s];
+        if (c.n == 0) continue;
+        if (c.s != s || c.n > d.n_small_colors || c.member_off > d.n_small_members || c.member_off + c.n * s > d.n_small_members ||
+            c.weight_off + c.n > d.n_small_colors)
+            return "a size class leaves its section";
+        nc += c.n;
+        nm += c.n * s;
+    }
+    if (nc != d.n_small_colors || nm != d.n_small_members) return "size classes do not add up";
+    auto monotone = [&](uint64_t off, uint64_t n, uint64_t last_max) {
+        const uint64_t* a = reinterpret_cast<const uint64_t*>(P + off);
+        for (uint64_t i = 0; i < n; i++) if (a[i + 1] < a[i]) return false;
+        return a[n] <= last_max;
+    };
+    if (!monotone(d.off_mid_offsets, d.n_mid_colors, d.n_mid_members_padded)) return "mid offsets";
+    if (!monotone(d.off_zero_offsets, d.n_zero_colors, d.n_zero_members)) return "zero-weight offsets";
+    if (!monotone(d.off_gram_offsets, d.n_gram_colors, d.n_gram_members)) return "Gram offsets";
+    const MidItem* mi = reinterpret_cast<const MidItem*>(P + d.off_mid_items);
+    for (uint64_t i = 0; i < d.n_mid_items; i++) if (mi[i].color >= d.n_mid_colors) return "a mid item names a colour that does not exist";
+    const GramWin* gw = reinterpret_cast<const GramWin*>(P + d.off_gram_wins);
+    for (uint64_t i = 0; i < d.n_gram_wins; i++)
+        if (gw[i].c0 + gw[i].n > d.n_gram_colors || gw[i].width == 0 || gw[i].width % kGramTile || gw[i].width > kGramMaxSamples + kGramTile ||
+            gw[i].extent > gw[i].width)
+            return "a Gram window is inconsistent";
+    if (d.shard_world && (d.shard_rank >= d.shard_world || d.shard_rb > d.shard_re || d.shard_re > N)) return "shard fields";
+    return nullptr;
+}
+}  // namespace ksb
+
 int ksb_index_from_blob(const void* descriptor, uint64_t descriptor_bytes, const void* payload, uint64_t payload_bytes,
                         ksb_index** out) {
     if (!descriptor || !payload || !out) { ksb::set_error("ksb_index_from_blob: null argument"); return KSB_ERR_ARG; }
@@ -1018,6 +1090,10 @@ int ksb_index_from_blob(const void* descriptor, uint64_t descriptor_bytes, const
     if (d.payload_bytes != payload_bytes) {
         ksb::set_error("payload is %llu bytes, descriptor says %llu", (unsigned long long)payload_bytes, (unsigned long long)d.payload_bytes);
         return KSB_ERR_ARG;
+    }
+    if (const char* why = ksb::validate_blob(d, static_cast<const uint8_t*>(payload), payload_bytes)) {
+        ksb::set_error("ksb_index_from_blob: the blob is not a valid index of this build (%s)", why);
+        return KSB_ERR_FORMAT;
     }
     ksb_index* ix = new (std::nothrow) ksb_index();
     if (!ix) { ksb::set_error("out of memory"); return KSB_ERR_NOMEM; }

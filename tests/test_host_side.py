@@ -308,3 +308,43 @@ def test_gram_windows_shrink_to_the_touched_samples(built_lib, monkeypatch):
     assert info["0"][0] == info["1"][0] == 400 and info["0"][2] == info["1"][2]
     assert info["1"][1] == 400 * (768 * 767 // 2)           # 700 samples -> six tiles of 128
     assert info["0"][1] == 400 * (2048 * 2047 // 2)         # the grid window itself
+
+
+def test_from_blob_rejects_a_blob_that_does_not_match_its_descriptor(built_lib):
+    """a (descriptor, payload) pair received over NCCL / gloo is checked before any offset in it is trusted"""
+    import numpy as np
+    from kspider_b200 import Index
+    from kspider_b200.capi import KsbError
+    from util import random_csr
+    idx = Index.from_csr(**random_csr(seed=5, n_samples=200, n_colors=2000, s_lo=1, s_hi=30, big=(70, 150), zero_every=13))
+    desc, payload = idx.descriptor(), idx.payload().copy()
+    ok = Index.from_blob(desc, payload)
+    assert ok.info.n_updates == idx.info.n_updates and np.array_equal(ok.payload(), payload)
+    words = np.frombuffer(desc, dtype=np.uint64).copy()
+    rng = np.random.default_rng(1)
+    rejected = 0
+    for _ in range(200):   # any single corrupted 8-byte field of the descriptor: rejected, or harmless (a counter the layout does not use)
+        w = words.copy()
+        k = int(rng.integers(1, w.size))
+        w[k] = w[k] + np.uint64(int(rng.integers(1, 1 << 20))) if rng.random() < 0.5 else np.uint64(int(rng.integers(0, 1 << 62)))
+        try:
+            Index.from_blob(w.tobytes(), payload)
+        except KsbError:
+            rejected += 1
+    assert rejected >= 60
+    with pytest.raises(KsbError):
+        Index.from_blob(desc, payload[:-256])          # truncated payload
+    bad = payload.copy()
+    gram_cols = int(idx.info.n_gram_colors)
+    if gram_cols:
+        # the Gram offsets are a monotone u64 array ending at n_gram_members: find it and break the monotony
+        arr = np.frombuffer(payload.tobytes(), dtype=np.uint64)
+        want_last = int(idx.info.n_gram_members)
+        hits = [i for i in np.flatnonzero(arr == want_last) if i >= gram_cols and arr[i - gram_cols] == 0 and np.all(np.diff(arr[i - gram_cols:i + 1].astype(np.int64)) >= 0)]
+        if hits:
+            i = hits[0]
+            bad8 = np.frombuffer(bad, dtype=np.uint64)
+            bad8 = bad8.copy()
+            bad8[i - 1] = np.uint64(want_last + 12345)
+            with pytest.raises(KsbError):
+                Index.from_blob(desc, np.frombuffer(bad8.tobytes(), dtype=np.uint8))
