@@ -1191,7 +1191,11 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
     uint32_t *vals = nullptr, *vals2 = nullptr;
     void* tmp = nullptr;
     size_t tmp_bytes = 0;
-    unsigned long long *acc_k = nullptr, *acc_s = nullptr;  // accumulated run
+    // sorted runs of unique keys, oldest first; neighbours are merged while their sizes are within a factor of two, so an
+    // entry takes part in O(log chunks) merges (merge path + reduce-by-key) instead of one re-sort of everything per chunk
+    struct Run { unsigned long long* k; unsigned long long* s; uint64_t n; };
+    std::vector<Run> runs;
+    unsigned long long *acc_k = nullptr, *acc_s = nullptr;  // the final run
     uint64_t acc_n = 0;
     ksb_result* r = nullptr;
     ksb_segment seg;
@@ -1200,6 +1204,37 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
     cudaEvent_t e0 = g_ctx[d->device].e0, e1 = g_ctx[d->device].e1;
     float emit_ms = 0.f, sort_ms = 0.f;
 #define SP(call) do { e = (call); if (e != cudaSuccess) goto cuda_fail; } while (0)
+    // merges the two newest runs into one (in place on the stack); false + e set on a CUDA error
+    auto merge_top = [&]() -> bool {
+        Run b = runs.back(); runs.pop_back();
+        Run a = runs.back(); runs.pop_back();
+        const uint64_t tot = a.n + b.n;
+        unsigned long long *mk = nullptr, *ms = nullptr, *part = nullptr, *nk = nullptr, *ns = nullptr;
+        void* mtmp = nullptr;
+        size_t mtb = 0;
+        bool ok = false;
+        unsigned long long mm = 0;
+        do {
+            if ((e = cub_reduce_bytes(tot, &mtb)) != cudaSuccess) break;
+            if ((e = cudaMallocAsync(&mk, 8 * tot, st)) != cudaSuccess) break;
+            if ((e = cudaMallocAsync(&ms, 8 * tot, st)) != cudaSuccess) break;
+            if ((e = cudaMallocAsync(&part, 8 * spill_merge_part_entries(tot), st)) != cudaSuccess) break;
+            if ((e = cudaMallocAsync(&nk, 8 * tot, st)) != cudaSuccess) break;
+            if ((e = cudaMallocAsync(&ns, 8 * tot, st)) != cudaSuccess) break;
+            if ((e = cudaMallocAsync(&mtmp, std::max<size_t>(mtb, 256), st)) != cudaSuccess) break;
+            if ((e = spill_merge_path(a.k, a.s, a.n, b.k, b.s, b.n, part, mk, ms, st)) != cudaSuccess) break;
+            if ((e = spill_reduce_sorted(mtmp, mtb, mk, ms, tot, nk, ns, d_cnt + 1, st)) != cudaSuccess) break;
+            if ((e = cudaMemcpyAsync(&mm, d_cnt + 1, 8, cudaMemcpyDeviceToHost, st)) != cudaSuccess) break;
+            if ((e = cudaStreamSynchronize(st)) != cudaSuccess) break;
+            ok = true;
+        } while (0);
+        d->launches += 3;
+        for (void* q : {(void*)mk, (void*)ms, (void*)part, mtmp, (void*)a.k, (void*)a.s, (void*)b.k, (void*)b.s})
+            if (q) cudaFreeAsync(q, st);
+        if (!ok) { if (nk) cudaFreeAsync(nk, st); if (ns) cudaFreeAsync(ns, st); return false; }
+        runs.push_back(Run{nk, ns, mm});
+        return true;
+    };
     SP(spill_temp_bytes(cap, end_bit, &tmp_bytes));
     SP(cudaMallocAsync(&keys, 8 * cap, st));
     SP(cudaMallocAsync(&keys2, 8 * cap, st));
@@ -1243,42 +1278,28 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
         SP(cudaMemcpyAsync(&m, d_cnt + 1, 8, cudaMemcpyDeviceToHost, st));
         SP(cudaStreamSynchronize(st));
         d->launches += 2;
-        if (acc_n == 0) {
-            SP(cudaMallocAsync(&acc_k, 8 * m, st));
-            SP(cudaMallocAsync(&acc_s, 8 * m, st));
-            SP(cudaMemcpyAsync(acc_k, uniq, 8 * m, cudaMemcpyDeviceToDevice, st));
-            SP(cudaMemcpyAsync(acc_s, sums, 8 * m, cudaMemcpyDeviceToDevice, st));
-            acc_n = m;
-        } else {  // merge: concat(acc, run) -> sort -> reduce
-            const uint64_t tot = acc_n + m;
-            unsigned long long *ck = nullptr, *cs = nullptr, *ck2 = nullptr, *cs2 = nullptr, *nk = nullptr, *ns = nullptr;
-            void* mtmp = nullptr;
-            size_t mtb = 0;
-            SP(spill_temp_bytes(tot, end_bit, &mtb));
-            SP(cudaMallocAsync(&ck, 8 * tot, st));
-            SP(cudaMallocAsync(&cs, 8 * tot, st));
-            SP(cudaMallocAsync(&ck2, 8 * tot, st));
-            SP(cudaMallocAsync(&cs2, 8 * tot, st));
-            SP(cudaMallocAsync(&nk, 8 * tot, st));
-            SP(cudaMallocAsync(&ns, 8 * tot, st));
-            SP(cudaMallocAsync(&mtmp, std::max<size_t>(mtb, 256), st));
-            SP(cudaMemcpyAsync(ck, acc_k, 8 * acc_n, cudaMemcpyDeviceToDevice, st));
-            SP(cudaMemcpyAsync(ck + acc_n, uniq, 8 * m, cudaMemcpyDeviceToDevice, st));
-            SP(cudaMemcpyAsync(cs, acc_s, 8 * acc_n, cudaMemcpyDeviceToDevice, st));
-            SP(cudaMemcpyAsync(cs + acc_n, sums, 8 * m, cudaMemcpyDeviceToDevice, st));
-            SP(spill_sort_reduce_runs(mtmp, mtb, ck, ck2, cs, cs2, tot, end_bit, nk, ns, d_cnt + 1, st));
-            unsigned long long mm = 0;
-            SP(cudaMemcpyAsync(&mm, d_cnt + 1, 8, cudaMemcpyDeviceToHost, st));
-            SP(cudaStreamSynchronize(st));
-            d->launches += 2;
-            cudaFreeAsync(acc_k, st); cudaFreeAsync(acc_s, st);
-            cudaFreeAsync(ck, st); cudaFreeAsync(cs, st); cudaFreeAsync(ck2, st); cudaFreeAsync(cs2, st); cudaFreeAsync(mtmp, st);
-            acc_k = nk; acc_s = ns; acc_n = mm;
+        {
+            Run nr{nullptr, nullptr, m};
+            SP(cudaMallocAsync(&nr.k, 8 * std::max<uint64_t>(m, 1), st));
+            e = cudaMallocAsync(&nr.s, 8 * std::max<uint64_t>(m, 1), st);
+            if (e != cudaSuccess) { cudaFreeAsync(nr.k, st); goto cuda_fail; }
+            runs.push_back(nr);
+            SP(cudaMemcpyAsync(nr.k, uniq, 8 * m, cudaMemcpyDeviceToDevice, st));
+            SP(cudaMemcpyAsync(nr.s, sums, 8 * m, cudaMemcpyDeviceToDevice, st));
         }
+        while (runs.size() >= 2 && runs[runs.size() - 2].n <= 2 * runs.back().n)
+            if (!merge_top()) goto cuda_fail;
         SP(cudaEventRecord(e1, st));
         SP(cudaStreamSynchronize(st));
         sort_ms += ev_ms(e0, e1);
     }
+    SP(cudaEventRecord(e0, st));
+    while (runs.size() >= 2)
+        if (!merge_top()) goto cuda_fail;
+    SP(cudaEventRecord(e1, st));
+    SP(cudaStreamSynchronize(st));
+    sort_ms += ev_ms(e0, e1);
+    if (!runs.empty()) { acc_k = runs[0].k; acc_s = runs[0].s; acc_n = runs[0].n; runs.clear(); }
     // ---- records from the final run
     r = new (std::nothrow) ksb_result();
     if (!r) { set_error("out of memory"); rc = KSB_ERR_NOMEM; goto done; }
@@ -1324,6 +1345,7 @@ done:
 #undef SP
     for (void* p : {(void*)keys, (void*)keys2, (void*)vals, (void*)vals2, (void*)uniq, (void*)sums, (void*)d_cnt, tmp, (void*)acc_k, (void*)acc_s})
         if (p) cudaFreeAsync(p, st);
+    for (const Run& q : runs) { if (q.k) cudaFreeAsync(q.k, st); if (q.s) cudaFreeAsync(q.s, st); }
     cudaStreamSynchronize(st);
     if (rc != KSB_OK) { if (r) ksb_result_free(r); return rc; }
     *out = r;

@@ -128,6 +128,15 @@ cudaError_t spill_sort_reduce_runs(void* tmp, size_t tmp_bytes, const unsigned l
                                    unsigned long long* sums_sorted, uint64_t n, int end_bit, unsigned long long* uniq,
                                    unsigned long long* sums, unsigned long long* d_runs, cudaStream_t st);
 
+// merge of two sorted runs of unique keys by merge path (duplicates side by side), and the reduce that adds them up
+cudaError_t spill_merge_path(const unsigned long long* ak, const unsigned long long* as, uint64_t na, const unsigned long long* bk,
+                             const unsigned long long* bs, uint64_t nb, unsigned long long* part, unsigned long long* out_k,
+                             unsigned long long* out_s, cudaStream_t st);
+uint64_t spill_merge_part_entries(uint64_t total);
+cudaError_t cub_reduce_bytes(uint64_t n, size_t* bytes);
+cudaError_t spill_reduce_sorted(void* tmp, size_t tmp_bytes, const unsigned long long* keys, const unsigned long long* sums_in, uint64_t n,
+                                unsigned long long* uniq, unsigned long long* sums, unsigned long long* d_runs, cudaStream_t st);
+
 // K5: two passes over the owned block.  block_counts has post_blocks(cells)+1 entries.
 constexpr uint32_t kPostThreads = 256;
 constexpr uint32_t kPostPerThread = 8;
