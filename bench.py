@@ -379,7 +379,7 @@ def main_b200(args):
     # ---- synthetic index: generated and parsed on rank 0 only
     idx = None
     s = None
-    shape = np.zeros(14, dtype=np.int64)
+    shape = np.zeros(15, dtype=np.int64)
     t_build = 0.0
     if rank == 0:
         s = make_workload(args.workload, args)
@@ -391,7 +391,7 @@ def main_b200(args):
         wsum = int((s.weights.astype(np.uint64) * (sizes * (sizes - 1) // 2).astype(np.uint64)).sum(dtype=np.uint64))  # < 2^63 on every config
         shape[:] = [inf.n_samples, inf.n_colors, inf.n_members, inf.n_updates, inf.n_small_updates, inf.n_small_members,
                     inf.n_small_colors, inf.payload_bytes, inf.n_gram_colors, inf.gram_planes, inf.n_gram_updates,
-                    inf.n_gram_members, inf.n_gram_macs, wsum]
+                    inf.n_gram_members, inf.n_gram_macs, wsum, inf.n_gram_cells]
     cpus = None
     my = None
     if world > 1:
@@ -409,7 +409,7 @@ def main_b200(args):
         shape[7] = int(payload_bytes_rank.cpu())  # bytes moved host -> GPUs per e2e step: all shards, each over its rank's link
     else:
         dev = idx.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
-    N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram, MAC_gram, WSUM = (int(v) for v in shape)
+    N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram, MAC_gram, WSUM, CELLS_gram = (int(v) for v in shape)
     spill = bool(dev.is_spill)
 
     host_ms = {"step": 0.0}
@@ -624,11 +624,23 @@ def main_b200(args):
         g_ops = 2.0 * MAC_gram * own_frac
         p_t = imma["tops"] if imma and "tops" in imma else 2.0 * float(peaks.get("bf16_tflops", 2250.0))
         tr, trs = traffic_of(args.workload, "k4_gram")
-        kernels.append({"bound": "tensor", "kernel": "k4_gram (+ kb_build)", "kernel_ms": alone["gram_ms"], "achieved": g_ops / (alone["gram_ms"] * 1e-3) / 1e12,
-                        "peak": p_t, "unit": "TFLOP/s", "algorithmic_ops": g_ops, "ops": "u8 x u8 -> s32 multiply-adds x 2 (loader's n_gram_macs: per window, colours x width(width-1)/2 x byte planes)",
-                        "traffic": tr, "traffic_source": trs,
-                        "peak_source": "int8 tcgen05 peak measured in this run (ksb_bench_imma)" if imma and "tops" in imma else "2 x MEASURED_PEAKS.json bf16_tflops",
-                        "updates_per_s": U_gram * own_frac / (alone["gram_ms"] * 1e-3), "colors": C_gram, "planes": P_gram})
+        g_ms = alone["gram_ms"]
+        tensor = {"bound": "tensor", "achieved": g_ops / (g_ms * 1e-3) / 1e12, "peak": p_t, "unit": "TFLOP/s", "algorithmic_ops": g_ops,
+                  "ops": "u8 x u8 -> s32 multiply-adds x 2 (loader's n_gram_macs: per window, colours x width(width-1)/2 x byte planes)",
+                  "peak_source": "int8 tcgen05 peak measured in this run (ksb_bench_imma)" if imma and "tops" in imma else "2 x MEASURED_PEAKS.json bf16_tflops"}
+        tensor["frac"] = tensor["achieved"] / p_t
+        # the other bound of the same launches: every cell a window can update takes one red.global.add.u64 (8 B read +
+        # 8 B write of the accumulator) and every member is read once by the bitmap build
+        g_bytes = 16.0 * CELLS_gram * own_frac + 4.0 * M_gram
+        hbm = {"bound": "hbm", "achieved": g_bytes / (g_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "algorithmic_bytes": g_bytes,
+               "bytes": "16 B per cell a Gram window can update (n_gram_cells) + 4 B per member of the Gram colours", "peak_source": peak_src}
+        hbm["frac"] = hbm["achieved"] / peak
+        binding, other = (tensor, hbm) if tensor["frac"] >= hbm["frac"] else (hbm, tensor)
+        entry = {"kernel": "k4_gram (+ kb_build)", "kernel_ms": g_ms, "traffic": tr, "traffic_source": trs,
+                 "updates_per_s": U_gram * own_frac / (g_ms * 1e-3), "colors": C_gram, "planes": P_gram,
+                 "binding": "the larger of the two fractions: the bound the launches are closer to", "other_bound": other}
+        entry.update(binding)
+        kernels.append(entry)
     for k in kernels:
         k["frac"] = k["achieved"] / k["peak"] if k["peak"] else None
     kernels.sort(key=lambda k: -k["kernel_ms"])

@@ -77,6 +77,7 @@ typedef struct ksb_index_info {
     uint64_t n_gram_macs;      /* sum over windows of colours x width(width-1)/2 x planes: u8 MACs K4 must evaluate */
     uint32_t pinned;           /* 1 if the payload lives in cudaMallocHost memory */
     uint32_t reserved;
+    uint64_t n_gram_cells;     /* sum over windows of extent(extent-1)/2: cells K4's epilogue can update (one red each) */
 } ksb_index_info;
 
 typedef struct ksb_opts {

@@ -472,7 +472,11 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_gram_members = section(packed_bytes(d.n_gram_members));
     d.off_gram_weights = section(WB * d.n_gram_colors);
     d.n_gram_wins = gwins.size();
-    for (const GramWin& w : gwins) d.n_gram_macs += (uint64_t)w.n * ((uint64_t)w.width * (w.width - 1) / 2) * gram_planes;
+    for (const GramWin& w : gwins) {
+        d.n_gram_macs += (uint64_t)w.n * ((uint64_t)w.width * (w.width - 1) / 2) * gram_planes;
+        const uint64_t ext = w.extent ? w.extent : w.width;
+        d.n_gram_cells += ext * (ext - 1) / 2;
+    }
     d.off_gram_wins = section(sizeof(GramWin) * d.n_gram_wins);
     d.payload_bytes = std::max<uint64_t>(p, 256);
 
@@ -1140,6 +1144,7 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     info->n_gram_members = d.n_gram_members;
     info->n_gram_windows = d.n_gram_wins;
     info->n_gram_macs = d.n_gram_macs;
+    info->n_gram_cells = d.n_gram_cells;
     info->pinned = ix->pinned ? 1 : 0;
     return KSB_OK;
 }

@@ -117,6 +117,7 @@ struct IndexDesc {
     uint64_t n_gram_wins;
     uint64_t n_small_updates;   // pair-updates of the K1 colours
     uint64_t n_gram_macs;       // sum over Gram windows of colours x width(width-1)/2 x planes: the u8 MACs K4 must evaluate
+    uint64_t n_gram_cells;      // sum over Gram windows of extent(extent-1)/2: cells K4's epilogue can update (one red each)
     uint64_t member_bits;       // 16 or 32: width of the compact sample ids in the mid / zero member sections
                                 // (u16 when N <= 65536: halves the blob, i.e. the H2D / broadcast time)
     uint64_t packed_bits;       // 12, 16 or 32: the same for the small-colour and Gram member sections, which can
