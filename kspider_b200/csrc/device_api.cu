@@ -40,8 +40,7 @@ struct ksb_gram_chunk {
     uint32_t item_begin = 0, n_items = 0; // into the plan's item array
     uint32_t kblocks = 0;                 // K-blocks of all windows = pitch of the weight planes / 128
     uint32_t n_units = 0;                 // bitmap-build units (K-block x sample segment)
-    uint32_t unit_begin = 0;              // into the plan's unit array: first the units of sparse windows (n_units) ...
-    uint32_t n_dense_units = 0;           // ... then those of dense windows (kb_build_dense)
+    uint32_t unit_begin = 0;              // into the plan's unit array
     bool pipe = false;                    // short items: k4_gram_pipe (static schedule, double-buffered accumulators)
 };
 struct ksb_gram_plan {
@@ -675,7 +674,6 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     std::vector<GramUnit> units;
     struct Rows { uint32_t ilo, ihi; };  // owned rows of a window, as offsets inside it
     std::vector<Rows> wrows;
-    std::vector<uint8_t> wdense;           // per (sub-)window: its bitmap is dense enough for the ballot-transpose build
     ksb_gram_chunk cur;
     auto close_chunk = [&]() {
         if (cur.n_wins == 0) return;
@@ -711,10 +709,8 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         // with few units per CTA slot (a rank's share of a multi-GPU run) the long units of wide windows are the critical
         // path of the build: they are split; with many units the whole-row stores of unsplit units are cheaper
         const bool split_wide = cur.n_units < 3u * 6u * (uint32_t)d->sms;
-        std::vector<GramUnit> dense_units;
         for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) {
             const uint32_t kblocks = (wins[w].n + kGramKBlock - 1) / kGramKBlock, segs = (wins[w].width + kGramSeg - 1) / kGramSeg;
-            const uint32_t ext = wins[w].extent ? wins[w].extent : wins[w].width;
             for (uint32_t kb = 0; kb < kblocks; kb++)
                 for (uint32_t sg = 0; sg < segs; sg++) {
                     GramUnit u;
@@ -722,13 +718,10 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
                     u.kn = (uint16_t)std::min<uint64_t>(kGramKBlock, wins[w].n - (uint64_t)kb * kGramKBlock);
                     u.xbase = wins[w].x0 + sg * kGramSeg;
                     u.slen = std::min<uint32_t>(kGramSeg, wins[w].width - sg * kGramSeg);
-                    u.rows = ext > sg * kGramSeg ? std::min<uint32_t>(u.slen, ext - sg * kGramSeg) : 0u;
-                    u.pad = 0;
                     u.bits_row = wins[w].bits_off + (uint64_t)kb * wins[w].width + (uint64_t)sg * kGramSeg;
                     u.wq_off = sg == 0 ? (wins[w].k0 + kb) * kGramKBlock : 0xFFFFFFFFu;
                     u.w0 = 0;
                     u.nw = 4;
-                    if (wdense[w]) { dense_units.push_back(u); continue; }
                     if (u.slen >= 512 && split_wide) {  // a wide window holds long colours: four one-word units instead of one long one
                         for (uint8_t wd = 0; wd < 4; wd++) {
                             GramUnit q = u;
@@ -744,10 +737,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         // proxy for the members a unit places: colours of the K-block x samples of the segment (wide windows hold long colours)
         std::stable_sort(units.begin() + cur.unit_begin, units.end(),
                          [&](const GramUnit& a, const GramUnit& b) { return (uint64_t)a.kn * a.slen * a.nw > (uint64_t)b.kn * b.slen * b.nw; });
-        cur.n_units = (uint32_t)units.size() - cur.unit_begin;
-        std::stable_sort(dense_units.begin(), dense_units.end(), [](const GramUnit& a, const GramUnit& b) { return a.rows > b.rows; });  // a sweep costs its rows
-        cur.n_dense_units = (uint32_t)dense_units.size();
-        units.insert(units.end(), dense_units.begin(), dense_units.end());
+        if ((uint32_t)units.size() - cur.unit_begin != cur.n_units) cur.n_units = (uint32_t)units.size() - cur.unit_begin;
         auto cost = [&](const GramItem& it) {
             return (uint64_t)(it.kb1 - it.kb0) * (1 + std::min<uint32_t>(NB, (wins[cur.win_begin + it.win].width - it.j0 + kGramTile - 1) / kGramTile));
         };
@@ -787,12 +777,6 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
             cur.n_units += (uint32_t)kbs * ((w.width + kGramSeg - 1) / kGramSeg);
             wins.push_back(wd);
             wrows.push_back(rows);
-            {
-                const uint64_t ext = w.extent ? w.extent : w.width;
-                const char* kd = std::getenv("KSPIDER_KB_DENSE");  // 0 = never, 1 = always (default: by density)
-                const bool dense = kd ? std::atoi(kd) != 0 : (double)w.members >= 0.15 * (double)w.n * (double)ext;
-                wdense.push_back(dense ? 1 : 0);
-            }
             cur.n_wins++;
             cur.n_colors = wd.c0 + wd.n - cur.c_begin;
             cur.bits_rows += kbs * w.width;
@@ -864,9 +848,6 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
         KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
                                  LaunchCfg{d->sms, sb}));
-        KSB_CUDA(launch_kb_build_dense(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin + c.n_units, c.n_dense_units, gp.kpad,
-                                       gp.planes, d->d_gbits, d->d_gwq, LaunchCfg{d->sms, sb}));
-        if (c.n_units && c.n_dense_units) d->launches++;
         if (sb != st) {
             KSB_CUDA(cudaEventRecord(ev_built, sb));
             KSB_CUDA(cudaStreamWaitEvent(st, ev_built, 0));

@@ -274,93 +274,6 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// kb_build_dense: the same unit for a DENSE window (clade / family windows: a colour holds 50-90 % of the samples of
-// its window).  Scattering members costs ~45 instructions each (colour search + shared atomic); here a warp owns the
-// 32 colours of one bitmap word -- a lane per colour, walking its own SORTED member list with the next member already
-// loaded -- and sweeps the rows of the segment: `has = (current member == row)`, one ballot per row IS the word of that
-// row; lane (row % 32) keeps it and every 32 rows the warp stores 32 words.  No atomics, no search, ~9 warp instructions
-// per row and word whatever the number of members; rows beyond the window's extent are zero-filled without a sweep.
-// ------------------------------------------------------------------------------------------------
-template <class MT>
-__global__ void __launch_bounds__(128) kb_build_dense(const unsigned long long* __restrict__ gram_off,
-                                                      const MT* __restrict__ gram_members,
-                                                      const void* __restrict__ gram_weights, uint32_t weight_bits,
-                                                      const GramUnit* __restrict__ units, uint32_t n_units,
-                                                      uint32_t kpad, uint32_t planes, uint32_t* __restrict__ bits,
-                                                      uint8_t* __restrict__ wq) {
-    __shared__ __align__(16) uint32_t sm[kGramSeg * 4];  // word-major: sm[word][row]
-    const uint32_t tid = threadIdx.x, lane = tid & 31u, wrp = tid >> 5;
-    if (blockIdx.x >= n_units) return;
-    GramUnit nxt_u = units[blockIdx.x];
-    for (uint32_t unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-        const GramUnit gu = nxt_u;
-        if (unit + gridDim.x < n_units) nxt_u = units[unit + gridDim.x];
-        const uint32_t slen = gu.slen, kn = gu.kn, rows = min(gu.rows, slen);
-        const uint32_t k = 32u * wrp + lane;                 // this lane's colour inside the K-block
-        unsigned long long ptr = 0, end = 0;
-        if (k < kn) { ptr = __ldg(gram_off + gu.c0k + k); end = __ldg(gram_off + gu.c0k + k + 1); }
-        // rows the sweep does not visit are zero
-        for (uint32_t r = (rows & ~31u) + lane; r < slen; r += 32) sm[wrp * kGramSeg + r] = 0u;
-        // first member at or after the segment's first sample (lists are ascending; a member below xbase wraps high)
-        uint32_t cur = 0xFFFFFFFFu, nx = 0xFFFFFFFFu;
-        if (ptr < end) {
-            cur = ldm<MT>(gram_members, ptr) - gu.xbase;
-            if (cur >= 0x80000000u) {  // the list starts before this segment (segments beyond the first): skip ahead
-                unsigned long long lo = ptr, hi = end;
-                while (lo < hi) {
-                    const unsigned long long mid = (lo + hi) >> 1;
-                    if (ldm<MT>(gram_members, mid) < gu.xbase) lo = mid + 1; else hi = mid;
-                }
-                ptr = lo;
-                cur = ptr < end ? ldm<MT>(gram_members, ptr) - gu.xbase : 0xFFFFFFFFu;
-            }
-            if (ptr + 1 < end) nx = ldm<MT>(gram_members, ptr + 1) - gu.xbase;
-        }
-        uint32_t keep = 0;
-        for (uint32_t r = 0; r < rows; r++) {
-            const bool has = cur == r;
-            const uint32_t word = __ballot_sync(0xffffffffu, has);
-            if ((r & 31u) == lane) keep = word;
-            if (has) {
-                ptr++;
-                cur = nx;
-                nx = ptr + 1 < end ? ldm<MT>(gram_members, ptr + 1) - gu.xbase : 0xFFFFFFFFu;
-            }
-            if ((r & 31u) == 31u || r + 1 == rows) {
-                const uint32_t rr = (r & ~31u) + lane;
-                if (rr < slen) sm[wrp * kGramSeg + rr] = rr <= r ? keep : 0u;
-            }
-        }
-        if (gu.wq_off != 0xFFFFFFFFu) {
-            const uint32_t wt = tid < kn ? ldw(gram_weights, weight_bits, gu.c0k + tid) : 0u;
-            for (uint32_t p = 0; p < planes; p++)
-                wq[(unsigned long long)p * kpad + (unsigned long long)gu.wq_off + tid] = (uint8_t)(wt >> (8u * p));
-        }
-        __syncthreads();
-        uint4* dst = reinterpret_cast<uint4*>(bits) + gu.bits_row;
-        for (uint32_t r = tid; r < slen; r += 128) dst[r] = make_uint4(sm[r], sm[kGramSeg + r], sm[2u * kGramSeg + r], sm[3u * kGramSeg + r]);
-        __syncthreads();
-    }
-}
-
-cudaError_t launch_kb_build_dense(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
-                                  const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
-                                  uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {
-    if (n_units == 0) return cudaSuccess;
-    const unsigned cap = (unsigned)lc.sms * 6u;  // 32 KB of shared memory per CTA
-    const unsigned ctas = n_units < cap ? n_units : cap;
-    if (member_bits == 10)
-        kb_build_dense<P10><<<ctas, 128, 0, lc.stream>>>(gram_off, static_cast<const P10*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
-    else if (member_bits == 12)
-        kb_build_dense<P12><<<ctas, 128, 0, lc.stream>>>(gram_off, static_cast<const P12*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
-    else if (member_bits == 16)
-        kb_build_dense<uint16_t><<<ctas, 128, 0, lc.stream>>>(gram_off, static_cast<const uint16_t*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
-    else
-        kb_build_dense<uint32_t><<<ctas, 128, 0, lc.stream>>>(gram_off, static_cast<const uint32_t*>(gram_members), gram_weights, weight_bits, units, n_units, kpad, planes, bits, wq);
-    return cudaGetLastError();
-}
-
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
                             const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {

@@ -281,7 +281,6 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             std::vector<std::pair<uint64_t, uint64_t>> kept;  // [begin, end) ranges of cand
             std::vector<std::pair<uint64_t, uint64_t>> kept_span;  // (first sample, width) of the kept windows
             std::vector<uint64_t> kept_extent;                      // samples from the first to the last touched one
-            std::vector<uint64_t> kept_members;                     // members of the window's colours
             for (uint64_t b = 0; b < cand.size();) {
                 uint64_t e = b, upd = 0, mem = 0, lo = ~0ull, hi = 0;
                 while (e < cand.size() && cand[e].first == cand[b].first) {
@@ -304,10 +303,10 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 const double t_gram = width * width * kpad * (double)planes / rate + (double)mem / 1.0e11 +
                                       tiles * (tiles + 1) / 2 / (double)(4 / planes) * 30e-9 + width * width / 2 / kGramRedRate;
                 const double t_red = (double)upd / kGramRedRate;
-                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); kept_span.emplace_back(lo, span_w); kept_extent.push_back(hi - lo); kept_members.push_back(mem); gain += t_red - t_gram; }
+                if (forced >= 2 || t_gram < t_red) { kept.emplace_back(b, e); kept_span.emplace_back(lo, span_w); kept_extent.push_back(hi - lo); gain += t_red - t_gram; }
                 b = e;
             }
-            if (forced < 2 && gain < 30e-6) { kept.clear(); kept_span.clear(); kept_extent.clear(); kept_members.clear(); }  // launches + memsets of the path itself
+            if (forced < 2 && gain < 30e-6) { kept.clear(); kept_span.clear(); kept_extent.clear(); }  // launches + memsets of the path itself
             std::fill(gkey.begin(), gkey.end(), NOKEY);
             uint64_t smallest = ~0ull;
             const bool shrink = !(std::getenv("KSPIDER_GRAM_SHRINK") && std::atoi(std::getenv("KSPIDER_GRAM_SHRINK")) == 0);
@@ -315,7 +314,6 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 auto& r = kept[ki];
                 const Level& lv = levels[cand[r.first].first & 0xFF];
                 GramWin w;
-                w.members = kept_members[ki];
                 w.c0 = gram_list.size();
                 w.n = (uint32_t)(r.second - r.first);
                 if (shrink) {

@@ -193,8 +193,6 @@ struct GramUnit {                    // one bitmap-build unit of a chunk (plan_g
     uint32_t xbase;                  // first sample of the segment
     uint32_t slen;                   // samples in the segment
     uint32_t wq_off;                 // offset of the K-block in a weight byte plane, 0xFFFFFFFF when another unit writes it
-    uint32_t rows;                   // rows of the segment that can hold a bit (the window's extent ends there); <= slen
-    uint32_t pad;
 };
 struct GramItem {
     uint32_t win;                 // index into the chunk's window list
@@ -222,11 +220,6 @@ cudaError_t launch_k4_gram_pipe(const GramParams& prm, const TriGeom& g, const L
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
                             const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
-// the same units for DENSE windows (a member in more than ~1/6 of the (colour, sample) positions): ballot transpose,
-// no atomics and no colour search -- a lane per colour walks its sorted member list while the warp sweeps the rows
-cudaError_t launch_kb_build_dense(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
-                                  const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
-                                  uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 
 // device handle shared by the translation units of the C-ABI (device_api.cu): validates / selects the ordinal

@@ -48,8 +48,7 @@ struct GramWin {
     uint32_t n;
     uint32_t x0;
     uint32_t width;
-    uint32_t extent;  // samples from x0 to the last one touched (<= width); 0 = unknown
-    uint64_t members; // members of the window's colours: members / (n * extent) is the density of its bitmap
+    uint32_t extent;  // samples from x0 to the last one touched (<= width); 0 in blobs written before the field existed
 };
 
 // One K2 work item: columns [b0, b0+kMidCols) x rows [a0, a0+kMidRows) of mid colour `color`
