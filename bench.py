@@ -186,10 +186,15 @@ def host_threads() -> int:
     return max(1, min(os.cpu_count() or 1, 128))
 
 
-def reference_sample(name: str):
+def reference_sample(name: str, one_thread: bool = False):
     """Bounded sample of the workload for the CPU legs of the B200 arm: the same generator and seed at a size the
-    reference finishes in ~10-30 s on the box's cores."""
+    reference finishes in ~10-30 s on the box's cores (one_thread: at a size ONE thread finishes in that time)."""
     from kspider_b200 import synth
+    if one_thread and name == "cfg4":
+        return synth.fracminhash_index(n_clades=40, clade_size=50, sketch=1000, core=600, family_pool=400, seed=100,
+                                       name="cfg4_sample_t1"), "40 of the 2000 clades (2 of 100 families)"
+    if one_thread and name == "cfg3":
+        return synth.fracminhash_index(n_clades=20, seed=31, name="cfg3_sample_t1"), "20 of the 200 clades (1 of 10 families)"
     if name in ("cfg2", "cfg2_small"):
         return synth.zipf_index(1000, 1_000_000, seed=12345, name="cfg2_sample"), \
             "1/10 of the workload: same generator/seed at 1M colours (U = 1.21e8 pair-updates)"
@@ -308,7 +313,7 @@ def main_reference(args):
         shutil.rmtree(td, ignore_errors=True)
         # one thread, on the bounded sample (a full-config run at T = 1 is several minutes to hours)
         os.makedirs(td, exist_ok=True)
-        sample, desc = reference_sample(args.workload)
+        sample, desc = reference_sample(args.workload, one_thread=True)
         sp = os.path.join(td, sample.name)
         write_files_with_reference_writer(sample, sp)
         t1 = run_reference_binary(sp, 1)

@@ -791,7 +791,7 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kScanQueue = 1024;  // kept pairs of one block queued in shared memory; a denser block appends the rest directly
 constexpr uint32_t kScanCtasPerSm = 6;  // 24 KB of shared memory, 42 registers x 256 threads per CTA
-struct ScanCut { uint32_t mode, use_max, m, shift, tie_keeps; };
+struct ScanCut { uint32_t mode, use_max, m, shift; unsigned long long add; };
 __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__ TriGeom G,
                                                          const uint32_t* __restrict__ touched,
                                                          const uint32_t* __restrict__ block_rows,
@@ -890,9 +890,11 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
                         // EXACT integer form of `float32 quotient >= c*` (no conversion, no division): the correctly
                         // rounded quotient S / T reaches c* iff the real quotient reaches the midpoint M * 2^-shift
                         // between c* and its predecessor (ties go to the even one of the two), i.e. iff
-                        // S << shift >= M * T.  S < 2^24 and T < 2^24 are exact as float32, M < 2^26, shift <= 39.
-                        const unsigned long long lhs = v[k] << cut.shift, rhs = (unsigned long long)cut.m * T;
-                        if (lhs > rhs || (lhs == rhs && cut.tie_keeps)) {
+                        // S * 2^shift >= M * T (> when the tie goes down).  S < 2^24 and T < 2^24 are exact as float32,
+                        // M < 2^26, shift <= 39.
+                        // as a threshold on S: ceil(M T / 2^shift) when a tie is kept, floor(..) + 1 otherwise (cut.add)
+                        const unsigned long long thr = ((unsigned long long)cut.m * T + cut.add) >> cut.shift;
+                        if (v[k] >= thr) {
                             const uint32_t pos = atomicAdd(&qn, 1u);
                             if (pos < kScanQueue) q[pos] = ((unsigned long long)i << 32) | j;
                             else {
@@ -987,7 +989,8 @@ static ScanCut make_scan_cut(int dist_col, float cstar) {
     if (M != std::floor(M) || shift < 0 || shift > 39) return c;
     c.m = (uint32_t)M;
     c.shift = (uint32_t)shift;
-    c.tie_keeps = (bits & 1u) == 0u ? 1u : 0u;  // round-half-to-even lands on c* iff its mantissa is even
+    // round-half-to-even lands on c* iff its mantissa is even: then S 2^shift >= M T keeps (ceil), else > (floor + 1)
+    c.add = (bits & 1u) == 0u ? (1ull << shift) - 1ull : (1ull << shift);
     c.mode = 1;
     return c;
 }
