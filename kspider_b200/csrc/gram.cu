@@ -129,6 +129,13 @@ __device__ __forceinline__ uint32_t lds32(uint32_t a) {
     return v;
 }
 
+// Order of the 128 colours of a K-block along the K axis of the expanded operand tiles.  Colour k is bit (k & 31) of
+// word (k >> 5) of a bitmap row; the expansion turns a word into eight 4-byte groups with ONE shift and ONE mask each,
+//     group q = (word >> q) & 0x01010101      byte t of group q  <=>  bit q + 8 t,
+// so colour k sits at K position (k & ~31) + 4 * (k & 7) + ((k & 31) >> 3).  A Gram product does not care about the
+// order of K as long as both operands agree: the weight byte planes (kb_build) are stored in the same order.
+__device__ __forceinline__ uint32_t kperm(uint32_t k) { return (k & ~31u) + 4u * (k & 7u) + ((k & 31u) >> 3); }
+
 __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const TriGeom& g) {
     if (x - g.rb >= g.nrows) return 0ull;
     return (unsigned long long)g.tri + 8ull * (__ldg(g.rowbase + x) - g.base);
@@ -142,7 +149,7 @@ __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const Tr
 //     bits[(bits_off + kblock * width + sample - x0) * 4 + word]      bit (colour % 128) of the sample
 // is assembled in shared memory (shared atomicOr over the K-block's contiguous member array) and written out once,
 // coalesced -- zeros included, so the bitmap needs no memset and no global atomics.  Segment 0 also
-// writes the byte planes of the weights to wq[plane * kpad + (k0 + kblock) * 128 + k].
+// writes the byte planes of the weights to wq[plane * kpad + (k0 + kblock) * 128 + kperm(k)].
 // ------------------------------------------------------------------------------------------------
 template <class MT>
 __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __restrict__ gram_off,
@@ -259,7 +266,7 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
         if (gu.wq_off != 0xFFFFFFFFu && tid < kKB) {
             const uint32_t wt = tid < kn ? ldw(gram_weights, weight_bits, gu.c0k + tid) : 0u;
             for (uint32_t p = 0; p < planes; p++)
-                wq[(unsigned long long)p * kpad + (unsigned long long)gu.wq_off + tid] = (uint8_t)(wt >> (8u * p));
+                wq[(unsigned long long)p * kpad + (unsigned long long)gu.wq_off + kperm(tid)] = (uint8_t)(wt >> (8u * p));
         }
         __syncthreads();
         uint4* dst = reinterpret_cast<uint4*>(bits) + gu.bits_row;
@@ -378,9 +385,9 @@ __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ Gr
 #pragma unroll
                     for (uint32_t wd = 0; wd < 2; wd++) {
                         const uint32_t word = wd ? bits.y : bits.x;
-                        uint32_t s4[8];  // 4 bits -> 4 bytes of 0/1
+                        uint32_t s4[8];  // 32 bits -> 8 x 4 bytes of 0/1
 #pragma unroll
-                        for (uint32_t n = 0; n < 8; n++) s4[n] = (((word >> (4 * n)) & 0xFu) * 0x00204081u) & 0x01010101u;
+                        for (uint32_t n = 0; n < 8; n++) s4[n] = (word >> n) & 0x01010101u;  // K order inside a word: see kperm()
 #pragma unroll
                         for (uint32_t c = 0; c < 2; c++) {
                             const uint32_t chunk = (h * 2 + wd) * 2 + c;  // 16-byte chunk inside the 128-byte row
@@ -691,7 +698,7 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
                         const uint32_t word = wd ? bits.y : bits.x;
                         uint32_t s4[8];
 #pragma unroll
-                        for (uint32_t q = 0; q < 8; q++) s4[q] = (((word >> (4 * q)) & 0xFu) * 0x00204081u) & 0x01010101u;
+                        for (uint32_t q = 0; q < 8; q++) s4[q] = (word >> q) & 0x01010101u;  // K order inside a word: see kperm()
 #pragma unroll
                         for (uint32_t c = 0; c < 2; c++) {
                             const uint32_t chunk = (h * 2 + wd) * 2 + c;
