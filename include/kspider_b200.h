@@ -363,6 +363,30 @@ int ksb_cluster_table(const ksb_table* t, uint64_t n_nodes, double cut_pct, int 
                       uint64_t* n_edges);
 int ksb_ani_table(const ksb_table* t, int ksize, int device, double* ani_out, uint64_t* n_invalid);
 
+/* ---- allocation-free variant --------------------------------------------------------------------------------
+ * ksb_cluster_edges_noalloc has NO counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It is the device step of ksb_cluster_table (threshold on the float32 containment
+ * through ksb_threshold_float_pct, node = id - 1, lock-free union-find, label = smallest node index of the
+ * component) on rows that are ALREADY in device memory, and it calls no cudaMalloc / cudaFree / allocating
+ * library routine and does not synchronise: it enqueues four kernels on `stream` (a cudaStream_t as void*, used
+ * as given: NULL = the CUDA default stream) of the CURRENT device and returns.
+ *   d_source_1, d_source_2, d_cont   device, n_rows entries: sample ids (1-based, as in the TSV) and the float32
+ *                                    containment column to threshold
+ *   d_labels_out                     device, n_nodes entries
+ *   d_counters_out                   device, two u64 (may be NULL): [0] = kept edges, [1] = 0xFFFFFFFF, or the
+ *                                    smallest row index (saturated to 0xFFFFFFFE) of a KEPT row naming a node
+ *                                    >= n_nodes -- such rows are skipped, where ksb_cluster_table fails
+ * The union-find forest and the counters live in one file-scope `static __device__` array of
+ * 256 + 4 * KSB_NOALLOC_MAX_NODES bytes that every GPU loading the library holds until exit; n_nodes beyond
+ * KSB_NOALLOC_MAX_NODES is refused with KSB_ERR_ARG.  Every call on a device shares that array (the part a
+ * call uses is re-initialised at its start): calls that overlap on the GPU -- two streams, two threads -- race;
+ * order them.  The first call on a device resolves the array's device address (cudaGetSymbolAddress): make it
+ * outside a graph capture (n_rows = 0 is enough). */
+#define KSB_NOALLOC_MAX_NODES (1ull << 20)
+int ksb_cluster_edges_noalloc(const uint32_t* d_source_1, const uint32_t* d_source_2, const float* d_cont, uint64_t n_rows,
+                              uint64_t n_nodes, double cut_pct, void* stream, uint32_t* d_labels_out, uint64_t* d_counters_out);
+
 /* ---- synthetic index files (bench / tests): real phmap dump bytes ------------------------- */
 int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uint64_t* color_ids,
                           const uint64_t* offsets, const uint32_t* members, uint64_t n_counts,

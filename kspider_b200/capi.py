@@ -132,6 +132,8 @@ _PROTOS = {
     "ksb_sidecar_matches": (C.c_int, [C.c_char_p, C.c_char_p]),
     "ksb_cluster_table": (C.c_int, [C.c_void_p, C.c_uint64, C.c_double, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_ani_table": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "ksb_cluster_edges_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double,
+                                            C.c_void_p, C.c_void_p, C.c_void_p]),
     "ksb_write_index_files": (C.c_int, [C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
                                         C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
     "ksb_bench_imma": (C.c_int, [C.c_uint32, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_double)]),

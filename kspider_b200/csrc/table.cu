@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 
 #include "kernels.cuh"
 #include "table.hpp"
@@ -123,6 +124,43 @@ __global__ void __launch_bounds__(256) kt_union(const Rows<TEXT> R, unsigned lon
 cudaError_t launch_k8_ani_cols(const double* dmin, const double* dmax, const float* fmin, const float* fmax, uint64_t n_rows,
                                double inv_k, double* out, unsigned long long* n_bad, const LaunchCfg& lc);
 
+}  // namespace ksb
+
+// ------------------------------------------------------------------------------------------------
+// ksb_cluster_edges_noalloc: the threshold + connected-components step of ksb_cluster_table for callers
+// that may not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No
+// counterpart in the reference.  The union-find forest
+// and the two counters -- what ksb_cluster_table takes from cudaMallocAsync -- live in ONE file-scope
+// device array that every GPU loading the library holds until exit.  All calls on a device share it:
+// the part a call uses is re-initialised at its start, and calls that overlap on the GPU race.
+// ------------------------------------------------------------------------------------------------
+namespace ksb {
+namespace {
+constexpr uint64_t kNoAllocMaxNodes = KSB_NOALLOC_MAX_NODES;
+// [0, 256): counters {u64 n_edges, u32 bad row (0xFFFFFFFF = none)}; [256, ..): parent[kNoAllocMaxNodes]
+static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + 4 * kNoAllocMaxNodes];
+
+struct NoAllocCtx {
+    bool ready = false;
+    int sms = 0;
+    unsigned char* base = nullptr;  // DEVICE address of g_noalloc_scratch on this ordinal
+};
+NoAllocCtx g_noalloc[64];
+std::mutex g_noalloc_mu;
+
+__global__ void kt_noalloc_begin(uint32_t* parent, uint32_t n_nodes, unsigned long long* n_edges, uint32_t* bad) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_nodes) parent[i] = i;
+    if (i == 0) { *n_edges = 0ull; *bad = 0xFFFFFFFFu; }
+}
+// compress the forest and hand labels + counters to the caller's buffers in the same pass
+__global__ void kt_noalloc_finish(uint32_t* parent, uint32_t n_nodes, const unsigned long long* n_edges, const uint32_t* bad,
+                                  uint32_t* labels_out, unsigned long long* counters_out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_nodes) labels_out[i] = uf_find(parent, i);
+    if (i == 0 && counters_out) { counters_out[0] = *n_edges; counters_out[1] = (unsigned long long)*bad; }
+}
+}  // namespace
 }  // namespace ksb
 
 using namespace ksb;
@@ -262,6 +300,71 @@ int ksb_ani_table(const ksb_table* t, int ksize, int device, double* ani_out, ui
         if (p) cudaFreeAsync(p, st);
     cudaStreamSynchronize(st);
     return rc;
+}
+
+
+int ksb_cluster_edges_noalloc(const uint32_t* d_source_1, const uint32_t* d_source_2, const float* d_cont, uint64_t n_rows,
+                              uint64_t n_nodes, double cut_pct, void* stream, uint32_t* d_labels_out, uint64_t* d_counters_out) {
+    if (n_nodes > kNoAllocMaxNodes) {
+        set_error("ksb_cluster_edges_noalloc: %llu nodes exceed the static scratch of this build (KSB_NOALLOC_MAX_NODES = %llu); "
+                  "use ksb_cluster_table", (unsigned long long)n_nodes, (unsigned long long)kNoAllocMaxNodes);
+        return KSB_ERR_ARG;
+    }
+    if ((n_rows && (!d_source_1 || !d_source_2 || !d_cont)) || (n_nodes && !d_labels_out)) {
+        set_error("ksb_cluster_edges_noalloc: null argument");
+        return KSB_ERR_ARG;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        set_error("ksb_cluster_edges_noalloc: no usable current device (%s)", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return KSB_ERR_CUDA;
+    }
+    NoAllocCtx& c = g_noalloc[dev];
+    {
+        // set-up, once per device, with that device current: in host code the array's name is only a stand-in,
+        // the kernels need the address the symbol has on THIS device
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!c.ready) {
+            int major = 0;
+            if ((e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev)) == cudaSuccess && major != 10) {
+                set_error("ksb_cluster_edges_noalloc: device %d is sm_%dx; this library is built for sm_100a only", dev, major);
+                return KSB_ERR_CUDA;
+            }
+            if (e == cudaSuccess) e = cudaDeviceGetAttribute(&c.sms, cudaDevAttrMultiProcessorCount, dev);
+            void* p = nullptr;
+            if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) {
+                set_error("ksb_cluster_edges_noalloc: cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+                (void)cudaGetLastError();
+                return KSB_ERR_CUDA;
+            }
+            c.base = static_cast<unsigned char*>(p);
+            c.ready = true;
+        }
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    unsigned long long* d_ne = reinterpret_cast<unsigned long long*>(c.base);
+    uint32_t* d_bad = reinterpret_cast<uint32_t*>(c.base + 8);
+    uint32_t* d_parent = reinterpret_cast<uint32_t*>(c.base + 256);
+    float cstar = ksb_threshold_float_pct(cut_pct);
+    if (cstar != cstar) cstar = INFINITY;
+    const unsigned init_ctas = (unsigned)std::max<uint64_t>(1, (n_nodes + 255) / 256);
+    kt_noalloc_begin<<<init_ctas, 256, 0, st>>>(d_parent, (uint32_t)n_nodes, d_ne, d_bad);
+    if (n_rows) {
+        const unsigned ctas = (unsigned)std::min<uint64_t>((uint64_t)c.sms * 8u, (n_rows + 2047) / 2048);
+        const Rows<false> R{d_source_1, d_source_2, nullptr, d_cont, cut_pct, cstar};
+        kt_hook_min<false><<<ctas, 256, 0, st>>>(R, n_rows, (uint32_t)n_nodes, d_parent, d_bad);
+        kt_union<false><<<ctas, 256, 0, st>>>(R, n_rows, (uint32_t)n_nodes, d_parent, d_ne);
+    }
+    kt_noalloc_finish<<<init_ctas, 256, 0, st>>>(d_parent, (uint32_t)n_nodes, d_ne, d_bad, d_labels_out,
+                                                  reinterpret_cast<unsigned long long*>(d_counters_out));
+    if ((e = cudaGetLastError()) != cudaSuccess) {
+        set_error("ksb_cluster_edges_noalloc: %s", cudaGetErrorString(e));
+        return KSB_ERR_CUDA;
+    }
+    return KSB_OK;
 }
 
 }  // extern "C"
