@@ -503,7 +503,7 @@ static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
         size_t first = 0;
         for (size_t k = 0; k < nck; k++) {
             const ksb_gram_chunk& c = plan->chunks[k];
-            uint64_t end = D.off_gram_members + ((D.packed_bits * goff[c.c_begin + c.n_colors] + 7) / 8 + 64 + 255) / 256 * 256;
+            uint64_t end = D.off_gram_members + ((gram_member_bits(D) * goff[c.c_begin + c.n_colors] + 7) / 8 + 64 + 255) / 256 * 256;
             if (k + 1 == nck || end > D.off_gram_weights) end = D.off_gram_weights;
             if (end - done < (4ull << 20) && k + 1 < nck) continue;  // too small for a piece of its own: rides with the next
             KSB_CUDA(copy(done, end));
@@ -716,7 +716,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
                     GramUnit u;
                     u.c0k = wins[w].c0 + (uint64_t)kb * kGramKBlock;
                     u.kn = (uint16_t)std::min<uint64_t>(kGramKBlock, wins[w].n - (uint64_t)kb * kGramKBlock);
-                    u.xbase = wins[w].x0 + sg * kGramSeg;
+                    u.xbase = (d->desc.gram_rel_bits ? 0u : wins[w].x0) + sg * kGramSeg;  // in the coordinates the members are stored in
                     u.slen = std::min<uint32_t>(kGramSeg, wins[w].width - sg * kGramSeg);
                     u.bits_row = wins[w].bits_off + (uint64_t)kb * wins[w].width + (uint64_t)sg * kGramSeg;
                     u.wq_off = sg == 0 ? (wins[w].k0 + kb) * kGramKBlock : 0xFFFFFFFFu;
@@ -846,7 +846,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
             KSB_CUDA(cudaStreamWaitEvent(sb, ce, 0));
         }
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
-        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)D.packed_bits, gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
+        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)gram_member_bits(D), gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
                                  LaunchCfg{d->sms, sb}));
         if (sb != st) {
             KSB_CUDA(cudaEventRecord(ev_built, sb));
@@ -1259,8 +1259,9 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, sb, lc));
         else if (ch.kind == 2)
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets),
-                                  P + D.off_gram_members, (uint32_t)D.packed_bits,
-                                  P + D.off_gram_weights, (uint32_t)D.weight_bits, g, sb, lc));
+                                  P + D.off_gram_members, (uint32_t)gram_member_bits(D),
+                                  P + D.off_gram_weights, (uint32_t)D.weight_bits, g, sb, lc,
+                                  D.gram_rel_bits ? reinterpret_cast<const GramWin*>(P + D.off_gram_wins) : nullptr, (uint32_t)D.n_gram_wins));
         else
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_zero_offsets),
                                   P + D.off_zero_members, (uint32_t)D.member_bits, nullptr, 32u, g, sb, lc));

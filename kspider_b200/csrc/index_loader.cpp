@@ -447,8 +447,24 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         const char* wb = std::getenv("KSPIDER_WEIGHT_BITS");
         d.weight_bits = (wb && std::atoi(wb) == 32) ? 32 : (wmax < (1u << 8) ? 8 : (wmax < (1u << 16) ? 16 : 32));
     }
-    const uint64_t PB = d.packed_bits, WB = d.weight_bits / 8;
+    {   // Gram members as offsets inside their window when that is narrower than a compact id (KSPIDER_GRAM_REL=0|10|12|16
+        // overrides; a width the widest window does not fit is ignored).  Default: 16 bits when ids need 32 -- the packed
+        // widths cost kb_build its 16-byte loads, so they are only taken on request.
+        uint64_t maxw = 0;
+        for (const GramWin& w : gwins) maxw = std::max<uint64_t>(maxw, w.width);
+        const char* gr = std::getenv("KSPIDER_GRAM_REL");
+        const int grv = gr ? std::atoi(gr) : -1;
+        uint64_t rel = 0;
+        if (any_gram) {
+            if (grv == 10 || grv == 12 || grv == 16) rel = (uint64_t)grv;
+            else if (grv != 0 && d.packed_bits == 32) rel = 16;
+            if (rel && (maxw > (1ull << rel) || rel >= d.packed_bits)) rel = 0;
+        }
+        d.gram_rel_bits = rel;
+    }
+    const uint64_t PB = d.packed_bits, WB = d.weight_bits / 8, GB = gram_member_bits(d);
     auto packed_bytes = [&](uint64_t n) { return (PB * n + 7) / 8 + 8; };
+    auto gram_bytes = [&](uint64_t n) { return (GB * n + 7) / 8 + 8; };
 
     bt.lap("  member width");
     // ---- payload layout
@@ -469,7 +485,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
     d.off_zero_members = section(MB * d.n_zero_members);
     d.off_gram_offsets = section(8 * (d.n_gram_colors + 1));
-    d.off_gram_members = section(packed_bytes(d.n_gram_members));
+    d.off_gram_members = section(gram_bytes(d.n_gram_members));
     d.off_gram_weights = section(WB * d.n_gram_colors);
     d.n_gram_wins = gwins.size();
     for (const GramWin& w : gwins) {
@@ -507,10 +523,10 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     // full byte is stored plainly, its half byte is OR-ed atomically (the other half may belong to a
     // neighbouring colour that another thread is writing; the payload starts zeroed).  10-bit packing:
     // element i = bits [10i, 10i+10) — 4 elements per 5 bytes, so an element always lies in 2 bytes.
-    auto put_m = [&](uint8_t* sec, uint64_t i, uint32_t v) {
-        if (PB == 32) { reinterpret_cast<uint32_t*>(sec)[i] = v; return; }
-        if (PB == 16) { reinterpret_cast<uint16_t*>(sec)[i] = (uint16_t)v; return; }
-        if (PB == 10) {
+    auto put_m = [&](uint8_t* sec, uint64_t bits, uint64_t i, uint32_t v) {
+        if (bits == 32) { reinterpret_cast<uint32_t*>(sec)[i] = v; return; }
+        if (bits == 16) { reinterpret_cast<uint16_t*>(sec)[i] = (uint16_t)v; return; }
+        if (bits == 10) {
             uint8_t* p = sec + ((5 * i) >> 2);
             const uint32_t x = (v & 0x3FFu) << ((i & 3) << 1);
             __atomic_fetch_or(p, (uint8_t)x, __ATOMIC_RELAXED);
@@ -543,6 +559,11 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         gram_off[g] = o;
         o += raw.off[gram_list[g] + 1] - raw.off[gram_list[g]];
     }
+    std::vector<uint32_t> gram_x0;  // per Gram colour (CSR order): what its stored members are relative to
+    if (d.gram_rel_bits) {
+        gram_x0.resize(gram_list.size());
+        for (const GramWin& w : gwins) std::fill(gram_x0.begin() + w.c0, gram_x0.begin() + w.c0 + w.n, w.x0);
+    }
     // groupID_to_kmerCount[id]: a map, so one value per id; missing -> 0 (operator[] default)
     for (size_t i = 0; i < raw.total_ids.size(); i++) totals[compact(raw.total_ids[i])] = raw.total_vals[i];
 
@@ -571,7 +592,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             const uint32_t* src = &raw.members[raw.off[c]];
             const uint32_t w = raw.weights[c];
             uint8_t* sec;        // member section of this colour and its first element there
-            uint64_t e0;
+            uint64_t e0, pbits = PB;
+            uint32_t rel0 = 0;   // Gram members may be stored relative to their window
             const bool packed = (k == K_GRAM) || (k != K_MID && k != K_ZERO);
             if (k == K_MID) {
                 sec = mid_m;
@@ -593,6 +615,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             } else if (k == K_GRAM) {
                 sec = gram_m;
                 e0 = gram_off[gkey[c]];
+                pbits = GB;
+                if (d.gram_rel_bits) rel0 = gram_x0[gkey[c]];
                 put_w(gram_w, gkey[c], w);
                 gramu += s * (s - 1) / 2;
             } else {
@@ -605,7 +629,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             for (uint64_t i = 0; i < s; i++) {
                 const uint32_t ci = compact(src[i]);
                 cm[i] = ci;
-                if (packed) put_m(sec, e0 + i, ci);
+                if (packed) put_m(sec, pbits, e0 + i, ci - rel0);
                 else if (MB == 2) reinterpret_cast<uint16_t*>(sec)[e0 + i] = (uint16_t)ci;
                 else reinterpret_cast<uint32_t*>(sec)[e0 + i] = ci;
                 if (k != K_ZERO) { rows[ci] += s - 1 - i; rowsum[ci] += w; }
@@ -901,11 +925,11 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     raw.n_colors_file = D.n_colors_file;
     raw.off.push_back(0);
     // one colour: sorted compact members sec[b .. b+s) of a `bits`-wide section
-    auto take = [&](const uint8_t* sec, uint64_t bits, uint64_t b, uint64_t s, uint32_t w) {
+    auto take = [&](const uint8_t* sec, uint64_t bits, uint64_t b, uint64_t s, uint32_t w, uint32_t add = 0) {
         uint64_t lo = 0, hi = s;  // first member >= r0
-        while (lo < hi) { const uint64_t mid = (lo + hi) / 2; if (member(sec, bits, b + mid) < r0) lo = mid + 1; else hi = mid; }
-        if (s - lo < 2 || member(sec, bits, b + lo) >= r1) return;  // no owned row with a later column
-        for (uint64_t i = lo; i < s; i++) raw.members.push_back(sids[member(sec, bits, b + i)]);
+        while (lo < hi) { const uint64_t mid = (lo + hi) / 2; if (member(sec, bits, b + mid) + add < r0) lo = mid + 1; else hi = mid; }
+        if (s - lo < 2 || member(sec, bits, b + lo) + add >= r1) return;  // no owned row with a later column
+        for (uint64_t i = lo; i < s; i++) raw.members.push_back(sids[member(sec, bits, b + i) + add]);
         raw.off.push_back(raw.members.size());
         raw.weights.push_back(w);
     };
@@ -926,8 +950,13 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     }
     {
         const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_gram_offsets);
-        for (uint64_t c = 0; c < D.n_gram_colors; c++)
-            take(P + D.off_gram_members, D.packed_bits, off[c], off[c + 1] - off[c], weight(P + D.off_gram_weights, c));
+        const GramWin* gw = reinterpret_cast<const GramWin*>(P + D.off_gram_wins);
+        uint64_t wi = 0;  // windows partition the Gram colours in ascending c0
+        for (uint64_t c = 0; c < D.n_gram_colors; c++) {
+            while (D.gram_rel_bits && wi + 1 < D.n_gram_wins && c >= gw[wi].c0 + gw[wi].n) wi++;
+            take(P + D.off_gram_members, gram_member_bits(D), off[c], off[c + 1] - off[c], weight(P + D.off_gram_weights, c),
+                 D.gram_rel_bits ? gw[wi].x0 : 0u);
+        }
     }
     raw.total_ids.assign(sids, sids + N);
     raw.total_vals.assign(totals, totals + N);
@@ -1020,6 +1049,7 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     if (d.member_bits != 16 && d.member_bits != 32) return "member_bits";
     if (d.packed_bits != 10 && d.packed_bits != 12 && d.packed_bits != 16 && d.packed_bits != 32) return "packed_bits";
     if (d.weight_bits != 8 && d.weight_bits != 16 && d.weight_bits != 32) return "weight_bits";
+    if (d.gram_rel_bits != 0 && d.gram_rel_bits != 10 && d.gram_rel_bits != 12 && d.gram_rel_bits != 16) return "gram_rel_bits";
     const uint64_t lim = 1ull << 40;
     for (uint64_t v : {d.n_small_members, d.n_small_colors, d.n_mid_colors, d.n_mid_members_padded, d.n_mid_items, d.n_zero_colors,
                        d.n_zero_members, d.n_gram_colors, d.n_gram_members, d.n_gram_wins})
@@ -1044,7 +1074,7 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     section(d.off_zero_offsets, 8 * (d.n_zero_colors + 1));
     section(d.off_zero_members, MB * d.n_zero_members);
     section(d.off_gram_offsets, 8 * (d.n_gram_colors + 1));
-    section(d.off_gram_members, packed_bytes(d.n_gram_members));
+    section(d.off_gram_members, (gram_member_bits(d) * d.n_gram_members + 7) / 8 + 8);
     section(d.off_gram_weights, WB * d.n_gram_colors);
     section(d.off_gram_wins, sizeof(GramWin) * d.n_gram_wins);
     if (!ok) return "section offsets do not match the layout of this build";
@@ -1073,7 +1103,8 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     const GramWin* gw = reinterpret_cast<const GramWin*>(P + d.off_gram_wins);
     for (uint64_t i = 0; i < d.n_gram_wins; i++)
         if (gw[i].c0 + gw[i].n > d.n_gram_colors || gw[i].width == 0 || gw[i].width % kGramTile || gw[i].width > kGramMaxSamples + kGramTile ||
-            gw[i].extent > gw[i].width)
+            gw[i].extent > gw[i].width || (d.gram_rel_bits && gw[i].width > (1ull << d.gram_rel_bits)) ||
+            (d.gram_rel_bits && gw[i].c0 != (i ? gw[i - 1].c0 + gw[i - 1].n : 0)))
             return "a Gram window is inconsistent";
     if (d.shard_world && (d.shard_rank >= d.shard_world || d.shard_rb > d.shard_re || d.shard_re > N)) return "shard fields";
     return nullptr;

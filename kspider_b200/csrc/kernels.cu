@@ -534,7 +534,8 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
                                                    const unsigned long long* __restrict__ off,
                                                    const MT* __restrict__ members,
                                                    const void* __restrict__ weights, uint32_t weight_bits,  // nullptr = weight 0
-                                                   const __grid_constant__ TriGeom G, const SpillSink sink) {
+                                                   const __grid_constant__ TriGeom G, const SpillSink sink,
+                                                   const GramWin* __restrict__ wins, uint32_t n_wins) {  // non-null: members are offsets inside the colour's window
     const uint32_t lane = threadIdx.x & 31u;
     const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
@@ -542,12 +543,21 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
         const unsigned long long o = off[c];
         const uint32_t s = (uint32_t)(off[c + 1] - o);
         const unsigned long long w = weights ? ldw(weights, weight_bits, c) : 0ull;
+        uint32_t x0 = 0;
+        if (wins) {  // the window holding colour c (windows partition the colours in ascending c0): warp-uniform search
+            uint32_t lo = 0, hi = n_wins;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (__ldg(&wins[mid].c0) <= c) lo = mid; else hi = mid;
+            }
+            x0 = __ldg(&wins[lo].x0);
+        }
         for (uint32_t a = 0; a + 1 < s; a++) {
-            const unsigned long long r = SpillSink::row(ldm<MT>(members, o + a), G);
+            const unsigned long long r = SpillSink::row(ldm<MT>(members, o + a) + x0, G);
             if (r == 0ull) continue;  // warp-uniform
             for (uint32_t b0 = a + 1; b0 < s; b0 += 32) {
                 const uint32_t b = b0 + lane;
-                sink.add(b < s, r, b < s ? ldm<MT>(members, o + b) : 0u, w);
+                sink.add(b < s, r, b < s ? ldm<MT>(members, o + b) + x0 : 0u, w);
             }
         }
     }
@@ -555,20 +565,20 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
 
 cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
                                uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb,
-                               const LaunchCfg& lc) {
+                               const LaunchCfg& lc, const GramWin* wins, uint32_t n_wins) {
     if (c_end <= c_begin) return cudaSuccess;
     unsigned long long ctas = (c_end - c_begin + 7) / 8;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
     const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
     if (member_bits == 10)
-        k3_emit_csr<P10><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P10*>(members), weights, weight_bits, g, sink);
+        k3_emit_csr<P10><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P10*>(members), weights, weight_bits, g, sink, wins, n_wins);
     else if (member_bits == 12)
-        k3_emit_csr<P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P12*>(members), weights, weight_bits, g, sink);
+        k3_emit_csr<P12><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const P12*>(members), weights, weight_bits, g, sink, wins, n_wins);
     else if (member_bits == 16)
-        k3_emit_csr<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint16_t*>(members), weights, weight_bits, g, sink);
+        k3_emit_csr<uint16_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint16_t*>(members), weights, weight_bits, g, sink, wins, n_wins);
     else
-        k3_emit_csr<uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint32_t*>(members), weights, weight_bits, g, sink);
+        k3_emit_csr<uint32_t><<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, off, static_cast<const uint32_t*>(members), weights, weight_bits, g, sink, wins, n_wins);
     return cudaGetLastError();
 }
 

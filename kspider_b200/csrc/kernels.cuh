@@ -113,7 +113,8 @@ cudaError_t launch_k2_spill(const MidItem* items, uint64_t item_begin, uint64_t 
                             const uint32_t* mid_sizes, const void* mid_members, uint32_t member_bits, const uint32_t* mid_weights,
                             const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
 cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
-                               uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc);
+                               uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc,
+                               const GramWin* wins = nullptr, uint32_t n_wins = 0);  // wins: members are offsets inside the colour's Gram window
 
 cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
                              const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,

@@ -123,13 +123,18 @@ struct IndexDesc {
     uint64_t packed_bits;       // 12, 16 or 32: the same for the small-colour and Gram member sections, which can
                                 // also be 12-bit packed (N <= 4096); these two sections are most of the blob
     uint64_t weight_bits;       // 8, 16 or 32: element width of the small-colour and Gram weight sections
+    uint64_t gram_rel_bits;     // 0: the Gram member section holds compact sample ids, packed_bits wide.  10, 12 or 16: it
+                                // holds OFFSETS INSIDE THE COLOUR'S WINDOW (member - GramWin::x0) of that width -- a window
+                                // is at most 2^bits samples wide whatever N is, so an index of > 65536 samples ships 2-byte
+                                // Gram members instead of 4-byte ones (cfg4: the blob, i.e. the H2D time, 307 -> 163 MB)
     // row-block shard (ksb_index_shard): this blob holds only what the owner of triangle rows
     // [shard_rb, shard_re) needs -- colours with a member in that range, cut down to their members
     // >= shard_rb.  shard_world == 0: the whole index.
     uint64_t shard_world, shard_rank, shard_rb, shard_re;
     uint64_t payload_bytes;
 };
-constexpr uint64_t kIndexMagic = 0x33305844494253ULL | (0x4BULL << 56);
+constexpr uint64_t kIndexMagic = 0x34305844494253ULL | (0x4BULL << 56);
+inline uint64_t gram_member_bits(const IndexDesc& d) { return d.gram_rel_bits ? d.gram_rel_bits : d.packed_bits; }
 
 }  // namespace ksb
 

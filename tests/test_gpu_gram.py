@@ -208,3 +208,25 @@ def test_gram_pipelined_upload_pieces(ksb, gram_env, monkeypatch):
         res.close()
     dev = idx.upload(device=0)
     assert_records_equal(dev.run_all_passes().records(), want)
+
+
+@pytest.mark.parametrize("mbits,rel", [("16", "0"), ("16", "12"), ("16", "10"), ("32", None), ("32", "12"), ("32", "0")])
+def test_gram_members_relative_to_their_window(ksb, gram_env, monkeypatch, mbits, rel):
+    """Gram members shipped as offsets inside their window (IndexDesc::gram_rel_bits; the default for indexes whose ids
+    need 32 bits is 16-bit offsets): kb_build, the row-block shards and the spill emitter (k3_emit_csr) decode every
+    encoding to the same rows, bit for bit the oracle's."""
+    gram_env(16)
+    monkeypatch.setenv("KSPIDER_MEMBER_BITS", mbits)
+    if rel is None:
+        monkeypatch.delenv("KSPIDER_GRAM_REL", raising=False)
+    else:
+        monkeypatch.setenv("KSPIDER_GRAM_REL", rel)
+    csr = _clade_csr(seed=63, n_clades=16, clade=50, fam=4, n_core=150, n_fam=40, n_noise=300, n_samples=5000)
+    want = oracle_records(csr)
+    idx = ksb.Index.from_csr(**csr, host_threads=3)
+    assert idx.info.n_gram_colors > 0 and idx.info.n_gram_windows > 3
+    assert_records_equal(idx.pairwise(device=0).records(), want)
+    parts = [idx.shard(r, 3).pairwise().records() for r in range(3)]
+    assert_records_equal(np.concatenate(parts), want)
+    got = idx.pairwise(spill="always", dense_budget_bytes=1).records()
+    assert_records_equal(got, want)

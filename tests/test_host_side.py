@@ -348,3 +348,52 @@ def test_from_blob_rejects_a_blob_that_does_not_match_its_descriptor(built_lib):
             bad8[i - 1] = np.uint64(want_last + 12345)
             with pytest.raises(KsbError):
                 Index.from_blob(desc, np.frombuffer(bad8.tobytes(), dtype=np.uint8))
+
+
+def test_gram_members_stored_relative_to_their_window(built_lib, monkeypatch):
+    """Loader: Gram-routed colours may ship their members as offsets inside their window (IndexDesc::gram_rel_bits:
+    2-byte members for an index whose compact ids need 4 bytes).  The encoding never changes what the index says:
+    shards rebuilt from the PACKED Gram section of every encoding are byte-identical, and the blob shrinks."""
+    from kspider_b200 import Index
+    rng = np.random.default_rng(15)
+    n = 6000
+    ids = np.arange(1, n + 1, dtype=np.uint32)
+    members, offsets = [], [0]
+    for fam0, fam, s, cnt in ((900, 700, 350, 300), (3000, 100, 60, 500), (5100, 800, 90, 200)):
+        for _ in range(cnt):
+            m = np.sort(rng.choice(fam, size=s, replace=False)) + fam0
+            members.append(ids[m])
+            offsets.append(offsets[-1] + m.size)
+    nc = len(offsets) - 1
+    csr = dict(offsets=np.array(offsets, dtype=np.uint64), members=np.concatenate(members).astype(np.uint32),
+               weights=rng.integers(1, 200, size=nc).astype(np.uint32), total_ids=ids, total_vals=np.full(n, 10 ** 6, dtype=np.uint32))
+    monkeypatch.setenv("KSPIDER_GRAM", "16")
+    shards, sizes = {}, {}
+    for mbits, rel in (("16", "0"), ("16", "12"), ("16", "10"), ("32", None), ("32", "0"), ("32", "12")):
+        monkeypatch.setenv("KSPIDER_MEMBER_BITS", mbits)
+        if rel is None:
+            monkeypatch.delenv("KSPIDER_GRAM_REL", raising=False)
+        else:
+            monkeypatch.setenv("KSPIDER_GRAM_REL", rel)
+        idx = Index.from_csr(**csr, host_threads=2)
+        assert idx.info.n_gram_colors == nc
+        sizes[(mbits, rel)] = int(idx.info.payload_bytes)
+        cp = Index.from_blob(idx.descriptor(), idx.payload())   # the validator accepts every encoding it wrote
+        assert cp.info.n_updates == idx.info.n_updates
+        # the shards are built under ONE setting, from the parents' differently encoded sections
+        monkeypatch.setenv("KSPIDER_MEMBER_BITS", "16")
+        monkeypatch.setenv("KSPIDER_GRAM_REL", "0")
+        shards[(mbits, rel)] = []
+        for r in range(2):
+            sh = idx.shard(r, 2, host_threads=2)   # kept alive while its payload view is copied
+            shards[(mbits, rel)].append(bytes(sh.payload()))
+            sh.close()
+        idx.close()
+    base = shards[("16", "0")]
+    for key, got in shards.items():
+        assert got == base, key
+    gm = int(csr["members"].size)
+    assert sizes[("16", "0")] - sizes[("16", "12")] >= gm // 2 - 4096          # 16 -> 12 bits per Gram member
+    assert sizes[("16", "12")] - sizes[("16", "10")] >= gm // 4 - 4096          # every window here is at most 1024 samples wide
+    assert sizes[("32", "0")] - sizes[("32", None)] >= 2 * gm - 4096          # default: 32 -> 16 bits when ids need 32
+    assert sizes[("32", None)] - sizes[("32", "12")] >= gm // 2 - 4096
