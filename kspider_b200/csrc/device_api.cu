@@ -36,6 +36,7 @@ struct ksb_pass {
 struct ksb_gram_chunk {
     uint64_t c_begin = 0, n_colors = 0;   // contiguous range of the Gram CSR
     uint64_t bits_rows = 0;               // 16-byte bitmap rows of the chunk
+    uint64_t blob_row0 = 0;               // bitmap form of the blob (IndexDesc::gram_form 1): the chunk's first row in the blob's bitmap section
     uint32_t win_begin = 0, n_wins = 0;   // into the plan's window array
     uint32_t item_begin = 0, n_items = 0; // into the plan's item array
     uint32_t kblocks = 0;                 // K-blocks of all windows = pitch of the weight planes / 128
@@ -503,7 +504,8 @@ static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
         size_t first = 0;
         for (size_t k = 0; k < nck; k++) {
             const ksb_gram_chunk& c = plan->chunks[k];
-            uint64_t end = D.off_gram_members + ((gram_member_bits(D) * goff[c.c_begin + c.n_colors] + 7) / 8 + 64 + 255) / 256 * 256;
+            uint64_t end = D.gram_form ? D.off_gram_members + (16 * (c.blob_row0 + c.bits_rows + kGramTile) + 255) / 256 * 256
+                                       : D.off_gram_members + ((gram_member_bits(D) * goff[c.c_begin + c.n_colors] + 7) / 8 + 64 + 255) / 256 * 256;
             if (k + 1 == nck || end > D.off_gram_weights) end = D.off_gram_weights;
             if (end - done < (4ull << 20) && k + 1 < nck) continue;  // too small for a piece of its own: rides with the next
             KSB_CUDA(copy(done, end));
@@ -709,7 +711,8 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         // with few units per CTA slot (a rank's share of a multi-GPU run) the long units of wide windows are the critical
         // path of the build: they are split; with many units the whole-row stores of unsplit units are cheaper
         const bool split_wide = cur.n_units < 3u * 6u * (uint32_t)d->sms;
-        for (uint32_t w = cur.win_begin; w < cur.win_begin + cur.n_wins; w++) {
+        if (d->desc.gram_form) cur.n_units = 0;
+        for (uint32_t w = cur.win_begin; !d->desc.gram_form && w < cur.win_begin + cur.n_wins; w++) {
             const uint32_t kblocks = (wins[w].n + kGramKBlock - 1) / kGramKBlock, segs = (wins[w].width + kGramSeg - 1) / kGramSeg;
             for (uint32_t kb = 0; kb < kblocks; kb++)
                 for (uint32_t sg = 0; sg < segs; sg++) {
@@ -750,8 +753,12 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         cur.win_begin = (uint32_t)wins.size();
     };
     new_chunk(0);
+    const bool bitmap_form = d->desc.gram_form != 0;  // the chunk's bitmap is a slice of the blob: nothing to build
+    uint64_t blob_row = 0;                            // first bitmap row of the current window in the blob
     for (const GramWin& w : d->gwins) {
         const uint64_t x0 = w.x0, x1 = (uint64_t)w.x0 + w.width;
+        const uint64_t win_row0 = blob_row;
+        blob_row += gram_win_rows(w);
         if (p.re <= x0 || p.rb >= x1 || w.n == 0) {  // no owned row inside the window
             if (cur.n_wins) { close_chunk(); }
             new_chunk(w.c0 + w.n);
@@ -764,7 +771,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         for (uint64_t kb = 0; kb < kb_total; kb += kb_max) {
             const uint64_t kbs = std::min(kb_max, kb_total - kb);
             if (cur.n_wins && cur.bits_rows + kbs * w.width > chunk_rows) { close_chunk(); new_chunk(w.c0 + kb * kGramKBlock); }
-            if (cur.n_wins == 0) cur.c_begin = w.c0 + kb * kGramKBlock;
+            if (cur.n_wins == 0) { cur.c_begin = w.c0 + kb * kGramKBlock; cur.blob_row0 = win_row0 + kb * w.width; }
             GramWinDev wd;
             wd.c0 = w.c0 + kb * kGramKBlock;
             wd.n = (uint32_t)std::min<uint64_t>(kbs * kGramKBlock, w.n - kb * kGramKBlock);
@@ -786,7 +793,7 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
     close_chunk();
     uint64_t need_bits = 0, need_wq = 0;
     for (const ksb_gram_chunk& c : plan.chunks) {
-        need_bits = std::max(need_bits, (c.bits_rows + kGramTile) * 16);  // tiles start at any row: the last may hang over
+        if (!bitmap_form) need_bits = std::max(need_bits, (c.bits_rows + kGramTile) * 16);  // tiles start at any row: the last may hang over
         need_wq = std::max<uint64_t>(need_wq, (uint64_t)d->g_planes * c.kblocks * kGramKBlock + 256);
     }
     if (!plan.chunks.empty()) {
@@ -830,7 +837,7 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
     bool first = true;
     for (const ksb_gram_chunk& c : plan.chunks) {
         GramParams gp;
-        gp.bits = d->d_gbits;
+        gp.bits = D.gram_form ? reinterpret_cast<const uint32_t*>(P + D.off_gram_members) + 4 * c.blob_row0 : d->d_gbits;
         gp.wq = d->d_gwq;
         gp.wins = plan.d_wins + c.win_begin;
         gp.items = plan.d_items + c.item_begin;
@@ -846,8 +853,11 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
             KSB_CUDA(cudaStreamWaitEvent(sb, ce, 0));
         }
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
-        KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)gram_member_bits(D), gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
-                                 LaunchCfg{d->sms, sb}));
+        if (D.gram_form)
+            KSB_CUDA(launch_kb_weights(gp.wins, gp.n_wins, c.kblocks, gw, (uint32_t)D.weight_bits, gp.kpad, gp.planes, d->d_gwq, LaunchCfg{d->sms, sb}));
+        else
+            KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)gram_member_bits(D), gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
+                                     LaunchCfg{d->sms, sb}));
         if (sb != st) {
             KSB_CUDA(cudaEventRecord(ev_built, sb));
             KSB_CUDA(cudaStreamWaitEvent(st, ev_built, 0));
@@ -1257,6 +1267,11 @@ int ksb_device_run_spill(ksb_device* d, int want_records, ksb_result** out) {
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_sizes),
                                P + D.off_mid_members, (uint32_t)D.member_bits,
                                reinterpret_cast<const uint32_t*>(P + D.off_mid_weights), g, sb, lc));
+        else if (ch.kind == 2 && D.gram_form)
+            SP(launch_k3_emit_bitmap(ch.b, ch.e, reinterpret_cast<const GramWin*>(P + D.off_gram_wins), (uint32_t)D.n_gram_wins,
+                                     reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets),
+                                     reinterpret_cast<const uint32_t*>(P + D.off_gram_members), P + D.off_gram_weights,
+                                     (uint32_t)D.weight_bits, g, sb, lc));
         else if (ch.kind == 2)
             SP(launch_k3_emit_csr(ch.b, ch.e, reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets),
                                   P + D.off_gram_members, (uint32_t)gram_member_bits(D),

@@ -281,6 +281,36 @@ __global__ void __launch_bounds__(256) kb_build(const unsigned long long* __rest
     }
 }
 
+// kb_weights: the weight byte planes of a chunk whose bitmaps are part of the blob (IndexDesc::gram_form 1) -- all that
+// is left of kb_build there.  One CTA per K-block of the chunk; wq[plane * kpad + (k0 + kblock) * 128 + kperm(k)].
+__global__ void __launch_bounds__(kKB) kb_weights(const GramWinDev* __restrict__ wins, uint32_t n_wins,
+                                                  const void* __restrict__ gram_weights, uint32_t weight_bits,
+                                                  uint32_t kpad, uint32_t planes, uint8_t* __restrict__ wq) {
+    __shared__ uint32_t s_win;
+    const uint32_t kb = blockIdx.x, tid = threadIdx.x;
+    if (tid == 0) {  // the window whose K-blocks [k0, k0 + ceil(n / 128)) hold kb: windows are listed in ascending k0
+        uint32_t lo = 0, hi = n_wins;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (wins[mid].k0 <= kb) lo = mid; else hi = mid;
+        }
+        s_win = lo;
+    }
+    __syncthreads();
+    const GramWinDev w = wins[s_win];
+    const uint32_t k = (kb - w.k0) * kKB + tid;
+    const uint32_t wt = k < w.n ? ldw(gram_weights, weight_bits, w.c0 + k) : 0u;
+    for (uint32_t p = 0; p < planes; p++)
+        wq[(unsigned long long)p * kpad + (unsigned long long)kb * kKB + kperm(tid)] = (uint8_t)(wt >> (8u * p));
+}
+
+cudaError_t launch_kb_weights(const GramWinDev* wins, uint32_t n_wins, uint32_t kblocks, const void* gram_weights, uint32_t weight_bits,
+                              uint32_t kpad, uint32_t planes, uint8_t* wq, const LaunchCfg& lc) {
+    if (kblocks == 0) return cudaSuccess;
+    kb_weights<<<kblocks, kKB, 0, lc.stream>>>(wins, n_wins, gram_weights, weight_bits, kpad, planes, wq);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
                             const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc) {

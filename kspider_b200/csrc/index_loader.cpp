@@ -462,6 +462,18 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         }
         d.gram_rel_bits = rel;
     }
+    {   // Gram colours as ready-made bitmaps when that is the smaller blob (KSPIDER_GRAM_FORM=csr|bitmap overrides)
+        uint64_t rows = 0;
+        for (const GramWin& w : gwins) rows += gram_win_rows(w);
+        const uint64_t csr_bytes = (gram_member_bits(d) * mtot[K_GRAM] + 7) / 8 + 8 * (uint64_t)gram_list.size();
+        const char* gf = std::getenv("KSPIDER_GRAM_FORM");
+        bool bitmap = any_gram && 16 * rows < csr_bytes;
+        if (gf && !std::strcmp(gf, "csr")) bitmap = false;
+        if (gf && !std::strcmp(gf, "bitmap")) bitmap = any_gram;
+        d.gram_form = bitmap ? 1 : 0;
+        d.gram_bitmap_rows = bitmap ? rows : 0;
+        if (bitmap) d.gram_rel_bits = 0;
+    }
     const uint64_t PB = d.packed_bits, WB = d.weight_bits / 8, GB = gram_member_bits(d);
     auto packed_bytes = [&](uint64_t n) { return (PB * n + 7) / 8 + 8; };
     auto gram_bytes = [&](uint64_t n) { return (GB * n + 7) / 8 + 8; };
@@ -484,8 +496,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_mid_items = section(sizeof(MidItem) * d.n_mid_items);
     d.off_zero_offsets = section(8 * (d.n_zero_colors + 1));
     d.off_zero_members = section(MB * d.n_zero_members);
-    d.off_gram_offsets = section(8 * (d.n_gram_colors + 1));
-    d.off_gram_members = section(gram_bytes(d.n_gram_members));
+    d.off_gram_offsets = section(d.gram_form ? 8 * (gwins.size() + 1) : 8 * (d.n_gram_colors + 1));
+    d.off_gram_members = section(d.gram_form ? 16 * (d.gram_bitmap_rows + kGramTile) : gram_bytes(d.n_gram_members));
     d.off_gram_weights = section(WB * d.n_gram_colors);
     d.n_gram_wins = gwins.size();
     for (const GramWin& w : gwins) {
@@ -555,15 +567,29 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
 
     std::copy(sample_ids.begin(), sample_ids.end(), sids);
     if (!gwins.empty()) std::memcpy(P + d.off_gram_wins, gwins.data(), sizeof(GramWin) * gwins.size());
-    for (uint64_t g = 0, o = 0; g < gram_list.size(); g++) {  // Gram CSR: colours grouped by window
-        gram_off[g] = o;
-        o += raw.off[gram_list[g] + 1] - raw.off[gram_list[g]];
-    }
+    if (!d.gram_form)
+        for (uint64_t g = 0, o = 0; g < gram_list.size(); g++) {  // Gram CSR: colours grouped by window
+            gram_off[g] = o;
+            o += raw.off[gram_list[g] + 1] - raw.off[gram_list[g]];
+        }
     std::vector<uint32_t> gram_x0;  // per Gram colour (CSR order): what its stored members are relative to
     if (d.gram_rel_bits) {
         gram_x0.resize(gram_list.size());
         for (const GramWin& w : gwins) std::fill(gram_x0.begin() + w.c0, gram_x0.begin() + w.c0 + w.n, w.x0);
     }
+    std::vector<uint32_t> gram_win_of;  // bitmap form: window of every Gram colour; gram_off = first bitmap row of every window
+    if (d.gram_form) {
+        gram_win_of.resize(gram_list.size());
+        uint64_t row = 0;
+        for (size_t wi = 0; wi < gwins.size(); wi++) {
+            const GramWin& w = gwins[wi];
+            std::fill(gram_win_of.begin() + w.c0, gram_win_of.begin() + w.c0 + w.n, (uint32_t)wi);
+            gram_off[wi] = row;
+            row += gram_win_rows(w);
+        }
+        gram_off[gwins.size()] = row;
+    }
+    uint32_t* gram_bits = reinterpret_cast<uint32_t*>(gram_m);
     // groupID_to_kmerCount[id]: a map, so one value per id; missing -> 0 (operator[] default)
     for (size_t i = 0; i < raw.total_ids.size(); i++) totals[compact(raw.total_ids[i])] = raw.total_vals[i];
 
@@ -594,6 +620,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             uint8_t* sec;        // member section of this colour and its first element there
             uint64_t e0, pbits = PB;
             uint32_t rel0 = 0;   // Gram members may be stored relative to their window
+            uint32_t* brow = nullptr;  // bitmap form: the colour's word of the bitmap row of sample x0, and its bit
+            uint32_t bbit = 0;
             const bool packed = (k == K_GRAM) || (k != K_MID && k != K_ZERO);
             if (k == K_MID) {
                 sec = mid_m;
@@ -614,9 +642,18 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 zero_off[at[k]] = mat[k];
             } else if (k == K_GRAM) {
                 sec = gram_m;
-                e0 = gram_off[gkey[c]];
-                pbits = GB;
-                if (d.gram_rel_bits) rel0 = gram_x0[gkey[c]];
+                if (d.gram_form) {
+                    const GramWin& gwn = gwins[gram_win_of[gkey[c]]];
+                    const uint64_t lc = gkey[c] - gwn.c0;
+                    brow = gram_bits + 4 * (gram_off[gram_win_of[gkey[c]]] + (lc / kGramKBlock) * gwn.width) + ((lc % kGramKBlock) >> 5);
+                    bbit = 1u << (lc & 31u);
+                    rel0 = gwn.x0;
+                    e0 = 0;
+                } else {
+                    e0 = gram_off[gkey[c]];
+                    pbits = GB;
+                    if (d.gram_rel_bits) rel0 = gram_x0[gkey[c]];
+                }
                 put_w(gram_w, gkey[c], w);
                 gramu += s * (s - 1) / 2;
             } else {
@@ -629,7 +666,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             for (uint64_t i = 0; i < s; i++) {
                 const uint32_t ci = compact(src[i]);
                 cm[i] = ci;
-                if (packed) put_m(sec, pbits, e0 + i, ci - rel0);
+                if (brow) __atomic_fetch_or(brow + 4 * (uint64_t)(ci - rel0), bbit, __ATOMIC_RELAXED);  // other colours of the K-block share the word
+                else if (packed) put_m(sec, pbits, e0 + i, ci - rel0);
                 else if (MB == 2) reinterpret_cast<uint16_t*>(sec)[e0 + i] = (uint16_t)ci;
                 else reinterpret_cast<uint32_t*>(sec)[e0 + i] = ci;
                 if (k != K_ZERO) { rows[ci] += s - 1 - i; rowsum[ci] += w; }
@@ -648,7 +686,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         t_mid_members[t] = midm;
         t_gram_updates[t] = gramu;
     });
-    gram_off[d.n_gram_colors] = d.n_gram_members;
+    if (!d.gram_form) gram_off[d.n_gram_colors] = d.n_gram_members;
     mid_off[d.n_mid_colors] = d.n_mid_members_padded;
     zero_off[d.n_zero_colors] = d.n_zero_members;
     for (int t = 0; t < T; t++) {
@@ -951,8 +989,28 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     {
         const uint64_t* off = reinterpret_cast<const uint64_t*>(P + D.off_gram_offsets);
         const GramWin* gw = reinterpret_cast<const GramWin*>(P + D.off_gram_wins);
+        if (D.gram_form) {
+            // bitmap form: the member lists of a K-block's 128 colours are read back from its rows (samples ascending)
+            const uint32_t* bits = reinterpret_cast<const uint32_t*>(P + D.off_gram_members);
+            std::vector<uint32_t> lists[kGramKBlock];
+            for (uint64_t w = 0; w < D.n_gram_wins; w++) {
+                const uint64_t kblocks = ((uint64_t)gw[w].n + kGramKBlock - 1) / kGramKBlock;
+                for (uint64_t kb = 0; kb < kblocks; kb++) {
+                    const uint64_t kn = std::min<uint64_t>(kGramKBlock, gw[w].n - kb * kGramKBlock);
+                    for (uint64_t k = 0; k < kn; k++) lists[k].clear();
+                    const uint32_t* rows = bits + 4 * (off[w] + kb * gw[w].width);
+                    for (uint32_t x = 0; x < gw[w].width; x++)
+                        for (uint32_t wd = 0; wd < 4; wd++)
+                            for (uint32_t v = rows[4 * (uint64_t)x + wd]; v; v &= v - 1)
+                                lists[32 * wd + (uint32_t)__builtin_ctz(v)].push_back(gw[w].x0 + x);
+                    for (uint64_t k = 0; k < kn; k++)
+                        take(reinterpret_cast<const uint8_t*>(lists[k].data()), 32, 0, lists[k].size(),
+                             weight(P + D.off_gram_weights, gw[w].c0 + kb * kGramKBlock + k));
+                }
+            }
+        }
         uint64_t wi = 0;  // windows partition the Gram colours in ascending c0
-        for (uint64_t c = 0; c < D.n_gram_colors; c++) {
+        for (uint64_t c = 0; !D.gram_form && c < D.n_gram_colors; c++) {
             while (D.gram_rel_bits && wi + 1 < D.n_gram_wins && c >= gw[wi].c0 + gw[wi].n) wi++;
             take(P + D.off_gram_members, gram_member_bits(D), off[c], off[c + 1] - off[c], weight(P + D.off_gram_weights, c),
                  D.gram_rel_bits ? gw[wi].x0 : 0u);
@@ -1073,8 +1131,9 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     section(d.off_mid_items, sizeof(MidItem) * d.n_mid_items);
     section(d.off_zero_offsets, 8 * (d.n_zero_colors + 1));
     section(d.off_zero_members, MB * d.n_zero_members);
-    section(d.off_gram_offsets, 8 * (d.n_gram_colors + 1));
-    section(d.off_gram_members, (gram_member_bits(d) * d.n_gram_members + 7) / 8 + 8);
+    if (d.gram_form > 1 || (!d.gram_form && d.gram_bitmap_rows) || d.gram_bitmap_rows > lim) return "gram_form";
+    section(d.off_gram_offsets, d.gram_form ? 8 * (d.n_gram_wins + 1) : 8 * (d.n_gram_colors + 1));
+    section(d.off_gram_members, d.gram_form ? 16 * (d.gram_bitmap_rows + kGramTile) : (gram_member_bits(d) * d.n_gram_members + 7) / 8 + 8);
     section(d.off_gram_weights, WB * d.n_gram_colors);
     section(d.off_gram_wins, sizeof(GramWin) * d.n_gram_wins);
     if (!ok) return "section offsets do not match the layout of this build";
@@ -1097,7 +1156,7 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     };
     if (!monotone(d.off_mid_offsets, d.n_mid_colors, d.n_mid_members_padded)) return "mid offsets";
     if (!monotone(d.off_zero_offsets, d.n_zero_colors, d.n_zero_members)) return "zero-weight offsets";
-    if (!monotone(d.off_gram_offsets, d.n_gram_colors, d.n_gram_members)) return "Gram offsets";
+    if (!d.gram_form && !monotone(d.off_gram_offsets, d.n_gram_colors, d.n_gram_members)) return "Gram offsets";
     const MidItem* mi = reinterpret_cast<const MidItem*>(P + d.off_mid_items);
     for (uint64_t i = 0; i < d.n_mid_items; i++) if (mi[i].color >= d.n_mid_colors) return "a mid item names a colour that does not exist";
     const GramWin* gw = reinterpret_cast<const GramWin*>(P + d.off_gram_wins);
@@ -1106,6 +1165,16 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
             gw[i].extent > gw[i].width || (d.gram_rel_bits && gw[i].width > (1ull << d.gram_rel_bits)) ||
             (d.gram_rel_bits && gw[i].c0 != (i ? gw[i - 1].c0 + gw[i - 1].n : 0)))
             return "a Gram window is inconsistent";
+    if (d.gram_form) {  // the windows' bitmaps lie back to back, in window order, and colours are numbered in window order
+        const uint64_t* wr = reinterpret_cast<const uint64_t*>(P + d.off_gram_offsets);
+        uint64_t row = 0, c = 0;
+        for (uint64_t i = 0; i < d.n_gram_wins; i++) {
+            if (wr[i] != row || gw[i].c0 != c) return "Gram bitmap rows do not match the windows";
+            row += gram_win_rows(gw[i]);
+            c += gw[i].n;
+        }
+        if (wr[d.n_gram_wins] != row || row != d.gram_bitmap_rows || c != d.n_gram_colors) return "Gram bitmap rows do not match the windows";
+    }
     if (d.shard_world && (d.shard_rank >= d.shard_world || d.shard_rb > d.shard_re || d.shard_re > N)) return "shard fields";
     return nullptr;
 }

@@ -563,6 +563,60 @@ __global__ void __launch_bounds__(256) k3_emit_csr(unsigned long long c_begin, u
     }
 }
 
+// Gram colours held as bitmaps (IndexDesc::gram_form 1) in spill mode: a warp per colour walks the colour's bit
+// column of its window -- 32 samples per step, members found by ballot -- and for every owned member (row) sweeps the
+// rest of the column for the later members.  O(s * width / 32) warp steps per colour instead of O(s^2 / 32); only the
+// fallback path pays it.
+__global__ void __launch_bounds__(256) k3_emit_bitmap(unsigned long long c_begin, unsigned long long c_end,
+                                                      const GramWin* __restrict__ wins, uint32_t n_wins,
+                                                      const unsigned long long* __restrict__ win_rows,
+                                                      const uint32_t* __restrict__ bits,
+                                                      const void* __restrict__ weights, uint32_t weight_bits,
+                                                      const __grid_constant__ TriGeom G, const SpillSink sink) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned long long warp = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+    for (unsigned long long c = c_begin + warp; c < c_end; c += nwarps) {
+        uint32_t lo = 0, hi = n_wins;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(&wins[mid].c0) <= c) lo = mid; else hi = mid;
+        }
+        const uint32_t x0 = __ldg(&wins[lo].x0), width = __ldg(&wins[lo].width);
+        const uint32_t lc = (uint32_t)(c - __ldg(&wins[lo].c0));
+        // word (lc % 128) / 32 of the 16-byte row of sample x0 in the colour's K-block; the rows follow at 4 words each
+        const uint32_t* col = bits + 4ull * (__ldg(win_rows + lo) + (unsigned long long)(lc / kGramKBlock) * width) + ((lc % kGramKBlock) >> 5);
+        const uint32_t bit = lc & 31u;
+        const unsigned long long w = ldw(weights, weight_bits, c);
+        for (uint32_t a0 = 0; a0 < width; a0 += 32) {
+            uint32_t rows_m = __ballot_sync(KSB_FULL, (__ldg(col + 4ull * (a0 + lane)) >> bit) & 1u);  // width is a multiple of 128
+            while (rows_m) {
+                const uint32_t a = a0 + (uint32_t)__ffs(rows_m) - 1u;
+                rows_m &= rows_m - 1u;
+                const unsigned long long r = SpillSink::row(x0 + a, G);
+                if (r == 0ull) continue;  // warp-uniform
+                for (uint32_t b0 = a & ~31u; b0 < width; b0 += 32) {
+                    const uint32_t b = b0 + lane;
+                    const bool in = b > a && ((__ldg(col + 4ull * b) >> bit) & 1u);
+                    sink.add(in, r, x0 + b, w);
+                }
+            }
+        }
+    }
+}
+
+cudaError_t launch_k3_emit_bitmap(uint64_t c_begin, uint64_t c_end, const GramWin* wins, uint32_t n_wins, const unsigned long long* win_rows,
+                                  const uint32_t* bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb,
+                                  const LaunchCfg& lc) {
+    if (c_end <= c_begin) return cudaSuccess;
+    unsigned long long ctas = (c_end - c_begin + 7) / 8;
+    const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
+    if (ctas > cap) ctas = cap;
+    const SpillSink sink{sb.keys, sb.vals, sb.cursor, sb.shift};
+    k3_emit_bitmap<<<(unsigned)ctas, 256, 0, lc.stream>>>(c_begin, c_end, wins, n_wins, win_rows, bits, weights, weight_bits, g, sink);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned long long* off, const void* members,
                                uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb,
                                const LaunchCfg& lc, const GramWin* wins, uint32_t n_wins) {

@@ -116,6 +116,11 @@ cudaError_t launch_k3_emit_csr(uint64_t c_begin, uint64_t c_end, const unsigned 
                                uint32_t member_bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb, const LaunchCfg& lc,
                                const GramWin* wins = nullptr, uint32_t n_wins = 0);  // wins: members are offsets inside the colour's Gram window
 
+// the same for Gram colours that the blob holds as bitmaps (IndexDesc::gram_form 1): colours [c_begin, c_end)
+cudaError_t launch_k3_emit_bitmap(uint64_t c_begin, uint64_t c_end, const GramWin* wins, uint32_t n_wins, const unsigned long long* win_rows,
+                                  const uint32_t* bits, const void* weights, uint32_t weight_bits, const TriGeom& g, const SpillBuf& sb,
+                                  const LaunchCfg& lc);
+
 cudaError_t launch_k5_sparse(const unsigned long long* keys, const unsigned long long* sums, uint64_t n, uint32_t shift,
                              const uint32_t* totals, const uint32_t* sample_ids, ksb_record* records,
                              unsigned long long* pairs, float* cmax, const LaunchCfg& lc);
@@ -221,6 +226,8 @@ cudaError_t launch_k4_gram_pipe(const GramParams& prm, const TriGeom& g, const L
 cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram_members, uint32_t member_bits,
                             const void* gram_weights, uint32_t weight_bits, const GramUnit* units, uint32_t n_units,
                             uint32_t kpad, uint32_t planes, uint32_t* bits, uint8_t* wq, const LaunchCfg& lc);
+cudaError_t launch_kb_weights(const GramWinDev* wins, uint32_t n_wins, uint32_t kblocks, const void* gram_weights, uint32_t weight_bits,
+                              uint32_t kpad, uint32_t planes, uint8_t* wq, const LaunchCfg& lc);
 cudaError_t launch_k4_gram(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc);
 
 // device handle shared by the translation units of the C-ABI (device_api.cu): validates / selects the ordinal

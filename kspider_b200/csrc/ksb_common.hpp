@@ -127,13 +127,23 @@ struct IndexDesc {
                                 // holds OFFSETS INSIDE THE COLOUR'S WINDOW (member - GramWin::x0) of that width -- a window
                                 // is at most 2^bits samples wide whatever N is, so an index of > 65536 samples ships 2-byte
                                 // Gram members instead of 4-byte ones (cfg4: the blob, i.e. the H2D time, 307 -> 163 MB)
+    uint64_t gram_form;         // 0: the Gram colours are a CSR (off_gram_offsets = u64[n_gram_colors + 1], off_gram_members =
+                                // member lists) and kb_build turns them into bitmaps every step.  1: the blob carries the
+                                // BITMAPS K4 reads -- per window, K-block-major, one 16-byte row (= 128 colours) per sample:
+                                // bits[(win_row[w] + kblock * width + sample - x0) * 4 + word], bit (colour % 32) -- in
+                                // off_gram_members ((gram_bitmap_rows + kGramTile) x 16 B) and off_gram_offsets holds
+                                // win_row = u64[n_gram_wins + 1].  Taken when that is SMALLER than the CSR (dense colours:
+                                // a clade colour of 45 members in a 128-sample window is 16 B instead of 90): cfg4's
+                                // Gram section 147 -> 27 MB, and the step needs no bitmap build.
+    uint64_t gram_bitmap_rows;  // 16-byte rows of all windows' bitmaps (form 1)
     // row-block shard (ksb_index_shard): this blob holds only what the owner of triangle rows
     // [shard_rb, shard_re) needs -- colours with a member in that range, cut down to their members
     // >= shard_rb.  shard_world == 0: the whole index.
     uint64_t shard_world, shard_rank, shard_rb, shard_re;
     uint64_t payload_bytes;
 };
-constexpr uint64_t kIndexMagic = 0x34305844494253ULL | (0x4BULL << 56);
+constexpr uint64_t kIndexMagic = 0x35305844494253ULL | (0x4BULL << 56);
+inline uint64_t gram_win_rows(const GramWin& w) { return (((uint64_t)w.n + kGramKBlock - 1) / kGramKBlock) * w.width; }
 inline uint64_t gram_member_bits(const IndexDesc& d) { return d.gram_rel_bits ? d.gram_rel_bits : d.packed_bits; }
 
 }  // namespace ksb

@@ -135,8 +135,16 @@ def _clade_csr(seed, n_clades, clade, fam, n_core, n_fam, n_noise, w_hi=200, n_s
     return dict(offsets=offsets, members=members, weights=weights, total_ids=ids, total_vals=totals)
 
 
+@pytest.fixture(params=["csr", "bitmap"])
+def gram_form(request, monkeypatch):
+    """Both forms of the Gram section of the blob: member lists that kb_build turns into bitmaps every step, and the
+    ready-made bitmaps (IndexDesc::gram_form; the loader takes the smaller one when nothing is forced)."""
+    monkeypatch.setenv("KSPIDER_GRAM_FORM", request.param)
+    return request.param
+
+
 @pytest.mark.parametrize("mode", ["auto", 2, 16])
-def test_gram_windows_bit_exact_vs_oracle(ksb, gram_env, mode):
+def test_gram_windows_bit_exact_vs_oracle(ksb, gram_env, gram_form, mode):
     """Colours local to clades / families go to small Gram windows (several levels of the window
     grid, windows overlapping by half); the result is the oracle's, bit for bit."""
     gram_env(mode)
@@ -150,7 +158,7 @@ def test_gram_windows_bit_exact_vs_oracle(ksb, gram_env, mode):
 
 
 @pytest.mark.parametrize("world", [2, 5])
-def test_gram_windows_row_blocks_passes_and_chunks(ksb, gram_env, world, monkeypatch):
+def test_gram_windows_row_blocks_passes_and_chunks(ksb, gram_env, gram_form, world, monkeypatch):
     gram_env(2)
     monkeypatch.setenv("KSPIDER_GRAM_CHUNK_MB", "1")  # many chunks, windows cut into sub-windows
     csr = _clade_csr(seed=61, n_clades=9, clade=70, fam=3, n_core=3000, n_fam=40, n_noise=50, w_hi=70000)
@@ -182,7 +190,7 @@ def test_gram_windows_beyond_max_width(ksb, gram_env):
     assert sum(int(v) for v in rec["shared_kmers"]) == sum(int(x) * int(k * (k - 1) // 2) for x, k in zip(w, sizes))
 
 
-def test_gram_pipelined_upload_pieces(ksb, gram_env, monkeypatch):
+def test_gram_pipelined_upload_pieces(ksb, gram_env, gram_form, monkeypatch):
     """ksb_pairwise copies the Gram members in one piece per K4 chunk (pieces under 4 MB ride with the
     next one) and every chunk's bitmap build waits for its own piece: several chunks and several pieces
     here, result bit-exact; the resident path (upload + run) must agree with it."""
@@ -210,14 +218,15 @@ def test_gram_pipelined_upload_pieces(ksb, gram_env, monkeypatch):
     assert_records_equal(dev.run_all_passes().records(), want)
 
 
-@pytest.mark.parametrize("mbits,rel", [("16", "0"), ("16", "12"), ("16", "10"), ("32", None), ("32", "12"), ("32", "0")])
+@pytest.mark.parametrize("mbits,rel", [("16", "0"), ("16", "12"), ("16", "10"), ("32", None), ("32", "12"), ("32", "0"), ("16", "bitmap"), ("32", "bitmap")])
 def test_gram_members_relative_to_their_window(ksb, gram_env, monkeypatch, mbits, rel):
     """Gram members shipped as offsets inside their window (IndexDesc::gram_rel_bits; the default for indexes whose ids
     need 32 bits is 16-bit offsets): kb_build, the row-block shards and the spill emitter (k3_emit_csr) decode every
     encoding to the same rows, bit for bit the oracle's."""
     gram_env(16)
     monkeypatch.setenv("KSPIDER_MEMBER_BITS", mbits)
-    if rel is None:
+    monkeypatch.setenv("KSPIDER_GRAM_FORM", "bitmap" if rel == "bitmap" else "csr")  # "bitmap": no member lists at all
+    if rel in (None, "bitmap"):
         monkeypatch.delenv("KSPIDER_GRAM_REL", raising=False)
     else:
         monkeypatch.setenv("KSPIDER_GRAM_REL", rel)

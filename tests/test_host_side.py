@@ -369,9 +369,14 @@ def test_gram_members_stored_relative_to_their_window(built_lib, monkeypatch):
                weights=rng.integers(1, 200, size=nc).astype(np.uint32), total_ids=ids, total_vals=np.full(n, 10 ** 6, dtype=np.uint32))
     monkeypatch.setenv("KSPIDER_GRAM", "16")
     shards, sizes = {}, {}
-    for mbits, rel in (("16", "0"), ("16", "12"), ("16", "10"), ("32", None), ("32", "0"), ("32", "12")):
+    for mbits, rel in (("16", "0"), ("16", "12"), ("16", "10"), ("32", None), ("32", "0"), ("32", "12"), ("16", "bitmap"), ("32", "auto")):
         monkeypatch.setenv("KSPIDER_MEMBER_BITS", mbits)
-        if rel is None:
+        # "bitmap" / "auto": the Gram colours travel as the bitmaps K4 reads (IndexDesc::gram_form 1) -- what the loader
+        # picks by itself for colours this dense; the other cases pin the CSR form and vary its member encoding
+        monkeypatch.delenv("KSPIDER_GRAM_FORM", raising=False)
+        if rel != "auto":
+            monkeypatch.setenv("KSPIDER_GRAM_FORM", "bitmap" if rel == "bitmap" else "csr")
+        if rel in (None, "bitmap", "auto"):
             monkeypatch.delenv("KSPIDER_GRAM_REL", raising=False)
         else:
             monkeypatch.setenv("KSPIDER_GRAM_REL", rel)
@@ -383,6 +388,7 @@ def test_gram_members_stored_relative_to_their_window(built_lib, monkeypatch):
         # the shards are built under ONE setting, from the parents' differently encoded sections
         monkeypatch.setenv("KSPIDER_MEMBER_BITS", "16")
         monkeypatch.setenv("KSPIDER_GRAM_REL", "0")
+        monkeypatch.setenv("KSPIDER_GRAM_FORM", "csr")
         shards[(mbits, rel)] = []
         for r in range(2):
             sh = idx.shard(r, 2, host_threads=2)   # kept alive while its payload view is copied
@@ -397,3 +403,7 @@ def test_gram_members_stored_relative_to_their_window(built_lib, monkeypatch):
     assert sizes[("16", "12")] - sizes[("16", "10")] >= gm // 4 - 4096          # every window here is at most 1024 samples wide
     assert sizes[("32", "0")] - sizes[("32", None)] >= 2 * gm - 4096          # default: 32 -> 16 bits when ids need 32
     assert sizes[("32", None)] - sizes[("32", "12")] >= gm // 2 - 4096
+    # bitmaps: about 300 colours x 768 samples + 500 x 128 + 200 x 896 bits in K-blocks of 128 colours (~80 kB) against
+    # 153 000 members and 1 000 offsets: smaller than the narrowest CSR, and what the loader picks by itself
+    assert sizes[("16", "10")] - sizes[("16", "bitmap")] >= 100_000
+    assert sizes[("32", "auto")] < sizes[("32", "12")] and sizes[("32", "auto")] - sizes[("16", "bitmap")] < 16384
