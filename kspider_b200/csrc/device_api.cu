@@ -2,6 +2,7 @@
 // accumulation, post-pass, clustering.  No CPU fallback: every entry point here needs a CUDA device.
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -47,9 +48,14 @@ struct ksb_gram_chunk {
 struct ksb_gram_plan {
     bool built = false;
     std::vector<ksb_gram_chunk> chunks;
-    ksb::GramWinDev* d_wins = nullptr;
-    ksb::GramItem* d_items = nullptr;
-    ksb::GramUnit* d_units = nullptr;
+    ksb::GramWinDev* d_wins = nullptr;   // the three tables are one device allocation (d_tables), filled by ONE copy kernel
+    ksb::GramItem* d_items = nullptr;    // from a pinned staging buffer: a cudaMemcpy from the vectors would queue on the
+    ksb::GramUnit* d_units = nullptr;    // copy engine BEHIND the blob that is already on its way (ksb_pairwise)
+    void* d_tables = nullptr;
+    void* h_tables = nullptr;            // pinned, kept until the device handle is released
+    uint64_t h_tables_bytes = 0;
+    cudaEvent_t ev_tables = nullptr;     // the copy kernel has run (recorded on the handle's stream)
+    bool tables_ordered = false;         // the stream the step runs on has been made to wait for it
 };
 
 struct ksb_device {
@@ -70,7 +76,8 @@ struct ksb_device {
     struct k1_piece { cudaEvent_t ev; unsigned long long task_begin, task_end; };
     std::vector<k1_piece> k1_pieces;       // K1 task ranges in the order their classes are copied
     std::vector<cudaEvent_t> gram_ev;      // per K4 chunk of pass 0: the copy piece holding its members has landed
-    std::vector<cudaEvent_t> gram_ev_own;  // the distinct events behind gram_ev (several chunks may share a piece)
+    std::vector<cudaEvent_t> gram_ev_own;  // the events of the pieces the Gram section is copied in
+    std::vector<uint64_t> gram_piece_end;  // payload offset each of those pieces ends at
     unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
     uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
     uint64_t tri_cells_alloc = 0;
@@ -78,8 +85,8 @@ struct ksb_device {
     uint32_t cur_pass = 0;
     uint64_t row_begin = 0, row_end = 0, owned_cells = 0, owned_updates = 0;
     std::vector<uint64_t> bandstart;       // host copy, [N+1]: first cell of row i in the banded accumulator
-    unsigned long long* d_bandstart = nullptr;  // [N+1]
-    unsigned long long* d_rowbase = nullptr;    // [N]  bandstart[i] - band_lo[i]
+    const unsigned long long* d_bandstart = nullptr;  // [N+1]   both inside the device payload (IndexDesc::off_bandstart / off_rowbase)
+    const unsigned long long* d_rowbase = nullptr;    // [N]  bandstart[i] - band_lo[i]
     ksb::K1Params k1;
     ksb_timings t;
     uint64_t launches = 0;
@@ -262,18 +269,26 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     const uint64_t N = d->desc.n_samples;
     const uint64_t U = d->desc.n_updates;
     const int W = std::max(1, d->world);
-    std::vector<uint64_t> cut(W + 1, N);
-    row_cuts(row_updates, N, U, W, cut.data());
-    d->row_begin = cut[d->rank];
-    d->row_end = cut[d->rank + 1];
-    if (d->rank == W - 1) d->row_end = N;
     if (d->desc.shard_world) {  // a row-block shard owns the rows it was cut for, whatever opts say
         d->row_begin = d->desc.shard_rb;
         d->row_end = d->desc.shard_re;
+    } else if (W == 1) {
+        d->row_begin = 0;
+        d->row_end = N;
+    } else {
+        std::vector<uint64_t> cut(W + 1, N);
+        row_cuts(row_updates, N, U, W, cut.data());
+        d->row_begin = cut[d->rank];
+        d->row_end = cut[d->rank + 1];
+        if (d->rank == W - 1) d->row_end = N;
     }
     d->owned_cells = rowstart(d, d->row_end) - rowstart(d, d->row_begin);
-    d->owned_updates = 0;
-    for (uint64_t i = d->row_begin; i < d->row_end; i++) d->owned_updates += row_updates[i];
+    if (d->desc.shard_world || W == 1) {
+        d->owned_updates = U;  // a shard's descriptor counts the updates of its own rows
+    } else {
+        d->owned_updates = 0;
+        for (uint64_t i = d->row_begin; i < d->row_end; i++) d->owned_updates += row_updates[i];
+    }
 
     // bytes per cell: 8 (u64) + 1/8 (touched bit) when needed
     const bool need_touch = d->desc.n_zero_colors != 0;
@@ -282,6 +297,10 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     if (max_cells < N) max_cells = N;  // at least one row
     d->passes.clear();
     uint64_t rb = d->row_begin;
+    if (rb < d->row_end && d->owned_cells <= max_cells) {  // the whole block in one pass: no walk over the rows
+        d->passes.push_back(ksb_pass{rb, d->row_end, rowstart(d, rb), d->owned_cells, d->owned_updates});
+        rb = d->row_end;
+    }
     while (rb < d->row_end) {
         uint64_t re = rb, cells = 0, upd = 0;
         while (re < d->row_end) {
@@ -301,8 +320,25 @@ static int plan_rows(ksb_device* d, const uint64_t* row_updates, uint64_t budget
     return KSB_OK;
 }
 
-static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint32_t* band_lo, const uint32_t* band_hi,
-                         const ksb_opts* opts) {
+// KSPIDER_SETUP_TIMERS=1: host wall clock of the set-up phases of a device handle on stderr (where the end-to-end call
+// spends its time before the first kernel)
+struct SetupTrace {
+    bool on;
+    std::chrono::steady_clock::time_point tp;
+    SetupTrace() : tp(std::chrono::steady_clock::now()) {
+        static const bool env = [] { const char* v = std::getenv("KSPIDER_SETUP_TIMERS"); return v && v[0] == '1'; }();
+        on = env;
+    }
+    void lap(const char* what) {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[ksb setup] %-28s %8.1f us\n", what, std::chrono::duration<double, std::micro>(now - tp).count());
+        tp = std::chrono::steady_clock::now();
+    }
+};
+
+static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint64_t* bandstart, const ksb_opts* opts) {
+    SetupTrace tr;
     if (d->desc.magic != kIndexMagic) { set_error("descriptor has a wrong magic (ABI mismatch?)"); return KSB_ERR_ARG; }
     if (d->desc.member_bits != 16 && d->desc.member_bits != 32) { set_error("descriptor: member_bits must be 16 or 32"); return KSB_ERR_ARG; }
     if (d->desc.packed_bits != 10 && d->desc.packed_bits != 12 && d->desc.packed_bits != 16 && d->desc.packed_bits != 32) { set_error("descriptor: packed_bits must be 10, 12, 16 or 32"); return KSB_ERR_ARG; }
@@ -322,23 +358,18 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
         const bool rows = opts && opts->want_records != 0;
         budget = (uint64_t)((double)fr * 0.8 * (rows ? 8.0 / 52.0 : 1.0));
     }
-    {   // banded accumulator: prefix of the band lengths, and the per-row base the kernels add columns to
+    tr.lap("  streams, events, mem info");
+    {   // banded accumulator: the prefix of the band lengths and the per-row base the kernels add columns to are sections of the blob
         const uint64_t N = d->desc.n_samples;
-        d->bandstart.assign(N + 1, 0);
-        std::vector<unsigned long long> rowbase(N ? N : 1, 0);
-        for (uint64_t i = 0; i < N; i++) {
-            if (band_hi[i] < band_lo[i] || band_hi[i] > N) { set_error("corrupt row band at %llu", (unsigned long long)i); return KSB_ERR_ARG; }
-            d->bandstart[i + 1] = d->bandstart[i] + (band_hi[i] - band_lo[i]);
-            rowbase[i] = d->bandstart[i] - band_lo[i];  // wraps for rows whose band starts past their first cells; used modulo 2^64
-        }
-        KSB_CUDA(cudaMallocAsync(&d->d_bandstart, 8 * (N + 1), d->stream));
-        KSB_CUDA(cudaMallocAsync(&d->d_rowbase, 8 * (N ? N : 1), d->stream));
-        KSB_CUDA(cudaMemcpyAsync(d->d_bandstart, d->bandstart.data(), 8 * (N + 1), cudaMemcpyHostToDevice, d->stream));
-        KSB_CUDA(cudaMemcpyAsync(d->d_rowbase, rowbase.data(), 8 * (N ? N : 1), cudaMemcpyHostToDevice, d->stream));
-        KSB_CUDA(cudaStreamSynchronize(d->stream));  // rowbase is a local
+        d->bandstart.assign(bandstart, bandstart + N + 1);
+        if (N && (d->bandstart[0] != 0 || d->bandstart[N] != d->desc.band_cells)) { set_error("corrupt row band tables"); return KSB_ERR_ARG; }
+        d->d_bandstart = reinterpret_cast<const unsigned long long*>(d->d_payload + d->desc.off_bandstart);
+        d->d_rowbase = reinterpret_cast<const unsigned long long*>(d->d_payload + d->desc.off_rowbase);
     }
+    tr.lap("  band tables");
     int rc = plan_rows(d, row_updates, budget);
     if (rc) return rc;
+    tr.lap("  plan_rows");
     d->budget = budget;
     d->spill = d->spill_mode == 1 || (d->spill_mode == 0 && d->passes.size() > 16);
     if (d->spill) {  // K3: one pseudo-pass over all owned rows, no dense block
@@ -357,7 +388,9 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint3
     KSB_CUDA(scan_block_counts(nullptr, &d->scan_tmp_bytes, d->d_block_counts, d->d_block_counts + d->post_blocks_alloc,
                                d->post_blocks_alloc, d->stream));
     KSB_CUDA(cudaMallocAsync(&d->d_scan_tmp, std::max<size_t>(d->scan_tmp_bytes, 256), d->stream));
+    tr.lap("  accumulator allocs");
     build_k1(d);
+    tr.lap("  build_k1");
     d->g_planes = d->desc.gram_planes <= 1 ? 1 : (d->desc.gram_planes == 2 ? 2 : 4);
     d->gplan.assign(d->passes.size(), ksb_gram_plan());
     return KSB_OK;
@@ -393,6 +426,40 @@ static void pinned_release(void* p, uint64_t bytes) {
     if (drop) cudaFreeHost(drop);
 }
 
+// the same for the K4 plan tables of a device handle (a few hundred kB; its own slot so that the records' buffer and
+// the tables do not evict each other)
+static void* g_plan_pin_ptr = nullptr;
+static uint64_t g_plan_pin_bytes = 0;
+static cudaError_t plan_pinned_acquire(void** out, uint64_t* bytes) {
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        if (g_plan_pin_ptr && g_plan_pin_bytes >= *bytes) {
+            *out = g_plan_pin_ptr;
+            *bytes = g_plan_pin_bytes;
+            g_plan_pin_ptr = nullptr;
+            g_plan_pin_bytes = 0;
+            return cudaSuccess;
+        }
+    }
+    *bytes = std::max<uint64_t>(*bytes + *bytes / 4, 1ull << 20);
+    return cudaMallocHost(out, *bytes);
+}
+static void plan_pinned_release(void* p, uint64_t bytes) {
+    void* drop = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_pin_mu);
+        if (bytes > g_plan_pin_bytes) { drop = g_plan_pin_ptr; g_plan_pin_ptr = p; g_plan_pin_bytes = bytes; }
+        else drop = p;
+    }
+    if (drop) cudaFreeHost(drop);
+}
+
+// pinned host memory -> device memory on the SMs (16 bytes per thread and step): PCIe reads that interleave with a DMA
+// copy in flight instead of waiting for it in the copy engine's queue
+__global__ void __launch_bounds__(256) k_host_to_device(uint4* __restrict__ dst, const uint4* __restrict__ src, uint32_t n16) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
 }  // namespace ksb
 
 using namespace ksb;
@@ -421,13 +488,8 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_touched) cudaFreeAsync(d->d_touched, fs);
     if (d->d_block_counts) cudaFreeAsync(d->d_block_counts, fs);
     if (d->d_scan_tmp) cudaFreeAsync(d->d_scan_tmp, fs);
-    if (d->d_bandstart) cudaFreeAsync(d->d_bandstart, fs);
-    if (d->d_rowbase) cudaFreeAsync(d->d_rowbase, fs);
-    for (ksb_gram_plan& gp : d->gplan) {
-        if (gp.d_wins) cudaFreeAsync(gp.d_wins, fs);
-        if (gp.d_items) cudaFreeAsync(gp.d_items, fs);
-        if (gp.d_units) cudaFreeAsync(gp.d_units, fs);
-    }
+    for (ksb_gram_plan& gp : d->gplan)
+        if (gp.d_tables) cudaFreeAsync(gp.d_tables, fs);
     if (d->d_gbits) cudaFreeAsync(d->d_gbits, fs);
     if (d->d_gwq) cudaFreeAsync(d->d_gwq, fs);
     if (d->d_parent) cudaFreeAsync(d->d_parent, fs);
@@ -435,6 +497,10 @@ void ksb_device_free(ksb_device* d) {
     if (d->d_edges) cudaFreeAsync(d->d_edges, fs);
     if (fs) cudaStreamSynchronize(fs);
     if (d->h_stage) pinned_release(d->h_stage, d->h_stage_bytes);
+    for (ksb_gram_plan& gp : d->gplan) {
+        if (gp.h_tables) plan_pinned_release(gp.h_tables, gp.h_tables_bytes);
+        if (gp.ev_tables) unpool_event(d->device, gp.ev_tables, false);
+    }
     if (d->cl_graph) cudaGraphExecDestroy(d->cl_graph);
     for (auto& e : d->ev) unpool_event(d->device, e);
     if (d->stream) { cudaStreamSynchronize(d->stream); unpool_stream(d->device, d->stream); }
@@ -459,12 +525,13 @@ static int opts_common(ksb_device* d, const ksb_opts* opts) {
     return KSB_OK;
 }
 
-// Enqueues the blob copy in pieces on the copy stream.  Phase A (before the device is planned, so that
-// the planning overlaps the copy): head (totals, ids, bands), then the mid, zero and Gram offset /
-// weight / window sections.  Phase B: the Gram members in one piece per K4 chunk (K4's bitmap build
-// starts first), then the small-colour classes from the largest size down in a few chunks -- the
-// order K1 consumes them -- each followed by an event.
-static int enqueue_copy_head(ksb_device* d, const ksb_index* ix) {
+// Enqueues the copy of the WHOLE blob on the copy stream, in the order the kernels consume it, before the device is
+// planned -- planning (row passes, K4 chunks and items) then runs under the copy instead of in front of it.
+// Head (totals, ids, bands, row tables), the mid / zero sections and the Gram offsets, weights and windows; then the
+// Gram section (members or bitmaps: what K4 waits for) in pieces of <= 4 MB, each followed by an event -- once the K4
+// chunks of the first pass are known (map_gram_pieces) a chunk waits for the piece its last byte lies in --; then the
+// small-colour classes from the largest size down in a few chunks, the order K1 consumes them, an event behind each.
+static int enqueue_copy_all(ksb_device* d, const ksb_index* ix) {
     const IndexDesc& D = d->desc;
     KSB_CUDA(pool_stream(d->device, &d->copy_stream));
     for (auto& e : d->ev_copy) KSB_CUDA(pool_event(d->device, &e));
@@ -483,40 +550,17 @@ static int enqueue_copy_head(ksb_device* d, const ksb_index* ix) {
     KSB_CUDA(copy(D.off_mid_offsets, D.off_gram_members));
     KSB_CUDA(copy(D.off_gram_weights, D.payload_bytes));
     KSB_CUDA(cudaEventRecord(d->ev_copy[2], cs));
-    return KSB_OK;
-}
-
-static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
-    const IndexDesc& D = d->desc;
-    cudaStream_t cs = d->copy_stream;
-    auto copy = [&](uint64_t b, uint64_t e) -> cudaError_t {
-        return e > b ? cudaMemcpyAsync(d->d_payload + b, ix->payload + b, e - b, cudaMemcpyHostToDevice, cs) : cudaSuccess;
-    };
-    // Gram member section (the bulk of the tail) in one piece per K4 chunk of pass 0, so that the bitmap
-    // build of chunk k starts when ITS colours have landed instead of after the whole section
-    const ksb_gram_plan* plan = (D.n_gram_colors && !d->gplan.empty() && d->gplan[0].built && !d->gplan[0].chunks.empty()) ? &d->gplan[0] : nullptr;
-    if (!plan) KSB_CUDA(copy(D.off_gram_members, D.off_gram_weights));  // no K4 launch in pass 0: nobody waits for it
-    if (plan) {
-        const uint64_t* goff = reinterpret_cast<const uint64_t*>(ix->payload + D.off_gram_offsets);
-        const size_t nck = plan->chunks.size();
-        d->gram_ev.assign(nck, nullptr);
-        uint64_t done = D.off_gram_members;
-        size_t first = 0;
-        for (size_t k = 0; k < nck; k++) {
-            const ksb_gram_chunk& c = plan->chunks[k];
-            uint64_t end = D.gram_form ? D.off_gram_members + (16 * (c.blob_row0 + c.bits_rows + kGramTile) + 255) / 256 * 256
-                                       : D.off_gram_members + ((gram_member_bits(D) * goff[c.c_begin + c.n_colors] + 7) / 8 + 64 + 255) / 256 * 256;
-            if (k + 1 == nck || end > D.off_gram_weights) end = D.off_gram_weights;
-            if (end - done < (4ull << 20) && k + 1 < nck) continue;  // too small for a piece of its own: rides with the next
-            KSB_CUDA(copy(done, end));
-            done = end;
-            cudaEvent_t e = nullptr;
-            KSB_CUDA(pool_event(d->device, &e, false));
-            d->gram_ev_own.push_back(e);
-            KSB_CUDA(cudaEventRecord(e, cs));
-            for (; first <= k; first++) d->gram_ev[first] = e;
-        }
+    const uint64_t piece = 4ull << 20;
+    for (uint64_t b = D.off_gram_members; b < D.off_gram_weights; b += piece) {
+        const uint64_t e = std::min<uint64_t>(b + piece, D.off_gram_weights);
+        KSB_CUDA(copy(b, e));
+        cudaEvent_t ev = nullptr;
+        KSB_CUDA(pool_event(d->device, &ev, false));
+        d->gram_ev_own.push_back(ev);
+        d->gram_piece_end.push_back(e);
+        KSB_CUDA(cudaEventRecord(ev, cs));
     }
+    build_k1(d);  // depends on the descriptor only
     const uint64_t mbits = D.packed_bits, wbytes = D.weight_bits / 8;
     const uint64_t small_bytes = mbits * D.n_small_members / 8 + wbytes * D.n_small_colors;
     const uint64_t chunk = std::max<uint64_t>(8ull << 20, small_bytes / 6);
@@ -543,6 +587,24 @@ static int enqueue_pipelined_copy(ksb_device* d, const ksb_index* ix) {
     return KSB_OK;
 }
 
+// the K4 chunks of pass 0 -> the copy piece whose arrival completes their part of the Gram section
+static void map_gram_pieces(ksb_device* d, const ksb_index* ix) {
+    const IndexDesc& D = d->desc;
+    const ksb_gram_plan* plan = (D.n_gram_colors && !d->gplan.empty() && d->gplan[0].built && !d->gplan[0].chunks.empty()) ? &d->gplan[0] : nullptr;
+    if (!plan || d->gram_piece_end.empty()) return;  // no K4 launch in pass 0: nobody waits for a piece
+    const uint64_t* goff = reinterpret_cast<const uint64_t*>(ix->payload + D.off_gram_offsets);
+    const size_t nck = plan->chunks.size();
+    d->gram_ev.assign(nck, nullptr);
+    for (size_t k = 0; k < nck; k++) {
+        const ksb_gram_chunk& c = plan->chunks[k];
+        uint64_t end = D.gram_form ? D.off_gram_members + 16 * (c.blob_row0 + c.bits_rows + kGramTile)
+                                   : D.off_gram_members + (gram_member_bits(D) * goff[c.c_begin + c.n_colors] + 7) / 8 + 64;
+        end = std::min<uint64_t>(end, D.off_gram_weights);
+        const size_t pi = std::lower_bound(d->gram_piece_end.begin(), d->gram_piece_end.end(), end) - d->gram_piece_end.begin();
+        d->gram_ev[k] = d->gram_ev_own[std::min(pi, d->gram_ev_own.size() - 1)];
+    }
+}
+
 static int upload_impl(const ksb_index* ix, const ksb_opts* opts, ksb_device** out, bool pipelined) {
     if (!ix || !out) { set_error("ksb_upload: null argument"); return KSB_ERR_ARG; }
     *out = nullptr;
@@ -561,26 +623,37 @@ static int upload_impl(const ksb_index* ix, const ksb_opts* opts, ksb_device** o
     if (e == cudaSuccess) e = cudaMallocAsync(&d->d_payload, d->desc.payload_bytes, d->stream);
     if (e != cudaSuccess) { set_error("cudaMalloc(%llu) for the index: %s", (unsigned long long)d->desc.payload_bytes, cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
     d->own_payload = true;
+    SetupTrace tr;
+    auto lap = [&](const char* what) { tr.lap(what); };
     const bool pipe = pipelined && ix->pinned;
     if (pipe) {
-        rc = enqueue_copy_head(d, ix);
+        rc = enqueue_copy_all(d, ix);
         if (rc) return fail(rc);
     }
+    lap("copy enqueue");
     const uint64_t* row_updates = reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_row_updates);
     if (d->desc.n_gram_wins) {
         const GramWin* gw = reinterpret_cast<const GramWin*>(ix->payload + d->desc.off_gram_wins);
         d->gwins.assign(gw, gw + d->desc.n_gram_wins);
     }
-    rc = finish_device(d, row_updates, reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_lo),
-                       reinterpret_cast<const uint32_t*>(ix->payload + d->desc.off_band_hi), opts);
+    rc = finish_device(d, row_updates, reinterpret_cast<const uint64_t*>(ix->payload + d->desc.off_bandstart), opts);
     if (rc) return fail(rc);
+    lap("finish_device");
     if (pipe && !d->spill) {
         if (d->desc.n_gram_colors && !d->passes.empty() && d->passes[0].cells) {
             rc = plan_gram(d, 0);  // the copy is cut along the K4 chunks of the first pass
             if (rc) return fail(rc);
         }
-        rc = enqueue_pipelined_copy(d, ix);
-        if (rc) return fail(rc);
+        lap("plan_gram");
+        map_gram_pieces(d, ix);
+        *out = d;
+        return KSB_OK;
+    }
+    if (pipe) {  // the spill path takes the blob whole: wait for the copy that is already under way
+        e = cudaStreamSynchronize(d->copy_stream);
+        if (e != cudaSuccess) { set_error("index H2D copy: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); return fail(KSB_ERR_CUDA); }
+        d->t.h2d_ms = ev_ms(d->ev_copy[0], d->ev_copy[3]);
+        d->copy_pending = false;
         *out = d;
         return KSB_OK;
     }
@@ -619,10 +692,9 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
         cudaError_t e = cudaMemcpy(row_updates.data(), d->d_payload + d->desc.off_row_updates, 8 * d->desc.n_samples, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { set_error("reading row histogram from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
     }
-    std::vector<uint32_t> blo(d->desc.n_samples), bhi(d->desc.n_samples);
+    std::vector<uint64_t> bst(d->desc.n_samples + 1, 0);
     if (d->desc.n_samples) {
-        cudaError_t e = cudaMemcpy(blo.data(), d->d_payload + d->desc.off_band_lo, 4 * d->desc.n_samples, cudaMemcpyDeviceToHost);
-        if (e == cudaSuccess) e = cudaMemcpy(bhi.data(), d->d_payload + d->desc.off_band_hi, 4 * d->desc.n_samples, cudaMemcpyDeviceToHost);
+        cudaError_t e = cudaMemcpy(bst.data(), d->d_payload + d->desc.off_bandstart, 8 * (d->desc.n_samples + 1), cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { set_error("reading row bands from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
     }
     if (d->desc.n_gram_wins) {
@@ -631,7 +703,7 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
         if (e != cudaSuccess) { set_error("reading Gram windows from the device payload: %s", cudaGetErrorString(e)); (void)cudaGetLastError(); ksb_device_free(d); return KSB_ERR_CUDA; }
 
     }
-    rc = finish_device(d, row_updates.data(), blo.data(), bhi.data(), opts);
+    rc = finish_device(d, row_updates.data(), bst.data(), opts);
     if (rc) { ksb_device_free(d); return rc; }
     *out = d;
     return KSB_OK;
@@ -808,13 +880,28 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
             KSB_CUDA(cudaMallocAsync(&d->d_gwq, need_wq, d->stream));
             d->gwq_bytes = need_wq;
         }
-        KSB_CUDA(cudaMallocAsync(&plan.d_wins, sizeof(GramWinDev) * wins.size(), d->stream));
-        KSB_CUDA(cudaMallocAsync(&plan.d_items, sizeof(GramItem) * items.size(), d->stream));
-        KSB_CUDA(cudaMemcpyAsync(plan.d_wins, wins.data(), sizeof(GramWinDev) * wins.size(), cudaMemcpyHostToDevice, d->stream));
-        KSB_CUDA(cudaMemcpyAsync(plan.d_items, items.data(), sizeof(GramItem) * items.size(), cudaMemcpyHostToDevice, d->stream));
-        KSB_CUDA(cudaMallocAsync(&plan.d_units, sizeof(GramUnit) * std::max<size_t>(units.size(), 1), d->stream));
-        KSB_CUDA(cudaMemcpyAsync(plan.d_units, units.data(), sizeof(GramUnit) * units.size(), cudaMemcpyHostToDevice, d->stream));
-        KSB_CUDA(cudaStreamSynchronize(d->stream));  // wins / items are locals
+        auto up256 = [](uint64_t b) { return (b + 255) / 256 * 256; };
+        const uint64_t o_items = up256(sizeof(GramWinDev) * wins.size());
+        const uint64_t o_units = o_items + up256(sizeof(GramItem) * items.size());
+        const uint64_t total = o_units + up256(sizeof(GramUnit) * std::max<size_t>(units.size(), 1));
+        plan.h_tables_bytes = total;
+        KSB_CUDA(plan_pinned_acquire(&plan.h_tables, &plan.h_tables_bytes));
+        uint8_t* H = static_cast<uint8_t*>(plan.h_tables);
+        std::memcpy(H, wins.data(), sizeof(GramWinDev) * wins.size());
+        std::memcpy(H + o_items, items.data(), sizeof(GramItem) * items.size());
+        if (!units.empty()) std::memcpy(H + o_units, units.data(), sizeof(GramUnit) * units.size());
+        KSB_CUDA(cudaMallocAsync(&plan.d_tables, total, d->stream));
+        uint8_t* T = static_cast<uint8_t*>(plan.d_tables);
+        plan.d_wins = reinterpret_cast<GramWinDev*>(T);
+        plan.d_items = reinterpret_cast<GramItem*>(T + o_items);
+        plan.d_units = reinterpret_cast<GramUnit*>(T + o_units);
+        const uint32_t n16 = (uint32_t)(total / 16);
+        k_host_to_device<<<std::min<uint32_t>((n16 + 255) / 256, 4u * (uint32_t)d->sms), 256, 0, d->stream>>>(
+            reinterpret_cast<uint4*>(T), reinterpret_cast<const uint4*>(H), n16);
+        KSB_CUDA(cudaGetLastError());
+        KSB_CUDA(pool_event(d->device, &plan.ev_tables, false));
+        KSB_CUDA(cudaEventRecord(plan.ev_tables, d->stream));
+        d->launches++;
     }
     plan.built = true;
     return KSB_OK;
@@ -828,7 +915,14 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
     using namespace ksb;
     const int prc = plan_gram(d, d->cur_pass);
     if (prc) return prc;
-    const ksb_gram_plan& plan = d->gplan[d->cur_pass];
+    ksb_gram_plan& plan = d->gplan[d->cur_pass];
+    if (!plan.tables_ordered && plan.ev_tables) {
+        // first use of the plan: its tables were written by a kernel on the handle's own stream.  Never reached inside a
+        // graph capture: cluster_prepare plans and orders every pass before a capture starts.
+        KSB_CUDA(cudaStreamWaitEvent(st_build, plan.ev_tables, 0));
+        if (st != st_build) KSB_CUDA(cudaStreamWaitEvent(st, plan.ev_tables, 0));
+        plan.tables_ordered = true;
+    }
     const IndexDesc& D = d->desc;
     const uint8_t* P = d->d_payload;
     const unsigned long long* goff = reinterpret_cast<const unsigned long long*>(P + D.off_gram_offsets);
@@ -1402,7 +1496,12 @@ static int cluster_prepare(ksb_device* d, cudaStream_t st) {
     }
     if (d->desc.n_gram_colors)
         for (uint32_t p = 0; p < d->passes.size(); p++)
-            if (d->passes[p].cells) { const int rc = plan_gram(d, p); if (rc) return rc; }  // allocates and copies: never inside a capture
+            if (d->passes[p].cells) {  // allocates and copies: never inside a capture
+                const int rc = plan_gram(d, p);
+                if (rc) return rc;
+                ksb_gram_plan& gp = d->gplan[p];
+                if (!gp.tables_ordered && gp.ev_tables) { KSB_CUDA(cudaStreamWaitEvent(st, gp.ev_tables, 0)); gp.tables_ordered = true; }
+            }
     return KSB_OK;
 }
 

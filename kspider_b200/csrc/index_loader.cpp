@@ -487,6 +487,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
     d.off_row_updates = section(8 * N);
     d.off_band_lo = section(4 * N);
     d.off_band_hi = section(4 * N);
+    d.off_bandstart = section(8 * (N + 1));
+    d.off_rowbase = section(8 * N);
     d.off_small_members = section(packed_bytes(d.n_small_members));
     d.off_small_weights = section(WB * d.n_small_colors);
     d.off_mid_offsets = section(8 * (d.n_mid_colors + 1));
@@ -721,6 +723,15 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         band_lo[i] = lo;
         band_hi[i] = hi;
         d.band_cells += hi - lo;
+    }
+    {   // the accumulator's row tables travel with the blob: a device handle neither computes nor copies them separately
+        uint64_t* bandstart = reinterpret_cast<uint64_t*>(P + d.off_bandstart);
+        uint64_t* rowbase = reinterpret_cast<uint64_t*>(P + d.off_rowbase);
+        bandstart[0] = 0;
+        for (uint64_t i = 0; i < N; i++) {
+            bandstart[i + 1] = bandstart[i] + (band_hi[i] - band_lo[i]);
+            rowbase[i] = bandstart[i] - band_lo[i];  // wraps for rows whose band starts past their first cells; used modulo 2^64
+        }
     }
     ix->totals_file_ids = std::move(raw.total_ids);
     ix->totals_file_vals = std::move(raw.total_vals);
@@ -1122,6 +1133,8 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     section(d.off_row_updates, 8 * N);
     section(d.off_band_lo, 4 * N);
     section(d.off_band_hi, 4 * N);
+    section(d.off_bandstart, 8 * (N + 1));
+    section(d.off_rowbase, 8 * N);
     section(d.off_small_members, packed_bytes(d.n_small_members));
     section(d.off_small_weights, WB * d.n_small_colors);
     section(d.off_mid_offsets, 8 * (d.n_mid_colors + 1));
@@ -1138,6 +1151,16 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     section(d.off_gram_wins, sizeof(GramWin) * d.n_gram_wins);
     if (!ok) return "section offsets do not match the layout of this build";
     if (std::max<uint64_t>(p, 256) != d.payload_bytes || d.payload_bytes != payload_bytes) return "payload size does not match the layout";
+    {   // row bands and the tables derived from them
+        const uint32_t* blo = reinterpret_cast<const uint32_t*>(P + d.off_band_lo);
+        const uint32_t* bhi = reinterpret_cast<const uint32_t*>(P + d.off_band_hi);
+        const uint64_t* bs = reinterpret_cast<const uint64_t*>(P + d.off_bandstart);
+        const uint64_t* rb = reinterpret_cast<const uint64_t*>(P + d.off_rowbase);
+        if (N && bs[0] != 0) return "row band tables";
+        for (uint64_t i = 0; i < N; i++)
+            if (bhi[i] < blo[i] || bhi[i] > N || bs[i + 1] != bs[i] + (bhi[i] - blo[i]) || rb[i] != bs[i] - blo[i]) return "row band tables";
+        if (N && bs[N] != d.band_cells) return "row band tables";
+    }
     uint64_t nc = 0, nm = 0;
     for (uint32_t s = 2; s <= kSmallMax; s++) {
         const SmallClass& c = d.cls[s];

@@ -94,6 +94,8 @@ struct IndexDesc {
     uint64_t off_band_lo;       // u32[N]   first column row i is ever paired with
     uint64_t off_band_hi;       // u32[N]   one past the last such column (lo = hi = 0: row never touched)
     uint64_t band_cells;        // sum of (hi - lo): cells of the banded accumulator
+    uint64_t off_bandstart;     // u64[N+1] first cell of row i in the banded accumulator (prefix of hi - lo)
+    uint64_t off_rowbase;       // u64[N]   bandstart[i] - band_lo[i] (modulo 2^64): what the kernels add a column to
     uint64_t off_small_members; // member_bits/8 x [n_small_members]
     uint64_t off_small_weights; // u32[n_small_colors]
     uint64_t off_mid_offsets;   // u64[n_mid_colors+1]  start of each colour in the mid-members section,
@@ -142,7 +144,7 @@ struct IndexDesc {
     uint64_t shard_world, shard_rank, shard_rb, shard_re;
     uint64_t payload_bytes;
 };
-constexpr uint64_t kIndexMagic = 0x35305844494253ULL | (0x4BULL << 56);
+constexpr uint64_t kIndexMagic = 0x36305844494253ULL | (0x4BULL << 56);
 inline uint64_t gram_win_rows(const GramWin& w) { return (((uint64_t)w.n + kGramKBlock - 1) / kGramKBlock) * w.width; }
 inline uint64_t gram_member_bits(const IndexDesc& d) { return d.gram_rel_bits ? d.gram_rel_bits : d.packed_bits; }
 
