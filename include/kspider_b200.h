@@ -199,9 +199,14 @@ int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, 
 /* Clears the owned block and runs the pair-emission kernels on `stream` (a cudaStream_t passed as
  * void*; NULL = the library's own stream).  Returns after enqueueing unless sync != 0. */
 int ksb_accumulate(ksb_device* dev, void* stream, int sync);
-/* device pointer of the owned block of the packed upper triangle (u64 cells) */
+/* device pointer of the owned block of the banded upper triangle: cells of ksb_device_cell_bits(dev) bits -- 32 when the
+ * index proves that no cell can exceed 2^32 - 1 (a cell is a sum of weights of colours holding its row; the loader
+ * keeps the largest per-sample sum of weights) and the block is large enough to stream through HBM (> 16 MB as u64;
+ * KSPIDER_CELL_BITS=32 takes them for any size), 64 otherwise or with KSPIDER_CELL_BITS=64.  The values are those of
+ * the reference's u64 PAIRS_COUNTER either way (src/pairwise.cpp:222-225). */
 void* ksb_device_triangle(const ksb_device* dev, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end);
-/* copies the current pass's block to host memory (cells must equal the pass's cell count) */
+int ksb_device_cell_bits(const ksb_device* dev);
+/* copies the current pass's block to host memory as u64 cells (cells must equal the pass's cell count) */
 int ksb_device_read_triangle(const ksb_device* dev, uint64_t* host_out, uint64_t cells);
 /* When the owned row block does not fit dense_budget_bytes it is processed in several dense passes
  * (sub-blocks of rows): select one with ksb_device_set_pass before ksb_accumulate / ksb_postpass. */

@@ -204,6 +204,11 @@ class Device:
         p = lib().ksb_device_triangle(self._h, C.byref(c), C.byref(rb), C.byref(re))
         return p, c.value, rb.value, re.value
 
+    @property
+    def cell_bits(self) -> int:
+        """32 when the index proves that no cell of the accumulator can exceed 2^32 - 1, else 64 (ksb_device_cell_bits)."""
+        return int(lib().ksb_device_cell_bits(self._h))
+
     def read_triangle(self) -> np.ndarray:
         _, cells, _, _ = self.triangle()
         out = np.empty(cells, dtype=np.uint64)

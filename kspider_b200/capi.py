@@ -80,6 +80,7 @@ _PROTOS = {
     "ksb_device_triangle": (C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                          C.POINTER(C.c_uint64)]),
     "ksb_device_read_triangle": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "ksb_device_cell_bits": (C.c_int, [C.c_void_p]),
     "ksb_device_is_spill": (C.c_int, [C.c_void_p]),
     "ksb_device_set_overlap": (C.c_int, [C.c_void_p, C.c_int]),
     "ksb_device_run_spill": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),

@@ -78,7 +78,8 @@ struct ksb_device {
     std::vector<cudaEvent_t> gram_ev;      // per K4 chunk of pass 0: the copy piece holding its members has landed
     std::vector<cudaEvent_t> gram_ev_own;  // the events of the pieces the Gram section is copied in
     std::vector<uint64_t> gram_piece_end;  // payload offset each of those pieces ends at
-    unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad)
+    unsigned long long* d_tri = nullptr;   // max-pass cells (+8 pad); u32 cells when cell_bits == 32
+    uint32_t cell_bits = 64;               // 32 when no cell can exceed 2^32 - 1 (IndexDesc::max_row_sum; KSPIDER_CELL_BITS=64 forces u64)
     uint32_t* d_touched = nullptr;         // one bit per cell, only when zero-weight colours exist
     uint64_t tri_cells_alloc = 0;
     std::vector<ksb_pass> passes;
@@ -153,7 +154,7 @@ static TriGeom geom_of(const ksb_device* d, const ksb_pass& p) {
     g.bandstart = d->d_bandstart;
     g.band_lo = reinterpret_cast<const uint32_t*>(d->d_payload + d->desc.off_band_lo);
     g.band_hi = reinterpret_cast<const uint32_t*>(d->d_payload + d->desc.off_band_hi);
-    g.pad = 0;
+    g.cell_bits = d->cell_bits;
     g.n = (uint32_t)d->desc.n_samples;
     g.rb = (uint32_t)p.rb;
     g.nrows = (uint32_t)(p.re - p.rb);
@@ -379,7 +380,15 @@ static int finish_device(ksb_device* d, const uint64_t* row_updates, const uint6
         return KSB_OK;
     }
     const uint64_t cells = d->tri_cells_alloc;
-    KSB_CUDA(cudaMallocAsync(&d->d_tri, 8 * (cells + 8), d->stream));
+    {   // a cell is a sum of weights of colours holding its row: bounded by the row's own sum of weights (the loader's max_row_sum)
+        // u32 cells pay where the block streams through HBM; on a small L2-resident block (cfg2: 4 MB) they change nothing
+        // for K1 and cost K4 beside it (measured: cfg2 step 1.86 -> 2.31 ms), so those keep u64.  KSPIDER_CELL_BITS=32|64 forces.
+        const char* cb = std::getenv("KSPIDER_CELL_BITS");
+        const int cbv = cb ? std::atoi(cb) : 0;
+        const bool fits = d->desc.max_row_sum < (1ull << 32);
+        d->cell_bits = (fits && cbv != 64 && (cbv == 32 || 8 * cells > (16ull << 20))) ? 32u : 64u;
+    }
+    KSB_CUDA(cudaMallocAsync(&d->d_tri, (d->cell_bits / 8) * (cells + 16), d->stream));
     if (d->desc.n_zero_colors) KSB_CUDA(cudaMallocAsync(&d->d_touched, 4 * (cells / 32 + 2), d->stream));
     d->post_blocks_alloc = post_blocks(cells) + 1;
     KSB_CUDA(cudaMallocAsync(&d->d_block_counts, 8 * d->post_blocks_alloc * 3, d->stream));  // counts, offsets, u32 block rows
@@ -984,7 +993,7 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     const IndexDesc& D = d->desc;
     const uint8_t* P = d->d_payload;
     KSB_CUDA(cudaEventRecord(d->ev[0], st));
-    KSB_CUDA(cudaMemsetAsync(d->d_tri, 0, 8 * (p.cells + 8), st));
+    KSB_CUDA(cudaMemsetAsync(d->d_tri, 0, (d->cell_bits / 8) * (p.cells + 8), st));
     if (d->d_touched) KSB_CUDA(cudaMemsetAsync(d->d_touched, 0, 4 * (p.cells / 32 + 2), st));
     KSB_CUDA(cudaEventRecord(d->ev[1], st));
     if (d->copy_pending) {  // first accumulation after a pipelined upload
@@ -1010,7 +1019,7 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
         const char* env = std::getenv("KSPIDER_L2_BLOCK_MB");  // 0 = off; set = forced (no gain/cost rule)
         const uint64_t blk_mb = env ? (uint64_t)std::atoi(env) : 48;
         const uint64_t atom_upd = D.n_updates - D.n_gram_updates, atom_mem = D.n_members - D.n_gram_members - D.n_zero_members;
-        const uint64_t bytes = 8 * p.cells;
+        const uint64_t bytes = (d->cell_bits / 8) * p.cells;
         if (blk_mb && bytes > 2 * (blk_mb << 20) && atom_mem) {
             uint64_t n_sub = std::min<uint64_t>(64, (bytes + (blk_mb << 20) - 1) / (blk_mb << 20));
             // gain: the pass's atomic updates at the L2 rate instead of the HBM rate (1/27G - 1/190G s each);
@@ -1044,7 +1053,7 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
             // (5.3e14 u8 MACs/s; 1.9e11 reds/s on an L2-resident block, 2.7e10 otherwise).
             const char* kc = std::getenv("KSPIDER_K1_CTAS");
             const double t4 = (double)D.n_gram_macs / 5.3e14;
-            const double t1 = (double)(D.n_updates - D.n_gram_updates) / (8 * p.cells <= (96ull << 20) ? 1.9e11 : 2.7e10);
+            const double t1 = (double)(D.n_updates - D.n_gram_updates) / ((d->cell_bits / 8) * p.cells <= (96ull << 20) ? 1.9e11 : 2.7e10);
             const int fit = t4 >= 0.5 * t1 ? (d->g_planes <= 1 ? 3 : 2) : 8;
             lc1.k1_ctas = (kc && std::atoi(kc) > 0 && std::atoi(kc) <= 8) ? std::atoi(kc) : fit;
             const char* cv = std::getenv("KSPIDER_CARVEOUT");
@@ -1112,9 +1121,17 @@ int ksb_device_read_triangle(const ksb_device* d, uint64_t* host_out, uint64_t c
     if (cells != p.cells) { set_error("ksb_device_read_triangle: the current pass has %llu cells, caller asked for %llu", (unsigned long long)p.cells, (unsigned long long)cells); return KSB_ERR_ARG; }
     KSB_CUDA(cudaSetDevice(d->device));
     KSB_CUDA(cudaStreamSynchronize(d->stream));
-    if (cells) KSB_CUDA(cudaMemcpy(host_out, d->d_tri, 8 * cells, cudaMemcpyDeviceToHost));
+    if (cells && d->cell_bits == 32) {  // u32 cells on the device: widened here, in place, from the top down
+        KSB_CUDA(cudaMemcpy(host_out, d->d_tri, 4 * cells, cudaMemcpyDeviceToHost));
+        const uint32_t* narrow = reinterpret_cast<const uint32_t*>(host_out);
+        for (uint64_t i = cells; i-- > 0;) host_out[i] = narrow[i];
+    } else if (cells) {
+        KSB_CUDA(cudaMemcpy(host_out, d->d_tri, 8 * cells, cudaMemcpyDeviceToHost));
+    }
     return KSB_OK;
 }
+
+int ksb_device_cell_bits(const ksb_device* d) { return d ? (int)d->cell_bits : 0; }
 
 void* ksb_device_triangle(const ksb_device* d, uint64_t* cells, uint64_t* row_begin, uint64_t* row_end) {
     if (!d) return nullptr;

@@ -136,9 +136,16 @@ __device__ __forceinline__ uint32_t lds32(uint32_t a) {
 // order of K as long as both operands agree: the weight byte planes (kb_build) are stored in the same order.
 __device__ __forceinline__ uint32_t kperm(uint32_t k) { return (k & ~31u) + 4u * (k & 7u) + ((k & 31u) >> 3); }
 
+// address of the virtual cell (x, 0) of the owned block (0: row not owned), u64 or u32 cells (TriGeom::cell_bits)
+template <bool C32>
 __device__ __forceinline__ unsigned long long gram_row_addr(uint32_t x, const TriGeom& g) {
     if (x - g.rb >= g.nrows) return 0ull;
-    return (unsigned long long)g.tri + 8ull * (__ldg(g.rowbase + x) - g.base);
+    return (unsigned long long)g.tri + (C32 ? 4ull : 8ull) * (__ldg(g.rowbase + x) - g.base);
+}
+template <bool C32>
+__device__ __forceinline__ void gram_red(unsigned long long row_addr, uint32_t j, unsigned long long v) {
+    if (C32) asm volatile("red.global.add.u32 [%0], %1;" ::"l"(row_addr + 4ull * j), "r"((uint32_t)v) : "memory");
+    else asm volatile("red.global.add.u64 [%0], %1;" ::"l"(row_addr + 8ull * j), "l"(v) : "memory");
 }
 
 }  // namespace
@@ -347,7 +354,7 @@ cudaError_t launch_kb_build(const unsigned long long* gram_off, const void* gram
 //             that one warp instruction adds 2 x 16 consecutive cells of triangle rows
 //             (red.global.add.u64).
 // ------------------------------------------------------------------------------------------------
-template <int P>
+template <int P, bool C32>
 __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ GramParams prm,
                                                         const __grid_constant__ TriGeom G) {
     constexpr uint32_t NB = 4 / P;
@@ -471,8 +478,8 @@ __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ Gr
                         const uint32_t il = i0 + 32u * lq + 2 * y + rsel;
                         const uint32_t i = win.x0 + il;
                         if (il < jl && jl < win.width && j < G.n && acc[y] != 0ull) {
-                            const unsigned long long ra = gram_row_addr(i, G);
-                            if (ra != 0ull) asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
+                            const unsigned long long ra = gram_row_addr<C32>(i, G);
+                            if (ra != 0ull) gram_red<C32>(ra, j, acc[y]);
                         }
                     }
                 }
@@ -614,7 +621,7 @@ cudaError_t launch_imma_peak(uint32_t iters, uint32_t* sink, double* macs, const
 // the row / column groups that are padding, and groups entirely below the diagonal are skipped.
 // ------------------------------------------------------------------------------------------------
 constexpr uint32_t kPipeStages = 3;
-template <int P>
+template <int P, bool C32>
 __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams prm, const __grid_constant__ TriGeom G) {
     constexpr uint32_t NB = 2 / P;
     constexpr uint32_t kStageBytes = (P + NB) * kTileBytes;
@@ -668,7 +675,7 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
             if (row0 < ext) {
                 // address of the virtual cell (row, 0) of the warp's 32 rows, one per lane: the chunk loop takes
                 // them by shuffle instead of a dependent global load in front of every red
-                const unsigned long long ra_lane = (row0 + lane < win.width) ? gram_row_addr(win.x0 + row0 + lane, G) : 0ull;
+                const unsigned long long ra_lane = (row0 + lane < win.width) ? gram_row_addr<C32>(win.x0 + row0 + lane, G) : 0ull;
                 const uint32_t ra_lo = (uint32_t)ra_lane, ra_hi = (uint32_t)(ra_lane >> 32);
                 for (uint32_t ch = wg; ch < ncol * 8u; ch += 4) {
                     const uint32_t ct = ch >> 3, c16 = ch & 7u;
@@ -696,8 +703,7 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
                     for (uint32_t y = 0; y < 16; y++) {
                         const uint32_t src = 2 * y + rsel;
                         const unsigned long long ra = ((unsigned long long)__shfl_sync(0xffffffffu, ra_hi, src) << 32) | __shfl_sync(0xffffffffu, ra_lo, src);
-                        if (row0 + src < jl && col_ok && acc[y] != 0ull && ra != 0ull)
-                            asm volatile("red.global.add.u64 [%0], %1;" ::"l"(ra + 8ull * j), "l"(acc[y]) : "memory");
+                        if (row0 + src < jl && col_ok && acc[y] != 0ull && ra != 0ull) gram_red<C32>(ra, j, acc[y]);
                     }
                 }
             }
@@ -828,10 +834,13 @@ static size_t gram_pipe_smem_bytes(int P) {
 template <int P>
 static cudaError_t launch_gram_pipe_p(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc) {
     const size_t smem = gram_pipe_smem_bytes(P);
-    cudaError_t e = cudaFuncSetAttribute(k4_gram_pipe<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const bool c32 = g.cell_bits == 32;
+    cudaError_t e = c32 ? cudaFuncSetAttribute(k4_gram_pipe<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                        : cudaFuncSetAttribute(k4_gram_pipe<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     unsigned long long ctas = prm.n_items < (unsigned long long)lc.sms ? prm.n_items : (unsigned long long)lc.sms;
-    k4_gram_pipe<P><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
+    if (c32) k4_gram_pipe<P, true><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
+    else k4_gram_pipe<P, false><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
     return cudaGetLastError();
 }
 
@@ -856,10 +865,13 @@ static size_t gram_smem_bytes(int P) {
 template <int P>
 static cudaError_t launch_gram_p(const GramParams& prm, const TriGeom& g, const LaunchCfg& lc) {
     const size_t smem = gram_smem_bytes(P);
-    cudaError_t e = cudaFuncSetAttribute(k4_gram<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const bool c32 = g.cell_bits == 32;
+    cudaError_t e = c32 ? cudaFuncSetAttribute(k4_gram<P, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                        : cudaFuncSetAttribute(k4_gram<P, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     unsigned long long ctas = prm.n_items < (unsigned long long)lc.sms ? prm.n_items : (unsigned long long)lc.sms;
-    k4_gram<P><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
+    if (c32) k4_gram<P, true><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
+    else k4_gram<P, false><<<(unsigned)ctas, kThreads, smem, lc.stream>>>(prm, g);
     return cudaGetLastError();
 }
 

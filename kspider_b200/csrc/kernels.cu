@@ -46,6 +46,17 @@ struct DenseSink {
         if (pred) red_add_u64(r + c, w);
     }
 };
+// the same on u32 cells (TriGeom::cell_bits == 32: no cell can exceed 2^32 - 1, so no carry is ever lost)
+struct DenseSink32 {
+    static __device__ __forceinline__ unsigned long long row(uint32_t x, const TriGeom& g) {
+        if (x - g.rb >= g.nrows) return 0ull;
+        return (unsigned long long)g.tri + 4ull * (__ldg(g.rowbase + x) - g.base);
+    }
+    static __device__ __forceinline__ unsigned long long col(uint32_t x) { return 4ull * x; }
+    __device__ __forceinline__ void add(bool pred, unsigned long long r, unsigned long long c, unsigned long long w) const {
+        if (pred) asm volatile("red.global.add.u32 [%0], %1;" ::"l"(r + c), "r"((uint32_t)w) : "memory");
+    }
+};
 struct SpillSink {
     unsigned long long* keys;
     uint32_t* vals;
@@ -154,14 +165,21 @@ __global__ void __launch_bounds__(256) k1_small(const __grid_constant__ K1Params
 // takes are K4's.
 // tri[cell] += w on the lanes with pred != 0; address arithmetic and predicate stay inside one asm block
 // so that the red is predicated instead of branched around
+template <bool C32>
 __device__ __forceinline__ void red_cell_if(unsigned long long tri, uint32_t cell, unsigned long long w, uint32_t pred) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %3, 0;\n\tmad.wide.u32 a, %1, 8, %0;\n\t@p red.global.add.u64 [a], %2;\n\t}" ::"l"(tri),
-        "r"(cell), "l"(w), "r"(pred)
-        : "memory");
+    if (C32)
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %3, 0;\n\tmad.wide.u32 a, %1, 4, %0;\n\t@p red.global.add.u32 [a], %2;\n\t}" ::"l"(tri),
+            "r"(cell), "r"((uint32_t)w), "r"(pred)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %3, 0;\n\tmad.wide.u32 a, %1, 8, %0;\n\t@p red.global.add.u64 [a], %2;\n\t}" ::"l"(tri),
+            "r"(cell), "l"(w), "r"(pred)
+            : "memory");
 }
 
-template <class MT>
+template <class MT, bool C32 = false>
 __global__ void __launch_bounds__(256, 6) k1_small_c32(const __grid_constant__ K1Params P,
                                                     const MT* __restrict__ members,
                                                     const void* __restrict__ weights,
@@ -227,10 +245,10 @@ __global__ void __launch_bounds__(256, 6) k1_small_c32(const __grid_constant__ K
                 const uint32_t q2 = __shfl_sync(KSB_FULL, r32, src + 2u);
                 const uint32_t q3 = __shfl_sync(KSB_FULL, r32, src + 3u);
                 const uint32_t m = act >> ar;  // ar < ar1 <= 31
-                red_cell_if(tri, q0 + x, ww, m & 1u);
-                red_cell_if(tri, q1 + x, ww, m & 2u);
-                red_cell_if(tri, q2 + x, ww, m & 4u);
-                red_cell_if(tri, q3 + x, ww, m & 8u);
+                red_cell_if<C32>(tri, q0 + x, ww, m & 1u);
+                red_cell_if<C32>(tri, q1 + x, ww, m & 2u);
+                red_cell_if<C32>(tri, q2 + x, ww, m & 4u);
+                red_cell_if<C32>(tri, q3 + x, ww, m & 8u);
             }
         } else {
             const unsigned long long mi = moff + t_in * s;
@@ -247,13 +265,13 @@ __global__ void __launch_bounds__(256, 6) k1_small_c32(const __grid_constant__ K
             for (uint32_t ar = 0; ar < 32; ar++) {
                 const uint32_t r = __shfl_sync(KSB_FULL, r0, ar);
                 if ((own0 >> ar) & 1u) {  // warp-uniform
-                    red_cell_if(tri, r + x0, w, lane > ar);
-                    red_cell_if(tri, r + x1, w, v1);
+                    red_cell_if<C32>(tri, r + x0, w, lane > ar);
+                    red_cell_if<C32>(tri, r + x1, w, v1);
                 }
             }
             for (uint32_t ar = 32; ar + 1 < s; ar++) {
                 const uint32_t r = __shfl_sync(KSB_FULL, r1, ar - 32);
-                red_cell_if(tri, r + x1, w, ((own1 >> (ar - 32)) & 1u) != 0u && v1 && lane + 32 > ar);
+                red_cell_if<C32>(tri, r + x1, w, ((own1 >> (ar - 32)) & 1u) != 0u && v1 && lane + 32 > ar);
             }
         }
     }
@@ -271,7 +289,7 @@ cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t mem
     const bool force64 = k1c && std::atoi(k1c) == 64;
     const bool c32 = !force64 && g.cells < (1ull << 32);
     const int carve = lc.beside_gram ? (int)cudaSharedmemCarveoutMaxShared : (int)cudaSharedmemCarveoutDefault;
-    auto go = [&](auto kern64, auto kern32, auto mem) {
+    auto go = [&](auto kern64, auto kern32, auto sink, auto mem) {
         if (c32) {
             cudaFuncSetAttribute(kern32, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
             const unsigned long long cap32 = (unsigned long long)lc.sms * (unsigned long long)(lc.k1_ctas < 6 ? lc.k1_ctas : 6);  // 40 registers: 6 resident CTAs / SM
@@ -279,13 +297,20 @@ cudaError_t launch_k1_small(const K1Params& p, const void* members, uint32_t mem
             kern32<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, mem, weights, g, task_begin, task_end);
         } else {
             cudaFuncSetAttribute(kern64, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
-            kern64<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, mem, weights, g, DenseSink{}, task_begin, task_end);
+            kern64<<<(unsigned)ctas, 256, 0, lc.stream>>>(p, mem, weights, g, sink, task_begin, task_end);
         }
     };
-    if (member_bits == 10) go(k1_small<DenseSink, P10>, k1_small_c32<P10>, static_cast<const P10*>(members));
-    else if (member_bits == 12) go(k1_small<DenseSink, P12>, k1_small_c32<P12>, static_cast<const P12*>(members));
-    else if (member_bits == 16) go(k1_small<DenseSink, uint16_t>, k1_small_c32<uint16_t>, static_cast<const uint16_t*>(members));
-    else go(k1_small<DenseSink, uint32_t>, k1_small_c32<uint32_t>, static_cast<const uint32_t*>(members));
+    if (g.cell_bits == 32) {  // u32 cells
+        if (member_bits == 10) go(k1_small<DenseSink32, P10>, k1_small_c32<P10, true>, DenseSink32{}, static_cast<const P10*>(members));
+        else if (member_bits == 12) go(k1_small<DenseSink32, P12>, k1_small_c32<P12, true>, DenseSink32{}, static_cast<const P12*>(members));
+        else if (member_bits == 16) go(k1_small<DenseSink32, uint16_t>, k1_small_c32<uint16_t, true>, DenseSink32{}, static_cast<const uint16_t*>(members));
+        else go(k1_small<DenseSink32, uint32_t>, k1_small_c32<uint32_t, true>, DenseSink32{}, static_cast<const uint32_t*>(members));
+        return cudaGetLastError();
+    }
+    if (member_bits == 10) go(k1_small<DenseSink, P10>, k1_small_c32<P10>, DenseSink{}, static_cast<const P10*>(members));
+    else if (member_bits == 12) go(k1_small<DenseSink, P12>, k1_small_c32<P12>, DenseSink{}, static_cast<const P12*>(members));
+    else if (member_bits == 16) go(k1_small<DenseSink, uint16_t>, k1_small_c32<uint16_t>, DenseSink{}, static_cast<const uint16_t*>(members));
+    else go(k1_small<DenseSink, uint32_t>, k1_small_c32<uint32_t>, DenseSink{}, static_cast<const uint32_t*>(members));
     return cudaGetLastError();
 }
 
@@ -505,6 +530,13 @@ cudaError_t launch_k2_mid(const MidItem* items, uint64_t n_items, const unsigned
     unsigned long long ctas = n_items;
     const unsigned long long cap = (unsigned long long)lc.sms * 8ull;
     if (ctas > cap) ctas = cap;
+    if (g.cell_bits == 32) {
+        if (member_bits == 16)
+            k2_mid<DenseSink32, uint16_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, static_cast<const uint16_t*>(mid_members), mid_weights, g, DenseSink32{});
+        else
+            k2_mid<DenseSink32, uint32_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, static_cast<const uint32_t*>(mid_members), mid_weights, g, DenseSink32{});
+        return cudaGetLastError();
+    }
     if (member_bits == 16)
         k2_mid<DenseSink, uint16_t><<<(unsigned)ctas, kMidCols, 0, lc.stream>>>(items, 0ull, n_items, mid_off, mid_sizes, static_cast<const uint16_t*>(mid_members), mid_weights, g, DenseSink{});
     else
@@ -683,7 +715,20 @@ cudaError_t launch_kz_touch(uint64_t n_zero, const unsigned long long* zero_off,
 __device__ __forceinline__ uint32_t k5_flags(const TriGeom& G, const uint32_t* __restrict__ touched,
                                              unsigned long long cell0, unsigned long long v[kPostPerThread]) {
     uint32_t flags = 0;
-    if (cell0 + kPostPerThread <= G.cells) {
+    if (G.cell_bits == 32) {  // u32 cells (kernel-uniform)
+        const uint32_t* t32 = reinterpret_cast<const uint32_t*>(G.tri);
+        if (cell0 + kPostPerThread <= G.cells) {
+            const uint4* p = reinterpret_cast<const uint4*>(t32 + cell0);
+#pragma unroll
+            for (uint32_t q = 0; q < kPostPerThread / 4; q++) {
+                const uint4 t = p[q];
+                v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+            }
+        } else {
+#pragma unroll
+            for (uint32_t q = 0; q < kPostPerThread; q++) v[q] = (cell0 + q < G.cells) ? t32[cell0 + q] : 0ull;
+        }
+    } else if (cell0 + kPostPerThread <= G.cells) {
         const ulonglong2* p = reinterpret_cast<const ulonglong2*>(G.tri + cell0);
 #pragma unroll
         for (uint32_t q = 0; q < kPostPerThread / 2; q++) {
@@ -778,7 +823,7 @@ __global__ void __launch_bounds__(kPostThreads) k5_emit(const __grid_constant__ 
         bool f = false;
         v[q] = 0ull;
         if (cell < G.cells) {
-            v[q] = G.tri[cell];
+            v[q] = G.cell_bits == 32 ? (unsigned long long)reinterpret_cast<const uint32_t*>(G.tri)[cell] : G.tri[cell];
             f = v[q] != 0ull;
             if (touched != nullptr && !f) f = (touched[cell >> 5] >> (cell & 31u)) & 1u;
         }
@@ -1011,6 +1056,162 @@ __global__ void __launch_bounds__(kPostThreads) k56_scan(const __grid_constant__
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// k56_rows: the same post-pass walking the block ROW BY ROW.  The banded block stores the cells of a row back to back
+// (columns band_lo[i] .. band_hi[i]), so a warp that owns a row knows (i, j) of every cell it loads without any search:
+// lane = column, 32 consecutive cells (256 B) and their 32 totals (128 B) per step, four steps in flight; the row's own
+// total, band and first cell are loaded once per row.  k56_scan, which cuts the block into 2048-cell chunks regardless
+// of rows, spends ~68 instructions per cell on finding and following rows (ncu: issue-bound at 41 % of the HBM peak
+// on cfg4); here a cell costs a load, a gather from the (L2-resident) totals, a multiply-add, a shift and a compare.
+// Rows are dealt to the warps of the grid round-robin (neighbouring rows of a clade / family differ in length by one
+// cell, so every warp gets the same mix).  Kept pairs go to a per-warp queue in shared memory (ballot + popc, no
+// atomics) that is flushed to the edge list with one global atomicAdd per ~100 pairs.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kRowsQueue = 128;      // per warp; flushed when a step could overflow it
+constexpr uint32_t kRowsCtasPerSm = 8;
+__device__ __noinline__ bool k56_keep_slow(unsigned long long v, uint32_t ti, uint32_t tj, int dist_col, float cstar) {
+    float c;
+    if (dist_col != 4 && ti != 0u && tj != 0u) {
+        // min / max of the two quotients = the quotient by the larger / smaller total (see k56_scan)
+        c = __fdiv_rn(__ull2float_rn(v), __uint2float_rn(dist_col == 3 ? max(ti, tj) : min(ti, tj)));
+    } else {
+        float cmin, cavg, cmax;
+        containment(v, ti, tj, cmin, cavg, cmax);
+        c = dist_col == 3 ? cmin : (dist_col == 4 ? cavg : cmax);
+    }
+    return !(c < cstar);  // NaN is kept, as in `if distance < cutoff: continue`
+}
+template <bool TOUCHED, bool USE_MAX, class CT>
+__global__ void __launch_bounds__(256) k56_rows(const __grid_constant__ TriGeom G, const uint32_t* __restrict__ touched,
+                                                const uint32_t* __restrict__ totals, int dist_col, float cstar,
+                                                const ScanCut cut, unsigned long long* __restrict__ edges,
+                                                unsigned long long cap, unsigned long long* counters) {
+    __shared__ unsigned long long q[8][kRowsQueue];
+    __shared__ uint32_t rows_cta;
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    const uint32_t warp = blockIdx.x * 8u + wid, nwarps = gridDim.x * 8u;
+    const uint32_t lane_lt = (1u << lane) - 1u;
+    unsigned long long* myq = q[wid];
+    uint32_t qn = 0;           // warp-uniform
+    uint32_t rows_seen = 0;    // touched cells this lane saw
+    if (threadIdx.x == 0) rows_cta = 0;
+    const bool fast = cut.mode == 1u;
+    const unsigned long long cm = cut.m, cadd = cut.add;
+    const uint32_t cshift = cut.shift;
+    for (uint32_t r = warp; r < G.nrows; r += nwarps) {
+        const uint32_t i = G.rb + r;
+        const uint32_t lo = __ldg(G.band_lo + i), hi = __ldg(G.band_hi + i);
+        if (hi <= lo) continue;
+        const unsigned long long c0 = __ldg(G.bandstart + i) - G.base;  // first cell of the row inside the owned block
+        const uint32_t ti = __ldg(totals + i);
+        const uint32_t len = hi - lo;
+        const unsigned long long ihi = (unsigned long long)i << 32;
+        // a kept pair goes to the warp's queue (every lane calls; ballot + popc, no atomics)
+        auto enqueue = [&](bool keep, uint32_t x) {
+            const uint32_t m = __ballot_sync(KSB_FULL, keep);
+            if (m != 0u) {
+                if (keep) myq[qn + __popc(m & lane_lt)] = ihi | (lo + x);
+                qn += __popc(m);
+                __syncwarp();
+                if (qn > kRowsQueue - 32u) {  // flush: one global atomicAdd per ~100 kept pairs
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(counters + 1, (unsigned long long)qn);
+                    base = shfl_u64(base, 0);
+                    for (uint32_t k = lane; k < qn; k += 32u)
+                        if (base + k < cap) edges[base + k] = myq[k];
+                    __syncwarp();
+                    qn = 0;
+                }
+            }
+        };
+        // one cell, any value: (value, total of its column, column)
+        auto cell = [&](unsigned long long v, uint32_t tj, uint32_t x, bool inside) {
+            bool t = v != 0ull;
+            if (TOUCHED) {
+                if (!t && inside) {
+                    const unsigned long long cidx = c0 + x;
+                    t = (__ldg(touched + (cidx >> 5)) >> (cidx & 31u)) & 1u;
+                }
+            }
+            bool keep = false;
+            if (t) {
+                rows_seen++;
+                const uint32_t mn = min(ti, tj);
+                const uint32_t T = USE_MAX ? max(ti, tj) : mn;
+                // eligible for the exact integer form of `float32 quotient >= c*` (see k56_scan / make_scan_cut):
+                // S < 2^24, 0 < T < 2^24, no zero total
+                const bool ok = fast && (uint32_t)(v >> 24) == 0u && (uint32_t)(v >> 32) == 0u && T - 1u < (1u << 24) - 1u && (!USE_MAX || mn != 0u);
+                if (ok) keep = v >= ((cm * T + cadd) >> cshift);
+                else keep = k56_keep_slow(v, ti, tj, dist_col, cstar);
+            }
+            enqueue(keep, x);
+        };
+        const CT* vp = reinterpret_cast<const CT*>(G.tri) + c0 + lane;
+        const uint32_t* tp = totals + lo + lane;
+        // Whole groups of 128 cells whose sums and totals are all below 2^24 take the integer test without any per-cell
+        // eligibility check: a cell is touched iff it is non-zero (no zero-weight colours in this variant), and a zero
+        // total needs no special case -- S / 0 = inf >= c* is what S * 2^shift >= M * 0 says too.  c* <= 2^7 makes the
+        // threshold on S fit 32 bits (M T < 2^50, shift >= 18).
+        const bool row_fast = !TOUCHED && fast && cshift >= 18u && (USE_MAX || ti < (1u << 24));
+        uint32_t x0 = 0;
+        for (; x0 + 128u <= len; x0 += 128u) {  // four full steps in flight, no bounds
+            const CT v0 = vp[x0], v1 = vp[x0 + 32u], v2 = vp[x0 + 64u], v3 = vp[x0 + 96u];
+            const uint32_t t0 = __ldg(tp + x0), t1 = __ldg(tp + x0 + 32u), t2 = __ldg(tp + x0 + 64u), t3 = __ldg(tp + x0 + 96u);
+            bool small = row_fast;
+            if (row_fast) {
+                const unsigned long long vo = (unsigned long long)(v0 | v1 | v2 | v3);
+                small = (vo >> 24) == 0ull;
+                if (USE_MAX) small = small && ((t0 | t1 | t2 | t3) >> 24) == 0u;
+            }
+            if (__all_sync(KSB_FULL, small)) {
+                const CT vv[4] = {v0, v1, v2, v3};
+                const uint32_t tt[4] = {t0, t1, t2, t3};
+#pragma unroll
+                for (uint32_t u = 0; u < 4; u++) {
+                    const uint32_t S = (uint32_t)vv[u];
+                    const uint32_t T = USE_MAX ? max(ti, tt[u]) : min(ti, tt[u]);
+                    const uint32_t thr = (uint32_t)((cm * T + cadd) >> cshift);
+                    const bool nz = S != 0u;
+                    rows_seen += nz ? 1u : 0u;
+                    enqueue(nz && S >= thr, x0 + 32u * u + lane);
+                }
+            } else {
+                cell(v0, t0, x0 + lane, true);
+                cell(v1, t1, x0 + 32u + lane, true);
+                cell(v2, t2, x0 + 64u + lane, true);
+                cell(v3, t3, x0 + 96u + lane, true);
+            }
+        }
+        if (x0 < len) {  // the row's last, partial group
+            unsigned long long v[4];
+            uint32_t tj[4];
+#pragma unroll
+            for (uint32_t u = 0; u < 4; u++) {
+                const uint32_t x = x0 + 32u * u + lane;
+                v[u] = x < len ? vp[x0 + 32u * u] : 0ull;
+                tj[u] = x < len ? __ldg(tp + x0 + 32u * u) : 1u;
+            }
+#pragma unroll
+            for (uint32_t u = 0; u < 4; u++) {
+                if (x0 + 32u * u >= len) break;  // warp-uniform
+                cell(v[u], tj[u], x0 + 32u * u + lane, x0 + 32u * u + lane < len);
+            }
+        }
+    }
+    if (qn) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(counters + 1, (unsigned long long)qn);
+        base = shfl_u64(base, 0);
+        for (uint32_t k = lane; k < qn; k += 32u)
+            if (base + k < cap) edges[base + k] = myq[k];
+    }
+    rows_seen = __reduce_add_sync(KSB_FULL, rows_seen);
+    __syncthreads();
+    if (lane == 0 && rows_seen) atomicAdd(&rows_cta, rows_seen);  // one counter update per CTA
+    __syncthreads();
+    if (threadIdx.x == 0 && rows_cta) atomicAdd(counters, (unsigned long long)rows_cta);
+}
+
 // hook (atomicMin accelerator, see k6_hook_min) and union over a compact edge list whose length lives on the device
 __global__ void __launch_bounds__(256) k6_edges_hook(const unsigned long long* __restrict__ edges, unsigned long long cap,
                                                      const unsigned long long* __restrict__ counters, uint32_t* parent) {
@@ -1065,6 +1266,32 @@ cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, cons
     const uint64_t nb = post_blocks(g.cells);
     if (nb == 0) return cudaSuccess;
     const ScanCut cut = make_scan_cut(dist_col, cstar);
+    // row-wise scan unless the rows are too short to feed a warp (fewer than 32 cells per owned row on average) or
+    // KSPIDER_K56=scan asks for the chunk-wise kernel; KSPIDER_K56=rows forces it
+    static const int mode = [] { const char* v = std::getenv("KSPIDER_K56"); return !v ? 0 : (!std::strcmp(v, "scan") ? 1 : (!std::strcmp(v, "rows") ? 2 : 0)); }();
+    if (mode == 2 || g.cell_bits == 32 || (mode == 0 && g.cells >= 32ull * g.nrows)) {  // k56_scan stages u64 cells only
+        // persistent warps: exactly the CTAs that are resident at once (the kernel's registers allow 5 per SM)
+        static const int per_sm = [] {
+            int n = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k56_rows<false, false, unsigned long long>, 256, 0) != cudaSuccess || n < 1) { (void)cudaGetLastError(); n = 4; }
+            return n < (int)kRowsCtasPerSm ? n : (int)kRowsCtasPerSm;
+        }();
+        const uint64_t want = ((uint64_t)g.nrows + 7) / 8, capr = (uint64_t)lc.sms * (uint64_t)per_sm;
+        const unsigned ctas = (unsigned)(want < capr ? want : capr);
+        auto go = [&](auto kern) { kern<<<ctas, 256, 0, lc.stream>>>(g, touched_bits, totals, dist_col, cstar, cut, edges, cap, counters); };
+        const int variant = (touched_bits ? 4 : 0) | (cut.use_max ? 2 : 0) | (g.cell_bits == 32 ? 1 : 0);
+        switch (variant) {
+            case 0: go(k56_rows<false, false, unsigned long long>); break;
+            case 1: go(k56_rows<false, false, uint32_t>); break;
+            case 2: go(k56_rows<false, true, unsigned long long>); break;
+            case 3: go(k56_rows<false, true, uint32_t>); break;
+            case 4: go(k56_rows<true, false, unsigned long long>); break;
+            case 5: go(k56_rows<true, false, uint32_t>); break;
+            case 6: go(k56_rows<true, true, unsigned long long>); break;
+            default: go(k56_rows<true, true, uint32_t>); break;
+        }
+        return cudaGetLastError();
+    }
     const uint64_t capc = (uint64_t)lc.sms * kScanCtasPerSm;
     k56_scan<<<(unsigned)(nb < capc ? nb : capc), kPostThreads, 0, lc.stream>>>(g, touched_bits, block_rows, totals, dist_col, cstar, cut, edges,
                                                                                 cap, counters, (uint32_t)nb);

@@ -30,7 +30,9 @@ struct TriGeom {
     uint32_t n;                           // N
     uint32_t rb;                          // first owned row
     uint32_t nrows;                       // owned rows
-    uint32_t pad;
+    uint32_t cell_bits;                   // 64, or 32: the cells are u32 (tri then points at uint32_t cells) -- taken when the
+                                          // loader's bound on any cell (IndexDesc::max_row_sum) fits: every HBM-bound part of
+                                          // the step (clear, K4's reds, the post-pass scan) moves half the bytes
 };
 
 // Element accessors of the blob's member / weight sections.  Members of the small-colour and Gram
