@@ -416,6 +416,7 @@ def main_b200(args):
         dev = idx.upload(device=local_rank, dense_budget_bytes=budget, spill=args.spill)
     N, C_, M, U, U_small, M_small, C_small, payload_bytes, C_gram, P_gram, U_gram, M_gram, MAC_gram, WSUM, CELLS_gram = (int(v) for v in shape)
     spill = bool(dev.is_spill)
+    gram_form = int((my if my is not None else idx).info.gram_form)   # bit 0: bitmaps in the blob; >> 8: bits of a window-relative member
 
     host_ms = {"step": 0.0}
     last = {}
@@ -614,8 +615,8 @@ def main_b200(args):
                         "updates_per_s": um / (alone["mid_ms"] * 1e-3)})
     if alone["post_ms"] > 0:
         kb = 8 * owned_cells + 8 * int(last["edges"])
-        tr, trs = traffic_of(args.workload, "k56_scan")
-        kernels.append({"bound": "hbm", "kernel": "k56_scan", "kernel_ms": alone["post_ms"], "achieved": kb / (alone["post_ms"] * 1e-3) / 1e9,
+        tr, trs = traffic_of(args.workload, "k56")
+        kernels.append({"bound": "hbm", "kernel": "k56_rows / k56_scan (cluster-only post-pass)", "kernel_ms": alone["post_ms"], "achieved": kb / (alone["post_ms"] * 1e-3) / 1e9,
                         "peak": peak, "unit": "GB/s", "algorithmic_bytes": kb, "traffic": tr, "traffic_source": trs, "peak_source": peak_src,
                         "bytes": "8 B per cell of the owned block (read once) + 8 B per kept edge"})
     imma = None
@@ -641,7 +642,7 @@ def main_b200(args):
                "bytes": "16 B per cell a Gram window can update (n_gram_cells) + 4 B per member of the Gram colours", "peak_source": peak_src}
         hbm["frac"] = hbm["achieved"] / peak
         binding, other = (tensor, hbm) if tensor["frac"] >= hbm["frac"] else (hbm, tensor)
-        entry = {"kernel": "k4_gram (+ kb_build)", "kernel_ms": g_ms, "traffic": tr, "traffic_source": trs,
+        entry = {"kernel": "k4_gram (+ kb_build)" if (gram_form & 1) == 0 else "k4_gram (+ kb_weights; the bitmaps are part of the resident blob)", "kernel_ms": g_ms, "traffic": tr, "traffic_source": trs,
                  "updates_per_s": U_gram * own_frac / (g_ms * 1e-3), "colors": C_gram, "planes": P_gram,
                  "binding": "the larger of the two fractions: the bound the launches are closer to", "other_bound": other}
         entry.update(binding)
@@ -709,7 +710,9 @@ def main_b200(args):
                        "clusters": int(np.unique(labels_step).size), "step": "cluster-only (ksb_device_cluster), one CUDA graph launch per step" if not spill else "spill: sort-reduce records + K6/K7",
                        "parallelism": f"row-blocks x{world}", "passes": dev.n_passes, "spill": spill,
                        "index_build_s": t_build,
-                       "l2": f"inputs larger than L2 (CSR blob {payload_bytes / 1e6:.0f} MB streamed every step; the owned block of the triangle ({owned_cells * 8 / 1e6:.0f} MB) is cleared every step)"},
+                       "blob": {"bytes": payload_bytes, "gram_section": "bitmaps" if (gram_form & 1) else ("member lists" + (f", {gram_form >> 8}-bit offsets inside the window" if gram_form >> 8 else ""))},
+                       "cell_bits": dev.cell_bits,
+                       "l2": f"inputs larger than L2 (blob {payload_bytes / 1e6:.0f} MB streamed every step; the owned block of the triangle ({owned_cells * dev.cell_bits / 8 / 1e6:.0f} MB of u{dev.cell_bits} cells) is cleared every step)"},
             "phases_ms": phase, "phases_note": "per-kernel timers of extra legs run kernel by kernel (the timed steps are graph replays)", "kernels_alone_ms": alone, "host_ms_per_step": host_step_ms, "wall_ms_per_step": wall_ms / args.steps,
             "timer": "torch.cuda.Event pair on the current stream around the K steps (every step ends with a stream synchronisation); phases: library CUDA events on the launching stream",
             "clocks": clocks, "e2e": e2e, "e2e_records": e2e_rec, "check": check_blk, "wall": wall,

@@ -76,7 +76,8 @@ typedef struct ksb_index_info {
     uint64_t n_gram_windows;   /* sample windows the K4 colours are grouped into */
     uint64_t n_gram_macs;      /* sum over windows of colours x width(width-1)/2 x planes: u8 MACs K4 must evaluate */
     uint32_t pinned;           /* 1 if the payload lives in cudaMallocHost memory */
-    uint32_t reserved;
+    uint32_t gram_form;        /* Gram section of the blob: 0 = member lists (CSR; gram_form >> 8 = bits of a window-relative
+                                  member, 0 = absolute ids), 1 = the K-block-major bitmaps K4 reads (no bitmap build per step) */
     uint64_t n_gram_cells;     /* sum over windows of extent(extent-1)/2: cells K4's epilogue can update (one red each) */
 } ksb_index_info;
 

@@ -27,7 +27,7 @@ class IndexInfo(C.Structure):
         "n_samples", "n_colors_file", "n_colors", "n_members", "n_updates", "n_small_colors",
         "n_mid_colors", "n_gram_colors", "gram_min_size", "gram_planes", "n_gram_updates", "n_zero_colors", "max_color_size", "payload_bytes", "triangle_cells",
         "n_small_members", "n_small_updates", "n_gram_members", "n_gram_windows", "n_gram_macs")] + \
-        [("pinned", C.c_uint32), ("reserved", C.c_uint32), ("n_gram_cells", C.c_uint64)]
+        [("pinned", C.c_uint32), ("gram_form", C.c_uint32), ("n_gram_cells", C.c_uint64)]
 
 
 class Opts(C.Structure):

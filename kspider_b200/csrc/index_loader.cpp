@@ -1269,6 +1269,7 @@ int ksb_index_get_info(const ksb_index* ix, ksb_index_info* info) {
     info->n_gram_macs = d.n_gram_macs;
     info->n_gram_cells = d.n_gram_cells;
     info->pinned = ix->pinned ? 1 : 0;
+    info->gram_form = (uint32_t)(d.gram_form | (d.gram_rel_bits << 8));
     return KSB_OK;
 }
 
