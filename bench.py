@@ -704,7 +704,7 @@ def main_b200(args):
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "u64", "data": "synthetic",
+            "dtype": f"u{dev.cell_bits}", "data": "synthetic",
             "config": {"workload": WORKLOAD_DESC[args.workload], "name": args.workload, "samples": N, "colors": C_,
                        "members": M, "pair_updates": U, "rows": rows, "edges": n_edges, "cutoff": args.cutoff,
                        "clusters": int(np.unique(labels_step).size), "step": "cluster-only (ksb_device_cluster), one CUDA graph launch per step" if not spill else "spill: sort-reduce records + K6/K7",

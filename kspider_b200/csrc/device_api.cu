@@ -54,6 +54,7 @@ struct ksb_gram_plan {
     void* d_tables = nullptr;
     void* h_tables = nullptr;            // pinned, kept until the device handle is released
     uint64_t h_tables_bytes = 0;
+    bool wq_static = false;              // the weight byte planes of the (only) chunk were laid out when the plan was built
     cudaEvent_t ev_tables = nullptr;     // the copy kernel has run (recorded on the handle's stream)
     bool tables_ordered = false;         // the stream the step runs on has been made to wait for it
 };
@@ -908,9 +909,19 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         k_host_to_device<<<std::min<uint32_t>((n16 + 255) / 256, 4u * (uint32_t)d->sms), 256, 0, d->stream>>>(
             reinterpret_cast<uint4*>(T), reinterpret_cast<const uint4*>(H), n16);
         KSB_CUDA(cudaGetLastError());
+        d->launches++;
+        if (bitmap_form && plan.chunks.size() == 1 && d->passes.size() == 1) {
+            // One pass, one chunk, bitmaps in the blob: the chunk's weight byte planes are as static as the window and item
+            // tables, so they are laid out here, once, instead of in front of K4 in every step (cfg4: 22 us per step).
+            const ksb_gram_chunk& c = plan.chunks[0];
+            if (d->copy_pending) KSB_CUDA(cudaStreamWaitEvent(d->stream, d->ev_copy[2], 0));  // the weights are on their way
+            KSB_CUDA(launch_kb_weights(plan.d_wins + c.win_begin, c.n_wins, c.kblocks, d->d_payload + d->desc.off_gram_weights,
+                                       (uint32_t)d->desc.weight_bits, c.kblocks * kGramKBlock, d->g_planes, d->d_gwq, LaunchCfg{d->sms, d->stream}));
+            plan.wq_static = true;
+            d->launches++;
+        }
         KSB_CUDA(pool_event(d->device, &plan.ev_tables, false));
         KSB_CUDA(cudaEventRecord(plan.ev_tables, d->stream));
-        d->launches++;
     }
     plan.built = true;
     return KSB_OK;
@@ -956,7 +967,9 @@ static int run_gram(ksb_device* d, const ksb::TriGeom& g, cudaStream_t st_build,
             KSB_CUDA(cudaStreamWaitEvent(sb, ce, 0));
         }
         KSB_CUDA(cudaMemsetAsync(gp.counter, 0, 256, sb));  // bitmap and weight planes are written in full by kb_build
-        if (D.gram_form)
+        if (D.gram_form && plan.wq_static)
+            d->launches--;  // nothing to lay out per step (the count below assumes two launches per chunk)
+        else if (D.gram_form)
             KSB_CUDA(launch_kb_weights(gp.wins, gp.n_wins, c.kblocks, gw, (uint32_t)D.weight_bits, gp.kpad, gp.planes, d->d_gwq, LaunchCfg{d->sms, sb}));
         else
             KSB_CUDA(launch_kb_build(goff, gmem, (uint32_t)gram_member_bits(D), gw, (uint32_t)D.weight_bits, plan.d_units + c.unit_begin, c.n_units, gp.kpad, gp.planes, d->d_gbits, d->d_gwq,
@@ -1530,6 +1543,7 @@ static int cluster_body(ksb_device* d, int dist_col, float cstar, cudaStream_t s
     KSB_CUDA(cudaMemsetAsync(d->d_cl_counters, 0, 32, st));
     KSB_CUDA(launch_k7_init(d->d_parent, N, lc));
     d->launches++;
+    bool all_rows = true;
     for (uint32_t p = 0; p < d->passes.size(); p++) {
         d->cur_pass = p;
         const int rc = ksb_accumulate(d, st, 0);
@@ -1537,21 +1551,23 @@ static int cluster_body(ksb_device* d, int dist_col, float cstar, cudaStream_t s
         const ksb_pass& ps = d->passes[p];
         if (ps.cells == 0) continue;
         const TriGeom g = geom_of(d, ps);
-        if (d->block_rows_pass != (int)p || d->passes.size() > 1) {
+        const bool rows = k56_uses_rows(g);  // row-wise scan: no block table, and the kept edges are hooked as they are appended
+        all_rows = all_rows && rows;
+        if (!rows && (d->block_rows_pass != (int)p || d->passes.size() > 1)) {
             KSB_CUDA(launch_k5_block_rows(g, block_rows, lc));
             d->block_rows_pass = (int)p;
             d->launches++;
         }
         KSB_CUDA(cudaEventRecord(d->ev[5], st));
         KSB_CUDA(launch_k56_scan(g, d->d_touched, block_rows, reinterpret_cast<const uint32_t*>(P + d->desc.off_totals), dist_col, cstar,
-                                 d->d_edges, d->edge_cap, d->d_cl_counters, lc));
+                                 d->d_edges, d->edge_cap, d->d_cl_counters, d->d_parent, lc));
         KSB_CUDA(cudaEventRecord(d->ev[6], st));
         d->launches++;
     }
-    KSB_CUDA(launch_k6_edges(d->d_edges, d->edge_cap, d->d_cl_counters, d->d_parent, d->edge_cap, lc));
+    KSB_CUDA(launch_k6_edges(d->d_edges, d->edge_cap, d->d_cl_counters, d->d_parent, d->edge_cap, all_rows, lc));
     KSB_CUDA(launch_k7_compress(d->d_parent, N, lc));
     KSB_CUDA(cudaEventRecord(d->ev[7], st));
-    d->launches += 3;
+    d->launches += all_rows ? 2 : 3;
     if (d_labels_out) KSB_CUDA(cudaMemcpyAsync(d_labels_out, d->d_parent, 4ull * N, cudaMemcpyDeviceToDevice, st));
     if (host_labels) KSB_CUDA(cudaMemcpyAsync(d->h_stage, d->d_parent, 4ull * N, cudaMemcpyDeviceToHost, st));
     KSB_CUDA(cudaMemcpyAsync(d->h_stage + 4ull * N, d->d_cl_counters, 16, cudaMemcpyDeviceToHost, st));

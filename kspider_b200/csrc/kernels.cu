@@ -1085,7 +1085,7 @@ template <bool TOUCHED, bool USE_MAX, class CT>
 __global__ void __launch_bounds__(256) k56_rows(const __grid_constant__ TriGeom G, const uint32_t* __restrict__ touched,
                                                 const uint32_t* __restrict__ totals, int dist_col, float cstar,
                                                 const ScanCut cut, unsigned long long* __restrict__ edges,
-                                                unsigned long long cap, unsigned long long* counters) {
+                                                unsigned long long cap, unsigned long long* counters, uint32_t* parent) {
     __shared__ unsigned long long q[8][kRowsQueue];
     __shared__ uint32_t rows_cta;
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
@@ -1098,27 +1098,67 @@ __global__ void __launch_bounds__(256) k56_rows(const __grid_constant__ TriGeom 
     const bool fast = cut.mode == 1u;
     const unsigned long long cm = cut.m, cadd = cut.add;
     const uint32_t cshift = cut.shift;
+    // Software pipeline.  The meta data of the NEXT row (band, first cell, total: dependent loads) is fetched when the current
+    // row starts, and the next 128-cell group -- of this row, or the first one of the next row -- is fetched before the current
+    // group is decoded, so neither the per-row prologue nor the per-group loads are waited for in the open.
+    struct Meta { uint32_t i, lo, len, ti; unsigned long long c0; };
+    struct Group { CT v0, v1, v2, v3; uint32_t t0, t1, t2, t3; };
+    auto load_meta = [&](uint32_t r) {
+        Meta m;
+        m.i = G.rb + r;
+        m.lo = __ldg(G.band_lo + m.i);
+        const uint32_t hi = __ldg(G.band_hi + m.i);
+        m.len = hi > m.lo ? hi - m.lo : 0u;
+        m.c0 = __ldg(G.bandstart + m.i) - G.base;  // first cell of the row inside the owned block
+        m.ti = __ldg(totals + m.i);
+        return m;
+    };
+    auto load_group = [&](const Meta& m, uint32_t x0) {
+        Group g;
+        const CT* vp = reinterpret_cast<const CT*>(G.tri) + m.c0 + x0 + lane;
+        const uint32_t* tp = totals + m.lo + x0 + lane;
+        if (x0 + 128u <= m.len) {  // only the row's last group checks bounds
+            g.v0 = vp[0]; g.v1 = vp[32]; g.v2 = vp[64]; g.v3 = vp[96];
+            g.t0 = __ldg(tp); g.t1 = __ldg(tp + 32); g.t2 = __ldg(tp + 64); g.t3 = __ldg(tp + 96);
+        } else {  // cells past the row's end read as untouched (0) with a harmless total
+            const uint32_t x = x0 + lane;
+            g.v0 = x < m.len ? vp[0] : (CT)0;        g.t0 = x < m.len ? __ldg(tp) : 1u;
+            g.v1 = x + 32u < m.len ? vp[32] : (CT)0; g.t1 = x + 32u < m.len ? __ldg(tp + 32) : 1u;
+            g.v2 = x + 64u < m.len ? vp[64] : (CT)0; g.t2 = x + 64u < m.len ? __ldg(tp + 64) : 1u;
+            g.v3 = x + 96u < m.len ? vp[96] : (CT)0; g.t3 = x + 96u < m.len ? __ldg(tp + 96) : 1u;
+        }
+        return g;
+    };
+    Meta m{};
+    Group g{};
+    if (warp < G.nrows) {
+        m = load_meta(warp);
+        if (m.len) g = load_group(m, 0u);
+    }
     for (uint32_t r = warp; r < G.nrows; r += nwarps) {
-        const uint32_t i = G.rb + r;
-        const uint32_t lo = __ldg(G.band_lo + i), hi = __ldg(G.band_hi + i);
-        if (hi <= lo) continue;
-        const unsigned long long c0 = __ldg(G.bandstart + i) - G.base;  // first cell of the row inside the owned block
-        const uint32_t ti = __ldg(totals + i);
-        const uint32_t len = hi - lo;
+        Meta mn{};
+        const bool has_next = r + nwarps < G.nrows;
+        if (has_next) mn = load_meta(r + nwarps);
+        const uint32_t i = m.i, lo = m.lo, len = m.len, ti = m.ti;
+        const unsigned long long c0 = m.c0;
         const unsigned long long ihi = (unsigned long long)i << 32;
         // a kept pair goes to the warp's queue (every lane calls; ballot + popc, no atomics)
         auto enqueue = [&](bool keep, uint32_t x) {
-            const uint32_t m = __ballot_sync(KSB_FULL, keep);
-            if (m != 0u) {
-                if (keep) myq[qn + __popc(m & lane_lt)] = ihi | (lo + x);
-                qn += __popc(m);
+            const uint32_t mk = __ballot_sync(KSB_FULL, keep);
+            if (mk != 0u) {
+                if (keep) myq[qn + __popc(mk & lane_lt)] = ihi | (lo + x);
+                qn += __popc(mk);
                 __syncwarp();
                 if (qn > kRowsQueue - 32u) {  // flush: one global atomicAdd per ~100 kept pairs
                     unsigned long long base = 0;
                     if (lane == 0) base = atomicAdd(counters + 1, (unsigned long long)qn);
                     base = shfl_u64(base, 0);
-                    for (uint32_t k = lane; k < qn; k += 32u)
-                        if (base + k < cap) edges[base + k] = myq[k];
+                    for (uint32_t k = lane; k < qn; k += 32u) {
+                        const unsigned long long ij = myq[k];
+                        if (base + k < cap) edges[base + k] = ij;
+                        // the hook of K6a (see k6_hook_min) on the way out: fire-and-forget, the unions follow in their own kernel
+                        if (parent != nullptr) atomicMin(parent + (uint32_t)ij, (uint32_t)(ij >> 32));
+                    }
                     __syncwarp();
                     qn = 0;
                 }
@@ -1136,36 +1176,35 @@ __global__ void __launch_bounds__(256) k56_rows(const __grid_constant__ TriGeom 
             bool keep = false;
             if (t) {
                 rows_seen++;
-                const uint32_t mn = min(ti, tj);
-                const uint32_t T = USE_MAX ? max(ti, tj) : mn;
+                const uint32_t mn_ = min(ti, tj);
+                const uint32_t T = USE_MAX ? max(ti, tj) : mn_;
                 // eligible for the exact integer form of `float32 quotient >= c*` (see k56_scan / make_scan_cut):
                 // S < 2^24, 0 < T < 2^24, no zero total
-                const bool ok = fast && (uint32_t)(v >> 24) == 0u && (uint32_t)(v >> 32) == 0u && T - 1u < (1u << 24) - 1u && (!USE_MAX || mn != 0u);
+                const bool ok = fast && (uint32_t)(v >> 24) == 0u && (uint32_t)(v >> 32) == 0u && T - 1u < (1u << 24) - 1u && (!USE_MAX || mn_ != 0u);
                 if (ok) keep = v >= ((cm * T + cadd) >> cshift);
                 else keep = k56_keep_slow(v, ti, tj, dist_col, cstar);
             }
             enqueue(keep, x);
         };
-        const CT* vp = reinterpret_cast<const CT*>(G.tri) + c0 + lane;
-        const uint32_t* tp = totals + lo + lane;
         // Whole groups of 128 cells whose sums and totals are all below 2^24 take the integer test without any per-cell
         // eligibility check: a cell is touched iff it is non-zero (no zero-weight colours in this variant), and a zero
         // total needs no special case -- S / 0 = inf >= c* is what S * 2^shift >= M * 0 says too.  c* <= 2^7 makes the
         // threshold on S fit 32 bits (M T < 2^50, shift >= 18).
         const bool row_fast = !TOUCHED && fast && cshift >= 18u && (USE_MAX || ti < (1u << 24));
-        uint32_t x0 = 0;
-        for (; x0 + 128u <= len; x0 += 128u) {  // four full steps in flight, no bounds
-            const CT v0 = vp[x0], v1 = vp[x0 + 32u], v2 = vp[x0 + 64u], v3 = vp[x0 + 96u];
-            const uint32_t t0 = __ldg(tp + x0), t1 = __ldg(tp + x0 + 32u), t2 = __ldg(tp + x0 + 64u), t3 = __ldg(tp + x0 + 96u);
+        for (uint32_t x0 = 0; x0 < len; x0 += 128u) {
+            Group gn{};
+            if (x0 + 128u < len) gn = load_group(m, x0 + 128u);
+            else if (has_next && mn.len) gn = load_group(mn, 0u);   // the next row's first group
             bool small = row_fast;
             if (row_fast) {
-                const unsigned long long vo = (unsigned long long)(v0 | v1 | v2 | v3);
+                const unsigned long long vo = (unsigned long long)(g.v0 | g.v1 | g.v2 | g.v3);
                 small = (vo >> 24) == 0ull;
-                if (USE_MAX) small = small && ((t0 | t1 | t2 | t3) >> 24) == 0u;
+                if (USE_MAX) small = small && ((g.t0 | g.t1 | g.t2 | g.t3) >> 24) == 0u;
             }
             if (__all_sync(KSB_FULL, small)) {
-                const CT vv[4] = {v0, v1, v2, v3};
-                const uint32_t tt[4] = {t0, t1, t2, t3};
+                const CT vv[4] = {g.v0, g.v1, g.v2, g.v3};
+                const uint32_t tt[4] = {g.t0, g.t1, g.t2, g.t3};
+                bool kp[4];
 #pragma unroll
                 for (uint32_t u = 0; u < 4; u++) {
                     const uint32_t S = (uint32_t)vv[u];
@@ -1173,37 +1212,33 @@ __global__ void __launch_bounds__(256) k56_rows(const __grid_constant__ TriGeom 
                     const uint32_t thr = (uint32_t)((cm * T + cadd) >> cshift);
                     const bool nz = S != 0u;
                     rows_seen += nz ? 1u : 0u;
-                    enqueue(nz && S >= thr, x0 + 32u * u + lane);
+                    kp[u] = nz && S >= thr;
+                }
+                if (__any_sync(KSB_FULL, kp[0] || kp[1] || kp[2] || kp[3])) {  // most groups keep nothing: one vote instead of four
+#pragma unroll
+                    for (uint32_t u = 0; u < 4; u++) enqueue(kp[u], x0 + 32u * u + lane);
                 }
             } else {
-                cell(v0, t0, x0 + lane, true);
-                cell(v1, t1, x0 + 32u + lane, true);
-                cell(v2, t2, x0 + 64u + lane, true);
-                cell(v3, t3, x0 + 96u + lane, true);
+                const uint32_t x = x0 + lane;
+                cell(g.v0, g.t0, x, x < len);
+                if (x0 + 32u < len) cell(g.v1, g.t1, x + 32u, x + 32u < len);   // warp-uniform
+                if (x0 + 64u < len) cell(g.v2, g.t2, x + 64u, x + 64u < len);
+                if (x0 + 96u < len) cell(g.v3, g.t3, x + 96u, x + 96u < len);
             }
+            g = gn;
         }
-        if (x0 < len) {  // the row's last, partial group
-            unsigned long long v[4];
-            uint32_t tj[4];
-#pragma unroll
-            for (uint32_t u = 0; u < 4; u++) {
-                const uint32_t x = x0 + 32u * u + lane;
-                v[u] = x < len ? vp[x0 + 32u * u] : 0ull;
-                tj[u] = x < len ? __ldg(tp + x0 + 32u * u) : 1u;
-            }
-#pragma unroll
-            for (uint32_t u = 0; u < 4; u++) {
-                if (x0 + 32u * u >= len) break;  // warp-uniform
-                cell(v[u], tj[u], x0 + 32u * u + lane, x0 + 32u * u + lane < len);
-            }
-        }
+        if (len == 0u && has_next && mn.len) g = load_group(mn, 0u);  // an empty row prefetched nothing
+        m = mn;
     }
     if (qn) {
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(counters + 1, (unsigned long long)qn);
         base = shfl_u64(base, 0);
-        for (uint32_t k = lane; k < qn; k += 32u)
-            if (base + k < cap) edges[base + k] = myq[k];
+        for (uint32_t k = lane; k < qn; k += 32u) {
+            const unsigned long long ij = myq[k];
+            if (base + k < cap) edges[base + k] = ij;
+            if (parent != nullptr) atomicMin(parent + (uint32_t)ij, (uint32_t)(ij >> 32));
+        }
     }
     rows_seen = __reduce_add_sync(KSB_FULL, rows_seen);
     __syncthreads();
@@ -1217,18 +1252,26 @@ __global__ void __launch_bounds__(256) k6_edges_hook(const unsigned long long* _
                                                      const unsigned long long* __restrict__ counters, uint32_t* parent) {
     const unsigned long long n = min(__ldg(counters + 1), cap);
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
-        const unsigned long long ij = __ldg(edges + r);
-        atomicMin(parent + (uint32_t)ij, (uint32_t)(ij >> 32));
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += 4ull * stride) {
+        unsigned long long ij[4];  // four independent loads in flight per thread
+#pragma unroll
+        for (uint32_t u = 0; u < 4; u++) ij[u] = r + u * stride < n ? __ldg(edges + r + u * stride) : ~0ull;
+#pragma unroll
+        for (uint32_t u = 0; u < 4; u++)
+            if (ij[u] != ~0ull) atomicMin(parent + (uint32_t)ij[u], (uint32_t)(ij[u] >> 32));
     }
 }
 __global__ void __launch_bounds__(256) k6_edges_union(const unsigned long long* __restrict__ edges, unsigned long long cap,
                                                       const unsigned long long* __restrict__ counters, uint32_t* parent) {
     const unsigned long long n = min(__ldg(counters + 1), cap);
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
-        const unsigned long long ij = __ldg(edges + r);
-        uf_union(parent, (uint32_t)(ij >> 32), (uint32_t)ij);
+    for (unsigned long long r = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += 4ull * stride) {
+        unsigned long long ij[4];
+#pragma unroll
+        for (uint32_t u = 0; u < 4; u++) ij[u] = r + u * stride < n ? __ldg(edges + r + u * stride) : ~0ull;
+#pragma unroll
+        for (uint32_t u = 0; u < 4; u++)
+            if (ij[u] != ~0ull) uf_union(parent, (uint32_t)(ij[u] >> 32), (uint32_t)ij[u]);
     }
 }
 
@@ -1260,26 +1303,34 @@ static ScanCut make_scan_cut(int dist_col, float cstar) {
     return c;
 }
 
+// row-wise scan unless the rows are too short to feed a warp (fewer than 32 cells per owned row on average) or
+// KSPIDER_K56=scan asks for the chunk-wise kernel; KSPIDER_K56=rows forces it; k56_scan stages u64 cells only
+bool k56_uses_rows(const TriGeom& g) {
+    static const int mode = [] { const char* v = std::getenv("KSPIDER_K56"); return !v ? 0 : (!std::strcmp(v, "scan") ? 1 : (!std::strcmp(v, "rows") ? 2 : 0)); }();
+    return mode == 2 || g.cell_bits == 32 || (mode == 0 && g.cells >= 32ull * g.nrows);
+}
+
 cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, const uint32_t* block_rows, const uint32_t* totals,
                             int dist_col, float cstar, unsigned long long* edges, unsigned long long cap,
-                            unsigned long long* counters, const LaunchCfg& lc) {
+                            unsigned long long* counters, uint32_t* parent, const LaunchCfg& lc) {
     const uint64_t nb = post_blocks(g.cells);
     if (nb == 0) return cudaSuccess;
     const ScanCut cut = make_scan_cut(dist_col, cstar);
-    // row-wise scan unless the rows are too short to feed a warp (fewer than 32 cells per owned row on average) or
-    // KSPIDER_K56=scan asks for the chunk-wise kernel; KSPIDER_K56=rows forces it
-    static const int mode = [] { const char* v = std::getenv("KSPIDER_K56"); return !v ? 0 : (!std::strcmp(v, "scan") ? 1 : (!std::strcmp(v, "rows") ? 2 : 0)); }();
-    if (mode == 2 || g.cell_bits == 32 || (mode == 0 && g.cells >= 32ull * g.nrows)) {  // k56_scan stages u64 cells only
-        // persistent warps: exactly the CTAs that are resident at once (the kernel's registers allow 5 per SM)
-        static const int per_sm = [] {
-            int n = 0;
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k56_rows<false, false, unsigned long long>, 256, 0) != cudaSuccess || n < 1) { (void)cudaGetLastError(); n = 4; }
-            return n < (int)kRowsCtasPerSm ? n : (int)kRowsCtasPerSm;
-        }();
-        const uint64_t want = ((uint64_t)g.nrows + 7) / 8, capr = (uint64_t)lc.sms * (uint64_t)per_sm;
-        const unsigned ctas = (unsigned)(want < capr ? want : capr);
-        auto go = [&](auto kern) { kern<<<ctas, 256, 0, lc.stream>>>(g, touched_bits, totals, dist_col, cstar, cut, edges, cap, counters); };
+    if (k56_uses_rows(g)) {
+        // persistent warps: exactly the CTAs that are resident at once (the variant's registers decide: 4 or 5 per SM)
+        const uint64_t want = ((uint64_t)g.nrows + 7) / 8;
         const int variant = (touched_bits ? 4 : 0) | (cut.use_max ? 2 : 0) | (g.cell_bits == 32 ? 1 : 0);
+        static int per_sm[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // per kernel variant (the variants share one function-pointer type)
+        auto go = [&](auto kern) {
+            int& ps = per_sm[variant];
+            if (ps == 0) {
+                int n = 0;
+                if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, 256, 0) != cudaSuccess || n < 1) { (void)cudaGetLastError(); n = 4; }
+                ps = n < (int)kRowsCtasPerSm ? n : (int)kRowsCtasPerSm;
+            }
+            const uint64_t capr = (uint64_t)lc.sms * (uint64_t)ps;
+            kern<<<(unsigned)(want < capr ? want : capr), 256, 0, lc.stream>>>(g, touched_bits, totals, dist_col, cstar, cut, edges, cap, counters, parent);
+        };
         switch (variant) {
             case 0: go(k56_rows<false, false, unsigned long long>); break;
             case 1: go(k56_rows<false, false, uint32_t>); break;
@@ -1298,10 +1349,10 @@ cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, cons
     return cudaGetLastError();
 }
 cudaError_t launch_k6_edges(const unsigned long long* edges, unsigned long long cap, const unsigned long long* counters,
-                            uint32_t* parent, uint64_t expect, const LaunchCfg& lc) {
+                            uint32_t* parent, uint64_t expect, bool hooked, const LaunchCfg& lc) {
     const unsigned long long want = (std::max<uint64_t>(expect, 1) + 255) / 256, capc = (unsigned long long)lc.sms * 8ull;
     const unsigned ctas = (unsigned)(want < capc ? want : capc);
-    k6_edges_hook<<<ctas, 256, 0, lc.stream>>>(edges, cap, counters, parent);
+    if (!hooked) k6_edges_hook<<<ctas, 256, 0, lc.stream>>>(edges, cap, counters, parent);  // k56_rows hooks while it appends
     k6_edges_union<<<ctas, 256, 0, lc.stream>>>(edges, cap, counters, parent);
     return cudaGetLastError();
 }

@@ -161,9 +161,11 @@ cudaError_t launch_k5_emit(const TriGeom& g, const uint32_t* touched_bits, const
 // K56: cluster-only scan (containment + threshold + append of the kept pairs only) and the edge-list unions
 cudaError_t launch_k56_scan(const TriGeom& g, const uint32_t* touched_bits, const uint32_t* block_rows, const uint32_t* totals,
                             int dist_col, float cstar, unsigned long long* edges, unsigned long long cap,
-                            unsigned long long* counters, const LaunchCfg& lc);
+                            unsigned long long* counters, uint32_t* parent, const LaunchCfg& lc);
+// true: the pass is scanned row by row (k56_rows: needs no block_rows table, and hooks the kept edges into `parent` itself)
+bool k56_uses_rows(const TriGeom& g);
 cudaError_t launch_k6_edges(const unsigned long long* edges, unsigned long long cap, const unsigned long long* counters,
-                            uint32_t* parent, uint64_t expect, const LaunchCfg& lc);
+                            uint32_t* parent, uint64_t expect, bool hooked, const LaunchCfg& lc);
 
 // K6+K7
 cudaError_t launch_k67_union(const ksb_record* records, const unsigned long long* pairs, const float* colvals, uint64_t n_rows,
