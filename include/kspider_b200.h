@@ -365,6 +365,9 @@ int ksb_write_sidecar(const ksb_result* r, const char* path, const char* tsv_pat
 int ksb_write_sidecar_records(const ksb_record* records, uint64_t n_rows, const char* path, uint64_t tsv_bytes,
                               uint64_t tsv_mtime_ns, int append);
 int ksb_sidecar_matches(const char* sidecar, const char* pairwise_tsv);
+/* names the (finished) TSV a side-car belongs to: size and modification time into its header.  ksb_dropin_pairwise writes
+ * the TSV and the side-car at the same time and stamps the side-car when both are complete. */
+int ksb_sidecar_stamp(const char* sidecar, const char* pairwise_tsv);
 int ksb_cluster_table(const ksb_table* t, uint64_t n_nodes, double cut_pct, int device, uint32_t* labels_out,
                       uint64_t* n_edges);
 int ksb_ani_table(const ksb_table* t, int ksize, int device, double* ani_out, uint64_t* n_invalid);

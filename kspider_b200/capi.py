@@ -131,6 +131,7 @@ _PROTOS = {
     "ksb_write_sidecar": (C.c_int, [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int]),
     "ksb_write_sidecar_records": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_uint64, C.c_uint64, C.c_int]),
     "ksb_sidecar_matches": (C.c_int, [C.c_char_p, C.c_char_p]),
+    "ksb_sidecar_stamp": (C.c_int, [C.c_char_p, C.c_char_p]),
     "ksb_cluster_table": (C.c_int, [C.c_void_p, C.c_uint64, C.c_double, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_ani_table": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_cluster_edges_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double,

@@ -243,6 +243,12 @@ int check_device(int device, int* sms) {
 
 cudaStream_t service_stream(int dev) { return g_ctx[dev].stream; }
 
+int warm_device(int device) {
+    const int dev = check_device(device, nullptr);
+    if (dev < 0) return dev;
+    return cudaFree(nullptr) == cudaSuccess ? KSB_OK : KSB_ERR_CUDA;
+}
+
 static void build_k1(ksb_device* d) {
     K1Params& p = d->k1;
     std::memset(&p, 0, sizeof p);

@@ -33,8 +33,14 @@ void pairwise(std::string index_prefix, int user_threads) {
     // the reference prints three load timers (src/pairwise.cpp:133,155,181); the loader does the
     // three loads in one call, so the first line carries the time and the other two are ~0
     auto t0 = Clock::now();
+    // the CUDA contexts come up (~0.25 s each) while the index files are parsed; an error here is reported by the run itself
+    std::vector<std::thread> warm;
+    for (int g = 0; g < gpus; g++) warm.emplace_back([=] { (void)ksb::warm_device(dev0 + g); });
     ksb_index* ix = nullptr;
-    if (ksb_index_load(index_prefix.c_str(), threads, &ix) != KSB_OK) fail("loading the index");
+    const int lrc = ksb_index_load(index_prefix.c_str(), threads, &ix);
+    const std::string lerr = lrc == KSB_OK ? "" : ksb_last_error();
+    for (auto& t : warm) t.join();
+    if (lrc != KSB_OK) { ksb::set_error("%s", lerr.c_str()); fail("loading the index"); }
     t_load = secs_since(t0);
     std::cout << "mapping colors to groups: " << t_load << " secs" << std::endl;
     t0 = Clock::now();
@@ -84,20 +90,41 @@ void pairwise(std::string index_prefix, int user_threads) {
     std::cout << "writing pairwise matrix to " << out << std::endl;
     int rc = KSB_OK;
     t0 = Clock::now();
+    // binary side-car for `cluster` / `--estimate-ani` (they then skip the text): the same rows, 32 bytes each, written by a
+    // thread of its own while the TSV is formatted, and stamped with the TSV's size and time once both are complete
+    const char* sc = std::getenv("KSPIDER_SIDECAR");
+    const bool want_side = !(sc && sc[0] == '0');
+    const std::string side = index_prefix + "_kSpider_pairwise.ksb";
+    int side_rc = KSB_OK;
+    std::string side_err;
+    double side_secs = 0;
+    std::thread side_writer;
+    if (want_side)
+        side_writer = std::thread([&] {
+            const auto ts = Clock::now();
+            for (int g = 0; g < gpus && side_rc == KSB_OK; g++) {
+                uint64_t n = 0;
+                const ksb_record* rec = ksb_result_records(res[g], &n);
+                side_rc = ksb_write_sidecar_records(rec, n, side.c_str(), 0, 0, g != 0);
+            }
+            if (side_rc != KSB_OK) side_err = ksb_last_error();
+            side_secs = secs_since(ts);
+        });
     for (int g = 0; g < gpus && rc == KSB_OK; g++)
         rc = g == 0 ? ksb_write_tsv(res[g], out.c_str(), threads) : ksb_append_tsv(res[g], out.c_str(), threads);
     t_tsv = secs_since(t0);
+    std::string tsv_err = rc == KSB_OK ? "" : ksb_last_error();
     t0 = Clock::now();
-    // binary side-car for `cluster` / `--estimate-ani` (they then skip the text): the same rows, 32 bytes each
-    const char* sc = std::getenv("KSPIDER_SIDECAR");
-    if (rc == KSB_OK && !(sc && sc[0] == '0')) {
-        const std::string side = index_prefix + "_kSpider_pairwise.ksb";
-        for (int g = 0; g < gpus && rc == KSB_OK; g++) rc = ksb_write_sidecar(res[g], side.c_str(), out.c_str(), g != 0);
+    if (want_side) {
+        side_writer.join();
+        if (rc == KSB_OK && side_rc != KSB_OK) { rc = side_rc; tsv_err = side_err; }
+        if (rc == KSB_OK) { rc = ksb_sidecar_stamp(side.c_str(), out.c_str()); if (rc != KSB_OK) tsv_err = ksb_last_error(); }
     }
-    t_side = secs_since(t0);
+    t_side = secs_since(t0);  // what the side-car adds to the wall time (its writing overlaps the TSV: side_secs)
+    (void)side_secs;
     if (verbose) std::cerr << "ksb_phases load_s=" << t_load << " seq_to_kmers_s=" << t_seq << " gpu_s=" << t_gpu << " tsv_s=" << t_tsv
                            << " sidecar_s=" << t_side << std::endl;
-    const std::string err = rc == KSB_OK ? "" : ksb_last_error();
+    const std::string err = tsv_err;
     for (auto* r : res) ksb_result_free(r);
     ksb_index_free(ix);
     if (rc != KSB_OK) throw std::runtime_error("kSpider::pairwise: writing " + out + ": " + err);

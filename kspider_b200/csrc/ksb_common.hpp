@@ -150,6 +150,11 @@ inline uint64_t gram_member_bits(const IndexDesc& d) { return d.gram_rel_bits ? 
 
 }  // namespace ksb
 
+namespace ksb {
+// creates the CUDA context of `device` (device_api.cu): the drop-in calls it on a thread of its own while the index files are parsed
+int warm_device(int device);
+}  // namespace ksb
+
 struct ksb_index {
     ksb::IndexDesc desc;
     uint8_t* payload = nullptr;

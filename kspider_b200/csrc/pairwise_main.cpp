@@ -3,6 +3,8 @@
 #include <exception>
 #include <string>
 
+#include <unistd.h>
+
 #include "kspider_dropin.hpp"
 
 int main(int argc, char** argv) {
@@ -13,5 +15,8 @@ int main(int argc, char** argv) {
         std::fprintf(stderr, "%s\n", e.what());
         return 1;
     }
-    return 0;
+    // both TSVs are written and closed: leave without tearing down the CUDA context and the pinned buffers one by one
+    // (~0.2 s of the binary's wall time on a 100 000-sample index)
+    std::fflush(nullptr);
+    _exit(0);
 }

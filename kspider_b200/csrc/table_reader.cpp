@@ -318,6 +318,24 @@ int ksb_write_sidecar(const ksb_result* r, const char* path, const char* tsv_pat
     return ksb_write_sidecar_records(rec, n, path, (uint64_t)st.st_size, (uint64_t)st.st_mtim.tv_sec * 1000000000ull + (uint64_t)st.st_mtim.tv_nsec, append);
 }
 
+// Re-stamps a side-car with the size and modification time of the TSV it belongs to: the drop-in writes both files at the
+// same time (two threads) and can only name the finished TSV afterwards.
+int ksb_sidecar_stamp(const char* sidecar, const char* pairwise_tsv) {
+    if (!sidecar || !pairwise_tsv) { set_error("ksb_sidecar_stamp: null argument"); return KSB_ERR_ARG; }
+    struct stat st;
+    if (stat(pairwise_tsv, &st) != 0) { set_error("ksb_sidecar_stamp: cannot stat %s: %s", pairwise_tsv, strerror(errno)); return KSB_ERR_IO; }
+    FILE* f = fopen(sidecar, "r+b");
+    SidecarHeader h{};
+    if (!f || fread(&h, sizeof h, 1, f) != 1 || h.magic != kSideMagic) { if (f) fclose(f); set_error("%s: not a side-car", sidecar); return KSB_ERR_IO; }
+    h.tsv_bytes = (uint64_t)st.st_size;
+    h.tsv_mtime_ns = (uint64_t)st.st_mtim.tv_sec * 1000000000ull + (uint64_t)st.st_mtim.tv_nsec;
+    int rc = KSB_OK;
+    if (fseek(f, 0, SEEK_SET) != 0 || fwrite(&h, sizeof h, 1, f) != 1) rc = KSB_ERR_IO;
+    if (fclose(f) != 0) rc = KSB_ERR_IO;
+    if (rc) set_error("write error on %s", sidecar);
+    return rc;
+}
+
 int ksb_sidecar_matches(const char* sidecar, const char* pairwise_tsv) {
     if (!sidecar || !pairwise_tsv) return 0;
     struct stat st, ss;
