@@ -549,8 +549,13 @@ static int opts_common(ksb_device* d, const ksb_opts* opts) {
 // small-colour classes from the largest size down in a few chunks, the order K1 consumes them, an event behind each.
 static int enqueue_copy_all(ksb_device* d, const ksb_index* ix) {
     const IndexDesc& D = d->desc;
-    KSB_CUDA(pool_stream(d->device, &d->copy_stream));
-    for (auto& e : d->ev_copy) KSB_CUDA(pool_event(d->device, &e));
+    // a handle that ksb_pairwise_cluster kept from its last call uploads again with the stream and events it has
+    const bool again = d->copy_stream != nullptr;
+    if (!again) {
+        KSB_CUDA(pool_stream(d->device, &d->copy_stream));
+        for (auto& e : d->ev_copy) KSB_CUDA(pool_event(d->device, &e));
+    }
+    size_t n_gram_ev = 0, n_k1_ev = 0;
     cudaStream_t cs = d->copy_stream;
     cudaEvent_t alloc = nullptr;  // d_payload was allocated in stream order on d->stream
     KSB_CUDA(pool_event(d->device, &alloc, false));
@@ -570,11 +575,13 @@ static int enqueue_copy_all(ksb_device* d, const ksb_index* ix) {
     for (uint64_t b = D.off_gram_members; b < D.off_gram_weights; b += piece) {
         const uint64_t e = std::min<uint64_t>(b + piece, D.off_gram_weights);
         KSB_CUDA(copy(b, e));
-        cudaEvent_t ev = nullptr;
-        KSB_CUDA(pool_event(d->device, &ev, false));
-        d->gram_ev_own.push_back(ev);
-        d->gram_piece_end.push_back(e);
-        KSB_CUDA(cudaEventRecord(ev, cs));
+        if (n_gram_ev == d->gram_ev_own.size()) {
+            cudaEvent_t ev = nullptr;
+            KSB_CUDA(pool_event(d->device, &ev, false));
+            d->gram_ev_own.push_back(ev);
+            d->gram_piece_end.push_back(e);
+        }
+        KSB_CUDA(cudaEventRecord(d->gram_ev_own[n_gram_ev++], cs));
     }
     build_k1(d);  // depends on the descriptor only
     const uint64_t mbits = D.packed_bits, wbytes = D.weight_bits / 8;
@@ -589,13 +596,15 @@ static int enqueue_copy_all(ksb_device* d, const ksb_index* ix) {
         const K1Class &hi = k1.cls[c], &lo = k1.cls[e - 1];
         KSB_CUDA(copy(D.off_small_members + mbits * lo.member_off / 8, D.off_small_members + (mbits * (hi.member_off + hi.n * hi.s) + 7) / 8 + 1));
         KSB_CUDA(copy(D.off_small_weights + wbytes * lo.weight_off, D.off_small_weights + wbytes * (hi.weight_off + hi.n)));
-        ksb_device::k1_piece pc;
-        pc.ev = nullptr;
-        KSB_CUDA(pool_event(d->device, &pc.ev, false));
-        KSB_CUDA(cudaEventRecord(pc.ev, cs));
-        pc.task_begin = hi.task_begin;
-        pc.task_end = e < k1.n_cls ? k1.cls[e].task_begin : k1.n_tasks;
-        d->k1_pieces.push_back(pc);
+        if (n_k1_ev == d->k1_pieces.size()) {
+            ksb_device::k1_piece pc;
+            pc.ev = nullptr;
+            KSB_CUDA(pool_event(d->device, &pc.ev, false));
+            pc.task_begin = hi.task_begin;
+            pc.task_end = e < k1.n_cls ? k1.cls[e].task_begin : k1.n_tasks;
+            d->k1_pieces.push_back(pc);
+        }
+        KSB_CUDA(cudaEventRecord(d->k1_pieces[n_k1_ev++].ev, cs));
         c = e;
     }
     KSB_CUDA(cudaEventRecord(d->ev_copy[3], cs));
@@ -1738,6 +1747,38 @@ int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out) {
 // upload + cluster-only step + release in one call: the end-to-end path when only the labels are wanted
 // (host index in, N labels out; H2D = the blob, D2H = 4 N + 16 bytes).  A device that has to spill falls back to
 // the record path on the device (sort-reduce run, then K6 + K7 over its records).
+// ksb_pairwise_cluster keeps the device handle of its last call on an index -- allocations, row passes, K4 plan and
+// its tables, streams and events; nothing of the RESULT -- in the index (ksb_index::dev_cache; released with it).  The next
+// call with the same options uploads the blob again (the inputs travel host -> device in every call) and runs: what a caller
+// pays per call is the copy and the kernels, not 0.3-0.8 ms of host-side planning that depends on how busy the host is.
+// KSPIDER_E2E_CACHE=0 disables.
+struct E2eCache {
+    std::mutex mu;
+    ksb_device* dev = nullptr;
+    bool in_use = false;
+    ksb_opts key{};
+};
+static void e2e_cache_free(void* p) {
+    E2eCache* c = static_cast<E2eCache*>(p);
+    if (!c) return;
+    if (c->dev) ksb_device_free(c->dev);
+    delete c;
+}
+static std::mutex g_e2e_mu;  // guards the creation of an index's cache object
+static E2eCache* e2e_cache_of(const ksb_index* ix) {
+    static const bool on = [] { const char* v = std::getenv("KSPIDER_E2E_CACHE"); return !(v && v[0] == '0'); }();
+    if (!on || !ix->pinned) return nullptr;
+    std::lock_guard<std::mutex> lk(g_e2e_mu);
+    if (!ix->dev_cache) {
+        ix->dev_cache = new (std::nothrow) E2eCache();
+        ix->dev_cache_free = e2e_cache_free;
+    }
+    return static_cast<E2eCache*>(ix->dev_cache);
+}
+static bool same_opts(const ksb_opts& a, const ksb_opts& b) {
+    return a.device == b.device && a.rank == b.rank && a.world == b.world && a.dense_budget_bytes == b.dense_budget_bytes && a.spill_mode == b.spill_mode;
+}
+
 int ksb_pairwise_cluster(const ksb_index* ix, const ksb_opts* opts, int dist_col, double cut_pct, uint32_t* labels_out,
                          uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows, ksb_result_info* info_out) {
     if (!ix || (!labels_out && !d_labels_out)) { set_error("ksb_pairwise_cluster: null argument"); return KSB_ERR_ARG; }
@@ -1745,8 +1786,42 @@ int ksb_pairwise_cluster(const ksb_index* ix, const ksb_opts* opts, int dist_col
     auto ms_since = [](Clock::time_point t) { return std::chrono::duration<float, std::milli>(Clock::now() - t).count(); };
     ksb_device* d = nullptr;
     auto t0 = Clock::now();
-    int rc = upload_impl(ix, opts, &d, true);
-    if (rc) return rc;
+    ksb_opts key{};
+    if (opts) key = *opts;
+    else key.device = -1;
+    if (key.device < 0) { int cur = 0; if (cudaGetDevice(&cur) == cudaSuccess) key.device = cur; else (void)cudaGetLastError(); }
+    if (key.world <= 1) { key.world = 1; key.rank = 0; }
+    E2eCache* cache = e2e_cache_of(ix);
+    bool cached = false, holds_slot = false;
+    if (cache) {
+        std::lock_guard<std::mutex> lk(cache->mu);
+        if (!cache->in_use) {
+            cache->in_use = holds_slot = true;
+            if (cache->dev && same_opts(cache->key, key)) { d = cache->dev; cache->dev = nullptr; cached = true; }
+            else if (cache->dev) { ksb_device_free(cache->dev); cache->dev = nullptr; }
+        }
+    }
+    auto release_slot = [&](ksb_device* keep) {
+        if (!holds_slot) { if (keep) ksb_device_free(keep); return; }
+        std::lock_guard<std::mutex> lk(cache->mu);
+        cache->dev = keep;
+        cache->key = key;
+        cache->in_use = false;
+    };
+    int rc = KSB_OK;
+    if (cached) {
+        // the kept handle: fresh timers, the blob on its way again, the first pass's K4 chunks mapped to the copy pieces
+        rc = cudaSetDevice(d->device) == cudaSuccess ? KSB_OK : KSB_ERR_CUDA;
+        std::memset(&d->t, 0, sizeof d->t);
+        d->launches = 0;
+        d->cur_pass = 0;
+        if (rc == KSB_OK) rc = enqueue_copy_all(d, ix);
+        if (rc == KSB_OK) map_gram_pieces(d, ix);
+        if (rc != KSB_OK) { release_slot(nullptr); ksb_device_free(d); return rc; }
+    } else {
+        rc = upload_impl(ix, opts, &d, true);
+        if (rc) { release_slot(nullptr); return rc; }
+    }
     const float setup_ms = ms_since(t0);
     t0 = Clock::now();
     ksb_result_info info;
@@ -1769,7 +1844,8 @@ int ksb_pairwise_cluster(const ksb_index* ix, const ksb_opts* opts, int dist_col
     }
     const float step_ms = ms_since(t0);
     t0 = Clock::now();
-    ksb_device_free(d);
+    if (rc == KSB_OK && !d->spill && holds_slot) release_slot(d);  // kept for the next call on this index
+    else { release_slot(nullptr); ksb_device_free(d); }
     if (rc) return rc;
     info.t.host_setup_ms = setup_ms;
     info.t.host_accumulate_ms = step_ms;

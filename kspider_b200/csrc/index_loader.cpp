@@ -1326,6 +1326,7 @@ int ksb_write_seq_to_kmers(const ksb_index* ix, const char* path) {
 
 void ksb_index_free(ksb_index* ix) {
     if (!ix) return;
+    if (ix->dev_cache && ix->dev_cache_free) ix->dev_cache_free(ix->dev_cache);
     if (ix->payload) {
         if (ix->pinned) cudaFreeHost(ix->payload); else free(ix->payload);
     }

@@ -159,6 +159,10 @@ struct ksb_index {
     ksb::IndexDesc desc;
     uint8_t* payload = nullptr;
     bool pinned = false;
+    // ksb_pairwise_cluster keeps the device handle of its last call on this index (allocations, row passes, K4 plan):
+    // the next call with the same options only uploads the blob again and runs (device_api.cu; released with the index)
+    mutable void* dev_cache = nullptr;
+    mutable void (*dev_cache_free)(void*) = nullptr;
     // totals file in slot order, for the seqToKmersNo.tsv writer (src/pairwise.cpp:173-180)
     std::vector<uint32_t> totals_file_ids, totals_file_vals;
 };
