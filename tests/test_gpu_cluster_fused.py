@@ -114,3 +114,41 @@ def test_graph_replay_equals_kernel_by_kernel(ksb):
     lab, ne, nr = dev.cluster(400, "min_cont", 0.1)
     ref, ref_ne, ref_rows = oracle_labels(csr, idx.sample_ids, "min_cont", 0.1)
     assert (ne, nr) == (ref_ne, ref_rows) and np.array_equal(lab, ref)
+
+
+def test_end_to_end_call_reuses_its_device_handle(ksb, monkeypatch):
+    """ksb_pairwise_cluster keeps the device handle of its last call in the index and only uploads the blob again: calls
+    in a row with other thresholds and columns, other options (which replace the kept handle), a dense budget that needs
+    several passes, row blocks, and a different index in between all give the oracle's labels; so does the call with the
+    cache switched off."""
+    csr = spread_totals(random_csr(seed=61, n_samples=380, n_colors=2200, s_lo=2, s_hi=9, zero_every=19, big=(80, 200, 370)), 61)
+    other = spread_totals(random_csr(seed=62, n_samples=150, n_colors=500, s_lo=2, s_hi=6), 62)
+    idx = ksb.Index.from_csr(**csr)
+    idx2 = ksb.Index.from_csr(**other)
+    n, ids = int(idx.info.n_samples), idx.sample_ids
+
+    def call(ix, c, dist, cutoff, **kw):
+        labels, ne, nr, info = ix.pairwise_cluster(dist, cutoff, **kw)
+        want, want_ne, want_rows = oracle_labels(c, ix.sample_ids, dist, cutoff)
+        assert (ne, nr) == (want_ne, want_rows) and np.array_equal(labels, want), (dist, cutoff, kw)
+        return info
+
+    first = call(idx, csr, "max_cont", 0.05)
+    again = call(idx, csr, "max_cont", 0.05)
+    assert again.t.host_setup_ms < first.t.host_setup_ms       # nothing is planned or allocated the second time
+    for dist in ("min_cont", "avg_cont", "max_cont"):
+        for cutoff in (0.0, 0.2, 1.0):
+            call(idx, csr, dist, cutoff)
+    call(idx2, other, "max_cont", 0.1)                          # another index has its own handle
+    call(idx, csr, "max_cont", 0.3, dense_budget_bytes=120_000)  # other options: the kept handle is replaced
+    call(idx, csr, "max_cont", 0.3, dense_budget_bytes=120_000)
+    call(idx, csr, "min_cont", 0.1)
+    # row blocks: each call returns the labels of its own rows' edges; merged they are the whole partition
+    parts = [idx.pairwise_cluster("max_cont", 0.05, rank=r, world=2)[0] for r in range(2)]
+    merged = ksb.cluster_merge(parts[0], parts[1]) if hasattr(ksb, "cluster_merge") else None
+    if merged is not None:
+        assert np.array_equal(merged, oracle_labels(csr, ids, "max_cont", 0.05)[0])
+    monkeypatch.setenv("KSPIDER_E2E_CACHE", "0")                # read once per process: a fresh index still answers the same
+    idx3 = ksb.Index.from_csr(**csr)
+    call(idx3, csr, "max_cont", 0.05)
+    idx.close(); idx2.close(); idx3.close()
