@@ -618,7 +618,7 @@ def main_b200(args):
         tr, trs = traffic_of(args.workload, "k56")
         kernels.append({"bound": "hbm", "kernel": "k56_rows / k56_scan (cluster-only post-pass)", "kernel_ms": alone["post_ms"], "achieved": kb / (alone["post_ms"] * 1e-3) / 1e9,
                         "peak": peak, "unit": "GB/s", "algorithmic_bytes": kb, "traffic": tr, "traffic_source": trs, "peak_source": peak_src,
-                        "bytes": "8 B per cell of the owned block (read once) + 8 B per kept edge"})
+                        "bytes": "8 B per cell of the owned block (read once) + 8 B per kept edge (algorithmic: u64 cells; with u32 cells the scan reads half of it)"})
     imma = None
     if C_gram and alone["gram_ms"] > 0:
         try:   # int8 tensor peak measured in this run, in K4's own instruction shape
@@ -639,7 +639,9 @@ def main_b200(args):
         # 8 B write of the accumulator) and every member is read once by the bitmap build
         g_bytes = 16.0 * CELLS_gram * own_frac + 4.0 * M_gram
         hbm = {"bound": "hbm", "achieved": g_bytes / (g_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "algorithmic_bytes": g_bytes,
-               "bytes": "16 B per cell a Gram window can update (n_gram_cells) + 4 B per member of the Gram colours", "peak_source": peak_src}
+               "bytes": "16 B per cell a Gram window can update (n_gram_cells) + 4 B per member of the Gram colours", "peak_source": peak_src,
+               "note": "ALGORITHMIC bytes (SURVEY 8d: a u64 cell read and written per update, members as u32).  With u32 cells and the "
+                       "bitmap form of the blob the launches move less than half of that (`traffic`), so this fraction can exceed 1."}
         hbm["frac"] = hbm["achieved"] / peak
         binding, other = (tensor, hbm) if tensor["frac"] >= hbm["frac"] else (hbm, tensor)
         entry = {"kernel": "k4_gram (+ kb_build)" if (gram_form & 1) == 0 else "k4_gram (+ kb_weights; the bitmaps are part of the resident blob)", "kernel_ms": g_ms, "traffic": tr, "traffic_source": trs,
