@@ -258,7 +258,11 @@ int ksb_pairwise(const ksb_index* ix, const ksb_opts* opts, ksb_result** out);
 /* upload + ksb_device_cluster + release in one call: host index in, cluster labels out -- the end-to-end path
  * when only the labels are wanted (H2D: the blob; D2H: 4 N + 16 bytes).  labels_out: host, d_labels_out: device
  * memory of opts->device (either may be NULL; the multi-GPU path merges the device copies).  info_out (optional): rows, updates,
- * launches, timings of the run.  A device that must spill runs the sort-reduce path and clusters its records. */
+ * launches, timings of the run.  A device that must spill runs the sort-reduce path and clusters its records.
+ * The call keeps the device handle it built (device allocations of the blob and the accumulator, row passes, the K4 plan,
+ * streams and events -- never a result) inside `ix` and releases it in ksb_index_free: the next call on the same index
+ * with the same device / rank / world / budget / spill mode uploads the blob again and runs, without planning or
+ * allocating anything.  KSPIDER_E2E_CACHE=0 builds and releases a handle per call. */
 int ksb_pairwise_cluster(const ksb_index* ix, const ksb_opts* opts, int dist_col, double cut_pct, uint32_t* labels_out,
                          uint32_t* d_labels_out, uint64_t* n_edges, uint64_t* n_rows, ksb_result_info* info_out);
 
