@@ -867,8 +867,9 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
         const uint64_t kb_max = std::max<uint64_t>(1, std::min<uint64_t>(16384, chunk_rows / w.width));
         for (uint64_t kb = 0; kb < kb_total; kb += kb_max) {
             const uint64_t kbs = std::min(kb_max, kb_total - kb);
-            if (cur.n_wins && cur.bits_rows + kbs * w.width > chunk_rows) { close_chunk(); new_chunk(w.c0 + kb * kGramKBlock); }
-            if (cur.n_wins == 0) { cur.c_begin = w.c0 + kb * kGramKBlock; cur.blob_row0 = win_row0 + kb * w.width; }
+            const uint64_t kpitch = bitmap_form ? gram_win_stride(w) : w.width;  // rows per K-block where the bitmap lives
+            if (cur.n_wins && cur.bits_rows + kbs * kpitch > chunk_rows) { close_chunk(); new_chunk(w.c0 + kb * kGramKBlock); }
+            if (cur.n_wins == 0) { cur.c_begin = w.c0 + kb * kGramKBlock; cur.blob_row0 = win_row0 + kb * kpitch; }
             GramWinDev wd;
             wd.c0 = w.c0 + kb * kGramKBlock;
             wd.n = (uint32_t)std::min<uint64_t>(kbs * kGramKBlock, w.n - kb * kGramKBlock);
@@ -878,12 +879,14 @@ static int plan_gram(ksb_device* d, uint32_t pass) {
             wd.tiles = tiles;
             wd.k0 = cur.kblocks;
             wd.extent = w.extent ? (uint32_t)std::min<uint64_t>(w.extent, w.width) : 0u;
+            wd.kstride = bitmap_form ? gram_win_stride(w) : w.width;
+            wd.pad = 0;
             cur.n_units += (uint32_t)kbs * ((w.width + kGramSeg - 1) / kGramSeg);
             wins.push_back(wd);
             wrows.push_back(rows);
             cur.n_wins++;
             cur.n_colors = wd.c0 + wd.n - cur.c_begin;
-            cur.bits_rows += kbs * w.width;
+            cur.bits_rows += kbs * kpitch;
             cur.kblocks += (uint32_t)kbs;
         }
     }

@@ -454,6 +454,7 @@ __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ Gr
                 const uint32_t tp = smem_a + warp * (32 * 17 * 4);  // stage memory is idle now
                 const uint32_t lq = warp & 3u, wg = warp >> 2;
                 const uint32_t rsel = lane >> 4, csel = lane & 15u;
+                const uint32_t ext = win.extent ? win.extent : win.width;
                 for (uint32_t ch = wg; ch < ncol * 8u; ch += 4) {
                     const uint32_t ct = ch >> 3, c16 = ch & 7u;
                     unsigned long long acc[16];
@@ -477,7 +478,7 @@ __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ Gr
                     for (uint32_t y = 0; y < 16; y++) {
                         const uint32_t il = i0 + 32u * lq + 2 * y + rsel;
                         const uint32_t i = win.x0 + il;
-                        if (il < jl && jl < win.width && j < G.n && acc[y] != 0ull) {
+                        if (il < jl && jl < ext && j < G.n && acc[y] != 0ull) {  // columns (hence rows) past the extent may hold foreign bits
                             const unsigned long long ra = gram_row_addr<C32>(i, G);
                             if (ra != 0ull) gram_red<C32>(ra, j, acc[y]);
                         }
@@ -523,7 +524,7 @@ __global__ void __maxnreg__(P == 4 ? 72 : 64) k4_gram(const __grid_constant__ Gr
                     const uint32_t slot = it % kRing;
                     const uint32_t bar = bar_ready0 + 8u * slot;
                     const uint32_t dst = smem_u32(ring + slot * kSlotBytes);
-                    const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.width) * 16ull;
+                    const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.kstride) * 16ull;
                     mbar_expect_tx(bar, bytes);
                     tma_load_1d(dst, kbase + (unsigned long long)i0 * 16ull, 2048u, bar);
                     tma_load_1d(dst + 2048u, kbase + (unsigned long long)j0 * 16ull, ncol * 2048u, bar);
@@ -698,7 +699,7 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
                     }
                     const uint32_t jl = col0 + csel;
                     const uint32_t j = win.x0 + jl;
-                    const bool col_ok = jl < win.width && j < G.n;
+                    const bool col_ok = jl < ext && j < G.n;  // columns (hence rows) past the extent may hold foreign bits
 #pragma unroll
                     for (uint32_t y = 0; y < 16; y++) {
                         const uint32_t src = 2 * y + rsel;
@@ -806,7 +807,7 @@ __global__ void __maxnreg__(64) k4_gram_pipe(const __grid_constant__ GramParams 
                     if (it >= kRing) mbar_wait(bar_rfree + 8u * slot, ((it / kRing) - 1u) & 1u);
                     const uint32_t bar = bar_ready + 8u * slot;
                     const uint32_t dst = ring_a + slot * kSlotBytes;
-                    const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.width) * 16ull;
+                    const uint8_t* kbase = gbits + (win.bits_off + (unsigned long long)kb * win.kstride) * 16ull;
                     mbar_expect_tx(bar, bytes);
                     tma_load_1d(dst, kbase + (unsigned long long)gi.i0 * 16ull, 2048u, bar);
                     tma_load_1d(dst + 2048u, kbase + (unsigned long long)gi.j0 * 16ull, ncol * 2048u, bar);

@@ -647,7 +647,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                 if (d.gram_form) {
                     const GramWin& gwn = gwins[gram_win_of[gkey[c]]];
                     const uint64_t lc = gkey[c] - gwn.c0;
-                    brow = gram_bits + 4 * (gram_off[gram_win_of[gkey[c]]] + (lc / kGramKBlock) * gwn.width) + ((lc % kGramKBlock) >> 5);
+                    brow = gram_bits + 4 * (gram_off[gram_win_of[gkey[c]]] + (lc / kGramKBlock) * gram_win_stride(gwn)) + ((lc % kGramKBlock) >> 5);
                     bbit = 1u << (lc & 31u);
                     rel0 = gwn.x0;
                     e0 = 0;
@@ -1009,8 +1009,9 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
                 for (uint64_t kb = 0; kb < kblocks; kb++) {
                     const uint64_t kn = std::min<uint64_t>(kGramKBlock, gw[w].n - kb * kGramKBlock);
                     for (uint64_t k = 0; k < kn; k++) lists[k].clear();
-                    const uint32_t* rows = bits + 4 * (off[w] + kb * gw[w].width);
-                    for (uint32_t x = 0; x < gw[w].width; x++)
+                    const uint32_t stride = gram_win_stride(gw[w]);
+                    const uint32_t* rows = bits + 4 * (off[w] + kb * stride);
+                    for (uint32_t x = 0; x < stride; x++)
                         for (uint32_t wd = 0; wd < 4; wd++)
                             for (uint32_t v = rows[4 * (uint64_t)x + wd]; v; v &= v - 1)
                                 lists[32 * wd + (uint32_t)__builtin_ctz(v)].push_back(gw[w].x0 + x);

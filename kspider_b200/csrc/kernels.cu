@@ -614,14 +614,15 @@ __global__ void __launch_bounds__(256) k3_emit_bitmap(unsigned long long c_begin
             const uint32_t mid = (lo + hi) >> 1;
             if (__ldg(&wins[mid].c0) <= c) lo = mid; else hi = mid;
         }
-        const uint32_t x0 = __ldg(&wins[lo].x0), width = __ldg(&wins[lo].width);
+        const uint32_t x0 = __ldg(&wins[lo].x0), ext = __ldg(&wins[lo].extent);
+        const uint32_t width = ext ? ext : __ldg(&wins[lo].width);  // rows of a K-block in the blob (gram_win_stride): the samples the window's colours touch
         const uint32_t lc = (uint32_t)(c - __ldg(&wins[lo].c0));
         // word (lc % 128) / 32 of the 16-byte row of sample x0 in the colour's K-block; the rows follow at 4 words each
         const uint32_t* col = bits + 4ull * (__ldg(win_rows + lo) + (unsigned long long)(lc / kGramKBlock) * width) + ((lc % kGramKBlock) >> 5);
         const uint32_t bit = lc & 31u;
         const unsigned long long w = ldw(weights, weight_bits, c);
         for (uint32_t a0 = 0; a0 < width; a0 += 32) {
-            uint32_t rows_m = __ballot_sync(KSB_FULL, (__ldg(col + 4ull * (a0 + lane)) >> bit) & 1u);  // width is a multiple of 128
+            uint32_t rows_m = __ballot_sync(KSB_FULL, a0 + lane < width && ((__ldg(col + 4ull * (a0 + lane)) >> bit) & 1u));
             while (rows_m) {
                 const uint32_t a = a0 + (uint32_t)__ffs(rows_m) - 1u;
                 rows_m &= rows_m - 1u;
@@ -629,7 +630,7 @@ __global__ void __launch_bounds__(256) k3_emit_bitmap(unsigned long long c_begin
                 if (r == 0ull) continue;  // warp-uniform
                 for (uint32_t b0 = a & ~31u; b0 < width; b0 += 32) {
                     const uint32_t b = b0 + lane;
-                    const bool in = b > a && ((__ldg(col + 4ull * b) >> bit) & 1u);
+                    const bool in = b > a && b < width && ((__ldg(col + 4ull * b) >> bit) & 1u);
                     sink.add(in, r, x0 + b, w);
                 }
             }

@@ -191,6 +191,10 @@ struct GramWinDev {
     uint32_t k0;                  // first K-block of the window in the chunk's weight planes
     uint32_t extent;              // samples from x0 to the last one a colour of the window touches (<= width; 0 = unknown):
                                   // rows / columns beyond it are padding of the last tile and hold no update
+    uint32_t kstride;             // 16-byte rows from one K-block of the window to the next: width in a chunk buffer kb_build
+                                  // fills, the extent in the blob's own bitmaps (gram_win_stride) -- rows a tile reads past a
+                                  // K-block's own are then FOREIGN bits, and the epilogue masks every row / column >= extent
+    uint32_t pad;
 };
 constexpr uint32_t kGramSeg = 2048;  // samples per bitmap-build unit: 32 KB of shared memory
 struct GramUnit {                    // one bitmap-build unit of a chunk (plan_gram lists them, heaviest first): a K-block

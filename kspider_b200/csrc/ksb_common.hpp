@@ -144,8 +144,13 @@ struct IndexDesc {
     uint64_t shard_world, shard_rank, shard_rb, shard_re;
     uint64_t payload_bytes;
 };
-constexpr uint64_t kIndexMagic = 0x36305844494253ULL | (0x4BULL << 56);
-inline uint64_t gram_win_rows(const GramWin& w) { return (((uint64_t)w.n + kGramKBlock - 1) / kGramKBlock) * w.width; }
+constexpr uint64_t kIndexMagic = 0x37305844494253ULL | (0x4BULL << 56);
+// Bitmap form of the blob: a K-block of a window holds one 16-byte row per sample from x0 up to the LAST one a colour of the
+// window touches (`extent`), not up to the tile-padded width -- a 50-sample clade in its 128-sample window is 50 rows per
+// K-block, not 128 (cfg4: 27 -> 16 MB of bitmaps).  K4 still fetches whole 128-row tiles: what it reads past a K-block's rows
+// are the next K-block's, and every cell of a row or column >= extent is masked in the epilogue.
+inline uint32_t gram_win_stride(const GramWin& w) { return w.extent ? w.extent : w.width; }
+inline uint64_t gram_win_rows(const GramWin& w) { return (((uint64_t)w.n + kGramKBlock - 1) / kGramKBlock) * gram_win_stride(w); }
 inline uint64_t gram_member_bits(const IndexDesc& d) { return d.gram_rel_bits ? d.gram_rel_bits : d.packed_bits; }
 
 }  // namespace ksb
