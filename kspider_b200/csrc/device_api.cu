@@ -73,6 +73,8 @@ struct ksb_device {
     // accumulation waits for exactly the piece each kernel reads
     cudaStream_t copy_stream = nullptr;
     bool copy_pending = false;
+    bool defer_copy_sync = false;          // the cluster-only step: do not stop the host inside ksb_accumulate for the end of the upload
+    bool copy_harvest = false;             //   (the stream waits for it; its timer is read when the step is collected)
     cudaEvent_t ev_copy[4] = {};           // copy start, head landed, tail landed, copy end
     struct k1_piece { cudaEvent_t ev; unsigned long long task_begin, task_end; };
     std::vector<k1_piece> k1_pieces;       // K1 task ranges in the order their classes are copied
@@ -1134,8 +1136,12 @@ int ksb_accumulate(ksb_device* d, void* stream_v, int sync) {
     KSB_CUDA(cudaEventRecord(d->ev[8], st));
     if (d->copy_pending) {
         KSB_CUDA(cudaStreamWaitEvent(st, d->ev_copy[3], 0));
-        KSB_CUDA(cudaStreamSynchronize(st));
-        d->t.h2d_ms = ev_ms(d->ev_copy[0], d->ev_copy[3]);  // overlaps accumulate_ms
+        if (d->defer_copy_sync) {
+            d->copy_harvest = true;  // the step's scan and unions are enqueued behind this without a host round trip
+        } else {
+            KSB_CUDA(cudaStreamSynchronize(st));
+            d->t.h2d_ms = ev_ms(d->ev_copy[0], d->ev_copy[3]);  // overlaps accumulate_ms
+        }
         d->copy_pending = false;
     }
     if (sync) {
@@ -1564,7 +1570,9 @@ static int cluster_body(ksb_device* d, int dist_col, float cstar, cudaStream_t s
     bool all_rows = true;
     for (uint32_t p = 0; p < d->passes.size(); p++) {
         d->cur_pass = p;
+        d->defer_copy_sync = true;
         const int rc = ksb_accumulate(d, st, 0);
+        d->defer_copy_sync = false;
         if (rc) return rc;
         const ksb_pass& ps = d->passes[p];
         if (ps.cells == 0) continue;
@@ -1651,6 +1659,7 @@ int ksb_device_cluster_collect(ksb_device* d, uint32_t* labels_out, uint64_t* n_
     if (!d->cl_stream || !d->h_stage) { set_error("ksb_device_cluster_collect: no step was enqueued"); return KSB_ERR_ARG; }
     KSB_CUDA(cudaSetDevice(d->device));
     KSB_CUDA(cudaStreamSynchronize(d->cl_stream));
+    if (d->copy_harvest) { d->t.h2d_ms = ev_ms(d->ev_copy[0], d->ev_copy[3]); d->copy_harvest = false; }
     unsigned long long cnt[2];
     std::memcpy(cnt, d->h_stage + 4ull * N, 16);
     if (cnt[1] > d->edge_cap) {  // the list was too short: now the need is known exactly
