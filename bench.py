@@ -552,7 +552,7 @@ def main_b200(args):
                "d2h_bytes_per_step": (4 * N + 16) * world, "ms_per_step": med, "steps": n_e2e,
                "statistic": "median of the rounds", "min_ms": min(rounds), "max_ms": max(rounds),
                "rounds_ms": [round(v, 4) for v in rounds], "result": "cluster labels (uint32[N]) + kept-edge and row counts",
-               "timer": "host wall clock around ksb_pairwise_cluster (a synchronous call: pipelined H2D of the pinned blob, kernels, labels D2H); 5 rounds of `steps` calls after 3 warm-up calls, max over ranks per round",
+               "timer": "host wall clock around ksb_pairwise_cluster (a synchronous call: pipelined H2D of the pinned blob, kernels, labels D2H; the call keeps its device handle -- allocations and plans, no data -- between calls on one index, KSPIDER_E2E_CACHE=0 disables); 5 rounds of `steps` calls after 3 warm-up calls, max over ranks per round",
                "library_phases_ms_last_step": dict(e2e_lib),
                "host_numa": (f"rank bound to the {len(cpus)} CPUs next to its GPU before its pinned buffers were allocated" if cpus else "unbound")}
         if world == 1:
