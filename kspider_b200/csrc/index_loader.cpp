@@ -28,6 +28,26 @@
 
 namespace ksb {
 
+// Ascending order of one colour's member ids (distinct: they come out of a hash SET, in slot order).  The samples of a colour
+// of a clade- or family-structured index lie within a few hundred ids of each other, so the ids are dropped into a bitmap
+// over [min, max] (at most 64 words on the stack) and read back in order with ctz -- O(n + range / 64) instead of a
+// comparison sort of 40-500 elements, which was 60 % of the member extraction.  Wider ranges take std::sort.
+static inline void sort_members(uint32_t* v, uint64_t n) {
+    if (n < 2) return;
+    uint32_t lo = v[0], hi = v[0];
+    for (uint64_t i = 1; i < n; i++) { lo = v[i] < lo ? v[i] : lo; hi = v[i] > hi ? v[i] : hi; }
+    const uint64_t range = (uint64_t)hi - lo + 1;
+    if (range > 64 * 64 || range > 64 * n) { std::sort(v, v + n); return; }  // sparse in its range: the word scan would dominate
+    uint64_t bits[64];
+    const uint32_t words = (uint32_t)((range + 63) / 64);
+    for (uint32_t w = 0; w < words; w++) bits[w] = 0;
+    for (uint64_t i = 0; i < n; i++) { const uint32_t x = v[i] - lo; bits[x >> 6] |= 1ull << (x & 63); }
+    uint64_t k = 0;
+    for (uint32_t w = 0; w < words; w++)
+        for (uint64_t b = bits[w]; b; b &= b - 1) v[k++] = lo + 64 * w + (uint32_t)__builtin_ctzll(b);
+    if (k != n) std::sort(v, v + n);  // a repeated id (never from a set): keep every copy, as std::sort would
+}
+
 static thread_local std::string g_err;
 
 void set_error(const char* fmt, ...) {
@@ -271,11 +291,49 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             });
             uint64_t n_cand = 0;
             for (uint64_t v : tn) n_cand += v;
-            std::vector<std::pair<uint64_t, uint64_t>> cand;  // (window key, colour), input order inside a window
-            cand.reserve(n_cand);
-            for (uint64_t c = 0; c < C; c++)
-                if (gkey[c] != NOKEY) cand.emplace_back(gkey[c], c);
-            std::sort(cand.begin(), cand.end());
+            // (window key, colour) sorted by key, input order inside a window.  The keys are few (one per window) and the
+            // colours come in ascending order, so this is a counting sort by key -- a comparison sort of a million pairs
+            // was the largest serial piece of the loader.
+            std::vector<std::pair<uint64_t, uint64_t>> cand(n_cand);
+            {
+                std::vector<uint64_t> keys;  // distinct keys, ascending
+                {
+                    std::vector<std::vector<uint64_t>> tk(T);
+                    parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+                        std::vector<uint64_t>& k = tk[t];
+                        uint64_t last = NOKEY;
+                        for (uint64_t c = b; c < e; c++)
+                            if (gkey[c] != NOKEY && gkey[c] != last) { k.push_back(gkey[c]); last = gkey[c]; }  // runs of one window collapse
+                        std::sort(k.begin(), k.end());
+                        k.erase(std::unique(k.begin(), k.end()), k.end());
+                    });
+                    for (auto& k : tk) keys.insert(keys.end(), k.begin(), k.end());
+                    std::sort(keys.begin(), keys.end());
+                    keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+                }
+                const size_t K = keys.size();
+                auto slot_of = [&](uint64_t key) { return (size_t)(std::lower_bound(keys.begin(), keys.end(), key) - keys.begin()); };
+                // per thread and key: how many candidates; then every thread writes its own at its offsets
+                std::vector<std::vector<uint32_t>> cnt(T, std::vector<uint32_t>(K, 0));
+                std::vector<uint64_t> cb(T, 0), ce(T, 0);
+                parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
+                    cb[t] = b; ce[t] = e;
+                    uint64_t last = NOKEY; size_t ls = 0;
+                    for (uint64_t c = b; c < e; c++)
+                        if (gkey[c] != NOKEY) { if (gkey[c] != last) { last = gkey[c]; ls = slot_of(last); } cnt[t][ls]++; }
+                });
+                std::vector<std::vector<uint64_t>> at(T, std::vector<uint64_t>(K, 0));
+                uint64_t run = 0;
+                for (size_t k = 0; k < K; k++)
+                    for (int t = 0; t < T; t++) { at[t][k] = run; run += cnt[t][k]; }
+                parallel_chunks((uint64_t)T, T, [&](int, uint64_t tb, uint64_t te) {
+                    for (uint64_t t = tb; t < te; t++) {
+                        uint64_t last = NOKEY; size_t ls = 0;
+                        for (uint64_t c = cb[t]; c < ce[t]; c++)
+                            if (gkey[c] != NOKEY) { if (gkey[c] != last) { last = gkey[c]; ls = slot_of(last); } cand[at[t][ls]++] = {gkey[c], c}; }
+                    }
+                });
+            }
             // per window: keep it only if the tensor path wins (bitmap build + MMAs + per-item overhead + one pass of reds)
             double gain = 0.0;
             std::vector<std::pair<uint64_t, uint64_t>> kept;  // [begin, end) ranges of cand
@@ -896,7 +954,7 @@ static int load_files(const char* prefix, int threads, ksb_index** out) {
             }
             if (k != v.size) { bad = 1; continue; }
             if (k == 2) { if (dst[0] > dst[1]) std::swap(dst[0], dst[1]); }
-            else std::sort(dst, dst + k);
+            else sort_members(dst, k);
             uint32_t w = 0;
             wt.get(recs[c].id, &w);  // colorsCount[id] default-inserts 0 when absent
             raw.weights[c] = w;
