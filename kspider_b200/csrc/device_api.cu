@@ -11,6 +11,8 @@
 #include <new>
 #include <vector>
 
+#include <sys/mman.h>
+
 #include "kernels.cuh"
 
 namespace ksb {
@@ -137,8 +139,10 @@ struct ksb_result {
     int device = 0;
     uint64_t n_samples = 0;
     std::vector<ksb_segment> seg;
-    ksb_record* h_records = nullptr;  // pinned, all segments concatenated (only when want_records)
+    ksb_record* h_records = nullptr;  // all segments concatenated (only when want_records); pinned unless h_pageable
     uint64_t h_capacity = 0;
+    bool h_pageable = false;          // host-only results (want_records == 2: the TSV-writing drop-in) of more than 256 MB live in
+                                      // plain 2 MB-aligned memory: page-locking 1.6 GB costs ~0.5 s, a staged copy into it ~0.1 s
     bool have_host = false;
     bool host_only = false;           // want_records == 2: the device copies of a pass are released once its rows are on the host
     ksb_result_info info;
@@ -1195,7 +1199,7 @@ void ksb_result_free(ksb_result* r) {
         if (s.d_records) cudaFreeAsync(s.d_records, g_ctx[r->device].stream);
         if (s.d_pairs) cudaFreeAsync(s.d_pairs, g_ctx[r->device].stream);
     }
-    if (r->h_records) pinned_release(r->h_records, sizeof(ksb_record) * r->h_capacity);
+    if (r->h_records) { if (r->h_pageable) free(r->h_records); else pinned_release(r->h_records, sizeof(ksb_record) * r->h_capacity); }
     (void)cudaGetLastError();
     delete r;
 }
@@ -1280,9 +1284,20 @@ int ksb_postpass(ksb_device* d, int want_records, ksb_result** inout) {
             const uint64_t cap = std::max<uint64_t>(need, r->h_capacity * 2);
             ksb_record* nh = nullptr;
             uint64_t got = sizeof(ksb_record) * cap;
-            KSB_CUDA_R(pinned_acquire(reinterpret_cast<void**>(&nh), &got));
+            static const bool pin_always = [] { const char* v = std::getenv("KSPIDER_RECORDS_PINNED"); return v && v[0] == '1'; }();
+            const bool pageable = r->host_only && !pin_always && got > (256ull << 20);
+            if (pageable) {
+                got = (got + (2ull << 20) - 1) & ~((2ull << 20) - 1);
+                void* mem = nullptr;
+                if (posix_memalign(&mem, 2ull << 20, got) != 0) { set_error("out of host memory (%llu bytes of records)", (unsigned long long)got); if (created) ksb_result_free(r); return KSB_ERR_NOMEM; }
+                madvise(mem, got, MADV_HUGEPAGE);  // 2 MB pages where the system allows: 800 page faults instead of 400 000
+                nh = static_cast<ksb_record*>(mem);
+            } else {
+                KSB_CUDA_R(pinned_acquire(reinterpret_cast<void**>(&nh), &got));
+            }
             if (have) std::memcpy(nh, r->h_records, sizeof(ksb_record) * have);
-            if (r->h_records) pinned_release(r->h_records, sizeof(ksb_record) * r->h_capacity);
+            if (r->h_records) { if (r->h_pageable) free(r->h_records); else pinned_release(r->h_records, sizeof(ksb_record) * r->h_capacity); }
+            r->h_pageable = pageable;
             const uint64_t cap_got = got / sizeof(ksb_record);
             r->h_records = nh;
             r->h_capacity = cap_got;
