@@ -157,9 +157,19 @@ static inline uint64_t mid_items_of(uint64_t s) {
 
 // Intermediate form shared by both front ends: every colour of the file / input, members sorted
 // ascending and de-duplicated (ORIGINAL sample ids), weight already narrowed.
+// resize() without the serial zero-fill (and its page faults on one thread): the member array is written in full, in
+// parallel, right after it is sized
+template <class T>
+struct NoInitAlloc : std::allocator<T> {
+    template <class U> struct rebind { using other = NoInitAlloc<U>; };
+    NoInitAlloc() = default;
+    template <class U> NoInitAlloc(const NoInitAlloc<U>&) {}
+    template <class U> void construct(U* p) noexcept { ::new (static_cast<void*>(p)) U; }
+    template <class U, class... A> void construct(U* p, A&&... a) { ::new (static_cast<void*>(p)) U(std::forward<A>(a)...); }
+};
 struct RawIndex {
     std::vector<uint64_t> off;      // [C+1]
-    std::vector<uint32_t> members;  // [M]
+    std::vector<uint32_t, NoInitAlloc<uint32_t>> members;  // [M]
     std::vector<uint32_t> weights;  // [C]
     std::vector<uint32_t> total_ids, total_vals;  // slot / input order
     uint64_t n_colors_file = 0;
@@ -213,7 +223,7 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
         for (uint64_t v = 0; v <= max_id; v++)
             if (present[v]) { remap[v] = (uint32_t)sample_ids.size(); sample_ids.push_back((uint32_t)v); }
     } else {
-        sample_ids = raw.members;
+        sample_ids.assign(raw.members.begin(), raw.members.end());
         sample_ids.insert(sample_ids.end(), raw.total_ids.begin(), raw.total_ids.end());
         std::sort(sample_ids.begin(), sample_ids.end());
         sample_ids.erase(std::unique(sample_ids.begin(), sample_ids.end()), sample_ids.end());
