@@ -35,12 +35,20 @@ void pairwise(std::string index_prefix, int user_threads) {
     auto t0 = Clock::now();
     // the CUDA contexts come up (~0.25 s each) while the index files are parsed; an error here is reported by the run itself
     std::vector<std::thread> warm;
+    struct Joiner {  // whichever way this function is left
+        std::vector<std::thread>& v;
+        void join() { for (auto& t : v) if (t.joinable()) t.join(); }
+        ~Joiner() { join(); }
+    } warm_join{warm};
     for (int g = 0; g < gpus; g++) warm.emplace_back([=] { (void)ksb::warm_device(dev0 + g); });
     ksb_index* ix = nullptr;
     const int lrc = ksb_index_load(index_prefix.c_str(), threads, &ix);
-    const std::string lerr = lrc == KSB_OK ? "" : ksb_last_error();
-    for (auto& t : warm) t.join();
-    if (lrc != KSB_OK) { ksb::set_error("%s", lerr.c_str()); fail("loading the index"); }
+    if (lrc != KSB_OK) {
+        const std::string lerr = ksb_last_error();
+        warm_join.join();  // (the warm-up may leave its own message behind)
+        ksb::set_error("%s", lerr.c_str());
+        fail("loading the index");
+    }
     t_load = secs_since(t0);
     std::cout << "mapping colors to groups: " << t_load << " secs" << std::endl;
     t0 = Clock::now();
@@ -51,6 +59,7 @@ void pairwise(std::string index_prefix, int user_threads) {
     std::cout << "kmer counting: " << t_seq << " secs" << std::endl;
 
     t0 = Clock::now();
+    warm_join.join();  // a context that takes longer than the parsing (the first CUDA process on a box) counts as GPU time
     std::vector<ksb_result*> res(gpus, nullptr);
     std::vector<int> rcs(gpus, KSB_OK);
     std::vector<std::string> errs(gpus);
