@@ -283,12 +283,15 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
             }
             gkey.assign(C, NOKEY);
             std::vector<uint64_t> tn(T, 0);
+            std::vector<uint32_t> cfirst(C), clast(C);  // compact first / last member of every candidate: read once, here, by all threads
             parallel_chunks(C, T, [&](int t, uint64_t b, uint64_t e) {
                 uint64_t n = 0;
                 for (uint64_t c = b; c < e; c++) {
                     const uint64_t sz = raw.off[c + 1] - raw.off[c];
                     if (sz < 2 || sz < s_any || raw.weights[c] == 0) continue;
                     const uint64_t first = compact(raw.members[raw.off[c]]), last = compact(raw.members[raw.off[c + 1] - 1]);
+                    cfirst[c] = (uint32_t)first;
+                    clast[c] = (uint32_t)last;
                     for (size_t l = 0; l < levels.size(); l++) {
                         const Level& lv = levels[l];
                         const uint64_t x0 = lv.top ? 0 : first / lv.stride * lv.stride;
@@ -355,8 +358,8 @@ static int build_index(RawIndex& raw, int threads, ksb_index** out) {
                     const uint64_t c = cand[e].second, sz = raw.off[c + 1] - raw.off[c];
                     upd += sz * (sz - 1) / 2;
                     mem += sz;
-                    lo = std::min<uint64_t>(lo, compact(raw.members[raw.off[c]]));
-                    hi = std::max<uint64_t>(hi, (uint64_t)compact(raw.members[raw.off[c + 1] - 1]) + 1);
+                    lo = std::min<uint64_t>(lo, cfirst[c]);
+                    hi = std::max<uint64_t>(hi, (uint64_t)clast[c] + 1);
                     e++;
                 }
                 const Level& lv = levels[cand[b].first & 0xFF];
