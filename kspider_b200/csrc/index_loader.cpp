@@ -855,7 +855,12 @@ static int load_files(const char* prefix, int threads, ksb_index** out) {
             recs[r] = Rec{pos + 8, (uint32_t)color, (uint32_t)v.size};
             wide |= (color >> 32) != 0;
             max_id = std::max(max_id, (uint32_t)color);
-            pos += 8 + v.bytes;
+            // the walk is a chain of dependent cache misses (a record's length is in its own header): indexers write runs of
+            // colours of one capacity, so the headers a few records ahead are probably where this record's length says
+            const uint64_t step = 8 + v.bytes;
+            for (uint64_t a = 4; a <= 8; a += 2)
+                if (pos + a * step + 24 <= fs.size) __builtin_prefetch(fs.data + pos + a * step, 0, 0);
+            pos += step;
         }
         // int_vec_map key is uint32_t: insert_or_assign keeps the last record per narrowed id
         // (the writers iterate a map, so the u64 ids are distinct: two records can only share a NARROWED id when some id
