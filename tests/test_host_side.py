@@ -407,3 +407,39 @@ def test_gram_members_stored_relative_to_their_window(built_lib, monkeypatch):
     # 153 000 members and 1 000 offsets: smaller than the narrowest CSR, and what the loader picks by itself
     assert sizes[("16", "10")] - sizes[("16", "bitmap")] >= 100_000
     assert sizes[("32", "auto")] < sizes[("32", "12")] and sizes[("32", "auto")] - sizes[("16", "bitmap")] < 16384
+
+
+@pytest.mark.parametrize("shape", ["close_ids", "wide_ids", "top_of_u32", "mixed"])
+def test_loader_sorts_member_lists_like_from_csr(built_lib, tmp_path, shape):
+    """The file loader puts a colour's members (hash-slot order in the file) into ascending order either through a bitmap
+    over [min, max] (ids close together) or with std::sort (ids far apart): both must give exactly the index that
+    ksb_index_from_csr builds from the same lists -- byte-identical blobs -- also for ids at the top of the u32 range."""
+    from kspider_b200 import Index, write_index_files
+    rng = np.random.default_rng({"close_ids": 1, "wide_ids": 2, "top_of_u32": 3, "mixed": 4}[shape])
+    if shape == "close_ids":
+        pool = np.arange(1000, 1400, dtype=np.uint64)
+    elif shape == "wide_ids":
+        pool = np.sort(rng.choice(np.arange(1, 2 ** 32 - 2, 104729, dtype=np.uint64), size=400, replace=False))
+    elif shape == "top_of_u32":
+        pool = np.arange(2 ** 32 - 401, 2 ** 32 - 1, dtype=np.uint64)
+    else:
+        pool = np.sort(np.concatenate([np.arange(5, 205, dtype=np.uint64), rng.choice(np.arange(10 ** 6, 4 * 10 ** 9, 7919, dtype=np.uint64), size=200, replace=False)]))
+    cols, offsets = [], [0]
+    for s in list(rng.integers(2, 90, size=600)) + [300, 399]:
+        cols.append(rng.permutation(rng.choice(pool, size=int(s), replace=False)))  # unsorted on purpose
+        offsets.append(offsets[-1] + int(s))
+    members = np.concatenate(cols).astype(np.uint32)
+    csr = dict(offsets=np.array(offsets, dtype=np.uint64), members=members,
+               weights=rng.integers(1, 5000, size=len(cols)).astype(np.uint32),
+               total_ids=pool.astype(np.uint32), total_vals=rng.integers(1, 10 ** 6, size=pool.size).astype(np.uint32))
+    n = len(cols)
+    cids = np.arange(7, 7 + n, dtype=np.uint64)
+    prefix = str(tmp_path / shape)
+    write_index_files(prefix, cids, csr["offsets"], csr["members"], cids, csr["weights"].astype(np.uint64), csr["total_ids"], csr["total_vals"])
+    a = Index.load(prefix, 3)
+    b = Index.from_csr(**csr, host_threads=3)
+    assert a.descriptor() == b.descriptor()
+    assert np.array_equal(a.payload(), b.payload())
+    o = po.OracleIndex(prefix)
+    assert int((np.diff(o.offsets) >= 2).sum()) == a.info.n_colors
+    a.close(); b.close()
