@@ -443,3 +443,45 @@ def test_loader_sorts_member_lists_like_from_csr(built_lib, tmp_path, shape):
     o = po.OracleIndex(prefix)
     assert int((np.diff(o.offsets) >= 2).sum()) == a.info.n_colors
     a.close(); b.close()
+
+
+def test_from_blob_checks_the_bitmap_form_and_the_row_tables(built_lib, monkeypatch):
+    """A blob whose Gram section holds bitmaps (IndexDesc::gram_form 1) carries the first bitmap row of every window and
+    the accumulator's row tables (bandstart, rowbase): a descriptor / payload pair whose tables do not add up is refused."""
+    from kspider_b200 import Index
+    from kspider_b200.capi import KsbError
+    rng = np.random.default_rng(21)
+    n = 3000
+    ids = np.arange(1, n + 1, dtype=np.uint32)
+    cols, offsets = [], [0]
+    for lo in (100, 1200, 2500):
+        for _ in range(300):
+            m = np.sort(rng.choice(200, size=90, replace=False)) + lo
+            cols.append(ids[m]); offsets.append(offsets[-1] + m.size)
+    csr = dict(offsets=np.array(offsets, dtype=np.uint64), members=np.concatenate(cols).astype(np.uint32),
+               weights=rng.integers(1, 200, size=len(cols)).astype(np.uint32), total_ids=ids, total_vals=np.full(n, 10 ** 6, dtype=np.uint32))
+    monkeypatch.setenv("KSPIDER_GRAM", "16")
+    monkeypatch.setenv("KSPIDER_GRAM_FORM", "bitmap")
+    idx = Index.from_csr(**csr)
+    assert idx.info.gram_form & 1 and idx.info.n_gram_windows == 3
+    desc, payload = idx.descriptor(), idx.payload().copy()
+    assert np.array_equal(Index.from_blob(desc, payload).payload(), payload)
+    p64 = np.frombuffer(payload.tobytes(), dtype=np.uint64).copy()
+    lo, hi, cells = idx.bands()
+    start = np.concatenate([[0], np.cumsum(hi.astype(np.int64) - lo)]).astype(np.uint64)
+    # bandstart is the only place in the blob where this exact prefix-sum array stands: find it and break one entry
+    hits = [i for i in np.flatnonzero(p64 == start[-1]) if i >= n and np.array_equal(p64[i - n:i + 1], start)]
+    assert hits, "bandstart section not found"
+    bad = p64.copy()
+    bad[hits[0] - n // 2] += np.uint64(1)
+    with pytest.raises(KsbError):
+        Index.from_blob(desc, np.frombuffer(bad.tobytes(), dtype=np.uint8))
+    # the window row table: [0, rows of window 0, ...]; 3 windows of 3 K-blocks x 200-sample extent
+    rows = 3 * 200
+    want = np.array([0, rows, 2 * rows, 3 * rows], dtype=np.uint64)
+    whits = [i for i in range(p64.size - 3) if np.array_equal(p64[i:i + 4], want)]
+    assert whits, "window row table not found"
+    bad = p64.copy()
+    bad[whits[0] + 1] += np.uint64(8)
+    with pytest.raises(KsbError):
+        Index.from_blob(desc, np.frombuffer(bad.tobytes(), dtype=np.uint8))
