@@ -272,6 +272,9 @@ const ksb_record* ksb_result_records(const ksb_result* r, uint64_t* n_rows);
 int ksb_write_tsv(const ksb_result* r, const char* path, int host_threads);
 /* Appends rows of further results (other row blocks) to an existing TSV without a header. */
 int ksb_append_tsv(const ksb_result* r, const char* path, int host_threads);
+/* The same writer on host rows that are not inside a result (src/pairwise.cpp:242-275: header unless append, then one line per
+ * row in the order given): what ksb_write_tsv / ksb_append_tsv call with the result's rows. */
+int ksb_write_tsv_records(const ksb_record* records, uint64_t n_rows, const char* path, int host_threads, int append);
 /* K6+K7: threshold column dist_col (3=min,4=avg,5=max) at cutoff01 with the reference's text
  * semantics, union-find over the kept edges.  labels_out[N]: label = smallest compact sample index of
  * the component.  parent_inout (optional, N entries, device-independent host buffer) lets several row

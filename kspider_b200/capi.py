@@ -101,6 +101,7 @@ _PROTOS = {
     "ksb_result_records": (C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_write_tsv": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "ksb_append_tsv": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
+    "ksb_write_tsv_records": (C.c_int, [C.c_void_p, C.c_uint64, C.c_char_p, C.c_int, C.c_int]),
     "ksb_cluster": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_cluster_pct": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]),
     "ksb_cluster_pct_device": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_uint64)]),

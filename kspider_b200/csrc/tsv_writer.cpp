@@ -93,13 +93,7 @@ static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* ba
     return rc;
 }
 
-static int write_tsv_impl(const ksb_result* r, const char* path, int threads, bool append) {
-    if (!r || !path) { set_error("ksb_write_tsv: null argument"); return KSB_ERR_ARG; }
-    uint64_t n = 0;
-    const ksb_record* rec = ksb_result_records(r, &n);
-    ksb_result_info info;
-    ksb_result_get_info(r, &info);
-    if (info.n_rows && !rec) { set_error("ksb_write_tsv: the result holds no host records (run with want_records = 1)"); return KSB_ERR_ARG; }
+static int write_tsv_rows(const ksb_record* rec, uint64_t n, const char* path, int threads, bool append) {
     const int fd = open(path, append ? (O_WRONLY | O_CREAT) : (O_WRONLY | O_CREAT | O_TRUNC), 0644);
     if (fd < 0) { set_error("cannot write %s: %s", path, strerror(errno)); return KSB_ERR_IO; }
     int rc = KSB_OK;
@@ -116,6 +110,16 @@ static int write_tsv_impl(const ksb_result* r, const char* path, int threads, bo
     if (close(fd) != 0) rc = KSB_ERR_IO;
     if (rc == KSB_ERR_IO) set_error("write error on %s", path);
     return rc;
+}
+
+static int write_tsv_impl(const ksb_result* r, const char* path, int threads, bool append) {
+    if (!r || !path) { set_error("ksb_write_tsv: null argument"); return KSB_ERR_ARG; }
+    uint64_t n = 0;
+    const ksb_record* rec = ksb_result_records(r, &n);
+    ksb_result_info info;
+    ksb_result_get_info(r, &info);
+    if (info.n_rows && !rec) { set_error("ksb_write_tsv: the result holds no host records (run with want_records = 1)"); return KSB_ERR_ARG; }
+    return write_tsv_rows(rec, n, path, threads, append);
 }
 
 }  // namespace ksb
@@ -263,6 +267,10 @@ int ksb_write_ani_column(const double* ani, uint64_t n, const char* path, int ho
 
 int ksb_write_tsv(const ksb_result* r, const char* path, int host_threads) { return ksb::write_tsv_impl(r, path, host_threads, false); }
 int ksb_append_tsv(const ksb_result* r, const char* path, int host_threads) { return ksb::write_tsv_impl(r, path, host_threads, true); }
+int ksb_write_tsv_records(const ksb_record* records, uint64_t n_rows, const char* path, int host_threads, int append) {
+    if ((!records && n_rows) || !path) { ksb::set_error("ksb_write_tsv_records: null argument"); return KSB_ERR_ARG; }
+    return ksb::write_tsv_rows(records, n_rows, path, host_threads, append != 0);
+}
 
 int ksb_write_index_files(const char* index_prefix, uint64_t n_colors, const uint64_t* color_ids, const uint64_t* offsets,
                           const uint32_t* members, uint64_t n_counts, const uint64_t* count_ids, const uint64_t* count_vals,

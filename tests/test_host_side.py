@@ -165,6 +165,59 @@ def test_fast_format_float_is_exact_on_a_sweep(built_lib):
         assert fmt(float(v)) == "%g" % float(v), float(v)
 
 
+def test_tsv_writer_on_host_rows_is_the_reference_text(built_lib, tmp_path):
+    """src/pairwise.cpp:242-275 on rows that never saw a GPU: header, tab-separated integers, ostream<<float text, file order
+    = row order whatever the thread count and across the writer's batch boundary; appended blocks follow without a header."""
+    from kspider_b200.api import RECORD_DTYPE
+    rng = np.random.default_rng(7)
+    n = (1 << 22) + 12345  # one full batch of the writer and a ragged second one
+    rec = np.zeros(n, RECORD_DTYPE)
+    rec["source_1"] = rng.integers(0, 2 ** 32, n, dtype=np.uint64)
+    rec["source_2"] = rng.integers(0, 2 ** 32, n, dtype=np.uint64)
+    rec["shared_kmers"] = rng.integers(0, 2 ** 63, n, dtype=np.uint64) >> rng.integers(0, 63, n, dtype=np.uint64)
+    rec["shared_kmers"][:3] = (0, 2 ** 64 - 1, 10 ** 19)
+    a, b = rng.integers(1, 70000, n), rng.integers(1, 70000, n)
+    rec["min_containment"] = (np.minimum(a, b) / np.maximum(a, b)).astype(np.float32)
+    rec["avg_containment"] = (rng.random(n) * 10.0 ** rng.integers(-8, 3, n)).astype(np.float32)
+    rec["max_containment"] = rng.random(n, dtype=np.float32)
+    rec["max_containment"][:4] = (0.0, 1.0, 1e-7, 0.99999994)
+
+    def text_of(r):
+        return (f"{r['source_1']}\t{r['source_2']}\t{r['shared_kmers']}\t{'%g' % float(r['min_containment'])}\t"
+                f"{'%g' % float(r['avg_containment'])}\t{'%g' % float(r['max_containment'])}")
+
+    header = "source_1\tsource_2\tshared_kmers\tmin_containment\tavg_containment\tmax_containment"
+    paths = []
+    for threads in (1, 3, 8):
+        p = str(tmp_path / f"t{threads}.tsv")
+        assert built_lib.ksb_write_tsv_records(rec.ctypes.data, n, p.encode(), threads, 0) == 0
+        paths.append(p)
+    blobs = [open(p, "rb").read() for p in paths]
+    assert blobs[0] == blobs[1] == blobs[2]
+    lines = blobs[0].decode().split("\n")
+    assert lines[0] == header and lines[-1] == "" and len(lines) == n + 2
+    for k in np.concatenate([np.arange(64), np.arange((1 << 22) - 32, (1 << 22) + 32), np.arange(n - 64, n), rng.integers(0, n, 4000)]):
+        assert lines[1 + k] == text_of(rec[k]), k
+    # the three numeric columns of every line parse back to the rows (no line lost or torn at a thread / batch seam)
+    import pandas as pd
+    back = pd.read_csv(paths[0], sep="\t", dtype={"source_1": np.uint32, "source_2": np.uint32, "shared_kmers": np.uint64})
+    assert np.array_equal(back["source_1"].to_numpy(), rec["source_1"]) and np.array_equal(back["source_2"].to_numpy(), rec["source_2"])
+    assert np.array_equal(back["shared_kmers"].to_numpy(), rec["shared_kmers"])
+
+    # two blocks, the second appended == one call; an empty block writes the header alone; a missing directory is an IO error
+    p2 = str(tmp_path / "two.tsv")
+    cut = 1000
+    assert built_lib.ksb_write_tsv_records(rec.ctypes.data, cut, p2.encode(), 4, 0) == 0
+    assert built_lib.ksb_write_tsv_records(rec[cut:].ctypes.data, 5000 - cut, p2.encode(), 4, 1) == 0
+    assert open(p2, "rb").read() == ("\n".join(lines[:5001]) + "\n").encode()
+    p3 = str(tmp_path / "none.tsv")
+    assert built_lib.ksb_write_tsv_records(None, 0, p3.encode(), 4, 0) == 0
+    assert open(p3).read() == header + "\n"
+    from kspider_b200.capi import KSB_ERR_IO, KSB_ERR_ARG
+    assert built_lib.ksb_write_tsv_records(rec.ctypes.data, 10, str(tmp_path / "no" / "dir.tsv").encode(), 1, 0) == KSB_ERR_IO
+    assert built_lib.ksb_write_tsv_records(None, 10, p3.encode(), 1, 0) == KSB_ERR_ARG
+
+
 def test_threshold_float_is_the_exact_boundary(built_lib):
     """c* = smallest float32 whose printed text passes `float(text)*100 >= cutoff*100` (ks_clustering.py:97-105)."""
     from kspider_b200 import threshold_float
