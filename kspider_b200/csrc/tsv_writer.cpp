@@ -18,12 +18,102 @@
 
 namespace ksb {
 
+// "00".."99"
+static const char kPairs[201] =
+    "0001020304050607080910111213141516171819202122232425262728293031323334353637383940414243444546474849"
+    "5051525354555657585960616263646566676869707172737475767778798081828384858687888990919293949596979899";
+
+// decimal text of a u32 (two digits per division); returns length
+static inline int u32_to_dec(uint32_t v, char* out) {
+    const int n = v < 100u ? (v < 10u ? 1 : 2)
+                : v < 10000u ? (v < 1000u ? 3 : 4)
+                : v < 1000000u ? (v < 100000u ? 5 : 6)
+                : v < 100000000u ? (v < 10000000u ? 7 : 8)
+                : (v < 1000000000u ? 9 : 10);
+    char* p = out + n;
+    while (v >= 100u) {
+        const uint32_t q = v / 100u;
+        std::memcpy(p -= 2, kPairs + 2 * (v - q * 100u), 2);
+        v = q;
+    }
+    if (v >= 10u) std::memcpy(p - 2, kPairs + 2 * v, 2);
+    else p[-1] = (char)('0' + v);
+    return n;
+}
+
 // decimal text of a u64; returns length
 static inline int u64_to_dec(uint64_t v, char* out) {
-    char tmp[24];
-    int n = 0;
-    do { tmp[n++] = (char)('0' + v % 10); v /= 10; } while (v);
-    for (int i = 0; i < n; i++) out[i] = tmp[n - 1 - i];
+    if (v <= 0xFFFFFFFFull) return u32_to_dec((uint32_t)v, out);
+    // at most 20 digits: the top part (< 1.9e11) again by halves, then 9 zero-padded digits
+    const uint64_t hi = v / 1000000000ull;
+    uint32_t lo = (uint32_t)(v - hi * 1000000000ull);
+    const int n = u64_to_dec(hi, out);
+    char* p = out + n + 9;
+    for (int i = 0; i < 4; i++) {
+        const uint32_t q = lo / 100u;
+        std::memcpy(p -= 2, kPairs + 2 * (lo - q * 100u), 2);
+        lo = q;
+    }
+    p[-1] = (char)('0' + lo);
+    return n + 9;
+}
+
+// "%g" of a float (see ksb_format_float below for the why); in this unit so that the row loop inlines it
+static inline int format_float(float v, char* buf) {
+    uint32_t bits;
+    std::memcpy(&bits, &v, 4);
+    if (bits == 0) { buf[0] = '0'; return 1; }
+    const uint32_t ex = (bits >> 23) & 0xFFu;
+    if ((bits >> 31) == 0 && ex >= 113 && ex <= 146) {  // 2^-14 <= v < 2^20, positive, normal
+        const uint64_t M = (bits & 0x7FFFFFu) | 0x800000u;
+        const int sh = 150 - (int)ex;                    // v = M >> sh, 4 <= sh <= 37
+        static const uint64_t P10[12] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull,
+                                         100000000ull, 1000000000ull, 10000000000ull, 100000000000ull};
+        // decimal exponent k: 10^k <= v < 10^(k+1); start from the binary exponent, fix up exactly
+        int k = (int)(((int)ex - 127) * 1233) >> 12;     // floor(log10(2^e)) or one less
+        if (k < -5) k = -5;
+        if (k > 5) k = 5;
+        uint64_t q = 0, rem = 0;
+        for (int it = 0; it < 4; it++) {
+            const int p = 5 - k;                         // 0 <= p <= 10
+            if (p < 0 || p > 10) { k = 99; break; }
+            const uint64_t prod = M * P10[p];            // < 2^24 * 10^10 < 2^58
+            q = prod >> sh;
+            rem = prod & ((1ull << sh) - 1ull);
+            if (q < 100000ull) { k--; continue; }
+            if (q >= 1000000ull) { k++; continue; }
+            break;
+        }
+        if (k >= -4 && k <= 5 && q >= 100000ull && q < 1000000ull) {
+            const uint64_t half = 1ull << (sh - 1);
+            if (rem > half || (rem == half && (q & 1ull))) q++;
+            if (q == 1000000ull) { q = 100000ull; k++; }
+            if (k <= 5) {
+                char d[12] = {};
+                const uint32_t q32 = (uint32_t)q, hi2 = q32 / 10000u, lo4 = q32 - hi2 * 10000u, mid2 = lo4 / 100u;
+                std::memcpy(d, kPairs + 2 * hi2, 2);
+                std::memcpy(d + 2, kPairs + 2 * mid2, 2);
+                std::memcpy(d + 4, kPairs + 2 * (lo4 - mid2 * 100u), 2);
+                int last = 5;                              // last significant digit kept ("%g" strips trailing zeros)
+                while (last > 0 && d[last] == '0') last--;
+                // (whole digit groups are copied and the length cut afterwards: at most 11 bytes are touched)
+                if (k < 0) {
+                    std::memcpy(buf, "0.000", 5);
+                    const int n = 1 - k;                   // "0." and -k - 1 zeros
+                    std::memcpy(buf + n, d, 6);
+                    return n + last + 1;
+                }
+                std::memcpy(buf, d, 6);
+                if (last <= k) return k + 1;
+                buf[k + 1] = '.';
+                std::memcpy(buf + k + 2, d + k + 1, 5);    // k < last <= 5: at most 5 - k of them count
+                return last + 2;
+            }
+        }
+    }
+    char tmp[32];
+    const int n = snprintf(tmp, sizeof tmp, "%g", (double)v);
+    std::memcpy(buf, tmp, (size_t)n);
     return n;
 }
 
@@ -35,10 +125,30 @@ static const char kTsvHeader[] =
 // serialise on its inode lock whoever issues them, so one writer at full speed beside the formatters is what overlaps
 // (the copy into the page cache is the other half of the time: 1.64 GB on cfg4).  `base` = file offset of the first row;
 // returns the offset behind the last.
+struct TextBuf {  // per-thread text of one batch; never value-initialised (std::string::resize would clear 3x what is written)
+    char* p = nullptr;
+    size_t cap = 0, len = 0;
+    TextBuf() = default;
+    TextBuf(const TextBuf&) = delete;
+    TextBuf& operator=(const TextBuf&) = delete;
+    ~TextBuf() { std::free(p); }
+    bool reserve(size_t n) {
+        if (n <= cap) return true;
+        std::free(p);
+        p = (char*)std::malloc(n);
+        cap = p ? n : 0;
+        return p != nullptr;
+    }
+};
+
 static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* base, int threads) {
     const uint64_t kBatch = 1ull << 22;
+    const size_t kRowMax = 96;  // 10 + 10 + 20 digits, 3 x 16 for the floats, 6 separators
     if (threads < 1) threads = 1;
-    std::vector<std::string> bufs[2] = {std::vector<std::string>(threads), std::vector<std::string>(threads)};
+    std::vector<TextBuf> bufs[2];
+    bufs[0] = std::vector<TextBuf>(threads);
+    bufs[1] = std::vector<TextBuf>(threads);
+    std::vector<uint8_t> failed(threads, 0);
     std::thread writer[2];
     int wrc[2] = {KSB_OK, KSB_OK};
     uint64_t at = *base;
@@ -49,26 +159,28 @@ static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* ba
         if (writer[set].joinable()) { writer[set].join(); if (wrc[set] != KSB_OK) rc = wrc[set]; }  // the set's previous batch is in the file
         if (rc != KSB_OK) break;
         const uint64_t bn = std::min(kBatch, n - b0);
-        std::vector<std::string>& bs = bufs[set];
-        for (auto& s : bs) s.clear();
+        std::vector<TextBuf>& bs = bufs[set];
+        for (auto& s : bs) s.len = 0;
         parallel_chunks(bn, threads, [&](int t, uint64_t b, uint64_t e) {
-            std::string& s = bs[t];
-            s.resize((e - b) * 128);  // a row is at most 3 x 20 digits + 3 x 16 + 6 separators
-            char* const first = &s[0];
-            char* line = first;
+            TextBuf& s = bs[t];
+            if (!s.reserve((size_t)(e - b) * kRowMax + 16)) { failed[t] = 1; return; }
+            char* line = s.p;
             for (uint64_t i = b; i < e; i++) {
                 const ksb_record& r = rec[b0 + i];
-                line += u64_to_dec(r.source_1, line); *line++ = '\t';
-                line += u64_to_dec(r.source_2, line); *line++ = '\t';
+                line += u32_to_dec(r.source_1, line); *line++ = '\t';
+                line += u32_to_dec(r.source_2, line); *line++ = '\t';
                 line += u64_to_dec(r.shared_kmers, line); *line++ = '\t';
-                line += ksb_format_float(r.min_containment, line); *line++ = '\t';
-                line += ksb_format_float(r.avg_containment, line); *line++ = '\t';
-                line += ksb_format_float(r.max_containment, line); *line++ = '\n';
+                line += format_float(r.min_containment, line); *line++ = '\t';
+                line += format_float(r.avg_containment, line); *line++ = '\t';
+                line += format_float(r.max_containment, line); *line++ = '\n';
             }
-            s.resize((size_t)(line - first));
+            s.len = (size_t)(line - s.p);
         });
+        for (int t = 0; t < threads; t++)
+            if (failed[t]) rc = KSB_ERR_NOMEM;
+        if (rc != KSB_OK) break;
         uint64_t bytes = 0;
-        for (const auto& s : bs) bytes += s.size();
+        for (const auto& s : bs) bytes += s.len;
         const uint64_t off = at;
         at += bytes;
         if (k > 0 && writer[set ^ 1].joinable()) { writer[set ^ 1].join(); if (wrc[set ^ 1] != KSB_OK) rc = wrc[set ^ 1]; }  // file order: batch k - 1 first
@@ -77,8 +189,8 @@ static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* ba
         writer[set] = std::thread([&bs, &wrc, set, fd, off]() {
             uint64_t pos = off;
             for (const auto& s : bs) {
-                const char* p = s.data();
-                uint64_t left = s.size();
+                const char* p = s.p;
+                uint64_t left = s.len;
                 while (left) {
                     const ssize_t w = pwrite(fd, p, (size_t)left, (off_t)pos);
                     if (w < 0) { if (errno == EINTR) continue; wrc[set] = KSB_ERR_IO; return; }
@@ -109,6 +221,7 @@ static int write_tsv_rows(const ksb_record* rec, uint64_t n, const char* path, i
     if (rc == KSB_OK) rc = write_records(rec, n, fd, &base, threads);
     if (close(fd) != 0) rc = KSB_ERR_IO;
     if (rc == KSB_ERR_IO) set_error("write error on %s", path);
+    if (rc == KSB_ERR_NOMEM) set_error("out of host memory writing %s", path);
     return rc;
 }
 
@@ -133,62 +246,7 @@ extern "C" {
 // M and -38 <= E <= -4, so v * 10^p (p <= 10) is the exact integer M * 10^p shifted right by -E and
 // fits 64 bits; the six significant digits are that quotient rounded half-to-even on the exact
 // remainder -- what glibc prints.  Everything else (0 handled inline) goes through snprintf.
-int ksb_format_float(float v, char* buf) {
-    uint32_t bits;
-    std::memcpy(&bits, &v, 4);
-    if (bits == 0) { buf[0] = '0'; return 1; }
-    const uint32_t ex = (bits >> 23) & 0xFFu;
-    if ((bits >> 31) == 0 && ex >= 113 && ex <= 146) {  // 2^-14 <= v < 2^20, positive, normal
-        const uint64_t M = (bits & 0x7FFFFFu) | 0x800000u;
-        const int sh = 150 - (int)ex;                    // v = M >> sh, 4 <= sh <= 37
-        static const uint64_t P10[12] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull,
-                                         100000000ull, 1000000000ull, 10000000000ull, 100000000000ull};
-        // decimal exponent k: 10^k <= v < 10^(k+1); start from the binary exponent, fix up exactly
-        int k = (int)(((int)ex - 127) * 1233) >> 12;     // floor(log10(2^e)) or one less
-        if (k < -5) k = -5;
-        if (k > 5) k = 5;
-        uint64_t q = 0, rem = 0;
-        for (int it = 0; it < 4; it++) {
-            const int p = 5 - k;                         // 0 <= p <= 10
-            if (p < 0 || p > 10) { k = 99; break; }
-            const uint64_t prod = M * P10[p];            // < 2^24 * 10^10 < 2^58
-            q = prod >> sh;
-            rem = prod & ((1ull << sh) - 1ull);
-            if (q < 100000ull) { k--; continue; }
-            if (q >= 1000000ull) { k++; continue; }
-            break;
-        }
-        if (k >= -4 && k <= 5 && q >= 100000ull && q < 1000000ull) {
-            const uint64_t half = 1ull << (sh - 1);
-            if (rem > half || (rem == half && (q & 1ull))) q++;
-            if (q == 1000000ull) { q = 100000ull; k++; }
-            if (k <= 5) {
-                char d[6];
-                for (int i = 5; i >= 0; i--) { d[i] = (char)('0' + q % 10); q /= 10; }
-                int last = 5;                              // last significant digit kept ("%g" strips trailing zeros)
-                while (last > 0 && d[last] == '0') last--;
-                int n = 0;
-                if (k >= 0) {
-                    for (int i = 0; i <= k; i++) buf[n++] = d[i];
-                    if (last > k) {
-                        buf[n++] = '.';
-                        for (int i = k + 1; i <= last; i++) buf[n++] = d[i];
-                    }
-                } else {
-                    buf[n++] = '0';
-                    buf[n++] = '.';
-                    for (int i = 0; i < -k - 1; i++) buf[n++] = '0';
-                    for (int i = 0; i <= last; i++) buf[n++] = d[i];
-                }
-                return n;
-            }
-        }
-    }
-    char tmp[32];
-    const int n = snprintf(tmp, sizeof tmp, "%g", (double)v);
-    std::memcpy(buf, tmp, (size_t)n);
-    return n;
-}
+int ksb_format_float(float v, char* buf) { return ksb::format_float(v, buf); }
 
 // Python's repr(float) (what ks_pairwise.py:79 writes with f"{avg_ani}"): the shortest digit string that
 // round-trips (std::to_chars), laid out by CPython's rule for format code 'r' -- fixed notation when
