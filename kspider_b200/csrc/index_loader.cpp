@@ -1032,6 +1032,18 @@ int from_csr_owned(uint64_t n_colors, const uint64_t* offsets, const uint32_t* m
     return from_csr(n_colors, offsets, members, weights, n_totals, total_ids, total_vals, threads, out);
 }
 
+// element i of a member section of `bits`-wide compact ids (10 / 12: packed)
+static inline uint32_t blob_member(const uint8_t* sec, uint64_t bits, uint64_t i) {
+    if (bits == 32) return reinterpret_cast<const uint32_t*>(sec)[i];
+    if (bits == 16) return reinterpret_cast<const uint16_t*>(sec)[i];
+    if (bits == 10) {
+        const uint8_t* q = sec + ((5 * i) >> 2);
+        return (((uint32_t)q[0] | ((uint32_t)q[1] << 8)) >> ((i & 3) << 1)) & 0x3FFu;
+    }
+    const uint8_t* p = sec + ((3 * i) >> 1);
+    return (((uint32_t)p[0] | ((uint32_t)p[1] << 8)) >> ((i & 1) << 2)) & 0xFFFu;
+}
+
 // Row-block shard: walks every colour of the binned blob, keeps those with a member in rows
 // [r0, r1) (as a ROW, i.e. not as the colour's last member), cut down to their members >= r0, and
 // bins the result again.  Sample ids / totals are passed through unchanged so the compaction (and
@@ -1046,16 +1058,7 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     const uint32_t* sids = reinterpret_cast<const uint32_t*>(P + D.off_sample_ids);
     const uint32_t* totals = reinterpret_cast<const uint32_t*>(P + D.off_totals);
     // element i of a member section of `bits`-wide compact ids (12 = packed), element i of a weight section
-    auto member = [&](const uint8_t* sec, uint64_t bits, uint64_t i) -> uint32_t {
-        if (bits == 32) return reinterpret_cast<const uint32_t*>(sec)[i];
-        if (bits == 16) return reinterpret_cast<const uint16_t*>(sec)[i];
-        if (bits == 10) {
-            const uint8_t* q = sec + ((5 * i) >> 2);
-            return (((uint32_t)q[0] | ((uint32_t)q[1] << 8)) >> ((i & 3) << 1)) & 0x3FFu;
-        }
-        const uint8_t* p = sec + ((3 * i) >> 1);
-        return (((uint32_t)p[0] | ((uint32_t)p[1] << 8)) >> ((i & 1) << 2)) & 0xFFFu;
-    };
+    auto member = [&](const uint8_t* sec, uint64_t bits, uint64_t i) -> uint32_t { return blob_member(sec, bits, i); };
     auto weight = [&](const uint8_t* sec, uint64_t i) -> uint32_t {
         if (D.weight_bits == 8) return sec[i];
         if (D.weight_bits == 16) return reinterpret_cast<const uint16_t*>(sec)[i];
@@ -1064,11 +1067,20 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
     RawIndex raw;
     raw.n_colors_file = D.n_colors_file;
     raw.off.push_back(0);
+    bool corrupt = false;
     // one colour: sorted compact members sec[b .. b+s) of a `bits`-wide section
     auto take = [&](const uint8_t* sec, uint64_t bits, uint64_t b, uint64_t s, uint32_t w, uint32_t add = 0) {
         uint64_t lo = 0, hi = s;  // first member >= r0
         while (lo < hi) { const uint64_t mid = (lo + hi) / 2; if (member(sec, bits, b + mid) + add < r0) lo = mid + 1; else hi = mid; }
         if (s - lo < 2 || member(sec, bits, b + lo) + add >= r1) return;  // no owned row with a later column
+        // (a blob adopted through ksb_index_from_blob has had its tables checked, not its member values: a list that is not
+        // strictly ascending below N would index past `sids` here and past the Gram bitmaps in build_index)
+        uint64_t prev = 0;
+        for (uint64_t i = lo; i < s; i++) {
+            const uint64_t m = (uint64_t)member(sec, bits, b + i) + add;
+            if (m >= N || (i > lo && m <= prev)) { corrupt = true; return; }
+            prev = m;
+        }
         for (uint64_t i = lo; i < s; i++) raw.members.push_back(sids[member(sec, bits, b + i) + add]);
         raw.off.push_back(raw.members.size());
         raw.weights.push_back(w);
@@ -1119,6 +1131,7 @@ static int shard_index(const ksb_index* ix, int rank, int world, int threads, ks
                  D.gram_rel_bits ? gw[wi].x0 : 0u);
         }
     }
+    if (corrupt) { set_error("ksb_index_shard: the index holds a member list that is not strictly ascending below its sample count"); return KSB_ERR_FORMAT; }
     raw.total_ids.assign(sids, sids + N);
     raw.total_vals.assign(totals, totals + N);
     ksb_index* sh = nullptr;
@@ -1202,8 +1215,117 @@ namespace ksb {
 // A (descriptor, payload) pair that came from another process or rank (NCCL / gloo / a file) is checked before it is
 // trusted: the section offsets must be exactly the layout build_index derives from the descriptor's own counts, the
 // class table must add up, and the CSR offset arrays and window list inside the payload must stay inside their
-// sections.  (Member VALUES are not scanned: that is O(M); a sample index >= N inside a section can still not leave
-// the accumulator, because every kernel checks rows against the owned block and columns against the bands' extent.)
+// sections.  Then the member VALUES are scanned (validate_members, all host threads): the kernels check a row against the
+// owned block but add a column to the row's base as it comes, so a cell address is only as good as the member lists --
+// every list strictly ascending below N, every pair of a row inside that row's band, every Gram colour inside its window.
+// The member values of a blob whose tables validate_blob has already checked.
+static const char* validate_members(const IndexDesc& d, const uint8_t* P) {
+    const uint64_t N = d.n_samples;
+    const uint32_t* blo = reinterpret_cast<const uint32_t*>(P + d.off_band_lo);
+    const uint32_t* bhi = reinterpret_cast<const uint32_t*>(P + d.off_band_hi);
+    const uint64_t T = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    // (a thread per 2048 colours at most: the 63 size classes of a small index are not worth 63 x 16 thread starts)
+    auto par = [&](uint64_t n, const std::function<void(int, uint64_t, uint64_t)>& fn) { parallel_chunks(n, (int)std::min<uint64_t>(T, n / 2048 + 1), fn); };
+    std::atomic<int> bad{0};  // 1: a list is not strictly ascending below N, 2: a pair outside its row's band, 3: a Gram colour outside its window
+    // one colour of s members, get(i) = compact id: row get(i) pairs with the columns get(i + 1) .. get(s - 1)
+    auto check = [&](auto&& get, uint64_t s) -> int {
+        if (s == 0) return 0;
+        const uint64_t last = get(s - 1);
+        if (last >= N) return 1;
+        uint64_t prev = get(0);
+        if (s > 1 && prev >= last) return 1;
+        for (uint64_t i = 1; i < s; i++) {
+            const uint64_t m = get(i);
+            if (m <= prev || m > last) return 1;           // (so prev < last < N before it indexes the bands)
+            if (blo[prev] > m || bhi[prev] <= last) return 2;
+            prev = m;
+        }
+        return 0;
+    };
+    auto note = [&](int why) { if (why) { int z = 0; bad.compare_exchange_strong(z, why); } };
+    for (uint32_t sz = 2; sz <= kSmallMax; sz++) {
+        const SmallClass& sc = d.cls[sz];
+        const uint8_t* sec = P + d.off_small_members;
+        const uint64_t bits = d.packed_bits;
+        par(sc.n, [&](int, uint64_t b, uint64_t e) {
+            for (uint64_t c = b; c < e && !bad; c++) {
+                const uint64_t e0 = sc.member_off + c * sz;
+                note(check([&](uint64_t i) { return (uint64_t)blob_member(sec, bits, e0 + i); }, sz));
+            }
+        });
+    }
+    {
+        const uint64_t* off = reinterpret_cast<const uint64_t*>(P + d.off_mid_offsets);
+        const uint32_t* szs = reinterpret_cast<const uint32_t*>(P + d.off_mid_sizes);
+        const uint8_t* sec = P + d.off_mid_members;
+        par(d.n_mid_colors, [&](int, uint64_t b, uint64_t e) {
+            for (uint64_t c = b; c < e && !bad; c++)
+                note(check([&](uint64_t i) { return (uint64_t)blob_member(sec, d.member_bits, off[c] + i); }, szs[c]));
+        });
+    }
+    {
+        const uint64_t* off = reinterpret_cast<const uint64_t*>(P + d.off_zero_offsets);
+        const uint8_t* sec = P + d.off_zero_members;
+        par(d.n_zero_colors, [&](int, uint64_t b, uint64_t e) {
+            for (uint64_t c = b; c < e && !bad; c++)
+                note(check([&](uint64_t i) { return (uint64_t)blob_member(sec, d.member_bits, off[c] + i); }, off[c + 1] - off[c]));
+        });
+    }
+    const GramWin* gw = reinterpret_cast<const GramWin*>(P + d.off_gram_wins);
+    const uint64_t* goff = reinterpret_cast<const uint64_t*>(P + d.off_gram_offsets);
+    if (!d.gram_form) {
+        const uint8_t* sec = P + d.off_gram_members;
+        const uint64_t bits = gram_member_bits(d);
+        parallel_chunks(d.n_gram_wins, (int)T, [&](int, uint64_t wb, uint64_t we) {
+            for (uint64_t w = wb; w < we && !bad; w++) {
+                const uint64_t x0 = gw[w].x0, add = d.gram_rel_bits ? x0 : 0, stride = gram_win_stride(gw[w]);
+                for (uint64_t c = gw[w].c0; c < gw[w].c0 + gw[w].n && !bad; c++) {
+                    const uint64_t sz = goff[c + 1] - goff[c];
+                    auto get = [&](uint64_t i) { return (uint64_t)blob_member(sec, bits, goff[c] + i) + add; };
+                    note(check(get, sz));
+                    if (sz && !bad && (get(0) < x0 || get(sz - 1) - x0 >= stride)) note(3);
+                }
+            }
+        });
+        if (!d.gram_rel_bits)  // colours no window names are not run by K4, but the shard builder walks them
+            par(d.n_gram_colors, [&](int, uint64_t b, uint64_t e) {
+                for (uint64_t c = b; c < e && !bad; c++)
+                    note(check([&](uint64_t i) { return (uint64_t)blob_member(sec, bits, goff[c] + i); }, goff[c + 1] - goff[c]));
+            });
+    } else {
+        // bitmap form: a colour's list is read back from the rows of its K-block (ascending by construction); bits of
+        // colours past the window's last one would be multiplied with weights that are not theirs
+        const uint32_t* bitmap = reinterpret_cast<const uint32_t*>(P + d.off_gram_members);
+        std::vector<std::pair<uint32_t, uint32_t>> kbs;
+        for (uint64_t w = 0; w < d.n_gram_wins; w++)
+            for (uint32_t kb = 0; kb < ((uint64_t)gw[w].n + kGramKBlock - 1) / kGramKBlock; kb++) kbs.emplace_back((uint32_t)w, kb);
+        parallel_chunks(kbs.size(), (int)T, [&](int, uint64_t b, uint64_t e) {
+            std::vector<uint32_t> lists[kGramKBlock];
+            for (uint64_t q = b; q < e && !bad; q++) {
+                const GramWin& g = gw[kbs[q].first];
+                const uint64_t kb = kbs[q].second, kn = std::min<uint64_t>(kGramKBlock, g.n - kb * kGramKBlock);
+                const uint32_t stride = gram_win_stride(g);
+                const uint32_t* rows = bitmap + 4 * (goff[kbs[q].first] + kb * stride);
+                for (auto& l : lists) l.clear();
+                for (uint32_t x = 0; x < stride; x++)
+                    for (uint32_t wd = 0; wd < 4; wd++)
+                        for (uint32_t v = rows[4 * (uint64_t)x + wd]; v; v &= v - 1) lists[32 * wd + (uint32_t)__builtin_ctz(v)].push_back(g.x0 + x);
+                for (uint64_t k = 0; k < kGramKBlock && !bad; k++) {
+                    if (k >= kn) { if (!lists[k].empty()) note(3); continue; }
+                    const std::vector<uint32_t>& l = lists[k];
+                    note(check([&](uint64_t i) { return (uint64_t)l[i]; }, l.size()));
+                }
+            }
+        });
+    }
+    switch (bad.load()) {
+        case 0: return nullptr;
+        case 1: return "a member list is not strictly ascending below the sample count";
+        case 2: return "a member pair lies outside its row's band";
+        default: return "a Gram colour leaves its window";
+    }
+}
+
 static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t payload_bytes) {
     if (d.magic != kIndexMagic) return "wrong magic";
     if (d.n_samples > 0x7FFFFFFFull) return "more than 2^31 samples";
@@ -1253,6 +1375,10 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
             if (bhi[i] < blo[i] || bhi[i] > N || bs[i + 1] != bs[i] + (bhi[i] - blo[i]) || rb[i] != bs[i] - blo[i]) return "row band tables";
         if (N && bs[N] != d.band_cells) return "row band tables";
     }
+    {   // compact index -> sample id is the ascending order of the ids (build_index's compaction)
+        const uint32_t* sid = reinterpret_cast<const uint32_t*>(P + d.off_sample_ids);
+        for (uint64_t i = 1; i < N; i++) if (sid[i] <= sid[i - 1]) return "sample ids are not ascending";
+    }
     uint64_t nc = 0, nm = 0;
     for (uint32_t s = 2; s <= kSmallMax; s++) {
         const SmallClass& c = d.cls[s];
@@ -1260,6 +1386,7 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
         if (c.s != s || c.n > d.n_small_colors || c.member_off > d.n_small_members || c.member_off + c.n * s > d.n_small_members ||
             c.weight_off + c.n > d.n_small_colors)
             return "a size class leaves its section";
+        if (c.pairs != s * (s - 1) / 2 || c.magic != (uint32_t)(((1ull << 32) + c.pairs - 1) / c.pairs)) return "a size class has the wrong pair count";
         nc += c.n;
         nm += c.n * s;
     }
@@ -1272,14 +1399,29 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     if (!monotone(d.off_mid_offsets, d.n_mid_colors, d.n_mid_members_padded)) return "mid offsets";
     if (!monotone(d.off_zero_offsets, d.n_zero_colors, d.n_zero_members)) return "zero-weight offsets";
     if (!d.gram_form && !monotone(d.off_gram_offsets, d.n_gram_colors, d.n_gram_members)) return "Gram offsets";
+    {   // a mid colour: its size fits between its offsets, it starts on 8 members (16 bytes: K2 fetches rows with bulk copies)
+        const uint64_t* mo = reinterpret_cast<const uint64_t*>(P + d.off_mid_offsets);
+        const uint32_t* ms = reinterpret_cast<const uint32_t*>(P + d.off_mid_sizes);
+        for (uint64_t c = 0; c < d.n_mid_colors; c++)
+            if (ms[c] < 2 || ms[c] > mo[c + 1] - mo[c] || (mo[c] & 7)) return "a mid colour does not fit its offsets";
+    }
     const MidItem* mi = reinterpret_cast<const MidItem*>(P + d.off_mid_items);
-    for (uint64_t i = 0; i < d.n_mid_items; i++) if (mi[i].color >= d.n_mid_colors) return "a mid item names a colour that does not exist";
+    {   // a K2 item: a tile of its colour with at least one row (positions; K2 takes min(a0 + kMidRows, s - 1, b0 + kMidCols - 1) - a0 rows)
+        const uint32_t* ms = reinterpret_cast<const uint32_t*>(P + d.off_mid_sizes);
+        for (uint64_t i = 0; i < d.n_mid_items; i++) {
+            if (mi[i].color >= d.n_mid_colors) return "a mid item names a colour that does not exist";
+            const uint64_t sz = ms[mi[i].color], b0 = mi[i].b0, a0 = mi[i].a0;
+            if (b0 >= sz || b0 % kMidCols || a0 % kMidRows || a0 >= std::min<uint64_t>(sz - 1, b0 + kMidCols - 1)) return "a mid item is not a tile of its colour";
+        }
+    }
     const GramWin* gw = reinterpret_cast<const GramWin*>(P + d.off_gram_wins);
     for (uint64_t i = 0; i < d.n_gram_wins; i++)
         if (gw[i].c0 + gw[i].n > d.n_gram_colors || gw[i].width == 0 || gw[i].width % kGramTile || gw[i].width > kGramMaxSamples + kGramTile ||
             gw[i].extent > gw[i].width || (d.gram_rel_bits && gw[i].width > (1ull << d.gram_rel_bits)) ||
             (d.gram_rel_bits && gw[i].c0 != (i ? gw[i - 1].c0 + gw[i - 1].n : 0)))
             return "a Gram window is inconsistent";
+    for (uint64_t i = 0; i < d.n_gram_wins; i++)
+        if (gw[i].x0 >= N || (gw[i].extent && (uint64_t)gw[i].x0 + gw[i].extent > N)) return "a Gram window is inconsistent";
     if (d.gram_form) {  // the windows' bitmaps lie back to back, in window order, and colours are numbered in window order
         const uint64_t* wr = reinterpret_cast<const uint64_t*>(P + d.off_gram_offsets);
         uint64_t row = 0, c = 0;
@@ -1291,7 +1433,7 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
         if (wr[d.n_gram_wins] != row || row != d.gram_bitmap_rows || c != d.n_gram_colors) return "Gram bitmap rows do not match the windows";
     }
     if (d.shard_world && (d.shard_rank >= d.shard_world || d.shard_rb > d.shard_re || d.shard_re > N)) return "shard fields";
-    return nullptr;
+    return validate_members(d, P);
 }
 }  // namespace ksb
 

@@ -6,6 +6,7 @@
 #   SAN=thread tests/sanitize_cpu.sh [scratch_dir]   -> the same under ThreadSanitizer (the loader, the writers and the table
 #                                                       reader are multithreaded); reports inside libtorch's gloo are not ours,
 #                                                       and the tests that run the reference binary as a child fail under the preload
+#   FUZZ=1 tests/sanitize_cpu.sh [scratch_dir]      -> after the suite, tests/fuzz_host.py (damaged blobs, index files, tables) on the same build
 set -euo pipefail
 ROOT="$(cd "$(dirname "$0")/.." && pwd)"
 DST="${1:-$(mktemp -d /tmp/ksb_asan.XXXXXX)}"
@@ -31,3 +32,9 @@ tail -n 3 "$LOG"
 echo "sanitizer reports: $(grep -c -E 'runtime error|AddressSanitizer|WARNING: ThreadSanitizer' "$LOG" || true)," \
      "lines naming libkspider_b200: $(grep -c libkspider_b200 "$LOG" || true) (log: $LOG)"
 grep -E 'runtime error|AddressSanitizer' "$LOG" | sort | uniq -c | sort -rn | head -n 40 || true
+if [ "${FUZZ:-0}" != 0 ]; then
+    LD_PRELOAD="$PRE" TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" \
+    ASAN_OPTIONS=detect_leaks=0:halt_on_error=1 UBSAN_OPTIONS=print_stacktrace=1:halt_on_error=0 \
+        python tests/fuzz_host.py "${FUZZ_SEED:-0}" > "$DST/fuzz_host.log" 2>&1 || echo "fuzz_host.py did not finish: see $DST/fuzz_host.log"
+    grep -E 'accepted|runtime error|AddressSanitizer|ThreadSanitizer' "$DST/fuzz_host.log" | head -n 20 || true
+fi

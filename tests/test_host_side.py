@@ -538,3 +538,134 @@ def test_from_blob_checks_the_bitmap_form_and_the_row_tables(built_lib, monkeypa
     bad[whits[0] + 1] += np.uint64(8)
     with pytest.raises(KsbError):
         Index.from_blob(desc, np.frombuffer(bad.tobytes(), dtype=np.uint8))
+
+
+def _blob_fields(desc: bytes):
+    """The u64 fields of ksb::IndexDesc behind its size-class table (ksb_common.hpp), by name."""
+    names = ("off_totals off_sample_ids off_row_updates off_band_lo off_band_hi band_cells off_bandstart off_rowbase "
+             "off_small_members off_small_weights off_mid_offsets off_mid_sizes off_mid_members off_mid_weights off_mid_items "
+             "n_mid_items n_mid_members_padded off_zero_offsets off_zero_members n_gram_colors n_gram_members n_gram_updates "
+             "gram_planes gram_min_size off_gram_offsets off_gram_members off_gram_weights off_gram_wins n_gram_wins "
+             "n_small_updates n_gram_macs n_gram_cells member_bits packed_bits weight_bits gram_rel_bits gram_form "
+             "gram_bitmap_rows shard_world shard_rank shard_rb shard_re payload_bytes").split()
+    head, cls = 14 * 8, 65 * 40
+    assert len(desc) == head + cls + 8 * len(names), "IndexDesc changed: update this table"
+    tail = np.frombuffer(desc[head + cls:], dtype=np.uint64)
+    f = {k: int(v) for k, v in zip(names, tail)}
+    # size classes: {s, pairs, magic, pad} u32, {n, member_off, weight_off} u64
+    f["cls"] = [dict(zip(("s", "pairs", "magic", "pad"), np.frombuffer(desc[head + 40 * s:head + 40 * s + 16], np.uint32).tolist()),
+                     **dict(zip(("n", "member_off", "weight_off"), np.frombuffer(desc[head + 40 * s + 16:head + 40 * s + 40], np.uint64).tolist())))
+                for s in range(65)]
+    f["cls_at"] = head
+    return f
+
+
+def test_from_blob_scans_the_member_values(built_lib, monkeypatch):
+    """The kernels check a row against the owned block and add a column to the row's base as it comes, and the shard
+    builder indexes the sample table with what it reads: ksb_index_from_blob refuses a blob with a member list that is not
+    strictly ascending below N, a pair outside its row's band, a mid colour or K2 item that does not fit its offsets, sample
+    ids out of order, a size class with the wrong pair count, a Gram bit of a colour the window does not have."""
+    from kspider_b200 import Index
+    from kspider_b200.capi import KsbError
+    rng = np.random.default_rng(33)
+    n = 5000
+    ids = np.arange(1, n + 1, dtype=np.uint32)
+
+    def refused(desc, payload, what):
+        with pytest.raises(KsbError) as e:
+            Index.from_blob(bytes(desc), payload)
+        assert what in str(e.value), str(e.value)
+
+    # ---- (A) small, mid and zero-weight colours, no Gram path; the last sample is in no colour
+    cols, w = [], []
+    for _ in range(500):
+        cols.append(np.sort(rng.choice(n - 1, size=5, replace=False))); w.append(int(rng.integers(1, 50)))
+    for _ in range(3):
+        cols.append(np.sort(rng.choice(n - 1, size=300, replace=False))); w.append(7)
+    for _ in range(20):
+        cols.append(np.sort(rng.choice(n - 1, size=4, replace=False))); w.append(0)
+    offsets = np.concatenate([[0], np.cumsum([c.size for c in cols])]).astype(np.uint64)
+    monkeypatch.setenv("KSPIDER_GRAM", "off")
+    idx = Index.from_csr(offsets=offsets, members=ids[np.concatenate(cols)], weights=np.array(w, np.uint32), total_ids=ids,
+                         total_vals=np.full(n, 10 ** 6, dtype=np.uint32))
+    info = idx.info
+    assert info.n_mid_colors == 3 and info.n_zero_colors == 20 and info.n_small_colors == 500 and info.n_gram_colors == 0
+    desc, payload = idx.descriptor(), idx.payload().copy()
+    f = _blob_fields(desc)
+    assert f["packed_bits"] == 16 and f["member_bits"] == 16
+    Index.from_blob(desc, payload)
+
+    def u16(p, off):  # view of a u16 section from byte `off` on
+        return p[off:].view(np.uint16) if (p.size - off) % 2 == 0 else p[off:-1].view(np.uint16)
+
+    c5 = f["cls"][5]
+    assert c5["n"] == 500
+    p = payload.copy(); m = u16(p, f["off_small_members"])[c5["member_off"]:]
+    m[0], m[1] = m[1], m[0]
+    refused(desc, p, "ascending")
+    p = payload.copy(); m = u16(p, f["off_small_members"])[c5["member_off"]:]
+    m[5 + 2] = m[5 + 1]                          # a sample twice in one colour
+    refused(desc, p, "ascending")
+    p = payload.copy(); m = u16(p, f["off_small_members"])[c5["member_off"]:]
+    m[4] = n - 1                                 # ascending, below N, but no row's band reaches the last sample
+    refused(desc, p, "band")
+    p = payload.copy(); m = u16(p, f["off_small_members"])[c5["member_off"]:]
+    m[4] = n                                     # not a sample
+    refused(desc, p, "ascending")
+    p = payload.copy(); z = u16(p, f["off_zero_members"])
+    z[3] = n - 1
+    refused(desc, p, "band")
+    # mid colours: 300 members in 304 slots
+    p = payload.copy(); p[f["off_mid_sizes"]:].view(np.uint32)[1] = 400
+    refused(desc, p, "mid colour")
+    p = payload.copy(); p[f["off_mid_sizes"]:].view(np.uint32)[1] = 302      # fits the slots, reads the padding as members
+    refused(desc, p, "")
+    p = payload.copy(); p[f["off_mid_sizes"]:].view(np.uint32)[2] = 1
+    refused(desc, p, "mid colour")
+    p = payload.copy(); mm = u16(p, f["off_mid_members"]); mm[10], mm[11] = mm[11], mm[10]
+    refused(desc, p, "ascending")
+    assert f["n_mid_items"] == 3 * 2             # columns [0, 256) x rows [0, 255), columns [256, 300) x rows [0, 299)
+    for word, val in ((2, 512), (2, 8), (1, 512), (1, 128), (0, 3)):   # {color, b0, a0, pad}
+        p = payload.copy(); p[f["off_mid_items"]:].view(np.uint32)[4 * 1 + word] = val
+        refused(desc, p, "mid item")
+    p = payload.copy(); s_ = p[f["off_sample_ids"]:].view(np.uint32); s_[10], s_[11] = s_[11], s_[10]
+    refused(desc, p, "sample ids")
+    d = bytearray(desc); at = f["cls_at"] + 40 * 5 + 4          # cls[5].pairs
+    d[at:at + 4] = (11).to_bytes(4, "little")
+    refused(d, payload, "pair count")
+    # what the scan does not look at can change: a weight, a total
+    p = payload.copy(); p[f["off_totals"]:].view(np.uint32)[7] = 123
+    assert Index.from_blob(desc, p).info.n_samples == n
+
+    # ---- (B) Gram bitmaps: one window of 130 colours (two K-blocks, the second with two colours)
+    # (compact samples; every colour spans sample 128 and stays inside [64, 192): one window of the 128-wide grid level)
+    cols = [np.arange(100, 150)]                                   # colour A: its rows pair with nothing past 170
+    for _ in range(128):
+        cols.append(np.sort(np.concatenate([[100, 170], rng.choice(np.arange(101, 170), size=38, replace=False)])))
+    cols.append(np.concatenate([np.arange(64, 73), np.arange(180, 192)]))   # the only colour that reaches the window's last samples
+    offsets = np.concatenate([[0], np.cumsum([c.size for c in cols])]).astype(np.uint64)
+    monkeypatch.setenv("KSPIDER_GRAM", "16")
+    monkeypatch.setenv("KSPIDER_GRAM_FORM", "bitmap")
+    idx = Index.from_csr(offsets=offsets, members=ids[np.concatenate(cols)], weights=np.full(len(cols), 3, np.uint32), total_ids=ids,
+                         total_vals=np.full(n, 10 ** 6, dtype=np.uint32))
+    assert idx.info.gram_form & 1 and idx.info.n_gram_windows == 1 and idx.info.n_gram_colors == 130
+    desc, payload = idx.descriptor(), idx.payload().copy()
+    f = _blob_fields(desc)
+    Index.from_blob(desc, payload)
+    win = payload[f["off_gram_wins"]:f["off_gram_wins"] + 24]
+    x0, width, extent = (int(v) for v in win[12:24].view(np.uint32))
+    assert (x0, extent) == (64, 128) and int(win[8:12].view(np.uint32)[0]) == 130
+    bits = payload[f["off_gram_members"]:f["off_gram_members"] + 16 * 2 * extent].view(np.uint32).reshape(2, extent, 4)
+    # the K-block and bit of colour A: the only column with exactly the rows of samples 100..149
+    col_a = [(kb, k) for kb in range(2) for k in range(128)
+             if np.array_equal(np.flatnonzero((bits[kb, :, k // 32] >> np.uint32(k % 32)) & 1), np.arange(36, 86))]
+    assert len(col_a) == 1
+    kb, k = col_a[0]
+    p = payload.copy()
+    b = p[f["off_gram_members"]:f["off_gram_members"] + 16 * 2 * extent].view(np.uint32).reshape(2, extent, 4)
+    b[kb, 127, k // 32] |= np.uint32(1 << (k % 32))                 # sample 191 joins colour A: (100, 191) is outside row 100's band
+    refused(desc, p, "band")
+    p = payload.copy()
+    b = p[f["off_gram_members"]:f["off_gram_members"] + 16 * 2 * extent].view(np.uint32).reshape(2, extent, 4)
+    b[1, 5, 1] |= np.uint32(1 << 9)                                  # K-block 1 holds two colours: bit 41 is nobody's
+    refused(desc, p, "window")
