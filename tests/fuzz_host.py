@@ -102,3 +102,27 @@ for it in range(1500):
             else: n_bad += 1
     L.ksb_sidecar_matches(side.encode(), tsv.encode())
 print("tables accepted", n_ok, "refused", n_bad)
+# --- 4. the colored_kDataFrame file set (ksb_index_load_colored parses all five files on the host before any device work)
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CK = [".phmap", "colors.intvectors", "colorTableConfig.json", ".namesMap", ".extra"]
+ck0 = {suf: open(os.path.join(GOLD, "ckf_small" + suf), "rb").read() for suf in CK}
+cprefix = os.path.join(td, "ck")
+codes = {}
+for it in range(1500):
+    suf = CK[int(rng.integers(0, len(CK)))]
+    b = bytearray(ck0[suf])
+    kind = int(rng.integers(0, 4))
+    if kind == 0 and len(b):
+        for _ in range(int(rng.integers(1, 5))): b[int(rng.integers(0, len(b)))] = int(rng.integers(0, 256))
+    elif kind == 1:
+        b = b[: int(rng.integers(0, len(b) + 1))]
+    elif kind == 2 and len(b) > 8:
+        a = int(rng.integers(0, len(b) - 8)); b[a:a + 8] = struct.pack("<Q", [0, 2**32, 2**64 - 1, 2**31, int(rng.integers(0, 2**20))][int(rng.integers(0, 5))])
+    elif len(b):   # a digit / separator of the text files changed
+        for _ in range(int(rng.integers(1, 4))): b[int(rng.integers(0, len(b)))] = [32, 10, 48, 57, 45, 9, 0][int(rng.integers(0, 7))]
+    for s_, data in ck0.items(): open(cprefix + s_, "wb").write(bytes(b) if s_ == suf else data)
+    h = C.c_void_p()
+    rc = L.ksb_index_load_colored(cprefix.encode(), 2, -1, C.byref(h))
+    codes[rc] = codes.get(rc, 0) + 1
+    if rc == 0: L.ksb_index_free(h)
+print("colored file sets by return code", dict(sorted(codes.items())))
