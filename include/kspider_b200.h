@@ -197,7 +197,8 @@ void ksb_index_free(ksb_index* ix);
 /* Copies the blob to the device (timed: t.h2d_ms) and allocates the owned triangle block. */
 int ksb_upload(const ksb_index* ix, const ksb_opts* opts, ksb_device** out);
 /* Adopts a blob that is ALREADY in device memory (e.g. received by an NCCL broadcast).  The
- * descriptor is host memory.  The device buffer must outlive the ksb_device. */
+ * descriptor is host memory.  The device buffer must outlive the ksb_device.  Nothing in device memory can be checked from
+ * here: the payload is TRUSTED to be what ksb_index_payload of this build produced (ksb_index_from_blob is the checking door). */
 int ksb_adopt_device_payload(const void* descriptor, uint64_t descriptor_bytes, const void* d_payload,
                              uint64_t payload_bytes, const ksb_opts* opts, ksb_device** out);
 /* Clears the owned block and runs the pair-emission kernels on `stream` (a cudaStream_t passed as
