@@ -1541,7 +1541,7 @@ int ksb_blob_row_cuts(const void* descriptor, uint64_t descriptor_bytes, const v
     ksb::IndexDesc d;
     std::memcpy(&d, descriptor, sizeof d);
     if (d.magic != ksb::kIndexMagic || d.payload_bytes != payload_bytes || (!payload && payload_bytes) ||
-        d.off_row_updates + 8 * d.n_samples > payload_bytes) { ksb::set_error("ksb_blob_row_cuts: descriptor does not match the payload"); return KSB_ERR_ARG; }
+        d.n_samples > payload_bytes / 8 || d.off_row_updates > payload_bytes - 8 * d.n_samples || (d.off_row_updates & 7)) { /* (no sum that can wrap) */ ksb::set_error("ksb_blob_row_cuts: descriptor does not match the payload"); return KSB_ERR_ARG; }
     ksb::row_cuts(reinterpret_cast<const uint64_t*>(static_cast<const uint8_t*>(payload) + d.off_row_updates), d.n_samples,
                   d.n_updates, world, cuts_out);
     return KSB_OK;

@@ -669,3 +669,23 @@ def test_from_blob_scans_the_member_values(built_lib, monkeypatch):
     b = p[f["off_gram_members"]:f["off_gram_members"] + 16 * 2 * extent].view(np.uint32).reshape(2, extent, 4)
     b[1, 5, 1] |= np.uint32(1 << 9)                                  # K-block 1 holds two colours: bit 41 is nobody's
     refused(desc, p, "window")
+
+
+def test_blob_row_cuts_refuses_a_descriptor_that_points_outside_the_payload(built_lib):
+    """ksb_blob_row_cuts reads the per-row update counts straight out of a (descriptor, payload) pair: a sample count or
+    a section offset that would leave the payload -- also one large enough to wrap the sum -- is an argument error."""
+    from kspider_b200 import Index
+    from kspider_b200.capi import KSB_ERR_ARG
+    csr = random_csr(5, 60, 400, 1, 9)
+    idx = Index.from_csr(**csr)
+    desc, payload = idx.descriptor(), idx.payload().copy()
+    f = _blob_fields(desc)
+    cuts = np.zeros(4, np.uint64)
+    assert built_lib.ksb_blob_row_cuts(desc, len(desc), payload.ctypes.data, payload.size, 3, cuts.ctypes.data) == 0
+    assert cuts[0] == 0 and cuts[-1] == idx.info.n_samples and np.all(np.diff(cuts.astype(np.int64)) >= 0)
+    names_at = 14 * 8 + 65 * 40
+    for field_at, val in ((8, 2 ** 61 + 3), (8, payload.size), (names_at + 8 * 2, 2 ** 64 - 8), (names_at + 8 * 2, payload.size),
+                          (names_at + 8 * 2, f["off_row_updates"] + 4)):      # n_samples; off_row_updates
+        d = bytearray(desc)
+        d[field_at:field_at + 8] = int(val).to_bytes(8, "little")
+        assert built_lib.ksb_blob_row_cuts(bytes(d), len(d), payload.ctypes.data, payload.size, 3, cuts.ctypes.data) == KSB_ERR_ARG
