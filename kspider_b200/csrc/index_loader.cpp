@@ -1416,10 +1416,11 @@ static const char* validate_blob(const IndexDesc& d, const uint8_t* P, uint64_t 
     }
     const GramWin* gw = reinterpret_cast<const GramWin*>(P + d.off_gram_wins);
     for (uint64_t i = 0; i < d.n_gram_wins; i++)
-        if (gw[i].c0 + gw[i].n > d.n_gram_colors || gw[i].width == 0 || gw[i].width % kGramTile || gw[i].width > kGramMaxSamples + kGramTile ||
+        if (gw[i].c0 > d.n_gram_colors || gw[i].n > d.n_gram_colors - gw[i].c0 || gw[i].width == 0 || gw[i].width % kGramTile || gw[i].width > kGramMaxSamples + kGramTile ||
             gw[i].extent > gw[i].width || (d.gram_rel_bits && gw[i].width > (1ull << d.gram_rel_bits)) ||
-            (d.gram_rel_bits && gw[i].c0 != (i ? gw[i - 1].c0 + gw[i - 1].n : 0)))
+            gw[i].c0 != (i ? gw[i - 1].c0 + gw[i - 1].n : 0))  // the windows partition the Gram colours, in order
             return "a Gram window is inconsistent";
+    if ((d.n_gram_wins ? gw[d.n_gram_wins - 1].c0 + gw[d.n_gram_wins - 1].n : 0) != d.n_gram_colors) return "a Gram window is inconsistent";
     for (uint64_t i = 0; i < d.n_gram_wins; i++)
         if (gw[i].x0 >= N || (gw[i].extent && (uint64_t)gw[i].x0 + gw[i].extent > N)) return "a Gram window is inconsistent";
     if (d.gram_form) {  // the windows' bitmaps lie back to back, in window order, and colours are numbered in window order
