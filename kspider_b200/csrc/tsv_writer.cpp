@@ -141,9 +141,10 @@ struct TextBuf {  // per-thread text of one batch; never value-initialised (std:
     }
 };
 
-static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* base, int threads) {
+// fmt(first, last, out) writes the text of rows [first, last) at `out` (at most row_max bytes each) and returns its end
+template <class Fmt>
+static int write_text_batches(uint64_t n, int fd, uint64_t* base, int threads, size_t row_max, const Fmt& fmt) {
     const uint64_t kBatch = 1ull << 22;
-    const size_t kRowMax = 96;  // 10 + 10 + 20 digits, 3 x 16 for the floats, 6 separators
     if (threads < 1) threads = 1;
     std::vector<TextBuf> bufs[2];
     bufs[0] = std::vector<TextBuf>(threads);
@@ -163,18 +164,8 @@ static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* ba
         for (auto& s : bs) s.len = 0;
         parallel_chunks(bn, threads, [&](int t, uint64_t b, uint64_t e) {
             TextBuf& s = bs[t];
-            if (!s.reserve((size_t)(e - b) * kRowMax + 16)) { failed[t] = 1; return; }
-            char* line = s.p;
-            for (uint64_t i = b; i < e; i++) {
-                const ksb_record& r = rec[b0 + i];
-                line += u32_to_dec(r.source_1, line); *line++ = '\t';
-                line += u32_to_dec(r.source_2, line); *line++ = '\t';
-                line += u64_to_dec(r.shared_kmers, line); *line++ = '\t';
-                line += format_float(r.min_containment, line); *line++ = '\t';
-                line += format_float(r.avg_containment, line); *line++ = '\t';
-                line += format_float(r.max_containment, line); *line++ = '\n';
-            }
-            s.len = (size_t)(line - s.p);
+            if (!s.reserve((size_t)(e - b) * row_max + 16)) { failed[t] = 1; return; }
+            s.len = (size_t)(fmt(b0 + b, b0 + e, s.p) - s.p);
         });
         for (int t = 0; t < threads; t++)
             if (failed[t]) rc = KSB_ERR_NOMEM;
@@ -203,6 +194,22 @@ static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* ba
         if (writer[q].joinable()) { writer[q].join(); if (wrc[q] != KSB_OK) rc = wrc[q]; }
     if (rc == KSB_OK) *base = at;
     return rc;
+}
+
+static int write_records(const ksb_record* rec, uint64_t n, int fd, uint64_t* base, int threads) {
+    const size_t kRowMax = 96;  // 10 + 10 + 20 digits, 3 x 16 for the floats, 6 separators
+    return write_text_batches(n, fd, base, threads, kRowMax, [rec](uint64_t first, uint64_t last, char* line) {
+        for (uint64_t i = first; i < last; i++) {
+            const ksb_record& r = rec[i];
+            line += u32_to_dec(r.source_1, line); *line++ = '\t';
+            line += u32_to_dec(r.source_2, line); *line++ = '\t';
+            line += u64_to_dec(r.shared_kmers, line); *line++ = '\t';
+            line += format_float(r.min_containment, line); *line++ = '\t';
+            line += format_float(r.avg_containment, line); *line++ = '\t';
+            line += format_float(r.max_containment, line); *line++ = '\n';
+        }
+        return line;
+    });
 }
 
 static int write_tsv_rows(const ksb_record* rec, uint64_t n, const char* path, int threads, bool append) {
@@ -258,6 +265,12 @@ int ksb_format_double_repr(double v, char* buf) {
     if (std::signbit(v)) { buf[n++] = '-'; v = -v; }
     if (std::isinf(v)) { std::memcpy(buf + n, "inf", 3); return n + 3; }
     if (v == 0.0) { std::memcpy(buf + n, "0.0", 3); return n + 3; }
+    if (v >= 1e-4 && v < 1e16) {  // repr's fixed range: the shortest round-trip digits in fixed notation are what to_chars(fixed) writes
+        char* const b = buf + n;
+        char* e = std::to_chars(b, b + 30, v, std::chars_format::fixed).ptr;
+        if (!std::memchr(b, '.', (size_t)(e - b))) { *e++ = '.'; *e++ = '0'; }
+        return (int)(e - buf);
+    }
     char sci[40];
     const auto res = std::to_chars(sci, sci + sizeof sci, v, std::chars_format::scientific);  // d[.ddd]e[+-]XX, shortest
     char digits[24];
@@ -297,29 +310,21 @@ int ksb_format_double_repr(double v, char* buf) {
 // `P_kSpider_pairwise.ani_col.tsv` (ks_pairwise.py:33,64-80): header "avg_ani", one repr(float) per row.
 int ksb_write_ani_column(const double* ani, uint64_t n, const char* path, int host_threads) {
     if ((!ani && n) || !path) { ksb::set_error("ksb_write_ani_column: null argument"); return KSB_ERR_ARG; }
-    FILE* f = fopen(path, "wb");
-    if (!f) { ksb::set_error("cannot write %s: %s", path, strerror(errno)); return KSB_ERR_IO; }
-    int rc = fputs("avg_ani\n", f) < 0 ? KSB_ERR_IO : KSB_OK;
-    const int threads = host_threads < 1 ? 1 : host_threads;
-    std::vector<std::string> bufs(threads);
-    const uint64_t kBatch = 1ull << 21;
-    for (uint64_t b0 = 0; b0 < n && rc == KSB_OK; b0 += kBatch) {
-        const uint64_t bn = std::min(kBatch, n - b0);
-        ksb::parallel_chunks(bn, threads, [&](int t, uint64_t b, uint64_t e) {
-            std::string& s = bufs[t];
-            s.resize((e - b) * 32);
-            char* const base = &s[0];
-            char* line = base;
-            for (uint64_t i = b; i < e; i++) { line += ksb_format_double_repr(ani[b0 + i], line); *line++ = '\n'; }
-            s.resize((size_t)(line - base));
+    const int fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) { ksb::set_error("cannot write %s: %s", path, strerror(errno)); return KSB_ERR_IO; }
+    static const char kHeader[] = "avg_ani\n";
+    const size_t hl = sizeof(kHeader) - 1;
+    int rc = pwrite(fd, kHeader, hl, 0) == (ssize_t)hl ? KSB_OK : KSB_ERR_IO;
+    uint64_t base = hl;
+    // the pairwise TSV's writer: all threads format a batch while a writer thread puts the previous one into the file
+    if (rc == KSB_OK)
+        rc = ksb::write_text_batches(n, fd, &base, host_threads, 32, [ani](uint64_t first, uint64_t last, char* line) {
+            for (uint64_t i = first; i < last; i++) { line += ksb_format_double_repr(ani[i], line); *line++ = '\n'; }
+            return line;
         });
-        for (auto& s : bufs) {
-            if (!s.empty() && fwrite(s.data(), 1, s.size(), f) != s.size()) rc = KSB_ERR_IO;
-            s.clear();
-        }
-    }
-    if (fclose(f) != 0) rc = KSB_ERR_IO;
+    if (close(fd) != 0) rc = KSB_ERR_IO;
     if (rc == KSB_ERR_IO) ksb::set_error("write error on %s", path);
+    if (rc == KSB_ERR_NOMEM) ksb::set_error("out of host memory writing %s", path);
     return rc;
 }
 

@@ -41,6 +41,15 @@ def test_repr_formatter_matches_python(built_lib):
     vals = [0.0, -0.0, 1.0, 0.5, 1e-4, 9.999e-5, 1e-5, 1e16, 9.999999999999998e15, 1e15, 1e22, 1e-7, 0.1,
             0.30000000000000004, 1 / 3, 5e-324, 1.7976931348623157e308, float("inf"), float("-inf"), 100.0,
             0.9876543210987654, 1e100, 1.5e-100, 123.0, 1e21, 1e-310, 0.9999999999999999, 0.99]
+    # both ends of repr's fixed range from either side, integer-valued doubles up to 2^53 and past it, negatives
+    for e in range(-5, 18):
+        for toward in (0.0, 1e300):
+            x = 10.0 ** e
+            for _ in range(4):
+                vals += [x, -x]
+                x = math.nextafter(x, toward)
+    vals += [float(rng.randint(0, 10 ** 16)) for _ in range(2000)] + [rng.randint(1, 2 ** 53) / 2.0 ** rng.randint(0, 60) for _ in range(2000)]
+    vals += [4503599627370496.5, 9007199254740993.0, 9999999999999998.0, 123456789012345678.0, -0.25, -123456.789]
     for _ in range(100000):
         r = rng.random()
         if r < 0.5:
