@@ -126,3 +126,40 @@ for it in range(1500):
     codes[rc] = codes.get(rc, 0) + 1
     if rc == 0: L.ksb_index_free(h)
 print("colored file sets by return code", dict(sorted(codes.items())))
+# --- 5. ksb_index_from_csr on edge-shaped inputs (empty and one-member colours, zero weights, ids up to 2^32 - 1, a duplicate
+# member, offsets out of order); whatever it accepts must survive its own validator as a blob and as shards of 1, 2 and 5
+os.environ.pop("KSPIDER_GRAM", None); os.environ.pop("KSPIDER_GRAM_FORM", None)
+ok = bad = 0
+for it in range(int(os.environ.get('FUZZ_CSR', 150))):
+    nc = int(rng.integers(0, 40))
+    mode = int(rng.integers(0, 5))
+    hi = [8, 300, 70000, 2**20, 2**32][mode]
+    sizes = rng.integers(0, [6, 70, 200][int(rng.integers(0, 3))], nc)
+    if mode >= 3: sizes = np.minimum(sizes, 5)
+    cols = []
+    for s in sizes:
+        s = int(min(s, hi))
+        m = rng.choice(hi, size=s, replace=False) if hi <= 70000 else np.unique(rng.integers(0, hi, s, dtype=np.uint64))
+        if rng.random() < 0.02 and s > 1: m[0] = m[1]   # a duplicate: must be refused
+        cols.append(np.asarray(m, dtype=np.uint32))
+    offsets = np.concatenate([[0], np.cumsum([c.size for c in cols])]).astype(np.uint64)
+    members = np.concatenate(cols).astype(np.uint32) if cols else np.zeros(0, np.uint32)
+    weights = rng.integers(0, [2, 200, 2**32][int(rng.integers(0, 3))], nc, dtype=np.uint64).astype(np.uint32)
+    nt = int(rng.integers(0, 30))
+    tid = rng.integers(0, hi, nt, dtype=np.uint64).astype(np.uint32)
+    tv = rng.integers(0, 2**32, nt, dtype=np.uint64).astype(np.uint32)
+    if rng.random() < 0.03 and nc > 2: offsets[1], offsets[2] = offsets[2], offsets[1]
+    for env in ({}, {"KSPIDER_GRAM": "16"}, {"KSPIDER_GRAM": "16", "KSPIDER_GRAM_FORM": "csr"}):
+        os.environ.pop("KSPIDER_GRAM", None); os.environ.pop("KSPIDER_GRAM_FORM", None); os.environ.update(env)
+        try:
+            ix = Index.from_csr(offsets=offsets, members=members, weights=weights, total_ids=tid, total_vals=tv, host_threads=int(rng.integers(1, 5)))
+            i = ix.info
+            cp = Index.from_blob(ix.descriptor(), ix.payload())
+            for w in (1, 2, 5):
+                for r in range(w):
+                    sh = ix.shard(r, w, 2); Index.from_blob(sh.descriptor(), sh.payload())
+            ok += 1
+        except KsbError as e:
+            bad += 1
+            if "blob" in str(e): print("BLOB REFUSED", e, env, nc, mode); raise
+print("from_csr inputs accepted", ok, "refused", bad)

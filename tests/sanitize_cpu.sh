@@ -36,5 +36,5 @@ if [ "${FUZZ:-0}" != 0 ]; then
     LD_PRELOAD="$PRE" TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0" \
     ASAN_OPTIONS=detect_leaks=0:halt_on_error=1 UBSAN_OPTIONS=print_stacktrace=1:halt_on_error=0 \
         python tests/fuzz_host.py "${FUZZ_SEED:-0}" > "$DST/fuzz_host.log" 2>&1 || echo "fuzz_host.py did not finish: see $DST/fuzz_host.log"
-    grep -E 'accepted|return code|runtime error|AddressSanitizer|ThreadSanitizer' "$DST/fuzz_host.log" | head -n 20 || true
+    grep -E 'accepted|return code|BLOB REFUSED|runtime error|AddressSanitizer|ThreadSanitizer' "$DST/fuzz_host.log" | head -n 20 || true
 fi
